@@ -1,0 +1,440 @@
+"""oracle/pyoracle.py -- TEST INFRASTRUCTURE, not product code.
+
+ctypes/numpy front-ends for the two CPU checkers:
+
+* ``PortIndex``  -> oracle/liboracle_ivfflat.so, our plain-C restatement (ivfflat_oracle.c)
+* ``RefIndex``   -> oracle/_ref/libref_ivfflat.so, the UNMODIFIED reference compiled from
+                    /root/reference (ref_shim.cpp is only a C-ABI over its public C++ API)
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
+import this module. The product package (hnsw_ivf_b200) never does.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+METRIC_INNER_PRODUCT = 0
+METRIC_L2 = 1
+
+_f32p = C.POINTER(C.c_float)
+_i64p = C.POINTER(C.c_int64)
+
+
+def _f32(a):
+    a = np.ascontiguousarray(a, dtype=np.float32)
+    return a, a.ctypes.data_as(_f32p)
+
+
+def _i64(a):
+    a = np.ascontiguousarray(a, dtype=np.int64)
+    return a, a.ctypes.data_as(_i64p)
+
+
+# ------------------------------------------------------------------------------------------------
+# port (plain-C restatement)
+# ------------------------------------------------------------------------------------------------
+class OrcStats(C.Structure):
+    _fields_ = [("nq", C.c_size_t), ("nlist", C.c_size_t), ("ndis", C.c_size_t),
+                ("nheap_updates", C.c_size_t), ("quantization_time", C.c_double),
+                ("search_time", C.c_double)]
+
+
+_port = None
+
+
+def build_port():
+    subprocess.check_call(["make", "-s", "-C", _HERE, "port"])
+
+
+def port_lib():
+    global _port
+    if _port is None:
+        path = os.path.join(_HERE, "liboracle_ivfflat.so")
+        if not os.path.exists(path):
+            build_port()
+        L = C.CDLL(path)
+        L.orc_index_new.restype = C.c_void_p
+        L.orc_index_new.argtypes = [C.c_size_t, C.c_size_t, C.c_int]
+        L.orc_index_free.argtypes = [C.c_void_p]
+        L.orc_index_set_centroids.argtypes = [C.c_void_p, _f32p]
+        L.orc_index_list_size.restype = C.c_size_t
+        L.orc_index_list_size.argtypes = [C.c_void_p, C.c_size_t]
+        L.orc_index_list_codes.restype = _f32p
+        L.orc_index_list_codes.argtypes = [C.c_void_p, C.c_size_t]
+        L.orc_index_list_ids.restype = _i64p
+        L.orc_index_list_ids.argtypes = [C.c_void_p, C.c_size_t]
+        L.orc_index_ntotal.restype = C.c_int64
+        L.orc_index_ntotal.argtypes = [C.c_void_p]
+        L.orc_index_add_core.argtypes = [C.c_void_p, C.c_int64, _f32p, _i64p, _i64p]
+        L.orc_index_add_with_ids.argtypes = [C.c_void_p, C.c_int64, _f32p, _i64p]
+        L.orc_index_quantize.argtypes = [C.c_void_p, C.c_int64, _f32p, C.c_size_t, _f32p, _i64p]
+        L.orc_index_search_preassigned.restype = C.c_int
+        L.orc_index_search_preassigned.argtypes = [C.c_void_p, C.c_int64, _f32p, C.c_int64,
+                                                   C.c_size_t, _i64p, _f32p, _i64p,
+                                                   C.POINTER(OrcStats)]
+        L.orc_index_search.restype = C.c_int
+        L.orc_index_search.argtypes = [C.c_void_p, C.c_int64, _f32p, C.c_int64, C.c_size_t,
+                                       C.c_int, _f32p, _i64p, C.POINTER(OrcStats)]
+        L.orc_knn.argtypes = [C.c_int, _f32p, _f32p, C.c_size_t, C.c_size_t, C.c_size_t,
+                              C.c_size_t, _f32p, _i64p]
+        L.orc_merge_knn_results.argtypes = [C.c_int, C.c_size_t, C.c_size_t, C.c_int, _f32p,
+                                            _i64p, _f32p, _i64p]
+        L.orc_heap_heapify.argtypes = [C.c_int, C.c_size_t, _f32p, _i64p]
+        L.orc_heap_addn.restype = C.c_size_t
+        L.orc_heap_addn.argtypes = [C.c_int, C.c_size_t, _f32p, _i64p, _f32p, _i64p, C.c_size_t]
+        L.orc_heap_reorder.restype = C.c_size_t
+        L.orc_heap_reorder.argtypes = [C.c_int, C.c_size_t, _f32p, _i64p]
+        for fn in (L.orc_fvec_L2sqr, L.orc_fvec_inner_product):
+            fn.restype = C.c_float
+            fn.argtypes = [_f32p, _f32p, C.c_size_t]
+        _port = L
+    return _port
+
+
+class PortIndex:
+    """Restatement of IndexIVFFlat + IndexFlat quantizer (oracle/ivfflat_oracle.c)."""
+
+    def __init__(self, d, nlist, metric):
+        self.L = port_lib()
+        self.d, self.nlist, self.metric = int(d), int(nlist), int(metric)
+        self.h = C.c_void_p(self.L.orc_index_new(self.d, self.nlist, self.metric))
+        self.stats = OrcStats()
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.orc_index_free(self.h)
+            self.h = None
+
+    def set_centroids(self, c):
+        c, p = _f32(c)
+        assert c.shape == (self.nlist, self.d)
+        self.L.orc_index_set_centroids(self.h, p)
+
+    @property
+    def ntotal(self):
+        return self.L.orc_index_ntotal(self.h)
+
+    def add_with_ids(self, x, ids=None):
+        x, px = _f32(x)
+        pi = None
+        if ids is not None:
+            ids, pi = _i64(ids)
+        self.L.orc_index_add_with_ids(self.h, x.shape[0], px, pi)
+
+    def add_core(self, x, ids, assign):
+        x, px = _f32(x)
+        pi = None
+        if ids is not None:
+            ids, pi = _i64(ids)
+        assign, pa = _i64(assign)
+        self.L.orc_index_add_core(self.h, x.shape[0], px, pi, pa)
+
+    def list_size(self, l):
+        return self.L.orc_index_list_size(self.h, l)
+
+    def get_list(self, l):
+        n = self.list_size(l)
+        if n == 0:
+            return np.zeros((0, self.d), np.float32), np.zeros((0,), np.int64)
+        codes = np.ctypeslib.as_array(self.L.orc_index_list_codes(self.h, l), (n, self.d)).copy()
+        ids = np.ctypeslib.as_array(self.L.orc_index_list_ids(self.h, l), (n,)).copy()
+        return codes, ids
+
+    def quantize(self, x, nprobe):
+        x, px = _f32(x)
+        n = x.shape[0]
+        nprobe = min(nprobe, self.nlist)
+        Dq = np.empty((n, nprobe), np.float32)
+        Iq = np.empty((n, nprobe), np.int64)
+        self.L.orc_index_quantize(self.h, n, px, nprobe, Dq.ctypes.data_as(_f32p),
+                                  Iq.ctypes.data_as(_i64p))
+        return Dq, Iq
+
+    def search_preassigned(self, x, k, keys):
+        x, px = _f32(x)
+        keys, pk = _i64(keys)
+        n, nprobe = keys.shape
+        D = np.empty((n, k), np.float32)
+        I = np.empty((n, k), np.int64)
+        rc = self.L.orc_index_search_preassigned(self.h, n, px, k, nprobe, pk,
+                                                 D.ctypes.data_as(_f32p),
+                                                 I.ctypes.data_as(_i64p), C.byref(self.stats))
+        if rc:
+            raise RuntimeError("oracle search_preassigned failed rc=%d" % rc)
+        return D, I
+
+    def search(self, x, k, nprobe, nt=1):
+        x, px = _f32(x)
+        n = x.shape[0]
+        D = np.empty((n, k), np.float32)
+        I = np.empty((n, k), np.int64)
+        rc = self.L.orc_index_search(self.h, n, px, k, nprobe, nt, D.ctypes.data_as(_f32p),
+                                     I.ctypes.data_as(_i64p), C.byref(self.stats))
+        if rc:
+            raise RuntimeError("oracle search failed rc=%d" % rc)
+        return D, I
+
+
+def port_knn(metric, x, y, k):
+    L = port_lib()
+    x, px = _f32(x)
+    y, py = _f32(y)
+    D = np.empty((x.shape[0], k), np.float32)
+    I = np.empty((x.shape[0], k), np.int64)
+    L.orc_knn(metric, px, py, x.shape[1], x.shape[0], y.shape[0], k, D.ctypes.data_as(_f32p),
+              I.ctypes.data_as(_i64p))
+    return D, I
+
+
+def port_merge_knn_results(metric, all_D, all_I):
+    L = port_lib()
+    all_D, pd = _f32(all_D)
+    all_I, pi = _i64(all_I)
+    nshard, n, k = all_D.shape
+    D = np.empty((n, k), np.float32)
+    I = np.empty((n, k), np.int64)
+    L.orc_merge_knn_results(metric, n, k, nshard, pd, pi, D.ctypes.data_as(_f32p),
+                            I.ctypes.data_as(_i64p))
+    return D, I
+
+
+def port_heap_select(metric, k, vals, ids):
+    """heapify + addn + reorder: the reference's top-k semantics (strict compare, cmp2 order)."""
+    L = port_lib()
+    vals, pv = _f32(vals)
+    ids, pi = _i64(ids)
+    ov = np.empty(k, np.float32)
+    oi = np.empty(k, np.int64)
+    L.orc_heap_heapify(metric, k, ov.ctypes.data_as(_f32p), oi.ctypes.data_as(_i64p))
+    L.orc_heap_addn(metric, k, ov.ctypes.data_as(_f32p), oi.ctypes.data_as(_i64p), pv, pi,
+                    vals.shape[0])
+    L.orc_heap_reorder(metric, k, ov.ctypes.data_as(_f32p), oi.ctypes.data_as(_i64p))
+    return ov, oi
+
+
+# ------------------------------------------------------------------------------------------------
+# compiled reference (oracle/_ref)
+# ------------------------------------------------------------------------------------------------
+_ref = None
+_REF_DIR = os.path.join(_HERE, "_ref")
+
+
+def ref_available():
+    return os.path.exists(os.path.join(_REF_DIR, "libref_ivfflat.so"))
+
+
+def build_ref(reference_root="/root/reference"):
+    """Compile the reference from its own sources (only possible where they are mounted)."""
+    if not os.path.isdir(reference_root):
+        raise RuntimeError("reference sources not present; using prebuilt oracle/_ref if any")
+    subprocess.check_call(["make", "-s", "-j8", "-C", _HERE, "ref", "REF=" + reference_root])
+
+
+def ref_lib():
+    global _ref
+    if _ref is None:
+        if not ref_available():
+            raise RuntimeError("oracle/_ref/libref_ivfflat.so missing (run oracle/Makefile 'ref')")
+        # OpenBLAS inside faiss is called from faiss' own OpenMP slices: one BLAS thread each
+        os.environ.setdefault("OPENBLAS_NUM_THREADS", "1")
+        for dep in ("libquadmath-2284e583.so.0.0.0", "libgfortran-83c28eba.so.5.0.0"):
+            p = os.path.join(_REF_DIR, dep)
+            if os.path.exists(p):
+                C.CDLL(p, mode=C.RTLD_GLOBAL)
+        for f in sorted(os.listdir(_REF_DIR)):
+            if f.startswith("libopenblas"):
+                C.CDLL(os.path.join(_REF_DIR, f), mode=C.RTLD_GLOBAL)
+        L = C.CDLL(os.path.join(_REF_DIR, "libref_ivfflat.so"))
+        L.ref_last_error.restype = C.c_char_p
+        L.ref_getmillisecs.restype = C.c_double
+        L.ref_ivfflat_new.restype = C.c_void_p
+        L.ref_ivfflat_new.argtypes = [C.c_int64, C.c_int64, C.c_int]
+        L.ref_ivfflat_free.argtypes = [C.c_void_p]
+        L.ref_ivfflat_set_centroids.argtypes = [C.c_void_p, _f32p]
+        L.ref_ivfflat_train.argtypes = [C.c_void_p, C.c_int64, _f32p]
+        L.ref_ivfflat_get_centroids.argtypes = [C.c_void_p, _f32p]
+        L.ref_ivfflat_add_with_ids.argtypes = [C.c_void_p, C.c_int64, _f32p, _i64p]
+        L.ref_ivfflat_add_core.argtypes = [C.c_void_p, C.c_int64, _f32p, _i64p, _i64p]
+        L.ref_ivfflat_append_list.argtypes = [C.c_void_p, C.c_int64, C.c_int64, _i64p, _f32p]
+        L.ref_ivfflat_ntotal.restype = C.c_int64
+        L.ref_ivfflat_ntotal.argtypes = [C.c_void_p]
+        L.ref_ivfflat_list_size.restype = C.c_int64
+        L.ref_ivfflat_list_size.argtypes = [C.c_void_p, C.c_int64]
+        L.ref_ivfflat_get_list.argtypes = [C.c_void_p, C.c_int64, _f32p, _i64p]
+        L.ref_ivfflat_quantize.argtypes = [C.c_void_p, C.c_int64, _f32p, C.c_int64, _f32p, _i64p]
+        L.ref_ivfflat_search.argtypes = [C.c_void_p, C.c_int64, _f32p, C.c_int64, C.c_int64,
+                                         _f32p, _i64p]
+        L.ref_ivfflat_search_preassigned.argtypes = [C.c_void_p, C.c_int64, _f32p, C.c_int64,
+                                                     C.c_int64, _i64p, _f32p, _f32p, _i64p]
+        L.ref_ivfflat_set_parallel_mode.argtypes = [C.c_void_p, C.c_int]
+        L.ref_stats_get.argtypes = [C.POINTER(C.c_double)]
+        L.ref_knn.argtypes = [C.c_int, _f32p, _f32p, C.c_int64, C.c_int64, C.c_int64, C.c_int64,
+                              _f32p, _i64p]
+        L.ref_merge_knn_results.argtypes = [C.c_int, C.c_int64, C.c_int64, C.c_int, _f32p, _i64p,
+                                            _f32p, _i64p]
+        L.ref_heap_select.argtypes = [C.c_int, C.c_int64, C.c_int64, _f32p, _i64p, _f32p, _i64p]
+        for fn in (L.ref_fvec_L2sqr, L.ref_fvec_inner_product):
+            fn.restype = C.c_float
+            fn.argtypes = [_f32p, _f32p, C.c_int64]
+        _ref = L
+    return _ref
+
+
+def _chk(L, rc):
+    if rc:
+        raise RuntimeError("reference error %d: %s" % (rc, L.ref_last_error().decode()))
+
+
+class RefIndex:
+    """The reference's own IndexIVFFlat + IndexFlat quantizer (faiss/IndexIVFFlat.h:26)."""
+
+    def __init__(self, d, nlist, metric):
+        self.L = ref_lib()
+        self.d, self.nlist, self.metric = int(d), int(nlist), int(metric)
+        self.h = C.c_void_p(self.L.ref_ivfflat_new(self.d, self.nlist, self.metric))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            self.L.ref_ivfflat_free(self.h)
+            self.h = None
+
+    def set_centroids(self, c):
+        c, p = _f32(c)
+        assert c.shape == (self.nlist, self.d)
+        _chk(self.L, self.L.ref_ivfflat_set_centroids(self.h, p))
+
+    def train(self, x):
+        x, p = _f32(x)
+        _chk(self.L, self.L.ref_ivfflat_train(self.h, x.shape[0], p))
+
+    def get_centroids(self):
+        c = np.empty((self.nlist, self.d), np.float32)
+        _chk(self.L, self.L.ref_ivfflat_get_centroids(self.h, c.ctypes.data_as(_f32p)))
+        return c
+
+    @property
+    def ntotal(self):
+        return self.L.ref_ivfflat_ntotal(self.h)
+
+    def add_with_ids(self, x, ids=None):
+        x, px = _f32(x)
+        pi = None
+        if ids is not None:
+            ids, pi = _i64(ids)
+        _chk(self.L, self.L.ref_ivfflat_add_with_ids(self.h, x.shape[0], px, pi))
+
+    def add_core(self, x, ids, assign):
+        x, px = _f32(x)
+        pi = None
+        if ids is not None:
+            ids, pi = _i64(ids)
+        assign, pa = _i64(assign)
+        _chk(self.L, self.L.ref_ivfflat_add_core(self.h, x.shape[0], px, pi, pa))
+
+    def append_list(self, l, ids, codes):
+        codes, pc = _f32(codes)
+        ids, pi = _i64(ids)
+        _chk(self.L, self.L.ref_ivfflat_append_list(self.h, l, ids.shape[0], pi, pc))
+
+    def list_size(self, l):
+        return self.L.ref_ivfflat_list_size(self.h, l)
+
+    def get_list(self, l):
+        n = self.list_size(l)
+        codes = np.empty((n, self.d), np.float32)
+        ids = np.empty((n,), np.int64)
+        if n:
+            _chk(self.L, self.L.ref_ivfflat_get_list(self.h, l, codes.ctypes.data_as(_f32p),
+                                                     ids.ctypes.data_as(_i64p)))
+        return codes, ids
+
+    def quantize(self, x, nprobe):
+        x, px = _f32(x)
+        n = x.shape[0]
+        Dq = np.empty((n, nprobe), np.float32)
+        Iq = np.empty((n, nprobe), np.int64)
+        _chk(self.L, self.L.ref_ivfflat_quantize(self.h, n, px, nprobe,
+                                                 Dq.ctypes.data_as(_f32p),
+                                                 Iq.ctypes.data_as(_i64p)))
+        return Dq, Iq
+
+    def search(self, x, k, nprobe):
+        x, px = _f32(x)
+        n = x.shape[0]
+        D = np.empty((n, k), np.float32)
+        I = np.empty((n, k), np.int64)
+        _chk(self.L, self.L.ref_ivfflat_search(self.h, n, px, k, nprobe,
+                                               D.ctypes.data_as(_f32p), I.ctypes.data_as(_i64p)))
+        return D, I
+
+    def search_preassigned(self, x, k, keys, cdis=None):
+        x, px = _f32(x)
+        keys, pk = _i64(keys)
+        n, nprobe = keys.shape
+        if cdis is None:
+            cdis = np.zeros((n, nprobe), np.float32)
+        cdis, pc = _f32(cdis)
+        D = np.empty((n, k), np.float32)
+        I = np.empty((n, k), np.int64)
+        _chk(self.L, self.L.ref_ivfflat_search_preassigned(self.h, n, px, k, nprobe, pk, pc,
+                                                           D.ctypes.data_as(_f32p),
+                                                           I.ctypes.data_as(_i64p)))
+        return D, I
+
+    def set_parallel_mode(self, pm):
+        self.L.ref_ivfflat_set_parallel_mode(self.h, pm)
+
+
+def ref_stats(reset=False):
+    L = ref_lib()
+    out = (C.c_double * 6)()
+    L.ref_stats_get(out)
+    if reset:
+        L.ref_stats_reset()
+    keys = ("nq", "nlist", "ndis", "nheap_updates", "quantization_time", "search_time")
+    return dict(zip(keys, list(out)))
+
+
+def ref_set_threads(nt):
+    ref_lib().ref_set_omp_threads(int(nt))
+
+
+def ref_max_threads():
+    return ref_lib().ref_omp_max_threads()
+
+
+def ref_knn(metric, x, y, k):
+    L = ref_lib()
+    x, px = _f32(x)
+    y, py = _f32(y)
+    D = np.empty((x.shape[0], k), np.float32)
+    I = np.empty((x.shape[0], k), np.int64)
+    _chk(L, L.ref_knn(metric, px, py, x.shape[1], x.shape[0], y.shape[0], k,
+                      D.ctypes.data_as(_f32p), I.ctypes.data_as(_i64p)))
+    return D, I
+
+
+def ref_merge_knn_results(metric, all_D, all_I):
+    L = ref_lib()
+    all_D, pd = _f32(all_D)
+    all_I, pi = _i64(all_I)
+    nshard, n, k = all_D.shape
+    D = np.empty((n, k), np.float32)
+    I = np.empty((n, k), np.int64)
+    _chk(L, L.ref_merge_knn_results(metric, n, k, nshard, pd, pi, D.ctypes.data_as(_f32p),
+                                    I.ctypes.data_as(_i64p)))
+    return D, I
+
+
+def ref_heap_select(metric, k, vals, ids):
+    L = ref_lib()
+    vals, pv = _f32(vals)
+    ids, pi = _i64(ids)
+    ov = np.empty(k, np.float32)
+    oi = np.empty(k, np.int64)
+    L.ref_heap_select(metric, k, vals.shape[0], pv, pi, ov.ctypes.data_as(_f32p),
+                      oi.ctypes.data_as(_i64p))
+    return ov, oi
