@@ -1,0 +1,27 @@
+"""hnsw_ivf_b200 -- B200-native batched IVF-Flat search (one hot path of Quaternijkon/hnsw-ivf).
+
+Python host mirror of the reference's interface for this path. The product is the C-ABI shared
+library ``lib/libb200ivf.so`` (hand-written sm_100a CUDA, see csrc/); this module only binds it
+with ctypes, the way the reference's Python layer binds its C++ (faiss/python/class_wrappers.py:300
+``replacement_search``: numpy in, (D, I) out). There is NO CPU fallback: importing works without a
+GPU (so the symbols can be checked), but every compute call raises if the library or a CUDA device
+is missing.
+"""
+from .binding import (  # noqa: F401
+    METRIC_INNER_PRODUCT,
+    METRIC_L2,
+    B200Error,
+    IndexIVFFlat,
+    IndexIVFStats,
+    build_library,
+    library_path,
+    load_library,
+    merge_knn_results,
+)
+from .sharded import IndexShardsIVFFlat, list_range_of_rank  # noqa: F401
+
+__all__ = [
+    "METRIC_INNER_PRODUCT", "METRIC_L2", "B200Error", "IndexIVFFlat", "IndexIVFStats",
+    "IndexShardsIVFFlat", "build_library", "library_path", "load_library", "merge_knn_results",
+    "list_range_of_rank",
+]

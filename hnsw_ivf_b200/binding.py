@@ -1,0 +1,290 @@
+"""ctypes binding of include/b200ivf_c.h (the drop-in C-ABI).
+
+Buffers may be numpy arrays (host) or torch tensors (host or CUDA); CUDA tensors are passed as raw
+device pointers, so a search on resident inputs performs no host<->device copy.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+METRIC_INNER_PRODUCT = 0  # faiss/MetricType.h:23
+METRIC_L2 = 1             # faiss/MetricType.h:24
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+
+class B200Error(RuntimeError):
+    """Non-zero return code of the C-ABI (c_api/error_c.h:19-30 codes)."""
+
+    def __init__(self, code, msg):
+        super().__init__("b200ivf error %d: %s" % (code, msg))
+        self.code = code
+
+
+class IndexIVFStats(C.Structure):  # FaissIndexIVFStats, c_api/IndexIVF_c.h:162-169
+    _fields_ = [("nq", C.c_size_t), ("nlist", C.c_size_t), ("ndis", C.c_size_t),
+                ("nheap_updates", C.c_size_t), ("quantization_time", C.c_double),
+                ("search_time", C.c_double)]
+
+
+def library_path():
+    return os.path.join(_HERE, "lib", "libb200ivf.so")
+
+
+def build_library(verbose=False):
+    """Compile csrc/*.cu for sm_100a into lib/libb200ivf.so (nvcc cross-compiles without a GPU)."""
+    out = None if verbose else subprocess.DEVNULL
+    subprocess.check_call(["make", "-j8", "-C", os.path.join(_HERE, "csrc")], stdout=out)
+    return library_path()
+
+
+# every symbol include/b200ivf_c.h declares: (name, restype, argtypes)
+_vp, _f32p, _i64p = C.c_void_p, C.c_void_p, C.c_void_p
+SYMBOLS = [
+    ("b200_get_last_error", C.c_char_p, []),
+    ("b200_IndexIVFFlat_new_with_metric", C.c_int,
+     [C.POINTER(_vp), C.c_size_t, C.c_size_t, C.c_int, C.c_int]),
+    ("b200_IndexIVFFlat_free", None, [_vp]),
+    ("b200_IndexIVFFlat_nlist", C.c_size_t, [_vp]),
+    ("b200_IndexIVFFlat_nprobe", C.c_size_t, [_vp]),
+    ("b200_IndexIVFFlat_set_nprobe", None, [_vp, C.c_size_t]),
+    ("b200_IndexIVFFlat_d", C.c_int, [_vp]),
+    ("b200_IndexIVFFlat_ntotal", C.c_int64, [_vp]),
+    ("b200_IndexIVFFlat_is_trained", C.c_int, [_vp]),
+    ("b200_IndexIVFFlat_metric_type", C.c_int, [_vp]),
+    ("b200_IndexIVFFlat_set_centroids", C.c_int, [_vp, _f32p]),
+    ("b200_IndexIVFFlat_get_centroids", C.c_int, [_vp, _f32p]),
+    ("b200_IndexIVFFlat_set_list_range", C.c_int, [_vp, C.c_size_t, C.c_size_t]),
+    ("b200_IndexIVFFlat_add_with_ids", C.c_int, [_vp, C.c_int64, _f32p, _i64p]),
+    ("b200_IndexIVFFlat_add_core", C.c_int, [_vp, C.c_int64, _f32p, _i64p, _i64p]),
+    ("b200_IndexIVFFlat_reset", C.c_int, [_vp]),
+    ("b200_IndexIVFFlat_get_list_size", C.c_size_t, [_vp, C.c_size_t]),
+    ("b200_IndexIVFFlat_invlists_get_ids", C.c_int, [_vp, C.c_size_t, _i64p]),
+    ("b200_IndexIVFFlat_invlists_get_codes", C.c_int, [_vp, C.c_size_t, _f32p]),
+    ("b200_IndexIVFFlat_search", C.c_int, [_vp, C.c_int64, _f32p, C.c_int64, _f32p, _i64p]),
+    ("b200_IndexIVFFlat_search_preassigned", C.c_int,
+     [_vp, C.c_int64, _f32p, C.c_int64, _i64p, _f32p, _f32p, _i64p, C.c_int]),
+    ("b200_IndexIVFFlat_quantize", C.c_int, [_vp, C.c_int64, _f32p, C.c_int64, _f32p, _i64p]),
+    ("b200_IndexIVFFlat_get_stats", None, [_vp, C.POINTER(IndexIVFStats)]),
+    ("b200_IndexIVFFlat_reset_stats", None, [_vp]),
+    ("b200_IndexIVFFlat_last_timings", None, [_vp, C.POINTER(C.c_double)]),
+    ("b200_IndexIVFFlat_set_stream", C.c_int, [_vp, _vp]),
+    ("b200_merge_knn_results", C.c_int,
+     [C.c_int, C.c_int, C.c_int64, C.c_int64, _f32p, _i64p, _f32p, _i64p, C.c_int, _vp]),
+]
+
+
+def load_library():
+    """dlopen the C-ABI library and bind every declared symbol. Raises if it is not built."""
+    global _LIB
+    if _LIB is None:
+        path = library_path()
+        if not os.path.exists(path):
+            raise B200Error(-2, "%s is not built (run __graft_entry__.build()); "
+                            "there is no CPU fallback" % path)
+        lib = C.CDLL(path)
+        for name, res, args in SYMBOLS:
+            fn = getattr(lib, name)  # AttributeError if the .so lacks a declared symbol
+            fn.restype = res
+            fn.argtypes = args
+        _LIB = lib
+    return _LIB
+
+
+# ------------------------------------------------------------------------------------------------
+def _is_torch(a):
+    return type(a).__module__.startswith("torch")
+
+
+def _ptr(a, dtype, shape=None, name="buffer"):
+    """(keepalive, raw pointer) of a numpy array or torch tensor, checked for dtype/contiguity."""
+    if a is None:
+        return None, None
+    if _is_torch(a):
+        import torch
+        want = {np.float32: torch.float32, np.int64: torch.int64}[dtype]
+        if a.dtype != want:
+            raise TypeError("%s must be %s" % (name, want))
+        if not a.is_contiguous():
+            raise ValueError("%s must be contiguous" % name)
+        if shape is not None and tuple(a.shape) != tuple(shape):
+            raise ValueError("%s has shape %s, expected %s" % (name, tuple(a.shape), shape))
+        return a, a.data_ptr()
+    arr = np.ascontiguousarray(a, dtype=dtype)
+    if shape is not None and tuple(arr.shape) != tuple(shape):
+        raise ValueError("%s has shape %s, expected %s" % (name, arr.shape, shape))
+    return arr, arr.ctypes.data
+
+
+def _empty_like_input(x, shape, dtype):
+    """Result buffer living where the queries live (CUDA tensor -> CUDA tensor, else numpy)."""
+    if _is_torch(x):
+        import torch
+        td = {np.float32: torch.float32, np.int64: torch.int64}[dtype]
+        return torch.empty(shape, dtype=td, device=x.device)
+    return np.empty(shape, dtype=dtype)
+
+
+class IndexIVFFlat:
+    """Device-resident IndexIVFFlat with its flat quantizer (faiss/IndexIVFFlat.h:26).
+
+    Same field names and call shapes as the reference's Python surface: ``d``, ``nlist``,
+    ``nprobe``, ``ntotal``, ``is_trained``, ``metric_type``; ``add``, ``add_with_ids``,
+    ``search(x, k) -> (D, I)``, ``search_preassigned``. Training is out of scope for this path
+    (SURVEY.md 8f): centroids trained elsewhere are installed with ``set_centroids``.
+    """
+
+    def __init__(self, d, nlist, metric=METRIC_L2, device=0):
+        self._lib = load_library()
+        h = _vp()
+        self._h = None
+        self._check(self._lib.b200_IndexIVFFlat_new_with_metric(C.byref(h), d, nlist, metric,
+                                                                device))
+        self._h = h
+        self.device = device
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            self._lib.b200_IndexIVFFlat_free(self._h)
+            self._h = None
+
+    def _check(self, rc):
+        if rc != 0:
+            raise B200Error(rc, self._lib.b200_get_last_error().decode())
+
+    # ---- fields ------------------------------------------------------------------------------
+    d = property(lambda s: s._lib.b200_IndexIVFFlat_d(s._h))
+    nlist = property(lambda s: s._lib.b200_IndexIVFFlat_nlist(s._h))
+    ntotal = property(lambda s: s._lib.b200_IndexIVFFlat_ntotal(s._h))
+    is_trained = property(lambda s: bool(s._lib.b200_IndexIVFFlat_is_trained(s._h)))
+    metric_type = property(lambda s: s._lib.b200_IndexIVFFlat_metric_type(s._h))
+
+    @property
+    def nprobe(self):
+        return self._lib.b200_IndexIVFFlat_nprobe(self._h)
+
+    @nprobe.setter
+    def nprobe(self, v):
+        self._lib.b200_IndexIVFFlat_set_nprobe(self._h, int(v))
+
+    # ---- build -------------------------------------------------------------------------------
+    def set_centroids(self, c):
+        keep, p = _ptr(c, np.float32, (self.nlist, self.d), "centroids")
+        self._check(self._lib.b200_IndexIVFFlat_set_centroids(self._h, p))
+
+    def get_centroids(self):
+        out = np.empty((self.nlist, self.d), np.float32)
+        self._check(self._lib.b200_IndexIVFFlat_get_centroids(self._h, out.ctypes.data))
+        return out
+
+    def set_list_range(self, lo, hi):
+        self._check(self._lib.b200_IndexIVFFlat_set_list_range(self._h, lo, hi))
+
+    def add(self, x):
+        self.add_with_ids(x, None)
+
+    def add_with_ids(self, x, ids):
+        kx, px = _ptr(x, np.float32, None, "x")
+        n = kx.shape[0]
+        ki, pi = _ptr(ids, np.int64, (n,), "ids")
+        self._check(self._lib.b200_IndexIVFFlat_add_with_ids(self._h, n, px, pi))
+
+    def add_core(self, x, ids, assign):
+        kx, px = _ptr(x, np.float32, None, "x")
+        n = kx.shape[0]
+        ki, pi = _ptr(ids, np.int64, (n,), "ids")
+        ka, pa = _ptr(assign, np.int64, (n,), "assign")
+        self._check(self._lib.b200_IndexIVFFlat_add_core(self._h, n, px, pi, pa))
+
+    def reset(self):
+        self._check(self._lib.b200_IndexIVFFlat_reset(self._h))
+
+    def get_list_size(self, l):
+        return self._lib.b200_IndexIVFFlat_get_list_size(self._h, l)
+
+    def get_list(self, l):
+        n = self.get_list_size(l)
+        codes = np.empty((n, self.d), np.float32)
+        ids = np.empty((n,), np.int64)
+        if n:
+            self._check(self._lib.b200_IndexIVFFlat_invlists_get_codes(self._h, l,
+                                                                       codes.ctypes.data))
+            self._check(self._lib.b200_IndexIVFFlat_invlists_get_ids(self._h, l, ids.ctypes.data))
+        return codes, ids
+
+    # ---- search ------------------------------------------------------------------------------
+    def search(self, x, k, D=None, I=None):
+        kx, px = _ptr(x, np.float32, None, "x")
+        n = kx.shape[0]
+        if kx.ndim != 2 or kx.shape[1] != self.d:
+            raise ValueError("x must be [n][%d]" % self.d)
+        if D is None:
+            D = _empty_like_input(kx, (n, k), np.float32)
+        if I is None:
+            I = _empty_like_input(kx, (n, k), np.int64)
+        kd, pd = _ptr(D, np.float32, (n, k), "D")
+        ki, pi = _ptr(I, np.int64, (n, k), "I")
+        self._check(self._lib.b200_IndexIVFFlat_search(self._h, n, px, k, pd, pi))
+        return kd, ki
+
+    def search_preassigned(self, x, k, assign, centroid_dis=None, D=None, I=None):
+        kx, px = _ptr(x, np.float32, None, "x")
+        n = kx.shape[0]
+        nprobe = min(self.nprobe, self.nlist)
+        ka, pa = _ptr(assign, np.int64, (n, nprobe), "assign")
+        kc, pc = _ptr(centroid_dis, np.float32, None, "centroid_dis")
+        if D is None:
+            D = _empty_like_input(kx, (n, k), np.float32)
+        if I is None:
+            I = _empty_like_input(kx, (n, k), np.int64)
+        kd, pd = _ptr(D, np.float32, (n, k), "D")
+        ki, pi = _ptr(I, np.int64, (n, k), "I")
+        self._check(self._lib.b200_IndexIVFFlat_search_preassigned(self._h, n, px, k, pa, pc, pd,
+                                                                   pi, 0))
+        return kd, ki
+
+    def quantize(self, x, nprobe):
+        kx, px = _ptr(x, np.float32, None, "x")
+        n = kx.shape[0]
+        Dq = _empty_like_input(kx, (n, nprobe), np.float32)
+        Iq = _empty_like_input(kx, (n, nprobe), np.int64)
+        kd, pd = _ptr(Dq, np.float32, None, "Dq")
+        ki, pi = _ptr(Iq, np.int64, None, "Iq")
+        self._check(self._lib.b200_IndexIVFFlat_quantize(self._h, n, px, nprobe, pd, pi))
+        return kd, ki
+
+    # ---- stats / plumbing ----------------------------------------------------------------------
+    def get_stats(self):
+        s = IndexIVFStats()
+        self._lib.b200_IndexIVFFlat_get_stats(self._h, C.byref(s))
+        return s
+
+    def reset_stats(self):
+        self._lib.b200_IndexIVFFlat_reset_stats(self._h)
+
+    def last_timings(self):
+        ms = (C.c_double * 5)()
+        self._lib.b200_IndexIVFFlat_last_timings(self._h, ms)
+        return dict(zip(("coarse", "plan", "scan", "select", "total"), list(ms)))
+
+    def set_stream(self, cuda_stream_ptr):
+        self._check(self._lib.b200_IndexIVFFlat_set_stream(self._h, cuda_stream_ptr))
+
+
+def merge_knn_results(metric, all_D, all_I, device=0, stream=None):
+    """merge_knn_results (faiss/utils/Heap.cpp:158-232) on the device: [nshard][n][k] -> [n][k]."""
+    lib = load_library()
+    kd, pd = _ptr(all_D, np.float32, None, "all_D")
+    nshard, n, k = kd.shape
+    ki, pi = _ptr(all_I, np.int64, (nshard, n, k), "all_I")
+    D = _empty_like_input(kd, (n, k), np.float32)
+    I = _empty_like_input(kd, (n, k), np.int64)
+    ko, po = _ptr(D, np.float32, None, "D")
+    kj, pj = _ptr(I, np.int64, None, "I")
+    rc = lib.b200_merge_knn_results(metric, nshard, n, k, pd, pi, po, pj, device, stream)
+    if rc != 0:
+        raise B200Error(rc, lib.b200_get_last_error().decode())
+    return ko, kj

@@ -1,0 +1,170 @@
+// capi.cu -- the extern "C" layer declared in include/b200ivf_c.h. Same shape as the reference's C
+// API: reinterpret_cast of an opaque handle plus try/catch mapped to int codes
+// (c_api/macros_impl.h:22-55), thread-local last error (c_api/error_impl.cpp:15-27).
+#include "../../include/b200ivf_c.h"
+
+#include "index.h"
+
+#include <exception>
+#include <string>
+
+using b200ivf::IndexIVFFlatB200;
+
+namespace {
+thread_local std::string g_last_error;
+
+template <class F>
+int guarded(F&& f) {
+    try {
+        f();
+        return 0;
+    } catch (const b200ivf::B200Exception& e) {
+        g_last_error = e.what();
+        return -2; // FAISS_EXCEPT
+    } catch (const std::exception& e) {
+        g_last_error = e.what();
+        return -4; // STD_EXCEPT
+    } catch (...) {
+        g_last_error = "Unknown error";
+        return -1; // UNKNOWN_EXCEPT
+    }
+}
+
+inline IndexIVFFlatB200* H(B200IndexIVFFlat* p) {
+    return reinterpret_cast<IndexIVFFlatB200*>(p);
+}
+inline const IndexIVFFlatB200* H(const B200IndexIVFFlat* p) {
+    return reinterpret_cast<const IndexIVFFlatB200*>(p);
+}
+} // namespace
+
+extern "C" {
+
+const char* b200_get_last_error(void) {
+    return g_last_error.c_str();
+}
+
+int b200_IndexIVFFlat_new_with_metric(B200IndexIVFFlat** p_index, size_t d, size_t nlist,
+                                      B200MetricType metric, int device) {
+    return guarded([&] {
+        if (!p_index)
+            throw b200ivf::B200Exception("null output handle");
+        *p_index = reinterpret_cast<B200IndexIVFFlat*>(
+                new IndexIVFFlatB200(d, nlist, (int)metric, device));
+    });
+}
+
+void b200_IndexIVFFlat_free(B200IndexIVFFlat* index) {
+    delete H(index);
+}
+
+size_t b200_IndexIVFFlat_nlist(const B200IndexIVFFlat* index) {
+    return H(index)->nlist;
+}
+size_t b200_IndexIVFFlat_nprobe(const B200IndexIVFFlat* index) {
+    return H(index)->nprobe;
+}
+void b200_IndexIVFFlat_set_nprobe(B200IndexIVFFlat* index, size_t nprobe) {
+    H(index)->nprobe = nprobe;
+}
+int b200_IndexIVFFlat_d(const B200IndexIVFFlat* index) {
+    return H(index)->d;
+}
+b200_idx_t b200_IndexIVFFlat_ntotal(const B200IndexIVFFlat* index) {
+    return H(index)->ntotal;
+}
+int b200_IndexIVFFlat_is_trained(const B200IndexIVFFlat* index) {
+    return H(index)->is_trained ? 1 : 0;
+}
+B200MetricType b200_IndexIVFFlat_metric_type(const B200IndexIVFFlat* index) {
+    return (B200MetricType)H(index)->metric_type;
+}
+
+int b200_IndexIVFFlat_set_centroids(B200IndexIVFFlat* index, const float* centroids) {
+    return guarded([&] { H(index)->set_centroids(centroids); });
+}
+int b200_IndexIVFFlat_get_centroids(const B200IndexIVFFlat* index, float* out) {
+    return guarded([&] { H(index)->get_centroids(out); });
+}
+int b200_IndexIVFFlat_set_list_range(B200IndexIVFFlat* index, size_t lo, size_t hi) {
+    return guarded([&] { H(index)->set_list_range(lo, hi); });
+}
+int b200_IndexIVFFlat_add_with_ids(B200IndexIVFFlat* index, b200_idx_t n, const float* x,
+                                   const b200_idx_t* xids) {
+    return guarded([&] { H(index)->add_with_ids(n, x, xids); });
+}
+int b200_IndexIVFFlat_add_core(B200IndexIVFFlat* index, b200_idx_t n, const float* x,
+                               const b200_idx_t* xids, const int64_t* precomputed_idx) {
+    return guarded([&] {
+        if (!precomputed_idx) // FAISS_THROW_IF_NOT(coarse_idx), faiss/IndexIVFFlat.cpp:53
+            throw b200ivf::B200Exception("Error: 'coarse_idx' failed");
+        H(index)->add_core(n, x, xids, precomputed_idx);
+    });
+}
+int b200_IndexIVFFlat_reset(B200IndexIVFFlat* index) {
+    return guarded([&] { H(index)->reset(); });
+}
+
+size_t b200_IndexIVFFlat_get_list_size(const B200IndexIVFFlat* index, size_t list_no) {
+    size_t r = 0;
+    guarded([&] { r = H(index)->get_list_size(list_no); });
+    return r;
+}
+int b200_IndexIVFFlat_invlists_get_ids(const B200IndexIVFFlat* index, size_t list_no,
+                                       b200_idx_t* invlist) {
+    return guarded([&] { H(index)->get_list_ids(list_no, invlist); });
+}
+int b200_IndexIVFFlat_invlists_get_codes(const B200IndexIVFFlat* index, size_t list_no,
+                                         float* codes) {
+    return guarded([&] { H(index)->get_list_codes(list_no, codes); });
+}
+
+int b200_IndexIVFFlat_search(const B200IndexIVFFlat* index, b200_idx_t n, const float* x,
+                             b200_idx_t k, float* distances, b200_idx_t* labels) {
+    return guarded([&] { H(index)->search(n, x, k, distances, labels); });
+}
+int b200_IndexIVFFlat_search_preassigned(const B200IndexIVFFlat* index, b200_idx_t n,
+                                         const float* x, b200_idx_t k, const b200_idx_t* assign,
+                                         const float* centroid_dis, float* distances,
+                                         b200_idx_t* labels, int store_pairs) {
+    return guarded([&] {
+        if (!assign)
+            throw b200ivf::B200Exception("null assign table");
+        H(index)->search_preassigned(n, x, k, assign, centroid_dis, distances, labels,
+                                     store_pairs != 0);
+    });
+}
+int b200_IndexIVFFlat_quantize(const B200IndexIVFFlat* index, b200_idx_t n, const float* x,
+                               b200_idx_t nprobe, float* centroid_dis, b200_idx_t* assign) {
+    return guarded([&] { H(index)->quantize(n, x, nprobe, centroid_dis, assign); });
+}
+
+void b200_IndexIVFFlat_get_stats(const B200IndexIVFFlat* index, B200IndexIVFStats* stats) {
+    const b200ivf::IndexIVFStatsB200 s = H(index)->get_stats();
+    stats->nq = s.nq;
+    stats->nlist = s.nlist;
+    stats->ndis = s.ndis;
+    stats->nheap_updates = s.nheap_updates;
+    stats->quantization_time = s.quantization_time;
+    stats->search_time = s.search_time;
+}
+void b200_IndexIVFFlat_reset_stats(B200IndexIVFFlat* index) {
+    guarded([&] { H(index)->reset_stats(); });
+}
+void b200_IndexIVFFlat_last_timings(const B200IndexIVFFlat* index, double* ms5) {
+    H(index)->last_timings(ms5);
+}
+int b200_IndexIVFFlat_set_stream(B200IndexIVFFlat* index, void* cuda_stream) {
+    return guarded([&] { H(index)->set_stream((cudaStream_t)cuda_stream); });
+}
+
+int b200_merge_knn_results(B200MetricType metric, int nshard, b200_idx_t n, b200_idx_t k,
+                           const float* all_distances, const b200_idx_t* all_labels,
+                           float* distances, b200_idx_t* labels, int device, void* cuda_stream) {
+    return guarded([&] {
+        b200ivf::merge_knn_results((int)metric, nshard, n, k, all_distances, all_labels, distances,
+                                   labels, device, (cudaStream_t)cuda_stream);
+    });
+}
+
+} // extern "C"

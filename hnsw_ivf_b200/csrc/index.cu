@@ -1,0 +1,811 @@
+// index.cu -- host driver of the device-resident IVF-Flat index: owns the slab, plans launches,
+// stages host buffers, keeps statistics. Control flow restated from the reference's
+// IndexIVF::search (faiss/IndexIVF.cpp:303-397) / search_preassigned (:399-723) /
+// IndexIVFFlat::add_core (faiss/IndexIVFFlat.cpp:46-91), with the OpenMP query slicing replaced by
+// device-wide batches and the per-query heap by the scan/select kernels.
+#include "index.h"
+
+#include "common.cuh"
+#include "kernels.h"
+
+#include <algorithm>
+#include <cstring>
+
+namespace b200ivf {
+
+#define CUDA_CHECK(expr)                                                                     \
+    do {                                                                                     \
+        cudaError_t e__ = (expr);                                                            \
+        if (e__ != cudaSuccess) {                                                            \
+            throw B200Exception(std::string("CUDA error ") + std::to_string((int)e__) + " (" + \
+                                cudaGetErrorString(e__) + ") at " + __FILE__ + ":" +         \
+                                std::to_string(__LINE__));                                   \
+        }                                                                                    \
+    } while (0)
+
+#define B200_THROW_IF_NOT_MSG(cond, msg)                                                   \
+    do {                                                                                   \
+        if (!(cond))                                                                       \
+            throw B200Exception(std::string("Error: '") + #cond + "' failed: " + (msg));   \
+    } while (0)
+
+void Buffer::reserve(size_t n) {
+    if (n <= bytes)
+        return;
+    release();
+    size_t want = std::max(n, bytes + bytes / 2);
+    if (pinned_host)
+        CUDA_CHECK(cudaMallocHost(&p, want));
+    else
+        CUDA_CHECK(cudaMalloc(&p, want));
+    bytes = want;
+}
+
+void Buffer::release() {
+    if (p) {
+        if (pinned_host)
+            cudaFreeHost(p);
+        else
+            cudaFree(p);
+    }
+    p = nullptr;
+    bytes = 0;
+}
+
+namespace {
+
+bool is_device_pointer(const void* p) {
+    if (!p)
+        return false;
+    cudaPointerAttributes at;
+    cudaError_t e = cudaPointerGetAttributes(&at, p);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged;
+}
+
+struct DeviceGuard {
+    int prev = 0;
+    explicit DeviceGuard(int dev) {
+        CUDA_CHECK(cudaGetDevice(&prev));
+        if (prev != dev)
+            CUDA_CHECK(cudaSetDevice(dev));
+    }
+    ~DeviceGuard() {
+        cudaSetDevice(prev);
+    }
+};
+
+// shared-memory budget per CTA for the scan kernel (227 KB is the sm_100a limit)
+constexpr size_t kScanSmemBudget = 200 * 1024;
+// warps the scan should have available: 148 SMs x ~12 resident warps x 2 waves
+constexpr int64_t kTargetScanItems = 148 * 12 * 2;
+constexpr int kScanRowsPerStep = 4; // RV of the scan kernel
+
+struct ScanCfg {
+    int rq, wpc, cap;
+};
+
+ScanCfg choose_scan_cfg(int nf4, int k) {
+    const int cap = pow2_ceil(k + 32);
+    // preference order: many queries per warp first, then many warps per CTA
+    const int pref[9][2] = {{8, 4}, {4, 4}, {8, 2}, {4, 2}, {8, 1}, {4, 1}, {1, 4}, {1, 2}, {1, 1}};
+    for (const auto& p : pref)
+        if (scan_smem_bytes(p[0], p[1], nf4, cap) <= kScanSmemBudget)
+            return {p[0], p[1], cap};
+    if (scan_smem_bytes(1, 1, nf4, cap) <= 227 * 1024 - 1024)
+        return {1, 1, cap};
+    throw B200Exception("k too large for the scan kernel's shared-memory candidate buffer");
+}
+
+} // namespace
+
+struct IndexIVFFlatB200::Impl {
+    int nf4 = 0;
+    size_t list_lo = 0, list_hi = 0;
+    cudaStream_t own_stream = nullptr, stream = nullptr;
+
+    // coarse quantizer: centroid table as a one-list slab
+    Buffer cent_slab;
+    Buffer cent_meta; // uint32 blk0[1] | int32 len[1]
+    std::vector<float> h_centroids;
+
+    // inverted lists
+    Buffer slab, ids, list_blk0, list_len;
+    std::vector<uint32_t> h_blk0;
+    std::vector<int32_t> h_len;
+    size_t slab_blocks = 0;
+    int64_t nstored = 0;
+
+    // scratch (grow only)
+    Buffer coarse_ids, coarse_dis, part, count, fill, grp_start, item_off, pair_query, slot_of,
+            cplan, stage_x, stage_D, stage_I, stage_assign, dev_x, dev_D, dev_I, dev_assign64,
+            dev_stats, host_stats;
+    cudaEvent_t ev[6] = {};
+    double last_ms[5] = {0, 0, 0, 0, 0};
+    IndexIVFStatsB200 stats;
+
+    Impl() {
+        stage_x.pinned_host = stage_D.pinned_host = stage_I.pinned_host = true;
+        stage_assign.pinned_host = host_stats.pinned_host = true;
+    }
+};
+
+IndexIVFFlatB200::IndexIVFFlatB200(size_t d_, size_t nlist_, int metric, int device)
+        : d((int)d_), nlist(nlist_), metric_type(metric), impl_(nullptr), device_(device) {
+    B200_THROW_IF_NOT_MSG(d_ > 0 && d_ < (1u << 20), "invalid dimension");
+    B200_THROW_IF_NOT_MSG(nlist_ > 0 && nlist_ < (1u << 30), "invalid nlist");
+    B200_THROW_IF_NOT_MSG(metric == kMetricL2 || metric == kMetricInnerProduct,
+                          "metric type not supported"); // faiss/IndexIVFFlat.cpp:219
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        throw B200Exception(
+                "no CUDA device: the B200 IVF-Flat path has no CPU fallback");
+    }
+    B200_THROW_IF_NOT_MSG(device >= 0 && device < ndev, "invalid CUDA device ordinal");
+    DeviceGuard g(device_);
+    impl_ = new Impl;
+    impl_->nf4 = (d + 3) / 4;
+    impl_->list_hi = nlist;
+    CUDA_CHECK(cudaStreamCreateWithFlags(&impl_->own_stream, cudaStreamNonBlocking));
+    impl_->stream = impl_->own_stream;
+    for (auto& ev : impl_->ev)
+        CUDA_CHECK(cudaEventCreate(&ev));
+    impl_->h_blk0.assign(nlist, 0);
+    impl_->h_len.assign(nlist, 0);
+    impl_->list_blk0.reserve(sizeof(uint32_t) * nlist);
+    impl_->list_len.reserve(sizeof(int32_t) * nlist);
+    CUDA_CHECK(cudaMemset(impl_->list_blk0.p, 0, sizeof(uint32_t) * nlist));
+    CUDA_CHECK(cudaMemset(impl_->list_len.p, 0, sizeof(int32_t) * nlist));
+    impl_->dev_stats.reserve(sizeof(unsigned long long) * 4);
+    impl_->host_stats.reserve(sizeof(unsigned long long) * 4);
+    CUDA_CHECK(cudaMemset(impl_->dev_stats.p, 0, sizeof(unsigned long long) * 4));
+}
+
+IndexIVFFlatB200::~IndexIVFFlatB200() {
+    if (!impl_)
+        return;
+    int prev = 0;
+    cudaGetDevice(&prev);
+    cudaSetDevice(device_);
+    cudaStreamSynchronize(impl_->stream);
+    Buffer* bufs[] = {&impl_->cent_slab, &impl_->cent_meta, &impl_->slab, &impl_->ids,
+                      &impl_->list_blk0, &impl_->list_len, &impl_->coarse_ids, &impl_->coarse_dis,
+                      &impl_->part, &impl_->count, &impl_->fill, &impl_->grp_start,
+                      &impl_->item_off, &impl_->pair_query, &impl_->slot_of, &impl_->cplan,
+                      &impl_->stage_x, &impl_->stage_D, &impl_->stage_I, &impl_->stage_assign,
+                      &impl_->dev_x, &impl_->dev_D, &impl_->dev_I, &impl_->dev_assign64,
+                      &impl_->dev_stats, &impl_->host_stats};
+    for (Buffer* b : bufs)
+        b->release();
+    for (auto& ev : impl_->ev)
+        if (ev)
+            cudaEventDestroy(ev);
+    if (impl_->own_stream)
+        cudaStreamDestroy(impl_->own_stream);
+    delete impl_;
+    cudaSetDevice(prev);
+}
+
+void IndexIVFFlatB200::set_stream(cudaStream_t s) {
+    std::lock_guard<std::mutex> lock(mu_);
+    DeviceGuard g(device_);
+    CUDA_CHECK(cudaStreamSynchronize(impl_->stream));
+    impl_->stream = s ? s : impl_->own_stream;
+}
+
+// ------------------------------------------------------------------------------------------------
+// coarse quantizer table
+// ------------------------------------------------------------------------------------------------
+void IndexIVFFlatB200::set_centroids(const float* c) {
+    std::lock_guard<std::mutex> lock(mu_);
+    DeviceGuard g(device_);
+    Impl& m = *impl_;
+    B200_THROW_IF_NOT_MSG(c != nullptr, "null centroids");
+    const size_t nfl = nlist * (size_t)d;
+    m.h_centroids.resize(nfl);
+    const float* cd = c;
+    if (is_device_pointer(c)) {
+        CUDA_CHECK(cudaMemcpy(m.h_centroids.data(), c, nfl * sizeof(float), cudaMemcpyDeviceToHost));
+    } else {
+        std::memcpy(m.h_centroids.data(), c, nfl * sizeof(float));
+        m.dev_x.reserve(nfl * sizeof(float));
+        CUDA_CHECK(cudaMemcpyAsync(m.dev_x.p, c, nfl * sizeof(float), cudaMemcpyHostToDevice,
+                                   m.stream));
+        cd = m.dev_x.as<float>();
+    }
+    const size_t nblk = (nlist + kBlockRows - 1) / kBlockRows;
+    const size_t slab_bytes = nblk * m.nf4 * kBlockRows * sizeof(float4);
+    m.cent_slab.reserve(slab_bytes);
+    CUDA_CHECK(cudaMemsetAsync(m.cent_slab.p, 0, slab_bytes, m.stream));
+    // identity placement: centroid j -> row j
+    std::vector<int64_t> rows(nlist);
+    for (size_t j = 0; j < nlist; ++j)
+        rows[j] = (int64_t)j;
+    m.dev_assign64.reserve(nlist * sizeof(int64_t));
+    CUDA_CHECK(cudaMemcpyAsync(m.dev_assign64.p, rows.data(), nlist * sizeof(int64_t),
+                               cudaMemcpyHostToDevice, m.stream));
+    m.dev_I.reserve(nblk * kBlockRows * sizeof(int64_t)); // throw-away id column
+    CUDA_CHECK(launch_scatter_rows(cd, nullptr, m.dev_assign64.as<int64_t>(), (int64_t)nlist, d,
+                                   m.nf4, m.cent_slab.as<float>(), m.dev_I.as<int64_t>(), 0,
+                                   m.stream));
+    m.cent_meta.reserve(16);
+    const uint32_t blk0 = 0;
+    const int32_t len = (int32_t)nlist;
+    CUDA_CHECK(cudaMemcpyAsync(m.cent_meta.p, &blk0, 4, cudaMemcpyHostToDevice, m.stream));
+    CUDA_CHECK(cudaMemcpyAsync((char*)m.cent_meta.p + 4, &len, 4, cudaMemcpyHostToDevice,
+                               m.stream));
+    CUDA_CHECK(cudaStreamSynchronize(m.stream));
+    is_trained = true;
+}
+
+void IndexIVFFlatB200::get_centroids(float* out) const {
+    std::lock_guard<std::mutex> lock(mu_);
+    B200_THROW_IF_NOT_MSG(is_trained, "index not trained");
+    std::memcpy(out, impl_->h_centroids.data(), impl_->h_centroids.size() * sizeof(float));
+}
+
+void IndexIVFFlatB200::set_list_range(size_t lo, size_t hi) {
+    std::lock_guard<std::mutex> lock(mu_);
+    B200_THROW_IF_NOT_MSG(lo <= hi && hi <= nlist, "invalid list range");
+    B200_THROW_IF_NOT_MSG(impl_->nstored == 0, "set_list_range must precede add");
+    impl_->list_lo = lo;
+    impl_->list_hi = hi;
+}
+
+void IndexIVFFlatB200::reset() {
+    std::lock_guard<std::mutex> lock(mu_);
+    DeviceGuard g(device_);
+    Impl& m = *impl_;
+    CUDA_CHECK(cudaStreamSynchronize(m.stream));
+    m.slab.release();
+    m.ids.release();
+    m.slab_blocks = 0;
+    m.nstored = 0;
+    std::fill(m.h_blk0.begin(), m.h_blk0.end(), 0u);
+    std::fill(m.h_len.begin(), m.h_len.end(), 0);
+    CUDA_CHECK(cudaMemset(m.list_blk0.p, 0, sizeof(uint32_t) * nlist));
+    CUDA_CHECK(cudaMemset(m.list_len.p, 0, sizeof(int32_t) * nlist));
+    ntotal = 0;
+}
+
+size_t IndexIVFFlatB200::get_list_size(size_t l) const {
+    std::lock_guard<std::mutex> lock(mu_);
+    B200_THROW_IF_NOT_MSG(l < nlist, "invalid list number");
+    return (size_t)impl_->h_len[l];
+}
+
+void IndexIVFFlatB200::get_list_ids(size_t l, int64_t* out) const {
+    std::lock_guard<std::mutex> lock(mu_);
+    DeviceGuard g(device_);
+    B200_THROW_IF_NOT_MSG(l < nlist, "invalid list number");
+    const Impl& m = *impl_;
+    const size_t len = (size_t)m.h_len[l];
+    if (len == 0)
+        return;
+    CUDA_CHECK(cudaStreamSynchronize(m.stream));
+    CUDA_CHECK(cudaMemcpy(out, m.ids.as<int64_t>() + (size_t)m.h_blk0[l] * kBlockRows,
+                          len * sizeof(int64_t), cudaMemcpyDeviceToHost));
+}
+
+void IndexIVFFlatB200::get_list_codes(size_t l, float* out) const {
+    std::lock_guard<std::mutex> lock(mu_);
+    DeviceGuard g(device_);
+    B200_THROW_IF_NOT_MSG(l < nlist, "invalid list number");
+    Impl& m = *impl_;
+    const size_t len = (size_t)m.h_len[l];
+    if (len == 0)
+        return;
+    m.dev_D.reserve(len * d * sizeof(float));
+    CUDA_CHECK(launch_gather_rows(m.slab.as<float>(), (int64_t)m.h_blk0[l] * kBlockRows,
+                                  (int64_t)len, d, m.nf4, m.dev_D.as<float>(), m.stream));
+    CUDA_CHECK(cudaMemcpyAsync(out, m.dev_D.p, len * d * sizeof(float), cudaMemcpyDeviceToHost,
+                               m.stream));
+    CUDA_CHECK(cudaStreamSynchronize(m.stream));
+}
+
+// ------------------------------------------------------------------------------------------------
+// search internals (all pointers are device pointers here)
+// ------------------------------------------------------------------------------------------------
+namespace {
+
+inline int64_t ceil_div(int64_t a, int64_t b) {
+    return (a + b - 1) / b;
+}
+
+} // namespace
+
+// K1 as a scan of the centroid table: the kc nearest centroids of each query, best first, ties by
+// centroid number as cmp2 orders them (faiss/IndexFlat.cpp:38-69 -> knn_L2sqr/knn_inner_product).
+static void run_coarse(int metric, int d, int nf4, size_t nlist, const Buffer& cent_slab,
+                       const Buffer& cent_meta, Buffer& cplan, Buffer& part, const float* xd,
+                       int64_t n, int kc, int32_t* out_ids32, int64_t* out_ids64, float* out_dis,
+                       cudaStream_t st) {
+    const ScanCfg cfg = choose_scan_cfg(nf4, kc);
+    const int64_t ngroups = ceil_div(n, cfg.rq);
+    const int64_t nblk = ceil_div((int64_t)nlist, kBlockRows);
+    int64_t S = ceil_div(kTargetScanItems, ngroups);
+    S = std::max<int64_t>(1, std::min<int64_t>(S, std::max<int64_t>(1, nblk / kScanRowsPerStep)));
+    S = std::min<int64_t>(S, 64);
+    part.reserve((size_t)n * S * kc * sizeof(uint64_t));
+    cplan.reserve(16);
+    int32_t* grp_start = cplan.as<int32_t>();
+    uint32_t* item_off = cplan.as<uint32_t>() + 2;
+    CUDA_CHECK(launch_plan_single(grp_start, item_off, (int)n, (uint32_t)(ngroups * S), st));
+    ScanArgs a;
+    a.slab = cent_slab.as<float4>();
+    a.list_blk0 = cent_meta.as<uint32_t>();
+    a.list_len = cent_meta.as<int32_t>() + 1;
+    a.grp_start = grp_start;
+    a.pair_query = nullptr;
+    a.item_off = item_off;
+    a.nlists = 1;
+    a.nsplit = (int)S;
+    a.k = kc;
+    a.cap = cfg.cap;
+    a.d = d;
+    a.nf4 = nf4;
+    a.queries = xd;
+    a.part = part.as<uint64_t>();
+    CUDA_CHECK(launch_ivf_scan(metric, cfg.rq, cfg.wpc, (uint32_t)(ngroups * S), a, st));
+    SelectArgs s;
+    s.part = part.as<uint64_t>();
+    s.slot_of = nullptr;
+    s.n = (int)n;
+    s.nseg = 1;
+    s.nsplit = (int)S;
+    s.kpart = kc;
+    s.k = kc;
+    s.metric = metric;
+    s.ids = nullptr;
+    s.out_dis = out_dis;
+    s.out_ids64 = out_ids64;
+    s.out_ids32 = out_ids32;
+    CUDA_CHECK(launch_select(s, st));
+}
+
+// device-side search of one batch: coarse ids given -> results written to device D/I
+struct BatchPlan {
+    ScanCfg cfg;
+    int64_t S;
+};
+
+static BatchPlan plan_batch(int nf4, int64_t k, int64_t nb, int64_t nprobe, int64_t nlists_owned,
+                            int64_t nstored) {
+    BatchPlan bp;
+    bp.cfg = choose_scan_cfg(nf4, (int)k);
+    const int64_t pairs = nb * nprobe;
+    const int64_t items_est =
+            std::max<int64_t>(1, std::max(ceil_div(pairs, bp.cfg.rq), std::min(pairs, nlists_owned)));
+    const int64_t avg_blocks =
+            std::max<int64_t>(1, nstored / std::max<int64_t>(1, nlists_owned) / kBlockRows);
+    int64_t S = ceil_div(kTargetScanItems, items_est);
+    S = std::max<int64_t>(1, std::min(S, std::max<int64_t>(1, avg_blocks / kScanRowsPerStep)));
+    bp.S = std::min<int64_t>(S, 32);
+    return bp;
+}
+
+void IndexIVFFlatB200::search(int64_t n, const float* x, int64_t k, float* D, int64_t* I) const {
+    search_preassigned(n, x, k, nullptr, nullptr, D, I, false);
+}
+
+void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
+                                          const int64_t* assign, const float* /*centroid_dis*/,
+                                          float* D, int64_t* I, bool store_pairs) const {
+    std::lock_guard<std::mutex> lock(mu_);
+    DeviceGuard g(device_);
+    Impl& m = *impl_;
+    // argument checks of IndexIVF::search / search_preassigned (faiss/IndexIVF.cpp:310-318,410-414)
+    B200_THROW_IF_NOT_MSG(k > 0, "k > 0");
+    B200_THROW_IF_NOT_MSG(is_trained, "index not trained");
+    B200_THROW_IF_NOT_MSG(!store_pairs, "store_pairs is not supported on the B200 path");
+    const int64_t np = (int64_t)std::min(nlist, nprobe);
+    B200_THROW_IF_NOT_MSG(np > 0, "nprobe > 0");
+    B200_THROW_IF_NOT_MSG(k <= 2048 && np <= 2048, "k and nprobe are limited to 2048");
+    for (double& v : m.last_ms)
+        v = 0;
+    if (n == 0)
+        return;
+    B200_THROW_IF_NOT_MSG(x && D && I, "null buffer");
+
+    const bool x_dev = is_device_pointer(x), D_dev = is_device_pointer(D),
+               I_dev = is_device_pointer(I);
+    const bool a_dev = assign && is_device_pointer(assign);
+    const int64_t nlists_owned = (int64_t)(m.list_hi - m.list_lo);
+
+    // batch size: bound the partial-candidate scratch
+    int64_t nb = std::min<int64_t>(n, 32768);
+    BatchPlan bp = plan_batch(m.nf4, k, nb, np, nlists_owned, m.nstored);
+    while (nb > 1 && (size_t)nb * np * bp.S * k * sizeof(uint64_t) > ((size_t)2 << 30)) {
+        nb = (nb + 1) / 2;
+        bp = plan_batch(m.nf4, k, nb, np, nlists_owned, m.nstored);
+    }
+    cudaStream_t st = m.stream;
+    unsigned long long* dstats = m.dev_stats.as<unsigned long long>();
+
+    for (int64_t i0 = 0; i0 < n; i0 += nb) {
+        const int64_t ni = std::min(nb, n - i0);
+        const int64_t pairs = ni * np;
+        bp = plan_batch(m.nf4, k, ni, np, nlists_owned, m.nstored);
+        CUDA_CHECK(cudaEventRecord(m.ev[0], st));
+        // queries
+        const float* xd = x + i0 * d;
+        if (!x_dev) {
+            m.dev_x.reserve((size_t)ni * d * sizeof(float));
+            CUDA_CHECK(cudaMemcpyAsync(m.dev_x.p, xd, (size_t)ni * d * sizeof(float),
+                                       cudaMemcpyHostToDevice, st));
+            xd = m.dev_x.as<float>();
+        }
+        float* Dd = D + i0 * k;
+        int64_t* Id = I + i0 * k;
+        if (!D_dev) {
+            m.dev_D.reserve((size_t)ni * k * sizeof(float));
+            Dd = m.dev_D.as<float>();
+        }
+        if (!I_dev) {
+            m.dev_I.reserve((size_t)ni * k * sizeof(int64_t));
+            Id = m.dev_I.as<int64_t>();
+        }
+        // stage 1: probe table
+        m.coarse_ids.reserve((size_t)pairs * sizeof(int32_t));
+        m.coarse_dis.reserve((size_t)pairs * sizeof(float));
+        if (assign) {
+            const int64_t* ad = assign + i0 * np;
+            if (!a_dev) {
+                m.dev_assign64.reserve((size_t)pairs * sizeof(int64_t));
+                CUDA_CHECK(cudaMemcpyAsync(m.dev_assign64.p, ad, (size_t)pairs * sizeof(int64_t),
+                                           cudaMemcpyHostToDevice, st));
+                ad = m.dev_assign64.as<int64_t>();
+            }
+            CUDA_CHECK(launch_i64_to_i32(ad, m.coarse_ids.as<int32_t>(), pairs, 0, (int32_t)nlist,
+                                         dstats + 3, st));
+        } else {
+            run_coarse(metric_type, d, m.nf4, nlist, m.cent_slab, m.cent_meta, m.cplan, m.part, xd,
+                       ni, (int)np, m.coarse_ids.as<int32_t>(), nullptr, m.coarse_dis.as<float>(),
+                       st);
+        }
+        CUDA_CHECK(cudaEventRecord(m.ev[1], st));
+        // stage 2: invert the probe table, scan the lists
+        m.count.reserve(nlist * sizeof(int32_t));
+        m.fill.reserve(nlist * sizeof(int32_t));
+        m.grp_start.reserve((nlist + 1) * sizeof(int32_t));
+        m.item_off.reserve((nlist + 1) * sizeof(uint32_t));
+        m.pair_query.reserve((size_t)pairs * sizeof(int32_t));
+        m.slot_of.reserve((size_t)pairs * sizeof(int32_t));
+        m.part.reserve((size_t)pairs * bp.S * k * sizeof(uint64_t));
+        PlanArgs pa;
+        pa.coarse_ids = m.coarse_ids.as<int32_t>();
+        pa.n = (int)ni;
+        pa.nprobe = (int)np;
+        pa.nlists = (int)nlist;
+        pa.list_len = m.list_len.as<int32_t>();
+        pa.count = m.count.as<int32_t>();
+        pa.fill = m.fill.as<int32_t>();
+        pa.grp_start = m.grp_start.as<int32_t>();
+        pa.item_off = m.item_off.as<uint32_t>();
+        pa.pair_query = m.pair_query.as<int32_t>();
+        pa.slot_of = m.slot_of.as<int32_t>();
+        pa.rq = bp.cfg.rq;
+        pa.nsplit = (int)bp.S;
+        pa.stats = dstats;
+        CUDA_CHECK(launch_plan(pa, st));
+        CUDA_CHECK(cudaEventRecord(m.ev[2], st));
+        ScanArgs sa;
+        sa.slab = m.slab.as<float4>();
+        sa.list_blk0 = m.list_blk0.as<uint32_t>();
+        sa.list_len = m.list_len.as<int32_t>();
+        sa.grp_start = pa.grp_start;
+        sa.pair_query = pa.pair_query;
+        sa.item_off = pa.item_off;
+        sa.nlists = (int)nlist;
+        sa.nsplit = (int)bp.S;
+        sa.k = (int)k;
+        sa.cap = bp.cfg.cap;
+        sa.d = d;
+        sa.nf4 = m.nf4;
+        sa.queries = xd;
+        sa.part = m.part.as<uint64_t>();
+        const int64_t max_items =
+                (ceil_div(pairs, bp.cfg.rq) + std::min<int64_t>(pairs, (int64_t)nlist)) * bp.S;
+        CUDA_CHECK(launch_ivf_scan(metric_type, bp.cfg.rq, bp.cfg.wpc, (uint32_t)max_items, sa, st));
+        CUDA_CHECK(cudaEventRecord(m.ev[3], st));
+        // stage 3: per-query k-select, row -> id
+        SelectArgs se;
+        se.part = m.part.as<uint64_t>();
+        se.slot_of = pa.slot_of;
+        se.n = (int)ni;
+        se.nseg = (int)np;
+        se.nsplit = (int)bp.S;
+        se.kpart = (int)k;
+        se.k = (int)k;
+        se.metric = metric_type;
+        se.ids = m.ids.as<int64_t>();
+        se.out_dis = Dd;
+        se.out_ids64 = Id;
+        se.out_ids32 = nullptr;
+        CUDA_CHECK(launch_select(se, st));
+        CUDA_CHECK(cudaEventRecord(m.ev[4], st));
+        if (!D_dev)
+            CUDA_CHECK(cudaMemcpyAsync(D + i0 * k, Dd, (size_t)ni * k * sizeof(float),
+                                       cudaMemcpyDeviceToHost, st));
+        if (!I_dev)
+            CUDA_CHECK(cudaMemcpyAsync(I + i0 * k, Id, (size_t)ni * k * sizeof(int64_t),
+                                       cudaMemcpyDeviceToHost, st));
+        CUDA_CHECK(cudaEventRecord(m.ev[5], st));
+        CUDA_CHECK(cudaMemcpyAsync(m.host_stats.p, dstats, 4 * sizeof(unsigned long long),
+                                   cudaMemcpyDeviceToHost, st));
+        CUDA_CHECK(cudaStreamSynchronize(st));
+        float ms;
+        for (int s = 0; s < 4; ++s) {
+            CUDA_CHECK(cudaEventElapsedTime(&ms, m.ev[s], m.ev[s + 1]));
+            m.last_ms[s] += ms;
+        }
+        CUDA_CHECK(cudaEventElapsedTime(&ms, m.ev[0], m.ev[5]));
+        m.last_ms[4] += ms;
+    }
+    const unsigned long long* hs = m.host_stats.as<unsigned long long>();
+    m.stats.nq = (size_t)hs[0];
+    m.stats.nlist = (size_t)hs[1];
+    m.stats.ndis = (size_t)hs[2];
+    m.stats.quantization_time += m.last_ms[0];
+    m.stats.search_time += m.last_ms[4];
+    if (hs[3] != 0) {
+        CUDA_CHECK(cudaMemset(dstats + 3, 0, sizeof(unsigned long long)));
+        // faiss/IndexIVF.cpp:520-524
+        throw B200Exception("Invalid key in search_preassigned (key >= nlist)");
+    }
+}
+
+void IndexIVFFlatB200::quantize(int64_t n, const float* x, int64_t kc, float* Dq,
+                                int64_t* Iq) const {
+    std::lock_guard<std::mutex> lock(mu_);
+    DeviceGuard g(device_);
+    Impl& m = *impl_;
+    B200_THROW_IF_NOT_MSG(is_trained, "index not trained");
+    B200_THROW_IF_NOT_MSG(kc > 0 && kc <= 2048, "nprobe must be in [1, 2048]");
+    if (n == 0)
+        return;
+    const bool x_dev = is_device_pointer(x), D_dev = is_device_pointer(Dq),
+               I_dev = is_device_pointer(Iq);
+    cudaStream_t st = m.stream;
+    const int64_t nb = std::min<int64_t>(n, 32768);
+    for (int64_t i0 = 0; i0 < n; i0 += nb) {
+        const int64_t ni = std::min(nb, n - i0);
+        const float* xd = x + i0 * d;
+        if (!x_dev) {
+            m.dev_x.reserve((size_t)ni * d * sizeof(float));
+            CUDA_CHECK(cudaMemcpyAsync(m.dev_x.p, xd, (size_t)ni * d * sizeof(float),
+                                       cudaMemcpyHostToDevice, st));
+            xd = m.dev_x.as<float>();
+        }
+        float* Dd = Dq + i0 * kc;
+        int64_t* Id = Iq + i0 * kc;
+        if (!D_dev) {
+            m.dev_D.reserve((size_t)ni * kc * sizeof(float));
+            Dd = m.dev_D.as<float>();
+        }
+        if (!I_dev) {
+            m.dev_I.reserve((size_t)ni * kc * sizeof(int64_t));
+            Id = m.dev_I.as<int64_t>();
+        }
+        run_coarse(metric_type, d, m.nf4, nlist, m.cent_slab, m.cent_meta, m.cplan, m.part, xd, ni,
+                   (int)kc, nullptr, Id, Dd, st);
+        if (!D_dev)
+            CUDA_CHECK(cudaMemcpyAsync(Dq + i0 * kc, Dd, (size_t)ni * kc * sizeof(float),
+                                       cudaMemcpyDeviceToHost, st));
+        if (!I_dev)
+            CUDA_CHECK(cudaMemcpyAsync(Iq + i0 * kc, Id, (size_t)ni * kc * sizeof(int64_t),
+                                       cudaMemcpyDeviceToHost, st));
+        CUDA_CHECK(cudaStreamSynchronize(st));
+    }
+}
+
+IndexIVFStatsB200 IndexIVFFlatB200::get_stats() const {
+    std::lock_guard<std::mutex> lock(mu_);
+    return impl_->stats;
+}
+
+void IndexIVFFlatB200::reset_stats() {
+    std::lock_guard<std::mutex> lock(mu_);
+    DeviceGuard g(device_);
+    CUDA_CHECK(cudaStreamSynchronize(impl_->stream));
+    CUDA_CHECK(cudaMemset(impl_->dev_stats.p, 0, 4 * sizeof(unsigned long long)));
+    impl_->stats = IndexIVFStatsB200();
+}
+
+void IndexIVFFlatB200::last_timings(double* ms5) const {
+    std::lock_guard<std::mutex> lock(mu_);
+    for (int i = 0; i < 5; ++i)
+        ms5[i] = impl_->last_ms[i];
+}
+
+// ------------------------------------------------------------------------------------------------
+// build path: IndexIVF::add_with_ids (faiss/IndexIVF.cpp:191-241) -> IndexIVFFlat::add_core
+// (faiss/IndexIVFFlat.cpp:46-91). Assignment = top-1 of the coarse quantizer on device; placement
+// keeps input order inside every list (each reference list is appended by exactly one thread).
+// ------------------------------------------------------------------------------------------------
+void IndexIVFFlatB200::add_with_ids(int64_t n, const float* x, const int64_t* xids) {
+    add_core(n, x, xids, nullptr);
+}
+
+void IndexIVFFlatB200::add_core(int64_t n, const float* x, const int64_t* xids,
+                                const int64_t* assign) {
+    std::lock_guard<std::mutex> lock(mu_);
+    DeviceGuard g(device_);
+    Impl& m = *impl_;
+    B200_THROW_IF_NOT_MSG(is_trained, "index not trained"); // IndexIVFFlat.cpp:52
+    if (n == 0)
+        return;
+    B200_THROW_IF_NOT_MSG(x != nullptr, "null vectors");
+    cudaStream_t st = m.stream;
+    const bool x_dev = is_device_pointer(x);
+    const bool ids_dev = xids && is_device_pointer(xids);
+    const bool a_dev = assign && is_device_pointer(assign);
+    const int64_t chunk = 1 << 20;
+
+    // pass 1: list number of every vector, on the host
+    std::vector<int64_t> h_assign((size_t)n);
+    if (assign) {
+        if (a_dev)
+            CUDA_CHECK(cudaMemcpy(h_assign.data(), assign, (size_t)n * sizeof(int64_t),
+                                  cudaMemcpyDeviceToHost));
+        else
+            std::memcpy(h_assign.data(), assign, (size_t)n * sizeof(int64_t));
+    } else {
+        for (int64_t i0 = 0; i0 < n; i0 += chunk) {
+            const int64_t ni = std::min(chunk, n - i0);
+            const float* xd = x + i0 * d;
+            if (!x_dev) {
+                m.dev_x.reserve((size_t)ni * d * sizeof(float));
+                CUDA_CHECK(cudaMemcpyAsync(m.dev_x.p, xd, (size_t)ni * d * sizeof(float),
+                                           cudaMemcpyHostToDevice, st));
+                xd = m.dev_x.as<float>();
+            }
+            m.dev_I.reserve((size_t)ni * sizeof(int64_t));
+            m.dev_D.reserve((size_t)ni * sizeof(float));
+            // quantizer->assign == search with k = 1 (faiss/Index.cpp:84-88)
+            for (int64_t j0 = 0; j0 < ni; j0 += 32768) {
+                const int64_t nj = std::min<int64_t>(32768, ni - j0);
+                run_coarse(metric_type, d, m.nf4, nlist, m.cent_slab, m.cent_meta, m.cplan, m.part,
+                           xd + j0 * d, nj, 1, nullptr, m.dev_I.as<int64_t>() + j0,
+                           m.dev_D.as<float>() + j0, st);
+            }
+            CUDA_CHECK(cudaMemcpyAsync(h_assign.data() + i0, m.dev_I.p,
+                                       (size_t)ni * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+            CUDA_CHECK(cudaStreamSynchronize(st));
+        }
+    }
+
+    // host: new list lengths and the destination row of every vector (stable within a list)
+    std::vector<int32_t> new_len(m.h_len);
+    std::vector<int64_t> dst((size_t)n);
+    int64_t nadd = 0;
+    for (int64_t i = 0; i < n; ++i) {
+        const int64_t l = h_assign[(size_t)i];
+        if (l < 0 || (size_t)l < m.list_lo || (size_t)l >= m.list_hi) {
+            B200_THROW_IF_NOT_MSG(l < (int64_t)nlist, "list number out of range in add_core");
+            dst[(size_t)i] = -1;
+            continue;
+        }
+        dst[(size_t)i] = new_len[(size_t)l]++; // offset in list for now
+        nadd++;
+    }
+    std::vector<uint32_t> new_blk0(nlist);
+    size_t blocks = 0;
+    for (size_t l = 0; l < nlist; ++l) {
+        new_blk0[l] = (uint32_t)blocks;
+        blocks += ((size_t)new_len[l] + kBlockRows - 1) / kBlockRows;
+    }
+    B200_THROW_IF_NOT_MSG(blocks * kBlockRows < ((size_t)1 << 32),
+                          "more than 2^32 rows on one device");
+    for (int64_t i = 0; i < n; ++i) {
+        const int64_t l = h_assign[(size_t)i];
+        if (dst[(size_t)i] >= 0)
+            dst[(size_t)i] += (int64_t)new_blk0[(size_t)l] * kBlockRows;
+    }
+
+    // device: new slab, old blocks moved, new rows scattered
+    Buffer nslab, nids, nblk0;
+    const size_t slab_bytes = blocks * m.nf4 * kBlockRows * sizeof(float4);
+    nslab.reserve(std::max<size_t>(slab_bytes, 16));
+    nids.reserve(std::max<size_t>(blocks * kBlockRows * sizeof(int64_t), 16));
+    nblk0.reserve(nlist * sizeof(uint32_t));
+    CUDA_CHECK(cudaMemsetAsync(nslab.p, 0, slab_bytes, st));
+    CUDA_CHECK(cudaMemsetAsync(nids.p, 0xff, blocks * kBlockRows * sizeof(int64_t), st));
+    CUDA_CHECK(cudaMemcpyAsync(nblk0.p, new_blk0.data(), nlist * sizeof(uint32_t),
+                               cudaMemcpyHostToDevice, st));
+    if (m.nstored > 0)
+        CUDA_CHECK(launch_move_blocks(m.slab.as<float4>(), m.ids.as<int64_t>(),
+                                      m.list_blk0.as<uint32_t>(), m.list_len.as<int32_t>(),
+                                      nblk0.as<uint32_t>(), (int)nlist, m.nf4, nslab.as<float4>(),
+                                      nids.as<int64_t>(), st));
+    for (int64_t i0 = 0; i0 < n; i0 += chunk) {
+        const int64_t ni = std::min(chunk, n - i0);
+        const float* xd = x + i0 * d;
+        if (!x_dev) {
+            m.dev_x.reserve((size_t)ni * d * sizeof(float));
+            CUDA_CHECK(cudaMemcpyAsync(m.dev_x.p, xd, (size_t)ni * d * sizeof(float),
+                                       cudaMemcpyHostToDevice, st));
+            xd = m.dev_x.as<float>();
+        }
+        const int64_t* idd = nullptr;
+        if (xids) {
+            idd = xids + i0;
+            if (!ids_dev) {
+                m.dev_I.reserve((size_t)ni * sizeof(int64_t));
+                CUDA_CHECK(cudaMemcpyAsync(m.dev_I.p, idd, (size_t)ni * sizeof(int64_t),
+                                           cudaMemcpyHostToDevice, st));
+                idd = m.dev_I.as<int64_t>();
+            }
+        }
+        m.dev_assign64.reserve((size_t)ni * sizeof(int64_t));
+        CUDA_CHECK(cudaMemcpyAsync(m.dev_assign64.p, dst.data() + i0, (size_t)ni * sizeof(int64_t),
+                                   cudaMemcpyHostToDevice, st));
+        CUDA_CHECK(launch_scatter_rows(xd, idd, m.dev_assign64.as<int64_t>(), ni, d, m.nf4,
+                                       nslab.as<float>(), nids.as<int64_t>(), ntotal + i0, st));
+        CUDA_CHECK(cudaStreamSynchronize(st)); // staging buffers are reused by the next chunk
+    }
+    CUDA_CHECK(cudaMemcpyAsync(m.list_len.p, new_len.data(), nlist * sizeof(int32_t),
+                               cudaMemcpyHostToDevice, st));
+    CUDA_CHECK(cudaMemcpyAsync(m.list_blk0.p, new_blk0.data(), nlist * sizeof(uint32_t),
+                               cudaMemcpyHostToDevice, st));
+    CUDA_CHECK(cudaStreamSynchronize(st));
+    m.slab.release();
+    m.ids.release();
+    m.slab = nslab;
+    m.ids = nids;
+    nblk0.release();
+    m.h_len.swap(new_len);
+    m.h_blk0.swap(new_blk0);
+    m.slab_blocks = blocks;
+    m.nstored += nadd;
+    ntotal += n; // IndexIVFFlat.cpp:90: every input vector counts, skipped or not
+}
+
+void merge_knn_results(int metric, int nshard, int64_t n, int64_t k, const float* all_D,
+                       const int64_t* all_I, float* D, int64_t* I, int device, cudaStream_t st) {
+    B200_THROW_IF_NOT_MSG(nshard > 0 && nshard <= 256, "nshard must be in [1, 256]");
+    B200_THROW_IF_NOT_MSG(k > 0, "k > 0");
+    if (n == 0)
+        return;
+    DeviceGuard g(device);
+    const size_t cnt = (size_t)nshard * n * k;
+    const bool in_dev = is_device_pointer(all_D) && is_device_pointer(all_I);
+    const bool out_dev = is_device_pointer(D) && is_device_pointer(I);
+    Buffer bD, bI, oD, oI;
+    const float* dD = all_D;
+    const int64_t* dI = all_I;
+    if (!in_dev) {
+        bD.reserve(cnt * sizeof(float));
+        bI.reserve(cnt * sizeof(int64_t));
+        CUDA_CHECK(cudaMemcpyAsync(bD.p, all_D, cnt * sizeof(float), cudaMemcpyHostToDevice, st));
+        CUDA_CHECK(cudaMemcpyAsync(bI.p, all_I, cnt * sizeof(int64_t), cudaMemcpyHostToDevice, st));
+        dD = bD.as<float>();
+        dI = bI.as<int64_t>();
+    }
+    float* rD = D;
+    int64_t* rI = I;
+    if (!out_dev) {
+        oD.reserve((size_t)n * k * sizeof(float));
+        oI.reserve((size_t)n * k * sizeof(int64_t));
+        rD = oD.as<float>();
+        rI = oI.as<int64_t>();
+    }
+    CUDA_CHECK(launch_merge_shards(metric, nshard, (int)n, (int)k, dD, dI, rD, rI, st));
+    if (!out_dev) {
+        CUDA_CHECK(cudaMemcpyAsync(D, rD, (size_t)n * k * sizeof(float), cudaMemcpyDeviceToHost, st));
+        CUDA_CHECK(cudaMemcpyAsync(I, rI, (size_t)n * k * sizeof(int64_t), cudaMemcpyDeviceToHost,
+                                   st));
+    }
+    CUDA_CHECK(cudaStreamSynchronize(st));
+    bD.release();
+    bI.release();
+    oD.release();
+    oI.release();
+}
+
+} // namespace b200ivf

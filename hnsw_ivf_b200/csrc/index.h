@@ -1,0 +1,91 @@
+// index.h -- host-side C++ object behind the C-ABI: a device-resident IndexIVFFlat with its flat
+// coarse quantizer. Mirrors the reference's interface for this one path (same names, argument
+// meaning and error behaviour): faiss/IndexIVFFlat.h:26-70, faiss/IndexIVF.h:44-96,303-337,
+// faiss/Index.h:77-148.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <mutex>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+namespace b200ivf {
+
+// the FaissException of this library (C-ABI code -2, c_api/error_c.h:26)
+struct B200Exception : std::runtime_error {
+    using std::runtime_error::runtime_error;
+};
+
+struct IndexIVFStatsB200 { // faiss/IndexIVF.h:567-580
+    size_t nq = 0, nlist = 0, ndis = 0, nheap_updates = 0;
+    double quantization_time = 0, search_time = 0;
+};
+
+// grow-only device / pinned-host buffer
+struct Buffer {
+    void* p = nullptr;
+    size_t bytes = 0;
+    bool pinned_host = false;
+    void reserve(size_t n);
+    void release();
+    template <class T>
+    T* as() const {
+        return reinterpret_cast<T*>(p);
+    }
+};
+
+class IndexIVFFlatB200 {
+  public:
+    IndexIVFFlatB200(size_t d, size_t nlist, int metric, int device);
+    ~IndexIVFFlatB200();
+    IndexIVFFlatB200(const IndexIVFFlatB200&) = delete;
+    IndexIVFFlatB200& operator=(const IndexIVFFlatB200&) = delete;
+
+    // ---- fields with the reference's names (faiss/Index.h:81-90, faiss/IndexIVF.h:44,95) ----
+    int d;
+    size_t nlist;
+    int metric_type;
+    size_t nprobe = 1;
+    int64_t ntotal = 0;
+    bool is_trained = false;
+
+    void set_centroids(const float* c);
+    void get_centroids(float* out) const;
+    void set_list_range(size_t lo, size_t hi);
+    void add_with_ids(int64_t n, const float* x, const int64_t* xids);
+    void add_core(int64_t n, const float* x, const int64_t* xids, const int64_t* assign);
+    void reset();
+    size_t get_list_size(size_t l) const;
+    void get_list_ids(size_t l, int64_t* out) const;
+    void get_list_codes(size_t l, float* out) const;
+
+    void search(int64_t n, const float* x, int64_t k, float* D, int64_t* I) const;
+    void search_preassigned(int64_t n, const float* x, int64_t k, const int64_t* assign,
+                            const float* centroid_dis, float* D, int64_t* I,
+                            bool store_pairs) const;
+    void quantize(int64_t n, const float* x, int64_t nprobe, float* Dq, int64_t* Iq) const;
+
+    IndexIVFStatsB200 get_stats() const;
+    void reset_stats();
+    void last_timings(double* ms5) const;
+    void set_stream(cudaStream_t s);
+
+    int device() const {
+        return device_;
+    }
+
+  private:
+    struct Impl;
+    Impl* impl_;
+    int device_;
+    mutable std::mutex mu_;
+};
+
+// merge of per-shard tables (faiss/utils/Heap.cpp:158-232) on `device`
+void merge_knn_results(int metric, int nshard, int64_t n, int64_t k, const float* all_D,
+                       const int64_t* all_I, float* D, int64_t* I, int device, cudaStream_t st);
+
+} // namespace b200ivf

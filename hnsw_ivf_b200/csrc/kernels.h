@@ -1,0 +1,90 @@
+// kernels.h -- launch interfaces of the hand-written sm_100a kernels (host side).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b200ivf {
+
+// ---- K2 (and K1 as a scan of the centroid table): ivf_scan ------------------------------------
+// One WARP per work item (list, sub-group of <= RQ queries probing it, row split). Replaces
+// IVFFlatScanner::scan_codes (faiss/IndexIVFFlat.cpp:155-179) run per (query, probe) by
+// IndexIVF::search_preassigned (faiss/IndexIVF.cpp:597-631).
+struct ScanArgs {
+    const float4* slab;         // interleaved 32-row blocks (common.cuh)
+    const uint32_t* list_blk0;  // [nlists] first block of each list
+    const int32_t* list_len;    // [nlists] rows in each list
+    const int32_t* grp_start;   // [nlists+1] first pair slot of each list's query group
+    const int32_t* pair_query;  // [npairs] query number of each pair slot (nullptr: identity)
+    const uint32_t* item_off;   // [nlists+1] exclusive prefix of ceil(count/RQ)*nsplit
+    int nlists;
+    int nsplit;                 // row splits per list
+    int k;                      // candidates kept per (pair, split)
+    int cap;                    // per-query candidate buffer entries, power of two >= k + 32
+    int d;                      // true dimension
+    int nf4;                    // float4 columns per row = ceil(d/4)
+    const float* queries;       // [n][d] row-major, device
+    uint64_t* part;             // [npairs][nsplit][k] keys out
+};
+
+// rq in {1,4,8}; warps_per_cta chosen by the caller so that shared memory fits.
+size_t scan_smem_bytes(int rq, int warps_per_cta, int nf4, int cap);
+cudaError_t launch_ivf_scan(int metric, int rq, int warps_per_cta, uint32_t max_items,
+                            const ScanArgs& a, cudaStream_t st);
+
+// ---- planning: invert the probe table into per-list query groups -------------------------------
+struct PlanArgs {
+    const int32_t* coarse_ids;  // [n][nprobe], -1 = no probe
+    int n, nprobe, nlists;
+    const int32_t* list_len;    // [nlists]
+    int32_t* count;             // [nlists] scratch (zeroed by launch_plan)
+    int32_t* fill;              // [nlists] scratch (zeroed by launch_plan)
+    int32_t* grp_start;         // [nlists+1] out
+    uint32_t* item_off;         // [nlists+1] out
+    int32_t* pair_query;        // [n*nprobe] out
+    int32_t* slot_of;           // [n*nprobe] out: pair slot of (q,p) or -1
+    int rq, nsplit;
+    unsigned long long* stats;  // [4] += {nq, nlist visited, ndis, invalid keys}
+};
+cudaError_t launch_plan(const PlanArgs& a, cudaStream_t st);
+// the one-list plan used when the "list" is the centroid table and every query probes it
+cudaError_t launch_plan_single(int32_t* grp_start, uint32_t* item_off, int n, uint32_t items,
+                               cudaStream_t st);
+
+// ---- K3: per-query k-select over the partial candidate lists ------------------------------------
+// Replaces heap_reorder (faiss/utils/Heap.h:420-450) / the CPU heap of search_preassigned.
+struct SelectArgs {
+    const uint64_t* part;       // [slots][nsplit][kpart]
+    const int32_t* slot_of;     // [n][nseg] pair slot or -1 (nullptr: slot = q, nseg must be 1)
+    int n, nseg, nsplit, kpart; // kpart = entries per partial list
+    int k;                      // results per query
+    int metric;
+    const int64_t* ids;         // slab row -> user id (nullptr: id = row)
+    float* out_dis;             // [n][k]
+    int64_t* out_ids64;         // [n][k] or nullptr
+    int32_t* out_ids32;         // [n][k] or nullptr
+};
+cudaError_t launch_select(const SelectArgs& a, cudaStream_t st);
+
+// ---- multi-shard merge (faiss/utils/Heap.cpp:158-232 semantics, on device) ---------------------
+cudaError_t launch_merge_shards(int metric, int nshard, int n, int k, const float* all_dis,
+                                const int64_t* all_ids, float* out_dis, int64_t* out_ids,
+                                cudaStream_t st);
+
+// ---- layout kernels (build path) ----------------------------------------------------------------
+// scatter row-major vectors into the interleaved slab: dst_row[i] < 0 skips vector i
+cudaError_t launch_scatter_rows(const float* x, const int64_t* xids, const int64_t* dst_row,
+                                int64_t n, int d, int nf4, float* slab, int64_t* ids,
+                                int64_t id_base, cudaStream_t st);
+// move whole 32-row blocks of every list from an old slab to a new one
+cudaError_t launch_move_blocks(const float4* old_slab, const int64_t* old_ids,
+                               const uint32_t* old_blk0, const int32_t* old_len,
+                               const uint32_t* new_blk0, int nlists, int nf4, float4* new_slab,
+                               int64_t* new_ids, cudaStream_t st);
+// gather a list back to row-major (get_list / reconstruct)
+cudaError_t launch_gather_rows(const float* slab, int64_t row0, int64_t nrows, int d, int nf4,
+                               float* out, cudaStream_t st);
+cudaError_t launch_i64_to_i32(const int64_t* in, int32_t* out, int64_t n, int32_t lo, int32_t hi,
+                              unsigned long long* bad, cudaStream_t st);
+
+} // namespace b200ivf

@@ -1,0 +1,130 @@
+// layout.cu -- build-path kernels: put row-major fp32 vectors (the reference's code bytes,
+// ArrayInvertedLists::codes, faiss/invlists/InvertedLists.h:243-245) into the device slab's
+// interleaved 32-row blocks (common.cuh) and back.
+#include "common.cuh"
+#include "kernels.h"
+
+#include <algorithm>
+
+namespace b200ivf {
+
+namespace {
+
+// one warp per vector: lane strides over dims
+__global__ void scatter_rows_kernel(const float* __restrict__ x, const int64_t* __restrict__ xids,
+                                    const int64_t* __restrict__ dst_row, int64_t n, int d, int nf4,
+                                    float* __restrict__ slab, int64_t* __restrict__ ids,
+                                    int64_t id_base) {
+    const int lane = threadIdx.x & 31;
+    const int64_t w0 = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+    const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t i = w0; i < n; i += nw) {
+        const int64_t row = dst_row[i];
+        if (row < 0)
+            continue;
+        const float* xi = x + i * d;
+        for (int dd = lane; dd < d; dd += 32)
+            slab[slab_float_index((size_t)row, dd, nf4)] = xi[dd];
+        if (lane == 0)
+            ids[row] = xids ? xids[i] : id_base + i;
+    }
+}
+
+// one CTA per list: whole blocks are position independent, so they move as plain float4 copies
+__global__ void move_blocks_kernel(const float4* __restrict__ old_slab,
+                                   const int64_t* __restrict__ old_ids,
+                                   const uint32_t* __restrict__ old_blk0,
+                                   const int32_t* __restrict__ old_len,
+                                   const uint32_t* __restrict__ new_blk0, int nlists, int nf4,
+                                   float4* __restrict__ new_slab, int64_t* __restrict__ new_ids) {
+    for (int l = blockIdx.x; l < nlists; l += gridDim.x) {
+        const int len = old_len[l];
+        if (len == 0)
+            continue;
+        const int nb = (len + kBlockRows - 1) / kBlockRows;
+        const size_t nvec = (size_t)nb * nf4 * kBlockRows;
+        const float4* src = old_slab + (size_t)old_blk0[l] * nf4 * kBlockRows;
+        float4* dst = new_slab + (size_t)new_blk0[l] * nf4 * kBlockRows;
+        for (size_t i = threadIdx.x; i < nvec; i += blockDim.x)
+            dst[i] = src[i];
+        const int64_t* sid = old_ids + (size_t)old_blk0[l] * kBlockRows;
+        int64_t* did = new_ids + (size_t)new_blk0[l] * kBlockRows;
+        for (int i = threadIdx.x; i < len; i += blockDim.x)
+            did[i] = sid[i];
+    }
+}
+
+__global__ void gather_rows_kernel(const float* __restrict__ slab, int64_t row0, int64_t nrows,
+                                   int d, int nf4, float* __restrict__ out) {
+    const int64_t total = nrows * d;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / d;
+        const int dd = (int)(i % d);
+        out[i] = slab[slab_float_index((size_t)(row0 + r), dd, nf4)];
+    }
+}
+
+__global__ void i64_to_i32_kernel(const int64_t* __restrict__ in, int32_t* __restrict__ out,
+                                  int64_t n, int32_t lo, int32_t hi, unsigned long long* bad) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t v = in[i];
+        int32_t o;
+        if (v < 0) {
+            o = -1;
+        } else if (v >= hi || v < lo) {
+            o = -1;
+            if (bad)
+                atomicAdd(bad, 1ull);
+        } else {
+            o = (int32_t)v;
+        }
+        out[i] = o;
+    }
+}
+
+inline int grid_for(int64_t work, int threads) {
+    return (int)std::max<int64_t>(1, std::min<int64_t>((work + threads - 1) / threads, 148 * 16));
+}
+
+} // namespace
+
+cudaError_t launch_scatter_rows(const float* x, const int64_t* xids, const int64_t* dst_row,
+                                int64_t n, int d, int nf4, float* slab, int64_t* ids,
+                                int64_t id_base, cudaStream_t st) {
+    if (n == 0)
+        return cudaSuccess;
+    scatter_rows_kernel<<<grid_for(n * 32, 256), 256, 0, st>>>(x, xids, dst_row, n, d, nf4, slab,
+                                                               ids, id_base);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_move_blocks(const float4* old_slab, const int64_t* old_ids,
+                               const uint32_t* old_blk0, const int32_t* old_len,
+                               const uint32_t* new_blk0, int nlists, int nf4, float4* new_slab,
+                               int64_t* new_ids, cudaStream_t st) {
+    if (nlists == 0)
+        return cudaSuccess;
+    move_blocks_kernel<<<std::min(nlists, 148 * 8), 256, 0, st>>>(
+            old_slab, old_ids, old_blk0, old_len, new_blk0, nlists, nf4, new_slab, new_ids);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_gather_rows(const float* slab, int64_t row0, int64_t nrows, int d, int nf4,
+                               float* out, cudaStream_t st) {
+    if (nrows == 0)
+        return cudaSuccess;
+    gather_rows_kernel<<<grid_for(nrows * d, 256), 256, 0, st>>>(slab, row0, nrows, d, nf4, out);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_i64_to_i32(const int64_t* in, int32_t* out, int64_t n, int32_t lo, int32_t hi,
+                              unsigned long long* bad, cudaStream_t st) {
+    if (n == 0)
+        return cudaSuccess;
+    i64_to_i32_kernel<<<grid_for(n, 256), 256, 0, st>>>(in, out, n, lo, hi, bad);
+    return cudaGetLastError();
+}
+
+} // namespace b200ivf

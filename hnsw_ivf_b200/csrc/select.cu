@@ -1,0 +1,217 @@
+// select.cu -- K3: fused per-query k-select over the partial candidate lists left by the scan, and
+// the device-side merge of per-shard result tables.
+//
+// Replaces, for one query: the CPU result heap of search_preassigned (heap_heapify :607,
+// heap_replace_top via scan_codes, heap_reorder :625 of faiss/IndexIVF.cpp) and, for the coarse
+// quantizer, HeapBlockResultHandler::add_results/end_multiple (faiss/impl/ResultHandler.h:263-286).
+// Output contract kept from heap_reorder (faiss/utils/Heap.h:420-450):
+//   * best first; exact-distance ties ordered by cmp2: L2 -> ascending id, IP -> descending id
+//     (the CMin heap pops (min dis, min id) first and writes it to the tail);
+//   * fewer than k candidates: labels -1, distances FLT_MAX (L2) / -FLT_MAX (IP).
+#include "common.cuh"
+#include "kernels.h"
+
+#include <algorithm>
+
+namespace b200ivf {
+
+namespace {
+
+// One CTA per query. Shared memory: keys[M] then dis[k] then ids[k].
+__global__ void select_kernel(const SelectArgs a, int M) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint64_t* keys = reinterpret_cast<uint64_t*>(smem_raw);
+    int64_t* sid = reinterpret_cast<int64_t*>(keys + M);
+    float* sdis = reinterpret_cast<float*>(sid + a.k);
+
+    const int q = blockIdx.x;
+    const int t = threadIdx.x;
+    const int per_seg = a.nsplit * a.kpart; // keys per pair slot
+    const int64_t total = (int64_t)a.nseg * per_seg;
+
+    int kept = 0; // keys[0..kept) hold the running best, sorted
+    int64_t done = 0;
+    do {
+        const int room = M - kept; // M >= k + 32, so there is always room
+        const int64_t left = total - done;
+        const int take = left < (int64_t)room ? (int)left : room;
+        for (int i = t; i < room; i += blockDim.x) {
+            uint64_t key = kSentinelKey;
+            if (i < take) {
+                const int64_t c = done + i;
+                const int seg = (int)(c / per_seg);
+                const int within = (int)(c % per_seg);
+                const int slot = a.slot_of ? a.slot_of[(int64_t)q * a.nseg + seg] : q;
+                if (slot >= 0)
+                    key = a.part[(int64_t)slot * per_seg + within];
+            }
+            keys[kept + i] = key;
+        }
+        __syncthreads();
+        block_sort_keys(keys, M);
+        kept = a.k;
+        done += take;
+    } while (done < total);
+
+    // decode the k best, map rows to user ids
+    const bool l2 = a.metric == kMetricL2;
+    for (int i = t; i < a.k; i += blockDim.x) {
+        const uint64_t key = keys[i];
+        if (key == kSentinelKey) {
+            sdis[i] = l2 ? kNeutralScore : -kNeutralScore;
+            sid[i] = -1;
+        } else {
+            const float s = key_score(key);
+            sdis[i] = l2 ? s : -s;
+            const uint32_t row = key_row(key);
+            sid[i] = a.ids ? a.ids[row] : (int64_t)row;
+        }
+    }
+    __syncthreads();
+    // exact-distance ties: order by id the way cmp2 does (ascending for L2, descending for IP)
+    for (int i = t; i < a.k; i += blockDim.x) {
+        const float di = sdis[i];
+        const int64_t idi = sid[i];
+        int pos = i;
+        if (idi >= 0) {
+            int lo = i, hi = i;
+            while (lo > 0 && sdis[lo - 1] == di && sid[lo - 1] >= 0)
+                --lo;
+            while (hi + 1 < a.k && sdis[hi + 1] == di && sid[hi + 1] >= 0)
+                ++hi;
+            if (hi > lo) {
+                int before = 0;
+                for (int j = lo; j <= hi; ++j) {
+                    const int64_t idj = sid[j];
+                    const bool first = l2 ? (idj < idi) : (idj > idi);
+                    // equal ids (duplicates): keep the original relative order
+                    before += (first || (idj == idi && j < i)) ? 1 : 0;
+                }
+                pos = lo + before;
+            }
+        }
+        const int64_t o = (int64_t)q * a.k + pos;
+        a.out_dis[o] = di;
+        if (a.out_ids64)
+            a.out_ids64[o] = idi;
+        if (a.out_ids32)
+            a.out_ids32[o] = (int32_t)idi;
+    }
+}
+
+// One warp per query: merge nshard sorted (n,k) tables. Same output as merge_knn_results
+// (faiss/utils/Heap.cpp:158-232) except that exact ties across shards are ordered by id rather
+// than by shard number.
+__global__ void merge_shards_kernel(int metric, int nshard, int n, int k, const float* all_dis,
+                                    const int64_t* all_ids, float* out_dis, int64_t* out_ids) {
+    const int q = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (q >= n)
+        return;
+    const bool l2 = metric == kMetricL2;
+    const size_t stride = (size_t)n * k;
+    // lane s (and s+32, ...) owns the head pointer of shard s
+    const int per = (nshard + 31) / 32;
+    int head[8]; // up to 256 shards
+    for (int i = 0; i < per && i < 8; ++i)
+        head[i] = 0;
+    for (int j = 0; j < k; ++j) {
+        float best = 0.f;
+        int64_t best_id = -1;
+        int best_s = -1;
+        for (int i = 0; i < per && i < 8; ++i) {
+            const int s = lane + 32 * i;
+            if (s < nshard && head[i] < k) {
+                const size_t o = stride * s + (size_t)q * k + head[i];
+                const int64_t id = all_ids[o];
+                if (id >= 0) {
+                    const float dv = all_dis[o];
+                    bool better;
+                    if (best_s < 0)
+                        better = true;
+                    else if (dv != best)
+                        better = l2 ? (dv < best) : (dv > best);
+                    else
+                        better = l2 ? (id < best_id) : (id > best_id);
+                    if (better) {
+                        best = dv;
+                        best_id = id;
+                        best_s = s;
+                    }
+                }
+            }
+        }
+        // warp arg-best
+        for (int o = 16; o > 0; o >>= 1) {
+            const float od = __shfl_xor_sync(0xffffffffu, best, o);
+            const int64_t oid = __shfl_xor_sync(0xffffffffu, best_id, o);
+            const int os = __shfl_xor_sync(0xffffffffu, best_s, o);
+            bool take;
+            if (os < 0)
+                take = false;
+            else if (best_s < 0)
+                take = true;
+            else if (od != best)
+                take = l2 ? (od < best) : (od > best);
+            else if (oid != best_id)
+                take = l2 ? (oid < best_id) : (oid > best_id);
+            else
+                take = os < best_s;
+            if (take) {
+                best = od;
+                best_id = oid;
+                best_s = os;
+            }
+        }
+        if (best_s >= 0) {
+            if ((best_s & 31) == lane)
+                head[best_s >> 5]++;
+        }
+        if (lane == 0) {
+            const size_t o = (size_t)q * k + j;
+            if (best_s >= 0) {
+                out_dis[o] = best;
+                out_ids[o] = best_id;
+            } else {
+                out_dis[o] = l2 ? kNeutralScore : -kNeutralScore;
+                out_ids[o] = -1;
+            }
+        }
+    }
+}
+
+} // namespace
+
+cudaError_t launch_select(const SelectArgs& a, cudaStream_t st) {
+    if (a.n == 0)
+        return cudaSuccess;
+    const int64_t total = (int64_t)a.nseg * a.nsplit * a.kpart;
+    int M = pow2_ceil(a.k + (int)std::min<int64_t>(std::max<int64_t>(total, 32), 2048));
+    if (M < 64)
+        M = 64;
+    const size_t smem = (size_t)M * 8 + (size_t)a.k * 12 + 16;
+    int threads = std::min(512, std::max(64, M / 2));
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(select_kernel,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess)
+            return e;
+    }
+    select_kernel<<<a.n, threads, smem, st>>>(a, M);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_merge_shards(int metric, int nshard, int n, int k, const float* all_dis,
+                                const int64_t* all_ids, float* out_dis, int64_t* out_ids,
+                                cudaStream_t st) {
+    if (n == 0)
+        return cudaSuccess;
+    if (nshard > 256)
+        return cudaErrorInvalidValue;
+    const int wpb = 4;
+    merge_shards_kernel<<<(n + wpb - 1) / wpb, wpb * 32, 0, st>>>(metric, nshard, n, k, all_dis,
+                                                                 all_ids, out_dis, out_ids);
+    return cudaGetLastError();
+}
+
+} // namespace b200ivf

@@ -1,0 +1,126 @@
+/* b200ivf_c.h -- C-ABI of the B200-native IVF-Flat search path.
+ *
+ * Drop-in boundary for ONE path of the reference (faiss 1.10 fork Quaternijkon/hnsw-ivf):
+ * batched IndexIVFFlat::search(n, x, k, D, I) with a flat coarse quantizer, METRIC_L2 /
+ * METRIC_INNER_PRODUCT, fp32. Conventions follow the reference's own C API:
+ *   - opaque handles, created by *_new*, destroyed by *_free      (c_api/macros_impl.h:90-93)
+ *   - every fallible call returns int: 0 OK, -1 unknown, -2 library exception, -4 std exception
+ *                                                                  (c_api/error_c.h:19-30)
+ *   - message of the last failure on this thread: b200_get_last_error()
+ *                                                                  (c_api/error_impl.cpp:15-27)
+ *   - idx_t = int64_t, metric enum values as faiss/MetricType.h:23-24
+ * Plain pointers and sizes only. x / distances / labels may be HOST or DEVICE pointers (detected
+ * with cudaPointerGetAttributes); host buffers are staged through pinned memory.
+ * There is no CPU fallback: every entry point fails with -2 if no CUDA device is usable.
+ */
+#ifndef B200IVF_C_H
+#define B200IVF_C_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef int64_t b200_idx_t; /* faiss idx_t, faiss/MetricType.h:50 */
+
+typedef enum B200MetricType { /* == FaissMetricType, c_api/Index_c.h:28-41 */
+    B200_METRIC_INNER_PRODUCT = 0,
+    B200_METRIC_L2 = 1
+} B200MetricType;
+
+typedef struct B200IndexIVFFlat_H B200IndexIVFFlat;
+
+/* layout identical to FaissIndexIVFStats, c_api/IndexIVF_c.h:162-169 */
+typedef struct B200IndexIVFStats {
+    size_t nq;
+    size_t nlist;
+    size_t ndis;
+    size_t nheap_updates; /* not tracked on device: always 0 */
+    double quantization_time; /* ms, device time of the coarse quantizer */
+    double search_time;       /* ms, device time of the whole search */
+} B200IndexIVFStats;
+
+/* c_api/error_impl.cpp:15-27 faiss_get_last_error */
+const char* b200_get_last_error(void);
+
+/* faiss_IndexIVFFlat_new_with_metric, c_api/IndexIVFFlat_c.h:53-58. The flat quantizer
+ * (IndexFlat, faiss/IndexFlat.h:23) is part of the object; `device` is the CUDA ordinal. */
+int b200_IndexIVFFlat_new_with_metric(B200IndexIVFFlat** p_index, size_t d, size_t nlist,
+                                      B200MetricType metric, int device);
+/* faiss_IndexIVFFlat_free, c_api/IndexIVFFlat_c.h:27 */
+void b200_IndexIVFFlat_free(B200IndexIVFFlat* index);
+
+/* getters/setters, c_api/IndexIVFFlat_c.h:29-32 + c_api/Index_c.h:85-97 */
+size_t b200_IndexIVFFlat_nlist(const B200IndexIVFFlat* index);
+size_t b200_IndexIVFFlat_nprobe(const B200IndexIVFFlat* index);
+void b200_IndexIVFFlat_set_nprobe(B200IndexIVFFlat* index, size_t nprobe);
+int b200_IndexIVFFlat_d(const B200IndexIVFFlat* index);
+b200_idx_t b200_IndexIVFFlat_ntotal(const B200IndexIVFFlat* index);
+int b200_IndexIVFFlat_is_trained(const B200IndexIVFFlat* index);
+B200MetricType b200_IndexIVFFlat_metric_type(const B200IndexIVFFlat* index);
+
+/* Install trained centroids == quantizer->add(nlist, c) on an IndexFlat; afterwards
+ * is_trained (faiss/IndexIVF.cpp:72-74,178). c: [nlist][d] fp32, host or device. */
+int b200_IndexIVFFlat_set_centroids(B200IndexIVFFlat* index, const float* centroids);
+int b200_IndexIVFFlat_get_centroids(const B200IndexIVFFlat* index, float* centroids_out);
+
+/* Restrict this handle to the inverted lists [list_lo, list_hi): the list-range shard of
+ * SUBSET_TYPE_INVLIST (faiss/invlists/InvertedLists.cpp:168-176, faiss/gpu/GpuCloner.cpp:303-314).
+ * Centroids stay complete; vectors assigned elsewhere are dropped by add. Call before add. */
+int b200_IndexIVFFlat_set_list_range(B200IndexIVFFlat* index, size_t list_lo, size_t list_hi);
+
+/* faiss_Index_add_with_ids, c_api/Index_c.h:133-137 (xids NULL: ids ntotal..ntotal+n-1,
+ * faiss/IndexIVFFlat.cpp:72) */
+int b200_IndexIVFFlat_add_with_ids(B200IndexIVFFlat* index, b200_idx_t n, const float* x,
+                                   const b200_idx_t* xids);
+/* faiss_IndexIVFFlat_add_core, c_api/IndexIVFFlat_c.h:60-65 (precomputed_idx < 0 skips) */
+int b200_IndexIVFFlat_add_core(B200IndexIVFFlat* index, b200_idx_t n, const float* x,
+                               const b200_idx_t* xids, const int64_t* precomputed_idx);
+/* faiss_Index_reset, c_api/Index_c.h:151 */
+int b200_IndexIVFFlat_reset(B200IndexIVFFlat* index);
+
+/* faiss_IndexIVF_get_list_size, c_api/IndexIVF_c.h:123 */
+size_t b200_IndexIVFFlat_get_list_size(const B200IndexIVFFlat* index, size_t list_no);
+/* faiss_IndexIVF_invlists_get_ids, c_api/IndexIVF_c.h:148-151 (host buffer) */
+int b200_IndexIVFFlat_invlists_get_ids(const B200IndexIVFFlat* index, size_t list_no,
+                                       b200_idx_t* invlist);
+/* InvertedLists::get_codes as fp32 rows (faiss/invlists/InvertedLists.h:62), host buffer */
+int b200_IndexIVFFlat_invlists_get_codes(const B200IndexIVFFlat* index, size_t list_no,
+                                         float* codes);
+
+/* faiss_Index_search, c_api/Index_c.h:108-114 == IndexIVF::search faiss/IndexIVF.cpp:303 */
+int b200_IndexIVFFlat_search(const B200IndexIVFFlat* index, b200_idx_t n, const float* x,
+                             b200_idx_t k, float* distances, b200_idx_t* labels);
+/* faiss_IndexIVF_search_preassigned, c_api/IndexIVF_c.h:112-121; store_pairs must be 0;
+ * nprobe is the handle's nprobe; centroid_dis may be NULL (unused by IVFFlat,
+ * faiss/IndexIVFFlat.cpp:143) */
+int b200_IndexIVFFlat_search_preassigned(const B200IndexIVFFlat* index, b200_idx_t n,
+                                         const float* x, b200_idx_t k, const b200_idx_t* assign,
+                                         const float* centroid_dis, float* distances,
+                                         b200_idx_t* labels, int store_pairs);
+/* quantizer->search (faiss/IndexFlat.cpp:38-69): the nprobe nearest centroids of each query */
+int b200_IndexIVFFlat_quantize(const B200IndexIVFFlat* index, b200_idx_t n, const float* x,
+                               b200_idx_t nprobe, float* centroid_dis, b200_idx_t* assign);
+
+/* indexIVF_stats (faiss/IndexIVF.cpp:1764) is per handle here */
+void b200_IndexIVFFlat_get_stats(const B200IndexIVFFlat* index, B200IndexIVFStats* stats);
+void b200_IndexIVFFlat_reset_stats(B200IndexIVFFlat* index);
+/* device time in ms of the stages of the LAST search call: {coarse, plan, scan, select, total} */
+void b200_IndexIVFFlat_last_timings(const B200IndexIVFFlat* index, double* ms5);
+
+/* Run on a caller-owned CUDA stream (cudaStream_t as void*; NULL = the handle's own stream). */
+int b200_IndexIVFFlat_set_stream(B200IndexIVFFlat* index, void* cuda_stream);
+
+/* merge_knn_results (faiss/utils/Heap.cpp:158-232) as used by IndexShardsIVF::search
+ * (faiss/IndexShardsIVF.cpp:224-242): all_* are [nshard][n][k] per-shard sorted tables, host or
+ * device; runs on `device`, on `cuda_stream` (may be NULL). */
+int b200_merge_knn_results(B200MetricType metric, int nshard, b200_idx_t n, b200_idx_t k,
+                           const float* all_distances, const b200_idx_t* all_labels,
+                           float* distances, b200_idx_t* labels, int device, void* cuda_stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200IVF_C_H */
