@@ -14,6 +14,7 @@ from .binding import (  # noqa: F401
     IndexIVFFlat,
     IndexIVFStats,
     build_library,
+    kernel_launches,
     library_path,
     load_library,
     merge_knn_results,
@@ -22,6 +23,6 @@ from .sharded import IndexShardsIVFFlat, list_range_of_rank  # noqa: F401
 
 __all__ = [
     "METRIC_INNER_PRODUCT", "METRIC_L2", "B200Error", "IndexIVFFlat", "IndexIVFStats",
-    "IndexShardsIVFFlat", "build_library", "library_path", "load_library", "merge_knn_results",
+    "IndexShardsIVFFlat", "build_library", "kernel_launches", "library_path", "load_library", "merge_knn_results",
     "list_range_of_rank",
 ]

@@ -72,6 +72,7 @@ SYMBOLS = [
     ("b200_IndexIVFFlat_reset_stats", None, [_vp]),
     ("b200_IndexIVFFlat_last_timings", None, [_vp, C.POINTER(C.c_double)]),
     ("b200_IndexIVFFlat_set_stream", C.c_int, [_vp, _vp]),
+    ("b200_kernel_launches", C.c_ulonglong, []),
     ("b200_merge_knn_results", C.c_int,
      [C.c_int, C.c_int, C.c_int64, C.c_int64, _f32p, _i64p, _f32p, _i64p, C.c_int, _vp]),
 ]
@@ -272,6 +273,11 @@ class IndexIVFFlat:
 
     def set_stream(self, cuda_stream_ptr):
         self._check(self._lib.b200_IndexIVFFlat_set_stream(self._h, cuda_stream_ptr))
+
+
+def kernel_launches():
+    """CUDA kernels launched by the library so far in this process."""
+    return int(load_library().b200_kernel_launches())
 
 
 def merge_knn_results(metric, all_D, all_I, device=0, stream=None):

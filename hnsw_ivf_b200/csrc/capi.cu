@@ -4,6 +4,7 @@
 #include "../../include/b200ivf_c.h"
 
 #include "index.h"
+#include "kernels.h"
 
 #include <exception>
 #include <string>
@@ -156,6 +157,10 @@ void b200_IndexIVFFlat_last_timings(const B200IndexIVFFlat* index, double* ms5) 
 }
 int b200_IndexIVFFlat_set_stream(B200IndexIVFFlat* index, void* cuda_stream) {
     return guarded([&] { H(index)->set_stream((cudaStream_t)cuda_stream); });
+}
+
+unsigned long long b200_kernel_launches(void) {
+    return b200ivf::g_kernel_launches.load();
 }
 
 int b200_merge_knn_results(B200MetricType metric, int nshard, b200_idx_t n, b200_idx_t k,

@@ -13,6 +13,8 @@
 
 namespace b200ivf {
 
+std::atomic<unsigned long long> g_kernel_launches{0};
+
 #define CUDA_CHECK(expr)                                                                     \
     do {                                                                                     \
         cudaError_t e__ = (expr);                                                            \

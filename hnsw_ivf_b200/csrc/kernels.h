@@ -4,7 +4,15 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
+
 namespace b200ivf {
+
+// number of kernels this library has launched (bench.py reports it as gpu_launches)
+extern std::atomic<unsigned long long> g_kernel_launches;
+inline void count_launches(int n) {
+    g_kernel_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed);
+}
 
 // ---- K2 (and K1 as a scan of the centroid table): ivf_scan ------------------------------------
 // One WARP per work item (list, sub-group of <= RQ queries probing it, row split). Replaces

@@ -97,6 +97,7 @@ cudaError_t launch_scatter_rows(const float* x, const int64_t* xids, const int64
         return cudaSuccess;
     scatter_rows_kernel<<<grid_for(n * 32, 256), 256, 0, st>>>(x, xids, dst_row, n, d, nf4, slab,
                                                                ids, id_base);
+    count_launches(1);
     return cudaGetLastError();
 }
 
@@ -108,6 +109,7 @@ cudaError_t launch_move_blocks(const float4* old_slab, const int64_t* old_ids,
         return cudaSuccess;
     move_blocks_kernel<<<std::min(nlists, 148 * 8), 256, 0, st>>>(
             old_slab, old_ids, old_blk0, old_len, new_blk0, nlists, nf4, new_slab, new_ids);
+    count_launches(1);
     return cudaGetLastError();
 }
 
@@ -116,6 +118,7 @@ cudaError_t launch_gather_rows(const float* slab, int64_t row0, int64_t nrows, i
     if (nrows == 0)
         return cudaSuccess;
     gather_rows_kernel<<<grid_for(nrows * d, 256), 256, 0, st>>>(slab, row0, nrows, d, nf4, out);
+    count_launches(1);
     return cudaGetLastError();
 }
 
@@ -124,6 +127,7 @@ cudaError_t launch_i64_to_i32(const int64_t* in, int32_t* out, int64_t n, int32_
     if (n == 0)
         return cudaSuccess;
     i64_to_i32_kernel<<<grid_for(n, 256), 256, 0, st>>>(in, out, n, lo, hi, bad);
+    count_launches(1);
     return cudaGetLastError();
 }
 

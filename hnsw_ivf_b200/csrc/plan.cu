@@ -127,6 +127,7 @@ __global__ void plan_single_kernel(int32_t* grp_start, uint32_t* item_off, int n
 cudaError_t launch_plan_single(int32_t* grp_start, uint32_t* item_off, int n, uint32_t items,
                                cudaStream_t st) {
     plan_single_kernel<<<1, 1, 0, st>>>(grp_start, item_off, n, items);
+    count_launches(1);
     return cudaGetLastError();
 }
 
@@ -142,8 +143,11 @@ cudaError_t launch_plan(const PlanArgs& a, cudaStream_t st) {
     const int threads = 256;
     const int grid = (int)std::min<int64_t>((total + threads - 1) / threads, 148 * 8);
     plan_count_kernel<<<grid, threads, 0, st>>>(a);
+    count_launches(1);
     plan_scan_kernel<<<1, 1024, 0, st>>>(a);
+    count_launches(1);
     plan_scatter_kernel<<<grid, threads, 0, st>>>(a);
+    count_launches(1);
     return cudaGetLastError();
 }
 

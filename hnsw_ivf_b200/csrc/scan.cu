@@ -226,6 +226,7 @@ cudaError_t launch_one(int wpc, uint32_t max_items, const ScanArgs& a, cudaStrea
     if (grid == 0)
         return cudaSuccess;
     kern<<<grid, wpc * 32, smem, st>>>(a);
+    count_launches(1);
     return cudaGetLastError();
 }
 

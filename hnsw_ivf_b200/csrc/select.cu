@@ -198,6 +198,7 @@ cudaError_t launch_select(const SelectArgs& a, cudaStream_t st) {
             return e;
     }
     select_kernel<<<a.n, threads, smem, st>>>(a, M);
+    count_launches(1);
     return cudaGetLastError();
 }
 
@@ -211,6 +212,7 @@ cudaError_t launch_merge_shards(int metric, int nshard, int n, int k, const floa
     const int wpb = 4;
     merge_shards_kernel<<<(n + wpb - 1) / wpb, wpb * 32, 0, st>>>(metric, nshard, n, k, all_dis,
                                                                  all_ids, out_dis, out_ids);
+    count_launches(1);
     return cudaGetLastError();
 }
 

@@ -113,6 +113,9 @@ void b200_IndexIVFFlat_last_timings(const B200IndexIVFFlat* index, double* ms5);
 /* Run on a caller-owned CUDA stream (cudaStream_t as void*; NULL = the handle's own stream). */
 int b200_IndexIVFFlat_set_stream(B200IndexIVFFlat* index, void* cuda_stream);
 
+/* Number of CUDA kernels this library has launched in this process (all handles). */
+unsigned long long b200_kernel_launches(void);
+
 /* merge_knn_results (faiss/utils/Heap.cpp:158-232) as used by IndexShardsIVF::search
  * (faiss/IndexShardsIVF.cpp:224-242): all_* are [nshard][n][k] per-shard sorted tables, host or
  * device; runs on `device`, on `cuda_stream` (may be NULL). */
