@@ -87,6 +87,26 @@ static __device__ __noinline__ void warp_sort_keys(uint64_t* a, int n, int lane)
     }
 }
 
+// A per-query candidate buffer of `cap` keys (power of two) holding `cnt` entries: sort it and keep
+// the k best; returns the new fill and the new acceptance threshold (the k-th best score once k
+// candidates exist -- the reference's heap top, faiss/utils/Heap.h:111-150).
+struct KeyBufState {
+    int cnt;
+    float thr;
+};
+static __device__ __noinline__ KeyBufState warp_compact_keys(uint64_t* buf, int cnt, float thr,
+                                                             int k, int cap, int lane) {
+    for (int i = cnt + lane; i < cap; i += 32)
+        buf[i] = kSentinelKey;
+    __syncwarp();
+    warp_sort_keys(buf, cap, lane);
+    if (cnt >= k) {
+        cnt = k;
+        thr = key_score(buf[k - 1]);
+    }
+    return {cnt, thr};
+}
+
 // Same network run by a whole thread block.
 __device__ __forceinline__ void block_sort_keys(uint64_t* a, int n) {
     for (int size = 2; size <= n; size <<= 1) {

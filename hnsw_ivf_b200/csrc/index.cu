@@ -102,6 +102,32 @@ ScanCfg choose_scan_cfg(int nf4, int k) {
     throw B200Exception("k too large for the scan kernel's shared-memory candidate buffer");
 }
 
+// the CTA-tiled scan (scan_tile.cu) takes the lists probed by more than kTileMinQueries queries
+constexpr int kTileMinQueries = 8;
+constexpr size_t kSmemPerSM = 233472, kSmemPerCtaMax = 232448, kSmemCtaReserve = 1024;
+
+struct TileCfg {
+    int wn = 0; // 0: tiled kernel not usable for this (d, k)
+    int nst = 0, cap = 0, tq = 0;
+};
+
+TileCfg choose_tile_cfg(int nf4, int k) {
+    TileCfg c;
+    c.cap = pow2_ceil(k + 32);
+    // preference: two CTAs per SM with a 3-deep ring, then shallower rings, then one CTA per SM
+    const int pref[6][3] = {{2, 3, 2}, {2, 2, 2}, {1, 3, 2}, {2, 4, 1}, {1, 4, 1}, {1, 2, 1}};
+    for (const auto& p : pref) {
+        const size_t sm = scan_tile_smem_bytes(p[0], nf4, c.cap, p[1]);
+        if (sm <= kSmemPerCtaMax && (sm + kSmemCtaReserve) * p[2] <= kSmemPerSM) {
+            c.wn = p[0];
+            c.nst = p[1];
+            c.tq = 32 * p[0];
+            return c;
+        }
+    }
+    return c;
+}
+
 } // namespace
 
 struct IndexIVFFlatB200::Impl {
@@ -122,7 +148,8 @@ struct IndexIVFFlatB200::Impl {
     int64_t nstored = 0;
 
     // scratch (grow only)
-    Buffer coarse_ids, coarse_dis, part, count, fill, grp_start, item_off, pair_query, slot_of,
+    Buffer coarse_ids, coarse_dis, part, count, fill, grp_start, item_off, item_off_tile,
+            pair_query, slot_of,
             cplan, stage_x, stage_D, stage_I, stage_assign, dev_x, dev_D, dev_I, dev_assign64,
             dev_stats, host_stats;
     cudaEvent_t ev[6] = {};
@@ -178,7 +205,7 @@ IndexIVFFlatB200::~IndexIVFFlatB200() {
     Buffer* bufs[] = {&impl_->cent_slab, &impl_->cent_meta, &impl_->slab, &impl_->ids,
                       &impl_->list_blk0, &impl_->list_len, &impl_->coarse_ids, &impl_->coarse_dis,
                       &impl_->part, &impl_->count, &impl_->fill, &impl_->grp_start,
-                      &impl_->item_off, &impl_->pair_query, &impl_->slot_of, &impl_->cplan,
+                      &impl_->item_off, &impl_->item_off_tile, &impl_->pair_query, &impl_->slot_of, &impl_->cplan,
                       &impl_->stage_x, &impl_->stage_D, &impl_->stage_I, &impl_->stage_assign,
                       &impl_->dev_x, &impl_->dev_D, &impl_->dev_I, &impl_->dev_assign64,
                       &impl_->dev_stats, &impl_->host_stats};
@@ -327,33 +354,57 @@ static void run_coarse(int metric, int d, int nf4, size_t nlist, const Buffer& c
                        const Buffer& cent_meta, Buffer& cplan, Buffer& part, const float* xd,
                        int64_t n, int kc, int32_t* out_ids32, int64_t* out_ids64, float* out_dis,
                        cudaStream_t st) {
+    const TileCfg tc = choose_tile_cfg(nf4, kc);
     const ScanCfg cfg = choose_scan_cfg(nf4, kc);
-    const int64_t ngroups = ceil_div(n, cfg.rq);
+    const bool tiled = tc.wn > 0 && n > kTileMinQueries;
+    const int64_t ngroups = ceil_div(n, tiled ? tc.tq : cfg.rq);
     const int64_t nblk = ceil_div((int64_t)nlist, kBlockRows);
-    int64_t S = ceil_div(kTargetScanItems, ngroups);
-    S = std::max<int64_t>(1, std::min<int64_t>(S, std::max<int64_t>(1, nblk / kScanRowsPerStep)));
+    const int64_t rows_step = tiled ? (16 / tc.wn) : kScanRowsPerStep; // 32-row blocks per step
+    const int64_t target = tiled ? 148 * 2 * 2 : kTargetScanItems;
+    int64_t S = ceil_div(target, ngroups);
+    S = std::max<int64_t>(1, std::min<int64_t>(S, std::max<int64_t>(1, nblk / rows_step)));
     S = std::min<int64_t>(S, 64);
     part.reserve((size_t)n * S * kc * sizeof(uint64_t));
     cplan.reserve(16);
     int32_t* grp_start = cplan.as<int32_t>();
     uint32_t* item_off = cplan.as<uint32_t>() + 2;
     CUDA_CHECK(launch_plan_single(grp_start, item_off, (int)n, (uint32_t)(ngroups * S), st));
-    ScanArgs a;
-    a.slab = cent_slab.as<float4>();
-    a.list_blk0 = cent_meta.as<uint32_t>();
-    a.list_len = cent_meta.as<int32_t>() + 1;
-    a.grp_start = grp_start;
-    a.pair_query = nullptr;
-    a.item_off = item_off;
-    a.nlists = 1;
-    a.nsplit = (int)S;
-    a.k = kc;
-    a.cap = cfg.cap;
-    a.d = d;
-    a.nf4 = nf4;
-    a.queries = xd;
-    a.part = part.as<uint64_t>();
-    CUDA_CHECK(launch_ivf_scan(metric, cfg.rq, cfg.wpc, (uint32_t)(ngroups * S), a, st));
+    if (tiled) {
+        TileScanArgs a;
+        a.slab = cent_slab.as<float4>();
+        a.list_blk0 = cent_meta.as<uint32_t>();
+        a.list_len = cent_meta.as<int32_t>() + 1;
+        a.grp_start = grp_start;
+        a.pair_query = nullptr;
+        a.item_off = item_off;
+        a.nlists = 1;
+        a.nsplit = (int)S;
+        a.k = kc;
+        a.cap = tc.cap;
+        a.d = d;
+        a.nf4 = nf4;
+        a.nstages = tc.nst;
+        a.queries = xd;
+        a.part = part.as<uint64_t>();
+        CUDA_CHECK(launch_ivf_scan_tile(metric, tc.wn, (uint32_t)(ngroups * S), a, st));
+    } else {
+        ScanArgs a;
+        a.slab = cent_slab.as<float4>();
+        a.list_blk0 = cent_meta.as<uint32_t>();
+        a.list_len = cent_meta.as<int32_t>() + 1;
+        a.grp_start = grp_start;
+        a.pair_query = nullptr;
+        a.item_off = item_off;
+        a.nlists = 1;
+        a.nsplit = (int)S;
+        a.k = kc;
+        a.cap = cfg.cap;
+        a.d = d;
+        a.nf4 = nf4;
+        a.queries = xd;
+        a.part = part.as<uint64_t>();
+        CUDA_CHECK(launch_ivf_scan(metric, cfg.rq, cfg.wpc, (uint32_t)(ngroups * S), a, st));
+    }
     SelectArgs s;
     s.part = part.as<uint64_t>();
     s.slot_of = nullptr;
@@ -476,6 +527,8 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
         m.fill.reserve(nlist * sizeof(int32_t));
         m.grp_start.reserve((nlist + 1) * sizeof(int32_t));
         m.item_off.reserve((nlist + 1) * sizeof(uint32_t));
+        m.item_off_tile.reserve((nlist + 1) * sizeof(uint32_t));
+        const TileCfg tc = choose_tile_cfg(m.nf4, (int)k);
         m.pair_query.reserve((size_t)pairs * sizeof(int32_t));
         m.slot_of.reserve((size_t)pairs * sizeof(int32_t));
         m.part.reserve((size_t)pairs * bp.S * k * sizeof(uint64_t));
@@ -493,6 +546,9 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
         pa.slot_of = m.slot_of.as<int32_t>();
         pa.rq = bp.cfg.rq;
         pa.nsplit = (int)bp.S;
+        pa.tile_tq = tc.tq;
+        pa.tile_min = kTileMinQueries;
+        pa.item_off_tile = m.item_off_tile.as<uint32_t>();
         pa.stats = dstats;
         CUDA_CHECK(launch_plan(pa, st));
         CUDA_CHECK(cudaEventRecord(m.ev[2], st));
@@ -514,6 +570,29 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
         const int64_t max_items =
                 (ceil_div(pairs, bp.cfg.rq) + std::min<int64_t>(pairs, (int64_t)nlist)) * bp.S;
         CUDA_CHECK(launch_ivf_scan(metric_type, bp.cfg.rq, bp.cfg.wpc, (uint32_t)max_items, sa, st));
+        if (tc.wn > 0) {
+            // lists probed by more than kTileMinQueries queries of this batch
+            TileScanArgs ta;
+            ta.slab = sa.slab;
+            ta.list_blk0 = sa.list_blk0;
+            ta.list_len = sa.list_len;
+            ta.grp_start = pa.grp_start;
+            ta.pair_query = pa.pair_query;
+            ta.item_off = pa.item_off_tile;
+            ta.nlists = (int)nlist;
+            ta.nsplit = (int)bp.S;
+            ta.k = (int)k;
+            ta.cap = tc.cap;
+            ta.d = d;
+            ta.nf4 = m.nf4;
+            ta.nstages = tc.nst;
+            ta.queries = xd;
+            ta.part = sa.part;
+            const int64_t max_tiles =
+                    (pairs / tc.tq + std::min<int64_t>(pairs / (kTileMinQueries + 1), (int64_t)nlist)) *
+                    bp.S;
+            CUDA_CHECK(launch_ivf_scan_tile(metric_type, tc.wn, (uint32_t)max_tiles, ta, st));
+        }
         CUDA_CHECK(cudaEventRecord(m.ev[3], st));
         // stage 3: per-query k-select, row -> id
         SelectArgs se;

@@ -40,6 +40,30 @@ size_t scan_smem_bytes(int rq, int warps_per_cta, int nf4, int cap);
 cudaError_t launch_ivf_scan(int metric, int rq, int warps_per_cta, uint32_t max_items,
                             const ScanArgs& a, cudaStream_t st);
 
+// ---- K2 for lists probed by many queries: CTA-tiled scan (scan_tile.cu) ------------------------
+// One CTA per work item (list, tile of <= 32*wn queries probing it, row split).
+struct TileScanArgs {
+    const float4* slab;
+    const uint32_t* list_blk0;
+    const int32_t* list_len;
+    const int32_t* grp_start;   // [nlists+1]
+    const int32_t* pair_query;  // [npairs] (nullptr: identity)
+    const uint32_t* item_off;   // [nlists+1] exclusive prefix of ceil(count/TQ)*nsplit over the
+                                // lists given to this kernel (0 items for the others)
+    int nlists;
+    int nsplit;
+    int k;
+    int cap;                    // power of two > k
+    int d;
+    int nf4;
+    int nstages;                // bulk-copy ring depth, 2..4
+    const float* queries;
+    uint64_t* part;             // [npairs][nsplit][k]
+};
+size_t scan_tile_smem_bytes(int wn, int nf4, int cap, int nstages);
+cudaError_t launch_ivf_scan_tile(int metric, int wn, uint32_t max_items, const TileScanArgs& a,
+                                 cudaStream_t st);
+
 // ---- planning: invert the probe table into per-list query groups -------------------------------
 struct PlanArgs {
     const int32_t* coarse_ids;  // [n][nprobe], -1 = no probe
@@ -52,6 +76,10 @@ struct PlanArgs {
     int32_t* pair_query;        // [n*nprobe] out
     int32_t* slot_of;           // [n*nprobe] out: pair slot of (q,p) or -1
     int rq, nsplit;
+    // lists with more than tile_min queries go to the tiled kernel (tile_tq queries per item) and
+    // get 0 items in item_off; the others get 0 items in item_off_tile. tile_tq = 0: no tiling.
+    int tile_tq, tile_min;
+    uint32_t* item_off_tile;    // [nlists+1] out (may be nullptr when tile_tq == 0)
     unsigned long long* stats;  // [4] += {nq, nlist visited, ndis, invalid keys}
 };
 cudaError_t launch_plan(const PlanArgs& a, cudaStream_t st);

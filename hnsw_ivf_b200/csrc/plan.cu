@@ -57,47 +57,60 @@ __global__ void plan_count_kernel(const PlanArgs a) {
 __global__ void plan_scan_kernel(const PlanArgs a) {
     __shared__ int s_cnt[1024];
     __shared__ unsigned s_itm[1024];
+    __shared__ unsigned s_til[1024];
     __shared__ int carry_cnt;
-    __shared__ unsigned carry_itm;
+    __shared__ unsigned carry_itm, carry_til;
     const int t = threadIdx.x;
     if (t == 0) {
         carry_cnt = 0;
         carry_itm = 0;
+        carry_til = 0;
     }
     __syncthreads();
     for (int base = 0; base < a.nlists; base += 1024) {
         const int l = base + t;
         const int c = l < a.nlists ? a.count[l] : 0;
-        const unsigned it = (unsigned)((c + a.rq - 1) / a.rq) * (unsigned)a.nsplit;
+        const bool tiled = a.tile_tq > 0 && c > a.tile_min;
+        const unsigned it = tiled ? 0u : (unsigned)((c + a.rq - 1) / a.rq) * (unsigned)a.nsplit;
+        const unsigned tl =
+                tiled ? (unsigned)((c + a.tile_tq - 1) / a.tile_tq) * (unsigned)a.nsplit : 0u;
         s_cnt[t] = c;
         s_itm[t] = it;
+        s_til[t] = tl;
         __syncthreads();
         for (int o = 1; o < 1024; o <<= 1) { // Hillis-Steele inclusive scan
             int vc = 0;
-            unsigned vi = 0;
+            unsigned vi = 0, vt = 0;
             if (t >= o) {
                 vc = s_cnt[t - o];
                 vi = s_itm[t - o];
+                vt = s_til[t - o];
             }
             __syncthreads();
             s_cnt[t] += vc;
             s_itm[t] += vi;
+            s_til[t] += vt;
             __syncthreads();
         }
         if (l < a.nlists) {
             a.grp_start[l] = carry_cnt + s_cnt[t] - c;
             a.item_off[l] = carry_itm + s_itm[t] - it;
+            if (a.item_off_tile)
+                a.item_off_tile[l] = carry_til + s_til[t] - tl;
         }
         __syncthreads();
         if (t == 1023) {
             carry_cnt += s_cnt[t];
             carry_itm += s_itm[t];
+            carry_til += s_til[t];
         }
         __syncthreads();
     }
     if (t == 0) {
         a.grp_start[a.nlists] = carry_cnt;
         a.item_off[a.nlists] = carry_itm;
+        if (a.item_off_tile)
+            a.item_off_tile[a.nlists] = carry_til;
     }
 }
 

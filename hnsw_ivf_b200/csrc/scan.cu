@@ -27,31 +27,14 @@ namespace b200ivf {
 
 namespace {
 
-struct PushState {
-    int cnt;
-    float thr;
-};
-
-// Sort the buffer and keep the k best; returns the new fill and threshold.
-__device__ __noinline__ PushState compact_buffer(uint64_t* buf, int cnt, float thr, int k, int cap,
-                                                 int lane) {
-    for (int i = cnt + lane; i < cap; i += 32)
-        buf[i] = kSentinelKey;
-    __syncwarp();
-    warp_sort_keys(buf, cap, lane);
-    if (cnt >= k) {
-        cnt = k;
-        thr = key_score(buf[k - 1]);
-    }
-    return {cnt, thr};
-}
+using PushState = KeyBufState;
 
 // Warp-collective append of the lanes whose `pass` is set (m = their ballot, non-zero).
 __device__ __noinline__ PushState push_candidates(uint64_t* buf, int cnt, float thr, int k, int cap,
                                                   bool pass, uint64_t key, unsigned m, int lane) {
     const int n = __popc(m);
     if (cnt + n > cap) {
-        PushState s = compact_buffer(buf, cnt, thr, k, cap, lane);
+        PushState s = warp_compact_keys(buf, cnt, thr, k, cap, lane);
         cnt = s.cnt;
         thr = s.thr;
     }
@@ -203,7 +186,7 @@ __global__ void __launch_bounds__(256) ivf_scan_kernel(const ScanArgs a) {
     for (int j = 0; j < RQ; ++j) {
         if (j < nqw) {
             uint64_t* buf = bufs + (size_t)j * a.cap;
-            PushState s = compact_buffer(buf, cnt[j], thr[j], a.k, a.cap, lane);
+            PushState s = warp_compact_keys(buf, cnt[j], thr[j], a.k, a.cap, lane);
             const int keep = min(s.cnt, a.k);
             uint64_t* out = a.part + ((size_t)(q0 + j) * a.nsplit + split) * a.k;
             for (int i = lane; i < a.k; i += 32)

@@ -1,0 +1,372 @@
+// scan_tile.cu -- K2 for lists that many queries of the batch probe: a CTA-tiled scan.
+//
+// Same contract as scan.cu (IVFFlatScanner::scan_codes faiss/IndexIVFFlat.cpp:155-179 applied to
+// every (query, probe) pair, k best keys per (pair, row split) left in `part`), different shape:
+// when a 10k-query batch probes 4096 lists, ~80 queries meet in every list, so the list rows are
+// worth staging ONCE in shared memory and applying to a tile of TQ queries, instead of letting
+// each warp re-stream them from L1/L2.
+//
+//  * Work item = (list, tile of <= TQ queries probing it, row split). One CTA of 8 warps.
+//  * The query tile is transposed into shared memory once ([float4 column][query]).
+//  * List rows arrive through a ring of NST stages filled by the bulk-copy engine
+//    (cp.async.bulk global -> shared, completion on an mbarrier): the device slab keeps each
+//    32-row block dimension-interleaved (common.cuh), so KC float4 columns of one block are one
+//    contiguous 512*KC-byte piece -- no tensor map, no per-thread address arithmetic.
+//  * Each thread owns 8 rows x 8 queries of fp32 accumulators. Lanes are arranged 8 (rows) x 4
+//    (queries): every LDS.128 of a warp touches 8 (rows) or 4 (queries) distinct consecutive
+//    float4 -- one conflict-free shared-memory wavefront per 32 FMAs x 8.
+//  * Direct (x-y)^2 / x*y accumulation in fp32, dimension order 0..d-1 per accumulator.
+//  * After the last column chunk of a row chunk, values that beat the query's current threshold
+//    (strict compare, as the reference's C::cmp(simi[0], dis)) are appended to a small per-query
+//    candidate buffer in shared memory; a full buffer is bitonic-sorted down to its k best, which
+//    tightens the threshold. Nothing is ever dropped: a push that finds the buffer full is retried
+//    after the compaction.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace b200ivf {
+
+namespace {
+
+constexpr int kTileThreads = 256;
+constexpr int kTileKC = 4; // float4 columns per pipeline stage
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+                 "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t done;
+    do {
+        asm volatile(
+                "{\n\t"
+                ".reg .pred p;\n\t"
+                "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+                "selp.u32 %0, 1, 0, p;\n\t"
+                "}"
+                : "=r"(done)
+                : "r"(smem_u32(bar)), "r"(parity)
+                : "memory");
+    } while (!done);
+}
+// one contiguous global -> shared bulk copy, completion counted in bytes on `bar`
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes,
+                                         uint64_t* bar) {
+    asm volatile(
+            "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+                    "r"(smem_u32(dst)),
+            "l"(src), "r"(bytes), "r"(smem_u32(bar))
+            : "memory");
+}
+
+template <int METRIC>
+__device__ __forceinline__ float acc4(float acc, const float4& x, const float4& y) {
+    if (METRIC == kMetricL2) {
+        float t;
+        t = x.x - y.x;
+        acc = fmaf(t, t, acc);
+        t = x.y - y.y;
+        acc = fmaf(t, t, acc);
+        t = x.z - y.z;
+        acc = fmaf(t, t, acc);
+        t = x.w - y.w;
+        acc = fmaf(t, t, acc);
+    } else {
+        acc = fmaf(x.x, y.x, acc);
+        acc = fmaf(x.y, y.y, acc);
+        acc = fmaf(x.z, y.z, acc);
+        acc = fmaf(x.w, y.w, acc);
+    }
+    return acc;
+}
+
+// WN = warps along the query axis (1 or 2): TQ = 32*WN queries, (8/WN)*64 rows per chunk
+template <int METRIC, int WN>
+__global__ void __launch_bounds__(kTileThreads, 2) ivf_scan_tile_kernel(const TileScanArgs a) {
+    constexpr int WM = 8 / WN;
+    constexpr int TQ = 32 * WN;
+    constexpr int RB = 2 * WM; // 32-row blocks per row chunk
+    constexpr int KC = kTileKC;
+    constexpr int STAGE_F4 = RB * KC * kBlockRows;
+
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int tid = threadIdx.x;
+    const int lane = tid & 31;
+    const int warp = tid >> 5;
+    const int wm = warp / WN, wn = warp % WN;
+    const int rg = lane & 7, qg = lane >> 3;
+
+    const uint32_t item = blockIdx.x;
+    if (item >= a.item_off[a.nlists])
+        return;
+    int lo = 0, hi = a.nlists;
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (a.item_off[mid] <= item)
+            lo = mid;
+        else
+            hi = mid;
+    }
+    const int l = lo;
+    const int g0 = a.grp_start[l];
+    const int cnt_l = a.grp_start[l + 1] - g0;
+    const int nsub = (cnt_l + TQ - 1) / TQ;
+    const uint32_t local = item - a.item_off[l];
+    const int split = (int)(local / (uint32_t)nsub);
+    const int sub = (int)(local % (uint32_t)nsub);
+    const int q0 = g0 + sub * TQ;
+    const int nqw = min(TQ, cnt_l - sub * TQ);
+
+    const int len = a.list_len[l];
+    const int nb = (len + kBlockRows - 1) / kBlockRows;
+    const int b0 = (int)(((long long)nb * split) / a.nsplit);
+    const int b1 = (int)(((long long)nb * (split + 1)) / a.nsplit);
+    const int nf4 = a.nf4;
+    const int nst = a.nstages;
+    const int cap = a.cap;
+
+    // shared-memory carve-up
+    float4* Xs = reinterpret_cast<float4*>(smem_raw);                 // [nf4][TQ]
+    float4* Ys = Xs + (size_t)nf4 * TQ;                               // [nst][RB][KC][32]
+    uint64_t* bufs = reinterpret_cast<uint64_t*>(Ys + (size_t)nst * STAGE_F4); // [TQ][cap]
+    uint64_t* full = bufs + (size_t)TQ * cap;                         // [nst]
+    float* thr_s = reinterpret_cast<float*>(full + 4);                // [TQ]
+    int* cnt_s = reinterpret_cast<int*>(thr_s + TQ);                  // [TQ]
+
+    const int nchunks = (b1 - b0 + RB - 1) / RB;
+    const int nkc = (nf4 + KC - 1) / KC;
+    const int niter = nchunks * nkc;
+    const uint32_t blk0 = a.list_blk0[l];
+    const float4* lbase = a.slab + (size_t)blk0 * nf4 * kBlockRows;
+
+    // producer: fill stage (it % nst) with column chunk (it % nkc) of row chunk (it / nkc)
+    auto issue = [&](int it) {
+        const int ci = it / nkc, ki = it - ci * nkc;
+        const int c0 = ki * KC;
+        const int ncol = min(KC, nf4 - c0);
+        const int bb0 = b0 + ci * RB;
+        const int nblk = min(RB, b1 - bb0);
+        const int st = it % nst;
+        const uint32_t bytes = (uint32_t)ncol * kBlockRows * sizeof(float4);
+        mbar_expect_tx(&full[st], bytes * nblk);
+        float4* dst = Ys + (size_t)st * STAGE_F4;
+        for (int r = 0; r < nblk; ++r)
+            bulk_g2s(dst + (size_t)r * KC * kBlockRows,
+                     lbase + ((size_t)(bb0 + r) * nf4 + c0) * kBlockRows, bytes, &full[st]);
+    };
+
+    if (tid == 0) {
+        for (int s = 0; s < nst; ++s)
+            mbar_init(&full[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    for (int j = tid; j < TQ; j += kTileThreads) {
+        thr_s[j] = j < nqw ? kNeutralScore : -__int_as_float(0x7f800000);
+        cnt_s[j] = 0;
+    }
+    __syncthreads();
+    if (tid == 0) {
+        const int npre = min(nst, niter);
+        for (int it = 0; it < npre; ++it)
+            issue(it);
+    }
+    // query tile, transposed: Xs[c][j] = dims [4c, 4c+4) of the j-th query of the tile
+    {
+        const int d = a.d;
+        const bool vec = (d & 3) == 0 && (reinterpret_cast<uintptr_t>(a.queries) & 15) == 0;
+        for (int idx = tid; idx < TQ * nf4; idx += kTileThreads) {
+            const int j = idx / nf4, c = idx - j * nf4;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (j < nqw) {
+                const int q = a.pair_query ? a.pair_query[q0 + j] : (q0 + j);
+                const float* src = a.queries + (size_t)q * d + 4 * c;
+                if (vec) {
+                    v = __ldg(reinterpret_cast<const float4*>(src));
+                } else {
+                    const int rem = d - 4 * c;
+                    v.x = __ldg(src);
+                    if (rem > 1)
+                        v.y = __ldg(src + 1);
+                    if (rem > 2)
+                        v.z = __ldg(src + 2);
+                    if (rem > 3)
+                        v.w = __ldg(src + 3);
+                }
+            }
+            Xs[(size_t)c * TQ + j] = v;
+        }
+    }
+    __syncthreads();
+
+    // queries handled by this warp: qg + 4*j (j < jmax) of its 32-query half
+    const int nq_half = max(0, min(32, nqw - wn * 32));
+    const int jmax = (nq_half + 3) >> 2;
+
+    float acc[8][8];
+    for (int it = 0; it < niter; ++it) {
+        const int ci = it / nkc, ki = it - ci * nkc;
+        const int c0 = ki * KC;
+        const int ncol = min(KC, nf4 - c0);
+        const int st = it % nst;
+        if (ki == 0) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    acc[i][j] = 0.f;
+        }
+        mbar_wait(&full[st], (uint32_t)((it / nst) & 1));
+        if (jmax > 0) {
+            const float4* Yst = Ys + (size_t)st * STAGE_F4 + (size_t)(2 * wm) * KC * kBlockRows + rg;
+            const float4* xp = Xs + (size_t)c0 * TQ + wn * 32 + qg;
+#pragma unroll
+            for (int c = 0; c < KC; ++c) {
+                if (c < ncol) {
+                    float4 y[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i)
+                        y[i] = Yst[((i >> 2) * KC + c) * kBlockRows + 8 * (i & 3)];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        if (j < jmax) {
+                            const float4 x = xp[(size_t)c * TQ + 4 * j];
+#pragma unroll
+                            for (int i = 0; i < 8; ++i)
+                                acc[i][j] = acc4<METRIC>(acc[i][j], x, y[i]);
+                        }
+                    }
+                }
+            }
+        }
+        __syncthreads(); // every warp is done with stage st
+        if (tid == 0 && it + nst < niter)
+            issue(it + nst);
+
+        if (ki == nkc - 1) {
+            // ---- candidates of this row chunk ------------------------------------------------
+            const int bb0 = b0 + ci * RB;
+            unsigned long long pend = 0ull;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const int qi = wn * 32 + qg + 4 * j;
+                const float t = thr_s[qi]; // -inf for padding queries
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    const int bb = bb0 + 2 * wm + (i >> 2);
+                    const int row = bb * kBlockRows + rg + 8 * (i & 3);
+                    const float s = (METRIC == kMetricL2 ? acc[i][j] : -acc[i][j]) + 0.f;
+                    acc[i][j] = s;
+                    if (bb < b1 && row < len && s < t)
+                        pend |= 1ull << (i * 8 + j);
+                }
+            }
+            for (;;) {
+                bool left = false;
+                if (pend) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const int qi = wn * 32 + qg + 4 * j;
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            if (pend & (1ull << (i * 8 + j))) {
+                                bool keep = false;
+                                if (acc[i][j] < thr_s[qi]) {
+                                    const int pos = atomicAdd(&cnt_s[qi], 1);
+                                    if (pos < cap) {
+                                        const int row = (bb0 + 2 * wm + (i >> 2)) * kBlockRows + rg +
+                                                8 * (i & 3);
+                                        bufs[(size_t)qi * cap + pos] = make_key(
+                                                acc[i][j], blk0 * kBlockRows + (uint32_t)row);
+                                    } else {
+                                        keep = true;
+                                    }
+                                }
+                                if (!keep)
+                                    pend &= ~(1ull << (i * 8 + j));
+                                else
+                                    left = true;
+                            }
+                        }
+                    }
+                }
+                if (!__syncthreads_or(left ? 1 : 0))
+                    break;
+                for (int qi = warp; qi < nqw; qi += kTileThreads / 32) {
+                    const int c = cnt_s[qi];
+                    if (c >= cap) {
+                        KeyBufState s = warp_compact_keys(bufs + (size_t)qi * cap, cap,
+                                                          thr_s[qi], a.k, cap, lane);
+                        if (lane == 0) {
+                            cnt_s[qi] = s.cnt;
+                            thr_s[qi] = s.thr;
+                        }
+                    }
+                }
+                __syncthreads();
+            }
+        }
+    }
+
+    // ---- the k best of every query of the tile -------------------------------------------------
+    __syncthreads();
+    for (int qi = warp; qi < nqw; qi += kTileThreads / 32) {
+        uint64_t* buf = bufs + (size_t)qi * cap;
+        const int c = min(cnt_s[qi], cap);
+        KeyBufState s = warp_compact_keys(buf, c, thr_s[qi], a.k, cap, lane);
+        const int keep = min(s.cnt, a.k);
+        uint64_t* out = a.part + ((size_t)(q0 + qi) * a.nsplit + split) * a.k;
+        for (int i = lane; i < a.k; i += 32)
+            out[i] = i < keep ? buf[i] : kSentinelKey;
+    }
+}
+
+template <int METRIC, int WN>
+cudaError_t launch_tile_one(uint32_t max_items, const TileScanArgs& a, cudaStream_t st) {
+    const size_t smem = scan_tile_smem_bytes(WN, a.nf4, a.cap, a.nstages);
+    auto kern = ivf_scan_tile_kernel<METRIC, WN>;
+    cudaError_t e =
+            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess)
+        return e;
+    if (max_items == 0)
+        return cudaSuccess;
+    kern<<<max_items, kTileThreads, smem, st>>>(a);
+    count_launches(1);
+    return cudaGetLastError();
+}
+
+} // namespace
+
+size_t scan_tile_smem_bytes(int wn, int nf4, int cap, int nstages) {
+    const size_t tq = 32 * (size_t)wn;
+    const size_t rb = 2 * (8 / (size_t)wn);
+    return tq * nf4 * sizeof(float4) + (size_t)nstages * rb * kTileKC * kBlockRows * sizeof(float4) +
+            tq * cap * sizeof(uint64_t) + 4 * sizeof(uint64_t) + tq * 8;
+}
+
+cudaError_t launch_ivf_scan_tile(int metric, int wn, uint32_t max_items, const TileScanArgs& a,
+                                 cudaStream_t st) {
+    if (a.nstages < 2 || a.nstages > 4)
+        return cudaErrorInvalidValue;
+    if (metric == kMetricL2) {
+        if (wn == 2)
+            return launch_tile_one<kMetricL2, 2>(max_items, a, st);
+        if (wn == 1)
+            return launch_tile_one<kMetricL2, 1>(max_items, a, st);
+    } else {
+        if (wn == 2)
+            return launch_tile_one<kMetricInnerProduct, 2>(max_items, a, st);
+        if (wn == 1)
+            return launch_tile_one<kMetricInnerProduct, 1>(max_items, a, st);
+    }
+    return cudaErrorInvalidValue;
+}
+
+} // namespace b200ivf
