@@ -87,6 +87,37 @@ static __device__ __noinline__ void warp_sort_keys(uint64_t* a, int n, int lane)
     }
 }
 
+// Ascending bitonic sort of exactly 64 keys in shared memory by one warp, done in registers:
+// lane holds elements `lane` and `lane + 32`; strides < 32 are shuffles, stride 32 is in-thread.
+static __device__ __forceinline__ void warp_sort64_keys(uint64_t* a, int lane) {
+    uint64_t v0 = a[lane], v1 = a[lane + 32];
+#pragma unroll
+    for (int size = 2; size <= 64; size <<= 1) {
+#pragma unroll
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            if (stride == 32) {
+                // elements lane and lane+32, ascending (size == 64)
+                const uint64_t lo = v0 < v1 ? v0 : v1, hi = v0 < v1 ? v1 : v0;
+                v0 = lo;
+                v1 = hi;
+            } else {
+                const uint64_t p0 = __shfl_xor_sync(0xffffffffu, v0, stride);
+                const uint64_t p1 = __shfl_xor_sync(0xffffffffu, v1, stride);
+                const bool lower = (lane & stride) == 0; // this lane holds the lower index
+                // element indices: e0 = lane, e1 = lane + 32
+                const bool up0 = (lane & size) == 0;
+                const bool up1 = ((lane + 32) & size) == 0;
+                const bool take_min0 = lower == up0, take_min1 = lower == up1;
+                v0 = take_min0 ? (v0 < p0 ? v0 : p0) : (v0 < p0 ? p0 : v0);
+                v1 = take_min1 ? (v1 < p1 ? v1 : p1) : (v1 < p1 ? p1 : v1);
+            }
+        }
+    }
+    a[lane] = v0;
+    a[lane + 32] = v1;
+    __syncwarp();
+}
+
 // A per-query candidate buffer of `cap` keys (power of two) holding `cnt` entries: sort it and keep
 // the k best; returns the new fill and the new acceptance threshold (the k-th best score once k
 // candidates exist -- the reference's heap top, faiss/utils/Heap.h:111-150).
@@ -99,7 +130,10 @@ static __device__ __noinline__ KeyBufState warp_compact_keys(uint64_t* buf, int 
     for (int i = cnt + lane; i < cap; i += 32)
         buf[i] = kSentinelKey;
     __syncwarp();
-    warp_sort_keys(buf, cap, lane);
+    if (cap == 64)
+        warp_sort64_keys(buf, lane);
+    else
+        warp_sort_keys(buf, cap, lane);
     if (cnt >= k) {
         cnt = k;
         thr = key_score(buf[k - 1]);

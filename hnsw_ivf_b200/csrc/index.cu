@@ -107,21 +107,20 @@ constexpr int kTileMinQueries = 8;
 constexpr size_t kSmemPerSM = 233472, kSmemPerCtaMax = 232448, kSmemCtaReserve = 1024;
 
 struct TileCfg {
-    int wn = 0; // 0: tiled kernel not usable for this (d, k)
-    int nst = 0, cap = 0, tq = 0;
+    bool ok = false; // false: tiled kernel not usable for this (d, k)
+    int nst = 0, cap = 0, tq = kTileTQ;
 };
 
 TileCfg choose_tile_cfg(int nf4, int k) {
     TileCfg c;
     c.cap = pow2_ceil(k + 32);
-    // preference: two CTAs per SM with a 3-deep ring, then shallower rings, then one CTA per SM
-    const int pref[6][3] = {{2, 3, 2}, {2, 2, 2}, {1, 3, 2}, {2, 4, 1}, {1, 4, 1}, {1, 2, 1}};
+    // preference: two CTAs per SM with the deepest ring that fits, then one CTA per SM
+    const int pref[6][2] = {{4, 2}, {3, 2}, {2, 2}, {4, 1}, {3, 1}, {2, 1}};
     for (const auto& p : pref) {
-        const size_t sm = scan_tile_smem_bytes(p[0], nf4, c.cap, p[1]);
-        if (sm <= kSmemPerCtaMax && (sm + kSmemCtaReserve) * p[2] <= kSmemPerSM) {
-            c.wn = p[0];
-            c.nst = p[1];
-            c.tq = 32 * p[0];
+        const size_t sm = scan_tile_smem_bytes(nf4, c.cap, p[0]);
+        if (sm <= kSmemPerCtaMax && (sm + kSmemCtaReserve) * p[1] <= kSmemPerSM) {
+            c.ok = true;
+            c.nst = p[0];
             return c;
         }
     }
@@ -356,10 +355,10 @@ static void run_coarse(int metric, int d, int nf4, size_t nlist, const Buffer& c
                        cudaStream_t st) {
     const TileCfg tc = choose_tile_cfg(nf4, kc);
     const ScanCfg cfg = choose_scan_cfg(nf4, kc);
-    const bool tiled = tc.wn > 0 && n > kTileMinQueries;
+    const bool tiled = tc.ok && n > kTileMinQueries;
     const int64_t ngroups = ceil_div(n, tiled ? tc.tq : cfg.rq);
     const int64_t nblk = ceil_div((int64_t)nlist, kBlockRows);
-    const int64_t rows_step = tiled ? (16 / tc.wn) : kScanRowsPerStep; // 32-row blocks per step
+    const int64_t rows_step = tiled ? 16 : kScanRowsPerStep; // 32-row blocks per step
     const int64_t target = tiled ? 148 * 2 * 2 : kTargetScanItems;
     int64_t S = ceil_div(target, ngroups);
     S = std::max<int64_t>(1, std::min<int64_t>(S, std::max<int64_t>(1, nblk / rows_step)));
@@ -386,7 +385,7 @@ static void run_coarse(int metric, int d, int nf4, size_t nlist, const Buffer& c
         a.nstages = tc.nst;
         a.queries = xd;
         a.part = part.as<uint64_t>();
-        CUDA_CHECK(launch_ivf_scan_tile(metric, tc.wn, (uint32_t)(ngroups * S), a, st));
+        CUDA_CHECK(launch_ivf_scan_tile(metric, (uint32_t)(ngroups * S), a, st));
     } else {
         ScanArgs a;
         a.slab = cent_slab.as<float4>();
@@ -546,7 +545,7 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
         pa.slot_of = m.slot_of.as<int32_t>();
         pa.rq = bp.cfg.rq;
         pa.nsplit = (int)bp.S;
-        pa.tile_tq = tc.tq;
+        pa.tile_tq = tc.ok ? tc.tq : 0;
         pa.tile_min = kTileMinQueries;
         pa.item_off_tile = m.item_off_tile.as<uint32_t>();
         pa.stats = dstats;
@@ -570,7 +569,7 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
         const int64_t max_items =
                 (ceil_div(pairs, bp.cfg.rq) + std::min<int64_t>(pairs, (int64_t)nlist)) * bp.S;
         CUDA_CHECK(launch_ivf_scan(metric_type, bp.cfg.rq, bp.cfg.wpc, (uint32_t)max_items, sa, st));
-        if (tc.wn > 0) {
+        if (tc.ok) {
             // lists probed by more than kTileMinQueries queries of this batch
             TileScanArgs ta;
             ta.slab = sa.slab;
@@ -591,7 +590,7 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
             const int64_t max_tiles =
                     (pairs / tc.tq + std::min<int64_t>(pairs / (kTileMinQueries + 1), (int64_t)nlist)) *
                     bp.S;
-            CUDA_CHECK(launch_ivf_scan_tile(metric_type, tc.wn, (uint32_t)max_tiles, ta, st));
+            CUDA_CHECK(launch_ivf_scan_tile(metric_type, (uint32_t)max_tiles, ta, st));
         }
         CUDA_CHECK(cudaEventRecord(m.ev[3], st));
         // stage 3: per-query k-select, row -> id

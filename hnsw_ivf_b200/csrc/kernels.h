@@ -41,7 +41,8 @@ cudaError_t launch_ivf_scan(int metric, int rq, int warps_per_cta, uint32_t max_
                             const ScanArgs& a, cudaStream_t st);
 
 // ---- K2 for lists probed by many queries: CTA-tiled scan (scan_tile.cu) ------------------------
-// One CTA per work item (list, tile of <= 32*wn queries probing it, row split).
+// One CTA per work item (list, tile of <= kTileTQ queries probing it, row split).
+constexpr int kTileTQ = 32;
 struct TileScanArgs {
     const float4* slab;
     const uint32_t* list_blk0;
@@ -60,8 +61,8 @@ struct TileScanArgs {
     const float* queries;
     uint64_t* part;             // [npairs][nsplit][k]
 };
-size_t scan_tile_smem_bytes(int wn, int nf4, int cap, int nstages);
-cudaError_t launch_ivf_scan_tile(int metric, int wn, uint32_t max_items, const TileScanArgs& a,
+size_t scan_tile_smem_bytes(int nf4, int cap, int nstages);
+cudaError_t launch_ivf_scan_tile(int metric, uint32_t max_items, const TileScanArgs& a,
                                  cudaStream_t st);
 
 // ---- planning: invert the probe table into per-list query groups -------------------------------

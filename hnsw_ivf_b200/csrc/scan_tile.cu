@@ -12,9 +12,14 @@
 //    (cp.async.bulk global -> shared, completion on an mbarrier): the device slab keeps each
 //    32-row block dimension-interleaved (common.cuh), so KC float4 columns of one block are one
 //    contiguous 512*KC-byte piece -- no tensor map, no per-thread address arithmetic.
-//  * Each thread owns 8 rows x 8 queries of fp32 accumulators. Lanes are arranged 8 (rows) x 4
-//    (queries): every LDS.128 of a warp touches 8 (rows) or 4 (queries) distinct consecutive
-//    float4 -- one conflict-free shared-memory wavefront per 32 FMAs x 8.
+//  * Each thread owns 8 rows x 8 queries of fp32 accumulators; a warp covers 64 rows x 32
+//    queries, the 8 warps of the CTA 512 rows. Lanes are arranged rows = lane >> 2, queries =
+//    lane & 3, so that each quarter-warp of an LDS.128 reads at most 64 distinct bytes: measured
+//    on B200 (tools/ubench_lds.cu) such a load costs 2.5 cycles of the SM's shared-memory pipe
+//    against 4.0 when a quarter-warp reads 8 distinct float4. 16 LDS.128 feed 256 FMAs per
+//    thread and column: ~60 % shared-memory pipe at full FMA rate.
+//  * A stage is released by an atomic counter: the last of the 8 warps to finish it refills it.
+//    The only CTA-wide barrier is one per 512-row chunk, in the candidate epilogue.
 //  * Direct (x-y)^2 / x*y accumulation in fp32, dimension order 0..d-1 per accumulator.
 //  * After the last column chunk of a row chunk, values that beat the query's current threshold
 //    (strict compare, as the reference's C::cmp(simi[0], dis)) are appended to a small per-query
@@ -29,7 +34,8 @@ namespace b200ivf {
 namespace {
 
 constexpr int kTileThreads = 256;
-constexpr int kTileKC = 4; // float4 columns per pipeline stage
+constexpr int kTileKC = 2; // float4 columns per pipeline stage
+constexpr int kTileRB = 16; // 32-row blocks per row chunk: two per warp
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
     return (uint32_t)__cvta_generic_to_shared(p);
@@ -87,21 +93,46 @@ __device__ __forceinline__ float acc4(float acc, const float4& x, const float4& 
     return acc;
 }
 
-// WN = warps along the query axis (1 or 2): TQ = 32*WN queries, (8/WN)*64 rows per chunk
-template <int METRIC, int WN>
+// One stage of the ring applied to the register tile. FULL: all 8 query slots are live and the
+// stage holds KC columns -- no branch inside, so ptxas can software-pipeline the LDS.128s.
+template <int METRIC, bool FULL>
+__device__ __forceinline__ void tile_stage(float (&acc)[8][8], const float4* __restrict__ Yw,
+                                           const float4* __restrict__ xp, int ncol, int jmax) {
+#pragma unroll
+    for (int c = 0; c < kTileKC; ++c) {
+        if (FULL || c < ncol) {
+            float4 y[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+                y[i] = Yw[((i >> 2) * kTileKC + c) * kBlockRows + 8 * (i & 3)];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                if (FULL || j < jmax) {
+                    const float4 x = xp[c * kTileTQ + 4 * j];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i)
+                        acc[i][j] = acc4<METRIC>(acc[i][j], x, y[i]);
+                }
+            }
+        }
+    }
+}
+
+// Thread (rg = lane >> 2, qg = lane & 3) of warp w owns rows {rg + 8 i} (i < 8) of the 64 rows
+// (two 32-row blocks) that warp w takes of every 512-row chunk, and queries {qg + 4 j} (j < 8).
+template <int METRIC>
 __global__ void __launch_bounds__(kTileThreads, 2) ivf_scan_tile_kernel(const TileScanArgs a) {
-    constexpr int WM = 8 / WN;
-    constexpr int TQ = 32 * WN;
-    constexpr int RB = 2 * WM; // 32-row blocks per row chunk
+    constexpr int TQ = kTileTQ;
+    constexpr int RB = kTileRB;
     constexpr int KC = kTileKC;
+    constexpr int NW = kTileThreads / 32;
     constexpr int STAGE_F4 = RB * KC * kBlockRows;
 
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int tid = threadIdx.x;
     const int lane = tid & 31;
     const int warp = tid >> 5;
-    const int wm = warp / WN, wn = warp % WN;
-    const int rg = lane & 7, qg = lane >> 3;
+    const int rg = lane >> 2, qg = lane & 3;
 
     const uint32_t item = blockIdx.x;
     if (item >= a.item_off[a.nlists])
@@ -136,8 +167,9 @@ __global__ void __launch_bounds__(kTileThreads, 2) ivf_scan_tile_kernel(const Ti
     float4* Xs = reinterpret_cast<float4*>(smem_raw);                 // [nf4][TQ]
     float4* Ys = Xs + (size_t)nf4 * TQ;                               // [nst][RB][KC][32]
     uint64_t* bufs = reinterpret_cast<uint64_t*>(Ys + (size_t)nst * STAGE_F4); // [TQ][cap]
-    uint64_t* full = bufs + (size_t)TQ * cap;                         // [nst]
-    float* thr_s = reinterpret_cast<float*>(full + 4);                // [TQ]
+    uint64_t* full = bufs + (size_t)TQ * cap;                         // [4] mbarriers
+    int* done_s = reinterpret_cast<int*>(full + 4);                   // [4] warps done per stage
+    float* thr_s = reinterpret_cast<float*>(done_s + 4);              // [TQ]
     int* cnt_s = reinterpret_cast<int*>(thr_s + TQ);                  // [TQ]
 
     const int nchunks = (b1 - b0 + RB - 1) / RB;
@@ -146,7 +178,8 @@ __global__ void __launch_bounds__(kTileThreads, 2) ivf_scan_tile_kernel(const Ti
     const uint32_t blk0 = a.list_blk0[l];
     const float4* lbase = a.slab + (size_t)blk0 * nf4 * kBlockRows;
 
-    // producer: fill stage (it % nst) with column chunk (it % nkc) of row chunk (it / nkc)
+    // producer step (one thread): fill stage (it % nst) with column chunk (it % nkc) of row chunk
+    // (it / nkc): one contiguous bulk copy per 32-row block
     auto issue = [&](int it) {
         const int ci = it / nkc, ki = it - ci * nkc;
         const int c0 = ki * KC;
@@ -163,8 +196,10 @@ __global__ void __launch_bounds__(kTileThreads, 2) ivf_scan_tile_kernel(const Ti
     };
 
     if (tid == 0) {
-        for (int s = 0; s < nst; ++s)
+        for (int s = 0; s < 4; ++s) {
             mbar_init(&full[s], 1);
+            done_s[s] = 0;
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     for (int j = tid; j < TQ; j += kTileThreads) {
@@ -205,9 +240,8 @@ __global__ void __launch_bounds__(kTileThreads, 2) ivf_scan_tile_kernel(const Ti
     }
     __syncthreads();
 
-    // queries handled by this warp: qg + 4*j (j < jmax) of its 32-query half
-    const int nq_half = max(0, min(32, nqw - wn * 32));
-    const int jmax = (nq_half + 3) >> 2;
+    const int jmax = (nqw + 3) >> 2; // live query slots per thread (uniform over the CTA)
+    const bool full_tile = jmax == 8;
 
     float acc[8][8];
     for (int it = 0; it < niter; ++it) {
@@ -215,6 +249,7 @@ __global__ void __launch_bounds__(kTileThreads, 2) ivf_scan_tile_kernel(const Ti
         const int c0 = ki * KC;
         const int ncol = min(KC, nf4 - c0);
         const int st = it % nst;
+        const int bbw = b0 + ci * RB + 2 * warp; // first of this warp's two blocks
         if (ki == 0) {
 #pragma unroll
             for (int i = 0; i < 8; ++i)
@@ -223,86 +258,58 @@ __global__ void __launch_bounds__(kTileThreads, 2) ivf_scan_tile_kernel(const Ti
                     acc[i][j] = 0.f;
         }
         mbar_wait(&full[st], (uint32_t)((it / nst) & 1));
-        if (jmax > 0) {
-            const float4* Yst = Ys + (size_t)st * STAGE_F4 + (size_t)(2 * wm) * KC * kBlockRows + rg;
-            const float4* xp = Xs + (size_t)c0 * TQ + wn * 32 + qg;
-#pragma unroll
-            for (int c = 0; c < KC; ++c) {
-                if (c < ncol) {
-                    float4 y[8];
-#pragma unroll
-                    for (int i = 0; i < 8; ++i)
-                        y[i] = Yst[((i >> 2) * KC + c) * kBlockRows + 8 * (i & 3)];
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        if (j < jmax) {
-                            const float4 x = xp[(size_t)c * TQ + 4 * j];
-#pragma unroll
-                            for (int i = 0; i < 8; ++i)
-                                acc[i][j] = acc4<METRIC>(acc[i][j], x, y[i]);
-                        }
-                    }
-                }
+        if (bbw < b1) { // warps whose rows lie past the end of the list skip the arithmetic
+            const float4* Yw =
+                    Ys + (size_t)st * STAGE_F4 + (size_t)(2 * warp) * KC * kBlockRows + rg;
+            const float4* xp = Xs + (size_t)c0 * TQ + qg;
+            if (full_tile && ncol == KC)
+                tile_stage<METRIC, true>(acc, Yw, xp, ncol, jmax);
+            else
+                tile_stage<METRIC, false>(acc, Yw, xp, ncol, jmax);
+        }
+        // release the stage: the last of the 8 warps to finish refills it (no CTA-wide barrier)
+        __syncwarp();
+        if (lane == 0) {
+            __threadfence_block();
+            const int prev = atomicAdd(&done_s[st], 1);
+            if (prev == NW - 1) {
+                done_s[st] = 0;
+                __threadfence_block();
+                if (it + nst < niter)
+                    issue(it + nst);
             }
         }
-        __syncthreads(); // every warp is done with stage st
-        if (tid == 0 && it + nst < niter)
-            issue(it + nst);
 
         if (ki == nkc - 1) {
             // ---- candidates of this row chunk ------------------------------------------------
-            const int bb0 = b0 + ci * RB;
+            const uint32_t grow0 = (blk0 + (uint32_t)bbw) * kBlockRows + rg;
             unsigned long long pend = 0ull;
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-                const int qi = wn * 32 + qg + 4 * j;
+                const int qi = qg + 4 * j;
                 const float t = thr_s[qi]; // -inf for padding queries
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
-                    const int bb = bb0 + 2 * wm + (i >> 2);
+                    const int bb = bbw + (i >> 2);
                     const int row = bb * kBlockRows + rg + 8 * (i & 3);
                     const float s = (METRIC == kMetricL2 ? acc[i][j] : -acc[i][j]) + 0.f;
                     acc[i][j] = s;
-                    if (bb < b1 && row < len && s < t)
-                        pend |= 1ull << (i * 8 + j);
-                }
-            }
-            for (;;) {
-                bool left = false;
-                if (pend) {
-#pragma unroll
-                    for (int j = 0; j < 8; ++j) {
-                        const int qi = wn * 32 + qg + 4 * j;
-#pragma unroll
-                        for (int i = 0; i < 8; ++i) {
-                            if (pend & (1ull << (i * 8 + j))) {
-                                bool keep = false;
-                                if (acc[i][j] < thr_s[qi]) {
-                                    const int pos = atomicAdd(&cnt_s[qi], 1);
-                                    if (pos < cap) {
-                                        const int row = (bb0 + 2 * wm + (i >> 2)) * kBlockRows + rg +
-                                                8 * (i & 3);
-                                        bufs[(size_t)qi * cap + pos] = make_key(
-                                                acc[i][j], blk0 * kBlockRows + (uint32_t)row);
-                                    } else {
-                                        keep = true;
-                                    }
-                                }
-                                if (!keep)
-                                    pend &= ~(1ull << (i * 8 + j));
-                                else
-                                    left = true;
-                            }
-                        }
+                    if (bb < b1 && row < len && s < t) {
+                        const int pos = atomicAdd(&cnt_s[qi], 1);
+                        if (pos < cap)
+                            bufs[(size_t)qi * cap + pos] = make_key(s, grow0 + 8 * i);
+                        else
+                            pend |= 1ull << (i * 8 + j);
                     }
                 }
-                if (!__syncthreads_or(left ? 1 : 0))
-                    break;
-                for (int qi = warp; qi < nqw; qi += kTileThreads / 32) {
-                    const int c = cnt_s[qi];
-                    if (c >= cap) {
-                        KeyBufState s = warp_compact_keys(bufs + (size_t)qi * cap, cap,
-                                                          thr_s[qi], a.k, cap, lane);
+            }
+            // a full buffer is compacted (threshold tightens), then the pushes that found it
+            // full are retried; rare after the first chunk
+            while (__syncthreads_or(pend != 0ull)) {
+                for (int qi = warp; qi < nqw; qi += NW) {
+                    if (cnt_s[qi] >= cap) {
+                        KeyBufState s = warp_compact_keys(bufs + (size_t)qi * cap, cap, thr_s[qi],
+                                                          a.k, cap, lane);
                         if (lane == 0) {
                             cnt_s[qi] = s.cnt;
                             thr_s[qi] = s.thr;
@@ -310,13 +317,36 @@ __global__ void __launch_bounds__(kTileThreads, 2) ivf_scan_tile_kernel(const Ti
                     }
                 }
                 __syncthreads();
+                if (pend) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const int qi = qg + 4 * j;
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const unsigned long long bit = 1ull << (i * 8 + j);
+                            if (pend & bit) {
+                                bool keep = false;
+                                if (acc[i][j] < thr_s[qi]) {
+                                    const int pos = atomicAdd(&cnt_s[qi], 1);
+                                    if (pos < cap)
+                                        bufs[(size_t)qi * cap + pos] =
+                                                make_key(acc[i][j], grow0 + 8 * i);
+                                    else
+                                        keep = true;
+                                }
+                                if (!keep)
+                                    pend &= ~bit;
+                            }
+                        }
+                    }
+                }
             }
         }
     }
 
     // ---- the k best of every query of the tile -------------------------------------------------
     __syncthreads();
-    for (int qi = warp; qi < nqw; qi += kTileThreads / 32) {
+    for (int qi = warp; qi < nqw; qi += NW) {
         uint64_t* buf = bufs + (size_t)qi * cap;
         const int c = min(cnt_s[qi], cap);
         KeyBufState s = warp_compact_keys(buf, c, thr_s[qi], a.k, cap, lane);
@@ -327,10 +357,10 @@ __global__ void __launch_bounds__(kTileThreads, 2) ivf_scan_tile_kernel(const Ti
     }
 }
 
-template <int METRIC, int WN>
+template <int METRIC>
 cudaError_t launch_tile_one(uint32_t max_items, const TileScanArgs& a, cudaStream_t st) {
-    const size_t smem = scan_tile_smem_bytes(WN, a.nf4, a.cap, a.nstages);
-    auto kern = ivf_scan_tile_kernel<METRIC, WN>;
+    const size_t smem = scan_tile_smem_bytes(a.nf4, a.cap, a.nstages);
+    auto kern = ivf_scan_tile_kernel<METRIC>;
     cudaError_t e =
             cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess)
@@ -344,29 +374,20 @@ cudaError_t launch_tile_one(uint32_t max_items, const TileScanArgs& a, cudaStrea
 
 } // namespace
 
-size_t scan_tile_smem_bytes(int wn, int nf4, int cap, int nstages) {
-    const size_t tq = 32 * (size_t)wn;
-    const size_t rb = 2 * (8 / (size_t)wn);
-    return tq * nf4 * sizeof(float4) + (size_t)nstages * rb * kTileKC * kBlockRows * sizeof(float4) +
-            tq * cap * sizeof(uint64_t) + 4 * sizeof(uint64_t) + tq * 8;
+size_t scan_tile_smem_bytes(int nf4, int cap, int nstages) {
+    const size_t tq = kTileTQ;
+    return tq * nf4 * sizeof(float4) +
+            (size_t)nstages * kTileRB * kTileKC * kBlockRows * sizeof(float4) +
+            tq * cap * sizeof(uint64_t) + 4 * sizeof(uint64_t) + 4 * sizeof(int) + tq * 8;
 }
 
-cudaError_t launch_ivf_scan_tile(int metric, int wn, uint32_t max_items, const TileScanArgs& a,
+cudaError_t launch_ivf_scan_tile(int metric, uint32_t max_items, const TileScanArgs& a,
                                  cudaStream_t st) {
     if (a.nstages < 2 || a.nstages > 4)
         return cudaErrorInvalidValue;
-    if (metric == kMetricL2) {
-        if (wn == 2)
-            return launch_tile_one<kMetricL2, 2>(max_items, a, st);
-        if (wn == 1)
-            return launch_tile_one<kMetricL2, 1>(max_items, a, st);
-    } else {
-        if (wn == 2)
-            return launch_tile_one<kMetricInnerProduct, 2>(max_items, a, st);
-        if (wn == 1)
-            return launch_tile_one<kMetricInnerProduct, 1>(max_items, a, st);
-    }
-    return cudaErrorInvalidValue;
+    if (metric == kMetricL2)
+        return launch_tile_one<kMetricL2>(max_items, a, st);
+    return launch_tile_one<kMetricInnerProduct>(max_items, a, st);
 }
 
 } // namespace b200ivf
