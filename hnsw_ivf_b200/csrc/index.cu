@@ -151,6 +151,9 @@ struct IndexIVFFlatB200::Impl {
             pair_query, slot_of,
             cplan, stage_x, stage_D, stage_I, stage_assign, dev_x, dev_D, dev_I, dev_assign64,
             dev_stats, host_stats;
+    // TMA views of the two slabs for the tiled scan (re-encoded whenever a slab moves)
+    alignas(64) unsigned char cent_map[kTensorMapBytes] = {};
+    alignas(64) unsigned char lists_map[kTensorMapBytes] = {};
     cudaEvent_t ev[6] = {};
     double last_ms[5] = {0, 0, 0, 0, 0};
     IndexIVFStatsB200 stats;
@@ -249,6 +252,7 @@ void IndexIVFFlatB200::set_centroids(const float* c) {
     const size_t nblk = (nlist + kBlockRows - 1) / kBlockRows;
     const size_t slab_bytes = nblk * m.nf4 * kBlockRows * sizeof(float4);
     m.cent_slab.reserve(slab_bytes);
+    CUDA_CHECK(make_slab_tensor_map(m.cent_map, m.cent_slab.p, m.nf4, nblk));
     CUDA_CHECK(cudaMemsetAsync(m.cent_slab.p, 0, slab_bytes, m.stream));
     // identity placement: centroid j -> row j
     std::vector<int64_t> rows(nlist);
@@ -350,7 +354,7 @@ inline int64_t ceil_div(int64_t a, int64_t b) {
 // K1 as a scan of the centroid table: the kc nearest centroids of each query, best first, ties by
 // centroid number as cmp2 orders them (faiss/IndexFlat.cpp:38-69 -> knn_L2sqr/knn_inner_product).
 static void run_coarse(int metric, int d, int nf4, size_t nlist, const Buffer& cent_slab,
-                       const Buffer& cent_meta, Buffer& cplan, Buffer& part, const float* xd,
+                       const void* cent_map, const Buffer& cent_meta, Buffer& cplan, Buffer& part, const float* xd,
                        int64_t n, int kc, int32_t* out_ids32, int64_t* out_ids64, float* out_dis,
                        cudaStream_t st) {
     const TileCfg tc = choose_tile_cfg(nf4, kc);
@@ -370,7 +374,7 @@ static void run_coarse(int metric, int d, int nf4, size_t nlist, const Buffer& c
     CUDA_CHECK(launch_plan_single(grp_start, item_off, (int)n, (uint32_t)(ngroups * S), st));
     if (tiled) {
         TileScanArgs a;
-        a.slab = cent_slab.as<float4>();
+        a.tmap = cent_map;
         a.list_blk0 = cent_meta.as<uint32_t>();
         a.list_len = cent_meta.as<int32_t>() + 1;
         a.grp_start = grp_start;
@@ -516,7 +520,7 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
             CUDA_CHECK(launch_i64_to_i32(ad, m.coarse_ids.as<int32_t>(), pairs, 0, (int32_t)nlist,
                                          dstats + 3, st));
         } else {
-            run_coarse(metric_type, d, m.nf4, nlist, m.cent_slab, m.cent_meta, m.cplan, m.part, xd,
+            run_coarse(metric_type, d, m.nf4, nlist, m.cent_slab, m.cent_map, m.cent_meta, m.cplan, m.part, xd,
                        ni, (int)np, m.coarse_ids.as<int32_t>(), nullptr, m.coarse_dis.as<float>(),
                        st);
         }
@@ -572,7 +576,7 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
         if (tc.ok) {
             // lists probed by more than kTileMinQueries queries of this batch
             TileScanArgs ta;
-            ta.slab = sa.slab;
+            ta.tmap = m.lists_map;
             ta.list_blk0 = sa.list_blk0;
             ta.list_len = sa.list_len;
             ta.grp_start = pa.grp_start;
@@ -672,7 +676,7 @@ void IndexIVFFlatB200::quantize(int64_t n, const float* x, int64_t kc, float* Dq
             m.dev_I.reserve((size_t)ni * kc * sizeof(int64_t));
             Id = m.dev_I.as<int64_t>();
         }
-        run_coarse(metric_type, d, m.nf4, nlist, m.cent_slab, m.cent_meta, m.cplan, m.part, xd, ni,
+        run_coarse(metric_type, d, m.nf4, nlist, m.cent_slab, m.cent_map, m.cent_meta, m.cplan, m.part, xd, ni,
                    (int)kc, nullptr, Id, Dd, st);
         if (!D_dev)
             CUDA_CHECK(cudaMemcpyAsync(Dq + i0 * kc, Dd, (size_t)ni * kc * sizeof(float),
@@ -750,7 +754,7 @@ void IndexIVFFlatB200::add_core(int64_t n, const float* x, const int64_t* xids,
             // quantizer->assign == search with k = 1 (faiss/Index.cpp:84-88)
             for (int64_t j0 = 0; j0 < ni; j0 += 32768) {
                 const int64_t nj = std::min<int64_t>(32768, ni - j0);
-                run_coarse(metric_type, d, m.nf4, nlist, m.cent_slab, m.cent_meta, m.cplan, m.part,
+                run_coarse(metric_type, d, m.nf4, nlist, m.cent_slab, m.cent_map, m.cent_meta, m.cplan, m.part,
                            xd + j0 * d, nj, 1, nullptr, m.dev_I.as<int64_t>() + j0,
                            m.dev_D.as<float>() + j0, st);
             }
@@ -838,6 +842,7 @@ void IndexIVFFlatB200::add_core(int64_t n, const float* x, const int64_t* xids,
     m.ids.release();
     m.slab = nslab;
     m.ids = nids;
+    CUDA_CHECK(make_slab_tensor_map(m.lists_map, m.slab.p, m.nf4, blocks));
     nblk0.release();
     m.h_len.swap(new_len);
     m.h_blk0.swap(new_blk0);

@@ -43,8 +43,10 @@ cudaError_t launch_ivf_scan(int metric, int rq, int warps_per_cta, uint32_t max_
 // ---- K2 for lists probed by many queries: CTA-tiled scan (scan_tile.cu) ------------------------
 // One CTA per work item (list, tile of <= kTileTQ queries probing it, row split).
 constexpr int kTileTQ = 32;
+constexpr int kTensorMapBytes = 128;
 struct TileScanArgs {
-    const float4* slab;
+    const void* tmap;           // HOST pointer to the 128-byte tensor map of the slab
+                                // (make_slab_tensor_map); passed to the kernel by value
     const uint32_t* list_blk0;
     const int32_t* list_len;
     const int32_t* grp_start;   // [nlists+1]
@@ -62,6 +64,7 @@ struct TileScanArgs {
     uint64_t* part;             // [npairs][nsplit][k]
 };
 size_t scan_tile_smem_bytes(int nf4, int cap, int nstages);
+cudaError_t make_slab_tensor_map(void* map_out, const void* slab, int nf4, uint64_t nblocks);
 cudaError_t launch_ivf_scan_tile(int metric, uint32_t max_items, const TileScanArgs& a,
                                  cudaStream_t st);
 

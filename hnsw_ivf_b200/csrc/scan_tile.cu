@@ -8,10 +8,11 @@
 //
 //  * Work item = (list, tile of <= TQ queries probing it, row split). One CTA of 8 warps.
 //  * The query tile is transposed into shared memory once ([float4 column][query]).
-//  * List rows arrive through a ring of NST stages filled by the bulk-copy engine
-//    (cp.async.bulk global -> shared, completion on an mbarrier): the device slab keeps each
-//    32-row block dimension-interleaved (common.cuh), so KC float4 columns of one block are one
-//    contiguous 512*KC-byte piece -- no tensor map, no per-thread address arithmetic.
+//  * List rows arrive through a ring of NST stages filled by TMA (cp.async.bulk.tensor, completion
+//    on an mbarrier). The device slab keeps each 32-row block dimension-interleaved (common.cuh);
+//    seen as a 3-D tensor [block][float4 column][128 floats] one box of 16 blocks x KC columns is
+//    one stage (16 KB) and ONE instruction by one thread; rows past the end of the slab and
+//    columns past nf4 are zero-filled by the engine.
 //  * Each thread owns 8 rows x 8 queries of fp32 accumulators; a warp covers 64 rows x 32
 //    queries, the 8 warps of the CTA 512 rows. Lanes are arranged rows = lane >> 2, queries =
 //    lane & 3, so that each quarter-warp of an LDS.128 reads at most 64 distinct bytes: measured
@@ -28,6 +29,8 @@
 //    after the compaction.
 #include "common.cuh"
 #include "kernels.h"
+
+#include <cuda.h>
 
 namespace b200ivf {
 
@@ -62,13 +65,13 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
                 : "memory");
     } while (!done);
 }
-// one contiguous global -> shared bulk copy, completion counted in bytes on `bar`
-__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes,
-                                         uint64_t* bar) {
+// one TMA box {128 floats, KC columns, RB blocks} at (0, col, blk) -> shared, bytes counted on `bar`
+__device__ __forceinline__ void tma_box_g2s(void* dst, const CUtensorMap* map, int col, int blk,
+                                            uint64_t* bar) {
     asm volatile(
-            "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
-                    "r"(smem_u32(dst)),
-            "l"(src), "r"(bytes), "r"(smem_u32(bar))
+            "cp.async.bulk.tensor.3d.shared::cluster.global.tile.mbarrier::complete_tx::bytes "
+            "[%0], [%1, {%2, %3, %4}], [%5];" ::"r"(smem_u32(dst)),
+            "l"(reinterpret_cast<uint64_t>(map)), "r"(0), "r"(col), "r"(blk), "r"(smem_u32(bar))
             : "memory");
 }
 
@@ -121,7 +124,8 @@ __device__ __forceinline__ void tile_stage(float (&acc)[8][8], const float4* __r
 // Thread (rg = lane >> 2, qg = lane & 3) of warp w owns rows {rg + 8 i} (i < 8) of the 64 rows
 // (two 32-row blocks) that warp w takes of every 512-row chunk, and queries {qg + 4 j} (j < 8).
 template <int METRIC>
-__global__ void __launch_bounds__(kTileThreads, 2) ivf_scan_tile_kernel(const TileScanArgs a) {
+__global__ void __launch_bounds__(kTileThreads, 2)
+        ivf_scan_tile_kernel(const TileScanArgs a, const __grid_constant__ CUtensorMap tmap) {
     constexpr int TQ = kTileTQ;
     constexpr int RB = kTileRB;
     constexpr int KC = kTileKC;
@@ -176,23 +180,15 @@ __global__ void __launch_bounds__(kTileThreads, 2) ivf_scan_tile_kernel(const Ti
     const int nkc = (nf4 + KC - 1) / KC;
     const int niter = nchunks * nkc;
     const uint32_t blk0 = a.list_blk0[l];
-    const float4* lbase = a.slab + (size_t)blk0 * nf4 * kBlockRows;
 
     // producer step (one thread): fill stage (it % nst) with column chunk (it % nkc) of row chunk
-    // (it / nkc): one contiguous bulk copy per 32-row block
+    // (it / nkc): one TMA box
     auto issue = [&](int it) {
         const int ci = it / nkc, ki = it - ci * nkc;
-        const int c0 = ki * KC;
-        const int ncol = min(KC, nf4 - c0);
-        const int bb0 = b0 + ci * RB;
-        const int nblk = min(RB, b1 - bb0);
         const int st = it % nst;
-        const uint32_t bytes = (uint32_t)ncol * kBlockRows * sizeof(float4);
-        mbar_expect_tx(&full[st], bytes * nblk);
-        float4* dst = Ys + (size_t)st * STAGE_F4;
-        for (int r = 0; r < nblk; ++r)
-            bulk_g2s(dst + (size_t)r * KC * kBlockRows,
-                     lbase + ((size_t)(bb0 + r) * nf4 + c0) * kBlockRows, bytes, &full[st]);
+        mbar_expect_tx(&full[st], (uint32_t)(STAGE_F4 * sizeof(float4)));
+        tma_box_g2s(Ys + (size_t)st * STAGE_F4, &tmap, ki * KC, (int)blk0 + b0 + ci * RB,
+                    &full[st]);
     };
 
     if (tid == 0) {
@@ -367,12 +363,44 @@ cudaError_t launch_tile_one(uint32_t max_items, const TileScanArgs& a, cudaStrea
         return e;
     if (max_items == 0)
         return cudaSuccess;
-    kern<<<max_items, kTileThreads, smem, st>>>(a);
+    kern<<<max_items, kTileThreads, smem, st>>>(a, *reinterpret_cast<const CUtensorMap*>(a.tmap));
     count_launches(1);
     return cudaGetLastError();
 }
 
 } // namespace
+
+// The slab as a rank-3 fp32 tensor {128 floats (one float4 column of a block), nf4, blocks} with a
+// {128, KC, RB} box. libcuda is reached through the runtime (no link-time dependency on it).
+cudaError_t make_slab_tensor_map(void* map_out, const void* slab, int nf4, uint64_t nblocks) {
+    static_assert(sizeof(CUtensorMap) == kTensorMapBytes, "CUtensorMap size");
+    using EncodeFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static EncodeFn encode = nullptr;
+    if (!encode) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault,
+                                                &qres);
+        if (e != cudaSuccess)
+            return e;
+        if (qres != cudaDriverEntryPointSuccess || !fn)
+            return cudaErrorNotSupported;
+        encode = reinterpret_cast<EncodeFn>(fn);
+    }
+    const cuuint64_t gdim[3] = {128, (cuuint64_t)nf4, nblocks ? nblocks : 1};
+    const cuuint64_t gstride[2] = {512, (cuuint64_t)nf4 * 512};
+    const cuuint32_t box[3] = {128, (cuuint32_t)kTileKC, (cuuint32_t)kTileRB};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    const CUresult r = encode(reinterpret_cast<CUtensorMap*>(map_out),
+                              CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<void*>(slab), gdim,
+                              gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                              CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? cudaSuccess : cudaErrorInvalidValue;
+}
 
 size_t scan_tile_smem_bytes(int nf4, int cap, int nstages) {
     const size_t tq = kTileTQ;
