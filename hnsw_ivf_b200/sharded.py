@@ -22,11 +22,13 @@ def gather_results(D_loc, I_loc, group=None):
     import torch
     import torch.distributed as dist
     world = dist.get_world_size(group)
-    all_D = torch.empty((world,) + tuple(D_loc.shape), dtype=D_loc.dtype, device=D_loc.device)
-    all_I = torch.empty((world,) + tuple(I_loc.shape), dtype=I_loc.dtype, device=I_loc.device)
+    n, k = D_loc.shape
+    # rank r's table lands in rows [r*n, (r+1)*n): the [world][n][k] layout merge_knn_results reads
+    all_D = torch.empty((world * n, k), dtype=D_loc.dtype, device=D_loc.device)
+    all_I = torch.empty((world * n, k), dtype=I_loc.dtype, device=I_loc.device)
     dist.all_gather_into_tensor(all_D, D_loc.contiguous(), group=group)
     dist.all_gather_into_tensor(all_I, I_loc.contiguous(), group=group)
-    return all_D, all_I
+    return all_D.view(world, n, k), all_I.view(world, n, k)
 
 
 class IndexShardsIVFFlat:
