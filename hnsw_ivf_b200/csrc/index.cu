@@ -9,6 +9,7 @@
 #include "kernels.h"
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 namespace b200ivf {
@@ -139,8 +140,9 @@ struct IndexIVFFlatB200::Impl {
     Buffer cent_meta; // uint32 blk0[1] | int32 len[1]
     std::vector<float> h_centroids;
 
+    Buffer cent_norms; // |c|^2 per centroid row (tensor-core scan, L2)
     // inverted lists
-    Buffer slab, ids, list_blk0, list_len;
+    Buffer slab, ids, list_blk0, list_len, norms;
     std::vector<uint32_t> h_blk0;
     std::vector<int32_t> h_len;
     size_t slab_blocks = 0;
@@ -154,11 +156,17 @@ struct IndexIVFFlatB200::Impl {
     // TMA views of the two slabs for the tiled scan (re-encoded whenever a slab moves)
     alignas(64) unsigned char cent_map[kTensorMapBytes] = {};
     alignas(64) unsigned char lists_map[kTensorMapBytes] = {};
+    // ... and for the tensor-core scan (column-outer box)
+    alignas(64) unsigned char cent_map_tc[kTensorMapBytes] = {};
+    alignas(64) unsigned char lists_map_tc[kTensorMapBytes] = {};
+    bool use_tc = true; // B200IVF_NO_TC=1 turns the tensor-core scan off (A/B runs)
     cudaEvent_t ev[6] = {};
     double last_ms[5] = {0, 0, 0, 0, 0};
     IndexIVFStatsB200 stats;
 
     Impl() {
+        const char* e = getenv("B200IVF_NO_TC");
+        use_tc = !(e && e[0] == '1');
         stage_x.pinned_host = stage_D.pinned_host = stage_I.pinned_host = true;
         stage_assign.pinned_host = host_stats.pinned_host = true;
     }
@@ -204,7 +212,7 @@ IndexIVFFlatB200::~IndexIVFFlatB200() {
     cudaGetDevice(&prev);
     cudaSetDevice(device_);
     cudaStreamSynchronize(impl_->stream);
-    Buffer* bufs[] = {&impl_->cent_slab, &impl_->cent_meta, &impl_->slab, &impl_->ids,
+    Buffer* bufs[] = {&impl_->cent_norms, &impl_->norms, &impl_->cent_slab, &impl_->cent_meta, &impl_->slab, &impl_->ids,
                       &impl_->list_blk0, &impl_->list_len, &impl_->coarse_ids, &impl_->coarse_dis,
                       &impl_->part, &impl_->count, &impl_->fill, &impl_->grp_start,
                       &impl_->item_off, &impl_->item_off_tile, &impl_->pair_query, &impl_->slot_of, &impl_->cplan,
@@ -265,6 +273,10 @@ void IndexIVFFlatB200::set_centroids(const float* c) {
     CUDA_CHECK(launch_scatter_rows(cd, nullptr, m.dev_assign64.as<int64_t>(), (int64_t)nlist, d,
                                    m.nf4, m.cent_slab.as<float>(), m.dev_I.as<int64_t>(), 0,
                                    m.stream));
+    CUDA_CHECK(make_slab_tensor_map_tc(m.cent_map_tc, m.cent_slab.p, m.nf4, nblk));
+    m.cent_norms.reserve(nblk * kBlockRows * sizeof(float));
+    CUDA_CHECK(launch_row_norms(m.cent_slab.as<float4>(), (int64_t)(nblk * kBlockRows), m.nf4,
+                                m.cent_norms.as<float>(), m.stream));
     m.cent_meta.reserve(16);
     const uint32_t blk0 = 0;
     const int32_t len = (int32_t)nlist;
@@ -296,6 +308,7 @@ void IndexIVFFlatB200::reset() {
     CUDA_CHECK(cudaStreamSynchronize(m.stream));
     m.slab.release();
     m.ids.release();
+    m.norms.release();
     m.slab_blocks = 0;
     m.nstored = 0;
     std::fill(m.h_blk0.begin(), m.h_blk0.end(), 0u);
@@ -351,76 +364,111 @@ inline int64_t ceil_div(int64_t a, int64_t b) {
 
 } // namespace
 
+// partial lists keep a few more than k entries (scan_tc_kpart), and the k-select re-scores
+// k + kRerankExtra survivors exactly, whenever the tensor-core scan (approximate scores) takes part
+constexpr int kRerankExtra = 8;
+
 // K1 as a scan of the centroid table: the kc nearest centroids of each query, best first, ties by
 // centroid number as cmp2 orders them (faiss/IndexFlat.cpp:38-69 -> knn_L2sqr/knn_inner_product).
-static void run_coarse(int metric, int d, int nf4, size_t nlist, const Buffer& cent_slab,
-                       const void* cent_map, const Buffer& cent_meta, Buffer& cplan, Buffer& part, const float* xd,
-                       int64_t n, int kc, int32_t* out_ids32, int64_t* out_ids64, float* out_dis,
-                       cudaStream_t st) {
-    const TileCfg tc = choose_tile_cfg(nf4, kc);
-    const ScanCfg cfg = choose_scan_cfg(nf4, kc);
-    const bool tiled = tc.ok && n > kTileMinQueries;
-    const int64_t ngroups = ceil_div(n, tiled ? tc.tq : cfg.rq);
+// With many queries the table is scanned on the tensor cores (scan_tc.cu, 3xTF32) and the
+// survivors re-scored exactly in the k-select; with few, by the SIMT scan kernels.
+void IndexIVFFlatB200::run_coarse_(const float* xd, int64_t n, int kc, int32_t* out_ids32,
+                                   int64_t* out_ids64, float* out_dis, cudaStream_t st) const {
+    Impl& m = *impl_;
+    const int nf4 = m.nf4;
+    const int kp_tc = scan_tc_kpart(nf4, kc);
+    const bool tc = m.use_tc && n > 32 && kp_tc > 0;
+    const int kp = tc ? kp_tc : kc;
+    const TileCfg tcfg = choose_tile_cfg(nf4, kp);
+    const ScanCfg cfg = choose_scan_cfg(nf4, kp);
+    const bool tiled = !tc && tcfg.ok && n > kTileMinQueries;
+    const int64_t tq = tc ? kTcTQ : (tiled ? tcfg.tq : cfg.rq);
+    const int64_t ngroups = ceil_div(n, tq);
     const int64_t nblk = ceil_div((int64_t)nlist, kBlockRows);
-    const int64_t rows_step = tiled ? 16 : kScanRowsPerStep; // 32-row blocks per step
-    const int64_t target = tiled ? 148 * 2 * 2 : kTargetScanItems;
+    const int64_t rows_step = tc ? 4 : (tiled ? 16 : kScanRowsPerStep); // 32-row blocks per step
+    const int64_t target = tc ? 148 * 2 : (tiled ? 148 * 2 * 2 : kTargetScanItems);
     int64_t S = ceil_div(target, ngroups);
     S = std::max<int64_t>(1, std::min<int64_t>(S, std::max<int64_t>(1, nblk / rows_step)));
     S = std::min<int64_t>(S, 64);
-    part.reserve((size_t)n * S * kc * sizeof(uint64_t));
-    cplan.reserve(16);
-    int32_t* grp_start = cplan.as<int32_t>();
-    uint32_t* item_off = cplan.as<uint32_t>() + 2;
+    m.part.reserve((size_t)n * S * kp * sizeof(uint64_t));
+    m.cplan.reserve(16);
+    int32_t* grp_start = m.cplan.as<int32_t>();
+    uint32_t* item_off = m.cplan.as<uint32_t>() + 2;
     CUDA_CHECK(launch_plan_single(grp_start, item_off, (int)n, (uint32_t)(ngroups * S), st));
-    if (tiled) {
-        TileScanArgs a;
-        a.tmap = cent_map;
-        a.list_blk0 = cent_meta.as<uint32_t>();
-        a.list_len = cent_meta.as<int32_t>() + 1;
+    if (tc) {
+        TcScanArgs a;
+        a.tmap = m.cent_map_tc;
+        a.list_blk0 = m.cent_meta.as<uint32_t>();
+        a.list_len = m.cent_meta.as<int32_t>() + 1;
         a.grp_start = grp_start;
         a.pair_query = nullptr;
         a.item_off = item_off;
+        a.norms = m.cent_norms.as<float>();
         a.nlists = 1;
         a.nsplit = (int)S;
-        a.k = kc;
-        a.cap = tc.cap;
+        a.kpart = kp;
         a.d = d;
         a.nf4 = nf4;
-        a.nstages = tc.nst;
+        a.nstages = kTcStages;
         a.queries = xd;
-        a.part = part.as<uint64_t>();
-        CUDA_CHECK(launch_ivf_scan_tile(metric, (uint32_t)(ngroups * S), a, st));
-    } else {
-        ScanArgs a;
-        a.slab = cent_slab.as<float4>();
-        a.list_blk0 = cent_meta.as<uint32_t>();
-        a.list_len = cent_meta.as<int32_t>() + 1;
+        a.part = m.part.as<uint64_t>();
+        CUDA_CHECK(launch_ivf_scan_tc(metric_type, (uint32_t)(ngroups * S), a, st));
+    } else if (tiled) {
+        TileScanArgs a;
+        a.tmap = m.cent_map;
+        a.list_blk0 = m.cent_meta.as<uint32_t>();
+        a.list_len = m.cent_meta.as<int32_t>() + 1;
         a.grp_start = grp_start;
         a.pair_query = nullptr;
         a.item_off = item_off;
         a.nlists = 1;
         a.nsplit = (int)S;
-        a.k = kc;
+        a.k = kp;
+        a.cap = tcfg.cap;
+        a.d = d;
+        a.nf4 = nf4;
+        a.nstages = tcfg.nst;
+        a.queries = xd;
+        a.part = m.part.as<uint64_t>();
+        CUDA_CHECK(launch_ivf_scan_tile(metric_type, (uint32_t)(ngroups * S), a, st));
+    } else {
+        ScanArgs a;
+        a.slab = m.cent_slab.as<float4>();
+        a.list_blk0 = m.cent_meta.as<uint32_t>();
+        a.list_len = m.cent_meta.as<int32_t>() + 1;
+        a.grp_start = grp_start;
+        a.pair_query = nullptr;
+        a.item_off = item_off;
+        a.nlists = 1;
+        a.nsplit = (int)S;
+        a.k = kp;
         a.cap = cfg.cap;
         a.d = d;
         a.nf4 = nf4;
         a.queries = xd;
-        a.part = part.as<uint64_t>();
-        CUDA_CHECK(launch_ivf_scan(metric, cfg.rq, cfg.wpc, (uint32_t)(ngroups * S), a, st));
+        a.part = m.part.as<uint64_t>();
+        CUDA_CHECK(launch_ivf_scan(metric_type, cfg.rq, cfg.wpc, (uint32_t)(ngroups * S), a, st));
     }
     SelectArgs s;
-    s.part = part.as<uint64_t>();
+    s.part = m.part.as<uint64_t>();
     s.slot_of = nullptr;
     s.n = (int)n;
     s.nseg = 1;
     s.nsplit = (int)S;
-    s.kpart = kc;
+    s.kpart = kp;
     s.k = kc;
-    s.metric = metric;
+    s.metric = metric_type;
     s.ids = nullptr;
     s.out_dis = out_dis;
     s.out_ids64 = out_ids64;
     s.out_ids32 = out_ids32;
+    if (tc) {
+        s.slab = m.cent_slab.as<float4>();
+        s.queries = xd;
+        s.d = d;
+        s.nf4 = nf4;
+        s.rerank_extra = kRerankExtra;
+    }
     CUDA_CHECK(launch_select(s, st));
 }
 
@@ -430,10 +478,10 @@ struct BatchPlan {
     int64_t S;
 };
 
-static BatchPlan plan_batch(int nf4, int64_t k, int64_t nb, int64_t nprobe, int64_t nlists_owned,
-                            int64_t nstored) {
+static BatchPlan plan_batch(int nf4, int64_t kpart, int64_t nb, int64_t nprobe,
+                            int64_t nlists_owned, int64_t nstored) {
     BatchPlan bp;
-    bp.cfg = choose_scan_cfg(nf4, (int)k);
+    bp.cfg = choose_scan_cfg(nf4, (int)kpart);
     const int64_t pairs = nb * nprobe;
     const int64_t items_est =
             std::max<int64_t>(1, std::max(ceil_div(pairs, bp.cfg.rq), std::min(pairs, nlists_owned)));
@@ -473,12 +521,17 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
     const bool a_dev = assign && is_device_pointer(assign);
     const int64_t nlists_owned = (int64_t)(m.list_hi - m.list_lo);
 
+    // tensor-core scan for the lists probed by many queries (d <= 128, moderate k)
+    const int kp_tc = scan_tc_kpart(m.nf4, (int)std::min<int64_t>(k, 1 << 20));
+    const bool tc = m.use_tc && kp_tc > 0;
+    const int64_t kp = tc ? kp_tc : k; // entries per partial list
+
     // batch size: bound the partial-candidate scratch
     int64_t nb = std::min<int64_t>(n, 32768);
-    BatchPlan bp = plan_batch(m.nf4, k, nb, np, nlists_owned, m.nstored);
-    while (nb > 1 && (size_t)nb * np * bp.S * k * sizeof(uint64_t) > ((size_t)2 << 30)) {
+    BatchPlan bp = plan_batch(m.nf4, kp, nb, np, nlists_owned, m.nstored);
+    while (nb > 1 && (size_t)nb * np * bp.S * kp * sizeof(uint64_t) > ((size_t)2 << 30)) {
         nb = (nb + 1) / 2;
-        bp = plan_batch(m.nf4, k, nb, np, nlists_owned, m.nstored);
+        bp = plan_batch(m.nf4, kp, nb, np, nlists_owned, m.nstored);
     }
     cudaStream_t st = m.stream;
     unsigned long long* dstats = m.dev_stats.as<unsigned long long>();
@@ -486,7 +539,7 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
     for (int64_t i0 = 0; i0 < n; i0 += nb) {
         const int64_t ni = std::min(nb, n - i0);
         const int64_t pairs = ni * np;
-        bp = plan_batch(m.nf4, k, ni, np, nlists_owned, m.nstored);
+        bp = plan_batch(m.nf4, kp, ni, np, nlists_owned, m.nstored);
         CUDA_CHECK(cudaEventRecord(m.ev[0], st));
         // queries
         const float* xd = x + i0 * d;
@@ -520,9 +573,8 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
             CUDA_CHECK(launch_i64_to_i32(ad, m.coarse_ids.as<int32_t>(), pairs, 0, (int32_t)nlist,
                                          dstats + 3, st));
         } else {
-            run_coarse(metric_type, d, m.nf4, nlist, m.cent_slab, m.cent_map, m.cent_meta, m.cplan, m.part, xd,
-                       ni, (int)np, m.coarse_ids.as<int32_t>(), nullptr, m.coarse_dis.as<float>(),
-                       st);
+            run_coarse_(xd, ni, (int)np, m.coarse_ids.as<int32_t>(), nullptr,
+                        m.coarse_dis.as<float>(), st);
         }
         CUDA_CHECK(cudaEventRecord(m.ev[1], st));
         // stage 2: invert the probe table, scan the lists
@@ -531,10 +583,12 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
         m.grp_start.reserve((nlist + 1) * sizeof(int32_t));
         m.item_off.reserve((nlist + 1) * sizeof(uint32_t));
         m.item_off_tile.reserve((nlist + 1) * sizeof(uint32_t));
-        const TileCfg tc = choose_tile_cfg(m.nf4, (int)k);
+        TileCfg tcfg = choose_tile_cfg(m.nf4, (int)kp);
+        if (tc)
+            tcfg.ok = false; // the tensor-core kernel takes the many-query lists instead
         m.pair_query.reserve((size_t)pairs * sizeof(int32_t));
         m.slot_of.reserve((size_t)pairs * sizeof(int32_t));
-        m.part.reserve((size_t)pairs * bp.S * k * sizeof(uint64_t));
+        m.part.reserve((size_t)pairs * bp.S * kp * sizeof(uint64_t));
         PlanArgs pa;
         pa.coarse_ids = m.coarse_ids.as<int32_t>();
         pa.n = (int)ni;
@@ -549,7 +603,7 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
         pa.slot_of = m.slot_of.as<int32_t>();
         pa.rq = bp.cfg.rq;
         pa.nsplit = (int)bp.S;
-        pa.tile_tq = tc.ok ? tc.tq : 0;
+        pa.tile_tq = tc ? kTcTQ : (tcfg.ok ? tcfg.tq : 0);
         pa.tile_min = kTileMinQueries;
         pa.item_off_tile = m.item_off_tile.as<uint32_t>();
         pa.stats = dstats;
@@ -564,7 +618,7 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
         sa.item_off = pa.item_off;
         sa.nlists = (int)nlist;
         sa.nsplit = (int)bp.S;
-        sa.k = (int)k;
+        sa.k = (int)kp;
         sa.cap = bp.cfg.cap;
         sa.d = d;
         sa.nf4 = m.nf4;
@@ -573,7 +627,29 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
         const int64_t max_items =
                 (ceil_div(pairs, bp.cfg.rq) + std::min<int64_t>(pairs, (int64_t)nlist)) * bp.S;
         CUDA_CHECK(launch_ivf_scan(metric_type, bp.cfg.rq, bp.cfg.wpc, (uint32_t)max_items, sa, st));
-        if (tc.ok) {
+        if (tc) {
+            // lists probed by more than kTileMinQueries queries of this batch: tensor cores
+            TcScanArgs ta;
+            ta.tmap = m.lists_map_tc;
+            ta.list_blk0 = sa.list_blk0;
+            ta.list_len = sa.list_len;
+            ta.grp_start = pa.grp_start;
+            ta.pair_query = pa.pair_query;
+            ta.item_off = pa.item_off_tile;
+            ta.norms = m.norms.as<float>();
+            ta.nlists = (int)nlist;
+            ta.nsplit = (int)bp.S;
+            ta.kpart = (int)kp;
+            ta.d = d;
+            ta.nf4 = m.nf4;
+            ta.nstages = kTcStages;
+            ta.queries = xd;
+            ta.part = sa.part;
+            const int64_t max_tiles =
+                    (pairs / kTcTQ + std::min<int64_t>(pairs / (kTileMinQueries + 1), (int64_t)nlist)) *
+                    bp.S;
+            CUDA_CHECK(launch_ivf_scan_tc(metric_type, (uint32_t)max_tiles, ta, st));
+        } else if (tcfg.ok) {
             // lists probed by more than kTileMinQueries queries of this batch
             TileScanArgs ta;
             ta.tmap = m.lists_map;
@@ -584,15 +660,15 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
             ta.item_off = pa.item_off_tile;
             ta.nlists = (int)nlist;
             ta.nsplit = (int)bp.S;
-            ta.k = (int)k;
-            ta.cap = tc.cap;
+            ta.k = (int)kp;
+            ta.cap = tcfg.cap;
             ta.d = d;
             ta.nf4 = m.nf4;
-            ta.nstages = tc.nst;
+            ta.nstages = tcfg.nst;
             ta.queries = xd;
             ta.part = sa.part;
             const int64_t max_tiles =
-                    (pairs / tc.tq + std::min<int64_t>(pairs / (kTileMinQueries + 1), (int64_t)nlist)) *
+                    (pairs / tcfg.tq + std::min<int64_t>(pairs / (kTileMinQueries + 1), (int64_t)nlist)) *
                     bp.S;
             CUDA_CHECK(launch_ivf_scan_tile(metric_type, (uint32_t)max_tiles, ta, st));
         }
@@ -604,10 +680,17 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
         se.n = (int)ni;
         se.nseg = (int)np;
         se.nsplit = (int)bp.S;
-        se.kpart = (int)k;
+        se.kpart = (int)kp;
         se.k = (int)k;
         se.metric = metric_type;
         se.ids = m.ids.as<int64_t>();
+        if (tc) {
+            se.slab = m.slab.as<float4>();
+            se.queries = xd;
+            se.d = d;
+            se.nf4 = m.nf4;
+            se.rerank_extra = kRerankExtra;
+        }
         se.out_dis = Dd;
         se.out_ids64 = Id;
         se.out_ids32 = nullptr;
@@ -676,8 +759,7 @@ void IndexIVFFlatB200::quantize(int64_t n, const float* x, int64_t kc, float* Dq
             m.dev_I.reserve((size_t)ni * kc * sizeof(int64_t));
             Id = m.dev_I.as<int64_t>();
         }
-        run_coarse(metric_type, d, m.nf4, nlist, m.cent_slab, m.cent_map, m.cent_meta, m.cplan, m.part, xd, ni,
-                   (int)kc, nullptr, Id, Dd, st);
+        run_coarse_(xd, ni, (int)kc, nullptr, Id, Dd, st);
         if (!D_dev)
             CUDA_CHECK(cudaMemcpyAsync(Dq + i0 * kc, Dd, (size_t)ni * kc * sizeof(float),
                                        cudaMemcpyDeviceToHost, st));
@@ -754,9 +836,8 @@ void IndexIVFFlatB200::add_core(int64_t n, const float* x, const int64_t* xids,
             // quantizer->assign == search with k = 1 (faiss/Index.cpp:84-88)
             for (int64_t j0 = 0; j0 < ni; j0 += 32768) {
                 const int64_t nj = std::min<int64_t>(32768, ni - j0);
-                run_coarse(metric_type, d, m.nf4, nlist, m.cent_slab, m.cent_map, m.cent_meta, m.cplan, m.part,
-                           xd + j0 * d, nj, 1, nullptr, m.dev_I.as<int64_t>() + j0,
-                           m.dev_D.as<float>() + j0, st);
+                run_coarse_(xd + j0 * d, nj, 1, nullptr, m.dev_I.as<int64_t>() + j0,
+                            m.dev_D.as<float>() + j0, st);
             }
             CUDA_CHECK(cudaMemcpyAsync(h_assign.data() + i0, m.dev_I.p,
                                        (size_t)ni * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
@@ -843,6 +924,12 @@ void IndexIVFFlatB200::add_core(int64_t n, const float* x, const int64_t* xids,
     m.slab = nslab;
     m.ids = nids;
     CUDA_CHECK(make_slab_tensor_map(m.lists_map, m.slab.p, m.nf4, blocks));
+    CUDA_CHECK(make_slab_tensor_map_tc(m.lists_map_tc, m.slab.p, m.nf4, blocks));
+    m.norms.release();
+    m.norms.reserve(std::max<size_t>(blocks * kBlockRows * sizeof(float), 16));
+    CUDA_CHECK(launch_row_norms(m.slab.as<float4>(), (int64_t)(blocks * kBlockRows), m.nf4,
+                                m.norms.as<float>(), st));
+    CUDA_CHECK(cudaStreamSynchronize(st));
     nblk0.release();
     m.h_len.swap(new_len);
     m.h_blk0.swap(new_blk0);

@@ -79,6 +79,9 @@ class IndexIVFFlatB200 {
 
   private:
     struct Impl;
+    // K1: the kc nearest centroids of n device-resident queries (ids as int32 and/or int64)
+    void run_coarse_(const float* xd, int64_t n, int kc, int32_t* out_ids32, int64_t* out_ids64,
+                     float* out_dis, cudaStream_t st) const;
     Impl* impl_;
     int device_;
     mutable std::mutex mu_;

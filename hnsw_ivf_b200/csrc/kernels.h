@@ -68,6 +68,36 @@ cudaError_t make_slab_tensor_map(void* map_out, const void* slab, int nf4, uint6
 cudaError_t launch_ivf_scan_tile(int metric, uint32_t max_items, const TileScanArgs& a,
                                  cudaStream_t st);
 
+// ---- K1 and K2 on the tensor cores (scan_tc.cu): tcgen05 3xTF32, d <= 128 ----------------------
+// One CTA per work item (list, tile of <= kTcTQ queries probing it, row split). Scores are
+// approximate (~1e-6 of |x||y|): launch_select must be given rerank = true downstream.
+constexpr int kTcTQ = 128;
+struct TcScanArgs {
+    const void* tmap;           // HOST pointer to the tensor map from make_slab_tensor_map_tc
+    const uint32_t* list_blk0;
+    const int32_t* list_len;
+    const int32_t* grp_start;   // [nlists+1]
+    const int32_t* pair_query;  // [npairs] (nullptr: identity)
+    const uint32_t* item_off;   // [nlists+1] exclusive prefix of ceil(count/kTcTQ)*nsplit
+    const float* norms;         // [slab rows] |y|^2 (read for METRIC_L2 only)
+    int nlists;
+    int nsplit;
+    int kpart;                  // keys kept per (pair, split): 16 or 32, from scan_tc_kpart
+    int d;
+    int nf4;                    // <= 32
+    int nstages;                // TMA ring depth (kTcStages)
+    const float* queries;
+    uint64_t* part;             // [npairs][nsplit][kpart]
+};
+constexpr int kTcStages = 6;
+// entries per partial list the tensor-core scan keeps for a request of k (>= k, with a margin
+// when there is room); 0 = not supported (d > 128 or k > 32)
+int scan_tc_kpart(int nf4, int k);
+size_t scan_tc_smem_bytes(int nstages);
+cudaError_t make_slab_tensor_map_tc(void* map_out, const void* slab, int nf4, uint64_t nblocks);
+cudaError_t launch_ivf_scan_tc(int metric, uint32_t max_items, const TcScanArgs& a,
+                               cudaStream_t st);
+
 // ---- planning: invert the probe table into per-list query groups -------------------------------
 struct PlanArgs {
     const int32_t* coarse_ids;  // [n][nprobe], -1 = no probe
@@ -103,6 +133,13 @@ struct SelectArgs {
     float* out_dis;             // [n][k]
     int64_t* out_ids64;         // [n][k] or nullptr
     int32_t* out_ids32;         // [n][k] or nullptr
+    // exact re-rank (needed when any partial list came from the tensor-core scan): the best
+    // k + rerank_extra keys are re-scored in plain fp32 (dimension order 0..d-1, the arithmetic of
+    // scan.cu) from the slab and the query before the final ordering. slab == nullptr: off.
+    const float4* slab = nullptr;
+    const float* queries = nullptr;
+    int d = 0, nf4 = 0;
+    int rerank_extra = 0;
 };
 cudaError_t launch_select(const SelectArgs& a, cudaStream_t st);
 
@@ -124,6 +161,9 @@ cudaError_t launch_move_blocks(const float4* old_slab, const int64_t* old_ids,
 // gather a list back to row-major (get_list / reconstruct)
 cudaError_t launch_gather_rows(const float* slab, int64_t row0, int64_t nrows, int d, int nf4,
                                float* out, cudaStream_t st);
+// |row|^2 of every slab row (the L2 epilogue of the tensor-core scan): rows [0, nrows)
+cudaError_t launch_row_norms(const float4* slab, int64_t nrows, int nf4, float* norms,
+                             cudaStream_t st);
 cudaError_t launch_i64_to_i32(const int64_t* in, int32_t* out, int64_t n, int32_t lo, int32_t hi,
                               unsigned long long* bad, cudaStream_t st);
 

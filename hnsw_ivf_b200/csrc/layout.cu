@@ -113,6 +113,34 @@ cudaError_t launch_move_blocks(const float4* old_slab, const int64_t* old_ids,
     return cudaGetLastError();
 }
 
+// one thread per row: lane = row within its 32-row block, so each column read is coalesced
+__global__ void row_norms_kernel(const float4* __restrict__ slab, int64_t nrows, int nf4,
+                                 float* __restrict__ norms) {
+    for (int64_t row = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; row < nrows;
+         row += (int64_t)gridDim.x * blockDim.x) {
+        const float4* p =
+                slab + (row / kBlockRows) * (int64_t)nf4 * kBlockRows + (row % kBlockRows);
+        float acc = 0.f;
+        for (int c = 0; c < nf4; ++c) {
+            const float4 v = p[(int64_t)c * kBlockRows];
+            acc = fmaf(v.x, v.x, acc);
+            acc = fmaf(v.y, v.y, acc);
+            acc = fmaf(v.z, v.z, acc);
+            acc = fmaf(v.w, v.w, acc);
+        }
+        norms[row] = acc;
+    }
+}
+
+cudaError_t launch_row_norms(const float4* slab, int64_t nrows, int nf4, float* norms,
+                             cudaStream_t st) {
+    if (nrows == 0)
+        return cudaSuccess;
+    row_norms_kernel<<<grid_for(nrows, 256), 256, 0, st>>>(slab, nrows, nf4, norms);
+    count_launches(1);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_gather_rows(const float* slab, int64_t row0, int64_t nrows, int d, int nf4,
                                float* out, cudaStream_t st) {
     if (nrows == 0)

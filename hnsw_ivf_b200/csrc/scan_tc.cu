@@ -1,0 +1,473 @@
+// scan_tc.cu -- the tensor-core form of the scan: K1 (coarse quantizer) and K2 for lists that more
+// than a handful of queries of the batch probe, for d <= 128.
+//
+// Same contract as scan.cu / scan_tile.cu (IVFFlatScanner::scan_codes,
+// faiss/IndexIVFFlat.cpp:155-179, applied to every (query, probe) pair; for K1 knn_L2sqr /
+// knn_inner_product over the centroid table, faiss/utils/distances.cpp:885-920,836-871): the best
+// `kpart` keys of every (pair, row split) are left in `part`. The scores this kernel produces are
+// 3xTF32 products (x_hi*y_hi + x_lo*y_hi + x_hi*y_lo, fp32 accumulate): good to ~1e-6 of |x||y|,
+// which is enough to SELECT; the k-select (select.cu) recomputes the survivors' distances in plain
+// fp32 in the reference's operation order before the final ordering, so the distances that leave
+// the library never come from the tensor core.
+//
+// Work item = (list, tile of <= 128 queries probing it, row split); one CTA each.
+//   D[128 queries x 128 rows] (TMEM, two buffers) += A[128 x 8] (TMEM) * B[128 rows x 8]^T (smem)
+//  * A: the query tile, scaled by -1 (inner product) or -2 (L2), split into tf32 hi / lo parts and
+//    written ONCE into tensor memory (tcgen05.st): 2 x d columns, lane = query.
+//  * B hi: list rows straight from HBM by TMA. The slab's 32-row dimension-interleaved blocks
+//    (common.cuh) are exactly the K-major no-swizzle UMMA operand layout (8 rows x 16 bytes = one
+//    128-byte core matrix, SBO = 128 B); the TMA box {128 floats, 4 blocks, 8 columns} puts the
+//    column stride at LBO = 2048 B. The tensor core ignores the low 13 mantissa bits of an fp32
+//    operand (measured, tools/tc_probe.cu), so the raw fp32 rows ARE the hi part.
+//  * B lo: y - trunc_tf32(y), rounded to tf32, computed by the split warps from the hi stage into a
+//    twin stage (generic-proxy writes + fence.proxy.async).
+//  * One thread issues the MMAs (3 per 8 dims); stages are released by tcgen05.commit.
+//  * Epilogue (4 warps, thread = query, lanes of TMEM): tcgen05.ld 32 columns at a time, add the
+//    row norm (L2: |y|^2 - 2xy + |x|^2), strict compare against the thread's own threshold (the
+//    reference's C::cmp(simi[0], dis)) into a 32-bit pass mask. Each thread keeps its KP best
+//    (score, row) SORTED IN REGISTERS, so the threshold is always the current KP-th best (as the
+//    reference's heap top is). Passing scores are staged in shared memory and every lane walks
+//    its OWN mask (ffs), so a warp spends max-over-lanes(popc) insertions per chunk, not one per
+//    column that any lane accepted. The accumulator buffer goes back to the MMA thread right
+//    after the last load.
+#include "common.cuh"
+#include "kernels.h"
+#include "tc_ptx.cuh"
+
+namespace b200ivf {
+
+namespace {
+
+using namespace ptx;
+
+constexpr int kTcThreads = 320;   // warps 0-3 epilogue, 4 TMA, 5 MMA, 6-9 split
+constexpr int kTcSplitWarp0 = 6;
+constexpr int kTcSplitThreads = 128;
+constexpr int kTcKC = 8;          // float4 columns per stage (4 MMA k-steps)
+constexpr int kTcTileBlocks = 4;  // 32-row blocks per MMA tile (N = 128)
+constexpr int kTcStageF4 = kTcKC * kTcTileBlocks * kBlockRows; // 1024 float4 = 16 KB
+constexpr uint32_t kTcLBO = kTcTileBlocks * 512, kTcSBO = 128;
+constexpr int kTcMaxStages = 8;
+constexpr uint32_t kTcColsD = 0, kTcColsAhi = 256, kTcColsAlo = 384;
+
+__device__ __forceinline__ float tf32_trunc(float x) {
+    return __uint_as_float(__float_as_uint(x) & 0xffffe000u);
+}
+__device__ __forceinline__ float tf32_rn(float x) {
+    return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u);
+}
+__device__ __forceinline__ float tf32_lo(float y) {
+    return tf32_rn(y - tf32_trunc(y));
+}
+
+struct TcSmem {
+    float4* hi;        // [nst][kTcStageF4]
+    float4* lo;        // [nst][kTcStageF4]
+    float* stg;        // [4 warps][32 columns][32 lanes] scores of the current chunk
+    uint64_t* full;    // [8] TMA landed
+    uint64_t* lo_rdy;  // [8] lo stage written
+    uint64_t* empty;   // [8] MMAs that read the stage are done
+    uint64_t* d_full;  // [2] accumulator buffer complete
+    uint64_t* d_empty; // [2] accumulator buffer drained by the epilogue
+    uint64_t* a_rdy;   // [1] query tile is in TMEM
+    uint32_t* tmem;    // [1]
+};
+
+__device__ __forceinline__ TcSmem carve(unsigned char* raw, int nst) {
+    TcSmem s;
+    s.hi = reinterpret_cast<float4*>(raw);
+    s.lo = s.hi + (size_t)nst * kTcStageF4;
+    s.stg = reinterpret_cast<float*>(s.lo + (size_t)nst * kTcStageF4);
+    s.full = reinterpret_cast<uint64_t*>(s.stg + 4 * 32 * 32);
+    s.lo_rdy = s.full + kTcMaxStages;
+    s.empty = s.lo_rdy + kTcMaxStages;
+    s.d_full = s.empty + kTcMaxStages;
+    s.d_empty = s.d_full + 2;
+    s.a_rdy = s.d_empty + 2;
+    s.tmem = reinterpret_cast<uint32_t*>(s.a_rdy + 1);
+    return s;
+}
+
+template <int METRIC, int KP>
+__global__ void __launch_bounds__(kTcThreads, 1)
+        ivf_scan_tc_kernel(const TcScanArgs a, const __grid_constant__ CUtensorMap tmap) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    const int tid = threadIdx.x;
+    const int lane = tid & 31;
+    const int warp = tid >> 5;
+
+    // ---- which item --------------------------------------------------------------------------
+    const uint32_t item = blockIdx.x;
+    if (item >= a.item_off[a.nlists])
+        return;
+    int lo_l = 0, hi_l = a.nlists;
+    while (hi_l - lo_l > 1) {
+        const int mid = (lo_l + hi_l) >> 1;
+        if (a.item_off[mid] <= item)
+            lo_l = mid;
+        else
+            hi_l = mid;
+    }
+    const int l = lo_l;
+    const int g0 = a.grp_start[l];
+    const int cnt_l = a.grp_start[l + 1] - g0;
+    const int nsub = (cnt_l + kTcTQ - 1) / kTcTQ;
+    const uint32_t local = item - a.item_off[l];
+    const int split = (int)(local / (uint32_t)nsub);
+    const int sub = (int)(local % (uint32_t)nsub);
+    const int q0 = g0 + sub * kTcTQ;
+    const int nqw = min(kTcTQ, cnt_l - sub * kTcTQ);
+
+    const int len = a.list_len[l];
+    const int nb = (len + kBlockRows - 1) / kBlockRows;
+    const int b0 = (int)(((long long)nb * split) / a.nsplit);
+    const int b1 = (int)(((long long)nb * (split + 1)) / a.nsplit);
+    const uint32_t blk0 = a.list_blk0[l];
+    const int nf4 = a.nf4;
+    const int nst = a.nstages;
+    const int ntiles = (b1 - b0 + kTcTileBlocks - 1) / kTcTileBlocks;
+    const int nsg = (nf4 + kTcKC - 1) / kTcKC;  // stages per tile
+    const int nks = (nf4 + 1) >> 1;             // MMA k-steps (8 dims each) per tile
+    const int niter = ntiles * nsg;
+
+    const TcSmem s = carve(smem_raw, nst);
+
+    if (tid == 0) {
+        for (int i = 0; i < kTcMaxStages; ++i) {
+            mbar_init(&s.full[i], 1);
+            mbar_init(&s.lo_rdy[i], kTcSplitThreads / 32);
+            mbar_init(&s.empty[i], 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&s.d_full[i], 1);
+            mbar_init(&s.d_empty[i], 4);
+        }
+        mbar_init(s.a_rdy, 4);
+        fence_barrier_init();
+    }
+    if (warp == 5) {
+        tmem_alloc(s.tmem, 512);
+        tmem_relinquish();
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem = *s.tmem;
+
+    if (warp == 4) {
+        // ======================= TMA producer ===================================================
+        if (lane == 0) {
+            tma_prefetch_desc(&tmap);
+            int st = 0;
+            uint32_t ph = 0;
+            for (int t = 0; t < ntiles; ++t) {
+                const int blk = (int)blk0 + b0 + t * kTcTileBlocks;
+                for (int sg = 0; sg < nsg; ++sg) {
+                    if (t * nsg + sg >= nst)
+                        mbar_wait(&s.empty[st], ph ^ 1u);
+                    mbar_expect_tx(&s.full[st], (uint32_t)(kTcStageF4 * sizeof(float4)));
+                    tma_load_3d(s.hi + (size_t)st * kTcStageF4, &tmap, 0, blk, sg * kTcKC,
+                                &s.full[st]);
+                    if (++st == nst) {
+                        st = 0;
+                        ph ^= 1u;
+                    }
+                }
+            }
+        }
+    } else if (warp == 5) {
+        // ======================= MMA issuer =====================================================
+        if (lane == 0) {
+            const uint32_t idesc = make_idesc_tf32(kTcTQ, kTcTileBlocks * kBlockRows);
+            mbar_wait(s.a_rdy, 0);
+            tc_fence_after_sync();
+            int st = 0;
+            uint32_t ph = 0;
+            for (int t = 0; t < ntiles; ++t) {
+                const int b = t & 1;
+                if (t >= 2) {
+                    mbar_wait(&s.d_empty[b], (uint32_t)(((t >> 1) & 1) ^ 1));
+                    tc_fence_after_sync();
+                }
+                const uint32_t tD = tmem + kTcColsD + (uint32_t)b * 128u;
+                for (int sg = 0; sg < nsg; ++sg) {
+                    mbar_wait(&s.full[st], ph);
+                    mbar_wait(&s.lo_rdy[st], ph);
+                    tc_fence_after_sync();
+                    const uint32_t bhi = smem_u32(s.hi + (size_t)st * kTcStageF4);
+                    const uint32_t blo = smem_u32(s.lo + (size_t)st * kTcStageF4);
+                    const int ks0 = sg * (kTcKC / 2);
+                    const int ksn = min(kTcKC / 2, nks - ks0);
+                    for (int ks = 0; ks < ksn; ++ks) {
+                        const uint64_t dhi =
+                                make_smem_desc_kmajor_noswz(bhi + ks * 2 * kTcLBO, kTcLBO, kTcSBO);
+                        const uint64_t dlo =
+                                make_smem_desc_kmajor_noswz(blo + ks * 2 * kTcLBO, kTcLBO, kTcSBO);
+                        const uint32_t acol = (uint32_t)(ks0 + ks) * 8u;
+                        // small terms first, the big product last
+                        mma_tf32_ts(tD, tmem + kTcColsAlo + acol, dhi, idesc,
+                                    (sg | ks) != 0 ? 1u : 0u);
+                        mma_tf32_ts(tD, tmem + kTcColsAhi + acol, dlo, idesc, 1u);
+                        mma_tf32_ts(tD, tmem + kTcColsAhi + acol, dhi, idesc, 1u);
+                    }
+                    mma_commit(&s.empty[st]);
+                    if (++st == nst) {
+                        st = 0;
+                        ph ^= 1u;
+                    }
+                }
+                mma_commit(&s.d_full[b]);
+            }
+        }
+    } else if (warp >= kTcSplitWarp0) {
+        // ======================= split warps: lo = tf32(y - trunc(y)) ===========================
+        const int t0 = tid - kTcSplitWarp0 * 32;
+        int st = 0;
+        uint32_t ph = 0;
+        for (int it = 0; it < niter; ++it) {
+            mbar_wait(&s.full[st], ph);
+            const float4* src = s.hi + (size_t)st * kTcStageF4;
+            float4* dst = s.lo + (size_t)st * kTcStageF4;
+#pragma unroll
+            for (int i = 0; i < kTcStageF4 / kTcSplitThreads; i += 4) {
+                float4 y[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    y[u] = src[t0 + (i + u) * kTcSplitThreads];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    float4 r;
+                    r.x = tf32_lo(y[u].x);
+                    r.y = tf32_lo(y[u].y);
+                    r.z = tf32_lo(y[u].z);
+                    r.w = tf32_lo(y[u].w);
+                    dst[t0 + (i + u) * kTcSplitThreads] = r;
+                }
+            }
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0)
+                mbar_arrive(&s.lo_rdy[st]);
+            if (++st == nst) {
+                st = 0;
+                ph ^= 1u;
+            }
+        }
+    } else {
+        // ======================= epilogue warps 0-3: thread = query =============================
+        const int qi = tid; // query slot of the tile == TMEM lane
+        const uint32_t lane_addr = (uint32_t)(warp * 32) << 16;
+        const bool live = qi < nqw;
+        float xn = 0.f;
+        {
+            // query -> TMEM (A operand): scaled, split into hi / lo, zero padded to 8 * nks dims
+            const int q = live ? (a.pair_query ? a.pair_query[q0 + qi] : (q0 + qi)) : -1;
+            const float* src = a.queries + (size_t)(q < 0 ? 0 : q) * a.d;
+            const float scale = METRIC == kMetricL2 ? -2.f : -1.f;
+            for (int c = 0; c < nks * 8; c += 8) {
+                uint32_t hi[8], lo[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    float x = 0.f;
+                    if (live && c + i < a.d)
+                        x = __ldg(src + c + i);
+                    xn = fmaf(x, x, xn);
+                    x *= scale;
+                    const float h = tf32_trunc(x);
+                    hi[i] = __float_as_uint(h);
+                    lo[i] = __float_as_uint(tf32_rn(x - h));
+                }
+                tmem_st_32x32b_x8(tmem + kTcColsAhi + lane_addr + (uint32_t)c, hi);
+                tmem_st_32x32b_x8(tmem + kTcColsAlo + lane_addr + (uint32_t)c, lo);
+            }
+            tmem_st_wait();
+            tc_fence_before_sync();
+            __syncwarp();
+            if (lane == 0)
+                mbar_arrive(s.a_rdy);
+        }
+        // the thread's KP best so far, ascending; empty slots hold FLT_MAX (heap_heapify's fill,
+        // faiss/utils/Heap.h:333) and row ~0; dead lanes hold -inf so that nothing passes
+        float vs[KP];
+        uint32_t vr[KP];
+#pragma unroll
+        for (int j = 0; j < KP; ++j) {
+            vs[j] = live ? kNeutralScore : -__int_as_float(0x7f800000);
+            vr[j] = 0xffffffffu;
+        }
+        float* stg = s.stg + warp * 1024 + lane;
+
+        for (int t = 0; t < ntiles; ++t) {
+            const int b = t & 1;
+            const int tb = b0 + t * kTcTileBlocks; // first block of the tile, list-relative
+            const int nvalid = min(kTcTileBlocks * kBlockRows,
+                                   min((b1 - tb) * kBlockRows, len - tb * kBlockRows));
+            const uint32_t grow0 = (blk0 + (uint32_t)tb) * kBlockRows;
+            mbar_wait(&s.d_full[b], (uint32_t)((t >> 1) & 1));
+            tc_fence_after_sync();
+            const uint32_t tD = tmem + kTcColsD + (uint32_t)b * 128u + lane_addr;
+#pragma unroll 1
+            for (int c0 = 0; c0 < kTcTileBlocks * kBlockRows; c0 += 32) {
+                uint32_t r[32];
+                tmem_ld_32x32b_x32(tD + (uint32_t)c0, r);
+                tmem_ld_wait();
+                if (c0 == kTcTileBlocks * kBlockRows - 32) {
+                    // accumulator buffer drained: hand it back to the MMA thread
+                    tc_fence_before_sync();
+                    __syncwarp();
+                    if (lane == 0)
+                        mbar_arrive(&s.d_empty[b]);
+                }
+                if (c0 >= nvalid)
+                    continue;
+                float sc[32];
+                if (METRIC == kMetricL2) {
+                    const float4* np =
+                            reinterpret_cast<const float4*>(a.norms + grow0 + (uint32_t)c0);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const float4 nv = __ldg(np + i);
+                        sc[4 * i + 0] = (__uint_as_float(r[4 * i + 0]) + nv.x) + xn;
+                        sc[4 * i + 1] = (__uint_as_float(r[4 * i + 1]) + nv.y) + xn;
+                        sc[4 * i + 2] = (__uint_as_float(r[4 * i + 2]) + nv.z) + xn;
+                        sc[4 * i + 3] = (__uint_as_float(r[4 * i + 3]) + nv.w) + xn;
+                    }
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i)
+                        sc[i] = __uint_as_float(r[i]) + 0.f;
+                }
+                float thr = vs[KP - 1];
+                unsigned mask = 0u;
+#pragma unroll
+                for (int i = 0; i < 32; ++i)
+                    mask |= (sc[i] < thr) ? (1u << i) : 0u;
+                const int nv_here = nvalid - c0; // columns of this chunk that are real rows
+                if (nv_here < 32)
+                    mask &= (1u << nv_here) - 1u;
+                if (__any_sync(0xffffffffu, mask != 0u)) {
+#pragma unroll
+                    for (int i = 0; i < 32; ++i)
+                        stg[i * 32] = sc[i];
+                    // every lane walks its own mask; a lane only reads what it wrote itself
+                    while (__any_sync(0xffffffffu, mask != 0u)) {
+                        if (mask) {
+                            const int j = __ffs(mask) - 1;
+                            mask &= mask - 1u;
+                            float sj = stg[j * 32];
+                            if (sj < thr) { // thr may have tightened since the mask was taken
+                                uint32_t rj = grow0 + (uint32_t)(c0 + j);
+#pragma unroll
+                                for (int u = 0; u < KP; ++u) {
+                                    const bool lt = sj < vs[u];
+                                    const float vmin = fminf(sj, vs[u]);
+                                    const float vmax = fmaxf(sj, vs[u]);
+                                    const uint32_t rmin = lt ? rj : vr[u];
+                                    const uint32_t rmax = lt ? vr[u] : rj;
+                                    vs[u] = vmin;
+                                    vr[u] = rmin;
+                                    sj = vmax;
+                                    rj = rmax;
+                                }
+                                thr = vs[KP - 1];
+                            }
+                        }
+                    }
+                }
+            }
+        }
+        // ---- the KP best of this thread's query --------------------------------------------------
+        if (live) {
+            uint64_t* out = a.part + ((size_t)(q0 + qi) * a.nsplit + split) * KP;
+#pragma unroll
+            for (int j = 0; j < KP; ++j)
+                out[j] = vr[j] == 0xffffffffu ? kSentinelKey : make_key(vs[j], vr[j]);
+        }
+    }
+
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 5)
+        tmem_dealloc(tmem, 512);
+}
+
+} // namespace
+
+// The slab as a rank-3 fp32 tensor {128 floats (one float4 column of a block), blocks, nf4}: the
+// column is the OUTER box dimension so that a box {128, 4 blocks, 8 columns} lands in shared memory
+// as [column][128 rows][16 bytes] -- the K-major operand layout of the MMA.
+cudaError_t make_slab_tensor_map_tc(void* map_out, const void* slab, int nf4, uint64_t nblocks) {
+    static_assert(sizeof(CUtensorMap) == kTensorMapBytes, "CUtensorMap size");
+    using EncodeFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static EncodeFn encode = nullptr;
+    if (!encode) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault,
+                                                &qres);
+        if (e != cudaSuccess)
+            return e;
+        if (qres != cudaDriverEntryPointSuccess || !fn)
+            return cudaErrorNotSupported;
+        encode = reinterpret_cast<EncodeFn>(fn);
+    }
+    const cuuint64_t gdim[3] = {128, nblocks ? nblocks : 1, (cuuint64_t)nf4};
+    const cuuint64_t gstride[2] = {(cuuint64_t)nf4 * 512, 512};
+    const cuuint32_t box[3] = {128, (cuuint32_t)kTcTileBlocks, (cuuint32_t)kTcKC};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    const CUresult r = encode(reinterpret_cast<CUtensorMap*>(map_out),
+                              CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<void*>(slab), gdim,
+                              gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                              CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    return r == CUDA_SUCCESS ? cudaSuccess : cudaErrorInvalidValue;
+}
+
+size_t scan_tc_smem_bytes(int nstages) {
+    return (size_t)nstages * 2 * kTcStageF4 * sizeof(float4) + 4 * 32 * 32 * sizeof(float) +
+            (kTcMaxStages * 3 + 2 * 2 + 1) * sizeof(uint64_t) + 16;
+}
+
+int scan_tc_kpart(int nf4, int k) {
+    if (nf4 > 32 || nf4 < 1)
+        return 0;
+    if (k + 4 <= 16)
+        return 16;
+    if (k <= 32)
+        return 32;
+    return 0;
+}
+
+template <int METRIC, int KP>
+static cudaError_t launch_tc_one(uint32_t max_items, const TcScanArgs& a, cudaStream_t st) {
+    const size_t smem = scan_tc_smem_bytes(a.nstages);
+    auto kern = ivf_scan_tc_kernel<METRIC, KP>;
+    cudaError_t e =
+            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess)
+        return e;
+    if (max_items == 0)
+        return cudaSuccess;
+    kern<<<max_items, kTcThreads, smem, st>>>(a, *reinterpret_cast<const CUtensorMap*>(a.tmap));
+    count_launches(1);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_ivf_scan_tc(int metric, uint32_t max_items, const TcScanArgs& a,
+                               cudaStream_t st) {
+    if (a.nstages < 2 || a.nstages > kTcMaxStages || a.nf4 > 32 ||
+        scan_tc_smem_bytes(a.nstages) > 227 * 1024)
+        return cudaErrorInvalidValue;
+    if (a.kpart == 16)
+        return metric == kMetricL2 ? launch_tc_one<kMetricL2, 16>(max_items, a, st)
+                                   : launch_tc_one<kMetricInnerProduct, 16>(max_items, a, st);
+    if (a.kpart == 32)
+        return metric == kMetricL2 ? launch_tc_one<kMetricL2, 32>(max_items, a, st)
+                                   : launch_tc_one<kMetricInnerProduct, 32>(max_items, a, st);
+    return cudaErrorInvalidValue;
+}
+
+} // namespace b200ivf

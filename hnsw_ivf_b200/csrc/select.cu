@@ -29,6 +29,8 @@ __global__ void select_kernel(const SelectArgs a, int M) {
     const int per_seg = a.nsplit * a.kpart; // keys per pair slot
     const int64_t total = (int64_t)a.nseg * per_seg;
 
+    // keys kept between rounds: k, plus a margin when the scores are approximate (tensor-core scan)
+    const int kk = a.slab ? a.k + a.rerank_extra : a.k;
     int kept = 0; // keys[0..kept) hold the running best, sorted
     int64_t done = 0;
     do {
@@ -49,9 +51,56 @@ __global__ void select_kernel(const SelectArgs a, int M) {
         }
         __syncthreads();
         block_sort_keys(keys, M);
-        kept = a.k;
+        kept = kk;
         done += take;
     } while (done < total);
+
+    if (a.slab) {
+        // exact re-rank of the survivors: plain fp32, dimension order 0..d-1 in one accumulator,
+        // the arithmetic of scan.cu / scan_tile.cu (fvec_L2sqr / fvec_inner_product,
+        // faiss/utils/distances_simd.cpp:220-229,195-202, up to summation order)
+        const bool l2m = a.metric == kMetricL2;
+        for (int i = t; i < kk; i += blockDim.x) {
+            const uint64_t key = keys[i];
+            if (key != kSentinelKey) {
+                const uint32_t row = key_row(key);
+                const float4* yp = a.slab + (size_t)(row / kBlockRows) * a.nf4 * kBlockRows +
+                        (row % kBlockRows);
+                const float* xp = a.queries + (size_t)q * a.d;
+                float acc = 0.f;
+                for (int c = 0; c < a.nf4; ++c) {
+                    const float4 y = __ldg(yp + (size_t)c * kBlockRows);
+                    const int rem = a.d - 4 * c;
+                    const float x0 = __ldg(xp + 4 * c);
+                    const float x1 = rem > 1 ? __ldg(xp + 4 * c + 1) : 0.f;
+                    const float x2 = rem > 2 ? __ldg(xp + 4 * c + 2) : 0.f;
+                    const float x3 = rem > 3 ? __ldg(xp + 4 * c + 3) : 0.f;
+                    if (l2m) {
+                        float u;
+                        u = x0 - y.x;
+                        acc = fmaf(u, u, acc);
+                        u = x1 - y.y;
+                        acc = fmaf(u, u, acc);
+                        u = x2 - y.z;
+                        acc = fmaf(u, u, acc);
+                        u = x3 - y.w;
+                        acc = fmaf(u, u, acc);
+                    } else {
+                        acc = fmaf(x0, y.x, acc);
+                        acc = fmaf(x1, y.y, acc);
+                        acc = fmaf(x2, y.z, acc);
+                        acc = fmaf(x3, y.w, acc);
+                    }
+                }
+                keys[i] = make_key((l2m ? acc : -acc) + 0.f, row);
+            }
+        }
+        const int P = pow2_ceil(kk);
+        for (int i = kk + t; i < P; i += blockDim.x)
+            keys[i] = kSentinelKey;
+        __syncthreads();
+        block_sort_keys(keys, P);
+    }
 
     // decode the k best, map rows to user ids
     const bool l2 = a.metric == kMetricL2;
@@ -186,7 +235,8 @@ cudaError_t launch_select(const SelectArgs& a, cudaStream_t st) {
     if (a.n == 0)
         return cudaSuccess;
     const int64_t total = (int64_t)a.nseg * a.nsplit * a.kpart;
-    int M = pow2_ceil(a.k + (int)std::min<int64_t>(std::max<int64_t>(total, 32), 2048));
+    const int kk = a.slab ? a.k + a.rerank_extra : a.k;
+    int M = pow2_ceil(kk + (int)std::min<int64_t>(std::max<int64_t>(total, 32), 2048));
     if (M < 64)
         M = 64;
     const size_t smem = (size_t)M * 8 + (size_t)a.k * 12 + 16;

@@ -1,0 +1,233 @@
+// tc_probe.cu -- hardware probe for the tcgen05 pieces of the tensor-core scan (run on a B200):
+//   * kind::tf32 MMA with A in TMEM (tcgen05.st) and B in shared memory straight from the device
+//     slab layout (K-major, no swizzle: SBO = 128 B, LBO = column stride of the TMA box)
+//   * what the tensor core does with the low 13 mantissa bits of fp32 inputs (truncate / round)
+//   * accuracy of the 3xTF32 split (hi*hi + lo*hi + hi*lo) against a double-precision product
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -I../hnsw_ivf_b200/csrc \
+//        tc_probe.cu -o tc_probe   (see tools/Makefile)
+#include "tc_ptx.cuh"
+
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+using namespace b200ivf::ptx;
+
+constexpr int M = 128, N = 128, K = 128, NF4 = K / 4;
+constexpr int KC = 8;                      // float4 columns per TMA box
+constexpr int BOX_BYTES = KC * 4 * 512;    // 16 KB
+constexpr uint32_t LBO = 4 * 512, SBO = 128;
+
+#define CK(x)                                                                          \
+    do {                                                                               \
+        cudaError_t e = (x);                                                           \
+        if (e != cudaSuccess) {                                                        \
+            printf("CUDA error %s at %s:%d\n", cudaGetErrorString(e), __FILE__, __LINE__); \
+            exit(1);                                                                   \
+        }                                                                              \
+    } while (0)
+
+__device__ __forceinline__ float tf32_trunc(float x) {
+    return __uint_as_float(__float_as_uint(x) & 0xffffe000u);
+}
+__device__ __forceinline__ float tf32_rn(float x) { // round to nearest (ties away), then truncate
+    return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u);
+}
+
+// mode 1: D = A*B^T with raw fp32 bits (one MMA per k-step); mode 3: 3xTF32
+__global__ void __launch_bounds__(256, 1)
+        probe_kernel(const float* __restrict__ A, const __grid_constant__ CUtensorMap tmap,
+                     float* __restrict__ D, int mode) {
+    extern __shared__ __align__(1024) unsigned char smem[];
+    float4* Bhi = reinterpret_cast<float4*>(smem);                   // [NF4][4 blocks][32 rows]
+    float4* Blo = Bhi + NF4 * 128;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(Blo + NF4 * 128);   // [0] tma, [1] mma done
+    uint32_t* tmem_base_s = reinterpret_cast<uint32_t*>(bars + 2);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    if (tid == 0) {
+        mbar_init(&bars[0], 1);
+        mbar_init(&bars[1], 1);
+        fence_barrier_init();
+    }
+    if (warp == 4) {
+        tmem_alloc(tmem_base_s, 512);
+        tmem_relinquish();
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem = *tmem_base_s;
+    const uint32_t tD = tmem, tAhi = tmem + 256, tAlo = tmem + 384;
+
+    if (warp == 4 && lane == 0) {
+        mbar_expect_tx(&bars[0], (uint32_t)(NF4 * 128 * sizeof(float4)));
+        for (int c = 0; c < NF4; c += KC)
+            tma_load_3d(Bhi + c * 128, &tmap, 0, 0, c, &bars[0]);
+    }
+    if (warp < 4) {
+        // A row `tid` -> TMEM lane tid, K consecutive columns
+        const float* a = A + (size_t)tid * K;
+        const uint32_t lane_addr = (uint32_t)(warp * 32) << 16;
+        for (int c = 0; c < K; c += 8) {
+            uint32_t hi[8], lo[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float x = a[c + i];
+                if (mode == 1) {
+                    hi[i] = __float_as_uint(x);
+                    lo[i] = 0;
+                } else {
+                    const float h = tf32_trunc(x);
+                    hi[i] = __float_as_uint(h);
+                    lo[i] = __float_as_uint(tf32_rn(x - h));
+                }
+            }
+            tmem_st_32x32b_x8(tAhi + lane_addr + c, hi);
+            tmem_st_32x32b_x8(tAlo + lane_addr + c, lo);
+        }
+        tmem_st_wait();
+    }
+    // B lo = y - trunc(y), same layout
+    mbar_wait(&bars[0], 0);
+    for (int i = tid; i < NF4 * 128; i += 256) {
+        const float4 y = Bhi[i];
+        float4 l;
+        l.x = tf32_rn(y.x - tf32_trunc(y.x));
+        l.y = tf32_rn(y.y - tf32_trunc(y.y));
+        l.z = tf32_rn(y.z - tf32_trunc(y.z));
+        l.w = tf32_rn(y.w - tf32_trunc(y.w));
+        Blo[i] = l;
+    }
+    fence_proxy_async_smem();
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+
+    if (warp == 5 && lane == 0) {
+        const uint32_t idesc = make_idesc_tf32(M, N);
+        const uint32_t bhi = smem_u32(Bhi), blo = smem_u32(Blo);
+        for (int ks = 0; ks < K / 8; ++ks) {
+            const uint64_t dhi = make_smem_desc_kmajor_noswz(bhi + ks * 2 * LBO, LBO, SBO);
+            const uint64_t dlo = make_smem_desc_kmajor_noswz(blo + ks * 2 * LBO, LBO, SBO);
+            mma_tf32_ts(tD, tAhi + ks * 8, dhi, idesc, ks > 0);
+            if (mode == 3) {
+                mma_tf32_ts(tD, tAlo + ks * 8, dhi, idesc, 1);
+                mma_tf32_ts(tD, tAhi + ks * 8, dlo, idesc, 1);
+            }
+        }
+        mma_commit(&bars[1]);
+    }
+    if (warp < 4) {
+        mbar_wait(&bars[1], 0);
+        tc_fence_after_sync();
+        const uint32_t lane_addr = (uint32_t)(warp * 32) << 16;
+        for (int c = 0; c < N; c += 32) {
+            uint32_t r[32];
+            tmem_ld_32x32b_x32(tD + lane_addr + c, r);
+            tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+                D[(size_t)tid * N + c + i] = __uint_as_float(r[i]);
+        }
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 4)
+        tmem_dealloc(tmem, 512);
+}
+
+static float h_trunc(float x) {
+    uint32_t u;
+    memcpy(&u, &x, 4);
+    u &= 0xffffe000u;
+    memcpy(&x, &u, 4);
+    return x;
+}
+static float h_rn(float x) {
+    uint32_t u;
+    memcpy(&u, &x, 4);
+    u = (u + 0x1000u) & 0xffffe000u;
+    memcpy(&x, &u, 4);
+    return x;
+}
+
+int main() {
+    std::vector<float> A((size_t)M * K), B((size_t)N * K), slab((size_t)N * NF4 * 4, 0.f);
+    srand(7);
+    for (auto& v : A)
+        v = (float)rand() / RAND_MAX * 2.f - 1.f;
+    for (auto& v : B)
+        v = (float)rand() / RAND_MAX * 2.f - 1.f;
+    for (int r = 0; r < N; ++r)
+        for (int k = 0; k < K; ++k) {
+            const size_t b = r / 32, ln = r % 32;
+            slab[((b * NF4 + (k >> 2)) * 32 + ln) * 4 + (k & 3)] = B[(size_t)r * K + k];
+        }
+    float *dA, *dS, *dD;
+    CK(cudaMalloc(&dA, A.size() * 4));
+    CK(cudaMalloc(&dS, slab.size() * 4));
+    CK(cudaMalloc(&dD, (size_t)M * N * 4));
+    CK(cudaMemcpy(dA, A.data(), A.size() * 4, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(dS, slab.data(), slab.size() * 4, cudaMemcpyHostToDevice));
+
+    // tensor map: {128 floats, blocks, nf4} with strides {512 B per block... see below}
+    using EncodeFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    CK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+    CUtensorMap tmap;
+    const cuuint64_t nblocks = N / 32;
+    const cuuint64_t gdim[3] = {128, nblocks, (cuuint64_t)NF4};
+    const cuuint64_t gstride[2] = {(cuuint64_t)NF4 * 512, 512}; // bytes: dim1 = block, dim2 = column
+    const cuuint32_t box[3] = {128, 4, KC};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = reinterpret_cast<EncodeFn>(fn)(
+            &tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, dS, gdim, gstride, box, estr,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+            CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        printf("cuTensorMapEncodeTiled failed: %d\n", (int)r);
+        return 1;
+    }
+    const size_t smem_bytes = 2 * NF4 * 128 * sizeof(float4) + 64;
+    CK(cudaFuncSetAttribute(probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                            (int)smem_bytes));
+    std::vector<float> D((size_t)M * N);
+    for (int mode : {1, 3}) {
+        CK(cudaMemset(dD, 0, D.size() * 4));
+        probe_kernel<<<1, 256, smem_bytes>>>(dA, tmap, dD, mode);
+        CK(cudaGetLastError());
+        CK(cudaDeviceSynchronize());
+        CK(cudaMemcpy(D.data(), dD, D.size() * 4, cudaMemcpyDeviceToHost));
+        double e_exact = 0, e_trunc = 0, e_rn = 0, e_f32 = 0, mag = 0;
+        for (int i = 0; i < M; ++i)
+            for (int j = 0; j < N; ++j) {
+                double ex = 0, tr = 0, rn = 0;
+                float f = 0.f;
+                for (int k = 0; k < K; ++k) {
+                    const float a = A[(size_t)i * K + k], b = B[(size_t)j * K + k];
+                    ex += (double)a * b;
+                    tr += (double)h_trunc(a) * h_trunc(b);
+                    rn += (double)h_rn(a) * h_rn(b);
+                    f = fmaf(a, b, f);
+                }
+                const double g = D[(size_t)i * N + j];
+                e_exact = fmax(e_exact, fabs(g - ex));
+                e_trunc = fmax(e_trunc, fabs(g - tr));
+                e_rn = fmax(e_rn, fabs(g - rn));
+                e_f32 = fmax(e_f32, fabs((double)f - ex));
+                mag = fmax(mag, fabs(ex));
+            }
+        printf("mode %d: max|D-exact| %.3e  max|D-trunc| %.3e  max|D-rn| %.3e  "
+               "(fp32 fma chain vs exact %.3e, max|exact| %.2f)\n",
+               mode, e_exact, e_trunc, e_rn, e_f32, mag);
+    }
+    printf("D[0][0..3] = %g %g %g %g\n", D[0], D[1], D[2], D[3]);
+    return 0;
+}
