@@ -149,6 +149,7 @@ struct IndexIVFFlatB200::Impl {
     int64_t nstored = 0;
 
     // scratch (grow only)
+    Buffer qthr; // per-query pruning bound shared by the tensor-core work items of one search
     Buffer coarse_ids, coarse_dis, part, count, fill, grp_start, item_off, item_off_tile,
             pair_query, slot_of,
             cplan, stage_x, stage_D, stage_I, stage_assign, dev_x, dev_D, dev_I, dev_assign64,
@@ -212,7 +213,7 @@ IndexIVFFlatB200::~IndexIVFFlatB200() {
     cudaGetDevice(&prev);
     cudaSetDevice(device_);
     cudaStreamSynchronize(impl_->stream);
-    Buffer* bufs[] = {&impl_->cent_norms, &impl_->norms, &impl_->cent_slab, &impl_->cent_meta, &impl_->slab, &impl_->ids,
+    Buffer* bufs[] = {&impl_->qthr, &impl_->cent_norms, &impl_->norms, &impl_->cent_slab, &impl_->cent_meta, &impl_->slab, &impl_->ids,
                       &impl_->list_blk0, &impl_->list_len, &impl_->coarse_ids, &impl_->coarse_dis,
                       &impl_->part, &impl_->count, &impl_->fill, &impl_->grp_start,
                       &impl_->item_off, &impl_->item_off_tile, &impl_->pair_query, &impl_->slot_of, &impl_->cplan,
@@ -390,7 +391,7 @@ void IndexIVFFlatB200::run_coarse_(const float* xd, int64_t n, int kc, int32_t* 
     int64_t S = ceil_div(target, ngroups);
     S = std::max<int64_t>(1, std::min<int64_t>(S, std::max<int64_t>(1, nblk / rows_step)));
     S = std::min<int64_t>(S, 64);
-    m.part.reserve((size_t)n * S * kp * sizeof(uint64_t));
+    m.part.reserve((size_t)n * S * (tc ? 2 : 1) * kp * sizeof(uint64_t));
     m.cplan.reserve(16);
     int32_t* grp_start = m.cplan.as<int32_t>();
     uint32_t* item_off = m.cplan.as<uint32_t>() + 2;
@@ -412,6 +413,9 @@ void IndexIVFFlatB200::run_coarse_(const float* xd, int64_t n, int kc, int32_t* 
         a.nstages = kTcStages;
         a.queries = xd;
         a.part = m.part.as<uint64_t>();
+        m.qthr.reserve((size_t)n * sizeof(uint32_t));
+        CUDA_CHECK(launch_fill_u32(m.qthr.as<uint32_t>(), n, ordered_bits(kNeutralScore), st));
+        a.qthr = m.qthr.as<uint32_t>();
         CUDA_CHECK(launch_ivf_scan_tc(metric_type, (uint32_t)(ngroups * S), a, st));
     } else if (tiled) {
         TileScanArgs a;
@@ -454,7 +458,7 @@ void IndexIVFFlatB200::run_coarse_(const float* xd, int64_t n, int kc, int32_t* 
     s.slot_of = nullptr;
     s.n = (int)n;
     s.nseg = 1;
-    s.nsplit = (int)S;
+    s.nsplit = (int)S * (tc ? 2 : 1);
     s.kpart = kp;
     s.k = kc;
     s.metric = metric_type;
@@ -467,7 +471,7 @@ void IndexIVFFlatB200::run_coarse_(const float* xd, int64_t n, int kc, int32_t* 
         s.queries = xd;
         s.d = d;
         s.nf4 = nf4;
-        s.rerank_extra = kRerankExtra;
+        s.rerank_extra = std::min(kRerankExtra, kp - kc);
     }
     CUDA_CHECK(launch_select(s, st));
 }
@@ -529,7 +533,8 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
     // batch size: bound the partial-candidate scratch
     int64_t nb = std::min<int64_t>(n, 32768);
     BatchPlan bp = plan_batch(m.nf4, kp, nb, np, nlists_owned, m.nstored);
-    while (nb > 1 && (size_t)nb * np * bp.S * kp * sizeof(uint64_t) > ((size_t)2 << 30)) {
+    const int pmul = tc ? 2 : 1; // partial lists per (pair, split)
+    while (nb > 1 && (size_t)nb * np * bp.S * pmul * kp * sizeof(uint64_t) > ((size_t)2 << 30)) {
         nb = (nb + 1) / 2;
         bp = plan_batch(m.nf4, kp, nb, np, nlists_owned, m.nstored);
     }
@@ -588,7 +593,7 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
             tcfg.ok = false; // the tensor-core kernel takes the many-query lists instead
         m.pair_query.reserve((size_t)pairs * sizeof(int32_t));
         m.slot_of.reserve((size_t)pairs * sizeof(int32_t));
-        m.part.reserve((size_t)pairs * bp.S * kp * sizeof(uint64_t));
+        m.part.reserve((size_t)pairs * bp.S * pmul * kp * sizeof(uint64_t));
         PlanArgs pa;
         pa.coarse_ids = m.coarse_ids.as<int32_t>();
         pa.n = (int)ni;
@@ -624,6 +629,7 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
         sa.nf4 = m.nf4;
         sa.queries = xd;
         sa.part = m.part.as<uint64_t>();
+        sa.part_mul = pmul;
         const int64_t max_items =
                 (ceil_div(pairs, bp.cfg.rq) + std::min<int64_t>(pairs, (int64_t)nlist)) * bp.S;
         CUDA_CHECK(launch_ivf_scan(metric_type, bp.cfg.rq, bp.cfg.wpc, (uint32_t)max_items, sa, st));
@@ -645,6 +651,9 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
             ta.nstages = kTcStages;
             ta.queries = xd;
             ta.part = sa.part;
+            m.qthr.reserve((size_t)ni * sizeof(uint32_t));
+            CUDA_CHECK(launch_fill_u32(m.qthr.as<uint32_t>(), ni, ordered_bits(kNeutralScore), st));
+            ta.qthr = m.qthr.as<uint32_t>();
             const int64_t max_tiles =
                     (pairs / kTcTQ + std::min<int64_t>(pairs / (kTileMinQueries + 1), (int64_t)nlist)) *
                     bp.S;
@@ -679,7 +688,7 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
         se.slot_of = pa.slot_of;
         se.n = (int)ni;
         se.nseg = (int)np;
-        se.nsplit = (int)bp.S;
+        se.nsplit = (int)bp.S * pmul;
         se.kpart = (int)kp;
         se.k = (int)k;
         se.metric = metric_type;
@@ -689,7 +698,7 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
             se.queries = xd;
             se.d = d;
             se.nf4 = m.nf4;
-            se.rerank_extra = kRerankExtra;
+            se.rerank_extra = (int)std::min<int64_t>(kRerankExtra, kp - k);
         }
         se.out_dis = Dd;
         se.out_ids64 = Id;

@@ -32,7 +32,9 @@ struct ScanArgs {
     int d;                      // true dimension
     int nf4;                    // float4 columns per row = ceil(d/4)
     const float* queries;       // [n][d] row-major, device
-    uint64_t* part;             // [npairs][nsplit][k] keys out
+    uint64_t* part;             // [npairs][nsplit][part_mul][k] keys out
+    int part_mul = 1;           // 2 when the tensor-core scan shares `part` (it leaves two lists
+                                // per (pair, split)): the second one is filled with sentinels
 };
 
 // rq in {1,4,8}; warps_per_cta chosen by the caller so that shared memory fits.
@@ -87,9 +89,18 @@ struct TcScanArgs {
     int nf4;                    // <= 32
     int nstages;                // TMA ring depth (kTcStages)
     const float* queries;
-    uint64_t* part;             // [npairs][nsplit][kpart]
+    uint64_t* part;             // [npairs][nsplit][2][kpart]: one list per epilogue group
+    // [n] per-query pruning bound shared by all the work items of a search: ordered_bits() of the
+    // best KP-th score any item has seen for the query so far (the reference keeps ONE heap per
+    // query across its probes, faiss/IndexIVF.cpp:597-631; this is that heap's top). Filled with
+    // ordered_bits(FLT_MAX) before the launch (launch_fill_u32). nullptr: off.
+    uint32_t* qthr = nullptr;
+    long long* trace = nullptr; // timing experiments only (B200IVF_TC_TRACE=<item>): clock64
+    uint32_t trace_item = 0;    // stamps of one CTA, [role][tile]
+    int dbg = 0;                // timing experiments only (B200IVF_TC_DBG): 1 = epilogue drops
+                                // every score, 2 = no MMAs issued, 4 = split warps do not compute
 };
-constexpr int kTcStages = 6;
+constexpr int kTcStages = 9;
 // entries per partial list the tensor-core scan keeps for a request of k (>= k, with a margin
 // when there is room); 0 = not supported (d > 128 or k > 32)
 int scan_tc_kpart(int nf4, int k);
@@ -164,6 +175,7 @@ cudaError_t launch_gather_rows(const float* slab, int64_t row0, int64_t nrows, i
 // |row|^2 of every slab row (the L2 epilogue of the tensor-core scan): rows [0, nrows)
 cudaError_t launch_row_norms(const float4* slab, int64_t nrows, int nf4, float* norms,
                              cudaStream_t st);
+cudaError_t launch_fill_u32(uint32_t* p, int64_t n, uint32_t v, cudaStream_t st);
 cudaError_t launch_i64_to_i32(const int64_t* in, int32_t* out, int64_t n, int32_t lo, int32_t hi,
                               unsigned long long* bad, cudaStream_t st);
 

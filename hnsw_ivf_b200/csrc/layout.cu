@@ -150,6 +150,20 @@ cudaError_t launch_gather_rows(const float* slab, int64_t row0, int64_t nrows, i
     return cudaGetLastError();
 }
 
+__global__ void fill_u32_kernel(uint32_t* p, int64_t n, uint32_t v) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n;
+         i += (int64_t)gridDim.x * blockDim.x)
+        p[i] = v;
+}
+
+cudaError_t launch_fill_u32(uint32_t* p, int64_t n, uint32_t v, cudaStream_t st) {
+    if (n == 0)
+        return cudaSuccess;
+    fill_u32_kernel<<<grid_for(n, 256), 256, 0, st>>>(p, n, v);
+    count_launches(1);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_i64_to_i32(const int64_t* in, int32_t* out, int64_t n, int32_t lo, int32_t hi,
                               unsigned long long* bad, cudaStream_t st) {
     if (n == 0)

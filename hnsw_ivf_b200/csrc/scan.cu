@@ -188,9 +188,13 @@ __global__ void __launch_bounds__(256) ivf_scan_kernel(const ScanArgs a) {
             uint64_t* buf = bufs + (size_t)j * a.cap;
             PushState s = warp_compact_keys(buf, cnt[j], thr[j], a.k, a.cap, lane);
             const int keep = min(s.cnt, a.k);
-            uint64_t* out = a.part + ((size_t)(q0 + j) * a.nsplit + split) * a.k;
+            uint64_t* out =
+                    a.part + ((size_t)(q0 + j) * a.nsplit + split) * a.part_mul * a.k;
             for (int i = lane; i < a.k; i += 32)
                 out[i] = i < keep ? buf[i] : kSentinelKey;
+            if (a.part_mul == 2)
+                for (int i = lane; i < a.k; i += 32)
+                    out[a.k + i] = kSentinelKey;
         }
     }
 }

@@ -4,11 +4,11 @@
 // Same contract as scan.cu / scan_tile.cu (IVFFlatScanner::scan_codes,
 // faiss/IndexIVFFlat.cpp:155-179, applied to every (query, probe) pair; for K1 knn_L2sqr /
 // knn_inner_product over the centroid table, faiss/utils/distances.cpp:885-920,836-871): the best
-// `kpart` keys of every (pair, row split) are left in `part`. The scores this kernel produces are
-// 3xTF32 products (x_hi*y_hi + x_lo*y_hi + x_hi*y_lo, fp32 accumulate): good to ~1e-6 of |x||y|,
-// which is enough to SELECT; the k-select (select.cu) recomputes the survivors' distances in plain
-// fp32 in the reference's operation order before the final ordering, so the distances that leave
-// the library never come from the tensor core.
+// KP keys of every (pair, row split, epilogue group) are left in `part`. The scores this kernel
+// produces are 3xTF32 products (x_hi*y_hi + x_lo*y_hi + x_hi*y_lo, fp32 accumulate): good to ~1e-6
+// of |x||y|, which is enough to SELECT; the k-select (select.cu) recomputes the survivors'
+// distances in plain fp32 in the reference's operation order before the final ordering, so the
+// distances that leave the library never come from the tensor core.
 //
 // Work item = (list, tile of <= 128 queries probing it, row split); one CTA each.
 //   D[128 queries x 128 rows] (TMEM, two buffers) += A[128 x 8] (TMEM) * B[128 rows x 8]^T (smem)
@@ -22,17 +22,22 @@
 //  * B lo: y - trunc_tf32(y), rounded to tf32, computed by the split warps from the hi stage into a
 //    twin stage (generic-proxy writes + fence.proxy.async).
 //  * One thread issues the MMAs (3 per 8 dims); stages are released by tcgen05.commit.
-//  * Epilogue (4 warps, thread = query, lanes of TMEM): tcgen05.ld 32 columns at a time, add the
-//    row norm (L2: |y|^2 - 2xy + |x|^2), strict compare against the thread's own threshold (the
-//    reference's C::cmp(simi[0], dis)) into a 32-bit pass mask. Each thread keeps its KP best
-//    (score, row) SORTED IN REGISTERS, so the threshold is always the current KP-th best (as the
-//    reference's heap top is). Passing scores are staged in shared memory and every lane walks
-//    its OWN mask (ffs), so a warp spends max-over-lanes(popc) insertions per chunk, not one per
-//    column that any lane accepted. The accumulator buffer goes back to the MMA thread right
-//    after the last load.
+//  * Epilogue: TWO groups of 4 warps (thread = query = TMEM lane); group g drains accumulator
+//    buffer g, i.e. the tiles t = g (mod 2), so each group has two MMA tile times per tile.
+//    Per 32 columns: tcgen05.ld, add the norms (L2: |y|^2 - 2xy + |x|^2), strict compare against
+//    the thread's own threshold (the reference's C::cmp(simi[0], dis)) into a pass mask. Each
+//    thread keeps its KP best (score, row) SORTED IN REGISTERS, so the threshold is always the
+//    current KP-th best, as the reference's heap top is. Sparse chunks (steady state): passing
+//    scores are staged in shared memory and every lane walks its OWN mask (ffs), so a warp
+//    spends max-over-lanes(popc) insertions, not one per column some lane accepted. Dense chunks
+//    (start of a list): the 32 scores are sorted by a register bitonic network and merged with
+//    the KP best in two half-cleaner steps.
 #include "common.cuh"
 #include "kernels.h"
 #include "tc_ptx.cuh"
+
+#include <cstdio>
+#include <cstdlib>
 
 namespace b200ivf {
 
@@ -40,15 +45,21 @@ namespace {
 
 using namespace ptx;
 
-constexpr int kTcThreads = 320;   // warps 0-3 epilogue, 4 TMA, 5 MMA, 6-9 split
-constexpr int kTcSplitWarp0 = 6;
+constexpr int kTcEpiWarps = 8;    // warps 0-3: epilogue group 0, warps 4-7: group 1
+constexpr int kTcTmaWarp = 8;
+constexpr int kTcMmaWarp = 9;
+constexpr int kTcSplitWarp0 = 10; // warps 10-13
 constexpr int kTcSplitThreads = 128;
+constexpr int kTcThreads = (kTcSplitWarp0 + kTcSplitThreads / 32) * 32; // 448
 constexpr int kTcKC = 8;          // float4 columns per stage (4 MMA k-steps)
 constexpr int kTcTileBlocks = 4;  // 32-row blocks per MMA tile (N = 128)
+constexpr int kTcTileRows = kTcTileBlocks * kBlockRows;
 constexpr int kTcStageF4 = kTcKC * kTcTileBlocks * kBlockRows; // 1024 float4 = 16 KB
 constexpr uint32_t kTcLBO = kTcTileBlocks * 512, kTcSBO = 128;
-constexpr int kTcMaxStages = 8;
+constexpr int kTcMaxStages = 12; // raw (hi) ring: deep, it hides the HBM latency
+constexpr int kTcLoStages = 3;   // lo ring: shallow, it only decouples the split warps from the MMAs
 constexpr uint32_t kTcColsD = 0, kTcColsAhi = 256, kTcColsAlo = 384;
+constexpr int kTcDenseMin = 6;    // network path when some lane has >= this many passing columns
 
 __device__ __forceinline__ float tf32_trunc(float x) {
     return __uint_as_float(__float_as_uint(x) & 0xffffe000u);
@@ -60,15 +71,122 @@ __device__ __forceinline__ float tf32_lo(float y) {
     return tf32_rn(y - tf32_trunc(y));
 }
 
+// ---- register sorting networks over (score, row) pairs ------------------------------------------
+// compare-exchange: afterwards a <= b
+__device__ __forceinline__ void ce(float& a, uint32_t& ia, float& b, uint32_t& ib) {
+    const bool sw = b < a;
+    const float lo = fminf(a, b), hi = fmaxf(a, b);
+    const uint32_t il = sw ? ib : ia, ih = sw ? ia : ib;
+    a = lo;
+    b = hi;
+    ia = il;
+    ib = ih;
+}
+// keep the smaller of (a, b) in a
+__device__ __forceinline__ void keep_min(float& a, uint32_t& ia, float b, uint32_t ib) {
+    const bool sw = b < a;
+    a = fminf(a, b);
+    ia = sw ? ib : ia;
+}
+// bitonic sequence of N (power of two) -> ascending
+template <int N>
+__device__ __forceinline__ void bitonic_merge(float* s, uint32_t* id) {
+#pragma unroll
+    for (int stride = N >> 1; stride > 0; stride >>= 1) {
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+            if ((i & stride) == 0)
+                ce(s[i], id[i], s[i | stride], id[i | stride]);
+        }
+    }
+}
+// any sequence of N -> ascending
+template <int N>
+__device__ __forceinline__ void bitonic_sort(float* s, uint32_t* id) {
+#pragma unroll
+    for (int size = 2; size <= N; size <<= 1) {
+#pragma unroll
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+#pragma unroll
+            for (int i = 0; i < N; ++i) {
+                const int j = i | stride;
+                if ((i & stride) == 0) {
+                    if ((i & size) == 0)
+                        ce(s[i], id[i], s[j], id[j]);
+                    else
+                        ce(s[j], id[j], s[i], id[i]);
+                }
+            }
+        }
+    }
+}
+
+// Merge the 32 scores of a chunk (non-candidates already set to +inf) into the thread's sorted KP
+// best. sc / id are clobbered.
+template <int KP>
+__device__ __forceinline__ void merge_chunk_network(float (&sc)[32], uint32_t (&id)[32],
+                                                    float (&vs)[KP], uint32_t (&vr)[KP]) {
+    bitonic_sort<16>(sc, id);
+    bitonic_sort<16>(sc + 16, id + 16);
+    if (KP == 16) {
+        // the 16 smallest of the chunk as a bitonic sequence, then sorted
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+            keep_min(sc[i], id[i], sc[31 - i], id[31 - i]);
+        bitonic_merge<16>(sc, id);
+        // the 16 smallest of (vs, chunk best)
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+            keep_min(vs[i], vr[i], sc[15 - i], id[15 - i]);
+        bitonic_merge<16>(vs, vr);
+    } else {
+        // [ascending 16, ascending 16] -> reverse the second half in place -> bitonic 32 -> sorted
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const float ts = sc[16 + i];
+            sc[16 + i] = sc[31 - i];
+            sc[31 - i] = ts;
+            const uint32_t ti = id[16 + i];
+            id[16 + i] = id[31 - i];
+            id[31 - i] = ti;
+        }
+        bitonic_merge<32>(sc, id);
+#pragma unroll
+        for (int i = 0; i < 32; ++i)
+            keep_min(vs[i], vr[i], sc[31 - i], id[31 - i]);
+        bitonic_merge<32>(vs, vr);
+    }
+}
+
+// sorted insertion of one candidate (chain through one FMNMX per slot)
+template <int KP>
+__device__ __forceinline__ void insert_sorted(float sj, uint32_t rj, float (&vs)[KP],
+                                              uint32_t (&vr)[KP]) {
+#pragma unroll
+    for (int u = 0; u < KP; ++u) {
+        const bool lt = sj < vs[u];
+        const float vmin = fminf(sj, vs[u]);
+        const float vmax = fmaxf(sj, vs[u]);
+        const uint32_t rmin = lt ? rj : vr[u];
+        const uint32_t rmax = lt ? vr[u] : rj;
+        vs[u] = vmin;
+        vr[u] = rmin;
+        sj = vmax;
+        rj = rmax;
+    }
+}
+
 struct TcSmem {
     float4* hi;        // [nst][kTcStageF4]
-    float4* lo;        // [nst][kTcStageF4]
-    float* stg;        // [4 warps][32 columns][32 lanes] scores of the current chunk
-    uint64_t* full;    // [8] TMA landed
-    uint64_t* lo_rdy;  // [8] lo stage written
-    uint64_t* empty;   // [8] MMAs that read the stage are done
+    float4* lo;        // [kTcLoStages][kTcStageF4]
+    float* stg;        // [8 warps][32 columns][32 lanes] scores of the current chunk
+    float* xnorm;      // [2][128] partial |x|^2 of the two halves of the query
+    uint64_t* full;    // [kTcMaxStages] TMA landed
+    uint64_t* empty;   // [kTcMaxStages] MMAs that read the raw stage are done
+    uint64_t* lo_rdy;  // [4] lo stage written
+    uint64_t* lo_empty;// [4] MMAs that read the lo stage are done
     uint64_t* d_full;  // [2] accumulator buffer complete
-    uint64_t* d_empty; // [2] accumulator buffer drained by the epilogue
+    uint64_t* d_empty; // [2] accumulator buffer drained by its epilogue group
     uint64_t* a_rdy;   // [1] query tile is in TMEM
     uint32_t* tmem;    // [1]
 };
@@ -77,16 +195,24 @@ __device__ __forceinline__ TcSmem carve(unsigned char* raw, int nst) {
     TcSmem s;
     s.hi = reinterpret_cast<float4*>(raw);
     s.lo = s.hi + (size_t)nst * kTcStageF4;
-    s.stg = reinterpret_cast<float*>(s.lo + (size_t)nst * kTcStageF4);
-    s.full = reinterpret_cast<uint64_t*>(s.stg + 4 * 32 * 32);
-    s.lo_rdy = s.full + kTcMaxStages;
-    s.empty = s.lo_rdy + kTcMaxStages;
-    s.d_full = s.empty + kTcMaxStages;
+    s.stg = reinterpret_cast<float*>(s.lo + (size_t)kTcLoStages * kTcStageF4);
+    s.xnorm = s.stg + kTcEpiWarps * 32 * 32;
+    s.full = reinterpret_cast<uint64_t*>(s.xnorm + 2 * kTcTQ);
+    s.empty = s.full + kTcMaxStages;
+    s.lo_rdy = s.empty + kTcMaxStages;
+    s.lo_empty = s.lo_rdy + 4;
+    s.d_full = s.lo_empty + 4;
     s.d_empty = s.d_full + 2;
     s.a_rdy = s.d_empty + 2;
     s.tmem = reinterpret_cast<uint32_t*>(s.a_rdy + 1);
     return s;
 }
+
+#define TC_TRACE(role, idx)                                              \
+    do {                                                                 \
+        if (tracing && (idx) < 64)                                       \
+            a.trace[(role) * 64 + (idx)] = clock64();                    \
+    } while (0)
 
 template <int METRIC, int KP>
 __global__ void __launch_bounds__(kTcThreads, 1)
@@ -131,21 +257,32 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     const int niter = ntiles * nsg;
 
     const TcSmem s = carve(smem_raw, nst);
+    const bool tracing = a.trace != nullptr && item == a.trace_item;
+    if (tid == 0) {
+        TC_TRACE(0, 0);
+        if (tracing) {
+            a.trace[0 * 64 + 2] = ntiles;
+            a.trace[0 * 64 + 3] = nqw;
+        }
+    }
 
     if (tid == 0) {
         for (int i = 0; i < kTcMaxStages; ++i) {
             mbar_init(&s.full[i], 1);
-            mbar_init(&s.lo_rdy[i], kTcSplitThreads / 32);
             mbar_init(&s.empty[i], 1);
+        }
+        for (int i = 0; i < 4; ++i) {
+            mbar_init(&s.lo_rdy[i], kTcSplitThreads / 32);
+            mbar_init(&s.lo_empty[i], 1);
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&s.d_full[i], 1);
             mbar_init(&s.d_empty[i], 4);
         }
-        mbar_init(s.a_rdy, 4);
+        mbar_init(s.a_rdy, kTcEpiWarps);
         fence_barrier_init();
     }
-    if (warp == 5) {
+    if (warp == kTcMmaWarp) {
         tmem_alloc(s.tmem, 512);
         tmem_relinquish();
     }
@@ -153,8 +290,10 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     __syncthreads();
     tc_fence_after_sync();
     const uint32_t tmem = *s.tmem;
+    if (tid == 0)
+        TC_TRACE(0, 1);
 
-    if (warp == 4) {
+    if (warp == kTcTmaWarp) {
         // ======================= TMA producer ===================================================
         if (lane == 0) {
             tma_prefetch_desc(&tmap);
@@ -165,24 +304,35 @@ __global__ void __launch_bounds__(kTcThreads, 1)
                 for (int sg = 0; sg < nsg; ++sg) {
                     if (t * nsg + sg >= nst)
                         mbar_wait(&s.empty[st], ph ^ 1u);
-                    mbar_expect_tx(&s.full[st], (uint32_t)(kTcStageF4 * sizeof(float4)));
-                    tma_load_3d(s.hi + (size_t)st * kTcStageF4, &tmap, 0, blk, sg * kTcKC,
-                                &s.full[st]);
+                    if ((a.dbg & 8) && t * nsg + sg >= nst) {
+                        mbar_arrive(&s.full[st]); // experiment: recycle the stage without a load
+                    } else {
+                        mbar_expect_tx(&s.full[st], (uint32_t)(kTcStageF4 * sizeof(float4)));
+                        tma_load_3d(s.hi + (size_t)st * kTcStageF4, &tmap, 0, blk, sg * kTcKC,
+                                    &s.full[st]);
+                    }
                     if (++st == nst) {
                         st = 0;
                         ph ^= 1u;
                     }
                 }
+                TC_TRACE(1, t);
             }
         }
-    } else if (warp == 5) {
+    } else if (warp == kTcMmaWarp) {
         // ======================= MMA issuer =====================================================
-        if (lane == 0) {
-            const uint32_t idesc = make_idesc_tf32(kTcTQ, kTcTileBlocks * kBlockRows);
+        // The whole warp runs the loop (converged control flow, uniform registers); one elected
+        // lane issues the tcgen05 instructions of a stage as one straight-line block.
+        {
+            const uint32_t idesc = make_idesc_tf32(kTcTQ, kTcTileRows);
             mbar_wait(s.a_rdy, 0);
             tc_fence_after_sync();
-            int st = 0;
-            uint32_t ph = 0;
+            if (lane == 0)
+                TC_TRACE(0, 4);
+            const uint64_t desc0 = make_smem_desc_kmajor_noswz(0, kTcLBO, kTcSBO);
+            const uint32_t hi0 = smem_u32(s.hi), lo0 = smem_u32(s.lo);
+            int st = 0, ls = 0;
+            uint32_t lph = 0;
             for (int t = 0; t < ntiles; ++t) {
                 const int b = t & 1;
                 if (t >= 2) {
@@ -191,45 +341,60 @@ __global__ void __launch_bounds__(kTcThreads, 1)
                 }
                 const uint32_t tD = tmem + kTcColsD + (uint32_t)b * 128u;
                 for (int sg = 0; sg < nsg; ++sg) {
-                    mbar_wait(&s.full[st], ph);
-                    mbar_wait(&s.lo_rdy[st], ph);
+                    // lo_rdy implies full: the split warps waited for the TMA before they wrote lo
+                    mbar_wait(&s.lo_rdy[ls], lph);
                     tc_fence_after_sync();
-                    const uint32_t bhi = smem_u32(s.hi + (size_t)st * kTcStageF4);
-                    const uint32_t blo = smem_u32(s.lo + (size_t)st * kTcStageF4);
+                    // descriptors advance by 2 columns (2 * LBO bytes, in 16-byte units) per k-step
+                    const uint64_t dhi =
+                            desc0 + (uint64_t)((hi0 + (uint32_t)st * kTcStageF4 * 16u) >> 4);
+                    const uint64_t dlo =
+                            desc0 + (uint64_t)((lo0 + (uint32_t)ls * kTcStageF4 * 16u) >> 4);
                     const int ks0 = sg * (kTcKC / 2);
-                    const int ksn = min(kTcKC / 2, nks - ks0);
-                    for (int ks = 0; ks < ksn; ++ks) {
-                        const uint64_t dhi =
-                                make_smem_desc_kmajor_noswz(bhi + ks * 2 * kTcLBO, kTcLBO, kTcSBO);
-                        const uint64_t dlo =
-                                make_smem_desc_kmajor_noswz(blo + ks * 2 * kTcLBO, kTcLBO, kTcSBO);
-                        const uint32_t acol = (uint32_t)(ks0 + ks) * 8u;
-                        // small terms first, the big product last
-                        mma_tf32_ts(tD, tmem + kTcColsAlo + acol, dhi, idesc,
-                                    (sg | ks) != 0 ? 1u : 0u);
-                        mma_tf32_ts(tD, tmem + kTcColsAhi + acol, dlo, idesc, 1u);
-                        mma_tf32_ts(tD, tmem + kTcColsAhi + acol, dhi, idesc, 1u);
+                    const int ksn = (a.dbg & 2) ? 0 : nks - ks0; // >= 1
+                    const uint32_t ahi = tmem + kTcColsAhi + (uint32_t)ks0 * 8u;
+                    const uint32_t alo = tmem + kTcColsAlo + (uint32_t)ks0 * 8u;
+                    if (elect_one_sync()) {
+#pragma unroll
+                        for (int ks = 0; ks < kTcKC / 2; ++ks) {
+                            if (ks < ksn) {
+                                const uint64_t kh = dhi + (uint64_t)(ks * ((2 * kTcLBO) >> 4));
+                                const uint64_t kl = dlo + (uint64_t)(ks * ((2 * kTcLBO) >> 4));
+                                // small terms first, the big product last
+                                mma_tf32_ts(tD, alo + ks * 8, kh, idesc, (sg | ks) != 0 ? 1u : 0u);
+                                mma_tf32_ts(tD, ahi + ks * 8, kl, idesc, 1u);
+                                mma_tf32_ts(tD, ahi + ks * 8, kh, idesc, 1u);
+                            }
+                        }
+                        mma_commit(&s.empty[st]);
+                        mma_commit(&s.lo_empty[ls]);
+                        if (sg == nsg - 1)
+                            mma_commit(&s.d_full[b]);
                     }
-                    mma_commit(&s.empty[st]);
-                    if (++st == nst) {
+                    __syncwarp();
+                    if (++st == nst)
                         st = 0;
-                        ph ^= 1u;
+                    if (++ls == kTcLoStages) {
+                        ls = 0;
+                        lph ^= 1u;
                     }
                 }
-                mma_commit(&s.d_full[b]);
+                if (lane == 0)
+                    TC_TRACE(2, t);
             }
         }
     } else if (warp >= kTcSplitWarp0) {
         // ======================= split warps: lo = tf32(y - trunc(y)) ===========================
         const int t0 = tid - kTcSplitWarp0 * 32;
-        int st = 0;
-        uint32_t ph = 0;
+        int st = 0, ls = 0;
+        uint32_t ph = 0, lph = 0;
         for (int it = 0; it < niter; ++it) {
             mbar_wait(&s.full[st], ph);
+            if (it >= kTcLoStages)
+                mbar_wait(&s.lo_empty[ls], lph ^ 1u);
             const float4* src = s.hi + (size_t)st * kTcStageF4;
-            float4* dst = s.lo + (size_t)st * kTcStageF4;
+            float4* dst = s.lo + (size_t)ls * kTcStageF4;
 #pragma unroll
-            for (int i = 0; i < kTcStageF4 / kTcSplitThreads; i += 4) {
+            for (int i = 0; i < kTcStageF4 / kTcSplitThreads && !(a.dbg & 4); i += 4) {
                 float4 y[4];
 #pragma unroll
                 for (int u = 0; u < 4; ++u)
@@ -247,44 +412,66 @@ __global__ void __launch_bounds__(kTcThreads, 1)
             fence_proxy_async_smem();
             __syncwarp();
             if (lane == 0)
-                mbar_arrive(&s.lo_rdy[st]);
+                mbar_arrive(&s.lo_rdy[ls]);
+            if (tid == kTcSplitWarp0 * 32 && (it + 1) % nsg == 0)
+                TC_TRACE(3, it / nsg);
             if (++st == nst) {
                 st = 0;
                 ph ^= 1u;
             }
+            if (++ls == kTcLoStages) {
+                ls = 0;
+                lph ^= 1u;
+            }
         }
     } else {
-        // ======================= epilogue warps 0-3: thread = query =============================
-        const int qi = tid; // query slot of the tile == TMEM lane
-        const uint32_t lane_addr = (uint32_t)(warp * 32) << 16;
+        // ======================= epilogue: 2 groups x 4 warps, thread = query ===================
+        const int grp = warp >> 2;            // accumulator buffer / tile parity this group drains
+        const int qi = tid & (kTcTQ - 1);     // query slot of the tile == TMEM lane
+        const uint32_t lane_addr = (uint32_t)((warp & 3) * 32) << 16;
         const bool live = qi < nqw;
         float xn = 0.f;
+        const int q = live ? (a.pair_query ? a.pair_query[q0 + qi] : (q0 + qi)) : -1;
         {
-            // query -> TMEM (A operand): scaled, split into hi / lo, zero padded to 8 * nks dims
-            const int q = live ? (a.pair_query ? a.pair_query[q0 + qi] : (q0 + qi)) : -1;
+            // query -> TMEM (A operand): scaled, split into hi / lo, zero padded to 8 * nks dims;
+            // group 0 writes the first half of the k-steps, group 1 the second
             const float* src = a.queries + (size_t)(q < 0 ? 0 : q) * a.d;
             const float scale = METRIC == kMetricL2 ? -2.f : -1.f;
-            for (int c = 0; c < nks * 8; c += 8) {
+            const int kh = (nks + 1) >> 1;
+            const int c_lo = grp == 0 ? 0 : kh * 8, c_hi = grp == 0 ? kh * 8 : nks * 8;
+            const bool vec = (a.d & 3) == 0 && (reinterpret_cast<uintptr_t>(a.queries) & 15) == 0;
+            for (int c = c_lo; c < c_hi; c += 8) {
+                float x[8];
+                if (live && vec && c + 8 <= a.d) {
+                    const float4 u0 = __ldg(reinterpret_cast<const float4*>(src + c));
+                    const float4 u1 = __ldg(reinterpret_cast<const float4*>(src + c + 4));
+                    x[0] = u0.x, x[1] = u0.y, x[2] = u0.z, x[3] = u0.w;
+                    x[4] = u1.x, x[5] = u1.y, x[6] = u1.z, x[7] = u1.w;
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i)
+                        x[i] = (live && c + i < a.d) ? __ldg(src + c + i) : 0.f;
+                }
                 uint32_t hi[8], lo[8];
 #pragma unroll
                 for (int i = 0; i < 8; ++i) {
-                    float x = 0.f;
-                    if (live && c + i < a.d)
-                        x = __ldg(src + c + i);
-                    xn = fmaf(x, x, xn);
-                    x *= scale;
-                    const float h = tf32_trunc(x);
+                    xn = fmaf(x[i], x[i], xn);
+                    const float xs = x[i] * scale;
+                    const float h = tf32_trunc(xs);
                     hi[i] = __float_as_uint(h);
-                    lo[i] = __float_as_uint(tf32_rn(x - h));
+                    lo[i] = __float_as_uint(tf32_rn(xs - h));
                 }
                 tmem_st_32x32b_x8(tmem + kTcColsAhi + lane_addr + (uint32_t)c, hi);
                 tmem_st_32x32b_x8(tmem + kTcColsAlo + lane_addr + (uint32_t)c, lo);
             }
             tmem_st_wait();
             tc_fence_before_sync();
+            s.xnorm[grp * kTcTQ + qi] = xn;
             __syncwarp();
             if (lane == 0)
                 mbar_arrive(s.a_rdy);
+            named_bar_sync(1, kTcEpiWarps * 32);
+            xn = s.xnorm[qi] + s.xnorm[kTcTQ + qi];
         }
         // the thread's KP best so far, ascending; empty slots hold FLT_MAX (heap_heapify's fill,
         // faiss/utils/Heap.h:333) and row ~0; dead lanes hold -inf so that nothing passes
@@ -296,29 +483,35 @@ __global__ void __launch_bounds__(kTcThreads, 1)
             vr[j] = 0xffffffffu;
         }
         float* stg = s.stg + warp * 1024 + lane;
+        // pruning bound of the query over ALL its work items (see TcScanArgs::qthr)
+        volatile uint32_t* gq = (a.qthr != nullptr && live) ? a.qthr + q : nullptr;
+        float thr_g = live ? kNeutralScore : -__int_as_float(0x7f800000);
 
-        for (int t = 0; t < ntiles; ++t) {
-            const int b = t & 1;
+        for (int t = grp; t < ntiles; t += 2) {
+            if (gq)
+                thr_g = fminf(thr_g, from_ordered_bits(*gq));
             const int tb = b0 + t * kTcTileBlocks; // first block of the tile, list-relative
-            const int nvalid = min(kTcTileBlocks * kBlockRows,
-                                   min((b1 - tb) * kBlockRows, len - tb * kBlockRows));
+            const int nvalid =
+                    min(kTcTileRows, min((b1 - tb) * kBlockRows, len - tb * kBlockRows));
             const uint32_t grow0 = (blk0 + (uint32_t)tb) * kBlockRows;
-            mbar_wait(&s.d_full[b], (uint32_t)((t >> 1) & 1));
+            mbar_wait(&s.d_full[grp], (uint32_t)((t >> 1) & 1));
             tc_fence_after_sync();
-            const uint32_t tD = tmem + kTcColsD + (uint32_t)b * 128u + lane_addr;
+            if ((tid & 127) == 0)
+                TC_TRACE(4, t);
+            const uint32_t tD = tmem + kTcColsD + (uint32_t)grp * 128u + lane_addr;
 #pragma unroll 1
-            for (int c0 = 0; c0 < kTcTileBlocks * kBlockRows; c0 += 32) {
+            for (int c0 = 0; c0 < kTcTileRows; c0 += 32) {
                 uint32_t r[32];
                 tmem_ld_32x32b_x32(tD + (uint32_t)c0, r);
                 tmem_ld_wait();
-                if (c0 == kTcTileBlocks * kBlockRows - 32) {
+                if (c0 == kTcTileRows - 32) {
                     // accumulator buffer drained: hand it back to the MMA thread
                     tc_fence_before_sync();
                     __syncwarp();
                     if (lane == 0)
-                        mbar_arrive(&s.d_empty[b]);
+                        mbar_arrive(&s.d_empty[grp]);
                 }
-                if (c0 >= nvalid)
+                if (c0 >= nvalid || (a.dbg & 1))
                     continue;
                 float sc[32];
                 if (METRIC == kMetricL2) {
@@ -337,7 +530,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
                     for (int i = 0; i < 32; ++i)
                         sc[i] = __uint_as_float(r[i]) + 0.f;
                 }
-                float thr = vs[KP - 1];
+                float thr = fminf(vs[KP - 1], thr_g);
                 unsigned mask = 0u;
 #pragma unroll
                 for (int i = 0; i < 32; ++i)
@@ -345,7 +538,18 @@ __global__ void __launch_bounds__(kTcThreads, 1)
                 const int nv_here = nvalid - c0; // columns of this chunk that are real rows
                 if (nv_here < 32)
                     mask &= (1u << nv_here) - 1u;
-                if (__any_sync(0xffffffffu, mask != 0u)) {
+                const int maxpop = __reduce_max_sync(0xffffffffu, __popc(mask));
+                if (maxpop >= kTcDenseMin) {
+                    // dense chunk: sort it in registers and merge
+                    uint32_t id[32];
+#pragma unroll
+                    for (int i = 0; i < 32; ++i) {
+                        if (!((mask >> i) & 1u))
+                            sc[i] = __int_as_float(0x7f800000);
+                        id[i] = grow0 + (uint32_t)(c0 + i);
+                    }
+                    merge_chunk_network<KP>(sc, id, vs, vr);
+                } else if (maxpop > 0) {
 #pragma unroll
                     for (int i = 0; i < 32; ++i)
                         stg[i * 32] = sc[i];
@@ -354,31 +558,29 @@ __global__ void __launch_bounds__(kTcThreads, 1)
                         if (mask) {
                             const int j = __ffs(mask) - 1;
                             mask &= mask - 1u;
-                            float sj = stg[j * 32];
+                            const float sj = stg[j * 32];
                             if (sj < thr) { // thr may have tightened since the mask was taken
-                                uint32_t rj = grow0 + (uint32_t)(c0 + j);
-#pragma unroll
-                                for (int u = 0; u < KP; ++u) {
-                                    const bool lt = sj < vs[u];
-                                    const float vmin = fminf(sj, vs[u]);
-                                    const float vmax = fmaxf(sj, vs[u]);
-                                    const uint32_t rmin = lt ? rj : vr[u];
-                                    const uint32_t rmax = lt ? vr[u] : rj;
-                                    vs[u] = vmin;
-                                    vr[u] = rmin;
-                                    sj = vmax;
-                                    rj = rmax;
-                                }
-                                thr = vs[KP - 1];
+                                insert_sorted<KP>(sj, grow0 + (uint32_t)(c0 + j), vs, vr);
+                                thr = fminf(vs[KP - 1], thr_g);
                             }
                         }
                     }
                 }
             }
+            // publish this thread's KP-th best if it tightens the query's bound
+            if (gq && vs[KP - 1] < thr_g) {
+                thr_g = vs[KP - 1];
+                atomicMin(a.qthr + q, ordered_bits(thr_g));
+            }
+            if ((tid & 127) == 0)
+                TC_TRACE(6, t);
         }
-        // ---- the KP best of this thread's query --------------------------------------------------
+        if ((tid & 127) == 0)
+            TC_TRACE(5, grp);
+        // ---- the KP best of this thread's query over this group's tiles ------------------------
         if (live) {
-            uint64_t* out = a.part + ((size_t)(q0 + qi) * a.nsplit + split) * KP;
+            uint64_t* out =
+                    a.part + (((size_t)(q0 + qi) * a.nsplit + split) * 2 + grp) * KP;
 #pragma unroll
             for (int j = 0; j < KP; ++j)
                 out[j] = vr[j] == 0xffffffffu ? kSentinelKey : make_key(vs[j], vr[j]);
@@ -387,8 +589,10 @@ __global__ void __launch_bounds__(kTcThreads, 1)
 
     tc_fence_before_sync();
     __syncthreads();
-    if (warp == 5)
+    if (warp == kTcMmaWarp)
         tmem_dealloc(tmem, 512);
+    if (tid == 0)
+        TC_TRACE(0, 5);
 }
 
 } // namespace
@@ -427,8 +631,9 @@ cudaError_t make_slab_tensor_map_tc(void* map_out, const void* slab, int nf4, ui
 }
 
 size_t scan_tc_smem_bytes(int nstages) {
-    return (size_t)nstages * 2 * kTcStageF4 * sizeof(float4) + 4 * 32 * 32 * sizeof(float) +
-            (kTcMaxStages * 3 + 2 * 2 + 1) * sizeof(uint64_t) + 16;
+    return (size_t)(nstages + kTcLoStages) * kTcStageF4 * sizeof(float4) +
+            (size_t)kTcEpiWarps * 32 * 32 * sizeof(float) + 2 * kTcTQ * sizeof(float) +
+            (kTcMaxStages * 2 + 4 * 2 + 2 * 2 + 1) * sizeof(uint64_t) + 16;
 }
 
 int scan_tc_kpart(int nf4, int k) {
@@ -442,7 +647,10 @@ int scan_tc_kpart(int nf4, int k) {
 }
 
 template <int METRIC, int KP>
-static cudaError_t launch_tc_one(uint32_t max_items, const TcScanArgs& a, cudaStream_t st) {
+static cudaError_t launch_tc_one(uint32_t max_items, const TcScanArgs& a_in, cudaStream_t st) {
+    TcScanArgs a = a_in;
+    static const int dbg = getenv("B200IVF_TC_DBG") ? atoi(getenv("B200IVF_TC_DBG")) : 0;
+    a.dbg = a.nlists > 1 ? dbg : 0; // never for the coarse quantizer: the probes must stay real
     const size_t smem = scan_tc_smem_bytes(a.nstages);
     auto kern = ivf_scan_tc_kernel<METRIC, KP>;
     cudaError_t e =
@@ -451,8 +659,32 @@ static cudaError_t launch_tc_one(uint32_t max_items, const TcScanArgs& a, cudaSt
         return e;
     if (max_items == 0)
         return cudaSuccess;
+    static const char* tr = getenv("B200IVF_TC_TRACE");
+    if (tr && a.nlists > 1) {
+        static long long* buf = nullptr;
+        if (!buf)
+            cudaMalloc(&buf, 7 * 64 * sizeof(long long));
+        cudaMemsetAsync(buf, 0, 7 * 64 * sizeof(long long), st);
+        a.trace = buf;
+        a.trace_item = (uint32_t)atoi(tr);
+    }
     kern<<<max_items, kTcThreads, smem, st>>>(a, *reinterpret_cast<const CUtensorMap*>(a.tmap));
     count_launches(1);
+    if (a.trace) {
+        long long h[7 * 64];
+        cudaStreamSynchronize(st);
+        cudaMemcpy(h, a.trace, sizeof(h), cudaMemcpyDeviceToHost);
+        const long long t0 = h[0];
+        fprintf(stderr, "TCTRACE item %u ntiles %lld nq %lld: sync %lld a_rdy %lld end %lld\n",
+                a.trace_item, h[2], h[3], h[1] - t0, h[4] - t0, h[5] - t0);
+        const char* names[7] = {"", "tma", "mma", "split", "epi_start", "epi_final", "epi_end"};
+        for (int r = 1; r < 7; ++r) {
+            fprintf(stderr, "TCTRACE %-9s", names[r]);
+            for (int i = 0; i < 24 && i < (r == 5 ? 2 : (int)h[2]); ++i)
+                fprintf(stderr, " %lld", h[r * 64 + i] ? h[r * 64 + i] - t0 : -1);
+            fprintf(stderr, "\n");
+        }
+    }
     return cudaGetLastError();
 }
 

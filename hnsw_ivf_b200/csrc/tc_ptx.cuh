@@ -15,6 +15,20 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
     return (uint32_t)__cvta_generic_to_shared(p);
 }
 
+// one lane of a converged warp (ptxas keeps tcgen05 issue under an elect.sync predicate cheap; under
+// a plain `lane == 0` branch it wraps every UTC instruction in a per-lane uniformisation loop)
+__device__ __forceinline__ bool elect_one_sync() {
+    uint32_t pred;
+    asm volatile(
+            "{\n\t"
+            ".reg .pred p;\n\t"
+            "elect.sync _|p, 0xffffffff;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t"
+            "}"
+            : "=r"(pred));
+    return pred != 0;
+}
+
 // ---- mbarrier -----------------------------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));

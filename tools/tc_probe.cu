@@ -7,6 +7,7 @@
 //        tc_probe.cu -o tc_probe   (see tools/Makefile)
 #include "tc_ptx.cuh"
 
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -39,17 +40,19 @@ __device__ __forceinline__ float tf32_rn(float x) { // round to nearest (ties aw
 // mode 1: D = A*B^T with raw fp32 bits (one MMA per k-step); mode 3: 3xTF32
 __global__ void __launch_bounds__(256, 1)
         probe_kernel(const float* __restrict__ A, const __grid_constant__ CUtensorMap tmap,
-                     float* __restrict__ D, int mode) {
+                     float* __restrict__ D, int mode, int reps, int nmma, long long* cycles) {
     extern __shared__ __align__(1024) unsigned char smem[];
     float4* Bhi = reinterpret_cast<float4*>(smem);                   // [NF4][4 blocks][32 rows]
     float4* Blo = Bhi + NF4 * 128;
     uint64_t* bars = reinterpret_cast<uint64_t*>(Blo + NF4 * 128);   // [0] tma, [1] mma done
-    uint32_t* tmem_base_s = reinterpret_cast<uint32_t*>(bars + 2);
+    uint32_t* tmem_base_s = reinterpret_cast<uint32_t*>(bars + 4);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     if (tid == 0) {
         mbar_init(&bars[0], 1);
         mbar_init(&bars[1], 1);
+        mbar_init(&bars[2], 0xfffff);
+        mbar_init(&bars[3], 0xfffff);
         fence_barrier_init();
     }
     if (warp == 4) {
@@ -106,7 +109,43 @@ __global__ void __launch_bounds__(256, 1)
     __syncthreads();
     tc_fence_after_sync();
 
-    if (warp == 5 && lane == 0) {
+    if (warp == 5 && lane == 0 && reps > 0) {
+        // timing: `reps` passes over the K loop, nmma MMAs (N = nmma_n) per k-step, one commit
+        const int nn = (nmma & 0x100) ? 256 : 128; // bit 8 of nmma: N = 256 (reads past Bhi into Blo)
+        const int per = nmma & 0xff;
+        const uint32_t idesc = make_idesc_tf32(M, nn);
+        const uint32_t bhi = smem_u32(Bhi), blo = smem_u32(Blo);
+        const long long t0 = clock64();
+        for (int r = 0; r < reps; ++r)
+            for (int ks = 0; ks < K / 8; ++ks) {
+                const uint64_t dhi = make_smem_desc_kmajor_noswz(bhi + ks * 2 * LBO, LBO, SBO);
+                const uint64_t dlo = make_smem_desc_kmajor_noswz(blo + ks * 2 * LBO, LBO, SBO);
+                if (nmma & 0x400) { // the real kernel's operand order, alternating D buffers
+                    const uint32_t tDb = tD + ((r & 1) ? 128u : 0u);
+                    mma_tf32_ts(tDb, tAlo + ks * 8, dhi, idesc, 1);
+                    mma_tf32_ts(tDb, tAhi + ks * 8, dlo, idesc, 1);
+                    mma_tf32_ts(tDb, tAhi + ks * 8, dhi, idesc, 1);
+                } else {
+                    mma_tf32_ts(tD, tAhi + ks * 8, dhi, idesc, 1);
+                    if (per > 1)
+                        mma_tf32_ts(tD, tAlo + ks * 8, dhi, idesc, 1);
+                    if (per > 2)
+                        mma_tf32_ts(tD, tAhi + ks * 8, dlo, idesc, 1);
+                }
+                if ((nmma & 0x1000) && (ks & 3) == 3)
+                    tc_fence_after_sync();
+                if ((nmma & 0x200) && (ks & 3) == 3) { // the real kernel's two commits per stage
+                    mma_commit(&bars[2]);
+                    mma_commit(&bars[3]);
+                }
+            }
+        const long long t1 = clock64();
+        mma_commit(&bars[1]);
+        mbar_wait(&bars[1], 0);
+        const long long t2 = clock64();
+        cycles[2 * blockIdx.x + 0] = t1 - t0;
+        cycles[2 * blockIdx.x + 1] = t2 - t0;
+    } else if (warp == 5 && lane == 0) {
         const uint32_t idesc = make_idesc_tf32(M, N);
         const uint32_t bhi = smem_u32(Bhi), blo = smem_u32(Blo);
         for (int ks = 0; ks < K / 8; ++ks) {
@@ -119,6 +158,11 @@ __global__ void __launch_bounds__(256, 1)
             }
         }
         mma_commit(&bars[1]);
+    }
+    if (warp >= 6 && reps > 0 && (nmma & 0x800)) {
+        // extra pollers, as the idle roles of the real kernel: spin until the MMAs are done
+        while (!mbar_try_wait(&bars[1], 0)) {
+        }
     }
     if (warp < 4) {
         mbar_wait(&bars[1], 0);
@@ -196,12 +240,13 @@ int main() {
         return 1;
     }
     const size_t smem_bytes = 2 * NF4 * 128 * sizeof(float4) + 64;
+    static_assert(true, "");
     CK(cudaFuncSetAttribute(probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                             (int)smem_bytes));
     std::vector<float> D((size_t)M * N);
     for (int mode : {1, 3}) {
         CK(cudaMemset(dD, 0, D.size() * 4));
-        probe_kernel<<<1, 256, smem_bytes>>>(dA, tmap, dD, mode);
+        probe_kernel<<<1, 256, smem_bytes>>>(dA, tmap, dD, mode, 0, 0, nullptr);
         CK(cudaGetLastError());
         CK(cudaDeviceSynchronize());
         CK(cudaMemcpy(D.data(), dD, D.size() * 4, cudaMemcpyDeviceToHost));
@@ -229,5 +274,26 @@ int main() {
                mode, e_exact, e_trunc, e_rn, e_f32, mag);
     }
     printf("D[0][0..3] = %g %g %g %g\n", D[0], D[1], D[2], D[3]);
+    long long* dC;
+    CK(cudaMalloc(&dC, 16 * 148));
+    for (int grid : {1, 148})
+        for (int nm : {3, 0x403, 0x603, 0xc03, 0x1603}) {
+            const int reps = 64;
+            probe_kernel<<<grid, 256, smem_bytes>>>(dA, tmap, dD, 3, reps, nm, dC);
+            CK(cudaGetLastError());
+            CK(cudaDeviceSynchronize());
+            std::vector<long long> hc(2 * grid);
+            CK(cudaMemcpy(hc.data(), dC, 16 * grid, cudaMemcpyDeviceToHost));
+            const int nmma = reps * (K / 8) * (nm & 0xff);
+            long long mn = hc[1], mx = hc[1];
+            for (int b = 0; b < grid; ++b) {
+                mn = std::min(mn, hc[2 * b + 1]);
+                mx = std::max(mx, hc[2 * b + 1]);
+            }
+            printf("timing grid %d, flags 0x%x, %d MMA/k-step%s: %d MMAs, issue %lld cyc, complete min %lld max %lld "
+                   "-> %.1f .. %.1f cyc/MMA\n",
+                   grid, nm, nm & 0xff, (nm & 0x200) ? " + 2 commits per 12" : "", nmma, hc[0], mn, mx,
+                   (double)mn / nmma, (double)mx / nmma);
+        }
     return 0;
 }
