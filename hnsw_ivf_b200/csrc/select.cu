@@ -18,7 +18,11 @@ namespace b200ivf {
 namespace {
 
 // One CTA per query. Shared memory: keys[M] then dis[k] then ids[k].
-__global__ void select_kernel(const SelectArgs a, int M) {
+// Fast path (prefilter != 0): every partial list is sorted, so the kk-th smallest of the list HEADS
+// is an upper bound T of the kk-th smallest key overall; only the keys <= T (a few dozen) are
+// gathered and sorted. Falls back to the chunked full sort if more than kSelCap keys qualify.
+constexpr int kSelCap = 512;
+__global__ void select_kernel(const SelectArgs a, int M, int prefilter) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint64_t* keys = reinterpret_cast<uint64_t*>(smem_raw);
     int64_t* sid = reinterpret_cast<int64_t*>(keys + M);
@@ -31,9 +35,55 @@ __global__ void select_kernel(const SelectArgs a, int M) {
 
     // keys kept between rounds: k, plus a margin when the scores are approximate (tensor-core scan)
     const int kk = a.slab ? a.k + a.rerank_extra : a.k;
+    __shared__ int s_cnt;
+    bool fast_done = false;
+    if (prefilter) {
+        const int L = a.nseg * a.nsplit;
+        const int Lp = pow2_ceil(L < 32 ? 32 : L);
+        for (int i = t; i < Lp; i += blockDim.x) {
+            uint64_t key = kSentinelKey;
+            if (i < L) {
+                const int seg = i / a.nsplit;
+                const int slot = a.slot_of ? a.slot_of[(int64_t)q * a.nseg + seg] : q;
+                if (slot >= 0)
+                    key = a.part[(int64_t)slot * per_seg + (int64_t)(i % a.nsplit) * a.kpart];
+            }
+            keys[i] = key;
+        }
+        if (t == 0)
+            s_cnt = 0;
+        __syncthreads();
+        block_sort_keys(keys, Lp);
+        const uint64_t T = keys[(kk < Lp ? kk : Lp) - 1];
+        __syncthreads();
+        for (int64_t c = t; c < total; c += blockDim.x) {
+            const int seg = (int)(c / per_seg);
+            const int slot = a.slot_of ? a.slot_of[(int64_t)q * a.nseg + seg] : q;
+            if (slot >= 0) {
+                const uint64_t key = a.part[(int64_t)slot * per_seg + (c % per_seg)];
+                if (key <= T && key != kSentinelKey) {
+                    const int pos = atomicAdd(&s_cnt, 1);
+                    if (pos < kSelCap)
+                        keys[pos] = key;
+                }
+            }
+        }
+        __syncthreads();
+        const int cnt = s_cnt;
+        if (cnt <= kSelCap) {
+            int P = pow2_ceil(cnt > kk ? cnt : kk);
+            if (P < 32)
+                P = 32;
+            for (int i = cnt + t; i < P; i += blockDim.x)
+                keys[i] = kSentinelKey;
+            __syncthreads();
+            block_sort_keys(keys, P);
+            fast_done = true;
+        }
+    }
     int kept = 0; // keys[0..kept) hold the running best, sorted
-    int64_t done = 0;
-    do {
+    int64_t done = fast_done ? total : 0;
+    while (done < total) {
         const int room = M - kept; // M >= k + 32, so there is always room
         const int64_t left = total - done;
         const int take = left < (int64_t)room ? (int)left : room;
@@ -53,7 +103,7 @@ __global__ void select_kernel(const SelectArgs a, int M) {
         block_sort_keys(keys, M);
         kept = kk;
         done += take;
-    } while (done < total);
+    }
 
     if (a.slab) {
         // exact re-rank of the survivors: plain fp32, dimension order 0..d-1 in one accumulator,
@@ -239,6 +289,10 @@ cudaError_t launch_select(const SelectArgs& a, cudaStream_t st) {
     int M = pow2_ceil(kk + (int)std::min<int64_t>(std::max<int64_t>(total, 32), 2048));
     if (M < 64)
         M = 64;
+    const int64_t L = (int64_t)a.nseg * a.nsplit;
+    const int prefilter = (total > 256 && L >= 4 && L <= 2048) ? 1 : 0;
+    if (prefilter)
+        M = std::max(M, std::max(kSelCap, pow2_ceil((int)L)));
     const size_t smem = (size_t)M * 8 + (size_t)a.k * 12 + 16;
     int threads = std::min(512, std::max(64, M / 2));
     if (smem > 48 * 1024) {
@@ -247,7 +301,7 @@ cudaError_t launch_select(const SelectArgs& a, cudaStream_t st) {
         if (e != cudaSuccess)
             return e;
     }
-    select_kernel<<<a.n, threads, smem, st>>>(a, M);
+    select_kernel<<<a.n, threads, smem, st>>>(a, M, prefilter);
     count_launches(1);
     return cudaGetLastError();
 }
