@@ -108,43 +108,67 @@ __global__ void select_kernel(const SelectArgs a, int M, int prefilter) {
     if (a.slab) {
         // exact re-rank of the survivors: plain fp32, dimension order 0..d-1 in one accumulator,
         // the arithmetic of scan.cu / scan_tile.cu (fvec_L2sqr / fvec_inner_product,
-        // faiss/utils/distances_simd.cpp:220-229,195-202, up to summation order)
+        // faiss/utils/distances_simd.cpp:220-229,195-202, up to summation order). The rows are
+        // fetched by the whole block, 32 float4 columns at a time, so that the (sequential) sums
+        // of the kk candidate threads never wait on global memory.
         const bool l2m = a.metric == kMetricL2;
-        for (int i = t; i < kk; i += blockDim.x) {
-            const uint64_t key = keys[i];
-            if (key != kSentinelKey) {
-                const uint32_t row = key_row(key);
-                const float4* yp = a.slab + (size_t)(row / kBlockRows) * a.nf4 * kBlockRows +
-                        (row % kBlockRows);
-                const float* xp = a.queries + (size_t)q * a.d;
-                float acc = 0.f;
-                for (int c = 0; c < a.nf4; ++c) {
-                    const float4 y = __ldg(yp + (size_t)c * kBlockRows);
-                    const int rem = a.d - 4 * c;
-                    const float x0 = __ldg(xp + 4 * c);
-                    const float x1 = rem > 1 ? __ldg(xp + 4 * c + 1) : 0.f;
-                    const float x2 = rem > 2 ? __ldg(xp + 4 * c + 2) : 0.f;
-                    const float x3 = rem > 3 ? __ldg(xp + 4 * c + 3) : 0.f;
+        float4* ybuf = reinterpret_cast<float4*>(sdis + a.k + 4);  // [kk][32]
+        ybuf = reinterpret_cast<float4*>((reinterpret_cast<uintptr_t>(ybuf) + 15) & ~(uintptr_t)15);
+        float4* xbuf = ybuf + (size_t)kk * 32;                      // [32]
+        const float* xp = a.queries + (size_t)q * a.d;
+        float acc = 0.f;
+        uint64_t mykey = kSentinelKey;
+        if (t < kk)
+            mykey = keys[t];
+        for (int c0 = 0; c0 < a.nf4; c0 += 32) {
+            const int nc = a.nf4 - c0 < 32 ? a.nf4 - c0 : 32;
+            for (int idx = t; idx < kk * nc; idx += blockDim.x) {
+                const int cand = idx / nc, c = idx - cand * nc;
+                const uint64_t key = keys[cand];
+                float4 y = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (key != kSentinelKey) {
+                    const uint32_t row = key_row(key);
+                    y = __ldg(a.slab + ((size_t)(row / kBlockRows) * a.nf4 + c0 + c) * kBlockRows +
+                              (row % kBlockRows));
+                }
+                ybuf[cand * 32 + c] = y;
+            }
+            for (int c = t; c < nc; c += blockDim.x) {
+                const int dd = 4 * (c0 + c);
+                float4 x;
+                x.x = __ldg(xp + dd);
+                x.y = dd + 1 < a.d ? __ldg(xp + dd + 1) : 0.f;
+                x.z = dd + 2 < a.d ? __ldg(xp + dd + 2) : 0.f;
+                x.w = dd + 3 < a.d ? __ldg(xp + dd + 3) : 0.f;
+                xbuf[c] = x;
+            }
+            __syncthreads();
+            if (t < kk && mykey != kSentinelKey) {
+                for (int c = 0; c < nc; ++c) {
+                    const float4 y = ybuf[t * 32 + c];
+                    const float4 x = xbuf[c];
                     if (l2m) {
                         float u;
-                        u = x0 - y.x;
+                        u = x.x - y.x;
                         acc = fmaf(u, u, acc);
-                        u = x1 - y.y;
+                        u = x.y - y.y;
                         acc = fmaf(u, u, acc);
-                        u = x2 - y.z;
+                        u = x.z - y.z;
                         acc = fmaf(u, u, acc);
-                        u = x3 - y.w;
+                        u = x.w - y.w;
                         acc = fmaf(u, u, acc);
                     } else {
-                        acc = fmaf(x0, y.x, acc);
-                        acc = fmaf(x1, y.y, acc);
-                        acc = fmaf(x2, y.z, acc);
-                        acc = fmaf(x3, y.w, acc);
+                        acc = fmaf(x.x, y.x, acc);
+                        acc = fmaf(x.y, y.y, acc);
+                        acc = fmaf(x.z, y.z, acc);
+                        acc = fmaf(x.w, y.w, acc);
                     }
                 }
-                keys[i] = make_key((l2m ? acc : -acc) + 0.f, row);
             }
+            __syncthreads();
         }
+        if (t < kk && mykey != kSentinelKey)
+            keys[t] = make_key((l2m ? acc : -acc) + 0.f, key_row(mykey));
         const int P = pow2_ceil(kk);
         for (int i = kk + t; i < P; i += blockDim.x)
             keys[i] = kSentinelKey;
@@ -293,8 +317,12 @@ cudaError_t launch_select(const SelectArgs& a, cudaStream_t st) {
     const int prefilter = (total > 256 && L >= 4 && L <= 2048) ? 1 : 0;
     if (prefilter)
         M = std::max(M, std::max(kSelCap, pow2_ceil((int)L)));
-    const size_t smem = (size_t)M * 8 + (size_t)a.k * 12 + 16;
+    size_t smem = (size_t)M * 8 + (size_t)a.k * 12 + 16;
+    if (a.slab)
+        smem += 32 + ((size_t)kk * 32 + 32) * sizeof(float4);
     int threads = std::min(512, std::max(64, M / 2));
+    if (prefilter)
+        threads = 128;
     if (smem > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(select_kernel,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
