@@ -149,6 +149,7 @@ struct IndexIVFFlatB200::Impl {
     int64_t nstored = 0;
 
     // scratch (grow only)
+    Buffer item_list; // list number of every tensor-core work item (written by the plan)
     Buffer qthr; // per-query pruning bound shared by the tensor-core work items of one search
     Buffer coarse_ids, coarse_dis, part, count, fill, grp_start, item_off, item_off_tile,
             pair_query, slot_of,
@@ -213,7 +214,7 @@ IndexIVFFlatB200::~IndexIVFFlatB200() {
     cudaGetDevice(&prev);
     cudaSetDevice(device_);
     cudaStreamSynchronize(impl_->stream);
-    Buffer* bufs[] = {&impl_->qthr, &impl_->cent_norms, &impl_->norms, &impl_->cent_slab, &impl_->cent_meta, &impl_->slab, &impl_->ids,
+    Buffer* bufs[] = {&impl_->item_list, &impl_->qthr, &impl_->cent_norms, &impl_->norms, &impl_->cent_slab, &impl_->cent_meta, &impl_->slab, &impl_->ids,
                       &impl_->list_blk0, &impl_->list_len, &impl_->coarse_ids, &impl_->coarse_dis,
                       &impl_->part, &impl_->count, &impl_->fill, &impl_->grp_start,
                       &impl_->item_off, &impl_->item_off_tile, &impl_->pair_query, &impl_->slot_of, &impl_->cplan,
@@ -391,6 +392,8 @@ void IndexIVFFlatB200::run_coarse_(const float* xd, int64_t n, int kc, int32_t* 
     int64_t S = ceil_div(target, ngroups);
     S = std::max<int64_t>(1, std::min<int64_t>(S, std::max<int64_t>(1, nblk / rows_step)));
     S = std::min<int64_t>(S, 64);
+    if (const char* e = getenv("B200IVF_COARSE_S")) // tuning experiments
+        S = std::max<int64_t>(1, std::min<int64_t>(atoi(e), std::max<int64_t>(1, nblk / rows_step)));
     m.part.reserve((size_t)n * S * (tc ? 2 : 1) * kp * sizeof(uint64_t));
     m.cplan.reserve(16);
     int32_t* grp_start = m.cplan.as<int32_t>();
@@ -611,6 +614,13 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
         pa.tile_tq = tc ? kTcTQ : (tcfg.ok ? tcfg.tq : 0);
         pa.tile_min = kTileMinQueries;
         pa.item_off_tile = m.item_off_tile.as<uint32_t>();
+        const int64_t max_tc_items =
+                (pairs / kTcTQ + std::min<int64_t>(pairs / (kTileMinQueries + 1), (int64_t)nlist)) *
+                bp.S;
+        if (tc) {
+            m.item_list.reserve((size_t)(max_tc_items + 1) * sizeof(int32_t));
+            pa.item_list_tile = m.item_list.as<int32_t>();
+        }
         pa.stats = dstats;
         CUDA_CHECK(launch_plan(pa, st));
         CUDA_CHECK(cudaEventRecord(m.ev[2], st));
@@ -654,10 +664,8 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
             m.qthr.reserve((size_t)ni * sizeof(uint32_t));
             CUDA_CHECK(launch_fill_u32(m.qthr.as<uint32_t>(), ni, ordered_bits(kNeutralScore), st));
             ta.qthr = m.qthr.as<uint32_t>();
-            const int64_t max_tiles =
-                    (pairs / kTcTQ + std::min<int64_t>(pairs / (kTileMinQueries + 1), (int64_t)nlist)) *
-                    bp.S;
-            CUDA_CHECK(launch_ivf_scan_tc(metric_type, (uint32_t)max_tiles, ta, st));
+            ta.item_list = m.item_list.as<int32_t>();
+            CUDA_CHECK(launch_ivf_scan_tc(metric_type, (uint32_t)max_tc_items, ta, st));
         } else if (tcfg.ok) {
             // lists probed by more than kTileMinQueries queries of this batch
             TileScanArgs ta;

@@ -81,6 +81,7 @@ struct TcScanArgs {
     const int32_t* grp_start;   // [nlists+1]
     const int32_t* pair_query;  // [npairs] (nullptr: identity)
     const uint32_t* item_off;   // [nlists+1] exclusive prefix of ceil(count/kTcTQ)*nsplit
+    const int32_t* item_list = nullptr; // [items] list of each item (else: binary search)
     const float* norms;         // [slab rows] |y|^2 (read for METRIC_L2 only)
     int nlists;
     int nsplit;
@@ -125,6 +126,7 @@ struct PlanArgs {
     // get 0 items in item_off; the others get 0 items in item_off_tile. tile_tq = 0: no tiling.
     int tile_tq, tile_min;
     uint32_t* item_off_tile;    // [nlists+1] out (may be nullptr when tile_tq == 0)
+    int32_t* item_list_tile = nullptr; // [tile items] out: list of each tile item (optional)
     unsigned long long* stats;  // [4] += {nq, nlist visited, ndis, invalid keys}
 };
 cudaError_t launch_plan(const PlanArgs& a, cudaStream_t st);

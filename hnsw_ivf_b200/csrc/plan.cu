@@ -97,6 +97,11 @@ __global__ void plan_scan_kernel(const PlanArgs a) {
             a.item_off[l] = carry_itm + s_itm[t] - it;
             if (a.item_off_tile)
                 a.item_off_tile[l] = carry_til + s_til[t] - tl;
+            if (a.item_list_tile) {
+                const unsigned o = carry_til + s_til[t] - tl;
+                for (unsigned j = 0; j < tl; ++j)
+                    a.item_list_tile[o + j] = l;
+            }
         }
         __syncthreads();
         if (t == 1023) {

@@ -227,12 +227,16 @@ __global__ void __launch_bounds__(kTcThreads, 1)
     if (item >= a.item_off[a.nlists])
         return;
     int lo_l = 0, hi_l = a.nlists;
-    while (hi_l - lo_l > 1) {
-        const int mid = (lo_l + hi_l) >> 1;
-        if (a.item_off[mid] <= item)
-            lo_l = mid;
-        else
-            hi_l = mid;
+    if (a.item_list) {
+        lo_l = a.item_list[item]; // written by the plan: no dependent-load chain
+    } else {
+        while (hi_l - lo_l > 1) {
+            const int mid = (lo_l + hi_l) >> 1;
+            if (a.item_off[mid] <= item)
+                lo_l = mid;
+            else
+                hi_l = mid;
+        }
     }
     const int l = lo_l;
     const int g0 = a.grp_start[l];
@@ -456,29 +460,43 @@ __global__ void __launch_bounds__(kTcThreads, 1)
             const int kh = (nks + 1) >> 1;
             const int c_lo = grp == 0 ? 0 : kh * 8, c_hi = grp == 0 ? kh * 8 : nks * 8;
             const bool vec = (a.d & 3) == 0 && (reinterpret_cast<uintptr_t>(a.queries) & 15) == 0;
-            for (int c = c_lo; c < c_hi; c += 8) {
-                float x[8];
-                if (live && vec && c + 8 <= a.d) {
-                    const float4 u0 = __ldg(reinterpret_cast<const float4*>(src + c));
-                    const float4 u1 = __ldg(reinterpret_cast<const float4*>(src + c + 4));
-                    x[0] = u0.x, x[1] = u0.y, x[2] = u0.z, x[3] = u0.w;
-                    x[4] = u1.x, x[5] = u1.y, x[6] = u1.z, x[7] = u1.w;
-                } else {
+            // all the loads of the thread's half first (<= 16 LDG.128 in flight), then the stores
+            float4 xv[16];
 #pragma unroll
-                    for (int i = 0; i < 8; ++i)
-                        x[i] = (live && c + i < a.d) ? __ldg(src + c + i) : 0.f;
+            for (int i = 0; i < 16; ++i) {
+                const int c = c_lo + 4 * i;
+                float4 u = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (live && c < c_hi) {
+                    if (vec && c + 4 <= a.d) {
+                        u = __ldg(reinterpret_cast<const float4*>(src + c));
+                    } else {
+                        u.x = c + 0 < a.d ? __ldg(src + c + 0) : 0.f;
+                        u.y = c + 1 < a.d ? __ldg(src + c + 1) : 0.f;
+                        u.z = c + 2 < a.d ? __ldg(src + c + 2) : 0.f;
+                        u.w = c + 3 < a.d ? __ldg(src + c + 3) : 0.f;
+                    }
                 }
-                uint32_t hi[8], lo[8];
+                xv[i] = u;
+            }
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    xn = fmaf(x[i], x[i], xn);
-                    const float xs = x[i] * scale;
-                    const float h = tf32_trunc(xs);
-                    hi[i] = __float_as_uint(h);
-                    lo[i] = __float_as_uint(tf32_rn(xs - h));
+            for (int i = 0; i < 8; ++i) {
+                const int c = c_lo + 8 * i;
+                if (c < c_hi) {
+                    const float x[8] = {xv[2 * i].x,     xv[2 * i].y,     xv[2 * i].z,
+                                        xv[2 * i].w,     xv[2 * i + 1].x, xv[2 * i + 1].y,
+                                        xv[2 * i + 1].z, xv[2 * i + 1].w};
+                    uint32_t hi[8], lo[8];
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        xn = fmaf(x[j], x[j], xn);
+                        const float xs = x[j] * scale;
+                        const float h = tf32_trunc(xs);
+                        hi[j] = __float_as_uint(h);
+                        lo[j] = __float_as_uint(tf32_rn(xs - h));
+                    }
+                    tmem_st_32x32b_x8(tmem + kTcColsAhi + lane_addr + (uint32_t)c, hi);
+                    tmem_st_32x32b_x8(tmem + kTcColsAlo + lane_addr + (uint32_t)c, lo);
                 }
-                tmem_st_32x32b_x8(tmem + kTcColsAhi + lane_addr + (uint32_t)c, hi);
-                tmem_st_32x32b_x8(tmem + kTcColsAlo + lane_addr + (uint32_t)c, lo);
             }
             tmem_st_wait();
             tc_fence_before_sync();

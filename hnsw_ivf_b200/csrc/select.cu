@@ -222,6 +222,218 @@ __global__ void select_kernel(const SelectArgs a, int M, int prefilter) {
     }
 }
 
+// ---- warp-per-query k-select (k <= 64, <= 256 partial lists) --------------------------------------
+// Same result as select_kernel, without a single block-wide barrier: the head-bound prefilter, the
+// stream compaction (ballot / popc), the sorts (bitonic, in the warp's own shared-memory strip) and
+// the exact re-rank (lane = candidate) are all warp-synchronous. 8 queries per CTA.
+constexpr int kSelWarpCap = 256;
+constexpr int kSelWarpK = 64;
+constexpr int kSelWarpBytes = kSelWarpCap * 8 + kSelWarpK * 12;
+
+template <bool L2M>
+__device__ __forceinline__ float rerank_one(const SelectArgs& a, int q, uint32_t row) {
+    const float4* yp = a.slab + (size_t)(row / kBlockRows) * a.nf4 * kBlockRows + (row % kBlockRows);
+    const float* xp = a.queries + (size_t)q * a.d;
+    const bool vec = (a.d & 3) == 0 && (reinterpret_cast<uintptr_t>(a.queries) & 15) == 0;
+    float acc = 0.f;
+    for (int c0 = 0; c0 < a.nf4; c0 += 8) {
+        float4 y[8], x[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int c = c0 + u;
+            y[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            x[u] = y[u];
+            if (c < a.nf4) {
+                y[u] = __ldg(yp + (size_t)c * kBlockRows);
+                if (vec) {
+                    x[u] = __ldg(reinterpret_cast<const float4*>(xp + 4 * c));
+                } else {
+                    const int dd = 4 * c;
+                    x[u].x = __ldg(xp + dd);
+                    x[u].y = dd + 1 < a.d ? __ldg(xp + dd + 1) : 0.f;
+                    x[u].z = dd + 2 < a.d ? __ldg(xp + dd + 2) : 0.f;
+                    x[u].w = dd + 3 < a.d ? __ldg(xp + dd + 3) : 0.f;
+                }
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            if (c0 + u < a.nf4) {
+                if (L2M) {
+                    float t;
+                    t = x[u].x - y[u].x;
+                    acc = fmaf(t, t, acc);
+                    t = x[u].y - y[u].y;
+                    acc = fmaf(t, t, acc);
+                    t = x[u].z - y[u].z;
+                    acc = fmaf(t, t, acc);
+                    t = x[u].w - y[u].w;
+                    acc = fmaf(t, t, acc);
+                } else {
+                    acc = fmaf(x[u].x, y[u].x, acc);
+                    acc = fmaf(x[u].y, y[u].y, acc);
+                    acc = fmaf(x[u].z, y[u].z, acc);
+                    acc = fmaf(x[u].w, y[u].w, acc);
+                }
+            }
+        }
+    }
+    return (L2M ? acc : -acc) + 0.f;
+}
+
+__global__ void __launch_bounds__(256) select_warp_kernel(const SelectArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int lane = threadIdx.x & 31;
+    const int w = threadIdx.x >> 5;
+    const int q = blockIdx.x * (blockDim.x >> 5) + w;
+    if (q >= a.n)
+        return;
+    uint64_t* keys = reinterpret_cast<uint64_t*>(smem_raw + (size_t)w * kSelWarpBytes);
+    int64_t* sid = reinterpret_cast<int64_t*>(keys + kSelWarpCap);
+    float* sdis = reinterpret_cast<float*>(sid + kSelWarpK);
+
+    const int per_seg = a.nsplit * a.kpart;
+    const int total = a.nseg * per_seg;
+    const int kk = a.slab ? a.k + a.rerank_extra : a.k;
+    const int L = a.nseg * a.nsplit;
+    const unsigned lt_mask = (1u << lane) - 1u;
+
+    // 1. the kk-th smallest list head bounds the kk-th smallest key
+    uint64_t T = kSentinelKey - 1;
+    if (L >= 2) {
+        const int Lp = pow2_ceil(L < 32 ? 32 : L);
+        for (int i = lane; i < Lp; i += 32) {
+            uint64_t key = kSentinelKey;
+            if (i < L) {
+                const int seg = i / a.nsplit;
+                const int slot = a.slot_of ? a.slot_of[(int64_t)q * a.nseg + seg] : q;
+                if (slot >= 0)
+                    key = a.part[(int64_t)slot * per_seg + (int64_t)(i % a.nsplit) * a.kpart];
+            }
+            keys[i] = key;
+        }
+        __syncwarp();
+        warp_sort_keys(keys, Lp, lane);
+        T = keys[(kk < Lp ? kk : Lp) - 1];
+        if (T == kSentinelKey)
+            T = kSentinelKey - 1;
+        __syncwarp();
+    }
+
+    // 2. stream the partial lists, keep the keys <= T; keys[0..kept) sorted, then cnt unsorted
+    int kept = 0, cnt = 0;
+    for (int c0 = 0; c0 < total; c0 += 256) {
+        uint64_t kv[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int c = c0 + u * 32 + lane;
+            kv[u] = kSentinelKey;
+            if (c < total) {
+                const int seg = c / per_seg;
+                const int slot = a.slot_of ? a.slot_of[(int64_t)q * a.nseg + seg] : q;
+                if (slot >= 0)
+                    kv[u] = a.part[(int64_t)slot * per_seg + (c - seg * per_seg)];
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            bool pass = kv[u] <= T;
+            unsigned m = __ballot_sync(0xffffffffu, pass);
+            if (m == 0u)
+                continue;
+            if (kept + cnt + __popc(m) > kSelWarpCap) {
+                for (int i = kept + cnt + lane; i < kSelWarpCap; i += 32)
+                    keys[i] = kSentinelKey;
+                __syncwarp();
+                warp_sort_keys(keys, kSelWarpCap, lane);
+                kept = kept + cnt < kk ? kept + cnt : kk;
+                cnt = 0;
+                if (kept == kk && keys[kk - 1] < T)
+                    T = keys[kk - 1];
+                __syncwarp();
+                pass = kv[u] <= T;
+                m = __ballot_sync(0xffffffffu, pass);
+            }
+            if (pass)
+                keys[kept + cnt + __popc(m & lt_mask)] = kv[u];
+            cnt += __popc(m);
+            __syncwarp();
+        }
+    }
+    // 3. sort what was kept
+    {
+        const int tot = kept + cnt;
+        int P = pow2_ceil(tot > kk ? tot : kk);
+        if (P < 32)
+            P = 32;
+        for (int i = tot + lane; i < P; i += 32)
+            keys[i] = kSentinelKey;
+        __syncwarp();
+        warp_sort_keys(keys, P, lane);
+    }
+    // 4. exact re-rank of the kk survivors (lane = candidate), see select_kernel
+    if (a.slab) {
+        for (int i = lane; i < kk; i += 32) {
+            const uint64_t key = keys[i];
+            if (key != kSentinelKey) {
+                const uint32_t row = key_row(key);
+                const float sc = a.metric == kMetricL2 ? rerank_one<true>(a, q, row)
+                                                       : rerank_one<false>(a, q, row);
+                keys[i] = make_key(sc, row);
+            }
+        }
+        int P = pow2_ceil(kk);
+        if (P < 32)
+            P = 32;
+        for (int i = kk + lane; i < P; i += 32)
+            keys[i] = kSentinelKey;
+        __syncwarp();
+        warp_sort_keys(keys, P, lane);
+    }
+    // 5. decode, order exact ties by id as cmp2 does, write
+    const bool l2 = a.metric == kMetricL2;
+    for (int i = lane; i < a.k; i += 32) {
+        const uint64_t key = keys[i];
+        if (key == kSentinelKey) {
+            sdis[i] = l2 ? kNeutralScore : -kNeutralScore;
+            sid[i] = -1;
+        } else {
+            const float sc = key_score(key);
+            sdis[i] = l2 ? sc : -sc;
+            const uint32_t row = key_row(key);
+            sid[i] = a.ids ? a.ids[row] : (int64_t)row;
+        }
+    }
+    __syncwarp();
+    for (int i = lane; i < a.k; i += 32) {
+        const float di = sdis[i];
+        const int64_t idi = sid[i];
+        int pos = i;
+        if (idi >= 0) {
+            int lo = i, hi = i;
+            while (lo > 0 && sdis[lo - 1] == di && sid[lo - 1] >= 0)
+                --lo;
+            while (hi + 1 < a.k && sdis[hi + 1] == di && sid[hi + 1] >= 0)
+                ++hi;
+            if (hi > lo) {
+                int before = 0;
+                for (int j = lo; j <= hi; ++j) {
+                    const int64_t idj = sid[j];
+                    const bool first = l2 ? (idj < idi) : (idj > idi);
+                    before += (first || (idj == idi && j < i)) ? 1 : 0;
+                }
+                pos = lo + before;
+            }
+        }
+        const int64_t o = (int64_t)q * a.k + pos;
+        a.out_dis[o] = di;
+        if (a.out_ids64)
+            a.out_ids64[o] = idi;
+        if (a.out_ids32)
+            a.out_ids32[o] = (int32_t)idi;
+    }
+}
+
 // One warp per query: merge nshard sorted (n,k) tables. Same output as merge_knn_results
 // (faiss/utils/Heap.cpp:158-232) except that exact ties across shards are ordered by id rather
 // than by shard number.
@@ -310,6 +522,13 @@ cudaError_t launch_select(const SelectArgs& a, cudaStream_t st) {
         return cudaSuccess;
     const int64_t total = (int64_t)a.nseg * a.nsplit * a.kpart;
     const int kk = a.slab ? a.k + a.rerank_extra : a.k;
+    if (a.k <= kSelWarpK && kk <= kSelWarpK && (int64_t)a.nseg * a.nsplit <= 256 &&
+        total < (1 << 30)) {
+        const int wpb = 8;
+        select_warp_kernel<<<(a.n + wpb - 1) / wpb, wpb * 32, wpb * kSelWarpBytes, st>>>(a);
+        count_launches(1);
+        return cudaGetLastError();
+    }
     int M = pow2_ceil(kk + (int)std::min<int64_t>(std::max<int64_t>(total, 32), 2048));
     if (M < 64)
         M = 64;
