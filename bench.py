@@ -337,6 +337,10 @@ def run_b200(args):
     d, nlist, metric, nq, k = w["d"], w["nlist"], w["metric"], w["nq"], w["k"]
     t_setup = time.perf_counter()
     xb, xq, cent = setup_data(torch, w, dev)
+    if world > 1:
+        # ONE set of trained centroids for all ranks (k-means uses float atomics: each rank's own
+        # run differs in the last bits, which would make list ownership inconsistent across shards)
+        dist.broadcast(cent, src=0)
 
     # ---- index: this rank's list range ----------------------------------------------------------
     if world > 1:

@@ -272,6 +272,14 @@ class IndexIVFFlat:
         return dict(zip(("coarse", "plan", "scan", "select", "total"), list(ms)))
 
     def set_stream(self, cuda_stream_ptr):
+        """Run on a caller-owned stream (e.g. ``torch.cuda.current_stream().cuda_stream``). torch's
+        default stream has handle 0, which the C-ABI reads as "the handle's own stream": it is
+        passed as cudaStreamLegacy (0x1) instead, so that the library really is stream-ordered
+        with the caller's torch work. ``None`` selects the handle's own stream."""
+        if cuda_stream_ptr is None:
+            cuda_stream_ptr = 0
+        elif cuda_stream_ptr == 0:
+            cuda_stream_ptr = 1  # cudaStreamLegacy
         self._check(self._lib.b200_IndexIVFFlat_set_stream(self._h, cuda_stream_ptr))
 
 

@@ -783,7 +783,10 @@ void IndexIVFFlatB200::quantize(int64_t n, const float* x, int64_t kc, float* Dq
         if (!I_dev)
             CUDA_CHECK(cudaMemcpyAsync(Iq + i0 * kc, Id, (size_t)ni * kc * sizeof(int64_t),
                                        cudaMemcpyDeviceToHost, st));
-        CUDA_CHECK(cudaStreamSynchronize(st));
+        // all-device calls stay asynchronous on the handle's stream (the next batch only reuses
+        // scratch in stream order); anything staged through host buffers must complete here
+        if (!(x_dev && D_dev && I_dev))
+            CUDA_CHECK(cudaStreamSynchronize(st));
     }
 }
 
@@ -985,6 +988,8 @@ void merge_knn_results(int metric, int nshard, int64_t n, int64_t k, const float
         rI = oI.as<int64_t>();
     }
     CUDA_CHECK(launch_merge_shards(metric, nshard, (int)n, (int)k, dD, dI, rD, rI, st));
+    if (in_dev && out_dev)
+        return; // asynchronous on `st`, nothing was staged
     if (!out_dev) {
         CUDA_CHECK(cudaMemcpyAsync(D, rD, (size_t)n * k * sizeof(float), cudaMemcpyDeviceToHost, st));
         CUDA_CHECK(cudaMemcpyAsync(I, rI, (size_t)n * k * sizeof(int64_t), cudaMemcpyDeviceToHost,

@@ -6,8 +6,14 @@ and CPU merge replaced by: replicated device quantizer, contiguous list ranges p
 (shard_type 4 / SUBSET_TYPE_INVLIST: faiss/gpu/GpuCloner.cpp:303-314,
 faiss/invlists/InvertedLists.cpp:168-176), an NCCL all-gather of the per-rank sorted (n,k) tables
 over NVLink, and the device merge kernel (csrc/select.cu). Each (query, probe) pair lands on exactly
-one rank, so total scan bytes do not grow with the number of GPUs; the only collective is the
-(n*k*12 byte per rank) result exchange.
+one rank, so total scan bytes do not grow with the number of GPUs.
+
+Coarse quantization is the common step of IndexShardsIVF::search (faiss/IndexShardsIVF.cpp:175-183:
+ONE quantizer->search, then per-shard search_preassigned). Here every rank holds the full centroid
+table, so the common step is split by QUERY: rank r quantizes queries [r*n/R, (r+1)*n/R), the
+[n][nprobe] probe table is all-gathered (n*nprobe*8 bytes in total) and every rank runs
+search_preassigned on all the queries against its own lists. Collectives per search: that
+all-gather and the (n*k*12 bytes per rank) result all-gather.
 """
 from .binding import IndexIVFFlat, merge_knn_results
 
@@ -39,7 +45,8 @@ class IndexShardsIVFFlat:
     list range.
     """
 
-    def __init__(self, d, nlist, metric, device=0, group=None, local=None, merge=None):
+    def __init__(self, d, nlist, metric, device=0, group=None, local=None, merge=None,
+                 shard_quantizer=True):
         import torch.distributed as dist
         self.group = group
         self.rank = dist.get_rank(group)
@@ -50,6 +57,7 @@ class IndexShardsIVFFlat:
             local = IndexIVFFlat(d, nlist, metric, device)
         local.set_list_range(self.list_lo, self.list_hi)
         self.local = local
+        self.shard_quantizer = shard_quantizer
         self._merge = merge or (lambda m, aD, aI: merge_knn_results(m, aD, aI, device=device))
 
     @property
@@ -75,8 +83,30 @@ class IndexShardsIVFFlat:
         if broadcast_from is not None:
             import torch.distributed as dist
             dist.broadcast(x, src=broadcast_from, group=self.group)
-        D_loc, I_loc = self.local.search(x, k)
         if self.world == 1:
-            return D_loc, I_loc
+            return self.local.search(x, k)
+        if self.shard_quantizer:
+            Iq = self._quantize_sharded(x)
+            D_loc, I_loc = self.local.search_preassigned(x, k, Iq)
+        else:
+            D_loc, I_loc = self.local.search(x, k)
         all_D, all_I = gather_results(D_loc, I_loc, self.group)
         return self._merge(self.metric, all_D, all_I)
+
+    def _quantize_sharded(self, x):
+        """[n][nprobe] int64 probe table: each rank quantizes its slice of the queries, all-gather.
+        Probes of lists this rank does not own are simply skipped by its search_preassigned (the
+        lists are empty there: faiss/IndexIVF.cpp:526-529)."""
+        import torch
+        import torch.distributed as dist
+        n = x.shape[0]
+        nprobe = min(self.local.nprobe, self.nlist)
+        chunk = (n + self.world - 1) // self.world
+        lo, hi = min(self.rank * chunk, n), min((self.rank + 1) * chunk, n)
+        mine = torch.full((chunk, nprobe), -1, dtype=torch.int64, device=x.device)
+        if hi > lo:
+            _, Iq = self.local.quantize(x[lo:hi].contiguous(), nprobe)
+            mine[:hi - lo] = torch.as_tensor(Iq).to(x.device)
+        allq = torch.empty((self.world * chunk, nprobe), dtype=torch.int64, device=x.device)
+        dist.all_gather_into_tensor(allq, mine, group=self.group)
+        return allq[:n].contiguous()

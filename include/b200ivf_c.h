@@ -110,7 +110,10 @@ void b200_IndexIVFFlat_reset_stats(B200IndexIVFFlat* index);
 /* device time in ms of the stages of the LAST search call: {coarse, plan, scan, select, total} */
 void b200_IndexIVFFlat_last_timings(const B200IndexIVFFlat* index, double* ms5);
 
-/* Run on a caller-owned CUDA stream (cudaStream_t as void*; NULL = the handle's own stream). */
+/* Run on a caller-owned CUDA stream (cudaStream_t as void*; NULL = the handle's own stream, a
+ * non-blocking one; pass cudaStreamLegacy, (void*)0x1, to be ordered with the legacy default
+ * stream). Calls whose buffers are all device pointers may return before the work completes:
+ * they are ordered on this stream. */
 int b200_IndexIVFFlat_set_stream(B200IndexIVFFlat* index, void* cuda_stream);
 
 /* Number of CUDA kernels this library has launched in this process (all handles). */

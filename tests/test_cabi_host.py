@@ -93,8 +93,18 @@ class _CpuLocal:
         import torch
         xn = x.numpy()
         _, Iq = self.o.quantize(xn, self.nprobe)
-        Iq = np.where((Iq >= self.lo) & (Iq < self.hi), Iq, -1)
-        D, I = self.o.search_preassigned(xn, k, Iq)
+        return self.search_preassigned(x, k, torch.from_numpy(Iq))
+
+    def quantize(self, x, nprobe):
+        import torch
+        Dq, Iq = self.o.quantize(np.ascontiguousarray(x.numpy()), nprobe)
+        return torch.from_numpy(Dq), torch.from_numpy(Iq)
+
+    def search_preassigned(self, x, k, Iq):
+        import torch
+        Iq = Iq.numpy()
+        Iq = np.where((Iq >= self.lo) & (Iq < self.hi), Iq, -1)  # other ranks' lists: empty here
+        D, I = self.o.search_preassigned(x.numpy(), k, np.ascontiguousarray(Iq))
         return torch.from_numpy(D), torch.from_numpy(I)
 
 
