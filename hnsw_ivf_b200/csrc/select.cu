@@ -237,43 +237,45 @@ __device__ __forceinline__ float rerank_one(const SelectArgs& a, int q, uint32_t
     const bool vec = (a.d & 3) == 0 && (reinterpret_cast<uintptr_t>(a.queries) & 15) == 0;
     float acc = 0.f;
     for (int c0 = 0; c0 < a.nf4; c0 += 8) {
-        float4 y[8], x[8];
+        // the 8 row loads (one 16-byte gather each, L2 latency) go out together; the query values
+        // are the same address in every lane (an L1 broadcast) and are fetched as they are used
+        float4 y[8];
 #pragma unroll
         for (int u = 0; u < 8; ++u) {
             const int c = c0 + u;
             y[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-            x[u] = y[u];
-            if (c < a.nf4) {
+            if (c < a.nf4)
                 y[u] = __ldg(yp + (size_t)c * kBlockRows);
-                if (vec) {
-                    x[u] = __ldg(reinterpret_cast<const float4*>(xp + 4 * c));
-                } else {
-                    const int dd = 4 * c;
-                    x[u].x = __ldg(xp + dd);
-                    x[u].y = dd + 1 < a.d ? __ldg(xp + dd + 1) : 0.f;
-                    x[u].z = dd + 2 < a.d ? __ldg(xp + dd + 2) : 0.f;
-                    x[u].w = dd + 3 < a.d ? __ldg(xp + dd + 3) : 0.f;
-                }
-            }
         }
 #pragma unroll
         for (int u = 0; u < 8; ++u) {
-            if (c0 + u < a.nf4) {
+            const int c = c0 + u;
+            if (c < a.nf4) {
+                float4 x;
+                if (vec) {
+                    x = __ldg(reinterpret_cast<const float4*>(xp + 4 * c));
+                } else {
+                    const int dd = 4 * c;
+                    x.x = __ldg(xp + dd);
+                    x.y = dd + 1 < a.d ? __ldg(xp + dd + 1) : 0.f;
+                    x.z = dd + 2 < a.d ? __ldg(xp + dd + 2) : 0.f;
+                    x.w = dd + 3 < a.d ? __ldg(xp + dd + 3) : 0.f;
+                }
                 if (L2M) {
                     float t;
-                    t = x[u].x - y[u].x;
+                    t = x.x - y[u].x;
                     acc = fmaf(t, t, acc);
-                    t = x[u].y - y[u].y;
+                    t = x.y - y[u].y;
                     acc = fmaf(t, t, acc);
-                    t = x[u].z - y[u].z;
+                    t = x.z - y[u].z;
                     acc = fmaf(t, t, acc);
-                    t = x[u].w - y[u].w;
+                    t = x.w - y[u].w;
                     acc = fmaf(t, t, acc);
                 } else {
-                    acc = fmaf(x[u].x, y[u].x, acc);
-                    acc = fmaf(x[u].y, y[u].y, acc);
-                    acc = fmaf(x[u].z, y[u].z, acc);
-                    acc = fmaf(x[u].w, y[u].w, acc);
+                    acc = fmaf(x.x, y[u].x, acc);
+                    acc = fmaf(x.y, y[u].y, acc);
+                    acc = fmaf(x.z, y[u].z, acc);
+                    acc = fmaf(x.w, y[u].w, acc);
                 }
             }
         }
@@ -281,7 +283,7 @@ __device__ __forceinline__ float rerank_one(const SelectArgs& a, int q, uint32_t
     return (L2M ? acc : -acc) + 0.f;
 }
 
-__global__ void __launch_bounds__(256) select_warp_kernel(const SelectArgs a) {
+__global__ void __launch_bounds__(256, 4) select_warp_kernel(const SelectArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31;
     const int w = threadIdx.x >> 5;
@@ -298,9 +300,16 @@ __global__ void __launch_bounds__(256) select_warp_kernel(const SelectArgs a) {
     const int L = a.nseg * a.nsplit;
     const unsigned lt_mask = (1u << lane) - 1u;
 
-    // 1. the kk-th smallest list head bounds the kk-th smallest key
+    // 1. a bound on the kk-th smallest key from one pivot per (sorted) partial list: at least
+    // r * m keys are <= the r-th smallest of the lists' m-th entries. m = 1 (many lists): the
+    // kk-th smallest head; few long lists (the coarse quantizer: 8 lists of 32 for kk = 40):
+    // m = ceil(kk / L), which cuts the 256 keys to about kk before anything is sorted.
     uint64_t T = kSentinelKey - 1;
     if (L >= 2) {
+        int m = (kk + L - 1) / L;
+        if (m > a.kpart)
+            m = a.kpart;
+        const int r = (kk + m - 1) / m;
         const int Lp = pow2_ceil(L < 32 ? 32 : L);
         for (int i = lane; i < Lp; i += 32) {
             uint64_t key = kSentinelKey;
@@ -308,13 +317,15 @@ __global__ void __launch_bounds__(256) select_warp_kernel(const SelectArgs a) {
                 const int seg = i / a.nsplit;
                 const int slot = a.slot_of ? a.slot_of[(int64_t)q * a.nseg + seg] : q;
                 if (slot >= 0)
-                    key = a.part[(int64_t)slot * per_seg + (int64_t)(i % a.nsplit) * a.kpart];
+                    key = a.part[(int64_t)slot * per_seg + (int64_t)(i % a.nsplit) * a.kpart +
+                                 (m - 1)];
             }
             keys[i] = key;
         }
         __syncwarp();
         warp_sort_keys(keys, Lp, lane);
-        T = keys[(kk < Lp ? kk : Lp) - 1];
+        if (r <= L)
+            T = keys[r - 1];
         if (T == kSentinelKey)
             T = kSentinelKey - 1;
         __syncwarp();
@@ -322,17 +333,22 @@ __global__ void __launch_bounds__(256) select_warp_kernel(const SelectArgs a) {
 
     // 2. stream the partial lists, keep the keys <= T; keys[0..kept) sorted, then cnt unsorted
     int kept = 0, cnt = 0;
+    // (segment, offset) of this lane's next key, advanced by 32 per load: no division per key
+    int seg = lane / per_seg, off = lane - seg * per_seg;
     for (int c0 = 0; c0 < total; c0 += 256) {
         uint64_t kv[8];
 #pragma unroll
         for (int u = 0; u < 8; ++u) {
-            const int c = c0 + u * 32 + lane;
             kv[u] = kSentinelKey;
-            if (c < total) {
-                const int seg = c / per_seg;
+            if (c0 + u * 32 + lane < total) {
                 const int slot = a.slot_of ? a.slot_of[(int64_t)q * a.nseg + seg] : q;
                 if (slot >= 0)
-                    kv[u] = a.part[(int64_t)slot * per_seg + (c - seg * per_seg)];
+                    kv[u] = a.part[(int64_t)slot * per_seg + off];
+            }
+            off += 32;
+            while (off >= per_seg) {
+                off -= per_seg;
+                ++seg;
             }
         }
 #pragma unroll

@@ -56,7 +56,8 @@ def main():
                 o[m] = r[col[m]] + (" " + u if u else "")
         # anything that names the tensor pipe, whatever this ncu version calls it
         for h in head:
-            if "tensor" in h and h not in o and r[col[h]] not in ("", "0"):
+            if "pipe_tensor" in h and "Triage" not in h and "pct" in h and h not in o and \
+                    r[col[h]] not in ("", "0"):
                 u = units[col[h]]
                 o[h] = r[col[h]] + (" " + u if u else "")
         res.append(o)
