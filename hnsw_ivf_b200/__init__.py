@@ -15,6 +15,7 @@ from .binding import (  # noqa: F401
     IndexIVFStats,
     build_library,
     kernel_launches,
+    tensor_core_launches,
     library_path,
     load_library,
     merge_knn_results,
@@ -23,6 +24,6 @@ from .sharded import IndexShardsIVFFlat, list_range_of_rank  # noqa: F401
 
 __all__ = [
     "METRIC_INNER_PRODUCT", "METRIC_L2", "B200Error", "IndexIVFFlat", "IndexIVFStats",
-    "IndexShardsIVFFlat", "build_library", "kernel_launches", "library_path", "load_library", "merge_knn_results",
+    "IndexShardsIVFFlat", "build_library", "kernel_launches", "tensor_core_launches", "library_path", "load_library", "merge_knn_results",
     "list_range_of_rank",
 ]

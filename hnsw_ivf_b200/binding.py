@@ -73,6 +73,7 @@ SYMBOLS = [
     ("b200_IndexIVFFlat_last_timings", None, [_vp, C.POINTER(C.c_double)]),
     ("b200_IndexIVFFlat_set_stream", C.c_int, [_vp, _vp]),
     ("b200_kernel_launches", C.c_ulonglong, []),
+    ("b200_tensor_core_launches", C.c_ulonglong, []),
     ("b200_merge_knn_results", C.c_int,
      [C.c_int, C.c_int, C.c_int64, C.c_int64, _f32p, _i64p, _f32p, _i64p, C.c_int, _vp]),
 ]
@@ -281,6 +282,11 @@ class IndexIVFFlat:
         elif cuda_stream_ptr == 0:
             cuda_stream_ptr = 1  # cudaStreamLegacy
         self._check(self._lib.b200_IndexIVFFlat_set_stream(self._h, cuda_stream_ptr))
+
+
+def tensor_core_launches():
+    """tensor-core scan launches so far (a subset of kernel_launches())"""
+    return int(load_library().b200_tensor_core_launches())
 
 
 def kernel_launches():

@@ -159,6 +159,10 @@ int b200_IndexIVFFlat_set_stream(B200IndexIVFFlat* index, void* cuda_stream) {
     return guarded([&] { H(index)->set_stream((cudaStream_t)cuda_stream); });
 }
 
+unsigned long long b200_tensor_core_launches(void) {
+    return b200ivf::g_tc_launches.load();
+}
+
 unsigned long long b200_kernel_launches(void) {
     return b200ivf::g_kernel_launches.load();
 }

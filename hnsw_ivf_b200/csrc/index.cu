@@ -15,6 +15,7 @@
 namespace b200ivf {
 
 std::atomic<unsigned long long> g_kernel_launches{0};
+std::atomic<unsigned long long> g_tc_launches{0};
 
 #define CUDA_CHECK(expr)                                                                     \
     do {                                                                                     \
@@ -105,6 +106,8 @@ ScanCfg choose_scan_cfg(int nf4, int k) {
 
 // the CTA-tiled scan (scan_tile.cu) takes the lists probed by more than kTileMinQueries queries
 constexpr int kTileMinQueries = 8;
+// the rows-major tensor-core kernel takes the whole scan when fewer queries than this meet in a list
+constexpr double kTcrMaxAvgQueries = 48.0;
 constexpr size_t kSmemPerSM = 233472, kSmemPerCtaMax = 232448, kSmemCtaReserve = 1024;
 
 struct TileCfg {
@@ -162,6 +165,10 @@ struct IndexIVFFlatB200::Impl {
     alignas(64) unsigned char cent_map_tc[kTensorMapBytes] = {};
     alignas(64) unsigned char lists_map_tc[kTensorMapBytes] = {};
     bool use_tc = true; // B200IVF_NO_TC=1 turns the tensor-core scan off (A/B runs)
+    // which tensor-core kernel: 0 = by the number of queries that meet in a list (rows-major
+    // scan_tcr.cu below kTcrMaxAvgQueries, queries-major scan_tc.cu above and for the coarse
+    // quantizer), 1 / 2 = always queries-major / rows-major (B200IVF_TC_MODE, A/B runs)
+    int tc_mode = 0;
     cudaEvent_t ev[6] = {};
     double last_ms[5] = {0, 0, 0, 0, 0};
     IndexIVFStatsB200 stats;
@@ -169,6 +176,8 @@ struct IndexIVFFlatB200::Impl {
     Impl() {
         const char* e = getenv("B200IVF_NO_TC");
         use_tc = !(e && e[0] == '1');
+        const char* e2 = getenv("B200IVF_TC_MODE");
+        tc_mode = e2 ? atoi(e2) : 0;
         stage_x.pinned_host = stage_D.pinned_host = stage_I.pinned_host = true;
         stage_assign.pinned_host = host_stats.pinned_host = true;
     }
@@ -384,7 +393,8 @@ void IndexIVFFlatB200::run_coarse_(const float* xd, int64_t n, int kc, int32_t* 
     const TileCfg tcfg = choose_tile_cfg(nf4, kp);
     const ScanCfg cfg = choose_scan_cfg(nf4, kp);
     const bool tiled = !tc && tcfg.ok && n > kTileMinQueries;
-    const int64_t tq = tc ? kTcTQ : (tiled ? tcfg.tq : cfg.rq);
+    const bool tcr = tc && m.tc_mode == 2; // full 128-query tiles: the queries-major kernel
+    const int64_t tq = tcr ? kTcrTQ : tc ? kTcTQ : (tiled ? tcfg.tq : cfg.rq);
     const int64_t ngroups = ceil_div(n, tq);
     const int64_t nblk = ceil_div((int64_t)nlist, kBlockRows);
     const int64_t rows_step = tc ? 4 : (tiled ? 16 : kScanRowsPerStep); // 32-row blocks per step
@@ -394,7 +404,8 @@ void IndexIVFFlatB200::run_coarse_(const float* xd, int64_t n, int kc, int32_t* 
     S = std::min<int64_t>(S, 64);
     if (const char* e = getenv("B200IVF_COARSE_S")) // tuning experiments
         S = std::max<int64_t>(1, std::min<int64_t>(atoi(e), std::max<int64_t>(1, nblk / rows_step)));
-    m.part.reserve((size_t)n * S * (tc ? 2 : 1) * kp * sizeof(uint64_t));
+    const int pmul = (tc && !tcr) ? 2 : 1;
+    m.part.reserve((size_t)n * S * pmul * kp * sizeof(uint64_t));
     m.cplan.reserve(16);
     int32_t* grp_start = m.cplan.as<int32_t>();
     uint32_t* item_off = m.cplan.as<uint32_t>() + 2;
@@ -419,7 +430,10 @@ void IndexIVFFlatB200::run_coarse_(const float* xd, int64_t n, int kc, int32_t* 
         m.qthr.reserve((size_t)n * sizeof(uint32_t));
         CUDA_CHECK(launch_fill_u32(m.qthr.as<uint32_t>(), n, ordered_bits(kNeutralScore), st));
         a.qthr = m.qthr.as<uint32_t>();
-        CUDA_CHECK(launch_ivf_scan_tc(metric_type, (uint32_t)(ngroups * S), a, st));
+        if (tcr)
+            CUDA_CHECK(launch_ivf_scan_tcr(metric_type, (uint32_t)(ngroups * S), a, st));
+        else
+            CUDA_CHECK(launch_ivf_scan_tc(metric_type, (uint32_t)(ngroups * S), a, st));
     } else if (tiled) {
         TileScanArgs a;
         a.tmap = m.cent_map;
@@ -461,7 +475,7 @@ void IndexIVFFlatB200::run_coarse_(const float* xd, int64_t n, int kc, int32_t* 
     s.slot_of = nullptr;
     s.n = (int)n;
     s.nseg = 1;
-    s.nsplit = (int)S * (tc ? 2 : 1);
+    s.nsplit = (int)S * pmul;
     s.kpart = kp;
     s.k = kc;
     s.metric = metric_type;
@@ -536,7 +550,14 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
     // batch size: bound the partial-candidate scratch
     int64_t nb = std::min<int64_t>(n, 32768);
     BatchPlan bp = plan_batch(m.nf4, kp, nb, np, nlists_owned, m.nstored);
-    const int pmul = tc ? 2 : 1; // partial lists per (pair, split)
+    // queries per probed list, on average: few -> rows-major kernel (its MMA time follows the
+    // query count and it streams a list at any count), many -> queries-major (128-query tiles)
+    const double avg_q = (double)std::min<int64_t>(n, 32768) * np /
+            (double)std::max<int64_t>(1, std::min<int64_t>(nlists_owned, std::min<int64_t>(n, 32768) * np));
+    const bool tcr = tc && (m.tc_mode == 2 || (m.tc_mode == 0 && avg_q < kTcrMaxAvgQueries));
+    const int pmul = (tc && !tcr) ? 2 : 1; // partial lists per (pair, split)
+    const int tc_tq = tcr ? kTcrTQ : kTcTQ;
+    const int tc_min = tcr ? 0 : kTileMinQueries; // lists with more queries than this: tensor cores
     while (nb > 1 && (size_t)nb * np * bp.S * pmul * kp * sizeof(uint64_t) > ((size_t)2 << 30)) {
         nb = (nb + 1) / 2;
         bp = plan_batch(m.nf4, kp, nb, np, nlists_owned, m.nstored);
@@ -611,12 +632,11 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
         pa.slot_of = m.slot_of.as<int32_t>();
         pa.rq = bp.cfg.rq;
         pa.nsplit = (int)bp.S;
-        pa.tile_tq = tc ? kTcTQ : (tcfg.ok ? tcfg.tq : 0);
-        pa.tile_min = kTileMinQueries;
+        pa.tile_tq = tc ? tc_tq : (tcfg.ok ? tcfg.tq : 0);
+        pa.tile_min = tc ? tc_min : kTileMinQueries;
         pa.item_off_tile = m.item_off_tile.as<uint32_t>();
         const int64_t max_tc_items =
-                (pairs / kTcTQ + std::min<int64_t>(pairs / (kTileMinQueries + 1), (int64_t)nlist)) *
-                bp.S;
+                (pairs / tc_tq + std::min<int64_t>(pairs / (tc_min + 1), (int64_t)nlist)) * bp.S;
         if (tc) {
             m.item_list.reserve((size_t)(max_tc_items + 1) * sizeof(int32_t));
             pa.item_list_tile = m.item_list.as<int32_t>();
@@ -642,7 +662,9 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
         sa.part_mul = pmul;
         const int64_t max_items =
                 (ceil_div(pairs, bp.cfg.rq) + std::min<int64_t>(pairs, (int64_t)nlist)) * bp.S;
-        CUDA_CHECK(launch_ivf_scan(metric_type, bp.cfg.rq, bp.cfg.wpc, (uint32_t)max_items, sa, st));
+        if (!tcr) // (every probed list goes to the rows-major tensor-core kernel otherwise)
+            CUDA_CHECK(launch_ivf_scan(metric_type, bp.cfg.rq, bp.cfg.wpc, (uint32_t)max_items, sa,
+                                       st));
         if (tc) {
             // lists probed by more than kTileMinQueries queries of this batch: tensor cores
             TcScanArgs ta;
@@ -665,7 +687,10 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
             CUDA_CHECK(launch_fill_u32(m.qthr.as<uint32_t>(), ni, ordered_bits(kNeutralScore), st));
             ta.qthr = m.qthr.as<uint32_t>();
             ta.item_list = m.item_list.as<int32_t>();
-            CUDA_CHECK(launch_ivf_scan_tc(metric_type, (uint32_t)max_tc_items, ta, st));
+            if (tcr)
+                CUDA_CHECK(launch_ivf_scan_tcr(metric_type, (uint32_t)max_tc_items, ta, st));
+            else
+                CUDA_CHECK(launch_ivf_scan_tc(metric_type, (uint32_t)max_tc_items, ta, st));
         } else if (tcfg.ok) {
             // lists probed by more than kTileMinQueries queries of this batch
             TileScanArgs ta;

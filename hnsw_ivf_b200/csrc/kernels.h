@@ -10,6 +10,8 @@ namespace b200ivf {
 
 // number of kernels this library has launched (bench.py reports it as gpu_launches)
 extern std::atomic<unsigned long long> g_kernel_launches;
+// ... and how many of them were tensor-core (tcgen05) scans
+extern std::atomic<unsigned long long> g_tc_launches;
 inline void count_launches(int n) {
     g_kernel_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed);
 }
@@ -109,6 +111,12 @@ size_t scan_tc_smem_bytes(int nstages);
 cudaError_t make_slab_tensor_map_tc(void* map_out, const void* slab, int nf4, uint64_t nblocks);
 cudaError_t launch_ivf_scan_tc(int metric, uint32_t max_items, const TcScanArgs& a,
                                cudaStream_t st);
+
+// ---- rows-major tensor-core scan (scan_tcr.cu): same arguments, <= kTcrTQ queries per item, ONE
+// sorted list of kpart keys per (pair, split); nstages is chosen by the launcher --------------------
+constexpr int kTcrTQ = 96;
+cudaError_t launch_ivf_scan_tcr(int metric, uint32_t max_items, const TcScanArgs& a,
+                                cudaStream_t st);
 
 // ---- planning: invert the probe table into per-list query groups -------------------------------
 struct PlanArgs {

@@ -704,6 +704,7 @@ static cudaError_t launch_tc_one(uint32_t max_items, const TcScanArgs& a_in, cud
     }
     kern<<<max_items, kTcThreads, smem, st>>>(a, *reinterpret_cast<const CUtensorMap*>(a.tmap));
     count_launches(1);
+    g_tc_launches.fetch_add(1, std::memory_order_relaxed);
     if (a.trace) {
         long long h[7 * 64];
         cudaStreamSynchronize(st);

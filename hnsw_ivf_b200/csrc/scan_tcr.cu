@@ -1,0 +1,834 @@
+// scan_tcr.cu -- the tensor-core scan, rows-major form: K1 (coarse quantizer) and K2 (list scan)
+// for d <= 128, any number of queries per list.
+//
+// Same contract as scan.cu (IVFFlatScanner::scan_codes, faiss/IndexIVFFlat.cpp:155-179, applied to
+// every (query, probe) pair; for K1 knn_L2sqr / knn_inner_product over the centroid table,
+// faiss/utils/distances.cpp:885-920,836-871): the best KP keys of every (pair, row split) are left
+// in `part`, sorted. Scores are 3xTF32 products (fp32 accumulate), good to ~1e-6 of |x||y|: enough
+// to SELECT; select.cu re-scores the survivors in plain fp32 before the final ordering.
+//
+// Work item = (list, tile of <= 96 queries probing it, row split); one CTA each.
+//   D[128 rows x N queries] (TMEM, two buffers) += A[128 rows x 8] (TMEM) * B[N queries x 8]^T (smem)
+// The list rows are the M side of the MMA and the queries the N side, because the time of a
+// tcgen05.mma is max(M,128) * N / 256 cycles: N follows the number of queries that really probe the
+// list (rounded up to 16), M = 128 costs the same whether it is full or not. With few queries per
+// list the kernel is a pure HBM stream; with ~100 it is tensor-pipe bound.
+//  * B: the query tile, scaled by -1 (inner product) or -2 (L2), split into tf32 hi / lo parts,
+//    written once per item into shared memory in the K-major no-swizzle canonical layout
+//    (8 queries x 16 bytes = one core matrix, SBO = 128 B, LBO = 97 * 16 B: odd, so that the
+//    coalesced prologue stores are bank-conflict free).
+//  * A: list rows arrive by TMA (box {128 floats, 4 blocks, 8 columns} of the slab = 128 rows x 32
+//    dims per stage). The split warps read a stage once from shared memory (lane = row) and write
+//    BOTH operand parts to tensor memory with tcgen05.st: hi = the raw fp32 bits (the tensor core
+//    ignores the low 13 mantissa bits, tools/tc_probe.cu), lo = tf32(y - trunc_tf32(y)). The raw
+//    stage is released to the TMA as soon as it is in registers; the MMAs never read row data from
+//    shared memory (per stage: 16 KB TMA write + 16 KB read + 12 * N * 32 B of B reads, against
+//    96 KB for the queries-major form, which was shared-memory-bandwidth bound).
+//  * One elected thread issues the MMAs (3 per 8 dims: lo*hi, hi*lo, hi*hi).
+//  * Epilogue (4 warps, thread = row = TMEM lane): per 16 queries one tcgen05.ld; score (+ |y|^2
+//    for L2) is compared with the query's pruning bound held in shared memory; a warp ballot skips
+//    the column when no row passes (the steady state). Passing (score, row) keys are appended to
+//    the query's candidate buffer (KP kept + 16 free entries) with a shared-memory atomic; at the
+//    end of a tile the warps compact the buffers that filled up (warp bitonic sort, keep KP,
+//    tighten the bound, publish it in qthr for the other CTAs working on the same query). A tile
+//    that overflows a buffer is re-examined for the dropped rows after the compaction (at most 8
+//    rounds: only while the bound is still loose, i.e. the first tile of the first lists).
+#include "common.cuh"
+#include "kernels.h"
+#include "tc_ptx.cuh"
+
+#include <cstdio>
+#include <cstdlib>
+
+namespace b200ivf {
+
+namespace {
+
+using namespace ptx;
+
+constexpr int kREpiWarps = 8;     // warps 0-7
+constexpr int kRTmaWarp = 8;
+constexpr int kRMmaWarp = 9;
+constexpr int kRSplitWarp0 = 10;  // warps 10-17
+constexpr int kRSplitWarps = 8;
+constexpr int kRThreads = (kRSplitWarp0 + kRSplitWarps) * 32; // 576
+constexpr int kRLoaderWarps = 17; // every warp but the TMA producer fills B in the prologue
+constexpr int kRKC = 8;           // float4 columns per stage (4 MMA k-steps)
+constexpr int kRTileBlocks = 4;   // 32-row blocks per tile (M = 128)
+constexpr int kRStageF4 = kRKC * kRTileBlocks * kBlockRows; // 1024 float4 = 16 KB
+constexpr int kRMaxStages = 12;   // raw ring (as deep as the item's query tile leaves room for)
+constexpr int kRAStages = 4;      // operand ring in tensor memory
+constexpr uint32_t kRColsD = 0;   // two accumulator buffers of 128 columns
+constexpr uint32_t kRColsA = 256; // kRAStages x (32 hi + 32 lo) columns
+constexpr int kRMaxChunks = 32;   // float4 columns of a query (d <= 128)
+constexpr uint32_t kRBSBO = 128;
+constexpr int kRFree = 16;        // free candidate entries beyond the KP kept
+constexpr int kRCompactMin = 8;   // compact a buffer once it holds this many new candidates
+
+__device__ __forceinline__ float tf32_trunc(float x) {
+    return __uint_as_float(__float_as_uint(x) & 0xffffe000u);
+}
+__device__ __forceinline__ float tf32_rn(float x) {
+    return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u);
+}
+__device__ __forceinline__ float tf32_lo(float y) {
+    return tf32_rn(y - tf32_trunc(y));
+}
+
+template <int KP>
+struct RCfg {
+    static constexpr int C = KP + kRFree;           // candidate entries per query
+};
+
+// ascending bitonic sort of one key per lane
+__device__ __forceinline__ uint64_t warp_sort32(uint64_t key, int lane) {
+#pragma unroll
+    for (int size = 2; size <= 32; size <<= 1) {
+#pragma unroll
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            const uint64_t other = __shfl_xor_sync(0xffffffffu, key, stride);
+            const bool up = (lane & size) == 0 || size == 32;
+            const bool lower = (lane & stride) == 0;
+            const bool take_min = up == lower;
+            const uint64_t mn = key < other ? key : other, mx = key < other ? other : key;
+            key = take_min ? mn : mx;
+        }
+    }
+    return key;
+}
+// ascending bitonic sort of two keys per lane: positions lane (a) and lane + 32 (b)
+__device__ __forceinline__ void warp_sort64(uint64_t& a, uint64_t& b, int lane) {
+    // sort a ascending and b descending, then one bitonic merge of 64
+    a = warp_sort32(a, lane);
+    b = warp_sort32(b, lane);
+    b = __shfl_sync(0xffffffffu, b, 31 - lane);
+    {
+        const uint64_t mn = a < b ? a : b, mx = a < b ? b : a;
+        a = mn;
+        b = mx;
+    }
+#pragma unroll
+    for (int stride = 16; stride > 0; stride >>= 1) {
+        const uint64_t oa = __shfl_xor_sync(0xffffffffu, a, stride);
+        const uint64_t ob = __shfl_xor_sync(0xffffffffu, b, stride);
+        const bool lower = (lane & stride) == 0;
+        a = lower ? (a < oa ? a : oa) : (a < oa ? oa : a);
+        b = lower ? (b < ob ? b : ob) : (b < ob ? ob : b);
+    }
+}
+
+// v[j] for a per-lane j (registers cannot be indexed dynamically: a 4-level select tree)
+__device__ __forceinline__ uint32_t sel16(const uint32_t (&v)[16], int j) {
+    uint32_t a8[8], a4[4], a2[2];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+        a8[i] = (j & 1) ? v[2 * i + 1] : v[2 * i];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+        a4[i] = (j & 2) ? a8[2 * i + 1] : a8[2 * i];
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+        a2[i] = (j & 4) ? a4[2 * i + 1] : a4[2 * i];
+    return (j & 8) ? a2[1] : a2[0];
+}
+// the bound the epilogue's filter uses: 2^-21 looser than the real one, so that the filter (which
+// rounds differently from the exact test that follows it) never rejects what the test would accept
+__device__ __forceinline__ float loosen(float x) {
+    return fmaf(fabsf(x), 4.76837158e-7f, x);
+}
+
+struct RSmem {
+    float4* raw;        // [nst][kRStageF4]
+    unsigned char* bhi; // query tile, hi part
+    unsigned char* blo; // query tile, lo part
+    uint64_t* cand;     // [kTcrTQ][C]
+    uint32_t* thr;      // [kTcrTQ] ordered bits of the pruning bound (full score)
+    float* thrp;        // [kTcrTQ] bound minus |x|^2: what the raw accumulator is compared with
+    float* thrf;        // [kTcrTQ] loosen(thrp): what the epilogue's filter uses
+    float* xn;          // [kTcrTQ] |x|^2 (L2) or 0
+    int* cnt;           // [kTcrTQ] entries in the candidate buffer (may run past C: overflow)
+    int* qid;           // [kTcrTQ] query number
+    int* flag;          // [4] by barrier epoch: 1 = some buffer wants compaction, 2 = overflowed
+    uint64_t* full;     // [kRMaxStages] TMA landed
+    uint64_t* empty;    // [kRMaxStages] the split warps have the stage in registers
+    uint64_t* a_rdy;    // [kRAStages] operand stage written to tensor memory
+    uint64_t* a_empty;  // [kRAStages] MMAs that read the operand stage are done
+    uint64_t* d_full;   // [2] accumulator buffer complete
+    uint64_t* d_empty;  // [2] accumulator buffer drained by the epilogue
+    uint32_t* tmem;     // [1]
+};
+
+// Shared memory is carved per ITEM: the B operand and the candidate buffers are sized by the item's
+// query count (n16) and dimension (nch chunks), and the raw ring gets every 16 KB stage that is
+// left -- with few queries the kernel is an HBM stream and lives on bytes in flight.
+//   B part: nch chunks x LBO bytes, LBO = (n16 + 1) * 16 (odd multiple of 16: the coalesced
+//   prologue stores of one query row hit 8 different 16-byte bank groups)
+__host__ __device__ inline uint32_t tcr_lbo(int n16) {
+    return (uint32_t)(n16 + 1) * 16u;
+}
+__host__ __device__ inline size_t tcr_rest_bytes(int kp, int n16, int nch) {
+    return 2 * (size_t)nch * tcr_lbo(n16) + (size_t)n16 * (kp + kRFree) * 8 +
+            (size_t)kTcrTQ * 6 * 4 + 4 * 4 + (2 * kRMaxStages + 2 * kRAStages + 4) * 8 + 16;
+}
+__host__ __device__ inline int tcr_stages(size_t smem_total, int kp, int n16, int nch) {
+    const size_t rest = tcr_rest_bytes(kp, n16, nch);
+    const int n = smem_total > rest ? (int)((smem_total - rest) / (kRStageF4 * sizeof(float4))) : 0;
+    return n > kRMaxStages ? kRMaxStages : n;
+}
+
+template <int KP>
+__device__ __forceinline__ RSmem carve_r(unsigned char* raw, int nst, int n16, int nch) {
+    RSmem s;
+    const size_t bbytes = (size_t)nch * tcr_lbo(n16);
+    s.raw = reinterpret_cast<float4*>(raw);
+    s.bhi = raw + (size_t)nst * kRStageF4 * sizeof(float4);
+    s.blo = s.bhi + bbytes;
+    s.cand = reinterpret_cast<uint64_t*>(s.blo + bbytes);
+    s.thr = reinterpret_cast<uint32_t*>(s.cand + (size_t)n16 * RCfg<KP>::C);
+    s.thrp = reinterpret_cast<float*>(s.thr + kTcrTQ);
+    s.thrf = s.thrp + kTcrTQ;
+    s.xn = s.thrf + kTcrTQ;
+    s.cnt = reinterpret_cast<int*>(s.xn + kTcrTQ);
+    s.qid = s.cnt + kTcrTQ;
+    s.flag = s.qid + kTcrTQ;
+    s.full = reinterpret_cast<uint64_t*>(s.flag + 4);
+    s.empty = s.full + kRMaxStages;
+    s.a_rdy = s.empty + kRMaxStages;
+    s.a_empty = s.a_rdy + kRAStages;
+    s.d_full = s.a_empty + kRAStages;
+    s.d_empty = s.d_full + 2;
+    s.tmem = reinterpret_cast<uint32_t*>(s.d_empty + 2);
+    return s;
+}
+
+// Compaction of the candidate buffers a warp owns (queries = warp mod 8), out of line: sort, keep
+// the best KP, tighten the query's bound and publish it for the other CTAs.
+template <int KP>
+__device__ __noinline__ void tcr_compact(uint64_t* cand, int* cnt, uint32_t* thr, float* thrp,
+                                         float* thrf, const float* xn, const int* qid,
+                                         uint32_t* qthr, int nqw, int warp, int lane,
+                                         bool final_pass) {
+    constexpr int C = KP + kRFree;
+    const int qmine = lane * kREpiWarps + warp;
+    const bool need = qmine < nqw && (final_pass || cnt[qmine] >= KP + kRCompactMin);
+    unsigned todo = __ballot_sync(0xffffffffu, need);
+    while (todo != 0u) {
+        const int qi = (__ffs(todo) - 1) * kREpiWarps + warp;
+        todo &= todo - 1u;
+        const int n = min(cnt[qi], C);
+        uint64_t* buf = cand + (size_t)qi * C;
+        uint64_t k0 = lane < n ? buf[lane] : kSentinelKey;
+        uint64_t kth;
+        if (C <= 32) {
+            k0 = warp_sort32(k0, lane);
+            if (lane < KP)
+                buf[lane] = k0;
+            kth = __shfl_sync(0xffffffffu, k0, KP - 1);
+        } else {
+            uint64_t k1 = lane + 32 < n ? buf[lane + 32] : kSentinelKey;
+            warp_sort64(k0, k1, lane);
+            if (lane < KP)
+                buf[lane] = k0;
+            if (lane + 32 < KP)
+                buf[lane + 32] = k1;
+            kth = KP <= 32 ? __shfl_sync(0xffffffffu, k0, (KP - 1) & 31)
+                           : __shfl_sync(0xffffffffu, k1, (KP - 1) & 31);
+        }
+        if (lane == 0) {
+            cnt[qi] = min(n, KP);
+            if (n >= KP) {
+                const uint32_t tb = (uint32_t)(kth >> 32);
+                const uint32_t old = atomicMin(&thr[qi], tb);
+                if (tb < old) {
+                    const float tp = from_ordered_bits(tb) - xn[qi];
+                    thrp[qi] = tp;
+                    thrf[qi] = loosen(tp);
+                    if (qthr)
+                        atomicMin(qthr + qid[qi], tb);
+                }
+            }
+        }
+        __syncwarp();
+    }
+}
+
+
+// wait with the waiting time added to a trace counter (timing experiments only)
+#define TCR_WAIT(bar, par, acc)                                          \
+    do {                                                                 \
+        if (tracing) {                                                   \
+            const long long w0_ = clock64();                             \
+            mbar_wait(bar, par);                                         \
+            acc += clock64() - w0_;                                      \
+        } else {                                                         \
+            mbar_wait(bar, par);                                         \
+        }                                                                \
+    } while (0)
+
+#define TCR_TRACE(role, idx)                                             \
+    do {                                                                 \
+        if (tracing && (idx) < 64)                                       \
+            a.trace[(role) * 64 + (idx)] = clock64();                    \
+    } while (0)
+
+template <int METRIC, int KP>
+__global__ void __launch_bounds__(kRThreads, 1)
+        ivf_scan_tcr_kernel(const TcScanArgs a, const __grid_constant__ CUtensorMap tmap) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    constexpr int C = RCfg<KP>::C;
+    const int tid = threadIdx.x;
+    const int lane = tid & 31;
+    const int warp = tid >> 5;
+
+    // ---- which item --------------------------------------------------------------------------
+    const uint32_t item = blockIdx.x;
+    if (item >= a.item_off[a.nlists])
+        return;
+    int lo_l = 0, hi_l = a.nlists;
+    if (a.item_list) {
+        lo_l = a.item_list[item]; // written by the plan: no dependent-load chain
+    } else {
+        while (hi_l - lo_l > 1) {
+            const int mid = (lo_l + hi_l) >> 1;
+            if (a.item_off[mid] <= item)
+                lo_l = mid;
+            else
+                hi_l = mid;
+        }
+    }
+    const int l = lo_l;
+    const int g0 = a.grp_start[l];
+    const int cnt_l = a.grp_start[l + 1] - g0;
+    const int nsub = (cnt_l + kTcrTQ - 1) / kTcrTQ;
+    const uint32_t local = item - a.item_off[l];
+    const int split = (int)(local / (uint32_t)nsub);
+    const int sub = (int)(local % (uint32_t)nsub);
+    // the queries of the list are spread evenly over its nsub tiles
+    const int qa = (int)(((long long)cnt_l * sub) / nsub);
+    const int qb = (int)(((long long)cnt_l * (sub + 1)) / nsub);
+    const int q0 = g0 + qa;
+    const int nqw = qb - qa;                  // 1 .. kTcrTQ
+    const int n16 = (nqw + 15) & ~15;         // MMA N
+
+    const int len = a.list_len[l];
+    const int nb = (len + kBlockRows - 1) / kBlockRows;
+    const int b0 = (int)(((long long)nb * split) / a.nsplit);
+    const int b1 = (int)(((long long)nb * (split + 1)) / a.nsplit);
+    const uint32_t blk0 = a.list_blk0[l];
+    const int nf4 = a.nf4;
+    const int ntiles = (b1 - b0 + kRTileBlocks - 1) / kRTileBlocks;
+    const int nsg = (nf4 + kRKC - 1) / kRKC;  // stages per tile
+    const int nks = (nf4 + 1) >> 1;           // MMA k-steps (8 dims each) per tile
+    const int niter = ntiles * nsg;
+    const int nst = tcr_stages((size_t)a.nstages * 1024, KP, n16, 2 * nks);
+    const uint32_t lbo = tcr_lbo(n16);
+
+    const RSmem s = carve_r<KP>(smem_raw, nst, n16, 2 * nks);
+    const bool tracing = a.trace != nullptr && item == a.trace_item;
+    if (tid == 0) {
+        TCR_TRACE(0, 0);
+        if (tracing) {
+            a.trace[0 * 64 + 2] = ntiles;
+            a.trace[0 * 64 + 3] = nqw;
+        }
+    }
+
+    if (tid == 0) {
+        for (int i = 0; i < kRMaxStages; ++i) {
+            mbar_init(&s.full[i], 1);
+            mbar_init(&s.empty[i], kRSplitWarps / 2);
+        }
+        for (int i = 0; i < kRAStages; ++i) {
+            mbar_init(&s.a_rdy[i], kRSplitWarps / 2);
+            mbar_init(&s.a_empty[i], 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&s.d_full[i], 1);
+            mbar_init(&s.d_empty[i], kREpiWarps);
+        }
+        for (int i = 0; i < 4; ++i)
+            s.flag[i] = 0;
+        fence_barrier_init();
+    }
+    if (warp == kRMmaWarp) {
+        tmem_alloc(s.tmem, 512);
+        tmem_relinquish();
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem = *s.tmem;
+    if (tid == 0)
+        TCR_TRACE(0, 1);
+
+    if (warp == kRTmaWarp) {
+        // ======================= TMA producer ===================================================
+        if (lane == 0 && ntiles > 0) {
+            tma_prefetch_desc(&tmap);
+            int st = 0;
+            uint32_t ph = 0;
+            long long w_empty = 0;
+            for (int t = 0; t < ntiles; ++t) {
+                const int blk = (int)blk0 + b0 + t * kRTileBlocks;
+                for (int sg = 0; sg < nsg; ++sg) {
+                    if (t * nsg + sg >= nst)
+                        TCR_WAIT(&s.empty[st], ph ^ 1u, w_empty);
+                    mbar_expect_tx(&s.full[st], (uint32_t)(kRStageF4 * sizeof(float4)));
+                    tma_load_3d(s.raw + (size_t)st * kRStageF4, &tmap, 0, blk, sg * kRKC,
+                                &s.full[st]);
+                    if (++st == nst) {
+                        st = 0;
+                        ph ^= 1u;
+                    }
+                }
+                TCR_TRACE(1, t);
+            }
+            if (tracing)
+                a.trace[9 * 64 + 4] = w_empty;
+        }
+        return; // takes no part in the named barriers below
+    }
+
+    // ---- prologue: the query tile -> shared memory (B operand), 13 warps --------------------------
+    {
+        const int wl = warp < kRTmaWarp ? warp : warp - 1;
+        const float scale = METRIC == kMetricL2 ? -2.f : -1.f;
+        const bool vec = (a.d & 3) == 0 && (reinterpret_cast<uintptr_t>(a.queries) & 15) == 0;
+        const int nch = 2 * nks; // chunks the MMAs read (the last one may be padding)
+        constexpr int kPer = (kTcrTQ + kRLoaderWarps - 1) / kRLoaderWarps; // 8
+        float4 xv[kPer];
+        int qn[kPer];
+#pragma unroll
+        for (int u = 0; u < kPer; ++u) {
+            const int n = wl + u * kRLoaderWarps;
+            qn[u] = n < nqw ? (a.pair_query ? a.pair_query[q0 + n] : q0 + n) : -1;
+        }
+#pragma unroll
+        for (int u = 0; u < kPer; ++u) {
+            xv[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (qn[u] >= 0 && lane < nf4) {
+                const float* src = a.queries + (size_t)qn[u] * a.d;
+                const int dd = 4 * lane;
+                if (vec) {
+                    xv[u] = __ldg(reinterpret_cast<const float4*>(src + dd));
+                } else {
+                    xv[u].x = __ldg(src + dd);
+                    xv[u].y = dd + 1 < a.d ? __ldg(src + dd + 1) : 0.f;
+                    xv[u].z = dd + 2 < a.d ? __ldg(src + dd + 2) : 0.f;
+                    xv[u].w = dd + 3 < a.d ? __ldg(src + dd + 3) : 0.f;
+                }
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < kPer; ++u) {
+            const int n = wl + u * kRLoaderWarps;
+            if (n < n16) {
+                const float4 x = xv[u];
+                float nn = x.x * x.x + x.y * x.y + x.z * x.z + x.w * x.w;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1)
+                    nn += __shfl_xor_sync(0xffffffffu, nn, o);
+                if (lane < nch) {
+                    float4 h, lo;
+                    h.x = x.x * scale;
+                    h.y = x.y * scale;
+                    h.z = x.z * scale;
+                    h.w = x.w * scale;
+                    lo.x = tf32_lo(h.x);
+                    lo.y = tf32_lo(h.y);
+                    lo.z = tf32_lo(h.z);
+                    lo.w = tf32_lo(h.w);
+                    const size_t off = (size_t)lane * lbo + (size_t)n * 16;
+                    *reinterpret_cast<float4*>(s.bhi + off) = h;
+                    *reinterpret_cast<float4*>(s.blo + off) = lo;
+                }
+                if (lane == 0 && n < kTcrTQ) {
+                    const int q = qn[u];
+                    const float xnq = (METRIC == kMetricL2 && q >= 0) ? nn : 0.f;
+                    uint32_t tb = ordered_bits(kNeutralScore);
+                    if (q >= 0 && a.qthr)
+                        tb = min(tb, a.qthr[q]);
+                    s.qid[n] = q;
+                    s.xn[n] = xnq;
+                    s.cnt[n] = 0;
+                    s.thr[n] = tb;
+                    // a padding column (q < 0) must never accept a row
+                    const float tp = q >= 0 ? from_ordered_bits(tb) - xnq : -kNeutralScore;
+                    s.thrp[n] = tp;
+                    s.thrf[n] = loosen(tp);
+                }
+            }
+        }
+        fence_proxy_async_smem(); // B is read by the tensor core through the async proxy
+        named_bar_sync(1, kRLoaderWarps * 32);
+    }
+    if (tid == 0)
+        TCR_TRACE(0, 4);
+
+    if (warp == kRMmaWarp) {
+        // ======================= MMA issuer =====================================================
+        // The whole warp runs the loop (converged control flow); one elected lane issues.
+        const uint32_t idesc = make_idesc_tf32(kRTileBlocks * kBlockRows, n16);
+        const uint64_t desc0 = make_smem_desc_kmajor_noswz(0, lbo, kRBSBO);
+        const uint32_t bhi0 = smem_u32(s.bhi), blo0 = smem_u32(s.blo);
+        tc_fence_after_sync();
+        int as = 0;
+        uint32_t aph = 0;
+        bool ready = false;
+        long long w_ardy = 0, w_dempty = 0, w_issue = 0;
+        for (int t = 0; t < ntiles; ++t) {
+            const int b = t & 1;
+            if (t >= 2) {
+                TCR_WAIT(&s.d_empty[b], (uint32_t)(((t >> 1) & 1) ^ 1), w_dempty);
+                tc_fence_after_sync();
+            }
+            const uint32_t tD = tmem + kRColsD + (uint32_t)b * 128u;
+            for (int sg = 0; sg < nsg; ++sg) {
+                if (!ready)
+                    TCR_WAIT(&s.a_rdy[as], aph, w_ardy);
+                tc_fence_after_sync();
+                const long long i0_ = tracing ? clock64() : 0;
+                const int ks0 = sg * (kRKC / 2);
+                const int ksn = (a.dbg & 8) ? 0 : nks - ks0; // >= 1
+                const uint32_t ahi = tmem + kRColsA + (uint32_t)as * 64u;
+                const uint32_t alo = ahi + 32u;
+                // B descriptors advance by 2 chunks (2 * LBO bytes, in 16-byte units) per k-step
+                const uint64_t dhi = desc0 + (uint64_t)((bhi0 + (uint32_t)(ks0 * 2) * lbo) >> 4);
+                const uint64_t dlo = desc0 + (uint64_t)((blo0 + (uint32_t)(ks0 * 2) * lbo) >> 4);
+                const int nas = as + 1 == kRAStages ? 0 : as + 1;
+                const uint32_t naph = as + 1 == kRAStages ? aph ^ 1u : aph;
+                if (elect_one_sync()) {
+#pragma unroll
+                    for (int ks = 0; ks < kRKC / 2 - 1; ++ks) {
+                        if (ks < ksn) {
+                            const uint64_t kh = dhi + (uint64_t)((uint32_t)ks * ((2u * lbo) >> 4));
+                            const uint64_t kl = dlo + (uint64_t)((uint32_t)ks * ((2u * lbo) >> 4));
+                            // small terms first, the big product last
+                            mma_tf32_ts(tD, alo + ks * 8, kh, idesc, (sg | ks) != 0 ? 1u : 0u);
+                            mma_tf32_ts(tD, ahi + ks * 8, kl, idesc, 1u);
+                            mma_tf32_ts(tD, ahi + ks * 8, kh, idesc, 1u);
+                        }
+                    }
+                }
+                __syncwarp();
+                ready = mbar_test_wait(&s.a_rdy[nas], naph); // next stage, MMAs still queued
+                if (elect_one_sync()) {
+                    constexpr int ks = kRKC / 2 - 1;
+                    if (ks < ksn) {
+                        const uint64_t kh = dhi + (uint64_t)((uint32_t)ks * ((2u * lbo) >> 4));
+                        const uint64_t kl = dlo + (uint64_t)((uint32_t)ks * ((2u * lbo) >> 4));
+                        mma_tf32_ts(tD, alo + ks * 8, kh, idesc, 1u);
+                        mma_tf32_ts(tD, ahi + ks * 8, kl, idesc, 1u);
+                        mma_tf32_ts(tD, ahi + ks * 8, kh, idesc, 1u);
+                    }
+                    mma_commit(&s.a_empty[as]);
+                    if (sg == nsg - 1)
+                        mma_commit(&s.d_full[b]);
+                }
+                __syncwarp();
+                if (tracing)
+                    w_issue += clock64() - i0_;
+                as = nas;
+                aph = naph;
+            }
+            if (lane == 0)
+                TCR_TRACE(2, t);
+        }
+        if (tracing && lane == 0) {
+            a.trace[9 * 64 + 2] = w_ardy;
+            a.trace[9 * 64 + 3] = w_dempty;
+            a.trace[9 * 64 + 6] = w_issue;
+        }
+    } else if (warp >= kRSplitWarp0) {
+        // ======================= split warps: raw stage -> (hi, lo) in tensor memory ============
+        // Two groups of 4 warps (one per TMEM lane quarter) take alternate stages, so that the
+        // load -> convert -> tcgen05.st -> wait chain of one stage overlaps the next stage's.
+        const int sw = warp - kRSplitWarp0;
+        const int quarter = warp & 3;             // the TMEM lanes this warp may touch
+        const int grp = sw >> 2;
+        const int row = quarter * 32 + lane;
+        const uint32_t lane_addr = (uint32_t)(quarter * 32) << 16;
+        long long w_full = 0, w_aempty = 0;
+        for (int it = grp; it < niter; it += 2) {
+            const int st = it % nst;
+            const uint32_t ph = (uint32_t)((it / nst) & 1);
+            const int as = it % kRAStages;
+            const uint32_t aph = (uint32_t)((it / kRAStages) & 1);
+            TCR_WAIT(&s.full[st], ph, w_full);
+            const float4* src = s.raw + (size_t)st * kRStageF4 + row;
+            if (it >= kRAStages) {
+                TCR_WAIT(&s.a_empty[as], aph ^ 1u, w_aempty);
+                tc_fence_after_sync();
+            }
+            const uint32_t ta = tmem + lane_addr + kRColsA + (uint32_t)as * 64u;
+#pragma unroll
+            for (int h = 0; h < 2 && !(a.dbg & 4); ++h) {
+                uint32_t hi[16], lo[16];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const float4 y = src[(h * 4 + u) * 128];
+                    hi[4 * u + 0] = __float_as_uint(y.x);
+                    hi[4 * u + 1] = __float_as_uint(y.y);
+                    hi[4 * u + 2] = __float_as_uint(y.z);
+                    hi[4 * u + 3] = __float_as_uint(y.w);
+                    lo[4 * u + 0] = __float_as_uint(tf32_lo(y.x));
+                    lo[4 * u + 1] = __float_as_uint(tf32_lo(y.y));
+                    lo[4 * u + 2] = __float_as_uint(tf32_lo(y.z));
+                    lo[4 * u + 3] = __float_as_uint(tf32_lo(y.w));
+                }
+                tmem_st_32x32b_x16(ta + (uint32_t)h * 16u, hi);
+                tmem_st_32x32b_x16(ta + 32u + (uint32_t)h * 16u, lo);
+            }
+            __syncwarp();
+            if (lane == 0)
+                mbar_arrive(&s.empty[st]); // the stage is in registers: the TMA may refill it
+            tmem_st_wait();
+            tc_fence_before_sync();
+            __syncwarp();
+            if (lane == 0)
+                mbar_arrive(&s.a_rdy[as]);
+            if (lane == 0 && quarter == 0 && (it + 1) % nsg == 0)
+                TCR_TRACE(3, it / nsg);
+        }
+        if (tracing && lane == 0 && quarter == 0 && grp == 0) {
+            a.trace[9 * 64 + 0] = w_full;
+            a.trace[9 * 64 + 1] = w_aempty;
+        }
+    } else {
+        // ======================= epilogue: 8 warps, thread = row of the tile ====================
+        // Warps e and e + 4 share a TMEM lane quarter and take alternate 16-query chunks.
+        const int quarter = warp & 3, half = warp >> 2;
+        const uint32_t lane_addr = (uint32_t)(quarter * 32) << 16;
+        const int nch16 = n16 >> 4;
+        const int rows_split = (b1 - b0) * kBlockRows;       // rows of this split (padded blocks)
+        const int row_lim = min(rows_split, len - b0 * kBlockRows);
+        // per-tile refresh of the bounds from the other CTAs: thread j looks after query j
+        const int myq = tid < nqw ? s.qid[tid] : -1;
+        long long w_dfull = 0;
+        int ep = 0; // barrier epochs: flag[ep & 3] collects what the pushes of the epoch want
+
+        for (int t = 0; t < ntiles; ++t) {
+            const int b = t & 1;
+            const int r_in_split = t * (kRTileBlocks * kBlockRows) + quarter * 32 + lane;
+            const bool valid = r_in_split < row_lim;
+            const uint32_t rowid = (blk0 + (uint32_t)b0) * kBlockRows + (uint32_t)r_in_split;
+            // a row that does not exist scores +inf
+            const float nrm = !valid ? __int_as_float(0x7f800000)
+                                     : (METRIC == kMetricL2 ? __ldg(a.norms + rowid) : 0.f);
+            const float nrmf = nrm * (1.f - 4.76837158e-7f); // the filter errs on the accept side
+            const uint32_t gthr = (myq >= 0 && a.qthr) ? __ldcg(a.qthr + myq) : 0xffffffffu;
+            uint32_t drop[kTcrTQ / 32] = {0u, 0u, 0u};
+            TCR_WAIT(&s.d_full[b], (uint32_t)((t >> 1) & 1), w_dfull);
+            tc_fence_after_sync();
+            const uint32_t tD = tmem + lane_addr + kRColsD + (uint32_t)b * 128u;
+            int n_events = 0, n_rounds = 0;
+            long long c_scan = 0, c_comp = 0;
+            for (int round = 0;; ++round) {
+                long long tt0 = tracing ? clock64() : 0;
+                ++n_rounds;
+                int fl = 0;
+#pragma unroll 1
+                for (int ch = half; ch < nch16; ch += 2) {
+                    uint32_t v[16];
+                    tmem_ld_32x32b_x16(tD + (uint32_t)ch * 16u, v);
+                    tmem_ld_wait();
+                    if (a.dbg & 1)
+                        continue;
+                    const uint32_t dword = ch < 2 ? drop[0] : (ch < 4 ? drop[1] : drop[2]);
+                    const uint32_t dbits = (dword >> ((ch & 1) * 16)) & 0xffffu;
+                    // filter: min over the 16 queries of (accumulator - loosened bound), one
+                    // FADD and half an FMNMX3 per element, one vote per chunk
+                    float dd[16];
+#pragma unroll
+                    for (int j4 = 0; j4 < 4; ++j4) {
+                        const float4 th = *reinterpret_cast<const float4*>(s.thrf + ch * 16 + j4 * 4);
+                        dd[4 * j4 + 0] = __uint_as_float(v[4 * j4 + 0]) - th.x;
+                        dd[4 * j4 + 1] = __uint_as_float(v[4 * j4 + 1]) - th.y;
+                        dd[4 * j4 + 2] = __uint_as_float(v[4 * j4 + 2]) - th.z;
+                        dd[4 * j4 + 3] = __uint_as_float(v[4 * j4 + 3]) - th.w;
+                    }
+                    float mn = dd[0];
+#pragma unroll
+                    for (int j = 1; j < 16; ++j)
+                        mn = fminf(mn, dd[j]);
+                    const bool hit = round == 0 ? (mn + nrmf <= 0.f) : dbits != 0u;
+                    if (!__any_sync(0xffffffffu, hit))
+                        continue;
+                    // the lanes that hold a candidate walk their own columns (divergent)
+                    uint32_t pm = 0u;
+                    if (round == 0) {
+#pragma unroll
+                        for (int j = 0; j < 16; ++j)
+                            pm |= (dd[j] + nrmf <= 0.f) ? (1u << j) : 0u;
+                    } else {
+                        pm = dbits;
+                    }
+                    uint32_t ndrop = 0u;
+                    while (pm != 0u) {
+                        const int j = __ffs(pm) - 1;
+                        pm &= pm - 1u;
+                        ++n_events;
+                        const int qi = ch * 16 + j;
+                        const float sc = __uint_as_float(sel16(v, j)) + nrm;
+                        if (sc <= s.thrp[qi]) {
+                            const int slot = atomicAdd(&s.cnt[qi], 1);
+                            if (slot < C) {
+                                s.cand[(size_t)qi * C + slot] = make_key(sc + s.xn[qi], rowid);
+                            } else {
+                                ndrop |= 1u << j;
+                                fl |= 2;
+                            }
+                            if (slot + 1 >= KP + kRCompactMin)
+                                fl |= 1;
+                        }
+                    }
+                    const uint32_t nword =
+                            (dword & ~(0xffffu << ((ch & 1) * 16))) | (ndrop << ((ch & 1) * 16));
+                    drop[0] = ch < 2 ? nword : drop[0];
+                    drop[1] = (ch >= 2 && ch < 4) ? nword : drop[1];
+                    drop[2] = ch >= 4 ? nword : drop[2];
+                }
+                if (fl)
+                    atomicOr(&s.flag[ep & 3], fl);
+                long long tt1 = tracing ? clock64() : 0;
+                c_scan += tt1 - tt0;
+                named_bar_sync(2, kREpiWarps * 32);
+                const int f = s.flag[ep & 3];
+                if (tid == 0)
+                    s.flag[(ep + 2) & 3] = 0;
+                ++ep;
+                if (round == 0 && myq >= 0 && gthr < s.thr[tid]) {
+                    // another CTA has a better bound for this query
+                    atomicMin(&s.thr[tid], gthr);
+                    const float tp = from_ordered_bits(gthr) - s.xn[tid];
+                    s.thrp[tid] = tp;
+                    s.thrf[tid] = loosen(tp);
+                }
+                if (f == 0) {
+                    c_comp += (tracing ? clock64() : 0) - tt1;
+                    break; // the common case: one barrier per tile
+                }
+                tcr_compact<KP>(s.cand, s.cnt, s.thr, s.thrp, s.thrf, s.xn, s.qid, a.qthr, nqw, warp, lane,
+                                false);
+                named_bar_sync(2, kREpiWarps * 32);
+                c_comp += (tracing ? clock64() : 0) - tt1;
+                if (!(f & 2) || round >= 16) // (8 rounds drain any tile; the cap is a safety net)
+                    break;
+            }
+            // accumulator buffer drained
+            tc_fence_before_sync();
+            __syncwarp();
+            if (lane == 0)
+                mbar_arrive(&s.d_empty[b]);
+            if (tid == 0) {
+                TCR_TRACE(4, t);
+                if (tracing && t < 64) {
+                    a.trace[5 * 64 + t] = n_rounds;
+                    a.trace[6 * 64 + t] = n_events;
+                    a.trace[7 * 64 + t] = c_scan;
+                    a.trace[8 * 64 + t] = c_comp;
+                }
+            }
+        }
+        if (tracing && tid == 0)
+            a.trace[9 * 64 + 5] = w_dfull;
+        // ---- item done: best KP of every query, sorted, to `part` --------------------------------
+        named_bar_sync(2, kREpiWarps * 32);
+        tcr_compact<KP>(s.cand, s.cnt, s.thr, s.thrp, s.thrf, s.xn, s.qid, a.qthr, nqw, warp, lane, true);
+        __syncwarp();
+        for (int qi = warp; qi < nqw; qi += kREpiWarps) {
+            const int n = s.cnt[qi];
+            uint64_t* out = a.part + ((size_t)(q0 + qi) * a.nsplit + split) * KP;
+            const uint64_t* buf = s.cand + (size_t)qi * C;
+            for (int i = lane; i < KP; i += 32)
+                out[i] = i < n ? buf[i] : kSentinelKey;
+        }
+    }
+
+    // ---- teardown -----------------------------------------------------------------------------------
+    tc_fence_before_sync();
+    named_bar_sync(1, kRLoaderWarps * 32);
+    if (warp == kRMmaWarp) {
+        tc_fence_after_sync();
+        tmem_dealloc(tmem, 512);
+    }
+    if (tid == 0)
+        TCR_TRACE(0, 5);
+}
+
+} // namespace
+
+// ---- host side ----------------------------------------------------------------------------------
+template <int METRIC, int KP>
+static cudaError_t launch_tcr_one(uint32_t max_items, const TcScanArgs& a_in, cudaStream_t st) {
+    TcScanArgs a = a_in;
+    const size_t smem = 227 * 1024;
+    a.nstages = (int)(smem / 1024); // the kernel carves per item (tcr_stages)
+    if (tcr_stages(smem, KP, kTcrTQ, 2 * ((a.nf4 + 1) >> 1)) < 3)
+        return cudaErrorInvalidValue;
+    static const int dbg = getenv("B200IVF_TC_DBG") ? atoi(getenv("B200IVF_TC_DBG")) : 0;
+    a.dbg = a.nlists > 1 ? dbg : 0; // timing experiments; never for the coarse quantizer
+    auto kern = ivf_scan_tcr_kernel<METRIC, KP>;
+    cudaError_t e =
+            cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess)
+        return e;
+    if (max_items == 0)
+        return cudaSuccess;
+    static const char* tr = getenv("B200IVF_TC_TRACE");
+    static const char* trc = getenv("B200IVF_TC_TRACE_COARSE");
+    if (tr && (a.nlists > 1) == (trc == nullptr)) {
+        static long long* buf = nullptr;
+        if (!buf)
+            cudaMalloc(&buf, 10 * 64 * sizeof(long long));
+        cudaMemsetAsync(buf, 0, 10 * 64 * sizeof(long long), st);
+        a.trace = buf;
+        a.trace_item = (uint32_t)atoi(tr);
+    }
+    kern<<<max_items, kRThreads, smem, st>>>(a, *reinterpret_cast<const CUtensorMap*>(a.tmap));
+    count_launches(1);
+    g_tc_launches.fetch_add(1, std::memory_order_relaxed);
+    if (a.trace) {
+        long long h[10 * 64];
+        cudaStreamSynchronize(st);
+        cudaMemcpy(h, a.trace, sizeof(h), cudaMemcpyDeviceToHost);
+        const long long t0 = h[0];
+        fprintf(stderr, "TCRTRACE item %u ntiles %lld nq %lld: sync %lld b_rdy %lld end %lld\n",
+                a.trace_item, h[2], h[3], h[1] - t0, h[4] - t0, h[5] - t0);
+        const char* names[5] = {"", "tma", "mma", "split", "epi"};
+        for (int r = 1; r < 5; ++r) {
+            fprintf(stderr, "TCRTRACE %-6s", names[r]);
+            for (int i = 0; i < 24 && i < (int)h[2]; ++i)
+                fprintf(stderr, " %lld", h[r * 64 + i] ? h[r * 64 + i] - t0 : -1);
+            fprintf(stderr, "\n");
+        }
+        fprintf(stderr,
+                "TCRTRACE waits: split full %lld a_empty %lld | mma a_rdy %lld d_empty %lld | tma empty "
+                "%lld | epi d_full %lld | mma issue %lld\n",
+                h[9 * 64 + 0], h[9 * 64 + 1], h[9 * 64 + 2], h[9 * 64 + 3], h[9 * 64 + 4],
+                h[9 * 64 + 5], h[9 * 64 + 6]);
+        const char* cn[4] = {"rounds", "events", "c_scan", "c_comp"};
+        for (int r = 5; r < 9; ++r) {
+            fprintf(stderr, "TCRTRACE %-6s", cn[r - 5]);
+            for (int i = 0; i < 24 && i < (int)h[2]; ++i)
+                fprintf(stderr, " %lld", h[r * 64 + i]);
+            fprintf(stderr, "\n");
+        }
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t launch_ivf_scan_tcr(int metric, uint32_t max_items, const TcScanArgs& a,
+                                cudaStream_t st) {
+    if (a.nf4 > kRMaxChunks || a.nf4 < 1)
+        return cudaErrorInvalidValue;
+    if (a.kpart == 16)
+        return metric == kMetricL2 ? launch_tcr_one<kMetricL2, 16>(max_items, a, st)
+                                   : launch_tcr_one<kMetricInnerProduct, 16>(max_items, a, st);
+    if (a.kpart == 32)
+        return metric == kMetricL2 ? launch_tcr_one<kMetricL2, 32>(max_items, a, st)
+                                   : launch_tcr_one<kMetricInnerProduct, 32>(max_items, a, st);
+    return cudaErrorInvalidValue;
+}
+
+} // namespace b200ivf

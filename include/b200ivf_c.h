@@ -118,6 +118,8 @@ int b200_IndexIVFFlat_set_stream(B200IndexIVFFlat* index, void* cuda_stream);
 
 /* Number of CUDA kernels this library has launched in this process (all handles). */
 unsigned long long b200_kernel_launches(void);
+/* ... of which tensor-core (tcgen05) scan launches; tests use it to prove which path ran */
+unsigned long long b200_tensor_core_launches(void);
 
 /* merge_knn_results (faiss/utils/Heap.cpp:158-232) as used by IndexShardsIVF::search
  * (faiss/IndexShardsIVF.cpp:224-242): all_* are [nshard][n][k] per-shard sorted tables, host or

@@ -109,19 +109,50 @@ __global__ void __launch_bounds__(256, 1)
     __syncthreads();
     tc_fence_after_sync();
 
-    if (warp == 5 && lane == 0 && reps > 0) {
+    if (warp == 5 && reps > 0) {
+        // the whole warp runs the loop, one elected lane issues (see scan_tcr.cu)
         // timing: `reps` passes over the K loop, nmma MMAs (N = nmma_n) per k-step, one commit
-        const int nn = (nmma & 0x100) ? 256 : 128; // bit 8 of nmma: N = 256 (reads past Bhi into Blo)
+        // bit 8 of nmma: N = 256 (reads past Bhi into Blo); bits 16+: N given explicitly
+        const int nn = (nmma >> 16) ? (nmma >> 16) : ((nmma & 0x100) ? 256 : 128);
         const int per = nmma & 0xff;
         const uint32_t idesc = make_idesc_tf32(M, nn);
         const uint32_t bhi = smem_u32(Bhi), blo = smem_u32(Blo);
         const long long t0 = clock64();
+        if (nmma & 0x4000) {
+            // the kernels' issue shape: 12 MMAs of a stage (4 k-steps) straight-line under one elect
+            const uint64_t d0 = make_smem_desc_kmajor_noswz(0, LBO, SBO);
+            for (int r = 0; r < reps; ++r)
+                for (int sg = 0; sg < K / 32; ++sg) {
+                    const uint32_t tDb = tD + ((r & 1) ? 128u : 0u);
+                    const uint64_t dhi = d0 + (uint64_t)((bhi + sg * 8 * LBO) >> 4);
+                    const uint64_t dlo = d0 + (uint64_t)((blo + sg * 8 * LBO) >> 4);
+                    if (elect_one_sync()) {
+#pragma unroll
+                        for (int ks = 0; ks < 4; ++ks) {
+                            const uint64_t kh = dhi + (uint64_t)(ks * ((2 * LBO) >> 4));
+                            const uint64_t kl = dlo + (uint64_t)(ks * ((2 * LBO) >> 4));
+                            mma_tf32_ts(tDb, tAlo + (sg * 4 + ks) * 8, kh, idesc, 1);
+                            mma_tf32_ts(tDb, tAhi + (sg * 4 + ks) * 8, kl, idesc, 1);
+                            mma_tf32_ts(tDb, tAhi + (sg * 4 + ks) * 8, kh, idesc, 1);
+                        }
+                        if (nmma & 0x200) {
+                            mma_commit(&bars[2]);
+                            mma_commit(&bars[3]);
+                        }
+                    }
+                    __syncwarp();
+                }
+        } else
         for (int r = 0; r < reps; ++r)
             for (int ks = 0; ks < K / 8; ++ks) {
                 const uint64_t dhi = make_smem_desc_kmajor_noswz(bhi + ks * 2 * LBO, LBO, SBO);
                 const uint64_t dlo = make_smem_desc_kmajor_noswz(blo + ks * 2 * LBO, LBO, SBO);
+                if (!elect_one_sync())
+                    continue;
                 if (nmma & 0x400) { // the real kernel's operand order, alternating D buffers
-                    const uint32_t tDb = tD + ((r & 1) ? 128u : 0u);
+                    // 0x2000: alternate the accumulator every k-step (two dependency chains)
+                    const uint32_t tDb =
+                            tD + ((((nmma & 0x2000) ? ks : r) & 1) ? 128u : 0u);
                     mma_tf32_ts(tDb, tAlo + ks * 8, dhi, idesc, 1);
                     mma_tf32_ts(tDb, tAhi + ks * 8, dlo, idesc, 1);
                     mma_tf32_ts(tDb, tAhi + ks * 8, dhi, idesc, 1);
@@ -139,12 +170,17 @@ __global__ void __launch_bounds__(256, 1)
                     mma_commit(&bars[3]);
                 }
             }
+        __syncwarp();
         const long long t1 = clock64();
-        mma_commit(&bars[1]);
+        if (elect_one_sync())
+            mma_commit(&bars[1]);
+        __syncwarp();
         mbar_wait(&bars[1], 0);
         const long long t2 = clock64();
-        cycles[2 * blockIdx.x + 0] = t1 - t0;
-        cycles[2 * blockIdx.x + 1] = t2 - t0;
+        if (lane == 0) {
+            cycles[2 * blockIdx.x + 0] = t1 - t0;
+            cycles[2 * blockIdx.x + 1] = t2 - t0;
+        }
     } else if (warp == 5 && lane == 0) {
         const uint32_t idesc = make_idesc_tf32(M, N);
         const uint32_t bhi = smem_u32(Bhi), blo = smem_u32(Blo);
@@ -277,7 +313,10 @@ int main() {
     long long* dC;
     CK(cudaMalloc(&dC, 16 * 148));
     for (int grid : {1, 148})
-        for (int nm : {3, 0x403, 0x603, 0xc03, 0x1603}) {
+        for (int nm : {3, 0x403, 0x603, (128 << 16) | 0x403, (96 << 16) | 0x403, (48 << 16) | 0x403,
+                       (16 << 16) | 0x403, (96 << 16) | 0x2403, (48 << 16) | 0x2403,
+                       (16 << 16) | 0x2403, (128 << 16) | 0x4603, (96 << 16) | 0x4603, (64 << 16) | 0x4603, (48 << 16) | 0x4603,
+                       (32 << 16) | 0x4603, (16 << 16) | 0x4603}) {
             const int reps = 64;
             probe_kernel<<<grid, 256, smem_bytes>>>(dA, tmap, dD, 3, reps, nm, dC);
             CK(cudaGetLastError());
@@ -290,9 +329,9 @@ int main() {
                 mn = std::min(mn, hc[2 * b + 1]);
                 mx = std::max(mx, hc[2 * b + 1]);
             }
-            printf("timing grid %d, flags 0x%x, %d MMA/k-step%s: %d MMAs, issue %lld cyc, complete min %lld max %lld "
+            printf("timing grid %d, flags 0x%x (N %d), %d MMA/k-step%s: %d MMAs, issue %lld cyc, complete min %lld max %lld "
                    "-> %.1f .. %.1f cyc/MMA\n",
-                   grid, nm, nm & 0xff, (nm & 0x200) ? " + 2 commits per 12" : "", nmma, hc[0], mn, mx,
+                   grid, nm & 0xffff, (nm >> 16) ? (nm >> 16) : 128, nm & 0xff, (nm & 0x200) ? " + 2 commits per 12" : "", nmma, hc[0], mn, mx,
                    (double)mn / nmma, (double)mx / nmma);
         }
     return 0;
