@@ -48,7 +48,7 @@ WORKLOADS = {
     # BASELINE.json configs[1]
     "C2": dict(desc="IVFFlat nlist=4096 IP, synthetic 10Mx128 fp32, 10k-query batch", d=128,
                nb=10_000_000, nlist=4096, metric=METRIC_IP, nq=10_000, k=10, normalize=True,
-               nprobes=[1, 2, 4, 8, 16, 32, 64, 128]),
+               nprobes=[1, 2, 4, 8, 12, 16, 20, 24, 28, 32, 48, 64, 96, 128]),
     # BASELINE.json configs[0] (the reference's own CPU-runnable case)
     "C1": dict(desc="IVFFlat nlist=1024 nprobe=16 L2, synthetic 1Mx128 fp32, 10k queries", d=128,
                nb=1_000_000, nlist=1024, metric=METRIC_L2, nq=10_000, k=10, normalize=False,

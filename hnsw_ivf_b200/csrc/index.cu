@@ -387,14 +387,17 @@ void IndexIVFFlatB200::run_coarse_(const float* xd, int64_t n, int kc, int32_t* 
                                    int64_t* out_ids64, float* out_dis, cudaStream_t st) const {
     Impl& m = *impl_;
     const int nf4 = m.nf4;
-    const int kp_tc = scan_tc_kpart(nf4, kc);
-    const bool tc = m.use_tc && n > 32 && kp_tc > 0;
-    const int kp = tc ? kp_tc : kc;
+    const int kp_q = scan_tc_kpart(nf4, kc);   // queries-major kernel: d <= 128
+    const int kp_r = scan_tcr_kpart(nf4, kc);  // rows-major kernel: d <= 1024
+    const bool tc = m.use_tc && n > 32 && (kp_q > 0 || kp_r > 0);
+    // full 128-query tiles: the queries-major kernel where it exists
+    const bool tcr = tc && (kp_q == 0 || (m.tc_mode == 2 && kp_r > 0));
+    const int kp = tc ? (tcr ? kp_r : kp_q) : kc;
+    const int tcr_tq = tcr ? scan_tcr_tq(nf4, kp) : 0;
     const TileCfg tcfg = choose_tile_cfg(nf4, kp);
     const ScanCfg cfg = choose_scan_cfg(nf4, kp);
     const bool tiled = !tc && tcfg.ok && n > kTileMinQueries;
-    const bool tcr = tc && m.tc_mode == 2; // full 128-query tiles: the queries-major kernel
-    const int64_t tq = tcr ? kTcrTQ : tc ? kTcTQ : (tiled ? tcfg.tq : cfg.rq);
+    const int64_t tq = tcr ? tcr_tq : tc ? kTcTQ : (tiled ? tcfg.tq : cfg.rq);
     const int64_t ngroups = ceil_div(n, tq);
     const int64_t nblk = ceil_div((int64_t)nlist, kBlockRows);
     const int64_t rows_step = tc ? 4 : (tiled ? 16 : kScanRowsPerStep); // 32-row blocks per step
@@ -430,6 +433,7 @@ void IndexIVFFlatB200::run_coarse_(const float* xd, int64_t n, int kc, int32_t* 
         m.qthr.reserve((size_t)n * sizeof(uint32_t));
         CUDA_CHECK(launch_fill_u32(m.qthr.as<uint32_t>(), n, ordered_bits(kNeutralScore), st));
         a.qthr = m.qthr.as<uint32_t>();
+        a.tq = tcr_tq;
         if (tcr)
             CUDA_CHECK(launch_ivf_scan_tcr(metric_type, (uint32_t)(ngroups * S), a, st));
         else
@@ -543,20 +547,23 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
     const int64_t nlists_owned = (int64_t)(m.list_hi - m.list_lo);
 
     // tensor-core scan for the lists probed by many queries (d <= 128, moderate k)
-    const int kp_tc = scan_tc_kpart(m.nf4, (int)std::min<int64_t>(k, 1 << 20));
-    const bool tc = m.use_tc && kp_tc > 0;
-    const int64_t kp = tc ? kp_tc : k; // entries per partial list
+    const int kp_q = scan_tc_kpart(m.nf4, (int)std::min<int64_t>(k, 1 << 20));  // d <= 128
+    const int kp_r = scan_tcr_kpart(m.nf4, (int)std::min<int64_t>(k, 1 << 20)); // d <= 1024
+    const bool tc = m.use_tc && (kp_q > 0 || kp_r > 0);
 
     // batch size: bound the partial-candidate scratch
     int64_t nb = std::min<int64_t>(n, 32768);
-    BatchPlan bp = plan_batch(m.nf4, kp, nb, np, nlists_owned, m.nstored);
     // queries per probed list, on average: few -> rows-major kernel (its MMA time follows the
     // query count and it streams a list at any count), many -> queries-major (128-query tiles)
     const double avg_q = (double)std::min<int64_t>(n, 32768) * np /
             (double)std::max<int64_t>(1, std::min<int64_t>(nlists_owned, std::min<int64_t>(n, 32768) * np));
-    const bool tcr = tc && (m.tc_mode == 2 || (m.tc_mode == 0 && avg_q < kTcrMaxAvgQueries));
+    const bool tcr = tc && (kp_q == 0 || (kp_r > 0 && (m.tc_mode == 2 || (m.tc_mode == 0 &&
+                                                                          avg_q < kTcrMaxAvgQueries))));
+    const int64_t kp = tc ? (tcr ? kp_r : kp_q) : k; // entries per partial list
+    const int tcr_tq = tcr ? scan_tcr_tq(m.nf4, (int)kp) : 0;
+    BatchPlan bp = plan_batch(m.nf4, kp, nb, np, nlists_owned, m.nstored);
     const int pmul = (tc && !tcr) ? 2 : 1; // partial lists per (pair, split)
-    const int tc_tq = tcr ? kTcrTQ : kTcTQ;
+    const int tc_tq = tcr ? tcr_tq : kTcTQ;
     const int tc_min = tcr ? 0 : kTileMinQueries; // lists with more queries than this: tensor cores
     while (nb > 1 && (size_t)nb * np * bp.S * pmul * kp * sizeof(uint64_t) > ((size_t)2 << 30)) {
         nb = (nb + 1) / 2;
@@ -687,6 +694,7 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
             CUDA_CHECK(launch_fill_u32(m.qthr.as<uint32_t>(), ni, ordered_bits(kNeutralScore), st));
             ta.qthr = m.qthr.as<uint32_t>();
             ta.item_list = m.item_list.as<int32_t>();
+            ta.tq = tcr_tq;
             if (tcr)
                 CUDA_CHECK(launch_ivf_scan_tcr(metric_type, (uint32_t)max_tc_items, ta, st));
             else

@@ -91,6 +91,7 @@ struct TcScanArgs {
     int d;
     int nf4;                    // <= 32
     int nstages;                // TMA ring depth (kTcStages)
+    int tq = 0;                 // rows-major kernel only: queries per item (scan_tcr_tq)
     const float* queries;
     uint64_t* part;             // [npairs][nsplit][2][kpart]: one list per epilogue group
     // [n] per-query pruning bound shared by all the work items of a search: ordered_bits() of the
@@ -115,6 +116,10 @@ cudaError_t launch_ivf_scan_tc(int metric, uint32_t max_items, const TcScanArgs&
 // ---- rows-major tensor-core scan (scan_tcr.cu): same arguments, <= kTcrTQ queries per item, ONE
 // sorted list of kpart keys per (pair, split); nstages is chosen by the launcher --------------------
 constexpr int kTcrTQ = 96;
+// d up to 1024; the queries per item shrink with the dimension (the query tile lives in shared
+// memory): scan_tcr_tq(nf4, kpart), 0 = unsupported. scan_tcr_kpart: as scan_tc_kpart.
+int scan_tcr_tq(int nf4, int kp);
+int scan_tcr_kpart(int nf4, int k);
 cudaError_t launch_ivf_scan_tcr(int metric, uint32_t max_items, const TcScanArgs& a,
                                 cudaStream_t st);
 

@@ -60,7 +60,7 @@ constexpr int kRMaxStages = 12;   // raw ring (as deep as the item's query tile 
 constexpr int kRAStages = 4;      // operand ring in tensor memory
 constexpr uint32_t kRColsD = 0;   // two accumulator buffers of 128 columns
 constexpr uint32_t kRColsA = 256; // kRAStages x (32 hi + 32 lo) columns
-constexpr int kRMaxChunks = 32;   // float4 columns of a query (d <= 128)
+constexpr int kRMaxChunks = 256;  // float4 columns of a query (d <= 1024)
 constexpr uint32_t kRBSBO = 128;
 constexpr int kRFree = 16;        // free candidate entries beyond the KP kept
 constexpr int kRCompactMin = 8;   // compact a buffer once it holds this many new candidates
@@ -299,7 +299,7 @@ __global__ void __launch_bounds__(kRThreads, 1)
     const int l = lo_l;
     const int g0 = a.grp_start[l];
     const int cnt_l = a.grp_start[l + 1] - g0;
-    const int nsub = (cnt_l + kTcrTQ - 1) / kTcrTQ;
+    const int nsub = (cnt_l + a.tq - 1) / a.tq;
     const uint32_t local = item - a.item_off[l];
     const int split = (int)(local / (uint32_t)nsub);
     const int sub = (int)(local % (uint32_t)nsub);
@@ -389,46 +389,47 @@ __global__ void __launch_bounds__(kRThreads, 1)
         return; // takes no part in the named barriers below
     }
 
-    // ---- prologue: the query tile -> shared memory (B operand), 13 warps --------------------------
+    // ---- prologue: the query tile -> shared memory (B operand), 17 warps -----------------------
     {
         const int wl = warp < kRTmaWarp ? warp : warp - 1;
         const float scale = METRIC == kMetricL2 ? -2.f : -1.f;
         const bool vec = (a.d & 3) == 0 && (reinterpret_cast<uintptr_t>(a.queries) & 15) == 0;
         const int nch = 2 * nks; // chunks the MMAs read (the last one may be padding)
-        constexpr int kPer = (kTcrTQ + kRLoaderWarps - 1) / kRLoaderWarps; // 8
-        float4 xv[kPer];
+        constexpr int kPer = (kTcrTQ + kRLoaderWarps - 1) / kRLoaderWarps; // 6
         int qn[kPer];
+        float nn[kPer];
 #pragma unroll
         for (int u = 0; u < kPer; ++u) {
             const int n = wl + u * kRLoaderWarps;
             qn[u] = n < nqw ? (a.pair_query ? a.pair_query[q0 + n] : q0 + n) : -1;
+            nn[u] = 0.f;
         }
+        // lane = chunk (float4 column) of the query row: one coalesced 512-byte read per 32 chunks
+        for (int cb = 0; cb < nch; cb += 32) {
+            const int c = cb + lane;
+            float4 xv[kPer];
 #pragma unroll
-        for (int u = 0; u < kPer; ++u) {
-            xv[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (qn[u] >= 0 && lane < nf4) {
-                const float* src = a.queries + (size_t)qn[u] * a.d;
-                const int dd = 4 * lane;
-                if (vec) {
-                    xv[u] = __ldg(reinterpret_cast<const float4*>(src + dd));
-                } else {
-                    xv[u].x = __ldg(src + dd);
-                    xv[u].y = dd + 1 < a.d ? __ldg(src + dd + 1) : 0.f;
-                    xv[u].z = dd + 2 < a.d ? __ldg(src + dd + 2) : 0.f;
-                    xv[u].w = dd + 3 < a.d ? __ldg(src + dd + 3) : 0.f;
+            for (int u = 0; u < kPer; ++u) {
+                xv[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (qn[u] >= 0 && c < nf4) {
+                    const float* src = a.queries + (size_t)qn[u] * a.d;
+                    const int dd = 4 * c;
+                    if (vec) {
+                        xv[u] = __ldg(reinterpret_cast<const float4*>(src + dd));
+                    } else {
+                        xv[u].x = __ldg(src + dd);
+                        xv[u].y = dd + 1 < a.d ? __ldg(src + dd + 1) : 0.f;
+                        xv[u].z = dd + 2 < a.d ? __ldg(src + dd + 2) : 0.f;
+                        xv[u].w = dd + 3 < a.d ? __ldg(src + dd + 3) : 0.f;
+                    }
                 }
             }
-        }
 #pragma unroll
-        for (int u = 0; u < kPer; ++u) {
-            const int n = wl + u * kRLoaderWarps;
-            if (n < n16) {
-                const float4 x = xv[u];
-                float nn = x.x * x.x + x.y * x.y + x.z * x.z + x.w * x.w;
-#pragma unroll
-                for (int o = 16; o > 0; o >>= 1)
-                    nn += __shfl_xor_sync(0xffffffffu, nn, o);
-                if (lane < nch) {
+            for (int u = 0; u < kPer; ++u) {
+                const int n = wl + u * kRLoaderWarps;
+                if (n < n16 && c < nch) {
+                    const float4 x = xv[u];
+                    nn[u] += x.x * x.x + x.y * x.y + x.z * x.z + x.w * x.w;
                     float4 h, lo;
                     h.x = x.x * scale;
                     h.y = x.y * scale;
@@ -438,13 +439,23 @@ __global__ void __launch_bounds__(kRThreads, 1)
                     lo.y = tf32_lo(h.y);
                     lo.z = tf32_lo(h.z);
                     lo.w = tf32_lo(h.w);
-                    const size_t off = (size_t)lane * lbo + (size_t)n * 16;
+                    const size_t off = (size_t)c * lbo + (size_t)n * 16;
                     *reinterpret_cast<float4*>(s.bhi + off) = h;
                     *reinterpret_cast<float4*>(s.blo + off) = lo;
                 }
-                if (lane == 0 && n < kTcrTQ) {
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < kPer; ++u) {
+            const int n = wl + u * kRLoaderWarps;
+            if (n < n16) { // (warp-uniform)
+                float v = nn[u];
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1)
+                    v += __shfl_xor_sync(0xffffffffu, v, o);
+                if (lane == 0) {
                     const int q = qn[u];
-                    const float xnq = (METRIC == kMetricL2 && q >= 0) ? nn : 0.f;
+                    const float xnq = (METRIC == kMetricL2 && q >= 0) ? v : 0.f;
                     uint32_t tb = ordered_bits(kNeutralScore);
                     if (q >= 0 && a.qthr)
                         tb = min(tb, a.qthr[q]);
@@ -764,7 +775,8 @@ static cudaError_t launch_tcr_one(uint32_t max_items, const TcScanArgs& a_in, cu
     TcScanArgs a = a_in;
     const size_t smem = 227 * 1024;
     a.nstages = (int)(smem / 1024); // the kernel carves per item (tcr_stages)
-    if (tcr_stages(smem, KP, kTcrTQ, 2 * ((a.nf4 + 1) >> 1)) < 3)
+    if (a.tq < 16 || a.tq > kTcrTQ || (a.tq & 15) ||
+        tcr_stages(smem, KP, a.tq, 2 * ((a.nf4 + 1) >> 1)) < 3)
         return cudaErrorInvalidValue;
     static const int dbg = getenv("B200IVF_TC_DBG") ? atoi(getenv("B200IVF_TC_DBG")) : 0;
     a.dbg = a.nlists > 1 ? dbg : 0; // timing experiments; never for the coarse quantizer
@@ -816,6 +828,22 @@ static cudaError_t launch_tcr_one(uint32_t max_items, const TcScanArgs& a_in, cu
         }
     }
     return cudaGetLastError();
+}
+
+// queries per item for dimension nf4*4 and kp kept keys: the largest multiple of 16 (<= kTcrTQ) that
+// leaves the raw ring at least 4 stages; 0 = the kernel cannot take this shape
+int scan_tcr_tq(int nf4, int kp) {
+    if (nf4 < 1 || nf4 > kRMaxChunks || (kp != 16 && kp != 32))
+        return 0;
+    const int nch = 2 * ((nf4 + 1) >> 1);
+    for (int tq = kTcrTQ; tq >= 16; tq -= 16)
+        if (tcr_stages(227 * 1024, kp, tq, nch) >= 4)
+            return tq;
+    return 0;
+}
+int scan_tcr_kpart(int nf4, int k) {
+    const int kp = k + 4 <= 16 ? 16 : (k <= 32 ? 32 : 0);
+    return kp && scan_tcr_tq(nf4, kp) ? kp : 0;
 }
 
 cudaError_t launch_ivf_scan_tcr(int metric, uint32_t max_items, const TcScanArgs& a,

@@ -56,6 +56,10 @@ def _pair(d, nb, nlist, metric, seed=1):
     (20, 20000, 16, 4, 1, 600),      # one TMA stage per tile, k = 1
     (64, 30000, 48, 12, 32, 900),    # largest k the tensor-core path takes
     (128, 3000, 64, 64, 10, 400),    # short lists (under one 128-row tile), nprobe = nlist
+    (128, 60000, 512, 4, 10, 300),   # ~2 queries per list: rows-major kernel, N = 16 tiles
+    (960, 12000, 32, 8, 10, 500),    # GIST-shaped rows (C3): rows-major kernel, 16 queries per item
+    (200, 20000, 32, 8, 10, 700),    # d > 128 with an odd number of float4 columns (50)
+    (260, 9000, 16, 4, 20, 300),     # d > 128, KP = 32
 ])
 def test_tc_equals_simt_and_oracle(cuda_device, metric, d, nb, nlist, nprobe, k, nq):
     import hnsw_ivf_b200 as b2
