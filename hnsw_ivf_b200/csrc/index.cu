@@ -9,8 +9,10 @@
 #include "kernels.h"
 
 #include <algorithm>
+#include <array>
 #include <cstdlib>
 #include <cstring>
+#include <map>
 
 namespace b200ivf {
 
@@ -33,9 +35,14 @@ std::atomic<unsigned long long> g_tc_launches{0};
             throw B200Exception(std::string("Error: '") + #cond + "' failed: " + (msg));   \
     } while (0)
 
+// bumped whenever any scratch buffer moves: a captured search graph holds raw pointers, so a graph
+// is only replayed while the generation it was captured under is still current
+static std::atomic<unsigned long long> g_alloc_gen{0};
+
 void Buffer::reserve(size_t n) {
     if (n <= bytes)
         return;
+    g_alloc_gen.fetch_add(1, std::memory_order_relaxed);
     release();
     size_t want = std::max(n, bytes + bytes / 2);
     if (pinned_host)
@@ -90,14 +97,17 @@ constexpr int kScanRowsPerStep = 4; // RV of the scan kernel
 
 struct ScanCfg {
     int rq, wpc, cap;
+    int rv = 4; // 32-row blocks per warp step
 };
 
-ScanCfg choose_scan_cfg(int nf4, int k) {
+// max_rq: queries per warp the caller can use (a warp computes all RQ accumulators whether or
+// not the list has that many queries, so RQ follows how many queries meet in a list)
+ScanCfg choose_scan_cfg(int nf4, int k, int max_rq = 8) {
     const int cap = pow2_ceil(k + 32);
     // preference order: many queries per warp first, then many warps per CTA
     const int pref[9][2] = {{8, 4}, {4, 4}, {8, 2}, {4, 2}, {8, 1}, {4, 1}, {1, 4}, {1, 2}, {1, 1}};
     for (const auto& p : pref)
-        if (scan_smem_bytes(p[0], p[1], nf4, cap) <= kScanSmemBudget)
+        if (p[0] <= max_rq && scan_smem_bytes(p[0], p[1], nf4, cap) <= kScanSmemBudget)
             return {p[0], p[1], cap};
     if (scan_smem_bytes(1, 1, nf4, cap) <= 227 * 1024 - 1024)
         return {1, 1, cap};
@@ -173,11 +183,35 @@ struct IndexIVFFlatB200::Impl {
     double last_ms[5] = {0, 0, 0, 0, 0};
     IndexIVFStatsB200 stats;
 
+    // small-batch searches are launch-bound (a dozen short kernels): the whole pipeline of one
+    // (batch size, nprobe, k) shape is captured into a CUDA graph the second time the shape is
+    // seen and replayed with one launch afterwards. B200IVF_NO_GRAPH=1 turns this off.
+    struct GraphEntry {
+        unsigned long long gen = 0; // g_alloc_gen at capture (exec == nullptr: shape seen once)
+        cudaGraphExec_t exec = nullptr;
+    };
+    std::map<std::array<int64_t, 4>, GraphEntry> graphs;
+    bool use_graph = true;
+    // average queries per probed list at or below which the SIMT warp kernel takes the whole scan
+    // (B200IVF_SIMT_MAXQ, A/B runs)
+    double simt_max_avg_q = 1.5;
+    unsigned long long graph_replays = 0;
+    void drop_graphs() {
+        for (auto& kv : graphs)
+            if (kv.second.exec)
+                cudaGraphExecDestroy(kv.second.exec);
+        graphs.clear();
+    }
+
     Impl() {
         const char* e = getenv("B200IVF_NO_TC");
         use_tc = !(e && e[0] == '1');
         const char* e2 = getenv("B200IVF_TC_MODE");
         tc_mode = e2 ? atoi(e2) : 0;
+        const char* e3 = getenv("B200IVF_NO_GRAPH");
+        use_graph = !(e3 && e3[0] == '1');
+        if (const char* e4 = getenv("B200IVF_SIMT_MAXQ"))
+            simt_max_avg_q = atof(e4);
         stage_x.pinned_host = stage_D.pinned_host = stage_I.pinned_host = true;
         stage_assign.pinned_host = host_stats.pinned_host = true;
     }
@@ -504,16 +538,28 @@ struct BatchPlan {
 };
 
 static BatchPlan plan_batch(int nf4, int64_t kpart, int64_t nb, int64_t nprobe,
-                            int64_t nlists_owned, int64_t nstored) {
+                            int64_t nlists_owned, int64_t nstored, bool simt_only = false) {
     BatchPlan bp;
-    bp.cfg = choose_scan_cfg(nf4, (int)kpart);
     const int64_t pairs = nb * nprobe;
+    // queries that meet in a probed list, on average (uniform-probe estimate)
+    const double avg_q =
+            (double)pairs / (double)std::max<int64_t>(1, std::min<int64_t>(nlists_owned, pairs));
+    // when the warp kernel is the whole scan, its queries-per-warp follows the regime: a warp
+    // pays for RQ accumulators per row whether the list has RQ queries or one
+    const int max_rq = !simt_only ? 8 : (avg_q <= 1.5 ? 1 : (avg_q <= 4.0 ? 4 : 8));
+    bp.cfg = choose_scan_cfg(nf4, (int)kpart, max_rq);
     const int64_t items_est =
             std::max<int64_t>(1, std::max(ceil_div(pairs, bp.cfg.rq), std::min(pairs, nlists_owned)));
     const int64_t avg_blocks =
             std::max<int64_t>(1, nstored / std::max<int64_t>(1, nlists_owned) / kBlockRows);
     int64_t S = ceil_div(kTargetScanItems, items_est);
-    S = std::max<int64_t>(1, std::min(S, std::max<int64_t>(1, avg_blocks / kScanRowsPerStep)));
+    // few pairs (small batches): split down to single blocks so that the whole GPU streams
+    if (simt_only && bp.cfg.rq == 1 && S > avg_blocks / kScanRowsPerStep) {
+        bp.cfg.rv = 1;
+        S = std::max<int64_t>(1, std::min(S, avg_blocks));
+    } else {
+        S = std::max<int64_t>(1, std::min(S, std::max<int64_t>(1, avg_blocks / kScanRowsPerStep)));
+    }
     bp.S = std::min<int64_t>(S, 32);
     return bp;
 }
@@ -549,25 +595,27 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
     // tensor-core scan for the lists probed by many queries (d <= 128, moderate k)
     const int kp_q = scan_tc_kpart(m.nf4, (int)std::min<int64_t>(k, 1 << 20));  // d <= 128
     const int kp_r = scan_tcr_kpart(m.nf4, (int)std::min<int64_t>(k, 1 << 20)); // d <= 1024
-    const bool tc = m.use_tc && (kp_q > 0 || kp_r > 0);
-
     // batch size: bound the partial-candidate scratch
     int64_t nb = std::min<int64_t>(n, 32768);
     // queries per probed list, on average: few -> rows-major kernel (its MMA time follows the
     // query count and it streams a list at any count), many -> queries-major (128-query tiles)
     const double avg_q = (double)std::min<int64_t>(n, 32768) * np /
             (double)std::max<int64_t>(1, std::min<int64_t>(nlists_owned, std::min<int64_t>(n, 32768) * np));
+    // hardly any list shared between queries (small batches, huge nlist): nothing to multiply, the
+    // scan is a pure stream -> the SIMT warp kernel alone (exact fp32, no re-rank needed)
+    const bool simt_only = !m.use_tc || avg_q <= m.simt_max_avg_q || (kp_q == 0 && kp_r == 0);
+    const bool tc = !simt_only;
     const bool tcr = tc && (kp_q == 0 || (kp_r > 0 && (m.tc_mode == 2 || (m.tc_mode == 0 &&
                                                                           avg_q < kTcrMaxAvgQueries))));
     const int64_t kp = tc ? (tcr ? kp_r : kp_q) : k; // entries per partial list
     const int tcr_tq = tcr ? scan_tcr_tq(m.nf4, (int)kp) : 0;
-    BatchPlan bp = plan_batch(m.nf4, kp, nb, np, nlists_owned, m.nstored);
+    BatchPlan bp = plan_batch(m.nf4, kp, nb, np, nlists_owned, m.nstored, simt_only);
     const int pmul = (tc && !tcr) ? 2 : 1; // partial lists per (pair, split)
     const int tc_tq = tcr ? tcr_tq : kTcTQ;
     const int tc_min = tcr ? 0 : kTileMinQueries; // lists with more queries than this: tensor cores
     while (nb > 1 && (size_t)nb * np * bp.S * pmul * kp * sizeof(uint64_t) > ((size_t)2 << 30)) {
         nb = (nb + 1) / 2;
-        bp = plan_batch(m.nf4, kp, nb, np, nlists_owned, m.nstored);
+        bp = plan_batch(m.nf4, kp, nb, np, nlists_owned, m.nstored, simt_only);
     }
     cudaStream_t st = m.stream;
     unsigned long long* dstats = m.dev_stats.as<unsigned long long>();
@@ -575,7 +623,7 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
     for (int64_t i0 = 0; i0 < n; i0 += nb) {
         const int64_t ni = std::min(nb, n - i0);
         const int64_t pairs = ni * np;
-        bp = plan_batch(m.nf4, kp, ni, np, nlists_owned, m.nstored);
+        bp = plan_batch(m.nf4, kp, ni, np, nlists_owned, m.nstored, simt_only);
         CUDA_CHECK(cudaEventRecord(m.ev[0], st));
         // queries
         const float* xd = x + i0 * d;
@@ -671,7 +719,7 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
                 (ceil_div(pairs, bp.cfg.rq) + std::min<int64_t>(pairs, (int64_t)nlist)) * bp.S;
         if (!tcr) // (every probed list goes to the rows-major tensor-core kernel otherwise)
             CUDA_CHECK(launch_ivf_scan(metric_type, bp.cfg.rq, bp.cfg.wpc, (uint32_t)max_items, sa,
-                                       st));
+                                       st, bp.cfg.rv));
         if (tc) {
             // lists probed by more than kTileMinQueries queries of this batch: tensor cores
             TcScanArgs ta;

@@ -41,8 +41,10 @@ struct ScanArgs {
 
 // rq in {1,4,8}; warps_per_cta chosen by the caller so that shared memory fits.
 size_t scan_smem_bytes(int rq, int warps_per_cta, int nf4, int cap);
+// rv: 32-row blocks per warp step, 4 (streaming) or 1 (rq == 1 only: one block per step with a
+// deeper unroll, for row splits of a single block in the latency-bound small-batch regime)
 cudaError_t launch_ivf_scan(int metric, int rq, int warps_per_cta, uint32_t max_items,
-                            const ScanArgs& a, cudaStream_t st);
+                            const ScanArgs& a, cudaStream_t st, int rv = 4);
 
 // ---- K2 for lists probed by many queries: CTA-tiled scan (scan_tile.cu) ------------------------
 // One CTA per work item (list, tile of <= kTileTQ queries probing it, row split).

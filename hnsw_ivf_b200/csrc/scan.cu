@@ -146,7 +146,9 @@ __global__ void __launch_bounds__(256) ivf_scan_kernel(const ScanArgs a) {
             for (int j = 0; j < RQ; ++j)
                 acc[v][j] = 0.f;
         }
-#pragma unroll 4
+        // loads in flight per lane = RV x unroll: 16 either way (a lone block per step, the
+        // latency-bound small-batch shape, gets the deeper unroll)
+#pragma unroll(RV == 1 ? 16 : 4)
         for (int c = 0; c < nf4; ++c) {
             float4 y[RV];
 #pragma unroll
@@ -225,10 +227,12 @@ size_t scan_smem_bytes(int rq, int warps_per_cta, int nf4, int cap) {
 }
 
 cudaError_t launch_ivf_scan(int metric, int rq, int wpc, uint32_t max_items, const ScanArgs& a,
-                            cudaStream_t st) {
+                            cudaStream_t st, int rv) {
 #define B200IVF_DISPATCH(M)                                    \
     switch (rq) {                                              \
         case 1:                                                \
+            if (rv == 1)                                       \
+                return launch_one<M, 1, 1>(wpc, max_items, a, st); \
             return launch_one<M, 1, 4>(wpc, max_items, a, st); \
         case 4:                                                \
             return launch_one<M, 4, 4>(wpc, max_items, a, st); \
