@@ -93,6 +93,7 @@ def torch_assign(torch, x, cent, metric, chunk=1 << 18):
     """top-1 centroid with library GEMMs (setup only: training + the reference arm's list build)"""
     out = torch.empty((x.shape[0],), dtype=torch.int64, device=x.device)
     cn = (cent * cent).sum(1)
+    chunk = max(1024, min(chunk, (1 << 31) // (4 * cent.shape[0])))  # score tiles of <= 2 GB
     for i0 in range(0, x.shape[0], chunk):
         xi = x[i0:i0 + chunk]
         ip = xi @ cent.T

@@ -19,11 +19,13 @@ from .binding import (  # noqa: F401
     library_path,
     load_library,
     merge_knn_results,
+    read_index,
+    write_index,
 )
 from .sharded import IndexShardsIVFFlat, list_range_of_rank  # noqa: F401
 
 __all__ = [
     "METRIC_INNER_PRODUCT", "METRIC_L2", "B200Error", "IndexIVFFlat", "IndexIVFStats",
-    "IndexShardsIVFFlat", "build_library", "kernel_launches", "tensor_core_launches", "library_path", "load_library", "merge_knn_results",
+    "IndexShardsIVFFlat", "build_library", "kernel_launches", "tensor_core_launches", "library_path", "load_library", "merge_knn_results", "read_index", "write_index",
     "list_range_of_rank",
 ]

@@ -76,6 +76,8 @@ SYMBOLS = [
     ("b200_tensor_core_launches", C.c_ulonglong, []),
     ("b200_merge_knn_results", C.c_int,
      [C.c_int, C.c_int, C.c_int64, C.c_int64, _f32p, _i64p, _f32p, _i64p, C.c_int, _vp]),
+    ("b200_write_index_fname", C.c_int, [_vp, C.c_char_p]),
+    ("b200_read_index_fname", C.c_int, [C.c_char_p, C.c_int, C.c_int, C.POINTER(_vp)]),
 ]
 
 
@@ -139,12 +141,15 @@ class IndexIVFFlat:
     (SURVEY.md 8f): centroids trained elsewhere are installed with ``set_centroids``.
     """
 
-    def __init__(self, d, nlist, metric=METRIC_L2, device=0):
+    def __init__(self, d, nlist, metric=METRIC_L2, device=0, _handle=None):
         self._lib = load_library()
         h = _vp()
         self._h = None
-        self._check(self._lib.b200_IndexIVFFlat_new_with_metric(C.byref(h), d, nlist, metric,
-                                                                device))
+        if _handle is not None:
+            h = _handle
+        else:
+            self._check(self._lib.b200_IndexIVFFlat_new_with_metric(C.byref(h), d, nlist, metric,
+                                                                    device))
         self._h = h
         self.device = device
 
@@ -282,6 +287,22 @@ class IndexIVFFlat:
         elif cuda_stream_ptr == 0:
             cuda_stream_ptr = 1  # cudaStreamLegacy
         self._check(self._lib.b200_IndexIVFFlat_set_stream(self._h, cuda_stream_ptr))
+
+
+def read_index(fname, io_flags=0, device=0):
+    """faiss.read_index for an IndexIVFFlat file written by the reference (or by write_index):
+    the lists go straight into HBM on `device` (faiss/impl/index_read.cpp:782-787)."""
+    lib = load_library()
+    h = _vp()
+    rc = lib.b200_read_index_fname(os.fsencode(fname), io_flags, device, C.byref(h))
+    if rc != 0:
+        raise B200Error(rc, lib.b200_get_last_error().decode())
+    return IndexIVFFlat(0, 0, device=device, _handle=h)
+
+
+def write_index(index, fname):
+    """faiss.write_index in the reference's own format (faiss/impl/index_write.cpp:635-638)."""
+    index._check(index._lib.b200_write_index_fname(index._h, os.fsencode(fname)))
 
 
 def tensor_core_launches():

@@ -176,4 +176,16 @@ int b200_merge_knn_results(B200MetricType metric, int nshard, b200_idx_t n, b200
     });
 }
 
+int b200_write_index_fname(const B200IndexIVFFlat* index, const char* fname) {
+    return guarded([&] { b200ivf::write_index(H(index), fname); });
+}
+
+int b200_read_index_fname(const char* fname, int io_flags, int device, B200IndexIVFFlat** p_out) {
+    return guarded([&] {
+        if (!p_out)
+            throw b200ivf::B200Exception("null output handle");
+        *p_out = reinterpret_cast<B200IndexIVFFlat*>(b200ivf::read_index(fname, io_flags, device));
+    });
+}
+
 } // extern "C"

@@ -35,14 +35,9 @@ std::atomic<unsigned long long> g_tc_launches{0};
             throw B200Exception(std::string("Error: '") + #cond + "' failed: " + (msg));   \
     } while (0)
 
-// bumped whenever any scratch buffer moves: a captured search graph holds raw pointers, so a graph
-// is only replayed while the generation it was captured under is still current
-static std::atomic<unsigned long long> g_alloc_gen{0};
-
 void Buffer::reserve(size_t n) {
     if (n <= bytes)
         return;
-    g_alloc_gen.fetch_add(1, std::memory_order_relaxed);
     release();
     size_t want = std::max(n, bytes + bytes / 2);
     if (pinned_host)
@@ -183,11 +178,15 @@ struct IndexIVFFlatB200::Impl {
     double last_ms[5] = {0, 0, 0, 0, 0};
     IndexIVFStatsB200 stats;
 
-    // small-batch searches are launch-bound (a dozen short kernels): the whole pipeline of one
-    // (batch size, nprobe, k) shape is captured into a CUDA graph the second time the shape is
-    // seen and replayed with one launch afterwards. B200IVF_NO_GRAPH=1 turns this off.
+    // small-batch searches are launch-bound (a dozen short kernels): the kernel pipeline of one
+    // (batch size, nprobe, k, preassigned?) shape is captured into a CUDA graph the second time the
+    // shape is seen and replayed with one launch afterwards. A graph holds raw pointers and launch
+    // shapes, so it is replayed only while `search_sig()` -- every buffer the pipeline touches plus
+    // the sizes the launch plan depends on -- is what it was at capture. B200IVF_NO_GRAPH=1: off.
     struct GraphEntry {
-        unsigned long long gen = 0; // g_alloc_gen at capture (exec == nullptr: shape seen once)
+        bool seen = false;
+        uint64_t sig = 0;
+        unsigned long long launches = 0; // kernels inside the graph (for b200_kernel_launches)
         cudaGraphExec_t exec = nullptr;
     };
     std::map<std::array<int64_t, 4>, GraphEntry> graphs;
@@ -201,6 +200,28 @@ struct IndexIVFFlatB200::Impl {
             if (kv.second.exec)
                 cudaGraphExecDestroy(kv.second.exec);
         graphs.clear();
+    }
+    uint64_t search_sig() const {
+        const Buffer* bufs[] = {&cent_slab, &cent_meta, &cent_norms, &slab, &ids, &list_blk0,
+                                &list_len, &norms, &item_list, &qthr, &coarse_ids, &coarse_dis,
+                                &part, &count, &fill, &grp_start, &item_off, &item_off_tile,
+                                &pair_query, &slot_of, &cplan, &dev_x, &dev_D, &dev_I,
+                                &dev_assign64, &dev_stats};
+        uint64_t h = 1469598103934665603ull; // FNV-1a over the pointers and sizes
+        auto mix = [&h](uint64_t v) {
+            for (int i = 0; i < 8; ++i) {
+                h ^= (v >> (8 * i)) & 0xff;
+                h *= 1099511628211ull;
+            }
+        };
+        for (const Buffer* b : bufs)
+            mix((uint64_t)(uintptr_t)b->p);
+        mix((uint64_t)nstored);
+        mix((uint64_t)slab_blocks);
+        mix((uint64_t)list_lo);
+        mix((uint64_t)list_hi);
+        mix((uint64_t)(uintptr_t)stream);
+        return h;
     }
 
     Impl() {
@@ -412,6 +433,8 @@ inline int64_t ceil_div(int64_t a, int64_t b) {
 // partial lists keep a few more than k entries (scan_tc_kpart), and the k-select re-scores
 // k + kRerankExtra survivors exactly, whenever the tensor-core scan (approximate scores) takes part
 constexpr int kRerankExtra = 8;
+// searches of at most this many queries go through a captured CUDA graph
+constexpr int64_t kGraphMaxBatch = 256;
 
 // K1 as a scan of the centroid table: the kc nearest centroids of each query, best first, ties by
 // centroid number as cmp2 orders them (faiss/IndexFlat.cpp:38-69 -> knn_L2sqr/knn_inner_product).
@@ -429,7 +452,8 @@ void IndexIVFFlatB200::run_coarse_(const float* xd, int64_t n, int kc, int32_t* 
     const int kp = tc ? (tcr ? kp_r : kp_q) : kc;
     const int tcr_tq = tcr ? scan_tcr_tq(nf4, kp) : 0;
     const TileCfg tcfg = choose_tile_cfg(nf4, kp);
-    const ScanCfg cfg = choose_scan_cfg(nf4, kp);
+    // few queries: a warp carries no more query accumulators than there are queries
+    const ScanCfg cfg = choose_scan_cfg(nf4, kp, n <= 1 ? 1 : (n <= 4 ? 4 : 8));
     const bool tiled = !tc && tcfg.ok && n > kTileMinQueries;
     const int64_t tq = tcr ? tcr_tq : tc ? kTcTQ : (tiled ? tcfg.tq : cfg.rq);
     const int64_t ngroups = ceil_div(n, tq);
@@ -438,7 +462,7 @@ void IndexIVFFlatB200::run_coarse_(const float* xd, int64_t n, int kc, int32_t* 
     const int64_t target = tc ? 148 * 2 : (tiled ? 148 * 2 * 2 : kTargetScanItems);
     int64_t S = ceil_div(target, ngroups);
     S = std::max<int64_t>(1, std::min<int64_t>(S, std::max<int64_t>(1, nblk / rows_step)));
-    S = std::min<int64_t>(S, 64);
+    S = std::min<int64_t>(S, (!tc && !tiled) ? 128 : 64);
     if (const char* e = getenv("B200IVF_COARSE_S")) // tuning experiments
         S = std::max<int64_t>(1, std::min<int64_t>(atoi(e), std::max<int64_t>(1, nblk / rows_step)));
     const int pmul = (tc && !tcr) ? 2 : 1;
@@ -620,47 +644,24 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
     cudaStream_t st = m.stream;
     unsigned long long* dstats = m.dev_stats.as<unsigned long long>();
 
-    for (int64_t i0 = 0; i0 < n; i0 += nb) {
-        const int64_t ni = std::min(nb, n - i0);
+    // the kernel pipeline of one batch; every pointer is a device pointer. `timed`: stage events
+    // are recorded (not while the pipeline is being captured into a graph)
+    auto enqueue = [&](int64_t ni, const float* xd, float* Dd, int64_t* Id, const int64_t* ad,
+                       bool timed) {
         const int64_t pairs = ni * np;
         bp = plan_batch(m.nf4, kp, ni, np, nlists_owned, m.nstored, simt_only);
-        CUDA_CHECK(cudaEventRecord(m.ev[0], st));
-        // queries
-        const float* xd = x + i0 * d;
-        if (!x_dev) {
-            m.dev_x.reserve((size_t)ni * d * sizeof(float));
-            CUDA_CHECK(cudaMemcpyAsync(m.dev_x.p, xd, (size_t)ni * d * sizeof(float),
-                                       cudaMemcpyHostToDevice, st));
-            xd = m.dev_x.as<float>();
-        }
-        float* Dd = D + i0 * k;
-        int64_t* Id = I + i0 * k;
-        if (!D_dev) {
-            m.dev_D.reserve((size_t)ni * k * sizeof(float));
-            Dd = m.dev_D.as<float>();
-        }
-        if (!I_dev) {
-            m.dev_I.reserve((size_t)ni * k * sizeof(int64_t));
-            Id = m.dev_I.as<int64_t>();
-        }
         // stage 1: probe table
         m.coarse_ids.reserve((size_t)pairs * sizeof(int32_t));
         m.coarse_dis.reserve((size_t)pairs * sizeof(float));
-        if (assign) {
-            const int64_t* ad = assign + i0 * np;
-            if (!a_dev) {
-                m.dev_assign64.reserve((size_t)pairs * sizeof(int64_t));
-                CUDA_CHECK(cudaMemcpyAsync(m.dev_assign64.p, ad, (size_t)pairs * sizeof(int64_t),
-                                           cudaMemcpyHostToDevice, st));
-                ad = m.dev_assign64.as<int64_t>();
-            }
+        if (ad) {
             CUDA_CHECK(launch_i64_to_i32(ad, m.coarse_ids.as<int32_t>(), pairs, 0, (int32_t)nlist,
                                          dstats + 3, st));
         } else {
             run_coarse_(xd, ni, (int)np, m.coarse_ids.as<int32_t>(), nullptr,
                         m.coarse_dis.as<float>(), st);
         }
-        CUDA_CHECK(cudaEventRecord(m.ev[1], st));
+        if (timed)
+            CUDA_CHECK(cudaEventRecord(m.ev[1], st));
         // stage 2: invert the probe table, scan the lists
         m.count.reserve(nlist * sizeof(int32_t));
         m.fill.reserve(nlist * sizeof(int32_t));
@@ -698,7 +699,8 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
         }
         pa.stats = dstats;
         CUDA_CHECK(launch_plan(pa, st));
-        CUDA_CHECK(cudaEventRecord(m.ev[2], st));
+        if (timed)
+            CUDA_CHECK(cudaEventRecord(m.ev[2], st));
         ScanArgs sa;
         sa.slab = m.slab.as<float4>();
         sa.list_blk0 = m.list_blk0.as<uint32_t>();
@@ -747,7 +749,7 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
                 CUDA_CHECK(launch_ivf_scan_tcr(metric_type, (uint32_t)max_tc_items, ta, st));
             else
                 CUDA_CHECK(launch_ivf_scan_tc(metric_type, (uint32_t)max_tc_items, ta, st));
-        } else if (tcfg.ok) {
+        } else if (tcfg.ok && ni > kTileMinQueries) {
             // lists probed by more than kTileMinQueries queries of this batch
             TileScanArgs ta;
             ta.tmap = m.lists_map;
@@ -770,7 +772,8 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
                     bp.S;
             CUDA_CHECK(launch_ivf_scan_tile(metric_type, (uint32_t)max_tiles, ta, st));
         }
-        CUDA_CHECK(cudaEventRecord(m.ev[3], st));
+        if (timed)
+            CUDA_CHECK(cudaEventRecord(m.ev[3], st));
         // stage 3: per-query k-select, row -> id
         SelectArgs se;
         se.part = m.part.as<uint64_t>();
@@ -793,6 +796,114 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
         se.out_ids64 = Id;
         se.out_ids32 = nullptr;
         CUDA_CHECK(launch_select(se, st));
+    };
+
+    // ---- small batches: one CUDA-graph launch per search (see Impl::GraphEntry) ----
+    const bool legacy_stream = st == nullptr || st == cudaStreamLegacy || st == cudaStreamPerThread;
+    if (m.use_graph && n <= kGraphMaxBatch && !legacy_stream && !getenv("B200IVF_TC_TRACE")) {
+        const int64_t pairs = n * np;
+        m.dev_x.reserve((size_t)n * d * sizeof(float));
+        m.dev_D.reserve((size_t)n * k * sizeof(float));
+        m.dev_I.reserve((size_t)n * k * sizeof(int64_t));
+        if (assign)
+            m.dev_assign64.reserve((size_t)pairs * sizeof(int64_t));
+        CUDA_CHECK(cudaEventRecord(m.ev[0], st));
+        CUDA_CHECK(cudaMemcpyAsync(m.dev_x.p, x, (size_t)n * d * sizeof(float), cudaMemcpyDefault, st));
+        if (assign)
+            CUDA_CHECK(cudaMemcpyAsync(m.dev_assign64.p, assign, (size_t)pairs * sizeof(int64_t),
+                                       cudaMemcpyDefault, st));
+        const int64_t* ad = assign ? m.dev_assign64.as<int64_t>() : nullptr;
+        Impl::GraphEntry& ge = m.graphs[{n, np, k, assign ? 1 : 0}];
+        uint64_t sig = m.search_sig();
+        if (ge.exec && ge.sig != sig) {
+            cudaGraphExecDestroy(ge.exec);
+            ge.exec = nullptr;
+        }
+        bool ran = false;
+        if (!ge.exec && ge.seen) {
+            // second sighting of the shape: capture (all scratch was sized by the first, eager run)
+            const unsigned long long l0 = g_kernel_launches.load();
+            cudaGraph_t graph = nullptr;
+            CUDA_CHECK(cudaStreamBeginCapture(st, cudaStreamCaptureModeRelaxed));
+            try {
+                enqueue(n, m.dev_x.as<float>(), m.dev_D.as<float>(), m.dev_I.as<int64_t>(), ad, false);
+            } catch (...) {
+                cudaStreamEndCapture(st, &graph);
+                if (graph)
+                    cudaGraphDestroy(graph);
+                cudaGetLastError();
+                throw;
+            }
+            CUDA_CHECK(cudaStreamEndCapture(st, &graph));
+            ge.launches = g_kernel_launches.load() - l0;
+            g_kernel_launches.fetch_sub(ge.launches); // nothing ran yet
+            const uint64_t sig2 = m.search_sig();
+            if (sig2 == sig) {
+                cudaError_t e = cudaGraphInstantiate(&ge.exec, graph, 0);
+                cudaGraphDestroy(graph);
+                CUDA_CHECK(e);
+                ge.sig = sig;
+            } else { // a scratch buffer moved while capturing: the graph is stale already
+                cudaGraphDestroy(graph);
+                sig = sig2;
+            }
+        }
+        if (ge.exec) {
+            CUDA_CHECK(cudaGraphLaunch(ge.exec, st));
+            g_kernel_launches.fetch_add(ge.launches);
+            m.graph_replays++;
+            ran = true;
+        }
+        if (!ran) {
+            ge.seen = true;
+            enqueue(n, m.dev_x.as<float>(), m.dev_D.as<float>(), m.dev_I.as<int64_t>(), ad, true);
+        }
+        CUDA_CHECK(cudaEventRecord(m.ev[4], st));
+        CUDA_CHECK(cudaMemcpyAsync(D, m.dev_D.p, (size_t)n * k * sizeof(float), cudaMemcpyDefault, st));
+        CUDA_CHECK(cudaMemcpyAsync(I, m.dev_I.p, (size_t)n * k * sizeof(int64_t), cudaMemcpyDefault, st));
+        CUDA_CHECK(cudaEventRecord(m.ev[5], st));
+        CUDA_CHECK(cudaMemcpyAsync(m.host_stats.p, dstats, 4 * sizeof(unsigned long long),
+                                   cudaMemcpyDeviceToHost, st));
+        CUDA_CHECK(cudaStreamSynchronize(st));
+        float ms;
+        if (!ran)
+            for (int s = 1; s < 4; ++s) { // stage times exist only for the eager run
+                CUDA_CHECK(cudaEventElapsedTime(&ms, m.ev[s], m.ev[s + 1]));
+                m.last_ms[s] += ms;
+            }
+        CUDA_CHECK(cudaEventElapsedTime(&ms, m.ev[0], m.ev[5]));
+        m.last_ms[4] += ms;
+    } else
+    for (int64_t i0 = 0; i0 < n; i0 += nb) {
+        const int64_t ni = std::min(nb, n - i0);
+        const int64_t pairs = ni * np;
+        CUDA_CHECK(cudaEventRecord(m.ev[0], st));
+        // queries
+        const float* xd = x + i0 * d;
+        if (!x_dev) {
+            m.dev_x.reserve((size_t)ni * d * sizeof(float));
+            CUDA_CHECK(cudaMemcpyAsync(m.dev_x.p, xd, (size_t)ni * d * sizeof(float),
+                                       cudaMemcpyHostToDevice, st));
+            xd = m.dev_x.as<float>();
+        }
+        float* Dd = D + i0 * k;
+        int64_t* Id = I + i0 * k;
+        if (!D_dev) {
+            m.dev_D.reserve((size_t)ni * k * sizeof(float));
+            Dd = m.dev_D.as<float>();
+        }
+        if (!I_dev) {
+            m.dev_I.reserve((size_t)ni * k * sizeof(int64_t));
+            Id = m.dev_I.as<int64_t>();
+        }
+        const int64_t* ad = assign ? assign + i0 * np : nullptr;
+        if (assign && !a_dev) {
+            m.dev_assign64.reserve((size_t)pairs * sizeof(int64_t));
+            CUDA_CHECK(cudaMemcpyAsync(m.dev_assign64.p, ad, (size_t)pairs * sizeof(int64_t),
+                                       cudaMemcpyHostToDevice, st));
+            ad = m.dev_assign64.as<int64_t>();
+        }
+        enqueue(ni, xd, Dd, Id, ad, true);
         CUDA_CHECK(cudaEventRecord(m.ev[4], st));
         if (!D_dev)
             CUDA_CHECK(cudaMemcpyAsync(D + i0 * k, Dd, (size_t)ni * k * sizeof(float),

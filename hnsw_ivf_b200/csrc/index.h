@@ -91,4 +91,10 @@ class IndexIVFFlatB200 {
 void merge_knn_results(int metric, int nshard, int64_t n, int64_t k, const float* all_D,
                        const int64_t* all_I, float* D, int64_t* I, int device, cudaStream_t st);
 
+// The reference's index file format for this index type ("IwFl" + "IxF2"/"IxFI" + "ilar"):
+// faiss/impl/index_read.cpp:782-787 / index_write.cpp:635-638 (index_io.cu). The caller owns the
+// returned index.
+IndexIVFFlatB200* read_index(const char* fname, int io_flags, int device);
+void write_index(const IndexIVFFlatB200* idx, const char* fname);
+
 } // namespace b200ivf

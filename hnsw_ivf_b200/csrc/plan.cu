@@ -53,69 +53,94 @@ __global__ void plan_count_kernel(const PlanArgs a) {
         atomicAdd(&a.stats[0], (unsigned long long)a.n);
 }
 
-// single-block exclusive scan over the lists: grp_start (pairs) and item_off (warp items)
-__global__ void plan_scan_kernel(const PlanArgs a) {
-    __shared__ int s_cnt[1024];
-    __shared__ unsigned s_itm[1024];
-    __shared__ unsigned s_til[1024];
-    __shared__ int carry_cnt;
-    __shared__ unsigned carry_itm, carry_til;
-    const int t = threadIdx.x;
-    if (t == 0) {
-        carry_cnt = 0;
-        carry_itm = 0;
-        carry_til = 0;
+// single-block exclusive scan over the lists: grp_start (pairs) and item_off (warp items).
+// Every thread owns a contiguous run of lists: serial sums, one shuffle scan over the 1024 thread
+// totals, then a second pass that writes the prefixes (two barriers in all; this kernel sits on
+// the latency path of every small-batch search).
+__device__ __forceinline__ void plan_list_items(const PlanArgs& a, int c, unsigned& it,
+                                                unsigned& tl) {
+    const bool tiled = a.tile_tq > 0 && c > a.tile_min;
+    it = tiled ? 0u : (unsigned)((c + a.rq - 1) / a.rq) * (unsigned)a.nsplit;
+    tl = tiled ? (unsigned)((c + a.tile_tq - 1) / a.tile_tq) * (unsigned)a.nsplit : 0u;
+}
+
+__global__ void __launch_bounds__(1024) plan_scan_kernel(const PlanArgs a) {
+    __shared__ int w_cnt[32];
+    __shared__ unsigned w_itm[32], w_til[32];
+    const int t = threadIdx.x, lane = t & 31, w = t >> 5;
+    const int per = (a.nlists + 1023) / 1024;
+    const int l0 = min(t * per, a.nlists), l1 = min(l0 + per, a.nlists);
+    int sc = 0;
+    unsigned si = 0, sl = 0;
+#pragma unroll 4
+    for (int l = l0; l < l1; ++l) {
+        const int c = a.count[l];
+        unsigned it, tl;
+        plan_list_items(a, c, it, tl);
+        sc += c;
+        si += it;
+        sl += tl;
+    }
+    int ic = sc; // inclusive scans over the thread totals
+    unsigned ii = si, il = sl;
+    for (int o = 1; o < 32; o <<= 1) {
+        const int vc = __shfl_up_sync(0xffffffffu, ic, o);
+        const unsigned vi = __shfl_up_sync(0xffffffffu, ii, o);
+        const unsigned vl = __shfl_up_sync(0xffffffffu, il, o);
+        if (lane >= o) {
+            ic += vc;
+            ii += vi;
+            il += vl;
+        }
+    }
+    if (lane == 31) {
+        w_cnt[w] = ic;
+        w_itm[w] = ii;
+        w_til[w] = il;
     }
     __syncthreads();
-    for (int base = 0; base < a.nlists; base += 1024) {
-        const int l = base + t;
-        const int c = l < a.nlists ? a.count[l] : 0;
-        const bool tiled = a.tile_tq > 0 && c > a.tile_min;
-        const unsigned it = tiled ? 0u : (unsigned)((c + a.rq - 1) / a.rq) * (unsigned)a.nsplit;
-        const unsigned tl =
-                tiled ? (unsigned)((c + a.tile_tq - 1) / a.tile_tq) * (unsigned)a.nsplit : 0u;
-        s_cnt[t] = c;
-        s_itm[t] = it;
-        s_til[t] = tl;
-        __syncthreads();
-        for (int o = 1; o < 1024; o <<= 1) { // Hillis-Steele inclusive scan
-            int vc = 0;
-            unsigned vi = 0, vt = 0;
-            if (t >= o) {
-                vc = s_cnt[t - o];
-                vi = s_itm[t - o];
-                vt = s_til[t - o];
-            }
-            __syncthreads();
-            s_cnt[t] += vc;
-            s_itm[t] += vi;
-            s_til[t] += vt;
-            __syncthreads();
-        }
-        if (l < a.nlists) {
-            a.grp_start[l] = carry_cnt + s_cnt[t] - c;
-            a.item_off[l] = carry_itm + s_itm[t] - it;
-            if (a.item_off_tile)
-                a.item_off_tile[l] = carry_til + s_til[t] - tl;
-            if (a.item_list_tile) {
-                const unsigned o = carry_til + s_til[t] - tl;
-                for (unsigned j = 0; j < tl; ++j)
-                    a.item_list_tile[o + j] = l;
+    if (w == 0) {
+        const int tc = w_cnt[lane];
+        const unsigned ti = w_itm[lane], tl = w_til[lane];
+        int xc = tc;
+        unsigned xi = ti, xl = tl;
+        for (int o = 1; o < 32; o <<= 1) {
+            const int vc = __shfl_up_sync(0xffffffffu, xc, o);
+            const unsigned vi = __shfl_up_sync(0xffffffffu, xi, o);
+            const unsigned vl = __shfl_up_sync(0xffffffffu, xl, o);
+            if (lane >= o) {
+                xc += vc;
+                xi += vi;
+                xl += vl;
             }
         }
-        __syncthreads();
-        if (t == 1023) {
-            carry_cnt += s_cnt[t];
-            carry_itm += s_itm[t];
-            carry_til += s_til[t];
-        }
-        __syncthreads();
+        w_cnt[lane] = xc - tc; // exclusive prefix of the warp
+        w_itm[lane] = xi - ti;
+        w_til[lane] = xl - tl;
     }
-    if (t == 0) {
-        a.grp_start[a.nlists] = carry_cnt;
-        a.item_off[a.nlists] = carry_itm;
+    __syncthreads();
+    int pc = w_cnt[w] + ic - sc;
+    unsigned pi = w_itm[w] + ii - si, pl = w_til[w] + il - sl;
+    for (int l = l0; l < l1; ++l) {
+        const int c = a.count[l];
+        unsigned it, tl;
+        plan_list_items(a, c, it, tl);
+        a.grp_start[l] = pc;
+        a.item_off[l] = pi;
         if (a.item_off_tile)
-            a.item_off_tile[a.nlists] = carry_til;
+            a.item_off_tile[l] = pl;
+        if (a.item_list_tile)
+            for (unsigned j = 0; j < tl; ++j)
+                a.item_list_tile[pl + j] = l;
+        pc += c;
+        pi += it;
+        pl += tl;
+    }
+    if (t == 1023) { // the last thread's running prefix ends at the totals
+        a.grp_start[a.nlists] = pc;
+        a.item_off[a.nlists] = pi;
+        if (a.item_off_tile)
+            a.item_off_tile[a.nlists] = pl;
     }
 }
 

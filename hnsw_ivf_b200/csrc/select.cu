@@ -538,7 +538,10 @@ cudaError_t launch_select(const SelectArgs& a, cudaStream_t st) {
         return cudaSuccess;
     const int64_t total = (int64_t)a.nseg * a.nsplit * a.kpart;
     const int kk = a.slab ? a.k + a.rerank_extra : a.k;
-    if (a.k <= kSelWarpK && kk <= kSelWarpK && (int64_t)a.nseg * a.nsplit <= 256 &&
+    // few queries with many keys each (small batches split over many warps): a warp per query
+    // would walk its keys serially and leave the GPU empty; a wide CTA per query instead
+    const bool few_wide = a.n <= 2 * 148 && total >= 1024;
+    if (!few_wide && a.k <= kSelWarpK && kk <= kSelWarpK && (int64_t)a.nseg * a.nsplit <= 256 &&
         total < (1 << 30)) {
         const int wpb = 8;
         select_warp_kernel<<<(a.n + wpb - 1) / wpb, wpb * 32, wpb * kSelWarpBytes, st>>>(a);
@@ -557,7 +560,8 @@ cudaError_t launch_select(const SelectArgs& a, cudaStream_t st) {
         smem += 32 + ((size_t)kk * 32 + 32) * sizeof(float4);
     int threads = std::min(512, std::max(64, M / 2));
     if (prefilter)
-        threads = 128;
+        threads = few_wide ? (int)std::min<int64_t>(1024, pow2_ceil((int)std::min<int64_t>(total / 4, 1024)))
+                           : 128;
     if (smem > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(select_kernel,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

@@ -128,6 +128,14 @@ int b200_merge_knn_results(B200MetricType metric, int nshard, b200_idx_t n, b200
                            const float* all_distances, const b200_idx_t* all_labels,
                            float* distances, b200_idx_t* labels, int device, void* cuda_stream);
 
+/* faiss_write_index_fname / faiss_read_index_fname (c_api/index_io_c.h:31,44) for this index type:
+ * the reference's own file format ("IwFl" header, IndexFlat quantizer "IxF2"/"IxFI", "ilar"
+ * ArrayInvertedLists; faiss/impl/index_write.cpp:635-638, index_read.cpp:782-787), so an index
+ * written by the reference loads onto `device` and an index built here is readable by the
+ * reference. io_flags is accepted for signature parity (no mmap: the lists live in HBM). */
+int b200_write_index_fname(const B200IndexIVFFlat* index, const char* fname);
+int b200_read_index_fname(const char* fname, int io_flags, int device, B200IndexIVFFlat** p_out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -260,6 +260,10 @@ def ref_lib():
         L.ref_ivfflat_add_core.argtypes = [C.c_void_p, C.c_int64, _f32p, _i64p, _i64p]
         L.ref_ivfflat_append_list.argtypes = [C.c_void_p, C.c_int64, C.c_int64, _i64p, _f32p]
         L.ref_ivfflat_ntotal.restype = C.c_int64
+        L.ref_read_index.restype = C.c_void_p
+        L.ref_read_index.argtypes = [C.c_char_p, _i64p]
+        L.ref_ivfflat_write_index.argtypes = [C.c_void_p, C.c_char_p]
+        L.ref_ivfflat_set_nprobe.argtypes = [C.c_void_p, C.c_int64]
         L.ref_ivfflat_ntotal.argtypes = [C.c_void_p]
         L.ref_ivfflat_list_size.restype = C.c_int64
         L.ref_ivfflat_list_size.argtypes = [C.c_void_p, C.c_int64]
@@ -387,6 +391,29 @@ class RefIndex:
     def set_parallel_mode(self, pm):
         self.L.ref_ivfflat_set_parallel_mode(self.h, pm)
 
+    def set_nprobe(self, nprobe):
+        """the nprobe FIELD (what write_index stores); search() here takes nprobe as an argument"""
+        self.L.ref_ivfflat_set_nprobe(self.h, int(nprobe))
+
+    def write_index(self, fname):
+        """faiss::write_index (faiss/impl/index_write.cpp:391,635-638)"""
+        _chk(self.L, self.L.ref_ivfflat_write_index(self.h, os.fsencode(fname)))
+
+    @classmethod
+    def read_index(cls, fname):
+        """faiss::read_index (faiss/impl/index_read.cpp:593,782-787) of an IndexIVFFlat file"""
+        L = ref_lib()
+        out = np.zeros(5, np.int64)
+        h = L.ref_read_index(os.fsencode(fname), out.ctypes.data_as(_i64p))
+        if not h:
+            raise RuntimeError("reference read_index failed: %s" % L.ref_last_error().decode())
+        r = cls.__new__(cls)
+        r.L = L
+        r.d, r.nlist, r.metric = int(out[0]), int(out[1]), int(out[2])
+        r.nprobe = int(out[3])
+        r.h = C.c_void_p(h)
+        return r
+
 
 def ref_stats(reset=False):
     L = ref_lib()
@@ -438,3 +465,73 @@ def ref_heap_select(metric, k, vals, ids):
     L.ref_heap_select(metric, k, vals.shape[0], pv, pi, ov.ctypes.data_as(_f32p),
                       oi.ctypes.data_as(_i64p))
     return ov, oi
+
+
+# ---- the reference's index file format, parsed with numpy (faiss/impl/index_write.cpp) -----------
+def _fourcc(s):
+    """faiss/impl/io.cpp:237-241"""
+    b = s.encode()
+    return b[0] | b[1] << 8 | b[2] << 16 | b[3] << 24
+
+
+def parse_index_file(path):
+    """Plain restatement of read_index for one index type: "IwFl" (faiss/impl/index_read.cpp:
+    782-787) = index header (:62-74) + nlist + nprobe + IndexFlat quantizer ("IxF2"/"IxFI", :593-611)
+    + direct map (:442-456) + "ilar" ArrayInvertedLists (:155-212). Returns a dict with the header
+    fields, the centroids and the lists as (codes [n][d] fp32, ids [n] int64)."""
+    buf = np.fromfile(path, dtype=np.uint8)
+    pos = [0]
+
+    def take(dtype, n=1):
+        dt = np.dtype(dtype)
+        a = np.frombuffer(buf, dtype=dt, count=n, offset=pos[0])
+        pos[0] += dt.itemsize * n
+        return a
+
+    def header():
+        d = int(take("<i4")[0])
+        ntotal = int(take("<i8")[0])
+        take("<i8", 2)  # two dummies
+        trained = bool(take("u1")[0])
+        metric = int(take("<i4")[0])
+        assert metric in (0, 1), "metric_arg follows for other metrics"
+        return d, ntotal, trained, metric
+
+    h = int(take("<u4")[0])
+    assert h == _fourcc("IwFl"), "not an IndexIVFFlat file"
+    d, ntotal, trained, metric = header()
+    nlist, nprobe = int(take("<u8")[0]), int(take("<u8")[0])
+    qh = int(take("<u4")[0])
+    assert qh in (_fourcc("IxF2"), _fourcc("IxFI"), _fourcc("IxFl"))
+    qd, qn, qtrained, qmetric = header()
+    nfl = int(take("<u8")[0])
+    centroids = take("<f4", nfl).reshape(-1, qd).copy()
+    dm_type = int(take("u1")[0])
+    take("<i8", int(take("<u8")[0]))
+    if dm_type == 2:
+        take("<i8", 2 * int(take("<u8")[0]))
+    ih = int(take("<u4")[0])
+    lists = None
+    if ih == _fourcc("ilar"):
+        il_nlist, code_size = int(take("<u8")[0]), int(take("<u8")[0])
+        assert il_nlist == nlist and code_size == 4 * d
+        lt = int(take("<u4")[0])
+        tab = take("<u8", int(take("<u8")[0]))
+        sizes = np.zeros(nlist, np.int64)
+        if lt == _fourcc("full"):
+            sizes[:] = tab
+        else:
+            assert lt == _fourcc("sprs")
+            sizes[tab[0::2].astype(np.int64)] = tab[1::2]
+        lists = []
+        for l in range(nlist):
+            n = int(sizes[l])
+            codes = take("<f4", n * d).reshape(n, d).copy()
+            ids = take("<i8", n).copy()
+            lists.append((codes, ids))
+    else:
+        assert ih == _fourcc("il00")
+    assert pos[0] == buf.size, "trailing bytes"
+    return dict(d=d, ntotal=ntotal, is_trained=trained, metric=metric, nlist=nlist, nprobe=nprobe,
+                quantizer=dict(fourcc=qh, d=qd, ntotal=qn, is_trained=qtrained, metric=qmetric),
+                centroids=centroids, direct_map_type=dm_type, lists=lists)

@@ -11,11 +11,14 @@
 //   IndexIVF::search_preassigned faiss/IndexIVF.cpp:399
 //   merge_knn_results           faiss/utils/Heap.cpp:158
 //   knn_L2sqr/knn_inner_product faiss/utils/distances.cpp:885,836
+//   write_index / read_index    faiss/impl/index_write.cpp:391, faiss/impl/index_read.cpp:593
 // Only tests/, __graft_entry__.smoke() and bench.py's CPU-baseline legs may load this library.
 
 #include <faiss/IndexFlat.h>
 #include <faiss/IndexIVFFlat.h>
+#include <faiss/impl/FaissAssert.h>
 #include <faiss/impl/FaissException.h>
+#include <faiss/index_io.h>
 #include <faiss/invlists/InvertedLists.h>
 #include <faiss/utils/Heap.h>
 #include <faiss/utils/distances.h>
@@ -179,6 +182,40 @@ int ref_ivfflat_search_preassigned(void* h, int64_t n, const float* x, int64_t k
         r->index->nprobe = nprobe;
         r->index->search_preassigned(n, x, k, assign, cdis, D, I, false);
     });
+}
+
+// faiss::write_index(index, fname): the reference's own file of this index
+int ref_ivfflat_write_index(void* h, const char* fname) {
+    auto* r = (RefIndex*)h;
+    return guarded([&] { faiss::write_index(r->index.get(), fname); });
+}
+
+// faiss::read_index(fname) -> handle (NULL on failure or if the file is not an IndexIVFFlat over
+// an IndexFlat quantizer). out5 = {d, nlist, metric, nprobe, ntotal}.
+void* ref_read_index(const char* fname, int64_t* out5) {
+    RefIndex* r = nullptr;
+    const int rc = guarded([&] {
+        std::unique_ptr<faiss::Index> idx(faiss::read_index(fname));
+        auto* ivf = dynamic_cast<faiss::IndexIVFFlat*>(idx.get());
+        FAISS_THROW_IF_NOT_MSG(ivf, "not an IndexIVFFlat file");
+        auto* q = dynamic_cast<faiss::IndexFlat*>(ivf->quantizer);
+        FAISS_THROW_IF_NOT_MSG(q, "quantizer is not an IndexFlat");
+        r = new RefIndex;
+        ivf->own_fields = false; // the quantizer is owned by the RefIndex below
+        r->quantizer.reset(q);
+        idx.release();
+        r->index.reset(ivf);
+        out5[0] = ivf->d;
+        out5[1] = (int64_t)ivf->nlist;
+        out5[2] = (int64_t)ivf->metric_type;
+        out5[3] = (int64_t)ivf->nprobe;
+        out5[4] = ivf->ntotal;
+    });
+    return rc == 0 ? r : nullptr;
+}
+
+void ref_ivfflat_set_nprobe(void* h, int64_t nprobe) {
+    ((RefIndex*)h)->index->nprobe = (size_t)nprobe;
 }
 
 void ref_ivfflat_set_parallel_mode(void* h, int pm) {

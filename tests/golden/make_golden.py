@@ -11,6 +11,8 @@ the reference's outputs for one case of the path:
   D, I          index.search(nq, xq, k) with nprobe        faiss/IndexIVF.cpp:303
   Dp, Ip        index.search_preassigned(..., Iq, Dq)      faiss/IndexIVF.cpp:399
   ndis          indexIVF_stats.ndis of the search          faiss/IndexIVF.cpp:721
+<name>.ivfflat (lowlevel_l2, lowlevel_ip, sparse_l2): the index file faiss::write_index wrote for
+the case (faiss/impl/index_write.cpp:635-638) -- golden bytes for the file reader / writer.
 The shapes follow the reference's own tests for this path (tests/test_lowlevel_ivf.cpp:43-75:
 d=32, nb=1000, nq=200, nlist=32, nprobe=4, k=10) plus k>=100, d%4!=0, nprobe=nlist and ties.
 """
@@ -38,6 +40,9 @@ CASES = [
     ("ties_ip", 0, 8, 600, 30, 4, 2, 12, 3),
     ("sift_shape_l2", 1, 128, 4000, 100, 32, 8, 10, 0),
 ]
+
+
+INDEX_FILES = ("lowlevel_l2", "lowlevel_ip")
 
 
 def main():
@@ -70,6 +75,24 @@ def main():
                             nprobe=nprobe, k=k, centroids=cent, xb=xb, ids=ids, xq=xq,
                             assign=assign, Dq=Dq, Iq=Iq, D=D, I=I, Dp=Dp, Ip=Ip, ndis=ndis)
         print(name, "ndis", ndis, "I[0]", I[0][:5])
+        if name in INDEX_FILES:
+            # the reference's own index file of this case (faiss::write_index), "full" size table
+            r.set_nprobe(nprobe)
+            r.write_index(os.path.join(HERE, name + ".ivfflat"))
+    # an index with most lists empty: write_index stores the "sprs" size table
+    # (faiss/impl/index_write.cpp:268-279)
+    d, nlist, nb = 16, 40, 300
+    xb = clustered(nb, d, 8, 5)
+    cent = sample_centroids(xb, nlist)
+    assign = np.array([3, 17, 38], np.int64)[np.arange(nb) % 3]
+    ids = np.arange(nb, dtype=np.int64) + 1000
+    r = po.RefIndex(d, nlist, 1)
+    r.set_centroids(cent)
+    r.add_core(xb, ids, assign)
+    r.set_nprobe(5)
+    r.write_index(os.path.join(HERE, "sparse_l2.ivfflat"))
+    with open(os.path.join(HERE, "sparse_l2.inputs"), "wb") as f:  # (an .npz by content)
+        np.savez_compressed(f, centroids=cent, xb=xb, ids=ids, assign=assign)
 
 
 if __name__ == "__main__":

@@ -187,3 +187,48 @@ def test_skips_and_padding():
     D, I = o.search_preassigned(clustered(3, d, 4, 3), k, keys)
     assert (I[0] >= 0).sum() == 2 and (I[1] >= 0).sum() == 0 and (I[2] >= 0).sum() == 4
     assert np.all(D[I < 0] == np.finfo(np.float32).max)
+
+
+# ---- the reference's index file format ------------------------------------
+GOLDEN_DIR = os.path.join(os.path.dirname(__file__), "golden")
+
+
+@pytest.mark.parametrize("name", ["lowlevel_l2", "lowlevel_ip"])
+def test_index_file_restatement_matches_reference_file(name):
+    """oracle.parse_index_file (the restated "IwFl" layout, faiss/impl/index_write.cpp:635-638)
+    against a file the unmodified reference wrote for a golden case"""
+    g = np.load(os.path.join(GOLDEN_DIR, name + ".npz"))
+    f = po.parse_index_file(os.path.join(GOLDEN_DIR, name + ".ivfflat"))
+    assert (f["d"], f["nlist"], f["nprobe"], f["metric"]) == (
+        g["xb"].shape[1], int(g["nlist"]), int(g["nprobe"]), int(g["metric"]))
+    assert f["ntotal"] == g["xb"].shape[0] and f["is_trained"]
+    assert f["quantizer"]["ntotal"] == f["nlist"] and f["quantizer"]["metric"] == f["metric"]
+    assert f["quantizer"]["fourcc"] == po._fourcc("IxF2" if f["metric"] == 1 else "IxFI")
+    assert np.array_equal(f["centroids"], g["centroids"])
+    assert f["direct_map_type"] == 0
+    for l in range(f["nlist"]):
+        want = np.nonzero(g["assign"] == l)[0]
+        codes, ids = f["lists"][l]
+        assert np.array_equal(ids, g["ids"][want]) and np.array_equal(codes, g["xb"][want])
+
+
+def test_index_file_sparse_size_table():
+    """more than half of the lists empty: "sprs" table (faiss/impl/index_write.cpp:268-279)"""
+    g = np.load(os.path.join(GOLDEN_DIR, "sparse_l2.inputs"))
+    f = po.parse_index_file(os.path.join(GOLDEN_DIR, "sparse_l2.ivfflat"))
+    assert f["nlist"] == 40 and f["nprobe"] == 5 and f["ntotal"] == 300
+    for l in range(40):
+        want = np.nonzero(g["assign"] == l)[0]
+        codes, ids = f["lists"][l]
+        assert np.array_equal(ids, g["ids"][want]) and np.array_equal(codes, g["xb"][want])
+
+
+@pytest.mark.skipif(not po.ref_available(), reason="oracle/_ref not built")
+def test_reference_reads_its_own_golden_file():
+    """the committed file is a live reference index: read_index + search == the golden outputs"""
+    g = np.load(os.path.join(GOLDEN_DIR, "lowlevel_l2.npz"))
+    r = po.RefIndex.read_index(os.path.join(GOLDEN_DIR, "lowlevel_l2.ivfflat"))
+    assert (r.d, r.nlist, r.nprobe, r.ntotal) == (32, 32, 4, 1000)
+    po.ref_set_threads(1)
+    D, I = r.search(g["xq"], int(g["k"]), int(g["nprobe"]))
+    assert np.array_equal(I, g["I"]) and np.array_equal(D, g["D"])

@@ -302,3 +302,43 @@ def test_golden_vectors(cuda_device, path):
     idx2.add_with_ids(g["xb"], g["ids"])
     diff = sum(abs(idx2.get_list_size(l) - int((g["assign"] == l).sum())) for l in range(nlist))
     assert diff <= (2 * g["xb"].shape[0]) // 100 if ties else diff <= 4, diff
+
+
+@pytest.mark.parametrize("metric", [L2, IP])
+def test_small_batch_graph_replay(cuda_device, metric):
+    """small batches run as one captured CUDA graph from the third call of a shape on: replays must
+    give what the eager first call gave, for new queries too, and a graph must not outlive an add()
+    that moves the slab (the low-latency regime of BASELINE config 5)"""
+    import hnsw_ivf_b200 as b2
+    d, nb, nlist, nprobe, k = 64, 20000, 128, 8, 10
+    xb, cent, o, g = _build_pair(d, nb, nlist, metric)
+    g.nprobe = nprobe
+    xq = clustered(64, d, 4 * nlist, 7)
+    for bs in (1, 5, 32):
+        outs = []
+        for r in range(4):  # eager, capture + replay, replay, replay
+            q = xq[r:r + bs]
+            Dq, Iq = o.quantize(q, nprobe)
+            Do, Io = o.search_preassigned(q, k, Iq)
+            Dg, Ig = g.search_preassigned(q, k, Iq)
+            assert_knn_parity(Do, Io, Dg, Ig, what="graph preassigned bs=%d call %d" % (bs, r))
+            De, Ie = g.search(q, k)
+            r2 = compare_knn(Do, Io, De, Ie)
+            assert r2["exact_id_rate"] > 0.97, r2
+            outs.append((De, Ie))
+    # grow the index: the slab moves, graphs captured before must be dropped
+    xb2 = clustered(3000, d, 4 * nlist, 11)
+    ids2 = np.arange(nb, nb + 3000, dtype=np.int64)
+    o.add_with_ids(xb2, ids2)
+    a2 = np.empty(3000, np.int64)
+    for l in range(nlist):
+        _, ids = o.get_list(l)
+        sel = ids[ids >= nb] - nb
+        a2[sel] = l
+    g.add_core(xb2, ids2, a2)
+    for r in range(3):
+        q = xq[r:r + 5]
+        Dq, Iq = o.quantize(q, nprobe)
+        Do, Io = o.search_preassigned(q, k, Iq)
+        Dg, Ig = g.search_preassigned(q, k, Iq)
+        assert_knn_parity(Do, Io, Dg, Ig, what="graph after add, call %d" % r)
