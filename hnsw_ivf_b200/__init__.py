@@ -11,8 +11,19 @@ from .binding import (  # noqa: F401
     METRIC_INNER_PRODUCT,
     METRIC_L2,
     B200Error,
+    IDSelector,
+    IDSelectorAnd,
+    IDSelectorArray,
+    IDSelectorBatch,
+    IDSelectorBitmap,
+    IDSelectorNot,
+    IDSelectorOr,
+    IDSelectorRange,
+    IDSelectorXOr,
     IndexIVFFlat,
     IndexIVFStats,
+    QueryLatencyStats,
+    SearchParametersIVF,
     build_library,
     kernel_launches,
     tensor_core_launches,
@@ -26,6 +37,9 @@ from .sharded import IndexShardsIVFFlat, list_range_of_rank  # noqa: F401
 
 __all__ = [
     "METRIC_INNER_PRODUCT", "METRIC_L2", "B200Error", "IndexIVFFlat", "IndexIVFStats",
+    "IDSelector", "IDSelectorRange", "IDSelectorBatch", "IDSelectorArray", "IDSelectorBitmap",
+    "IDSelectorNot", "IDSelectorAnd", "IDSelectorOr", "IDSelectorXOr", "SearchParametersIVF",
+    "QueryLatencyStats",
     "IndexShardsIVFFlat", "build_library", "kernel_launches", "tensor_core_launches", "library_path", "load_library", "merge_knn_results", "read_index", "write_index",
     "list_range_of_rank",
 ]

@@ -30,6 +30,11 @@ class IndexIVFStats(C.Structure):  # FaissIndexIVFStats, c_api/IndexIVF_c.h:162-
                 ("search_time", C.c_double)]
 
 
+class QueryLatencyStats(C.Structure):  # the fork's faiss/IndexIVF.h:28-32, microseconds
+    _fields_ = [("total_us", C.c_double), ("quantization_us", C.c_double),
+                ("list_scan_us", C.c_double)]
+
+
 def library_path():
     return os.path.join(_HERE, "lib", "libb200ivf.so")
 
@@ -76,6 +81,41 @@ SYMBOLS = [
     ("b200_tensor_core_launches", C.c_ulonglong, []),
     ("b200_merge_knn_results", C.c_int,
      [C.c_int, C.c_int, C.c_int64, C.c_int64, _f32p, _i64p, _f32p, _i64p, C.c_int, _vp]),
+    ("b200_IndexIVFFlat_train", C.c_int, [_vp, C.c_int64, _f32p]),
+    ("b200_IDSelectorRange_new", C.c_int, [C.POINTER(_vp), C.c_int64, C.c_int64]),
+    ("b200_IDSelectorBatch_new", C.c_int, [C.POINTER(_vp), C.c_size_t, _i64p, C.c_int]),
+    ("b200_IDSelectorBitmap_new", C.c_int, [C.POINTER(_vp), C.c_size_t, _vp, C.c_int]),
+    ("b200_IDSelectorNot_new", C.c_int, [C.POINTER(_vp), _vp]),
+    ("b200_IDSelectorAnd_new", C.c_int, [C.POINTER(_vp), _vp, _vp]),
+    ("b200_IDSelectorOr_new", C.c_int, [C.POINTER(_vp), _vp, _vp]),
+    ("b200_IDSelectorXOr_new", C.c_int, [C.POINTER(_vp), _vp, _vp]),
+    ("b200_IDSelector_is_member", C.c_int, [_vp, C.c_int64]),
+    ("b200_IDSelector_free", None, [_vp]),
+    ("b200_SearchParametersIVF_new", C.c_int, [C.POINTER(_vp)]),
+    ("b200_SearchParametersIVF_new_with", C.c_int, [C.POINTER(_vp), _vp, C.c_size_t, C.c_size_t]),
+    ("b200_SearchParametersIVF_free", None, [_vp]),
+    ("b200_SearchParametersIVF_sel", _vp, [_vp]),
+    ("b200_SearchParametersIVF_nprobe", C.c_size_t, [_vp]),
+    ("b200_SearchParametersIVF_set_nprobe", None, [_vp, C.c_size_t]),
+    ("b200_SearchParametersIVF_max_codes", C.c_size_t, [_vp]),
+    ("b200_SearchParametersIVF_set_max_codes", None, [_vp, C.c_size_t]),
+    ("b200_IndexIVFFlat_max_codes", C.c_size_t, [_vp]),
+    ("b200_IndexIVFFlat_set_max_codes", None, [_vp, C.c_size_t]),
+    ("b200_IndexIVFFlat_search_with_params", C.c_int,
+     [_vp, C.c_int64, _f32p, C.c_int64, _vp, _f32p, _i64p]),
+    ("b200_IndexIVFFlat_search_preassigned_with_params", C.c_int,
+     [_vp, C.c_int64, _f32p, C.c_int64, _i64p, _f32p, _f32p, _i64p, C.c_int, _vp]),
+    ("b200_IndexIVFFlat_search_stats", C.c_int,
+     [_vp, C.c_int64, _f32p, C.c_int64, _f32p, _i64p, _vp, C.POINTER(QueryLatencyStats)]),
+    ("b200_RangeSearchResult_new", C.c_int, [C.POINTER(_vp), C.c_int64]),
+    ("b200_RangeSearchResult_free", None, [_vp]),
+    ("b200_RangeSearchResult_nq", C.c_size_t, [_vp]),
+    ("b200_RangeSearchResult_lims", None, [_vp, C.POINTER(C.POINTER(C.c_size_t))]),
+    ("b200_RangeSearchResult_labels", None,
+     [_vp, C.POINTER(C.POINTER(C.c_int64)), C.POINTER(C.POINTER(C.c_float))]),
+    ("b200_IndexIVFFlat_range_search", C.c_int, [_vp, C.c_int64, _f32p, C.c_float, _vp, _vp]),
+    ("b200_IndexIVFFlat_range_search_preassigned", C.c_int,
+     [_vp, C.c_int64, _f32p, C.c_float, _i64p, _f32p, _vp, C.c_int, _vp]),
     ("b200_write_index_fname", C.c_int, [_vp, C.c_char_p]),
     ("b200_read_index_fname", C.c_int, [C.c_char_p, C.c_int, C.c_int, C.POINTER(_vp)]),
 ]
@@ -132,13 +172,115 @@ def _empty_like_input(x, shape, dtype):
     return np.empty(shape, dtype=dtype)
 
 
+def _rc(lib, rc):
+    if rc != 0:
+        raise B200Error(rc, lib.b200_get_last_error().decode())
+
+
+class IDSelector:
+    """Base of the selector family (faiss/impl/IDSelector.h:19-170): owns a C-ABI handle and keeps
+    its operands alive (the C objects borrow them, as the reference's do)."""
+
+    def __init__(self, handle, keep=()):
+        self._lib = load_library()
+        self._h = handle
+        self._keep = keep
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            self._lib.b200_IDSelector_free(self._h)
+            self._h = None
+
+    def is_member(self, i):
+        return bool(self._lib.b200_IDSelector_is_member(self._h, int(i)))
+
+
+def _new_sel(fn_name, *args, keep=()):
+    lib = load_library()
+    h = _vp()
+    _rc(lib, getattr(lib, fn_name)(C.byref(h), *args))
+    return IDSelector(h, keep)
+
+
+def IDSelectorRange(imin, imax):
+    """ids in [imin, imax) (faiss/impl/IDSelector.cpp:20-22)"""
+    return _new_sel("b200_IDSelectorRange_new", int(imin), int(imax))
+
+
+def IDSelectorBatch(indices, device=0):
+    """ids in a set (faiss/impl/IDSelector.cpp:84-108); IDSelectorArray is the same predicate"""
+    a = np.ascontiguousarray(indices, dtype=np.int64)
+    return _new_sel("b200_IDSelectorBatch_new", a.size, a.ctypes.data, device)
+
+
+IDSelectorArray = IDSelectorBatch
+
+
+def IDSelectorBitmap(bitmap, device=0):
+    """bit i of a uint8 bitmap, ids beyond it excluded (faiss/impl/IDSelector.cpp:117-123)"""
+    a = np.ascontiguousarray(bitmap, dtype=np.uint8)
+    return _new_sel("b200_IDSelectorBitmap_new", a.size, a.ctypes.data, device)
+
+
+def IDSelectorNot(sel):
+    return _new_sel("b200_IDSelectorNot_new", sel._h, keep=(sel,))
+
+
+def IDSelectorAnd(lhs, rhs):
+    return _new_sel("b200_IDSelectorAnd_new", lhs._h, rhs._h, keep=(lhs, rhs))
+
+
+def IDSelectorOr(lhs, rhs):
+    return _new_sel("b200_IDSelectorOr_new", lhs._h, rhs._h, keep=(lhs, rhs))
+
+
+def IDSelectorXOr(lhs, rhs):
+    return _new_sel("b200_IDSelectorXOr_new", lhs._h, rhs._h, keep=(lhs, rhs))
+
+
+class SearchParametersIVF:
+    """faiss.SearchParametersIVF(sel=None, nprobe=1, max_codes=0) (faiss/IndexIVF.h:73-88)"""
+
+    def __init__(self, sel=None, nprobe=1, max_codes=0):
+        self._lib = load_library()
+        self._sel = sel
+        h = _vp()
+        _rc(self._lib, self._lib.b200_SearchParametersIVF_new_with(
+            C.byref(h), sel._h if sel is not None else None, int(nprobe), int(max_codes)))
+        self._h = h
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            self._lib.b200_SearchParametersIVF_free(self._h)
+            self._h = None
+
+    sel = property(lambda s: s._sel)
+
+    @property
+    def nprobe(self):
+        return self._lib.b200_SearchParametersIVF_nprobe(self._h)
+
+    @nprobe.setter
+    def nprobe(self, v):
+        self._lib.b200_SearchParametersIVF_set_nprobe(self._h, int(v))
+
+    @property
+    def max_codes(self):
+        return self._lib.b200_SearchParametersIVF_max_codes(self._h)
+
+    @max_codes.setter
+    def max_codes(self, v):
+        self._lib.b200_SearchParametersIVF_set_max_codes(self._h, int(v))
+
+
 class IndexIVFFlat:
     """Device-resident IndexIVFFlat with its flat quantizer (faiss/IndexIVFFlat.h:26).
 
     Same field names and call shapes as the reference's Python surface: ``d``, ``nlist``,
     ``nprobe``, ``ntotal``, ``is_trained``, ``metric_type``; ``add``, ``add_with_ids``,
-    ``search(x, k) -> (D, I)``, ``search_preassigned``. Training is out of scope for this path
-    (SURVEY.md 8f): centroids trained elsewhere are installed with ``set_centroids``.
+    ``max_codes``; ``train``, ``add``, ``add_with_ids``, ``search(x, k, params=None) -> (D, I)``,
+    ``search_preassigned``, ``range_search(x, radius) -> (lims, D, I)``, and the fork's
+    ``search_stats``. Centroids trained elsewhere can be installed with ``set_centroids``.
     """
 
     def __init__(self, d, nlist, metric=METRIC_L2, device=0, _handle=None):
@@ -177,7 +319,22 @@ class IndexIVFFlat:
     def nprobe(self, v):
         self._lib.b200_IndexIVFFlat_set_nprobe(self._h, int(v))
 
+    @property
+    def max_codes(self):
+        return self._lib.b200_IndexIVFFlat_max_codes(self._h)
+
+    @max_codes.setter
+    def max_codes(self, v):
+        self._lib.b200_IndexIVFFlat_set_max_codes(self._h, int(v))
+
     # ---- build -------------------------------------------------------------------------------
+    def train(self, x):
+        """IndexIVF::train (faiss/IndexIVF.cpp:1404): k-means of the coarse quantizer on device"""
+        kx, px = _ptr(x, np.float32, None, "x")
+        if kx.ndim != 2 or kx.shape[1] != self.d:
+            raise ValueError("x must be [n][%d]" % self.d)
+        self._check(self._lib.b200_IndexIVFFlat_train(self._h, kx.shape[0], px))
+
     def set_centroids(self, c):
         keep, p = _ptr(c, np.float32, (self.nlist, self.d), "centroids")
         self._check(self._lib.b200_IndexIVFFlat_set_centroids(self._h, p))
@@ -223,7 +380,7 @@ class IndexIVFFlat:
         return codes, ids
 
     # ---- search ------------------------------------------------------------------------------
-    def search(self, x, k, D=None, I=None):
+    def search(self, x, k, D=None, I=None, params=None):
         kx, px = _ptr(x, np.float32, None, "x")
         n = kx.shape[0]
         if kx.ndim != 2 or kx.shape[1] != self.d:
@@ -234,13 +391,18 @@ class IndexIVFFlat:
             I = _empty_like_input(kx, (n, k), np.int64)
         kd, pd = _ptr(D, np.float32, (n, k), "D")
         ki, pi = _ptr(I, np.int64, (n, k), "I")
-        self._check(self._lib.b200_IndexIVFFlat_search(self._h, n, px, k, pd, pi))
+        if params is None:
+            self._check(self._lib.b200_IndexIVFFlat_search(self._h, n, px, k, pd, pi))
+        else:
+            self._check(self._lib.b200_IndexIVFFlat_search_with_params(self._h, n, px, k,
+                                                                       params._h, pd, pi))
         return kd, ki
 
-    def search_preassigned(self, x, k, assign, centroid_dis=None, D=None, I=None):
+    def search_preassigned(self, x, k, assign, centroid_dis=None, D=None, I=None,
+                           store_pairs=False, params=None):
         kx, px = _ptr(x, np.float32, None, "x")
         n = kx.shape[0]
-        nprobe = min(self.nprobe, self.nlist)
+        nprobe = min(params.nprobe if params is not None else self.nprobe, self.nlist)
         ka, pa = _ptr(assign, np.int64, (n, nprobe), "assign")
         kc, pc = _ptr(centroid_dis, np.float32, None, "centroid_dis")
         if D is None:
@@ -249,9 +411,68 @@ class IndexIVFFlat:
             I = _empty_like_input(kx, (n, k), np.int64)
         kd, pd = _ptr(D, np.float32, (n, k), "D")
         ki, pi = _ptr(I, np.int64, (n, k), "I")
-        self._check(self._lib.b200_IndexIVFFlat_search_preassigned(self._h, n, px, k, pa, pc, pd,
-                                                                   pi, 0))
+        if params is None and not store_pairs:
+            self._check(self._lib.b200_IndexIVFFlat_search_preassigned(self._h, n, px, k, pa, pc,
+                                                                       pd, pi, 0))
+        else:
+            self._check(self._lib.b200_IndexIVFFlat_search_preassigned_with_params(
+                self._h, n, px, k, pa, pc, pd, pi, int(bool(store_pairs)),
+                params._h if params is not None else None))
         return kd, ki
+
+    def search_stats(self, x, k, params=None):
+        """The fork's IndexIVF::search_stats (faiss/IndexIVF.cpp:727): (D, I, stats) with stats a
+        structured array of n (total_us, quantization_us, list_scan_us) rows."""
+        kx, px = _ptr(x, np.float32, None, "x")
+        n = kx.shape[0]
+        D = _empty_like_input(kx, (n, k), np.float32)
+        I = _empty_like_input(kx, (n, k), np.int64)
+        kd, pd = _ptr(D, np.float32, (n, k), "D")
+        ki, pi = _ptr(I, np.int64, (n, k), "I")
+        st = (QueryLatencyStats * max(n, 1))()
+        self._check(self._lib.b200_IndexIVFFlat_search_stats(
+            self._h, n, px, k, pd, pi, params._h if params is not None else None, st))
+        arr = np.frombuffer(st, dtype=[("total_us", "f8"), ("quantization_us", "f8"),
+                                       ("list_scan_us", "f8")], count=n).copy()
+        return kd, ki, arr
+
+    def _range_result(self, call, n):
+        rsr = _vp()
+        self._check(self._lib.b200_RangeSearchResult_new(C.byref(rsr), n))
+        try:
+            self._check(call(rsr))
+            lims_p = C.POINTER(C.c_size_t)()
+            lab_p = C.POINTER(C.c_int64)()
+            dis_p = C.POINTER(C.c_float)()
+            self._lib.b200_RangeSearchResult_lims(rsr, C.byref(lims_p))
+            self._lib.b200_RangeSearchResult_labels(rsr, C.byref(lab_p), C.byref(dis_p))
+            lims = np.ctypeslib.as_array(lims_p, shape=(n + 1,)).astype(np.uint64).copy()
+            tot = int(lims[-1])
+            if tot:
+                I = np.ctypeslib.as_array(lab_p, shape=(tot,)).copy()
+                D = np.ctypeslib.as_array(dis_p, shape=(tot,)).copy()
+            else:
+                I, D = np.empty((0,), np.int64), np.empty((0,), np.float32)
+            return lims, D, I
+        finally:
+            self._lib.b200_RangeSearchResult_free(rsr)
+
+    def range_search(self, x, radius, params=None):
+        """faiss Index.range_search -> (lims, D, I) (faiss/python/class_wrappers.py:370-401):
+        L2 keeps dis < radius, inner product dis > radius."""
+        kx, px = _ptr(x, np.float32, None, "x")
+        n = kx.shape[0]
+        return self._range_result(lambda r: self._lib.b200_IndexIVFFlat_range_search(
+            self._h, n, px, float(radius), r, params._h if params is not None else None), n)
+
+    def range_search_preassigned(self, x, radius, assign, store_pairs=False, params=None):
+        kx, px = _ptr(x, np.float32, None, "x")
+        n = kx.shape[0]
+        nprobe = min(params.nprobe if params is not None else self.nprobe, self.nlist)
+        ka, pa = _ptr(assign, np.int64, (n, nprobe), "assign")
+        return self._range_result(lambda r: self._lib.b200_IndexIVFFlat_range_search_preassigned(
+            self._h, n, px, float(radius), pa, None, r, int(bool(store_pairs)),
+            params._h if params is not None else None), n)
 
     def quantize(self, x, nprobe):
         kx, px = _ptr(x, np.float32, None, "x")

@@ -5,6 +5,7 @@
 
 #include "index.h"
 #include "kernels.h"
+#include "selector.h"
 
 #include <exception>
 #include <string>
@@ -37,6 +38,25 @@ inline IndexIVFFlatB200* H(B200IndexIVFFlat* p) {
 inline const IndexIVFFlatB200* H(const B200IndexIVFFlat* p) {
     return reinterpret_cast<const IndexIVFFlatB200*>(p);
 }
+inline const b200ivf::IDSelector* S(const B200IDSelector* p) {
+    return reinterpret_cast<const b200ivf::IDSelector*>(p);
+}
+inline const b200ivf::SearchParametersIVF* P(const B200SearchParametersIVF* p) {
+    return reinterpret_cast<const b200ivf::SearchParametersIVF*>(p);
+}
+inline b200ivf::RangeSearchResult* R(B200RangeSearchResult* p) {
+    return reinterpret_cast<b200ivf::RangeSearchResult*>(p);
+}
+template <class T>
+void put_selector(B200IDSelector** p_sel, T* sel) {
+    if (!p_sel) {
+        delete sel;
+        throw b200ivf::B200Exception("null output handle");
+    }
+    *p_sel = reinterpret_cast<B200IDSelector*>(static_cast<b200ivf::IDSelector*>(sel));
+}
+static_assert(sizeof(B200QueryLatencyStats) == sizeof(b200ivf::QueryLatencyStats),
+              "QueryLatencyStats layout");
 } // namespace
 
 extern "C" {
@@ -173,6 +193,159 @@ int b200_merge_knn_results(B200MetricType metric, int nshard, b200_idx_t n, b200
     return guarded([&] {
         b200ivf::merge_knn_results((int)metric, nshard, n, k, all_distances, all_labels, distances,
                                    labels, device, (cudaStream_t)cuda_stream);
+    });
+}
+
+int b200_IndexIVFFlat_train(B200IndexIVFFlat* index, b200_idx_t n, const float* x) {
+    return guarded([&] { H(index)->train(n, x); });
+}
+
+int b200_IDSelectorRange_new(B200IDSelector** p_sel, b200_idx_t imin, b200_idx_t imax) {
+    return guarded([&] { put_selector(p_sel, new b200ivf::IDSelectorRange(imin, imax)); });
+}
+int b200_IDSelectorBatch_new(B200IDSelector** p_sel, size_t n, const b200_idx_t* indices,
+                             int device) {
+    return guarded([&] { put_selector(p_sel, new b200ivf::IDSelectorBatch(n, indices, device)); });
+}
+int b200_IDSelectorBitmap_new(B200IDSelector** p_sel, size_t n, const uint8_t* bitmap,
+                              int device) {
+    return guarded([&] { put_selector(p_sel, new b200ivf::IDSelectorBitmap(n, bitmap, device)); });
+}
+int b200_IDSelectorNot_new(B200IDSelector** p_sel, const B200IDSelector* sel) {
+    return guarded([&] {
+        if (!sel)
+            throw b200ivf::B200Exception("null selector");
+        put_selector(p_sel, new b200ivf::IDSelectorNot(S(sel)));
+    });
+}
+static int binary_selector_new(B200IDSelector** p_sel, b200ivf::IDSelectorBinary::Op op,
+                               const B200IDSelector* lhs, const B200IDSelector* rhs) {
+    return guarded([&] {
+        if (!lhs || !rhs)
+            throw b200ivf::B200Exception("null selector");
+        put_selector(p_sel, new b200ivf::IDSelectorBinary(op, S(lhs), S(rhs)));
+    });
+}
+int b200_IDSelectorAnd_new(B200IDSelector** p_sel, const B200IDSelector* lhs,
+                           const B200IDSelector* rhs) {
+    return binary_selector_new(p_sel, b200ivf::IDSelectorBinary::AND, lhs, rhs);
+}
+int b200_IDSelectorOr_new(B200IDSelector** p_sel, const B200IDSelector* lhs,
+                          const B200IDSelector* rhs) {
+    return binary_selector_new(p_sel, b200ivf::IDSelectorBinary::OR, lhs, rhs);
+}
+int b200_IDSelectorXOr_new(B200IDSelector** p_sel, const B200IDSelector* lhs,
+                           const B200IDSelector* rhs) {
+    return binary_selector_new(p_sel, b200ivf::IDSelectorBinary::XOR, lhs, rhs);
+}
+int b200_IDSelector_is_member(const B200IDSelector* sel, b200_idx_t id) {
+    return S(sel)->is_member(id) ? 1 : 0;
+}
+void b200_IDSelector_free(B200IDSelector* sel) {
+    delete reinterpret_cast<b200ivf::IDSelector*>(sel);
+}
+
+int b200_SearchParametersIVF_new(B200SearchParametersIVF** p_sp) {
+    return b200_SearchParametersIVF_new_with(p_sp, nullptr, 1, 0); // IndexIVF.h:74-76 defaults
+}
+int b200_SearchParametersIVF_new_with(B200SearchParametersIVF** p_sp, B200IDSelector* sel,
+                                      size_t nprobe, size_t max_codes) {
+    return guarded([&] {
+        if (!p_sp)
+            throw b200ivf::B200Exception("null output handle");
+        auto* sp = new b200ivf::SearchParametersIVF;
+        sp->sel = S(sel);
+        sp->nprobe = nprobe;
+        sp->max_codes = max_codes;
+        *p_sp = reinterpret_cast<B200SearchParametersIVF*>(sp);
+    });
+}
+void b200_SearchParametersIVF_free(B200SearchParametersIVF* sp) {
+    delete reinterpret_cast<b200ivf::SearchParametersIVF*>(sp);
+}
+const B200IDSelector* b200_SearchParametersIVF_sel(const B200SearchParametersIVF* sp) {
+    return reinterpret_cast<const B200IDSelector*>(P(sp)->sel);
+}
+size_t b200_SearchParametersIVF_nprobe(const B200SearchParametersIVF* sp) {
+    return P(sp)->nprobe;
+}
+void b200_SearchParametersIVF_set_nprobe(B200SearchParametersIVF* sp, size_t nprobe) {
+    reinterpret_cast<b200ivf::SearchParametersIVF*>(sp)->nprobe = nprobe;
+}
+size_t b200_SearchParametersIVF_max_codes(const B200SearchParametersIVF* sp) {
+    return P(sp)->max_codes;
+}
+void b200_SearchParametersIVF_set_max_codes(B200SearchParametersIVF* sp, size_t max_codes) {
+    reinterpret_cast<b200ivf::SearchParametersIVF*>(sp)->max_codes = max_codes;
+}
+
+size_t b200_IndexIVFFlat_max_codes(const B200IndexIVFFlat* index) {
+    return H(index)->max_codes;
+}
+void b200_IndexIVFFlat_set_max_codes(B200IndexIVFFlat* index, size_t max_codes) {
+    H(index)->max_codes = max_codes;
+}
+
+int b200_IndexIVFFlat_search_with_params(const B200IndexIVFFlat* index, b200_idx_t n,
+                                         const float* x, b200_idx_t k,
+                                         const B200SearchParametersIVF* params, float* distances,
+                                         b200_idx_t* labels) {
+    return guarded([&] { H(index)->search(n, x, k, distances, labels, P(params)); });
+}
+int b200_IndexIVFFlat_search_preassigned_with_params(
+        const B200IndexIVFFlat* index, b200_idx_t n, const float* x, b200_idx_t k,
+        const b200_idx_t* assign, const float* centroid_dis, float* distances, b200_idx_t* labels,
+        int store_pairs, const B200SearchParametersIVF* params) {
+    return guarded([&] {
+        H(index)->search_preassigned(n, x, k, assign, centroid_dis, distances, labels,
+                                     store_pairs != 0, P(params));
+    });
+}
+int b200_IndexIVFFlat_search_stats(const B200IndexIVFFlat* index, b200_idx_t n, const float* x,
+                                   b200_idx_t k, float* distances, b200_idx_t* labels,
+                                   const B200SearchParametersIVF* params,
+                                   B200QueryLatencyStats* per_query_stats) {
+    return guarded([&] {
+        H(index)->search(n, x, k, distances, labels, P(params),
+                         reinterpret_cast<b200ivf::QueryLatencyStats*>(per_query_stats));
+    });
+}
+
+int b200_RangeSearchResult_new(B200RangeSearchResult** p_rsr, b200_idx_t nq) {
+    return guarded([&] {
+        if (!p_rsr || nq < 0)
+            throw b200ivf::B200Exception("invalid RangeSearchResult arguments");
+        *p_rsr = reinterpret_cast<B200RangeSearchResult*>(
+                new b200ivf::RangeSearchResult((size_t)nq));
+    });
+}
+void b200_RangeSearchResult_free(B200RangeSearchResult* rsr) {
+    delete R(rsr);
+}
+size_t b200_RangeSearchResult_nq(const B200RangeSearchResult* rsr) {
+    return reinterpret_cast<const b200ivf::RangeSearchResult*>(rsr)->nq;
+}
+void b200_RangeSearchResult_lims(B200RangeSearchResult* rsr, size_t** lims) {
+    *lims = R(rsr)->lims.data();
+}
+void b200_RangeSearchResult_labels(B200RangeSearchResult* rsr, b200_idx_t** labels,
+                                   float** distances) {
+    *labels = R(rsr)->labels.data();
+    *distances = R(rsr)->distances.data();
+}
+int b200_IndexIVFFlat_range_search(const B200IndexIVFFlat* index, b200_idx_t n, const float* x,
+                                   float radius, B200RangeSearchResult* result,
+                                   const B200SearchParametersIVF* params) {
+    return guarded([&] { H(index)->range_search(n, x, radius, R(result), P(params)); });
+}
+int b200_IndexIVFFlat_range_search_preassigned(const B200IndexIVFFlat* index, b200_idx_t n,
+                                               const float* x, float radius,
+                                               const b200_idx_t* assign, const float* centroid_dis,
+                                               B200RangeSearchResult* result, int store_pairs,
+                                               const B200SearchParametersIVF* params) {
+    return guarded([&] {
+        H(index)->range_search_preassigned(n, x, radius, assign, centroid_dis, R(result),
+                                           store_pairs != 0, P(params));
     });
 }
 

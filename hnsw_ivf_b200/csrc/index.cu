@@ -7,8 +7,11 @@
 
 #include "common.cuh"
 #include "kernels.h"
+#include "selector.h"
 
 #include <algorithm>
+#include <climits>
+#include <random>
 #include <array>
 #include <cstdlib>
 #include <cstring>
@@ -163,6 +166,11 @@ struct IndexIVFFlatB200::Impl {
             pair_query, slot_of,
             cplan, stage_x, stage_D, stage_I, stage_assign, dev_x, dev_D, dev_I, dev_assign64,
             dev_stats, host_stats;
+    // SearchParametersIVF scratch: selector row mask, max_codes limits per (query, probe) and per
+    // pair slot, per-query nscan (device + pinned host copy)
+    Buffer row_mask, limit_qp, limit_slot, query_ndis, host_query_ndis;
+    // range search scratch
+    Buffer pair_cnt, pair_off, qcnt, lims, host_lims, range_dis, range_ids;
     // TMA views of the two slabs for the tiled scan (re-encoded whenever a slab moves)
     alignas(64) unsigned char cent_map[kTensorMapBytes] = {};
     alignas(64) unsigned char lists_map[kTensorMapBytes] = {};
@@ -235,6 +243,7 @@ struct IndexIVFFlatB200::Impl {
             simt_max_avg_q = atof(e4);
         stage_x.pinned_host = stage_D.pinned_host = stage_I.pinned_host = true;
         stage_assign.pinned_host = host_stats.pinned_host = true;
+        host_query_ndis.pinned_host = host_lims.pinned_host = true;
     }
 };
 
@@ -284,9 +293,13 @@ IndexIVFFlatB200::~IndexIVFFlatB200() {
                       &impl_->item_off, &impl_->item_off_tile, &impl_->pair_query, &impl_->slot_of, &impl_->cplan,
                       &impl_->stage_x, &impl_->stage_D, &impl_->stage_I, &impl_->stage_assign,
                       &impl_->dev_x, &impl_->dev_D, &impl_->dev_I, &impl_->dev_assign64,
-                      &impl_->dev_stats, &impl_->host_stats};
+                      &impl_->dev_stats, &impl_->host_stats, &impl_->row_mask, &impl_->limit_qp,
+                      &impl_->limit_slot, &impl_->query_ndis, &impl_->host_query_ndis,
+                      &impl_->pair_cnt, &impl_->pair_off, &impl_->qcnt, &impl_->lims,
+                      &impl_->host_lims, &impl_->range_dis, &impl_->range_ids};
     for (Buffer* b : bufs)
         b->release();
+    impl_->drop_graphs();
     for (auto& ev : impl_->ev)
         if (ev)
             cudaEventDestroy(ev);
@@ -308,6 +321,10 @@ void IndexIVFFlatB200::set_stream(cudaStream_t s) {
 // ------------------------------------------------------------------------------------------------
 void IndexIVFFlatB200::set_centroids(const float* c) {
     std::lock_guard<std::mutex> lock(mu_);
+    set_centroids_(c);
+}
+
+void IndexIVFFlatB200::set_centroids_(const float* c) {
     DeviceGuard g(device_);
     Impl& m = *impl_;
     B200_THROW_IF_NOT_MSG(c != nullptr, "null centroids");
@@ -369,6 +386,10 @@ void IndexIVFFlatB200::set_list_range(size_t lo, size_t hi) {
 
 void IndexIVFFlatB200::reset() {
     std::lock_guard<std::mutex> lock(mu_);
+    reset_();
+}
+
+void IndexIVFFlatB200::reset_() {
     DeviceGuard g(device_);
     Impl& m = *impl_;
     CUDA_CHECK(cudaStreamSynchronize(m.stream));
@@ -562,7 +583,8 @@ struct BatchPlan {
 };
 
 static BatchPlan plan_batch(int nf4, int64_t kpart, int64_t nb, int64_t nprobe,
-                            int64_t nlists_owned, int64_t nstored, bool simt_only = false) {
+                            int64_t nlists_owned, int64_t nstored, bool simt_only = false,
+                            bool filtered = false) {
     BatchPlan bp;
     const int64_t pairs = nb * nprobe;
     // queries that meet in a probed list, on average (uniform-probe estimate)
@@ -578,7 +600,7 @@ static BatchPlan plan_batch(int nf4, int64_t kpart, int64_t nb, int64_t nprobe,
             std::max<int64_t>(1, nstored / std::max<int64_t>(1, nlists_owned) / kBlockRows);
     int64_t S = ceil_div(kTargetScanItems, items_est);
     // few pairs (small batches): split down to single blocks so that the whole GPU streams
-    if (simt_only && bp.cfg.rq == 1 && S > avg_blocks / kScanRowsPerStep) {
+    if (simt_only && !filtered && bp.cfg.rq == 1 && S > avg_blocks / kScanRowsPerStep) {
         bp.cfg.rv = 1;
         S = std::max<int64_t>(1, std::min(S, avg_blocks));
     } else {
@@ -588,25 +610,43 @@ static BatchPlan plan_batch(int nf4, int64_t kpart, int64_t nb, int64_t nprobe,
     return bp;
 }
 
-void IndexIVFFlatB200::search(int64_t n, const float* x, int64_t k, float* D, int64_t* I) const {
-    search_preassigned(n, x, k, nullptr, nullptr, D, I, false);
+void IndexIVFFlatB200::search(int64_t n, const float* x, int64_t k, float* D, int64_t* I,
+                              const SearchParametersIVF* params,
+                              QueryLatencyStats* per_query_stats) const {
+    search_impl_(n, x, k, nullptr, D, I, false, params, per_query_stats);
 }
 
 void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
                                           const int64_t* assign, const float* /*centroid_dis*/,
-                                          float* D, int64_t* I, bool store_pairs) const {
+                                          float* D, int64_t* I, bool store_pairs,
+                                          const SearchParametersIVF* params,
+                                          QueryLatencyStats* per_query_stats) const {
+    B200_THROW_IF_NOT_MSG(assign != nullptr, "null assign table");
+    search_impl_(n, x, k, assign, D, I, store_pairs, params, per_query_stats);
+}
+
+void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const int64_t* assign,
+                                    float* D, int64_t* I, bool store_pairs,
+                                    const SearchParametersIVF* params,
+                                    QueryLatencyStats* per_query) const {
     std::lock_guard<std::mutex> lock(mu_);
     DeviceGuard g(device_);
     Impl& m = *impl_;
-    // argument checks of IndexIVF::search / search_preassigned (faiss/IndexIVF.cpp:310-318,410-414)
+    // argument checks of IndexIVF::search / search_preassigned (faiss/IndexIVF.cpp:310-318,410-450)
     B200_THROW_IF_NOT_MSG(k > 0, "k > 0");
     B200_THROW_IF_NOT_MSG(is_trained, "index not trained");
-    B200_THROW_IF_NOT_MSG(!store_pairs, "store_pairs is not supported on the B200 path");
-    const int64_t np = (int64_t)std::min(nlist, nprobe);
+    const int64_t np = (int64_t)std::min(nlist, params ? params->nprobe : nprobe);
     B200_THROW_IF_NOT_MSG(np > 0, "nprobe > 0");
     B200_THROW_IF_NOT_MSG(k <= 2048 && np <= 2048, "k and nprobe are limited to 2048");
+    const IDSelector* sel = params ? params->sel : nullptr;
+    const size_t mc = params ? params->max_codes : max_codes;
+    B200_THROW_IF_NOT_MSG(!(sel && store_pairs), "selector and store_pairs cannot be combined");
+    // selector / max_codes: the exact SIMT scan with a row mask and per-pair row limits
+    const bool filtered = sel != nullptr || mc > 0;
     for (double& v : m.last_ms)
         v = 0;
+    if (per_query) // IndexIVF::search_stats zeroes the table first (faiss/IndexIVF.cpp:737-739)
+        std::fill(per_query, per_query + n, QueryLatencyStats());
     if (n == 0)
         return;
     B200_THROW_IF_NOT_MSG(x && D && I, "null buffer");
@@ -627,29 +667,36 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
             (double)std::max<int64_t>(1, std::min<int64_t>(nlists_owned, std::min<int64_t>(n, 32768) * np));
     // hardly any list shared between queries (small batches, huge nlist): nothing to multiply, the
     // scan is a pure stream -> the SIMT warp kernel alone (exact fp32, no re-rank needed)
-    const bool simt_only = !m.use_tc || avg_q <= m.simt_max_avg_q || (kp_q == 0 && kp_r == 0);
+    const bool simt_only =
+            filtered || !m.use_tc || avg_q <= m.simt_max_avg_q || (kp_q == 0 && kp_r == 0);
     const bool tc = !simt_only;
     const bool tcr = tc && (kp_q == 0 || (kp_r > 0 && (m.tc_mode == 2 || (m.tc_mode == 0 &&
                                                                           avg_q < kTcrMaxAvgQueries))));
     const int64_t kp = tc ? (tcr ? kp_r : kp_q) : k; // entries per partial list
     const int tcr_tq = tcr ? scan_tcr_tq(m.nf4, (int)kp) : 0;
-    BatchPlan bp = plan_batch(m.nf4, kp, nb, np, nlists_owned, m.nstored, simt_only);
+    BatchPlan bp = plan_batch(m.nf4, kp, nb, np, nlists_owned, m.nstored, simt_only, filtered);
     const int pmul = (tc && !tcr) ? 2 : 1; // partial lists per (pair, split)
     const int tc_tq = tcr ? tcr_tq : kTcTQ;
     const int tc_min = tcr ? 0 : kTileMinQueries; // lists with more queries than this: tensor cores
     while (nb > 1 && (size_t)nb * np * bp.S * pmul * kp * sizeof(uint64_t) > ((size_t)2 << 30)) {
         nb = (nb + 1) / 2;
-        bp = plan_batch(m.nf4, kp, nb, np, nlists_owned, m.nstored, simt_only);
+        bp = plan_batch(m.nf4, kp, nb, np, nlists_owned, m.nstored, simt_only, filtered);
     }
     cudaStream_t st = m.stream;
     unsigned long long* dstats = m.dev_stats.as<unsigned long long>();
+    const uint32_t* row_mask = nullptr;
+    if (sel && m.slab_blocks > 0) { // one pass over the id column per search call
+        m.row_mask.reserve(m.slab_blocks * sizeof(uint32_t));
+        sel->eval(m.ids.as<int64_t>(), (int64_t)m.slab_blocks, m.row_mask.as<uint32_t>(), st);
+        row_mask = m.row_mask.as<uint32_t>();
+    }
 
     // the kernel pipeline of one batch; every pointer is a device pointer. `timed`: stage events
     // are recorded (not while the pipeline is being captured into a graph)
     auto enqueue = [&](int64_t ni, const float* xd, float* Dd, int64_t* Id, const int64_t* ad,
                        bool timed) {
         const int64_t pairs = ni * np;
-        bp = plan_batch(m.nf4, kp, ni, np, nlists_owned, m.nstored, simt_only);
+        bp = plan_batch(m.nf4, kp, ni, np, nlists_owned, m.nstored, simt_only, filtered);
         // stage 1: probe table
         m.coarse_ids.reserve((size_t)pairs * sizeof(int32_t));
         m.coarse_dis.reserve((size_t)pairs * sizeof(float));
@@ -662,6 +709,20 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
         }
         if (timed)
             CUDA_CHECK(cudaEventRecord(m.ev[1], st));
+        if (mc > 0 || per_query) {
+            if (mc > 0) {
+                m.limit_qp.reserve((size_t)pairs * sizeof(int32_t));
+                m.limit_slot.reserve((size_t)pairs * sizeof(int32_t));
+            }
+            if (per_query)
+                m.query_ndis.reserve((size_t)ni * sizeof(unsigned long long));
+            CUDA_CHECK(launch_probe_limits(
+                    m.coarse_ids.as<int32_t>(), (int)ni, (int)np, (int)nlist,
+                    m.list_len.as<int32_t>(),
+                    mc > 0 ? (long long)std::min<size_t>(mc, (size_t)LLONG_MAX) : LLONG_MAX,
+                    mc > 0 ? m.limit_qp.as<int32_t>() : nullptr,
+                    per_query ? m.query_ndis.as<unsigned long long>() : nullptr, st));
+        }
         // stage 2: invert the probe table, scan the lists
         m.count.reserve(nlist * sizeof(int32_t));
         m.fill.reserve(nlist * sizeof(int32_t));
@@ -669,8 +730,9 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
         m.item_off.reserve((nlist + 1) * sizeof(uint32_t));
         m.item_off_tile.reserve((nlist + 1) * sizeof(uint32_t));
         TileCfg tcfg = choose_tile_cfg(m.nf4, (int)kp);
-        if (tc)
-            tcfg.ok = false; // the tensor-core kernel takes the many-query lists instead
+        if (tc || filtered)
+            tcfg.ok = false; // the tensor-core kernel takes the many-query lists instead (and a
+                             // filtered search stays in the warp kernel, which knows the mask)
         m.pair_query.reserve((size_t)pairs * sizeof(int32_t));
         m.slot_of.reserve((size_t)pairs * sizeof(int32_t));
         m.part.reserve((size_t)pairs * bp.S * pmul * kp * sizeof(uint64_t));
@@ -698,6 +760,10 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
             pa.item_list_tile = m.item_list.as<int32_t>();
         }
         pa.stats = dstats;
+        if (mc > 0) {
+            pa.limit_qp = m.limit_qp.as<int32_t>();
+            pa.limit_slot = m.limit_slot.as<int32_t>();
+        }
         CUDA_CHECK(launch_plan(pa, st));
         if (timed)
             CUDA_CHECK(cudaEventRecord(m.ev[2], st));
@@ -717,6 +783,8 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
         sa.queries = xd;
         sa.part = m.part.as<uint64_t>();
         sa.part_mul = pmul;
+        sa.row_mask = row_mask;
+        sa.pair_limit = mc > 0 ? m.limit_slot.as<int32_t>() : nullptr;
         const int64_t max_items =
                 (ceil_div(pairs, bp.cfg.rq) + std::min<int64_t>(pairs, (int64_t)nlist)) * bp.S;
         if (!tcr) // (every probed list goes to the rows-major tensor-core kernel otherwise)
@@ -784,7 +852,7 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
         se.kpart = (int)kp;
         se.k = (int)k;
         se.metric = metric_type;
-        se.ids = m.ids.as<int64_t>();
+        se.ids = store_pairs ? nullptr : m.ids.as<int64_t>(); // rows first, pairs below
         if (tc) {
             se.slab = m.slab.as<float4>();
             se.queries = xd;
@@ -796,11 +864,34 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
         se.out_ids64 = Id;
         se.out_ids32 = nullptr;
         CUDA_CHECK(launch_select(se, st));
+        if (store_pairs) // label = lo_build(list_no, offset), faiss/IndexIVFFlat.cpp:172
+            CUDA_CHECK(launch_rows_to_pairs(Id, ni * k, m.list_blk0.as<uint32_t>(), (int)nlist, st));
+    };
+    // per-query figures of IndexIVF::search_stats (faiss/IndexIVF.cpp:727-862): the coarse time is
+    // amortised over the batch as the reference does (:767-771); a batched kernel has no per-query
+    // scan time, so the batch's plan + scan + select time is shared out by each query's nscan
+    auto fill_per_query = [&](int64_t i0, int64_t ni, const double* ms_before) {
+        if (!per_query)
+            return;
+        const unsigned long long* qn = m.host_query_ndis.as<unsigned long long>();
+        double tot = 0;
+        for (int64_t i = 0; i < ni; ++i)
+            tot += (double)qn[i];
+        const double coarse_us = (m.last_ms[0] - ms_before[0]) * 1000.0 / (double)ni;
+        const double scan_us = ((m.last_ms[1] - ms_before[1]) + (m.last_ms[2] - ms_before[2]) +
+                                (m.last_ms[3] - ms_before[3])) * 1000.0;
+        for (int64_t i = 0; i < ni; ++i) {
+            QueryLatencyStats& o = per_query[i0 + i];
+            o.quantization_us = coarse_us;
+            o.list_scan_us = tot > 0 ? scan_us * (double)qn[i] / tot : scan_us / (double)ni;
+            o.total_us = o.quantization_us + o.list_scan_us;
+        }
     };
 
     // ---- small batches: one CUDA-graph launch per search (see Impl::GraphEntry) ----
     const bool legacy_stream = st == nullptr || st == cudaStreamLegacy || st == cudaStreamPerThread;
-    if (m.use_graph && n <= kGraphMaxBatch && !legacy_stream && !getenv("B200IVF_TC_TRACE")) {
+    if (m.use_graph && n <= kGraphMaxBatch && !legacy_stream && !filtered && !store_pairs &&
+        !per_query && !getenv("B200IVF_TC_TRACE")) {
         const int64_t pairs = n * np;
         m.dev_x.reserve((size_t)n * d * sizeof(float));
         m.dev_D.reserve((size_t)n * k * sizeof(float));
@@ -903,8 +994,16 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
                                        cudaMemcpyHostToDevice, st));
             ad = m.dev_assign64.as<int64_t>();
         }
+        double ms_before[5];
+        std::copy(m.last_ms, m.last_ms + 5, ms_before);
         enqueue(ni, xd, Dd, Id, ad, true);
         CUDA_CHECK(cudaEventRecord(m.ev[4], st));
+        if (per_query) {
+            m.host_query_ndis.reserve((size_t)ni * sizeof(unsigned long long));
+            CUDA_CHECK(cudaMemcpyAsync(m.host_query_ndis.p, m.query_ndis.p,
+                                       (size_t)ni * sizeof(unsigned long long),
+                                       cudaMemcpyDeviceToHost, st));
+        }
         if (!D_dev)
             CUDA_CHECK(cudaMemcpyAsync(D + i0 * k, Dd, (size_t)ni * k * sizeof(float),
                                        cudaMemcpyDeviceToHost, st));
@@ -922,6 +1021,7 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
         }
         CUDA_CHECK(cudaEventElapsedTime(&ms, m.ev[0], m.ev[5]));
         m.last_ms[4] += ms;
+        fill_per_query(i0, ni, ms_before);
     }
     const unsigned long long* hs = m.host_stats.as<unsigned long long>();
     m.stats.nq = (size_t)hs[0];
@@ -1013,6 +1113,11 @@ void IndexIVFFlatB200::add_with_ids(int64_t n, const float* x, const int64_t* xi
 void IndexIVFFlatB200::add_core(int64_t n, const float* x, const int64_t* xids,
                                 const int64_t* assign) {
     std::lock_guard<std::mutex> lock(mu_);
+    add_core_(n, x, xids, assign);
+}
+
+void IndexIVFFlatB200::add_core_(int64_t n, const float* x, const int64_t* xids,
+                                 const int64_t* assign) {
     DeviceGuard g(device_);
     Impl& m = *impl_;
     B200_THROW_IF_NOT_MSG(is_trained, "index not trained"); // IndexIVFFlat.cpp:52
@@ -1148,6 +1253,381 @@ void IndexIVFFlatB200::add_core(int64_t n, const float* x, const int64_t* xids,
     m.slab_blocks = blocks;
     m.nstored += nadd;
     ntotal += n; // IndexIVFFlat.cpp:90: every input vector counts, skipped or not
+}
+
+// ------------------------------------------------------------------------------------------------
+// range search: IndexIVF::range_search (faiss/IndexIVF.cpp:1203-1241) -> range_search_preassigned
+// (:1243-1399, parallel_mode 0: every probe of every query is scanned, max_codes is not consulted
+// on that path) -> IVFFlatScanner::scan_codes_range (faiss/IndexIVFFlat.cpp:181-201). Results of a
+// query come out in probe order, then list order, as RangeQueryResult::add appends them.
+// ------------------------------------------------------------------------------------------------
+void IndexIVFFlatB200::range_search(int64_t n, const float* x, float radius,
+                                    RangeSearchResult* result,
+                                    const SearchParametersIVF* params) const {
+    range_impl_(n, x, radius, nullptr, result, false, params);
+}
+
+void IndexIVFFlatB200::range_search_preassigned(int64_t n, const float* x, float radius,
+                                                const int64_t* assign, const float* /*cdis*/,
+                                                RangeSearchResult* result, bool store_pairs,
+                                                const SearchParametersIVF* params) const {
+    B200_THROW_IF_NOT_MSG(assign != nullptr, "null assign table");
+    range_impl_(n, x, radius, assign, result, store_pairs, params);
+}
+
+void IndexIVFFlatB200::range_impl_(int64_t n, const float* x, float radius, const int64_t* assign,
+                                   RangeSearchResult* result, bool store_pairs,
+                                   const SearchParametersIVF* params) const {
+    std::lock_guard<std::mutex> lock(mu_);
+    DeviceGuard g(device_);
+    Impl& m = *impl_;
+    B200_THROW_IF_NOT_MSG(is_trained, "index not trained");
+    B200_THROW_IF_NOT_MSG(result != nullptr, "null result");
+    B200_THROW_IF_NOT_MSG((int64_t)result->nq == n, "result->nq must equal the number of queries");
+    const int64_t np = (int64_t)std::min(nlist, params ? params->nprobe : nprobe);
+    B200_THROW_IF_NOT_MSG(np > 0, "nprobe > 0"); // faiss/IndexIVF.cpp:1255
+    B200_THROW_IF_NOT_MSG(np <= 2048, "nprobe is limited to 2048");
+    const IDSelector* sel = params ? params->sel : nullptr;
+    B200_THROW_IF_NOT_MSG(!(sel && store_pairs), "selector and store_pairs cannot be combined");
+    result->lims.assign((size_t)n + 1, 0);
+    result->labels.clear();
+    result->distances.clear();
+    for (double& v : m.last_ms)
+        v = 0;
+    if (n == 0)
+        return;
+    B200_THROW_IF_NOT_MSG(x != nullptr, "null buffer");
+    cudaStream_t st = m.stream;
+    unsigned long long* dstats = m.dev_stats.as<unsigned long long>();
+    const bool x_dev = is_device_pointer(x);
+    const bool a_dev = assign && is_device_pointer(assign);
+    const uint32_t* row_mask = nullptr;
+    if (sel && m.slab_blocks > 0) {
+        m.row_mask.reserve(m.slab_blocks * sizeof(uint32_t));
+        sel->eval(m.ids.as<int64_t>(), (int64_t)m.slab_blocks, m.row_mask.as<uint32_t>(), st);
+        row_mask = m.row_mask.as<uint32_t>();
+    }
+    int64_t nb = std::min<int64_t>(n, 32768);
+    while (nb > 1 && nb * np > ((int64_t)1 << 26))
+        nb = (nb + 1) / 2;
+    size_t base = 0;
+    for (int64_t i0 = 0; i0 < n; i0 += nb) {
+        const int64_t ni = std::min(nb, n - i0);
+        const int64_t pairs = ni * np;
+        CUDA_CHECK(cudaEventRecord(m.ev[0], st));
+        const float* xd = x + i0 * d;
+        if (!x_dev) {
+            m.dev_x.reserve((size_t)ni * d * sizeof(float));
+            CUDA_CHECK(cudaMemcpyAsync(m.dev_x.p, xd, (size_t)ni * d * sizeof(float),
+                                       cudaMemcpyHostToDevice, st));
+            xd = m.dev_x.as<float>();
+        }
+        m.coarse_ids.reserve((size_t)pairs * sizeof(int32_t));
+        m.coarse_dis.reserve((size_t)pairs * sizeof(float));
+        if (assign) {
+            const int64_t* ad = assign + i0 * np;
+            if (!a_dev) {
+                m.dev_assign64.reserve((size_t)pairs * sizeof(int64_t));
+                CUDA_CHECK(cudaMemcpyAsync(m.dev_assign64.p, ad, (size_t)pairs * sizeof(int64_t),
+                                           cudaMemcpyHostToDevice, st));
+                ad = m.dev_assign64.as<int64_t>();
+            }
+            CUDA_CHECK(launch_i64_to_i32(ad, m.coarse_ids.as<int32_t>(), pairs, 0, (int32_t)nlist,
+                                         dstats + 3, st));
+        } else {
+            run_coarse_(xd, ni, (int)np, m.coarse_ids.as<int32_t>(), nullptr,
+                        m.coarse_dis.as<float>(), st);
+        }
+        CUDA_CHECK(cudaEventRecord(m.ev[1], st));
+        // plan with one query per item and no row split: item == pair slot
+        m.count.reserve(nlist * sizeof(int32_t));
+        m.fill.reserve(nlist * sizeof(int32_t));
+        m.grp_start.reserve((nlist + 1) * sizeof(int32_t));
+        m.item_off.reserve((nlist + 1) * sizeof(uint32_t));
+        m.pair_query.reserve((size_t)pairs * sizeof(int32_t));
+        m.slot_of.reserve((size_t)pairs * sizeof(int32_t));
+        PlanArgs pa;
+        pa.coarse_ids = m.coarse_ids.as<int32_t>();
+        pa.n = (int)ni;
+        pa.nprobe = (int)np;
+        pa.nlists = (int)nlist;
+        pa.list_len = m.list_len.as<int32_t>();
+        pa.count = m.count.as<int32_t>();
+        pa.fill = m.fill.as<int32_t>();
+        pa.grp_start = m.grp_start.as<int32_t>();
+        pa.item_off = m.item_off.as<uint32_t>();
+        pa.pair_query = m.pair_query.as<int32_t>();
+        pa.slot_of = m.slot_of.as<int32_t>();
+        pa.rq = 1;
+        pa.nsplit = 1;
+        pa.tile_tq = 0;
+        pa.tile_min = 0;
+        pa.item_off_tile = nullptr;
+        pa.stats = dstats;
+        CUDA_CHECK(launch_plan(pa, st));
+        m.pair_cnt.reserve((size_t)pairs * sizeof(int32_t));
+        m.pair_off.reserve((size_t)pairs * sizeof(uint32_t));
+        m.qcnt.reserve((size_t)ni * sizeof(unsigned long long));
+        m.lims.reserve((size_t)(ni + 1) * sizeof(unsigned long long));
+        m.host_lims.reserve((size_t)(ni + 1) * sizeof(unsigned long long));
+        RangeArgs ra;
+        ra.slab = m.slab.as<float4>();
+        ra.list_blk0 = m.list_blk0.as<uint32_t>();
+        ra.list_len = m.list_len.as<int32_t>();
+        ra.grp_start = pa.grp_start;
+        ra.pair_query = pa.pair_query;
+        ra.nlists = (int)nlist;
+        ra.d = d;
+        ra.nf4 = m.nf4;
+        ra.queries = xd;
+        ra.radius = radius;
+        ra.row_mask = row_mask;
+        ra.ids = store_pairs ? nullptr : m.ids.as<int64_t>();
+        ra.pair_cnt = m.pair_cnt.as<int32_t>();
+        CUDA_CHECK(launch_range_scan(metric_type, false, pairs, ra, st));
+        CUDA_CHECK(launch_range_offsets(pa.slot_of, m.pair_cnt.as<int32_t>(), (int)ni, (int)np,
+                                        m.pair_off.as<uint32_t>(),
+                                        m.qcnt.as<unsigned long long>(),
+                                        m.lims.as<unsigned long long>(), st));
+        CUDA_CHECK(cudaMemcpyAsync(m.host_lims.p, m.lims.p,
+                                   (size_t)(ni + 1) * sizeof(unsigned long long),
+                                   cudaMemcpyDeviceToHost, st));
+        CUDA_CHECK(cudaMemcpyAsync(m.host_stats.p, dstats, 4 * sizeof(unsigned long long),
+                                   cudaMemcpyDeviceToHost, st));
+        CUDA_CHECK(cudaStreamSynchronize(st));
+        const unsigned long long* hl = m.host_lims.as<unsigned long long>();
+        const size_t total = (size_t)hl[ni];
+        if (total > 0) {
+            m.range_dis.reserve(total * sizeof(float));
+            m.range_ids.reserve(total * sizeof(int64_t));
+            ra.pair_off = m.pair_off.as<uint32_t>();
+            ra.lims = m.lims.as<unsigned long long>();
+            ra.out_dis = m.range_dis.as<float>();
+            ra.out_ids = m.range_ids.as<int64_t>();
+            CUDA_CHECK(launch_range_scan(metric_type, true, pairs, ra, st));
+            if (store_pairs)
+                CUDA_CHECK(launch_rows_to_pairs(m.range_ids.as<int64_t>(), (int64_t)total,
+                                                m.list_blk0.as<uint32_t>(), (int)nlist, st));
+            result->distances.resize(base + total);
+            result->labels.resize(base + total);
+            CUDA_CHECK(cudaMemcpyAsync(result->distances.data() + base, m.range_dis.p,
+                                       total * sizeof(float), cudaMemcpyDeviceToHost, st));
+            CUDA_CHECK(cudaMemcpyAsync(result->labels.data() + base, m.range_ids.p,
+                                       total * sizeof(int64_t), cudaMemcpyDeviceToHost, st));
+        }
+        CUDA_CHECK(cudaEventRecord(m.ev[5], st));
+        CUDA_CHECK(cudaStreamSynchronize(st));
+        for (int64_t i = 0; i < ni; ++i)
+            result->lims[(size_t)(i0 + i)] = base + (size_t)hl[i];
+        base += total;
+        float ms;
+        CUDA_CHECK(cudaEventElapsedTime(&ms, m.ev[0], m.ev[1]));
+        m.last_ms[0] += ms;
+        CUDA_CHECK(cudaEventElapsedTime(&ms, m.ev[1], m.ev[5]));
+        m.last_ms[2] += ms;
+        CUDA_CHECK(cudaEventElapsedTime(&ms, m.ev[0], m.ev[5]));
+        m.last_ms[4] += ms;
+        const unsigned long long* hs = m.host_stats.as<unsigned long long>();
+        if (hs[3] != 0) {
+            CUDA_CHECK(cudaMemset(dstats + 3, 0, sizeof(unsigned long long)));
+            throw B200Exception("Invalid key in range_search_preassigned (key >= nlist)");
+        }
+    }
+    result->lims[(size_t)n] = base;
+    const unsigned long long* hs = m.host_stats.as<unsigned long long>();
+    m.stats.nq = (size_t)hs[0];
+    m.stats.nlist = (size_t)hs[1];
+    m.stats.ndis = (size_t)hs[2];
+    m.stats.quantization_time += m.last_ms[0];
+    m.stats.search_time += m.last_ms[4];
+}
+
+// ------------------------------------------------------------------------------------------------
+// training: IndexIVF::train (faiss/IndexIVF.cpp:1404-1423) -> Level1Quantizer::train_q1 (:66-127,
+// quantizer_trains_alone == 0) -> Clustering::train_encoded (faiss/Clustering.cpp:296-600) with the
+// flat quantizer of the index's own metric as the assignment index. The host keeps the reference's
+// control flow and random choices (std::mt19937 subsample and initial picks, split_clusters); the
+// device does the work: assignment = K1 with k = 1, update = the add path (rows grouped per list
+// in input order) followed by list_means_kernel, which sums a list's rows in that order -- the
+// order compute_centroids uses (:183-204) -- so equal assignments give bit-equal centroids.
+// ------------------------------------------------------------------------------------------------
+namespace {
+
+// faiss::rand_perm (faiss/utils/random.cpp:184-194) over RandomGenerator == std::mt19937
+std::vector<int64_t> ref_rand_perm(size_t n, int64_t seed) {
+    std::vector<int64_t> perm(n);
+    for (size_t i = 0; i < n; ++i)
+        perm[i] = (int64_t)i;
+    std::mt19937 mt((unsigned int)seed);
+    for (size_t i = 0; i + 1 < n; ++i) {
+        const size_t i2 = i + (size_t)(mt() % (unsigned long)(int)(n - i));
+        std::swap(perm[i], perm[i2]);
+    }
+    return perm;
+}
+
+// Clustering::post_process_centroids with spherical set (faiss/Clustering.cpp:52-56,
+// fvec_renorm_L2 faiss/utils/distances.cpp:95-105)
+void renorm_rows(std::vector<float>& c, size_t k, size_t d) {
+    for (size_t i = 0; i < k; ++i) {
+        float* xi = c.data() + i * d;
+        float nr = 0.f;
+        for (size_t j = 0; j < d; ++j)
+            nr += xi[j] * xi[j];
+        if (nr > 0) {
+            const float inv_nr = (float)(1.0 / sqrtf(nr));
+            for (size_t j = 0; j < d; ++j)
+                xi[j] *= inv_nr;
+        }
+    }
+}
+
+// split_clusters (faiss/Clustering.cpp:232-276): an empty cluster takes a copy of a big one, chosen
+// with probability proportional to its size, both perturbed symmetrically by 1/1024
+int split_clusters_host(size_t d, size_t k, size_t n, std::vector<float>& hassign,
+                        std::vector<float>& centroids) {
+    int nsplit = 0;
+    if (n <= k)
+        return 0; // (the reference's pick loop cannot terminate in that case)
+    std::mt19937 rng(1234);
+    const double eps = 1 / 1024.;
+    for (size_t ci = 0; ci < k; ++ci) {
+        if (hassign[ci] != 0)
+            continue;
+        size_t cj;
+        for (cj = 0; true; cj = (cj + 1) % k) {
+            const float p = (float)((hassign[cj] - 1.0) / (float)(n - k));
+            const float r = rng() / float(rng.max());
+            if (r < p)
+                break;
+        }
+        std::memcpy(centroids.data() + ci * d, centroids.data() + cj * d, sizeof(float) * d);
+        for (size_t j = 0; j < d; ++j) {
+            float& a = centroids[ci * d + j];
+            float& b = centroids[cj * d + j];
+            if (j % 2 == 0) {
+                a = (float)(a * (1 + eps));
+                b = (float)(b * (1 - eps));
+            } else {
+                a = (float)(a * (1 - eps));
+                b = (float)(b * (1 + eps));
+            }
+        }
+        hassign[ci] = hassign[cj] / 2;
+        hassign[cj] -= hassign[ci];
+        nsplit++;
+    }
+    return nsplit;
+}
+
+} // namespace
+
+void IndexIVFFlatB200::train(int64_t n, const float* x) {
+    std::lock_guard<std::mutex> lock(mu_);
+    DeviceGuard g(device_);
+    Impl& m = *impl_;
+    if (is_trained) // "IVF quantizer does not need training", faiss/IndexIVF.cpp:72-74
+        return;
+    B200_THROW_IF_NOT_MSG(x != nullptr, "null training vectors");
+    B200_THROW_IF_NOT_MSG(n >= (int64_t)nlist, // faiss/Clustering.cpp:302-306
+                          "Number of training points should be at least as large as number of clusters");
+    B200_THROW_IF_NOT_MSG(m.nstored == 0 && ntotal == 0, "train needs an empty index");
+    cudaStream_t st = m.stream;
+    const size_t k = nlist, dd = (size_t)d;
+    const bool x_dev = is_device_pointer(x);
+
+    // subsample_training_set (faiss/Clustering.cpp:86-133): the first k * max_points_per_centroid
+    // entries of a seeded permutation
+    int64_t nx = n;
+    std::vector<int64_t> pick;
+    if ((size_t)n > k * (size_t)cp_max_points_per_centroid) {
+        pick = ref_rand_perm((size_t)n, cp_seed);
+        nx = (int64_t)(k * (size_t)cp_max_points_per_centroid);
+        pick.resize((size_t)nx);
+    }
+    Buffer xt, didx, dcent;
+    const float* xt_dev = x;
+    auto cleanup = [&] {
+        xt.release();
+        didx.release();
+        dcent.release();
+    };
+    try {
+        if (!pick.empty() || !x_dev) {
+            xt.reserve((size_t)nx * dd * sizeof(float));
+            if (x_dev) {
+                didx.reserve((size_t)nx * sizeof(int64_t));
+                CUDA_CHECK(cudaMemcpyAsync(didx.p, pick.data(), (size_t)nx * sizeof(int64_t),
+                                           cudaMemcpyHostToDevice, st));
+                CUDA_CHECK(launch_gather_by_index(x, didx.as<int64_t>(), nx, d, xt.as<float>(), st));
+                CUDA_CHECK(cudaStreamSynchronize(st));
+            } else if (pick.empty()) {
+                CUDA_CHECK(cudaMemcpy(xt.p, x, (size_t)nx * dd * sizeof(float),
+                                      cudaMemcpyHostToDevice));
+            } else {
+                std::vector<float> hx((size_t)nx * dd);
+                for (int64_t i = 0; i < nx; ++i)
+                    std::memcpy(hx.data() + (size_t)i * dd, x + (size_t)pick[(size_t)i] * dd,
+                                dd * sizeof(float));
+                CUDA_CHECK(cudaMemcpy(xt.p, hx.data(), hx.size() * sizeof(float),
+                                      cudaMemcpyHostToDevice));
+            }
+            xt_dev = xt.as<float>();
+        }
+        // initial centroids: k random training points (faiss/Clustering.cpp:425-441)
+        std::vector<int64_t> perm = ref_rand_perm((size_t)nx, (int64_t)cp_seed + 1);
+        perm.resize(k);
+        didx.reserve(k * sizeof(int64_t));
+        dcent.reserve(k * dd * sizeof(float));
+        CUDA_CHECK(cudaMemcpyAsync(didx.p, perm.data(), k * sizeof(int64_t), cudaMemcpyHostToDevice,
+                                   st));
+        CUDA_CHECK(launch_gather_by_index(xt_dev, didx.as<int64_t>(), (int64_t)k, d,
+                                          dcent.as<float>(), st));
+        std::vector<float> cent(k * dd);
+        CUDA_CHECK(cudaMemcpyAsync(cent.data(), dcent.p, k * dd * sizeof(float),
+                                   cudaMemcpyDeviceToHost, st));
+        CUDA_CHECK(cudaStreamSynchronize(st));
+        const bool spherical = metric_type == kMetricInnerProduct; // faiss/IndexIVF.cpp:179-182
+        if (spherical)
+            renorm_rows(cent, k, dd);
+
+        // Lloyd iterations over the whole list range, whatever shard this handle serves
+        const size_t keep_lo = m.list_lo, keep_hi = m.list_hi;
+        m.list_lo = 0;
+        m.list_hi = nlist;
+        try {
+            std::vector<float> hassign(k);
+            for (int it = 0; it < cp_niter; ++it) {
+                set_centroids_(cent.data());
+                reset_();
+                add_core_(nx, xt_dev, nullptr, nullptr); // assign (K1, k = 1) + group rows by list
+                CUDA_CHECK(launch_list_means(m.slab.as<float>(), m.list_blk0.as<uint32_t>(),
+                                             m.list_len.as<int32_t>(), (int)nlist, d, m.nf4,
+                                             dcent.as<float>(), st));
+                CUDA_CHECK(cudaMemcpyAsync(cent.data(), dcent.p, k * dd * sizeof(float),
+                                           cudaMemcpyDeviceToHost, st));
+                CUDA_CHECK(cudaStreamSynchronize(st));
+                for (size_t l = 0; l < k; ++l)
+                    hassign[l] = (float)m.h_len[l];
+                split_clusters_host(dd, k, (size_t)nx, hassign, cent);
+                if (spherical)
+                    renorm_rows(cent, k, dd);
+            }
+        } catch (...) {
+            m.list_lo = keep_lo;
+            m.list_hi = keep_hi;
+            is_trained = false;
+            throw;
+        }
+        reset_();
+        m.list_lo = keep_lo;
+        m.list_hi = keep_hi;
+        set_centroids_(cent.data()); // quantizer->add(nlist, centroids); is_trained = true
+    } catch (...) {
+        cleanup();
+        throw;
+    }
+    cleanup();
 }
 
 void merge_knn_results(int metric, int nshard, int64_t n, int64_t k, const float* all_D,

@@ -24,6 +24,26 @@ struct IndexIVFStatsB200 { // faiss/IndexIVF.h:567-580
     double quantization_time = 0, search_time = 0;
 };
 
+// per-query figures of the fork's IndexIVF::search_stats (faiss/IndexIVF.h:28-32), microseconds
+struct QueryLatencyStats {
+    double total_us = 0.0;
+    double quantization_us = 0.0;
+    double list_scan_us = 0.0;
+};
+
+struct IDSelector;          // selector.h
+struct SearchParametersIVF; // selector.h
+
+// faiss::RangeSearchResult (faiss/impl/AuxIndexStructures.h:30-58): query i has results
+// lims[i]..lims[i+1] in labels / distances; host memory owned by the object
+struct RangeSearchResult {
+    size_t nq = 0;
+    std::vector<size_t> lims; // [nq + 1]
+    std::vector<int64_t> labels;
+    std::vector<float> distances;
+    explicit RangeSearchResult(size_t nq_) : nq(nq_), lims(nq_ + 1, 0) {}
+};
+
 // grow-only device / pinned-host buffer
 struct Buffer {
     void* p = nullptr;
@@ -51,6 +71,11 @@ class IndexIVFFlatB200 {
     size_t nprobe = 1;
     int64_t ntotal = 0;
     bool is_trained = false;
+    size_t max_codes = 0; // faiss/IndexIVF.h:96 (0 = no limit)
+    // Level1Quantizer::cp as IndexIVF sets it up (faiss/IndexIVF.cpp:55, :179-182; Clustering.h:23-64)
+    int cp_niter = 10;
+    int cp_seed = 1234;
+    int cp_max_points_per_centroid = 256;
 
     void set_centroids(const float* c);
     void get_centroids(float* out) const;
@@ -62,10 +87,28 @@ class IndexIVFFlatB200 {
     void get_list_ids(size_t l, int64_t* out) const;
     void get_list_codes(size_t l, float* out) const;
 
-    void search(int64_t n, const float* x, int64_t k, float* D, int64_t* I) const;
+    // IndexIVF::train -> Level1Quantizer::train_q1 -> Clustering::train with the flat quantizer
+    // as the assignment index (faiss/IndexIVF.cpp:66-127, faiss/Clustering.cpp:296-600); a no-op
+    // when the quantizer already holds nlist centroids (:72-74). The index must be empty.
+    void train(int64_t n, const float* x);
+
+    // params (nullptr: the handle's nprobe / max_codes, no selector) and per_query_stats (nullptr:
+    // not wanted; HOST array of n entries) are the reference's SearchParametersIVF
+    // (faiss/IndexIVF.h:73-88) and the fork's QueryLatencyStats (search_stats, IndexIVF.cpp:727)
+    void search(int64_t n, const float* x, int64_t k, float* D, int64_t* I,
+                const SearchParametersIVF* params = nullptr,
+                QueryLatencyStats* per_query_stats = nullptr) const;
     void search_preassigned(int64_t n, const float* x, int64_t k, const int64_t* assign,
-                            const float* centroid_dis, float* D, int64_t* I,
-                            bool store_pairs) const;
+                            const float* centroid_dis, float* D, int64_t* I, bool store_pairs,
+                            const SearchParametersIVF* params = nullptr,
+                            QueryLatencyStats* per_query_stats = nullptr) const;
+    // IndexIVF::range_search / range_search_preassigned (faiss/IndexIVF.cpp:1203-1399)
+    void range_search(int64_t n, const float* x, float radius, RangeSearchResult* result,
+                      const SearchParametersIVF* params = nullptr) const;
+    void range_search_preassigned(int64_t n, const float* x, float radius, const int64_t* assign,
+                                  const float* centroid_dis, RangeSearchResult* result,
+                                  bool store_pairs = false,
+                                  const SearchParametersIVF* params = nullptr) const;
     void quantize(int64_t n, const float* x, int64_t nprobe, float* Dq, int64_t* Iq) const;
 
     IndexIVFStatsB200 get_stats() const;
@@ -79,6 +122,15 @@ class IndexIVFFlatB200 {
 
   private:
     struct Impl;
+    void set_centroids_(const float* c);
+    void reset_();
+    void add_core_(int64_t n, const float* x, const int64_t* xids, const int64_t* assign);
+    void search_impl_(int64_t n, const float* x, int64_t k, const int64_t* assign, float* D,
+                      int64_t* I, bool store_pairs, const SearchParametersIVF* params,
+                      QueryLatencyStats* per_query) const;
+    void range_impl_(int64_t n, const float* x, float radius, const int64_t* assign,
+                     RangeSearchResult* result, bool store_pairs,
+                     const SearchParametersIVF* params) const;
     // K1: the kc nearest centroids of n device-resident queries (ids as int32 and/or int64)
     void run_coarse_(const float* xd, int64_t n, int kc, int32_t* out_ids32, int64_t* out_ids64,
                      float* out_dis, cudaStream_t st) const;

@@ -37,6 +37,9 @@ struct ScanArgs {
     uint64_t* part;             // [npairs][nsplit][part_mul][k] keys out
     int part_mul = 1;           // 2 when the tensor-core scan shares `part` (it leaves two lists
                                 // per (pair, split)): the second one is filled with sentinels
+    // SearchParametersIVF (either one non-null selects the filtered kernel, rv must be 4):
+    const uint32_t* row_mask = nullptr;  // [slab blocks] selector mask, bit = row in block
+    const int32_t* pair_limit = nullptr; // [npairs] rows of the list that count for the pair
 };
 
 // rq in {1,4,8}; warps_per_cta chosen by the caller so that shared memory fits.
@@ -143,11 +146,53 @@ struct PlanArgs {
     uint32_t* item_off_tile;    // [nlists+1] out (may be nullptr when tile_tq == 0)
     int32_t* item_list_tile = nullptr; // [tile items] out: list of each tile item (optional)
     unsigned long long* stats;  // [4] += {nq, nlist visited, ndis, invalid keys}
+    // max_codes: rows that count for each (query, probe) from launch_probe_limits, and the same
+    // re-ordered by pair slot for the scan (both nullptr: every probed list counts whole)
+    const int32_t* limit_qp = nullptr; // [n][nprobe]
+    int32_t* limit_slot = nullptr;     // [n*nprobe] out
 };
+// max_codes walk of IndexIVF::search_preassigned (faiss/IndexIVF.cpp:597-631): writes the rows
+// that count per (query, probe) (limit_qp, may be nullptr), turns the probes after the stop into
+// -1 in coarse_ids, and leaves each query's nscan in query_ndis (may be nullptr).
+// max_codes <= 0 is not accepted: pass LLONG_MAX for "no limit".
+cudaError_t launch_probe_limits(int32_t* coarse_ids, int n, int nprobe, int nlists,
+                                const int32_t* list_len, long long max_codes, int32_t* limit_qp,
+                                unsigned long long* query_ndis, cudaStream_t st);
 cudaError_t launch_plan(const PlanArgs& a, cudaStream_t st);
 // the one-list plan used when the "list" is the centroid table and every query probes it
 cudaError_t launch_plan_single(int32_t* grp_start, uint32_t* item_off, int n, uint32_t items,
                                cudaStream_t st);
+
+// ---- range search (range.cu): IndexIVF::range_search_preassigned + scan_codes_range --------------
+// One warp per pair slot of a plan made with rq = 1, nsplit = 1 (item == pair slot). Two passes
+// with identical arithmetic: count, then fill at lims[query] + pair_off[slot].
+struct RangeArgs {
+    const float4* slab;
+    const uint32_t* list_blk0;
+    const int32_t* list_len;
+    const int32_t* grp_start;   // [nlists+1]
+    const int32_t* pair_query;  // [npairs]
+    int nlists;
+    int d, nf4;
+    const float* queries;
+    float radius;               // L2: dis < radius, inner product: dis > radius
+    const uint32_t* row_mask = nullptr; // selector mask or nullptr
+    const int64_t* ids = nullptr;       // slab row -> user id (nullptr: the row itself)
+    int32_t* pair_cnt = nullptr;        // [npairs] out of the count pass
+    const uint32_t* pair_off = nullptr; // [npairs] offset of the pair inside its query's run
+    const unsigned long long* lims = nullptr; // [n+1] first result of each query
+    float* out_dis = nullptr;
+    int64_t* out_ids = nullptr;
+};
+cudaError_t launch_range_scan(int metric, bool fill, int64_t max_pairs, const RangeArgs& a,
+                              cudaStream_t st);
+// pair_cnt + slot_of -> pair_off, qcnt[n] (hits per query), lims[n+1] (exclusive prefix)
+cudaError_t launch_range_offsets(const int32_t* slot_of, const int32_t* pair_cnt, int n, int nprobe,
+                                 uint32_t* pair_off, unsigned long long* qcnt,
+                                 unsigned long long* lims, cudaStream_t st);
+// store_pairs labels: slab row -> list_no << 32 | offset (faiss/invlists/DirectMap.h:22-24)
+cudaError_t launch_rows_to_pairs(int64_t* labels, int64_t n, const uint32_t* list_blk0, int nlists,
+                                 cudaStream_t st);
 
 // ---- K3: per-query k-select over the partial candidate lists ------------------------------------
 // Replaces heap_reorder (faiss/utils/Heap.h:420-450) / the CPU heap of search_preassigned.
@@ -193,6 +238,13 @@ cudaError_t launch_gather_rows(const float* slab, int64_t row0, int64_t nrows, i
 cudaError_t launch_row_norms(const float4* slab, int64_t nrows, int nf4, float* norms,
                              cudaStream_t st);
 cudaError_t launch_fill_u32(uint32_t* p, int64_t n, uint32_t v, cudaStream_t st);
+// k-means update (Clustering.cpp:150-221 compute_centroids): centroid l = sum of the rows of list l
+// in list order (= input order, the reference's summation order) times 1/len; empty lists give 0
+cudaError_t launch_list_means(const float* slab, const uint32_t* list_blk0, const int32_t* list_len,
+                              int nlists, int d, int nf4, float* centroids, cudaStream_t st);
+// out[i] = x[idx[i]] for row-major [.][d] tables
+cudaError_t launch_gather_by_index(const float* x, const int64_t* idx, int64_t n, int d, float* out,
+                                   cudaStream_t st);
 cudaError_t launch_i64_to_i32(const int64_t* in, int32_t* out, int64_t n, int32_t lo, int32_t hi,
                               unsigned long long* bad, cudaStream_t st);
 

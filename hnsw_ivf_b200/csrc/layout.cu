@@ -173,4 +173,57 @@ cudaError_t launch_i64_to_i32(const int64_t* in, int32_t* out, int64_t n, int32_
     return cudaGetLastError();
 }
 
+namespace {
+// one thread per (list, dimension): a strictly sequential sum over the list's rows, so that the
+// result is the reference's (Clustering.cpp:183-204: c[j] += xi[j] in input order, then *= 1/n)
+__global__ void list_means_kernel(const float* __restrict__ slab,
+                                  const uint32_t* __restrict__ list_blk0,
+                                  const int32_t* __restrict__ list_len, int d, int nf4,
+                                  float* __restrict__ centroids) {
+    const int l = blockIdx.x;
+    const int len = list_len[l];
+    const size_t row0 = (size_t)list_blk0[l] * kBlockRows;
+    for (int dd = threadIdx.x; dd < d; dd += blockDim.x) {
+        float c = 0.f;
+        for (int r = 0; r < len; ++r)
+            c += slab[slab_float_index(row0 + r, dd, nf4)];
+        if (len > 0)
+            c *= 1.f / (float)len;
+        centroids[(size_t)l * d + dd] = c;
+    }
+}
+
+__global__ void gather_by_index_kernel(const float* __restrict__ x, const int64_t* __restrict__ idx,
+                                       int64_t n, int d, float* __restrict__ out) {
+    const int64_t total = n * d;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / d;
+        out[i] = x[idx[r] * d + (i - r * d)];
+    }
+}
+} // namespace
+
+cudaError_t launch_list_means(const float* slab, const uint32_t* list_blk0, const int32_t* list_len,
+                              int nlists, int d, int nf4, float* centroids, cudaStream_t st) {
+    if (nlists == 0)
+        return cudaSuccess;
+    const int threads = d >= 256 ? 256 : (d >= 128 ? 128 : 64);
+    list_means_kernel<<<nlists, threads, 0, st>>>(slab, list_blk0, list_len, d, nf4, centroids);
+    count_launches(1);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_gather_by_index(const float* x, const int64_t* idx, int64_t n, int d, float* out,
+                                   cudaStream_t st) {
+    if (n == 0)
+        return cudaSuccess;
+    const int threads = 256;
+    const int64_t total = n * d;
+    const int grid = (int)std::min<int64_t>((total + threads - 1) / threads, 148 * 16);
+    gather_by_index_kernel<<<grid, threads, 0, st>>>(x, idx, n, d, out);
+    count_launches(1);
+    return cudaGetLastError();
+}
+
 } // namespace b200ivf

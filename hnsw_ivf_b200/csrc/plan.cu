@@ -32,7 +32,7 @@ __global__ void plan_count_kernel(const PlanArgs a) {
         if (len == 0)
             continue;
         atomicAdd(&a.count[l], 1);
-        ndis += (unsigned long long)len;
+        ndis += (unsigned long long)(a.limit_qp ? a.limit_qp[i] : len);
         nvis++;
     }
     // warp-reduce the counters, one atomic per warp
@@ -153,8 +153,40 @@ __global__ void plan_scatter_kernel(const PlanArgs a) {
         if (l >= 0 && l < a.nlists && a.list_len[l] > 0) {
             slot = a.grp_start[l] + atomicAdd(&a.fill[l], 1);
             a.pair_query[slot] = (int)(i / a.nprobe);
+            if (a.limit_slot)
+                a.limit_slot[slot] = a.limit_qp[i];
         }
         a.slot_of[i] = slot;
+    }
+}
+
+// max_codes (faiss/IndexIVF.cpp:597-631, parallel_mode 0): a query walks its probes in order, a
+// list counts for min(list_size, max_codes - nscan) rows (scan_one_list's list_size_max, :545-548)
+// and the walk stops once nscan >= max_codes. One thread per query; probes after the stop are
+// turned into -1 in the probe table (keys < 0 and empty lists count for 0 rows, :512-529).
+__global__ void probe_limits_kernel(int32_t* coarse_ids, int n, int nprobe, int nlists,
+                                    const int32_t* __restrict__ list_len, long long max_codes,
+                                    int32_t* limit_qp, unsigned long long* query_ndis) {
+    for (int q = blockIdx.x * blockDim.x + threadIdx.x; q < n; q += gridDim.x * blockDim.x) {
+        long long nscan = 0;
+        bool stop = false;
+        for (int p = 0; p < nprobe; ++p) {
+            const int64_t i = (int64_t)q * nprobe + p;
+            const int l = coarse_ids[i];
+            int lim = 0;
+            if (stop) {
+                coarse_ids[i] = -1;
+            } else if (l >= 0 && l < nlists) {
+                const long long len = list_len[l];
+                lim = (int)(len < max_codes - nscan ? len : max_codes - nscan);
+                nscan += lim;
+                stop = len > 0 && nscan >= max_codes;
+            }
+            if (limit_qp)
+                limit_qp[i] = lim;
+        }
+        if (query_ndis)
+            query_ndis[q] = (unsigned long long)nscan;
     }
 }
 
@@ -170,6 +202,18 @@ __global__ void plan_single_kernel(int32_t* grp_start, uint32_t* item_off, int n
 cudaError_t launch_plan_single(int32_t* grp_start, uint32_t* item_off, int n, uint32_t items,
                                cudaStream_t st) {
     plan_single_kernel<<<1, 1, 0, st>>>(grp_start, item_off, n, items);
+    count_launches(1);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_probe_limits(int32_t* coarse_ids, int n, int nprobe, int nlists,
+                                const int32_t* list_len, long long max_codes, int32_t* limit_qp,
+                                unsigned long long* query_ndis, cudaStream_t st) {
+    if (n == 0)
+        return cudaSuccess;
+    const int threads = 128;
+    probe_limits_kernel<<<(n + threads - 1) / threads, threads, 0, st>>>(
+            coarse_ids, n, nprobe, nlists, list_len, max_codes, limit_qp, query_ndis);
     count_launches(1);
     return cudaGetLastError();
 }

@@ -65,7 +65,11 @@ __device__ __forceinline__ float accumulate4(float acc, const float4& x, const f
     return acc;
 }
 
-template <int METRIC, int RQ, int RV>
+// FILT: the SearchParametersIVF form (faiss/IndexIVF.h:73-88) -- rows are kept only where the
+// selector's row mask has their bit (IVFFlatScanner::scan_codes' use_sel arm,
+// faiss/IndexIVFFlat.cpp:166) and, for max_codes, only the first pair_limit[slot] rows of the list
+// count for that pair (scan_one_list's list_size_max, faiss/IndexIVF.cpp:545-548).
+template <int METRIC, int RQ, int RV, bool FILT>
 __global__ void __launch_bounds__(256) ivf_scan_kernel(const ScanArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31;
@@ -126,10 +130,12 @@ __global__ void __launch_bounds__(256) ivf_scan_kernel(const ScanArgs a) {
 
     float thr[RQ];
     int cnt[RQ];
+    int lim[RQ];
 #pragma unroll
     for (int j = 0; j < RQ; ++j) {
         thr[j] = kNeutralScore;
         cnt[j] = 0;
+        lim[j] = (FILT && a.pair_limit && j < nqw) ? a.pair_limit[q0 + j] : len;
     }
 
     const uint32_t blk0 = a.list_blk0[l];
@@ -165,13 +171,16 @@ __global__ void __launch_bounds__(256) ivf_scan_kernel(const ScanArgs a) {
 #pragma unroll
         for (int v = 0; v < RV; ++v) {
             const int row = (b + v) * kBlockRows + lane;
-            const bool rowok = (b + v < b1) && (row < len);
+            bool rowok = (b + v < b1) && (row < len);
+            if (FILT && a.row_mask && b + v < b1)
+                rowok = rowok && ((a.row_mask[blk0 + (uint32_t)(b + v)] >> lane) & 1u);
             const uint32_t grow = blk0 * kBlockRows + (uint32_t)row;
 #pragma unroll
             for (int j = 0; j < RQ; ++j) {
                 // smaller is better; "+ 0.f" folds -0 into +0 so equal scores have equal keys
                 const float score = (METRIC == kMetricL2 ? acc[v][j] : -acc[v][j]) + 0.f;
-                const bool pass = rowok && (j < nqw) && (score < thr[j]);
+                const bool pass =
+                        rowok && (j < nqw) && (!FILT || row < lim[j]) && (score < thr[j]);
                 const unsigned m = __ballot_sync(0xffffffffu, pass);
                 if (m) {
                     PushState s = push_candidates(bufs + (size_t)j * a.cap, cnt[j], thr[j], a.k,
@@ -201,10 +210,10 @@ __global__ void __launch_bounds__(256) ivf_scan_kernel(const ScanArgs a) {
     }
 }
 
-template <int METRIC, int RQ, int RV>
+template <int METRIC, int RQ, int RV, bool FILT = false>
 cudaError_t launch_one(int wpc, uint32_t max_items, const ScanArgs& a, cudaStream_t st) {
     const size_t smem = scan_smem_bytes(RQ, wpc, a.nf4, a.cap);
-    auto kern = ivf_scan_kernel<METRIC, RQ, RV>;
+    auto kern = ivf_scan_kernel<METRIC, RQ, RV, FILT>;
     if (smem > 48 * 1024) {
         cudaError_t e =
                 cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -228,7 +237,20 @@ size_t scan_smem_bytes(int rq, int warps_per_cta, int nf4, int cap) {
 
 cudaError_t launch_ivf_scan(int metric, int rq, int wpc, uint32_t max_items, const ScanArgs& a,
                             cudaStream_t st, int rv) {
+    const bool filt = a.row_mask != nullptr || a.pair_limit != nullptr;
 #define B200IVF_DISPATCH(M)                                    \
+    if (filt) {                                                \
+        switch (rq) {                                          \
+            case 1:                                            \
+                return launch_one<M, 1, 4, true>(wpc, max_items, a, st); \
+            case 4:                                            \
+                return launch_one<M, 4, 4, true>(wpc, max_items, a, st); \
+            case 8:                                            \
+                return launch_one<M, 8, 4, true>(wpc, max_items, a, st); \
+            default:                                           \
+                return cudaErrorInvalidValue;                  \
+        }                                                      \
+    }                                                          \
     switch (rq) {                                              \
         case 1:                                                \
             if (rv == 1)                                       \

@@ -93,7 +93,8 @@ int b200_IndexIVFFlat_invlists_get_codes(const B200IndexIVFFlat* index, size_t l
 /* faiss_Index_search, c_api/Index_c.h:108-114 == IndexIVF::search faiss/IndexIVF.cpp:303 */
 int b200_IndexIVFFlat_search(const B200IndexIVFFlat* index, b200_idx_t n, const float* x,
                              b200_idx_t k, float* distances, b200_idx_t* labels);
-/* faiss_IndexIVF_search_preassigned, c_api/IndexIVF_c.h:112-121; store_pairs must be 0;
+/* faiss_IndexIVF_search_preassigned, c_api/IndexIVF_c.h:112-121; store_pairs != 0 returns
+ * list_no << 32 | offset as labels (faiss/IndexIVFFlat.cpp:172);
  * nprobe is the handle's nprobe; centroid_dis may be NULL (unused by IVFFlat,
  * faiss/IndexIVFFlat.cpp:143) */
 int b200_IndexIVFFlat_search_preassigned(const B200IndexIVFFlat* index, b200_idx_t n,
@@ -135,6 +136,102 @@ int b200_merge_knn_results(B200MetricType metric, int nshard, b200_idx_t n, b200
  * reference. io_flags is accepted for signature parity (no mmap: the lists live in HBM). */
 int b200_write_index_fname(const B200IndexIVFFlat* index, const char* fname);
 int b200_read_index_fname(const char* fname, int io_flags, int device, B200IndexIVFFlat** p_out);
+
+/* ---- training ------------------------------------------------------------------------------
+ * faiss_Index_train, c_api/Index_c.h:72 == IndexIVF::train faiss/IndexIVF.cpp:1404 -> k-means of
+ * Level1Quantizer::train_q1 (:66-127; niter 10, <= 256 points per centroid, spherical for inner
+ * product, :55,:179-182). A no-op when centroids are installed already; the index must be empty. */
+int b200_IndexIVFFlat_train(B200IndexIVFFlat* index, b200_idx_t n, const float* x);
+
+/* ---- IDSelector family ---------------------------------------------------------------------
+ * faiss/impl/IDSelector.h:19-170, C API c_api/impl/AuxIndexStructures_c.h:51-116. Batch and
+ * Bitmap copy their input (host pointers) to `device`. Not/And/Or/XOr borrow their operands,
+ * which must outlive them, as in the reference. */
+typedef struct B200IDSelector_H B200IDSelector;
+int b200_IDSelectorRange_new(B200IDSelector** p_sel, b200_idx_t imin, b200_idx_t imax);
+int b200_IDSelectorBatch_new(B200IDSelector** p_sel, size_t n, const b200_idx_t* indices,
+                             int device);
+int b200_IDSelectorBitmap_new(B200IDSelector** p_sel, size_t n, const uint8_t* bitmap, int device);
+int b200_IDSelectorNot_new(B200IDSelector** p_sel, const B200IDSelector* sel);
+int b200_IDSelectorAnd_new(B200IDSelector** p_sel, const B200IDSelector* lhs,
+                           const B200IDSelector* rhs);
+int b200_IDSelectorOr_new(B200IDSelector** p_sel, const B200IDSelector* lhs,
+                          const B200IDSelector* rhs);
+int b200_IDSelectorXOr_new(B200IDSelector** p_sel, const B200IDSelector* lhs,
+                           const B200IDSelector* rhs);
+/* faiss_IDSelector_is_member, AuxIndexStructures_c.h:54 */
+int b200_IDSelector_is_member(const B200IDSelector* sel, b200_idx_t id);
+void b200_IDSelector_free(B200IDSelector* sel);
+
+/* ---- SearchParametersIVF -------------------------------------------------------------------
+ * faiss/IndexIVF.h:73-88, C API c_api/IndexIVF_c.h:22-35. sel may be NULL and is borrowed. */
+typedef struct B200SearchParametersIVF_H B200SearchParametersIVF;
+int b200_SearchParametersIVF_new(B200SearchParametersIVF** p_sp);
+int b200_SearchParametersIVF_new_with(B200SearchParametersIVF** p_sp, B200IDSelector* sel,
+                                      size_t nprobe, size_t max_codes);
+void b200_SearchParametersIVF_free(B200SearchParametersIVF* sp);
+const B200IDSelector* b200_SearchParametersIVF_sel(const B200SearchParametersIVF* sp);
+size_t b200_SearchParametersIVF_nprobe(const B200SearchParametersIVF* sp);
+void b200_SearchParametersIVF_set_nprobe(B200SearchParametersIVF* sp, size_t nprobe);
+size_t b200_SearchParametersIVF_max_codes(const B200SearchParametersIVF* sp);
+void b200_SearchParametersIVF_set_max_codes(B200SearchParametersIVF* sp, size_t max_codes);
+
+/* IndexIVF::max_codes (faiss/IndexIVF.h:96), used when a search passes no params */
+size_t b200_IndexIVFFlat_max_codes(const B200IndexIVFFlat* index);
+void b200_IndexIVFFlat_set_max_codes(B200IndexIVFFlat* index, size_t max_codes);
+
+/* faiss_Index_search_with_params, c_api/Index_c.h:128-135: nprobe / max_codes / selector of
+ * `params` (faiss/IndexIVF.cpp:416-450,597-631; faiss/IndexIVFFlat.cpp:166) */
+int b200_IndexIVFFlat_search_with_params(const B200IndexIVFFlat* index, b200_idx_t n,
+                                         const float* x, b200_idx_t k,
+                                         const B200SearchParametersIVF* params, float* distances,
+                                         b200_idx_t* labels);
+/* IndexIVF::search_preassigned with its trailing arguments (faiss/IndexIVF.h:235-246):
+ * store_pairs != 0 returns list_no << 32 | offset as labels (faiss/IndexIVFFlat.cpp:172);
+ * params may be NULL */
+int b200_IndexIVFFlat_search_preassigned_with_params(
+        const B200IndexIVFFlat* index, b200_idx_t n, const float* x, b200_idx_t k,
+        const b200_idx_t* assign, const float* centroid_dis, float* distances, b200_idx_t* labels,
+        int store_pairs, const B200SearchParametersIVF* params);
+
+/* the fork's IndexIVF::search_stats (faiss/IndexIVF.cpp:727-862, faiss/IndexIVF.h:28-32,322-330):
+ * search + one QueryLatencyStats per query (HOST array of n). quantization_us is the batch's
+ * coarse time / n as in the reference (:767-771); list_scan_us is the batch's plan + scan +
+ * select device time shared out by each query's scanned rows (a batched kernel has no per-query
+ * clock); total_us is their sum. params may be NULL. */
+typedef struct B200QueryLatencyStats {
+    double total_us;
+    double quantization_us;
+    double list_scan_us;
+} B200QueryLatencyStats;
+int b200_IndexIVFFlat_search_stats(const B200IndexIVFFlat* index, b200_idx_t n, const float* x,
+                                   b200_idx_t k, float* distances, b200_idx_t* labels,
+                                   const B200SearchParametersIVF* params,
+                                   B200QueryLatencyStats* per_query_stats);
+
+/* ---- range search --------------------------------------------------------------------------
+ * faiss::RangeSearchResult (faiss/impl/AuxIndexStructures.h:30-58), C API
+ * c_api/impl/AuxIndexStructures_c.h:20-49: query i owns entries lims[i]..lims[i+1]. The arrays
+ * are host memory owned by the object and valid until the next range search into it / free. */
+typedef struct B200RangeSearchResult_H B200RangeSearchResult;
+int b200_RangeSearchResult_new(B200RangeSearchResult** p_rsr, b200_idx_t nq);
+void b200_RangeSearchResult_free(B200RangeSearchResult* rsr);
+size_t b200_RangeSearchResult_nq(const B200RangeSearchResult* rsr);
+void b200_RangeSearchResult_lims(B200RangeSearchResult* rsr, size_t** lims);
+void b200_RangeSearchResult_labels(B200RangeSearchResult* rsr, b200_idx_t** labels,
+                                   float** distances);
+/* faiss_Index_range_search, c_api/Index_c.h:148-153 == IndexIVF::range_search
+ * faiss/IndexIVF.cpp:1203-1241: L2 keeps dis < radius, inner product dis > radius
+ * (faiss/IndexIVFFlat.cpp:196); params may be NULL (nprobe and selector are honoured) */
+int b200_IndexIVFFlat_range_search(const B200IndexIVFFlat* index, b200_idx_t n, const float* x,
+                                   float radius, B200RangeSearchResult* result,
+                                   const B200SearchParametersIVF* params);
+/* IndexIVF::range_search_preassigned, faiss/IndexIVF.cpp:1243-1399 */
+int b200_IndexIVFFlat_range_search_preassigned(const B200IndexIVFFlat* index, b200_idx_t n,
+                                               const float* x, float radius,
+                                               const b200_idx_t* assign, const float* centroid_dis,
+                                               B200RangeSearchResult* result, int store_pairs,
+                                               const B200SearchParametersIVF* params);
 
 #ifdef __cplusplus
 }

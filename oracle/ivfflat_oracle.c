@@ -295,6 +295,9 @@ const int64_t* orc_index_list_ids(const OrcIndex* ix, size_t l) {
 int64_t orc_index_ntotal(const OrcIndex* ix) {
     return ix->ntotal;
 }
+const float* orc_index_centroids(const OrcIndex* ix) {
+    return ix->centroids;
+}
 
 void orc_index_add_core(OrcIndex* ix, int64_t n, const float* x, const int64_t* xids,
                         const int64_t* assign) {
@@ -346,20 +349,116 @@ static double now_ms(void) {
     return tv.tv_sec * 1e3 + tv.tv_usec * 1e-3;
 }
 
-int orc_index_search_preassigned(const OrcIndex* ix, int64_t n, const float* x, int64_t k,
-                                 size_t nprobe, const int64_t* keys, float* D, int64_t* I,
-                                 OrcStats* stats) {
-    /* faiss/IndexIVF.cpp:399-723, parallel_mode 0, store_pairs=false, no selector, max_codes=0.
-     * Per query: heapify (:607), probes in the given order (:612-622), strict compare in
-     * scan_codes (faiss/IndexIVFFlat.cpp:155-179), reorder (:625). */
+/* ---------------------------------------------------------------------------------------------
+ * IDSelector family: faiss/impl/IDSelector.h:19-170, faiss/impl/IDSelector.cpp:17-123
+ * ------------------------------------------------------------------------------------------- */
+struct OrcSel {
+    int kind; /* ORC_SEL_* */
+    int64_t imin, imax;    /* range */
+    int64_t* set;          /* batch / array: sorted copy */
+    size_t nset;
+    uint8_t* bitmap;       /* bitmap copy, nbytes */
+    size_t nbytes;
+    const OrcSel *lhs, *rhs; /* not (lhs) / and / or / xor: borrowed */
+};
+
+static int cmp_i64(const void* a, const void* b) {
+    int64_t x = *(const int64_t*)a, y = *(const int64_t*)b;
+    return x < y ? -1 : (x > y ? 1 : 0);
+}
+
+OrcSel* orc_sel_range(int64_t imin, int64_t imax) {
+    OrcSel* s = (OrcSel*)calloc(1, sizeof(OrcSel));
+    s->kind = ORC_SEL_RANGE;
+    s->imin = imin;
+    s->imax = imax;
+    return s;
+}
+OrcSel* orc_sel_batch(size_t n, const int64_t* ids) {
+    OrcSel* s = (OrcSel*)calloc(1, sizeof(OrcSel));
+    s->kind = ORC_SEL_BATCH;
+    s->set = (int64_t*)malloc(sizeof(int64_t) * (n ? n : 1));
+    memcpy(s->set, ids, sizeof(int64_t) * n);
+    qsort(s->set, n, sizeof(int64_t), cmp_i64);
+    s->nset = n;
+    return s;
+}
+OrcSel* orc_sel_bitmap(size_t nbytes, const uint8_t* bitmap) {
+    OrcSel* s = (OrcSel*)calloc(1, sizeof(OrcSel));
+    s->kind = ORC_SEL_BITMAP;
+    s->bitmap = (uint8_t*)malloc(nbytes ? nbytes : 1);
+    memcpy(s->bitmap, bitmap, nbytes);
+    s->nbytes = nbytes;
+    return s;
+}
+OrcSel* orc_sel_combine(int kind, const OrcSel* lhs, const OrcSel* rhs) {
+    OrcSel* s = (OrcSel*)calloc(1, sizeof(OrcSel));
+    s->kind = kind;
+    s->lhs = lhs;
+    s->rhs = rhs;
+    return s;
+}
+void orc_sel_free(OrcSel* s) {
+    if (!s)
+        return;
+    free(s->set);
+    free(s->bitmap);
+    free(s);
+}
+int orc_sel_is_member(const OrcSel* s, int64_t id) {
+    switch (s->kind) {
+        case ORC_SEL_RANGE: /* IDSelector.cpp:20-22 */
+            return id >= s->imin && id < s->imax;
+        case ORC_SEL_BATCH: { /* IDSelector.cpp:102-108: set membership */
+            size_t lo = 0, hi = s->nset;
+            while (lo < hi) {
+                size_t mid = (lo + hi) / 2;
+                if (s->set[mid] < id)
+                    lo = mid + 1;
+                else
+                    hi = mid;
+            }
+            return lo < s->nset && s->set[lo] == id;
+        }
+        case ORC_SEL_BITMAP: { /* IDSelector.cpp:117-123 */
+            uint64_t i = (uint64_t)id;
+            if ((i >> 3) >= s->nbytes)
+                return 0;
+            return (s->bitmap[i >> 3] >> (i & 7)) & 1;
+        }
+        case ORC_SEL_NOT: /* IDSelector.h:133-139 */
+            return !orc_sel_is_member(s->lhs, id);
+        case ORC_SEL_AND:
+            return orc_sel_is_member(s->lhs, id) && orc_sel_is_member(s->rhs, id);
+        case ORC_SEL_OR:
+            return orc_sel_is_member(s->lhs, id) || orc_sel_is_member(s->rhs, id);
+        case ORC_SEL_XOR:
+            return orc_sel_is_member(s->lhs, id) ^ orc_sel_is_member(s->rhs, id);
+    }
+    return 0;
+}
+
+int orc_index_search_preassigned_ex(const OrcIndex* ix, int64_t n, const float* x, int64_t k,
+                                    size_t nprobe, const int64_t* keys, float* D, int64_t* I,
+                                    OrcStats* stats, size_t max_codes, const OrcSel* sel,
+                                    int store_pairs) {
+    /* faiss/IndexIVF.cpp:399-723, parallel_mode 0. Per query: heapify (:607), probes in the given
+     * order (:612-622) each cut to max_codes - nscan rows (:545-548) until nscan >= max_codes
+     * (:619-621), strict compare in scan_codes with the selector test first
+     * (faiss/IndexIVFFlat.cpp:155-179), label = lo_build(list, j) when store_pairs (:172),
+     * reorder (:625). */
     const int is_max = metric_is_max(ix->metric);
     const size_t d = ix->d;
     size_t nlistv = 0, ndis = 0, nheap = 0;
     int bad = 0;
     if (k <= 0 || nprobe == 0)
         return -2; /* FAISS_THROW_IF_NOT(k > 0), (nprobe > 0): IndexIVF.cpp:410,414 */
+    if (sel && store_pairs)
+        return -2; /* :428-430 */
     if (nprobe > ix->nlist)
         nprobe = ix->nlist;
+    if (max_codes == 0)
+        max_codes = (size_t)INT64_MAX; /* :453-455 */
 #pragma omp parallel for reduction(+ : nlistv, ndis, nheap) reduction(| : bad)
     for (int64_t i = 0; i < n; i++) {
         const float* xi = x + i * d;
@@ -379,18 +478,26 @@ int orc_index_search_preassigned(const OrcIndex* ix, int64_t n, const float* x, 
             if (ls == 0)
                 continue; /* :527 */
             nlistv++;
+            if (ls > max_codes - nscan)
+                ls = max_codes - nscan; /* :546-548 */
             const float* yl = ix->codes[key];
             const int64_t* idl = ix->ids[key];
             for (size_t j = 0; j < ls; j++) {
+                if (sel && !orc_sel_is_member(sel, idl[j]))
+                    continue; /* IndexIVFFlat.cpp:166 */
                 float dis = ix->metric == ORC_METRIC_INNER_PRODUCT
                         ? orc_fvec_inner_product(xi, yl + j * d, d)
                         : orc_fvec_L2sqr(xi, yl + j * d, d);
                 if (c_cmp(is_max, simi[0], dis)) {
-                    h_sift_from_top(is_max, k, simi, idxi, dis, idl[j]);
+                    int64_t id = store_pairs ? (int64_t)(((uint64_t)key << 32) | (uint64_t)j)
+                                             : idl[j];
+                    h_sift_from_top(is_max, k, simi, idxi, dis, id);
                     nheap++;
                 }
             }
             nscan += ls;
+            if (nscan >= max_codes)
+                break; /* :619-621 */
         }
         ndis += nscan;
         h_reorder(is_max, k, simi, idxi);
@@ -402,6 +509,232 @@ int orc_index_search_preassigned(const OrcIndex* ix, int64_t n, const float* x, 
         stats->nheap_updates += nheap;
     }
     return bad ? -2 : 0;
+}
+
+int orc_index_search_preassigned(const OrcIndex* ix, int64_t n, const float* x, int64_t k,
+                                 size_t nprobe, const int64_t* keys, float* D, int64_t* I,
+                                 OrcStats* stats) {
+    return orc_index_search_preassigned_ex(ix, n, x, k, nprobe, keys, D, I, stats, 0, NULL, 0);
+}
+
+int orc_index_range_search_preassigned(const OrcIndex* ix, int64_t n, const float* x, float radius,
+                                       size_t nprobe, const int64_t* keys, const OrcSel* sel,
+                                       int store_pairs, size_t* lims, int64_t** labels_out,
+                                       float** dis_out) {
+    /* faiss/IndexIVF.cpp:1243-1399 (parallel_mode 0) + scan_codes_range
+     * faiss/IndexIVFFlat.cpp:181-201: per query, probes in order, rows in list order, a row is
+     * kept when C::cmp(radius, dis) (L2: radius > dis, IP: radius < dis). */
+    const int is_max = metric_is_max(ix->metric);
+    const size_t d = ix->d;
+    if (nprobe == 0 || (sel && store_pairs))
+        return -2;
+    if (nprobe > ix->nlist)
+        nprobe = ix->nlist;
+    size_t cap = 1024, cnt = 0;
+    int64_t* lab = (int64_t*)malloc(cap * sizeof(int64_t));
+    float* dd = (float*)malloc(cap * sizeof(float));
+    int bad = 0;
+    for (int64_t i = 0; i < n; i++) {
+        const float* xi = x + i * d;
+        lims[i] = cnt;
+        for (size_t ik = 0; ik < nprobe; ik++) {
+            int64_t key = keys[i * nprobe + ik];
+            if (key < 0)
+                continue;
+            if ((size_t)key >= ix->nlist) {
+                bad = 1;
+                continue;
+            }
+            const size_t ls = ix->len[key];
+            const float* yl = ix->codes[key];
+            const int64_t* idl = ix->ids[key];
+            for (size_t j = 0; j < ls; j++) {
+                if (sel && !orc_sel_is_member(sel, idl[j]))
+                    continue;
+                float dis = ix->metric == ORC_METRIC_INNER_PRODUCT
+                        ? orc_fvec_inner_product(xi, yl + j * d, d)
+                        : orc_fvec_L2sqr(xi, yl + j * d, d);
+                if (c_cmp(is_max, radius, dis)) {
+                    if (cnt == cap) {
+                        cap *= 2;
+                        lab = (int64_t*)realloc(lab, cap * sizeof(int64_t));
+                        dd = (float*)realloc(dd, cap * sizeof(float));
+                    }
+                    lab[cnt] = store_pairs ? (int64_t)(((uint64_t)key << 32) | (uint64_t)j)
+                                           : idl[j];
+                    dd[cnt] = dis;
+                    cnt++;
+                }
+            }
+        }
+    }
+    lims[n] = cnt;
+    *labels_out = lab;
+    *dis_out = dd;
+    return bad ? -2 : 0;
+}
+
+void orc_free(void* p) {
+    free(p);
+}
+
+/* ---------------------------------------------------------------------------------------------
+ * training: Clustering::train_encoded (faiss/Clustering.cpp:296-600) as IndexIVF drives it
+ * (faiss/IndexIVF.cpp:66-127: the flat quantizer of the index's metric assigns; niter 10,
+ * spherical for inner product :179-182). RandomGenerator is std::mt19937
+ * (faiss/utils/random.cpp:37-49), restated here as MT19937 (Matsumoto & Nishimura 1998).
+ * ------------------------------------------------------------------------------------------- */
+typedef struct {
+    uint32_t mt[624];
+    int idx;
+} Mt19937;
+
+static void mt_seed(Mt19937* g, uint32_t seed) {
+    g->mt[0] = seed;
+    for (int i = 1; i < 624; i++)
+        g->mt[i] = 1812433253u * (g->mt[i - 1] ^ (g->mt[i - 1] >> 30)) + (uint32_t)i;
+    g->idx = 624;
+}
+
+static uint32_t mt_next(Mt19937* g) {
+    if (g->idx >= 624) {
+        for (int i = 0; i < 624; i++) {
+            uint32_t y = (g->mt[i] & 0x80000000u) | (g->mt[(i + 1) % 624] & 0x7fffffffu);
+            g->mt[i] = g->mt[(i + 397) % 624] ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
+        }
+        g->idx = 0;
+    }
+    uint32_t y = g->mt[g->idx++];
+    y ^= y >> 11;
+    y ^= (y << 7) & 0x9d2c5680u;
+    y ^= (y << 15) & 0xefc60000u;
+    y ^= y >> 18;
+    return y;
+}
+
+/* faiss::rand_perm, faiss/utils/random.cpp:184-194 */
+static void ref_rand_perm(int64_t* perm, size_t n, int64_t seed) {
+    Mt19937 g;
+    mt_seed(&g, (uint32_t)seed);
+    for (size_t i = 0; i < n; i++)
+        perm[i] = (int64_t)i;
+    for (size_t i = 0; i + 1 < n; i++) {
+        size_t i2 = i + (size_t)(mt_next(&g) % (uint32_t)(n - i));
+        int64_t t = perm[i];
+        perm[i] = perm[i2];
+        perm[i2] = t;
+    }
+}
+
+static void renorm_rows(float* c, size_t k, size_t d) { /* distances.cpp:95-105 */
+    for (size_t i = 0; i < k; i++) {
+        float* xi = c + i * d;
+        float nr = orc_fvec_norm_L2sqr(xi, d);
+        if (nr > 0) {
+            const float inv_nr = (float)(1.0 / sqrtf(nr));
+            for (size_t j = 0; j < d; j++)
+                xi[j] *= inv_nr;
+        }
+    }
+}
+
+int orc_index_train(OrcIndex* ix, int64_t n, const float* x, int niter, int seed,
+                    int max_points_per_centroid, double* objective_out) {
+    const size_t k = ix->nlist, d = ix->d;
+    if (n < (int64_t)k)
+        return -2; /* Clustering.cpp:302-306 */
+    int64_t nx = n;
+    float* xt = NULL;
+    const float* xs = x;
+    if ((size_t)n > k * (size_t)max_points_per_centroid) { /* subsample_training_set :86-133 */
+        int64_t* perm = (int64_t*)malloc(sizeof(int64_t) * (size_t)n);
+        ref_rand_perm(perm, (size_t)n, seed);
+        nx = (int64_t)(k * (size_t)max_points_per_centroid);
+        xt = (float*)malloc(sizeof(float) * (size_t)nx * d);
+        for (int64_t i = 0; i < nx; i++)
+            memcpy(xt + i * d, x + perm[i] * d, sizeof(float) * d);
+        free(perm);
+        xs = xt;
+    }
+    float* cent = ix->centroids;
+    { /* initial centroids: :425-441 */
+        int64_t* perm = (int64_t*)malloc(sizeof(int64_t) * (size_t)nx);
+        ref_rand_perm(perm, (size_t)nx, (int64_t)seed + 1);
+        for (size_t i = 0; i < k; i++)
+            memcpy(cent + i * d, xs + perm[i] * d, sizeof(float) * d);
+        free(perm);
+    }
+    const int spherical = ix->metric == ORC_METRIC_INNER_PRODUCT;
+    if (spherical)
+        renorm_rows(cent, k, d);
+    int64_t* assign = (int64_t*)malloc(sizeof(int64_t) * (size_t)nx);
+    float* dis = (float*)malloc(sizeof(float) * (size_t)nx);
+    float* hassign = (float*)malloc(sizeof(float) * k);
+    double obj = 0;
+    for (int it = 0; it < niter; it++) {
+        const int64_t bs = 65536;
+        for (int64_t i0 = 0; i0 < nx; i0 += bs) { /* index.search(nx, x, 1, dis, assign) :470-474 */
+            int64_t ni = nx - i0 < bs ? nx - i0 : bs;
+            orc_knn(ix->metric, xs + i0 * d, cent, d, ni, k, 1, dis + i0, assign + i0);
+        }
+        obj = 0;
+        for (int64_t j = 0; j < nx; j++)
+            obj += dis[j];
+        /* compute_centroids :150-221: sums in input order, then * 1/count */
+        memset(cent, 0, sizeof(float) * k * d);
+        memset(hassign, 0, sizeof(float) * k);
+        for (int64_t i = 0; i < nx; i++) {
+            float* c = cent + assign[i] * d;
+            const float* xi = xs + i * d;
+            hassign[assign[i]] += 1.0f;
+            for (size_t j = 0; j < d; j++)
+                c[j] += xi[j];
+        }
+        for (size_t ci = 0; ci < k; ci++) {
+            if (hassign[ci] == 0)
+                continue;
+            float norm = 1 / hassign[ci];
+            for (size_t j = 0; j < d; j++)
+                cent[ci * d + j] *= norm;
+        }
+        /* split_clusters :232-276 */
+        if ((size_t)nx > k) {
+            Mt19937 g;
+            mt_seed(&g, 1234);
+            for (size_t ci = 0; ci < k; ci++) {
+                if (hassign[ci] != 0)
+                    continue;
+                size_t cj;
+                for (cj = 0; 1; cj = (cj + 1) % k) {
+                    float p = (float)((hassign[cj] - 1.0) / (float)(nx - (int64_t)k));
+                    float r = mt_next(&g) / (float)4294967295u;
+                    if (r < p)
+                        break;
+                }
+                memcpy(cent + ci * d, cent + cj * d, sizeof(float) * d);
+                for (size_t j = 0; j < d; j++) {
+                    if (j % 2 == 0) {
+                        cent[ci * d + j] = (float)(cent[ci * d + j] * (1 + 1 / 1024.));
+                        cent[cj * d + j] = (float)(cent[cj * d + j] * (1 - 1 / 1024.));
+                    } else {
+                        cent[ci * d + j] = (float)(cent[ci * d + j] * (1 - 1 / 1024.));
+                        cent[cj * d + j] = (float)(cent[cj * d + j] * (1 + 1 / 1024.));
+                    }
+                }
+                hassign[ci] = hassign[cj] / 2;
+                hassign[cj] -= hassign[ci];
+            }
+        }
+        if (spherical)
+            renorm_rows(cent, k, d);
+    }
+    if (objective_out)
+        *objective_out = obj;
+    free(assign);
+    free(dis);
+    free(hassign);
+    free(xt);
+    return 0;
 }
 
 int orc_index_search(const OrcIndex* ix, int64_t n, const float* x, int64_t k, size_t nprobe,

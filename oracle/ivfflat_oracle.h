@@ -67,6 +67,43 @@ void orc_index_quantize(const OrcIndex* ix, int64_t n, const float* x, size_t np
 int orc_index_search_preassigned(const OrcIndex* ix, int64_t n, const float* x, int64_t k,
                                  size_t nprobe, const int64_t* keys, float* D, int64_t* I,
                                  OrcStats* stats);
+/* IDSelector family, faiss/impl/IDSelector.h:19-170 / IDSelector.cpp:17-123. batch/bitmap copy
+ * their input; not/and/or/xor borrow their operands (rhs NULL for not). */
+#define ORC_SEL_RANGE 0
+#define ORC_SEL_BATCH 1
+#define ORC_SEL_BITMAP 2
+#define ORC_SEL_NOT 3
+#define ORC_SEL_AND 4
+#define ORC_SEL_OR 5
+#define ORC_SEL_XOR 6
+typedef struct OrcSel OrcSel;
+OrcSel* orc_sel_range(int64_t imin, int64_t imax);
+OrcSel* orc_sel_batch(size_t n, const int64_t* ids);
+OrcSel* orc_sel_bitmap(size_t nbytes, const uint8_t* bitmap);
+OrcSel* orc_sel_combine(int kind, const OrcSel* lhs, const OrcSel* rhs);
+void orc_sel_free(OrcSel* s);
+int orc_sel_is_member(const OrcSel* s, int64_t id);
+
+/* search_preassigned with the SearchParametersIVF arms: max_codes (faiss/IndexIVF.cpp:545-548,
+ * 619-621; 0 = no limit), selector (faiss/IndexIVFFlat.cpp:166), store_pairs (:172) */
+int orc_index_search_preassigned_ex(const OrcIndex* ix, int64_t n, const float* x, int64_t k,
+                                    size_t nprobe, const int64_t* keys, float* D, int64_t* I,
+                                    OrcStats* stats, size_t max_codes, const OrcSel* sel,
+                                    int store_pairs);
+/* faiss/IndexIVF.cpp:1243-1399 + scan_codes_range faiss/IndexIVFFlat.cpp:181-201. lims: [n+1]
+ * caller buffer; *labels_out / *dis_out are malloc'd (orc_free). */
+int orc_index_range_search_preassigned(const OrcIndex* ix, int64_t n, const float* x, float radius,
+                                       size_t nprobe, const int64_t* keys, const OrcSel* sel,
+                                       int store_pairs, size_t* lims, int64_t** labels_out,
+                                       float** dis_out);
+void orc_free(void* p);
+/* k-means of the coarse quantizer as IndexIVF::train runs it (faiss/IndexIVF.cpp:66-127 ->
+ * faiss/Clustering.cpp:296-600); writes the centroids into the index. objective_out (may be
+ * NULL): sum of the assignment distances of the last iteration (:486-489). */
+int orc_index_train(OrcIndex* ix, int64_t n, const float* x, int niter, int seed,
+                    int max_points_per_centroid, double* objective_out);
+const float* orc_index_centroids(const OrcIndex* ix);
+
 /* faiss/IndexIVF.cpp:303-397; nt = number of OpenMP slices to emulate (slice size decides the
  * seq-vs-BLAS coarse form, :358-368). */
 int orc_index_search(const OrcIndex* ix, int64_t n, const float* x, int64_t k, size_t nprobe,

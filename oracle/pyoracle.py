@@ -75,6 +75,32 @@ def port_lib():
         L.orc_index_search_preassigned.argtypes = [C.c_void_p, C.c_int64, _f32p, C.c_int64,
                                                    C.c_size_t, _i64p, _f32p, _i64p,
                                                    C.POINTER(OrcStats)]
+        L.orc_index_search_preassigned_ex.restype = C.c_int
+        L.orc_index_search_preassigned_ex.argtypes = [C.c_void_p, C.c_int64, _f32p, C.c_int64,
+                                                      C.c_size_t, _i64p, _f32p, _i64p,
+                                                      C.POINTER(OrcStats), C.c_size_t, C.c_void_p,
+                                                      C.c_int]
+        L.orc_index_range_search_preassigned.restype = C.c_int
+        L.orc_index_range_search_preassigned.argtypes = [
+            C.c_void_p, C.c_int64, _f32p, C.c_float, C.c_size_t, _i64p, C.c_void_p, C.c_int,
+            C.POINTER(C.c_size_t), C.POINTER(_i64p), C.POINTER(_f32p)]
+        L.orc_free.argtypes = [C.c_void_p]
+        L.orc_index_train.restype = C.c_int
+        L.orc_index_train.argtypes = [C.c_void_p, C.c_int64, _f32p, C.c_int, C.c_int, C.c_int,
+                                      C.POINTER(C.c_double)]
+        L.orc_index_centroids.restype = _f32p
+        L.orc_index_centroids.argtypes = [C.c_void_p]
+        L.orc_sel_range.restype = C.c_void_p
+        L.orc_sel_range.argtypes = [C.c_int64, C.c_int64]
+        L.orc_sel_batch.restype = C.c_void_p
+        L.orc_sel_batch.argtypes = [C.c_size_t, _i64p]
+        L.orc_sel_bitmap.restype = C.c_void_p
+        L.orc_sel_bitmap.argtypes = [C.c_size_t, C.c_void_p]
+        L.orc_sel_combine.restype = C.c_void_p
+        L.orc_sel_combine.argtypes = [C.c_int, C.c_void_p, C.c_void_p]
+        L.orc_sel_free.argtypes = [C.c_void_p]
+        L.orc_sel_is_member.restype = C.c_int
+        L.orc_sel_is_member.argtypes = [C.c_void_p, C.c_int64]
         L.orc_index_search.restype = C.c_int
         L.orc_index_search.argtypes = [C.c_void_p, C.c_int64, _f32p, C.c_int64, C.c_size_t,
                                        C.c_int, _f32p, _i64p, C.POINTER(OrcStats)]
@@ -92,6 +118,69 @@ def port_lib():
             fn.argtypes = [_f32p, _f32p, C.c_size_t]
         _port = L
     return _port
+
+
+# ---- selector specs -------------------------------------------------------------------------------
+# One description of an IDSelector tree, understood by the port, the reference shim and the tests'
+# GPU builder: ("range", imin, imax) | ("batch", ids) | ("bitmap", uint8 array) | ("not", s) |
+# ("and", a, b) | ("or", a, b) | ("xor", a, b)
+_COMBINE = {"not": 3, "and": 4, "or": 5, "xor": 6}
+
+
+class _SelTree:
+    """Owns the C objects of one selector tree (children before parents) and frees them."""
+
+    def __init__(self, spec, leaf_range, leaf_batch, leaf_bitmap, combine, free):
+        self._free = free
+        self._nodes = []
+
+        def build(sp):
+            kind = sp[0]
+            if kind == "range":
+                h = leaf_range(int(sp[1]), int(sp[2]))
+            elif kind == "batch":
+                a = np.ascontiguousarray(sp[1], dtype=np.int64)
+                h = leaf_batch(a.size, a.ctypes.data_as(_i64p))
+            elif kind == "bitmap":
+                a = np.ascontiguousarray(sp[1], dtype=np.uint8)
+                h = leaf_bitmap(a.size, a.ctypes.data_as(C.c_void_p))
+            else:
+                lhs = build(sp[1])
+                rhs = build(sp[2]) if kind != "not" else None
+                h = combine(_COMBINE[kind], lhs, rhs)
+            h = C.c_void_p(h)
+            self._nodes.append(h)
+            return h
+
+        self.h = build(spec) if spec is not None else None
+
+    def __del__(self):
+        for h in reversed(getattr(self, "_nodes", [])):
+            self._free(h)
+        self._nodes = []
+
+
+def port_sel(spec):
+    L = port_lib()
+    return _SelTree(spec, L.orc_sel_range, L.orc_sel_batch, L.orc_sel_bitmap, L.orc_sel_combine,
+                    L.orc_sel_free)
+
+
+def sel_is_member_py(spec, i):
+    """pure-Python statement of the same predicates (faiss/impl/IDSelector.cpp:17-123)"""
+    kind = spec[0]
+    if kind == "range":
+        return spec[1] <= i < spec[2]
+    if kind == "batch":
+        return int(i) in set(int(v) for v in spec[1])
+    if kind == "bitmap":
+        b = np.asarray(spec[1], np.uint8)
+        u = int(i) & 0xFFFFFFFFFFFFFFFF
+        return (u >> 3) < b.size and bool((int(b[u >> 3]) >> (u & 7)) & 1)
+    if kind == "not":
+        return not sel_is_member_py(spec[1], i)
+    a, b = sel_is_member_py(spec[1], i), sel_is_member_py(spec[2], i)
+    return (a and b) if kind == "and" else (a or b) if kind == "or" else (a != b)
 
 
 class PortIndex:
@@ -165,6 +254,57 @@ class PortIndex:
         if rc:
             raise RuntimeError("oracle search_preassigned failed rc=%d" % rc)
         return D, I
+
+    def search_preassigned_ex(self, x, k, keys, max_codes=0, sel=None, store_pairs=False):
+        """search_preassigned with the SearchParametersIVF arms; sel is a selector spec"""
+        x, px = _f32(x)
+        keys, pk = _i64(keys)
+        n, nprobe = keys.shape
+        D = np.empty((n, k), np.float32)
+        I = np.empty((n, k), np.int64)
+        tree = port_sel(sel)
+        rc = self.L.orc_index_search_preassigned_ex(
+            self.h, n, px, k, nprobe, pk, D.ctypes.data_as(_f32p), I.ctypes.data_as(_i64p),
+            C.byref(self.stats), int(max_codes), tree.h, int(bool(store_pairs)))
+        if rc:
+            raise RuntimeError("oracle search_preassigned_ex failed rc=%d" % rc)
+        return D, I
+
+    def range_search_preassigned(self, x, radius, keys, sel=None, store_pairs=False):
+        x, px = _f32(x)
+        keys, pk = _i64(keys)
+        n, nprobe = keys.shape
+        lims = (C.c_size_t * (n + 1))()
+        lab, dis = _i64p(), _f32p()
+        tree = port_sel(sel)
+        rc = self.L.orc_index_range_search_preassigned(
+            self.h, n, px, float(radius), nprobe, pk, tree.h, int(bool(store_pairs)), lims,
+            C.byref(lab), C.byref(dis))
+        try:
+            if rc:
+                raise RuntimeError("oracle range_search_preassigned failed rc=%d" % rc)
+            lims = np.array(list(lims), dtype=np.uint64)
+            tot = int(lims[-1])
+            I = np.ctypeslib.as_array(lab, (tot,)).copy() if tot else np.empty((0,), np.int64)
+            D = np.ctypeslib.as_array(dis, (tot,)).copy() if tot else np.empty((0,), np.float32)
+        finally:
+            self.L.orc_free(lab)
+            self.L.orc_free(dis)
+        return lims, D, I
+
+    def train(self, x, niter=10, seed=1234, max_points_per_centroid=256):
+        """k-means as IndexIVF::train runs it; returns the last iteration's objective"""
+        x, px = _f32(x)
+        obj = C.c_double(0)
+        rc = self.L.orc_index_train(self.h, x.shape[0], px, niter, seed, max_points_per_centroid,
+                                    C.byref(obj))
+        if rc:
+            raise RuntimeError("oracle train failed rc=%d" % rc)
+        return obj.value
+
+    def get_centroids(self):
+        return np.ctypeslib.as_array(self.L.orc_index_centroids(self.h),
+                                     (self.nlist, self.d)).copy()
 
     def search(self, x, k, nprobe, nt=1):
         x, px = _f32(x)
@@ -274,6 +414,34 @@ def ref_lib():
         L.ref_ivfflat_search_preassigned.argtypes = [C.c_void_p, C.c_int64, _f32p, C.c_int64,
                                                      C.c_int64, _i64p, _f32p, _f32p, _i64p]
         L.ref_ivfflat_set_parallel_mode.argtypes = [C.c_void_p, C.c_int]
+        L.ref_sel_range_new.restype = C.c_void_p
+        L.ref_sel_range_new.argtypes = [C.c_int64, C.c_int64]
+        L.ref_sel_batch_new.restype = C.c_void_p
+        L.ref_sel_batch_new.argtypes = [C.c_int64, _i64p]
+        L.ref_sel_bitmap_new.restype = C.c_void_p
+        L.ref_sel_bitmap_new.argtypes = [C.c_int64, C.c_void_p]
+        L.ref_sel_combine_new.restype = C.c_void_p
+        L.ref_sel_combine_new.argtypes = [C.c_int, C.c_void_p, C.c_void_p]
+        L.ref_sel_is_member.argtypes = [C.c_void_p, C.c_int64]
+        L.ref_sel_free.argtypes = [C.c_void_p]
+        L.ref_ivfflat_search_params.argtypes = [C.c_void_p, C.c_int64, _f32p, C.c_int64, C.c_int64,
+                                                C.c_int64, C.c_void_p, _f32p, _i64p]
+        L.ref_ivfflat_search_preassigned_ex.argtypes = [
+            C.c_void_p, C.c_int64, _f32p, C.c_int64, C.c_int64, _i64p, _f32p, _f32p, _i64p,
+            C.c_int, C.c_int64, C.c_void_p]
+        L.ref_ivfflat_search_stats.argtypes = [C.c_void_p, C.c_int64, _f32p, C.c_int64, C.c_int64,
+                                               _f32p, _i64p, C.POINTER(C.c_double)]
+        L.ref_ivfflat_range_search.restype = C.c_void_p
+        L.ref_ivfflat_range_search.argtypes = [C.c_void_p, C.c_int64, _f32p, C.c_float, C.c_int64,
+                                               _i64p, C.c_int, C.c_void_p]
+        L.ref_range_lims.restype = C.POINTER(C.c_size_t)
+        L.ref_range_lims.argtypes = [C.c_void_p]
+        L.ref_range_labels.restype = _i64p
+        L.ref_range_labels.argtypes = [C.c_void_p]
+        L.ref_range_distances.restype = _f32p
+        L.ref_range_distances.argtypes = [C.c_void_p]
+        L.ref_range_free.argtypes = [C.c_void_p]
+        L.ref_ivfflat_set_cp.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int]
         L.ref_stats_get.argtypes = [C.POINTER(C.c_double)]
         L.ref_knn.argtypes = [C.c_int, _f32p, _f32p, C.c_int64, C.c_int64, C.c_int64, C.c_int64,
                               _f32p, _i64p]
@@ -285,6 +453,12 @@ def ref_lib():
             fn.argtypes = [_f32p, _f32p, C.c_int64]
         _ref = L
     return _ref
+
+
+def ref_sel(spec):
+    L = ref_lib()
+    return _SelTree(spec, L.ref_sel_range_new, L.ref_sel_batch_new, L.ref_sel_bitmap_new,
+                    L.ref_sel_combine_new, L.ref_sel_free)
 
 
 def _chk(L, rc):
@@ -387,6 +561,71 @@ class RefIndex:
                                                            D.ctypes.data_as(_f32p),
                                                            I.ctypes.data_as(_i64p)))
         return D, I
+
+    def search_params(self, x, k, nprobe, max_codes=0, sel=None):
+        """IndexIVF::search with SearchParametersIVF; sel is a selector spec"""
+        x, px = _f32(x)
+        n = x.shape[0]
+        D = np.empty((n, k), np.float32)
+        I = np.empty((n, k), np.int64)
+        tree = ref_sel(sel)
+        _chk(self.L, self.L.ref_ivfflat_search_params(self.h, n, px, k, nprobe, int(max_codes),
+                                                      tree.h, D.ctypes.data_as(_f32p),
+                                                      I.ctypes.data_as(_i64p)))
+        return D, I
+
+    def search_preassigned_ex(self, x, k, keys, max_codes=0, sel=None, store_pairs=False):
+        x, px = _f32(x)
+        keys, pk = _i64(keys)
+        n, nprobe = keys.shape
+        cdis, pc = _f32(np.zeros((n, nprobe), np.float32))
+        D = np.empty((n, k), np.float32)
+        I = np.empty((n, k), np.int64)
+        tree = ref_sel(sel)
+        _chk(self.L, self.L.ref_ivfflat_search_preassigned_ex(
+            self.h, n, px, k, nprobe, pk, pc, D.ctypes.data_as(_f32p), I.ctypes.data_as(_i64p),
+            int(bool(store_pairs)), int(max_codes), tree.h))
+        return D, I
+
+    def search_stats(self, x, k, nprobe):
+        """the fork's IndexIVF::search_stats -> (D, I, [n][3] total/quantization/list_scan us)"""
+        x, px = _f32(x)
+        n = x.shape[0]
+        D = np.empty((n, k), np.float32)
+        I = np.empty((n, k), np.int64)
+        st = np.zeros((n, 3), np.float64)
+        _chk(self.L, self.L.ref_ivfflat_search_stats(
+            self.h, n, px, k, nprobe, D.ctypes.data_as(_f32p), I.ctypes.data_as(_i64p),
+            st.ctypes.data_as(C.POINTER(C.c_double))))
+        return D, I, st
+
+    def range_search(self, x, radius, nprobe, keys=None, sel=None, store_pairs=False):
+        """IndexIVF::range_search (keys None) / range_search_preassigned -> (lims, D, I)"""
+        x, px = _f32(x)
+        n = x.shape[0]
+        pk = None
+        if keys is not None:
+            keys, pk = _i64(keys)
+        tree = ref_sel(sel)
+        res = self.L.ref_ivfflat_range_search(self.h, n, px, float(radius), nprobe, pk,
+                                              int(bool(store_pairs)), tree.h)
+        if not res:
+            raise RuntimeError("reference range_search: %s" % self.L.ref_last_error().decode())
+        res = C.c_void_p(res)
+        try:
+            lims = np.ctypeslib.as_array(self.L.ref_range_lims(res), (n + 1,)).astype(np.uint64)
+            tot = int(lims[-1])
+            if tot:
+                I = np.ctypeslib.as_array(self.L.ref_range_labels(res), (tot,)).copy()
+                D = np.ctypeslib.as_array(self.L.ref_range_distances(res), (tot,)).copy()
+            else:
+                I, D = np.empty((0,), np.int64), np.empty((0,), np.float32)
+        finally:
+            self.L.ref_range_free(res)
+        return lims, D, I
+
+    def set_cp(self, niter=10, seed=1234, max_points_per_centroid=256):
+        self.L.ref_ivfflat_set_cp(self.h, niter, seed, max_points_per_centroid)
 
     def set_parallel_mode(self, pm):
         self.L.ref_ivfflat_set_parallel_mode(self.h, pm)

@@ -12,12 +12,17 @@
 //   merge_knn_results           faiss/utils/Heap.cpp:158
 //   knn_L2sqr/knn_inner_product faiss/utils/distances.cpp:885,836
 //   write_index / read_index    faiss/impl/index_write.cpp:391, faiss/impl/index_read.cpp:593
+//   IDSelector*                 faiss/impl/IDSelector.h:19-170
+//   IndexIVF::range_search*     faiss/IndexIVF.cpp:1203-1399
+//   IndexIVF::search_stats      faiss/IndexIVF.cpp:727 (fork)
 // Only tests/, __graft_entry__.smoke() and bench.py's CPU-baseline legs may load this library.
 
 #include <faiss/IndexFlat.h>
 #include <faiss/IndexIVFFlat.h>
 #include <faiss/impl/FaissAssert.h>
+#include <faiss/impl/AuxIndexStructures.h>
 #include <faiss/impl/FaissException.h>
+#include <faiss/impl/IDSelector.h>
 #include <faiss/index_io.h>
 #include <faiss/invlists/InvertedLists.h>
 #include <faiss/utils/Heap.h>
@@ -28,6 +33,7 @@
 #include <cstring>
 #include <memory>
 #include <string>
+#include <vector>
 
 namespace {
 thread_local std::string g_err;
@@ -282,6 +288,133 @@ void ref_heap_select(int metric, int64_t k, int64_t n, const float* vals, const 
         faiss::heap_addn<C>(k, out_v, out_i, vals, ids, n);
         faiss::heap_reorder<C>(k, out_v, out_i);
     }
+}
+
+// ---- IDSelector family (faiss/impl/IDSelector.h); batch/bitmap inputs are copied so that the
+// Python caller need not keep them alive ---------------------------------------------------------
+struct RefSel {
+    std::unique_ptr<faiss::IDSelector> sel;
+    std::vector<uint8_t> bitmap;
+};
+void* ref_sel_range_new(int64_t imin, int64_t imax) {
+    auto* r = new RefSel;
+    r->sel.reset(new faiss::IDSelectorRange(imin, imax));
+    return r;
+}
+void* ref_sel_batch_new(int64_t n, const int64_t* ids) {
+    auto* r = new RefSel;
+    r->sel.reset(new faiss::IDSelectorBatch(n, ids));
+    return r;
+}
+void* ref_sel_bitmap_new(int64_t n, const uint8_t* bitmap) {
+    auto* r = new RefSel;
+    r->bitmap.assign(bitmap, bitmap + n);
+    r->sel.reset(new faiss::IDSelectorBitmap(n, r->bitmap.data()));
+    return r;
+}
+// kind: 3 not, 4 and, 5 or, 6 xor (operands borrowed)
+void* ref_sel_combine_new(int kind, void* lhs, void* rhs) {
+    auto* r = new RefSel;
+    const faiss::IDSelector* a = ((RefSel*)lhs)->sel.get();
+    const faiss::IDSelector* b = rhs ? ((RefSel*)rhs)->sel.get() : nullptr;
+    if (kind == 3)
+        r->sel.reset(new faiss::IDSelectorNot(a));
+    else if (kind == 4)
+        r->sel.reset(new faiss::IDSelectorAnd(a, b));
+    else if (kind == 5)
+        r->sel.reset(new faiss::IDSelectorOr(a, b));
+    else
+        r->sel.reset(new faiss::IDSelectorXOr(a, b));
+    return r;
+}
+int ref_sel_is_member(void* s, int64_t id) {
+    return ((RefSel*)s)->sel->is_member(id) ? 1 : 0;
+}
+void ref_sel_free(void* s) {
+    delete (RefSel*)s;
+}
+
+// IndexIVF::search with SearchParametersIVF (faiss/IndexIVF.cpp:303-397)
+int ref_ivfflat_search_params(void* h, int64_t n, const float* x, int64_t k, int64_t nprobe,
+                              int64_t max_codes, void* sel, float* D, int64_t* I) {
+    auto* r = (RefIndex*)h;
+    return guarded([&] {
+        faiss::SearchParametersIVF p;
+        p.nprobe = nprobe;
+        p.max_codes = max_codes;
+        p.sel = sel ? ((RefSel*)sel)->sel.get() : nullptr;
+        r->index->search(n, x, k, D, I, &p);
+    });
+}
+
+// IndexIVF::search_preassigned with every trailing argument (faiss/IndexIVF.cpp:399-723)
+int ref_ivfflat_search_preassigned_ex(void* h, int64_t n, const float* x, int64_t k,
+                                      int64_t nprobe, const int64_t* assign, const float* cdis,
+                                      float* D, int64_t* I, int store_pairs, int64_t max_codes,
+                                      void* sel) {
+    auto* r = (RefIndex*)h;
+    return guarded([&] {
+        faiss::SearchParametersIVF p;
+        p.nprobe = nprobe;
+        p.max_codes = max_codes;
+        p.sel = sel ? ((RefSel*)sel)->sel.get() : nullptr;
+        r->index->search_preassigned(n, x, k, assign, cdis, D, I, store_pairs != 0, &p);
+    });
+}
+
+// the fork's IndexIVF::search_stats (faiss/IndexIVF.cpp:727-862); stats: n x {total_us,
+// quantization_us, list_scan_us}
+int ref_ivfflat_search_stats(void* h, int64_t n, const float* x, int64_t k, int64_t nprobe,
+                             float* D, int64_t* I, double* stats3) {
+    auto* r = (RefIndex*)h;
+    static_assert(sizeof(faiss::QueryLatencyStats) == 3 * sizeof(double), "layout");
+    return guarded([&] {
+        r->index->nprobe = nprobe;
+        r->index->search_stats(n, x, k, D, I, nullptr, (faiss::QueryLatencyStats*)stats3);
+    });
+}
+
+// IndexIVF::range_search / range_search_preassigned (faiss/IndexIVF.cpp:1203-1399) into a
+// faiss::RangeSearchResult the caller reads and frees through the three functions below
+void* ref_ivfflat_range_search(void* h, int64_t n, const float* x, float radius, int64_t nprobe,
+                               const int64_t* assign, int store_pairs, void* sel) {
+    auto* r = (RefIndex*)h;
+    faiss::RangeSearchResult* res = nullptr;
+    const int rc = guarded([&] {
+        std::unique_ptr<faiss::RangeSearchResult> rr(new faiss::RangeSearchResult(n));
+        faiss::SearchParametersIVF p;
+        p.nprobe = nprobe;
+        p.sel = sel ? ((RefSel*)sel)->sel.get() : nullptr;
+        if (assign) {
+            std::vector<float> cd((size_t)n * nprobe, 0.f);
+            r->index->range_search_preassigned(n, x, radius, assign, cd.data(), rr.get(),
+                                               store_pairs != 0, &p);
+        } else {
+            r->index->range_search(n, x, radius, rr.get(), &p);
+        }
+        res = rr.release();
+    });
+    return rc == 0 ? res : nullptr;
+}
+const size_t* ref_range_lims(void* res) {
+    return ((faiss::RangeSearchResult*)res)->lims;
+}
+const int64_t* ref_range_labels(void* res) {
+    return ((faiss::RangeSearchResult*)res)->labels;
+}
+const float* ref_range_distances(void* res) {
+    return ((faiss::RangeSearchResult*)res)->distances;
+}
+void ref_range_free(void* res) {
+    delete (faiss::RangeSearchResult*)res;
+}
+
+// Level1Quantizer::cp knobs before train (faiss/Clustering.h:23-64)
+void ref_ivfflat_set_cp(void* h, int niter, int seed, int max_points_per_centroid) {
+    auto& cp = ((RefIndex*)h)->index->cp;
+    cp.niter = niter;
+    cp.seed = seed;
+    cp.max_points_per_centroid = max_points_per_centroid;
 }
 
 } // extern "C"

@@ -109,3 +109,59 @@ def compare_probes(Dq_ref, Iq_ref, Iq_new, Dq_new=None, rtol=RTOL, atol=1e-5):
     (near-)tied: same rule as compare_knn applied to the coarse table."""
     D_new = Dq_new if Dq_new is not None else Dq_ref
     return compare_knn(Dq_ref, Iq_ref, D_new, Iq_new, rtol, atol)
+
+
+def resolve_spec(spec, table):
+    """Selector spec of a golden file (arrays given by the NAME of an entry of `table`) -> the spec
+    oracle/pyoracle.py understands (arrays inline)."""
+    if spec is None:
+        return None
+    kind = spec[0]
+    if kind == "range":
+        return ("range", int(spec[1]), int(spec[2]))
+    if kind in ("batch", "bitmap"):
+        a = spec[1]
+        return (kind, np.asarray(table[a]) if isinstance(a, str) else np.asarray(a))
+    if kind == "not":
+        return ("not", resolve_spec(spec[1], table))
+    return (kind, resolve_spec(spec[1], table), resolve_spec(spec[2], table))
+
+
+def gpu_selector(spec, device=0):
+    """Selector spec -> hnsw_ivf_b200 selector object (the C-ABI's IDSelector family)."""
+    import hnsw_ivf_b200 as b2
+    if spec is None:
+        return None
+    kind = spec[0]
+    if kind == "range":
+        return b2.IDSelectorRange(spec[1], spec[2])
+    if kind == "batch":
+        return b2.IDSelectorBatch(spec[1], device)
+    if kind == "bitmap":
+        return b2.IDSelectorBitmap(spec[1], device)
+    if kind == "not":
+        return b2.IDSelectorNot(gpu_selector(spec[1], device))
+    ctor = {"and": b2.IDSelectorAnd, "or": b2.IDSelectorOr, "xor": b2.IDSelectorXOr}[kind]
+    return ctor(gpu_selector(spec[1], device), gpu_selector(spec[2], device))
+
+
+def compare_range(l_ref, D_ref, I_ref, l_new, D_new, I_new, radius, metric, rtol=RTOL):
+    """Range results per query as sets: ids may differ only where the reference distance is within
+    tolerance of the radius; common ids must agree on the distance. Returns the number of ids that
+    differ (all explained by the boundary), raises on anything else."""
+    n = len(l_ref) - 1
+    assert len(l_new) - 1 == n
+    boundary = 0
+    for q in range(n):
+        a = {int(i): float(v) for i, v in zip(I_ref[int(l_ref[q]):int(l_ref[q + 1])],
+                                              D_ref[int(l_ref[q]):int(l_ref[q + 1])])}
+        b = {int(i): float(v) for i, v in zip(I_new[int(l_new[q]):int(l_new[q + 1])],
+                                              D_new[int(l_new[q]):int(l_new[q + 1])])}
+        for i in set(a) & set(b):
+            assert _close(a[i], b[i], rtol, 1e-6), (q, i, a[i], b[i])
+        for i in set(a) ^ set(b):
+            v = a.get(i, b.get(i))
+            assert _close(v, radius, 4 * rtol, 1e-6), "query %d id %d dis %r radius %r" % (
+                q, i, v, radius)
+            boundary += 1
+    return boundary
