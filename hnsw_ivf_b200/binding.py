@@ -77,6 +77,7 @@ SYMBOLS = [
     ("b200_IndexIVFFlat_reset_stats", None, [_vp]),
     ("b200_IndexIVFFlat_last_timings", None, [_vp, C.POINTER(C.c_double)]),
     ("b200_IndexIVFFlat_set_stream", C.c_int, [_vp, _vp]),
+    ("b200_debug_trap_info", C.c_int, [C.POINTER(C.c_ulonglong)]),
     ("b200_kernel_launches", C.c_ulonglong, []),
     ("b200_tensor_core_launches", C.c_ulonglong, []),
     ("b200_merge_knn_results", C.c_int,
@@ -524,6 +525,17 @@ def read_index(fname, io_flags=0, device=0):
 def write_index(index, fname):
     """faiss.write_index in the reference's own format (faiss/impl/index_write.cpp:635-638)."""
     index._check(index._lib.b200_write_index_fname(index._h, os.fsencode(fname)))
+
+
+def debug_trap_info():
+    """None, or the note a stuck pipeline wait left before it trapped (see b200ivf_c.h)"""
+    out = (C.c_ulonglong * 8)()
+    if not load_library().b200_debug_trap_info(out):
+        return None
+    names = {1: "tma:empty", 2: "mma:d_empty", 3: "mma:a_rdy", 4: "split:full", 5: "split:a_empty",
+             6: "epi:d_full"}
+    return {"wait": names.get(int(out[0]) - 1, int(out[0]) - 1), "cta": int(out[1]),
+            "thread": int(out[2]), "iteration": int(out[3]), "parity": int(out[4])}
 
 
 def tensor_core_launches():

@@ -183,6 +183,13 @@ unsigned long long b200_tensor_core_launches(void) {
     return b200ivf::g_tc_launches.load();
 }
 
+int b200_debug_trap_info(unsigned long long* out8) {
+    const unsigned long long* h = b200ivf::tc_trap_info_host();
+    for (int i = 0; i < 8; ++i)
+        out8[i] = h ? h[i] : 0ull;
+    return h && h[0] ? 1 : 0;
+}
+
 unsigned long long b200_kernel_launches(void) {
     return b200ivf::g_kernel_launches.load();
 }

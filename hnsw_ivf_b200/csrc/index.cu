@@ -736,6 +736,15 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
         m.pair_query.reserve((size_t)pairs * sizeof(int32_t));
         m.slot_of.reserve((size_t)pairs * sizeof(int32_t));
         m.part.reserve((size_t)pairs * bp.S * pmul * kp * sizeof(uint64_t));
+        {
+            // debugging aid: B200IVF_POISON=1 fills the partial-candidate scratch with keys whose
+            // row is far outside the slab (any entry a scan kernel fails to write then faults in
+            // the k-select), =2 with sentinels
+            static const int poison = getenv("B200IVF_POISON") ? atoi(getenv("B200IVF_POISON")) : 0;
+            if (poison)
+                CUDA_CHECK(cudaMemsetAsync(m.part.p, poison == 1 ? 0x7f : 0xff,
+                                           (size_t)pairs * bp.S * pmul * kp * sizeof(uint64_t), st));
+        }
         PlanArgs pa;
         pa.coarse_ids = m.coarse_ids.as<int32_t>();
         pa.n = (int)ni;

@@ -104,6 +104,7 @@ struct TcScanArgs {
     // query across its probes, faiss/IndexIVF.cpp:597-631; this is that heap's top). Filled with
     // ordered_bits(FLT_MAX) before the launch (launch_fill_u32). nullptr: off.
     uint32_t* qthr = nullptr;
+    unsigned long long* trap = nullptr; // host-mapped note of a wait that gave up (tc_trap_info_*)
     long long* trace = nullptr; // timing experiments only (B200IVF_TC_TRACE=<item>): clock64
     uint32_t trace_item = 0;    // stamps of one CTA, [role][tile]
     int dbg = 0;                // timing experiments only (B200IVF_TC_DBG): 1 = epilogue drops
@@ -127,6 +128,11 @@ int scan_tcr_tq(int nf4, int kp);
 int scan_tcr_kpart(int nf4, int k);
 cudaError_t launch_ivf_scan_tcr(int metric, uint32_t max_items, const TcScanArgs& a,
                                 cudaStream_t st);
+// A pipeline wait of the tensor-core scan that makes no progress for ~2 s traps (the launch fails)
+// instead of hanging the GPU; before it does it notes {1 + which wait, CTA, thread, iteration,
+// parity} in host-mapped memory. nullptr until the first tensor-core launch.
+unsigned long long* tc_trap_info_device();
+const unsigned long long* tc_trap_info_host();
 
 // ---- planning: invert the probe table into per-list query groups -------------------------------
 struct PlanArgs {

@@ -173,7 +173,15 @@ __host__ __device__ inline size_t tcr_rest_bytes(int kp, int n16, int nch) {
 __host__ __device__ inline int tcr_stages(size_t smem_total, int kp, int n16, int nch) {
     const size_t rest = tcr_rest_bytes(kp, n16, nch);
     const int n = smem_total > rest ? (int)((smem_total - rest) / (kRStageF4 * sizeof(float4))) : 0;
-    return n > kRMaxStages ? kRMaxStages : n;
+    // EVEN, always: the two split-warp groups take alternate iterations, so with an even ring a
+    // stage is always consumed by the same group, which therefore saw the stage's previous phase
+    // complete before it waits for the next one. With an odd ring the groups swap stages every
+    // lap; a group that runs ahead then waits on parity p of a barrier still in the phase BEFORE
+    // the one it thinks it follows, the wait passes at once (try_wait.parity is true for the
+    // phase preceding the current one), and the ring protocol falls apart: stale stages, a second
+    // expect_tx on a barrier whose load is still in flight, loads landing after the CTA has gone
+    // (seen as rare launch failures on cold first searches at d = 960, where the ring had 5 stages).
+    return (n > kRMaxStages ? kRMaxStages : n) & ~1;
 }
 
 template <int KP>
@@ -254,14 +262,14 @@ __device__ __noinline__ void tcr_compact(uint64_t* cand, int* cnt, uint32_t* thr
 
 
 // wait with the waiting time added to a trace counter (timing experiments only)
-#define TCR_WAIT(bar, par, acc)                                          \
+#define TCR_WAIT(bar, par, acc, code, aux)                               \
     do {                                                                 \
         if (tracing) {                                                   \
             const long long w0_ = clock64();                             \
-            mbar_wait(bar, par);                                         \
+            mbar_wait_code(bar, par, a.trap, code, (unsigned)(aux));     \
             acc += clock64() - w0_;                                      \
         } else {                                                         \
-            mbar_wait(bar, par);                                         \
+            mbar_wait_code(bar, par, a.trap, code, (unsigned)(aux));     \
         }                                                                \
     } while (0)
 
@@ -372,10 +380,14 @@ __global__ void __launch_bounds__(kRThreads, 1)
                 const int blk = (int)blk0 + b0 + t * kRTileBlocks;
                 for (int sg = 0; sg < nsg; ++sg) {
                     if (t * nsg + sg >= nst)
-                        TCR_WAIT(&s.empty[st], ph ^ 1u, w_empty);
-                    mbar_expect_tx(&s.full[st], (uint32_t)(kRStageF4 * sizeof(float4)));
-                    tma_load_3d(s.raw + (size_t)st * kRStageF4, &tmap, 0, blk, sg * kRKC,
-                                &s.full[st]);
+                        TCR_WAIT(&s.empty[st], ph ^ 1u, w_empty, 1, t * nsg + sg);
+                    if (a.dbg & 16) {
+                        mbar_arrive(&s.full[st]);
+                    } else {
+                        mbar_expect_tx(&s.full[st], (uint32_t)(kRStageF4 * sizeof(float4)));
+                        tma_load_3d(s.raw + (size_t)st * kRStageF4, &tmap, 0, blk, sg * kRKC,
+                                    &s.full[st]);
+                    }
                     if (++st == nst) {
                         st = 0;
                         ph ^= 1u;
@@ -405,7 +417,7 @@ __global__ void __launch_bounds__(kRThreads, 1)
             nn[u] = 0.f;
         }
         // lane = chunk (float4 column) of the query row: one coalesced 512-byte read per 32 chunks
-        for (int cb = 0; cb < nch; cb += 32) {
+        for (int cb = 0; cb < nch && !(a.dbg & 32); cb += 32) {
             const int c = cb + lane;
             float4 xv[kPer];
 #pragma unroll
@@ -490,13 +502,13 @@ __global__ void __launch_bounds__(kRThreads, 1)
         for (int t = 0; t < ntiles; ++t) {
             const int b = t & 1;
             if (t >= 2) {
-                TCR_WAIT(&s.d_empty[b], (uint32_t)(((t >> 1) & 1) ^ 1), w_dempty);
+                TCR_WAIT(&s.d_empty[b], (uint32_t)(((t >> 1) & 1) ^ 1), w_dempty, 2, t);
                 tc_fence_after_sync();
             }
             const uint32_t tD = tmem + kRColsD + (uint32_t)b * 128u;
             for (int sg = 0; sg < nsg; ++sg) {
                 if (!ready)
-                    TCR_WAIT(&s.a_rdy[as], aph, w_ardy);
+                    TCR_WAIT(&s.a_rdy[as], aph, w_ardy, 3, t * nsg + sg);
                 tc_fence_after_sync();
                 const long long i0_ = tracing ? clock64() : 0;
                 const int ks0 = sg * (kRKC / 2);
@@ -532,9 +544,15 @@ __global__ void __launch_bounds__(kRThreads, 1)
                         mma_tf32_ts(tD, ahi + ks * 8, kl, idesc, 1u);
                         mma_tf32_ts(tD, ahi + ks * 8, kh, idesc, 1u);
                     }
-                    mma_commit(&s.a_empty[as]);
-                    if (sg == nsg - 1)
-                        mma_commit(&s.d_full[b]);
+                    if (a.dbg & 128) {
+                        mbar_arrive(&s.a_empty[as]);
+                        if (sg == nsg - 1)
+                            mbar_arrive(&s.d_full[b]);
+                    } else {
+                        mma_commit(&s.a_empty[as]);
+                        if (sg == nsg - 1)
+                            mma_commit(&s.d_full[b]);
+                    }
                 }
                 __syncwarp();
                 if (tracing)
@@ -565,10 +583,10 @@ __global__ void __launch_bounds__(kRThreads, 1)
             const uint32_t ph = (uint32_t)((it / nst) & 1);
             const int as = it % kRAStages;
             const uint32_t aph = (uint32_t)((it / kRAStages) & 1);
-            TCR_WAIT(&s.full[st], ph, w_full);
+            TCR_WAIT(&s.full[st], ph, w_full, 4, it);
             const float4* src = s.raw + (size_t)st * kRStageF4 + row;
             if (it >= kRAStages) {
-                TCR_WAIT(&s.a_empty[as], aph ^ 1u, w_aempty);
+                TCR_WAIT(&s.a_empty[as], aph ^ 1u, w_aempty, 5, it);
                 tc_fence_after_sync();
             }
             const uint32_t ta = tmem + lane_addr + kRColsA + (uint32_t)as * 64u;
@@ -629,7 +647,7 @@ __global__ void __launch_bounds__(kRThreads, 1)
             const float nrmf = nrm * (1.f - 4.76837158e-7f); // the filter errs on the accept side
             const uint32_t gthr = (myq >= 0 && a.qthr) ? __ldcg(a.qthr + myq) : 0xffffffffu;
             uint32_t drop[kTcrTQ / 32] = {0u, 0u, 0u};
-            TCR_WAIT(&s.d_full[b], (uint32_t)((t >> 1) & 1), w_dfull);
+            TCR_WAIT(&s.d_full[b], (uint32_t)((t >> 1) & 1), w_dfull, 6, t);
             tc_fence_after_sync();
             const uint32_t tD = tmem + lane_addr + kRColsD + (uint32_t)b * 128u;
             int n_events = 0, n_rounds = 0;
@@ -641,6 +659,8 @@ __global__ void __launch_bounds__(kRThreads, 1)
 #pragma unroll 1
                 for (int ch = half; ch < nch16; ch += 2) {
                     uint32_t v[16];
+                    if (a.dbg & 64)
+                        continue;
                     tmem_ld_32x32b_x16(tD + (uint32_t)ch * 16u, v);
                     tmem_ld_wait();
                     if (a.dbg & 1)
@@ -770,6 +790,33 @@ __global__ void __launch_bounds__(kRThreads, 1)
 } // namespace
 
 // ---- host side ----------------------------------------------------------------------------------
+// Host-mapped note a trapping wait leaves behind (mbar_wait_code): {1 + which wait, CTA, thread,
+// iteration, parity}. Pinned host memory, so it survives the context the trap kills.
+static unsigned long long* g_trap_host = nullptr;
+static unsigned long long* g_trap_dev = nullptr;
+unsigned long long* tc_trap_info_device() {
+    if (!g_trap_host) {
+        void* h = nullptr;
+        if (cudaHostAlloc(&h, 8 * sizeof(unsigned long long), cudaHostAllocMapped) != cudaSuccess) {
+            cudaGetLastError();
+            return nullptr;
+        }
+        g_trap_host = static_cast<unsigned long long*>(h);
+        for (int i = 0; i < 8; ++i)
+            g_trap_host[i] = 0;
+        void* d = nullptr;
+        if (cudaHostGetDevicePointer(&d, h, 0) != cudaSuccess) {
+            cudaGetLastError();
+            return nullptr;
+        }
+        g_trap_dev = static_cast<unsigned long long*>(d);
+    }
+    return g_trap_dev;
+}
+const unsigned long long* tc_trap_info_host() {
+    return g_trap_host;
+}
+
 template <int METRIC, int KP>
 static cudaError_t launch_tcr_one(uint32_t max_items, const TcScanArgs& a_in, cudaStream_t st) {
     TcScanArgs a = a_in;
@@ -787,6 +834,7 @@ static cudaError_t launch_tcr_one(uint32_t max_items, const TcScanArgs& a_in, cu
         return e;
     if (max_items == 0)
         return cudaSuccess;
+    a.trap = tc_trap_info_device();
     static const char* tr = getenv("B200IVF_TC_TRACE");
     static const char* trc = getenv("B200IVF_TC_TRACE_COARSE");
     if (tr && (a.nlists > 1) == (trc == nullptr)) {

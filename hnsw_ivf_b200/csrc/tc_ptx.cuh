@@ -86,6 +86,32 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     }
 }
 
+// The same wait, leaving a note for the host before the trap: `info` is host-mapped pinned memory
+// (readable after the context died), code says which wait it was.
+__device__ __forceinline__ void mbar_wait_code(uint64_t* bar, uint32_t parity,
+                                               unsigned long long* info, unsigned code,
+                                               unsigned aux) {
+    uint32_t spins = 0;
+    long long t0 = 0;
+    while (!mbar_try_wait(bar, parity)) {
+        if ((++spins & 1023u) == 0u) {
+            const long long now = clock64();
+            if (t0 == 0)
+                t0 = now;
+            else if (now - t0 > (4ll << 30)) { // ~2 s at 2 GHz
+                if (info && atomicCAS(info, 0ull, 1ull + code) == 0ull) {
+                    info[1] = blockIdx.x;
+                    info[2] = threadIdx.x;
+                    info[3] = aux;
+                    info[4] = parity;
+                    __threadfence_system();
+                }
+                __trap();
+            }
+        }
+    }
+}
+
 // ---- proxies / fences ---------------------------------------------------------------------------
 // generic-proxy writes to shared memory -> visible to the async proxy (TMA, tcgen05.mma operands)
 __device__ __forceinline__ void fence_proxy_async_smem() {

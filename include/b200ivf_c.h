@@ -122,6 +122,12 @@ unsigned long long b200_kernel_launches(void);
 /* ... of which tensor-core (tcgen05) scan launches; tests use it to prove which path ran */
 unsigned long long b200_tensor_core_launches(void);
 
+/* Debugging aid: a pipeline wait of the tensor-core scan that makes no progress for ~2 s traps
+ * (the call fails with a CUDA launch failure) instead of hanging the GPU. Returns 1 and fills
+ * out8 = {1 + which wait, CTA, thread, iteration, parity, 0, 0, 0} if that has happened in this
+ * process, else 0. */
+int b200_debug_trap_info(unsigned long long* out8);
+
 /* merge_knn_results (faiss/utils/Heap.cpp:158-232) as used by IndexShardsIVF::search
  * (faiss/IndexShardsIVF.cpp:224-242): all_* are [nshard][n][k] per-shard sorted tables, host or
  * device; runs on `device`, on `cuda_stream` (may be NULL). */
