@@ -78,6 +78,7 @@ SYMBOLS = [
     ("b200_IndexIVFFlat_last_timings", None, [_vp, C.POINTER(C.c_double)]),
     ("b200_IndexIVFFlat_set_stream", C.c_int, [_vp, _vp]),
     ("b200_debug_trap_info", C.c_int, [C.POINTER(C.c_ulonglong)]),
+    ("b200_IndexIVFFlat_set_option", C.c_int, [_vp, C.c_char_p, C.c_double]),
     ("b200_kernel_launches", C.c_ulonglong, []),
     ("b200_tensor_core_launches", C.c_ulonglong, []),
     ("b200_merge_knn_results", C.c_int,
@@ -498,6 +499,10 @@ class IndexIVFFlat:
         ms = (C.c_double * 5)()
         self._lib.b200_IndexIVFFlat_last_timings(self._h, ms)
         return dict(zip(("coarse", "plan", "scan", "select", "total"), list(ms)))
+
+    def set_option(self, name, value):
+        """kernel-selection knobs (see b200ivf_c.h); results do not depend on them"""
+        self._check(self._lib.b200_IndexIVFFlat_set_option(self._h, name.encode(), float(value)))
 
     def set_stream(self, cuda_stream_ptr):
         """Run on a caller-owned stream (e.g. ``torch.cuda.current_stream().cuda_stream``). torch's

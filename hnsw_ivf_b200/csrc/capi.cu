@@ -179,6 +179,10 @@ int b200_IndexIVFFlat_set_stream(B200IndexIVFFlat* index, void* cuda_stream) {
     return guarded([&] { H(index)->set_stream((cudaStream_t)cuda_stream); });
 }
 
+int b200_IndexIVFFlat_set_option(B200IndexIVFFlat* index, const char* name, double value) {
+    return guarded([&] { H(index)->set_option(name, value); });
+}
+
 unsigned long long b200_tensor_core_launches(void) {
     return b200ivf::g_tc_launches.load();
 }

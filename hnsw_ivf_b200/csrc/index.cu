@@ -202,6 +202,8 @@ struct IndexIVFFlatB200::Impl {
     // average queries per probed list at or below which the SIMT warp kernel takes the whole scan
     // (B200IVF_SIMT_MAXQ, A/B runs)
     double simt_max_avg_q = 1.5;
+    // ... and below which the rows-major tensor-core kernel is preferred to the queries-major one
+    double tcr_max_avg_q = kTcrMaxAvgQueries;
     unsigned long long graph_replays = 0;
     void drop_graphs() {
         for (auto& kv : graphs)
@@ -671,7 +673,7 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
             filtered || !m.use_tc || avg_q <= m.simt_max_avg_q || (kp_q == 0 && kp_r == 0);
     const bool tc = !simt_only;
     const bool tcr = tc && (kp_q == 0 || (kp_r > 0 && (m.tc_mode == 2 || (m.tc_mode == 0 &&
-                                                                          avg_q < kTcrMaxAvgQueries))));
+                                                                          avg_q < m.tcr_max_avg_q))));
     const int64_t kp = tc ? (tcr ? kp_r : kp_q) : k; // entries per partial list
     const int tcr_tq = tcr ? scan_tcr_tq(m.nf4, (int)kp) : 0;
     BatchPlan bp = plan_batch(m.nf4, kp, nb, np, nlists_owned, m.nstored, simt_only, filtered);
@@ -1089,6 +1091,28 @@ void IndexIVFFlatB200::quantize(int64_t n, const float* x, int64_t kc, float* Dq
         if (!(x_dev && D_dev && I_dev))
             CUDA_CHECK(cudaStreamSynchronize(st));
     }
+}
+
+void IndexIVFFlatB200::set_option(const char* name, double value) {
+    std::lock_guard<std::mutex> lock(mu_);
+    DeviceGuard g(device_);
+    Impl& m = *impl_;
+    B200_THROW_IF_NOT_MSG(name != nullptr, "null option name");
+    const std::string n(name);
+    CUDA_CHECK(cudaStreamSynchronize(m.stream));
+    m.drop_graphs(); // a captured pipeline embodies the old choice
+    if (n == "simt_max_avg_q")
+        m.simt_max_avg_q = value;
+    else if (n == "tcr_max_avg_q")
+        m.tcr_max_avg_q = value;
+    else if (n == "tc_mode")
+        m.tc_mode = (int)value;
+    else if (n == "use_tc")
+        m.use_tc = value != 0;
+    else if (n == "use_graph")
+        m.use_graph = value != 0;
+    else
+        throw B200Exception("unknown option '" + n + "'");
 }
 
 IndexIVFStatsB200 IndexIVFFlatB200::get_stats() const {

@@ -115,6 +115,11 @@ class IndexIVFFlatB200 {
     void reset_stats();
     void last_timings(double* ms5) const;
     void set_stream(cudaStream_t s);
+    // kernel-selection knobs (the ParameterSpace of this path): "simt_max_avg_q" / "tcr_max_avg_q"
+    // (queries per probed list below which the exact warp kernel / the rows-major tensor-core
+    // kernel takes the scan), "tc_mode" (0 auto, 1 queries-major, 2 rows-major), "use_tc",
+    // "use_graph". Results do not depend on them.
+    void set_option(const char* name, double value);
 
     int device() const {
         return device_;

@@ -117,6 +117,13 @@ void b200_IndexIVFFlat_last_timings(const B200IndexIVFFlat* index, double* ms5);
  * they are ordered on this stream. */
 int b200_IndexIVFFlat_set_stream(B200IndexIVFFlat* index, void* cuda_stream);
 
+/* Kernel-selection knobs of the scan (what faiss exposes through ParameterSpace::set_index_parameter,
+ * faiss/AutoTune.h:127-170, for its own indexes): "simt_max_avg_q", "tcr_max_avg_q" (queries per
+ * probed list below which the exact warp kernel / the rows-major tensor-core kernel takes the
+ * scan), "tc_mode" (0 auto, 1 queries-major, 2 rows-major), "use_tc", "use_graph". They change
+ * which kernels run, never the results. Unknown names fail with -2. */
+int b200_IndexIVFFlat_set_option(B200IndexIVFFlat* index, const char* name, double value);
+
 /* Number of CUDA kernels this library has launched in this process (all handles). */
 unsigned long long b200_kernel_launches(void);
 /* ... of which tensor-core (tcgen05) scan launches; tests use it to prove which path ran */

@@ -160,8 +160,10 @@ def regime_c4s(args, torch, b2, dev):
     Igt = Igt.cpu().numpy()
     Dd = torch.empty((w["nq"], k), dtype=torch.float32, device=dev)
     Id = torch.empty((w["nq"], k), dtype=torch.int64, device=dev)
-    for p in [int(s) for s in args.nprobes.split(",")]:
+    for p, opts in [(int(s), o) for s in args.nprobes.split(",") for o in option_grid(args.options)]:
         g.nprobe = p
+        for name, v in opts.items():
+            g.set_option(name, v)
         _, I = g.search(xq[:ngt].contiguous(), k)
         rec = B.recall_at_k(I.cpu().numpy(), Igt)
         ur = unique_rows(torch, g, xq, p, w["nlist"])
@@ -182,7 +184,7 @@ def regime_c4s(args, torch, b2, dev):
         scan = statistics.mean(t["scan"] for t in st)
         ndis = g.get_stats().ndis / args.steps
         out = {"regime": "C4s", "workload": w["desc"], "nb": w["nb"], "nlist": w["nlist"],
-               "nprobe": p, "recall_at_10_vs_nprobe256": rec, "ms_per_step": ms,
+               "nprobe": p, "options": opts, "recall_at_10_vs_nprobe256": rec, "ms_per_step": ms,
                "qps": w["nq"] / (ms * 1e-3),
                "stage_ms": {s: statistics.mean(t[s] for t in st) for s in st[0]},
                "scan_unique_bytes": ur * w["d"] * 4.0, "ndis": ndis,
@@ -193,6 +195,15 @@ def regime_c4s(args, torch, b2, dev):
         print(json.dumps(out), flush=True)
 
 
+def option_grid(spec):
+    """'a=1:2,b=3' -> [{}, ...] every combination ({} alone when spec is empty)"""
+    grid = [{}]
+    for part in [p for p in spec.split(",") if p]:
+        name, vals = part.split("=")
+        grid = [dict(g, **{name: float(v)}) for g in grid for v in vals.split(":")]
+    return grid
+
+
 def regime_sweep(args, torch, b2, dev):
     peak, _ = B.measured_hbm_peak()
     for name in args.workloads.split(","):
@@ -201,8 +212,10 @@ def regime_sweep(args, torch, b2, dev):
         k = w["k"]
         Dd = torch.empty((w["nq"], k), dtype=torch.float32, device=dev)
         Id = torch.empty((w["nq"], k), dtype=torch.int64, device=dev)
-        for p in w["nprobes"]:
+        for p, opts in [(p, o) for p in w["nprobes"] for o in option_grid(args.options)]:
             g.nprobe = p
+            for name, v in opts.items():
+                g.set_option(name, v)
             ur = unique_rows(torch, g, xq, p, w["nlist"])
             for _ in range(3):
                 g.search(xq, k, D=Dd, I=Id)
@@ -219,7 +232,8 @@ def regime_sweep(args, torch, b2, dev):
             ms = e0.elapsed_time(e1) / args.steps
             scan = statistics.mean(t["scan"] for t in st)
             ndis = g.get_stats().ndis / args.steps
-            out = {"regime": "sweep", "workload": name, "nprobe": p, "ms_per_step": ms,
+            out = {"regime": "sweep", "workload": name, "nprobe": p, "options": opts,
+                   "ms_per_step": ms,
                    "qps": w["nq"] / (ms * 1e-3),
                    "stage_ms": {s: round(statistics.mean(t[s] for t in st), 4) for s in st[0]},
                    "queries_per_probed_row": ndis / max(ur, 1),
@@ -242,6 +256,9 @@ def main():
                     help="C5: only run three searches of this batch size between cudaProfilerStart/Stop")
     ap.add_argument("--nprobes", default="1,2,4,8,16,32,64")
     ap.add_argument("--workloads", default="C1,C2,C3")
+    ap.add_argument("--options", default="",
+                    help="A/B runs: name=v1:v2:...,name2=... every combination of set_option values "
+                         "is measured at every nprobe (e.g. simt_max_avg_q=1.5:4:8)")
     args = ap.parse_args()
     import torch
     import hnsw_ivf_b200 as b2
