@@ -481,11 +481,14 @@ void IndexIVFFlatB200::run_coarse_(const float* xd, int64_t n, int kc, int32_t* 
     const int64_t tq = tcr ? tcr_tq : tc ? kTcTQ : (tiled ? tcfg.tq : cfg.rq);
     const int64_t ngroups = ceil_div(n, tq);
     const int64_t nblk = ceil_div((int64_t)nlist, kBlockRows);
-    const int64_t rows_step = tc ? 4 : (tiled ? 16 : kScanRowsPerStep); // 32-row blocks per step
+    // a lone query (or a handful) scanning the whole table is latency-bound: single-block row
+    // splits with the deeper unroll (rv = 1) put four times as many warps on the table
+    const bool fine = !tc && !tiled && cfg.rq == 1;
+    const int64_t rows_step = tc ? 4 : (tiled ? 16 : (fine ? 1 : kScanRowsPerStep)); // blocks per step
     const int64_t target = tc ? 148 * 2 : (tiled ? 148 * 2 * 2 : kTargetScanItems);
     int64_t S = ceil_div(target, ngroups);
     S = std::max<int64_t>(1, std::min<int64_t>(S, std::max<int64_t>(1, nblk / rows_step)));
-    S = std::min<int64_t>(S, (!tc && !tiled) ? 128 : 64);
+    S = std::min<int64_t>(S, fine ? 256 : ((!tc && !tiled) ? 128 : 64));
     if (const char* e = getenv("B200IVF_COARSE_S")) // tuning experiments
         S = std::max<int64_t>(1, std::min<int64_t>(atoi(e), std::max<int64_t>(1, nblk / rows_step)));
     const int pmul = (tc && !tcr) ? 2 : 1;
@@ -553,7 +556,8 @@ void IndexIVFFlatB200::run_coarse_(const float* xd, int64_t n, int kc, int32_t* 
         a.nf4 = nf4;
         a.queries = xd;
         a.part = m.part.as<uint64_t>();
-        CUDA_CHECK(launch_ivf_scan(metric_type, cfg.rq, cfg.wpc, (uint32_t)(ngroups * S), a, st));
+        CUDA_CHECK(launch_ivf_scan(metric_type, cfg.rq, cfg.wpc, (uint32_t)(ngroups * S), a, st,
+                                   fine ? 1 : 4));
     }
     SelectArgs s;
     s.part = m.part.as<uint64_t>();
@@ -909,11 +913,32 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
         m.dev_I.reserve((size_t)n * k * sizeof(int64_t));
         if (assign)
             m.dev_assign64.reserve((size_t)pairs * sizeof(int64_t));
+        // Host buffers go through the handle's pinned staging areas: a copy between pageable
+        // memory and the device makes the driver stage it and (device -> host) block the calling
+        // thread per copy; from pinned memory every copy is a plain enqueue and the call blocks
+        // once, in the stream synchronize at the end. These calls are latency-bound: it matters.
+        const size_t xbytes = (size_t)n * d * sizeof(float), abytes = (size_t)pairs * sizeof(int64_t);
+        const size_t Dbytes = (size_t)n * k * sizeof(float), Ibytes = (size_t)n * k * sizeof(int64_t);
+        const void* xsrc = x;
+        if (!x_dev) {
+            m.stage_x.reserve(xbytes);
+            std::memcpy(m.stage_x.p, x, xbytes);
+            xsrc = m.stage_x.p;
+        }
+        const void* asrc = assign;
+        if (assign && !a_dev) {
+            m.stage_assign.reserve(abytes);
+            std::memcpy(m.stage_assign.p, assign, abytes);
+            asrc = m.stage_assign.p;
+        }
+        if (!D_dev)
+            m.stage_D.reserve(Dbytes);
+        if (!I_dev)
+            m.stage_I.reserve(Ibytes);
         CUDA_CHECK(cudaEventRecord(m.ev[0], st));
-        CUDA_CHECK(cudaMemcpyAsync(m.dev_x.p, x, (size_t)n * d * sizeof(float), cudaMemcpyDefault, st));
+        CUDA_CHECK(cudaMemcpyAsync(m.dev_x.p, xsrc, xbytes, cudaMemcpyDefault, st));
         if (assign)
-            CUDA_CHECK(cudaMemcpyAsync(m.dev_assign64.p, assign, (size_t)pairs * sizeof(int64_t),
-                                       cudaMemcpyDefault, st));
+            CUDA_CHECK(cudaMemcpyAsync(m.dev_assign64.p, asrc, abytes, cudaMemcpyDefault, st));
         const int64_t* ad = assign ? m.dev_assign64.as<int64_t>() : nullptr;
         Impl::GraphEntry& ge = m.graphs[{n, np, k, assign ? 1 : 0}];
         uint64_t sig = m.search_sig();
@@ -961,12 +986,18 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
             enqueue(n, m.dev_x.as<float>(), m.dev_D.as<float>(), m.dev_I.as<int64_t>(), ad, true);
         }
         CUDA_CHECK(cudaEventRecord(m.ev[4], st));
-        CUDA_CHECK(cudaMemcpyAsync(D, m.dev_D.p, (size_t)n * k * sizeof(float), cudaMemcpyDefault, st));
-        CUDA_CHECK(cudaMemcpyAsync(I, m.dev_I.p, (size_t)n * k * sizeof(int64_t), cudaMemcpyDefault, st));
+        CUDA_CHECK(cudaMemcpyAsync(D_dev ? (void*)D : m.stage_D.p, m.dev_D.p, Dbytes,
+                                   cudaMemcpyDefault, st));
+        CUDA_CHECK(cudaMemcpyAsync(I_dev ? (void*)I : m.stage_I.p, m.dev_I.p, Ibytes,
+                                   cudaMemcpyDefault, st));
         CUDA_CHECK(cudaEventRecord(m.ev[5], st));
         CUDA_CHECK(cudaMemcpyAsync(m.host_stats.p, dstats, 4 * sizeof(unsigned long long),
                                    cudaMemcpyDeviceToHost, st));
         CUDA_CHECK(cudaStreamSynchronize(st));
+        if (!D_dev)
+            std::memcpy(D, m.stage_D.p, Dbytes);
+        if (!I_dev)
+            std::memcpy(I, m.stage_I.p, Ibytes);
         float ms;
         if (!ran)
             for (int s = 1; s < 4; ++s) { // stage times exist only for the eager run
