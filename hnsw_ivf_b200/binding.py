@@ -296,11 +296,22 @@ class IndexIVFFlat:
                                                                     device))
         self._h = h
         self.device = device
+        self._own_stream = True
 
     def __del__(self):
         if getattr(self, "_h", None):
             self._lib.b200_IndexIVFFlat_free(self._h)
             self._h = None
+
+    def _order_with_torch(self, *arrays):
+        """While the handle runs on its own (non-blocking) stream it is not ordered with torch's:
+        CUDA tensors handed to it may still be being produced there, and result tensors fresh from
+        torch's caching allocator may still be in use by queued torch work. So: wait for torch's
+        current stream first. After ``set_stream(torch.cuda.current_stream().cuda_stream)`` the
+        library is stream-ordered with torch and nothing is waited for."""
+        if self._own_stream and any(a is not None and _is_torch(a) and a.is_cuda for a in arrays):
+            import torch
+            torch.cuda.current_stream(self.device).synchronize()
 
     def _check(self, rc):
         if rc != 0:
@@ -335,10 +346,12 @@ class IndexIVFFlat:
         kx, px = _ptr(x, np.float32, None, "x")
         if kx.ndim != 2 or kx.shape[1] != self.d:
             raise ValueError("x must be [n][%d]" % self.d)
+        self._order_with_torch(kx)
         self._check(self._lib.b200_IndexIVFFlat_train(self._h, kx.shape[0], px))
 
     def set_centroids(self, c):
         keep, p = _ptr(c, np.float32, (self.nlist, self.d), "centroids")
+        self._order_with_torch(keep)
         self._check(self._lib.b200_IndexIVFFlat_set_centroids(self._h, p))
 
     def get_centroids(self):
@@ -356,6 +369,7 @@ class IndexIVFFlat:
         kx, px = _ptr(x, np.float32, None, "x")
         n = kx.shape[0]
         ki, pi = _ptr(ids, np.int64, (n,), "ids")
+        self._order_with_torch(kx, ki)
         self._check(self._lib.b200_IndexIVFFlat_add_with_ids(self._h, n, px, pi))
 
     def add_core(self, x, ids, assign):
@@ -363,6 +377,7 @@ class IndexIVFFlat:
         n = kx.shape[0]
         ki, pi = _ptr(ids, np.int64, (n,), "ids")
         ka, pa = _ptr(assign, np.int64, (n,), "assign")
+        self._order_with_torch(kx, ki, ka)
         self._check(self._lib.b200_IndexIVFFlat_add_core(self._h, n, px, pi, pa))
 
     def reset(self):
@@ -393,6 +408,7 @@ class IndexIVFFlat:
             I = _empty_like_input(kx, (n, k), np.int64)
         kd, pd = _ptr(D, np.float32, (n, k), "D")
         ki, pi = _ptr(I, np.int64, (n, k), "I")
+        self._order_with_torch(kx, kd, ki)
         if params is None:
             self._check(self._lib.b200_IndexIVFFlat_search(self._h, n, px, k, pd, pi))
         else:
@@ -413,6 +429,7 @@ class IndexIVFFlat:
             I = _empty_like_input(kx, (n, k), np.int64)
         kd, pd = _ptr(D, np.float32, (n, k), "D")
         ki, pi = _ptr(I, np.int64, (n, k), "I")
+        self._order_with_torch(kx, ka, kd, ki)
         if params is None and not store_pairs:
             self._check(self._lib.b200_IndexIVFFlat_search_preassigned(self._h, n, px, k, pa, pc,
                                                                        pd, pi, 0))
@@ -431,6 +448,7 @@ class IndexIVFFlat:
         I = _empty_like_input(kx, (n, k), np.int64)
         kd, pd = _ptr(D, np.float32, (n, k), "D")
         ki, pi = _ptr(I, np.int64, (n, k), "I")
+        self._order_with_torch(kx, kd, ki)
         st = (QueryLatencyStats * max(n, 1))()
         self._check(self._lib.b200_IndexIVFFlat_search_stats(
             self._h, n, px, k, pd, pi, params._h if params is not None else None, st))
@@ -464,6 +482,7 @@ class IndexIVFFlat:
         L2 keeps dis < radius, inner product dis > radius."""
         kx, px = _ptr(x, np.float32, None, "x")
         n = kx.shape[0]
+        self._order_with_torch(kx)
         return self._range_result(lambda r: self._lib.b200_IndexIVFFlat_range_search(
             self._h, n, px, float(radius), r, params._h if params is not None else None), n)
 
@@ -472,6 +491,7 @@ class IndexIVFFlat:
         n = kx.shape[0]
         nprobe = min(params.nprobe if params is not None else self.nprobe, self.nlist)
         ka, pa = _ptr(assign, np.int64, (n, nprobe), "assign")
+        self._order_with_torch(kx, ka)
         return self._range_result(lambda r: self._lib.b200_IndexIVFFlat_range_search_preassigned(
             self._h, n, px, float(radius), pa, None, r, int(bool(store_pairs)),
             params._h if params is not None else None), n)
@@ -483,7 +503,13 @@ class IndexIVFFlat:
         Iq = _empty_like_input(kx, (n, nprobe), np.int64)
         kd, pd = _ptr(Dq, np.float32, None, "Dq")
         ki, pi = _ptr(Iq, np.int64, None, "Iq")
+        self._order_with_torch(kx, kd, ki)
         self._check(self._lib.b200_IndexIVFFlat_quantize(self._h, n, px, nprobe, pd, pi))
+        if self._own_stream and _is_torch(kx) and kx.is_cuda:
+            # an all-device quantize returns before its kernels finish (b200ivf_c.h, set_stream);
+            # on the handle's own stream nothing orders torch's next read of the result with them
+            import torch
+            torch.cuda.synchronize(self.device)
         return kd, ki
 
     # ---- stats / plumbing ----------------------------------------------------------------------
@@ -509,6 +535,7 @@ class IndexIVFFlat:
         default stream has handle 0, which the C-ABI reads as "the handle's own stream": it is
         passed as cudaStreamLegacy (0x1) instead, so that the library really is stream-ordered
         with the caller's torch work. ``None`` selects the handle's own stream."""
+        self._own_stream = cuda_stream_ptr is None
         if cuda_stream_ptr is None:
             cuda_stream_ptr = 0
         elif cuda_stream_ptr == 0:
