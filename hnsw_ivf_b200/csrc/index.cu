@@ -489,6 +489,22 @@ void IndexIVFFlatB200::run_coarse_(const float* xd, int64_t n, int kc, int32_t* 
     int64_t S = ceil_div(target, ngroups);
     S = std::max<int64_t>(1, std::min<int64_t>(S, std::max<int64_t>(1, nblk / rows_step)));
     S = std::min<int64_t>(S, fine ? 256 : ((!tc && !tiled) ? 128 : 64));
+    if (tc) {
+        // one CTA per SM: pick the split count whose (waves x tiles per item + per-item prologue,
+        // worth ~3 tiles) is smallest, instead of a fixed item target (C2: 79 query tiles x 4
+        // splits = 316 items = 2.1 waves of 148 ran as 3 waves; x 3 splits = 2 waves, 10 % faster)
+        const int64_t T = ceil_div(nblk, rows_step);
+        const int64_t smax = std::max<int64_t>(1, std::min<int64_t>(16, T));
+        int64_t best = 1, best_cost = INT64_MAX;
+        for (int64_t c = 1; c <= smax; ++c) {
+            const int64_t cost = ceil_div(ngroups * c, 148) * (ceil_div(T, c) + 3);
+            if (cost < best_cost) {
+                best_cost = cost;
+                best = c;
+            }
+        }
+        S = best;
+    }
     if (const char* e = getenv("B200IVF_COARSE_S")) // tuning experiments
         S = std::max<int64_t>(1, std::min<int64_t>(atoi(e), std::max<int64_t>(1, nblk / rows_step)));
     const int pmul = (tc && !tcr) ? 2 : 1;
