@@ -496,13 +496,15 @@ class IndexIVFFlat:
             self._h, n, px, float(radius), pa, None, r, int(bool(store_pairs)),
             params._h if params is not None else None), n)
 
-    def quantize(self, x, nprobe):
+    def quantize(self, x, nprobe, Dq=None, Iq=None):
         kx, px = _ptr(x, np.float32, None, "x")
         n = kx.shape[0]
-        Dq = _empty_like_input(kx, (n, nprobe), np.float32)
-        Iq = _empty_like_input(kx, (n, nprobe), np.int64)
-        kd, pd = _ptr(Dq, np.float32, None, "Dq")
-        ki, pi = _ptr(Iq, np.int64, None, "Iq")
+        if Dq is None:
+            Dq = _empty_like_input(kx, (n, nprobe), np.float32)
+        if Iq is None:
+            Iq = _empty_like_input(kx, (n, nprobe), np.int64)
+        kd, pd = _ptr(Dq, np.float32, (n, nprobe), "Dq")
+        ki, pi = _ptr(Iq, np.int64, (n, nprobe), "Iq")
         self._order_with_torch(kx, kd, ki)
         self._check(self._lib.b200_IndexIVFFlat_quantize(self._h, n, px, nprobe, pd, pi))
         if self._own_stream and _is_torch(kx) and kx.is_cuda:
