@@ -573,6 +573,82 @@ cudaError_t launch_select(const SelectArgs& a, cudaStream_t st) {
     return cudaGetLastError();
 }
 
+// The same merge without its chain of dependent loads (the walk above pays one L2 round trip per
+// output slot): one warp per query loads all nshard * k entries at once into shared memory, every
+// entry finds its rank in the merged order as its own position plus, for every other shard, the
+// number of that shard's entries that come before it (a binary search: shard tables are sorted),
+// and the entries of rank < k go straight to their slots. nshard * k <= kMergeRankMax.
+constexpr int kMergeRankMax = 512;
+constexpr int kMergeRankWarps = 4;
+
+// equal distances: the lower shard number first, as the reference's heap over the shard heads
+// orders them (cmp2 on (distance, shard), faiss/utils/Heap.cpp:186-225); ids take no part, so the
+// order inside a shard's own run of equal distances is whatever the shard delivered
+__device__ __forceinline__ bool merge_before(bool l2, float da, int sa, float db, int sb) {
+    if (da != db)
+        return l2 ? (da < db) : (da > db);
+    return sa < sb;
+}
+
+__global__ void __launch_bounds__(kMergeRankWarps * 32)
+        merge_shards_rank_kernel(int metric, int nshard, int n, int k, const float* all_dis,
+                                 const int64_t* all_ids, float* out_dis, int64_t* out_ids) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int q = blockIdx.x * kMergeRankWarps + w;
+    if (q >= n)
+        return;
+    const bool l2 = metric == kMetricL2;
+    const int E = nshard * k;
+    int64_t* sid = reinterpret_cast<int64_t*>(smem_raw) + (size_t)w * E;
+    float* sd = reinterpret_cast<float*>(reinterpret_cast<int64_t*>(smem_raw) +
+                                         (size_t)kMergeRankWarps * E) + (size_t)w * E;
+    const size_t stride = (size_t)n * k;
+    for (int e = lane; e < E; e += 32) {
+        const int s = e / k, pos = e - s * k;
+        const size_t o = stride * s + (size_t)q * k + pos;
+        sid[e] = all_ids[o];
+        sd[e] = all_dis[o];
+    }
+    __syncwarp();
+    int nvalid = 0;
+    for (int e = lane; e < E; e += 32) {
+        const int64_t id = sid[e];
+        if (id < 0)
+            continue;
+        nvalid++;
+        const int s = e / k, pos = e - s * k;
+        const float dv = sd[e];
+        int rank = pos;
+        for (int s2 = 0; s2 < nshard; ++s2) {
+            if (s2 == s)
+                continue;
+            // entries of shard s2 that come before this one: first index that does not
+            int lo = 0, hi = k;
+            while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                const int64_t im = sid[s2 * k + mid];
+                if (im >= 0 && merge_before(l2, sd[s2 * k + mid], s2, dv, s))
+                    lo = mid + 1;
+                else
+                    hi = mid;
+            }
+            rank += lo;
+        }
+        if (rank < k) {
+            const size_t o = (size_t)q * k + rank;
+            out_dis[o] = dv;
+            out_ids[o] = id;
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1)
+        nvalid += __shfl_xor_sync(0xffffffffu, nvalid, o);
+    for (int j = nvalid + lane; j < k; j += 32) { // not enough results: the reference's padding
+        out_dis[(size_t)q * k + j] = l2 ? kNeutralScore : -kNeutralScore;
+        out_ids[(size_t)q * k + j] = -1;
+    }
+}
+
 cudaError_t launch_merge_shards(int metric, int nshard, int n, int k, const float* all_dis,
                                 const int64_t* all_ids, float* out_dis, int64_t* out_ids,
                                 cudaStream_t st) {
@@ -580,6 +656,14 @@ cudaError_t launch_merge_shards(int metric, int nshard, int n, int k, const floa
         return cudaSuccess;
     if (nshard > 256)
         return cudaErrorInvalidValue;
+    if ((int64_t)nshard * k <= kMergeRankMax) {
+        const size_t smem = (size_t)kMergeRankWarps * nshard * k * (sizeof(int64_t) + sizeof(float));
+        merge_shards_rank_kernel<<<(n + kMergeRankWarps - 1) / kMergeRankWarps,
+                                   kMergeRankWarps * 32, smem, st>>>(metric, nshard, n, k, all_dis,
+                                                                     all_ids, out_dis, out_ids);
+        count_launches(1);
+        return cudaGetLastError();
+    }
     const int wpb = 4;
     merge_shards_kernel<<<(n + wpb - 1) / wpb, wpb * 32, 0, st>>>(metric, nshard, n, k, all_dis,
                                                                  all_ids, out_dis, out_ids);

@@ -342,3 +342,49 @@ def test_small_batch_graph_replay(cuda_device, metric):
         Do, Io = o.search_preassigned(q, k, Iq)
         Dg, Ig = g.search_preassigned(q, k, Iq)
         assert_knn_parity(Do, Io, Dg, Ig, what="graph after add, call %d" % r)
+
+
+@pytest.mark.parametrize("metric", [L2, IP])
+@pytest.mark.parametrize("nshard,k", [(2, 10), (3, 1), (8, 10), (8, 64), (5, 100), (40, 16)])
+def test_merge_knn_results_tables(cuda_device, metric, nshard, k):
+    """merge_knn_results (faiss/utils/Heap.cpp:158-232) on random sorted per-shard tables with -1
+    padding and exact ties: both device kernels (rank merge for nshard*k <= 512, head walk above)
+    against the restatement"""
+    from oracle import pyoracle as po
+    import hnsw_ivf_b200 as b2
+    rng = np.random.default_rng(nshard * 100 + k)
+    n = 257
+    all_D = np.empty((nshard, n, k), np.float32)
+    all_I = np.empty((nshard, n, k), np.int64)
+    for s in range(nshard):
+        v = rng.integers(0, 40 * k, size=(n, k)).astype(np.float32) / 4.0  # coarse grid: many ties
+        v.sort(axis=1)
+        if metric == IP:
+            v = -v
+        ids = rng.permutation(n * k * nshard)[: n * k].reshape(n, k).astype(np.int64) * nshard + s
+        nvalid = rng.integers(0, k + 1, size=n)
+        nvalid[: n // 2] = k
+        for q in range(n):
+            ids[q, nvalid[q]:] = -1
+            v[q, nvalid[q]:] = np.finfo(np.float32).max if metric == L2 else -np.finfo(np.float32).max
+        all_D[s], all_I[s] = v, ids
+    Dg, Ig = b2.merge_knn_results(metric, all_D, all_I)
+    Dp, Ip = po.port_merge_knn_results(metric, all_D, all_I)
+    assert np.array_equal(Dg, Dp)
+    assert np.array_equal(Ig < 0, Ip < 0)
+    for q in range(n):
+        if np.array_equal(Ig[q], Ip[q]):
+            continue
+        # ids may differ only inside runs of equal distance (ties: by shard there, by id here),
+        # and then as sets unless the run is cut by the k-th slot
+        for val in np.unique(Dg[q][Ig[q] >= 0]):
+            m = Dg[q] == val
+            if m[-1]:
+                continue
+            assert set(Ig[q][m].tolist()) == set(Ip[q][m].tolist()), (q, val)
+        # every id we return is one of the inputs with that distance
+        for j in range(k):
+            if Ig[q, j] >= 0:
+                s = int(Ig[q, j] % nshard)
+                pos = np.nonzero(all_I[s, q] == Ig[q, j])[0]
+                assert pos.size == 1 and all_D[s, q, pos[0]] == Dg[q, j]
