@@ -28,7 +28,7 @@
 //  * Epilogue (4 warps, thread = row = TMEM lane): per 16 queries one tcgen05.ld; score (+ |y|^2
 //    for L2) is compared with the query's pruning bound held in shared memory; a warp ballot skips
 //    the column when no row passes (the steady state). Passing (score, row) keys are appended to
-//    the query's candidate buffer (KP kept + 16 free entries) with a shared-memory atomic; at the
+//    the query's candidate buffer (64 entries: KP kept + free ones) with a shared-memory atomic; at the
 //    end of a tile the warps compact the buffers that filled up (warp bitonic sort, keep KP,
 //    tighten the bound, publish it in qthr for the other CTAs working on the same query). A tile
 //    that overflows a buffer is re-examined for the dropped rows after the compaction (at most 8
@@ -62,8 +62,15 @@ constexpr uint32_t kRColsD = 0;   // two accumulator buffers of 128 columns
 constexpr uint32_t kRColsA = 256; // kRAStages x (32 hi + 32 lo) columns
 constexpr int kRMaxChunks = 256;  // float4 columns of a query (d <= 1024)
 constexpr uint32_t kRBSBO = 128;
-constexpr int kRFree = 16;        // free candidate entries beyond the KP kept
-constexpr int kRCompactMin = 8;   // compact a buffer once it holds this many new candidates
+// Candidate buffer of a query: kRCand entries = the KP kept + free ones. A buffer is compacted
+// (sorted, cut to KP, bound tightened) once it holds kRCompactAt entries, which leaves kRCand -
+// kRCompactAt slots for the rest of the tile before rows start to be dropped and re-examined.
+// A compaction stops the whole epilogue at two block barriers, and the epilogue is the stage that
+// paces the kernel when few queries meet in a list: with 16 free slots and a compaction every 8
+// new candidates there was about one per tile (10 queries x ~1 candidate per tile each); 64 entries
+// compacted at 48 make it one tile in four.
+constexpr int kRCand = 64;
+constexpr int kRCompactAt = 48;
 
 __device__ __forceinline__ float tf32_trunc(float x) {
     return __uint_as_float(__float_as_uint(x) & 0xffffe000u);
@@ -77,7 +84,8 @@ __device__ __forceinline__ float tf32_lo(float y) {
 
 template <int KP>
 struct RCfg {
-    static constexpr int C = KP + kRFree;           // candidate entries per query
+    static constexpr int C = kRCand;                // candidate entries per query
+    static_assert(KP + 16 <= kRCompactAt, "compaction must leave room above the kept entries");
 };
 
 // ascending bitonic sort of one key per lane
@@ -167,7 +175,7 @@ __host__ __device__ inline uint32_t tcr_lbo(int n16) {
     return (uint32_t)(n16 + 1) * 16u;
 }
 __host__ __device__ inline size_t tcr_rest_bytes(int kp, int n16, int nch) {
-    return 2 * (size_t)nch * tcr_lbo(n16) + (size_t)n16 * (kp + kRFree) * 8 +
+    return 2 * (size_t)nch * tcr_lbo(n16) + (size_t)n16 * kRCand * 8 +
             (size_t)kTcrTQ * 6 * 4 + 4 * 4 + (2 * kRMaxStages + 2 * kRAStages + 4) * 8 + 16;
 }
 __host__ __device__ inline int tcr_stages(size_t smem_total, int kp, int n16, int nch) {
@@ -216,9 +224,9 @@ __device__ __noinline__ void tcr_compact(uint64_t* cand, int* cnt, uint32_t* thr
                                          float* thrf, const float* xn, const int* qid,
                                          uint32_t* qthr, int nqw, int warp, int lane,
                                          bool final_pass) {
-    constexpr int C = KP + kRFree;
+    constexpr int C = kRCand;
     const int qmine = lane * kREpiWarps + warp;
-    const bool need = qmine < nqw && (final_pass || cnt[qmine] >= KP + kRCompactMin);
+    const bool need = qmine < nqw && (final_pass || cnt[qmine] >= kRCompactAt);
     unsigned todo = __ballot_sync(0xffffffffu, need);
     while (todo != 0u) {
         const int qi = (__ffs(todo) - 1) * kREpiWarps + warp;
@@ -709,7 +717,7 @@ __global__ void __launch_bounds__(kRThreads, 1)
                                 ndrop |= 1u << j;
                                 fl |= 2;
                             }
-                            if (slot + 1 >= KP + kRCompactMin)
+                            if (slot + 1 >= kRCompactAt)
                                 fl |= 1;
                         }
                     }
