@@ -257,3 +257,30 @@ def test_train_objective_and_recall(cuda_device, metric):
     Do, Io = o.search(xq, k, nprobe)
     _, gt = brute_force(metric, xq, xb, k)
     assert recall_at_k(I, gt) >= recall_at_k(Io, gt) - 0.02
+
+
+def test_more_queries_than_one_device_batch(cuda_device):
+    """n > 32768 queries: the host loop over device batches (range-search result offsets carried
+    across batches, per-query stats filled batch by batch, selector mask evaluated once)"""
+    import hnsw_ivf_b200 as b2
+    d, nb, nlist, nprobe, k, nq = 16, 20000, 32, 4, 5, 40000
+    xb, ids, o, g = _pair(d, nb, nlist, L2, seed=91)
+    xq = clustered(nq, d, 4 * nlist, 92)
+    Dq, Iq = o.quantize(xq, nprobe)
+    g.nprobe = nprobe
+    sp = ("range", 0, 2 * nb)
+    p = b2.SearchParametersIVF(sel=gpu_selector(sp), nprobe=nprobe, max_codes=1500)
+    Do, Io = o.search_preassigned_ex(xq, k, Iq, max_codes=1500, sel=sp)
+    Dg, Ig = g.search_preassigned(xq, k, Iq, params=p)
+    assert_knn_parity(Do, Io, Dg, Ig, what="two batches, params")
+    radius = float(np.median(Do[:, 2]))
+    lo, Dr, Ir = o.range_search_preassigned(xq, radius, Iq)
+    lg, Dgr, Igr = g.range_search_preassigned(xq, radius, Iq)
+    assert int(lo[-1]) > nq
+    nbd = compare_range(lo, Dr, Ir, lg, Dgr, Igr, radius, L2)
+    assert nbd <= 8, nbd
+    if nbd == 0:
+        assert np.array_equal(lo, lg) and np.array_equal(Ir, Igr)
+    Ds, Is, st = g.search_stats(xq, k)
+    D2, I2 = g.search(xq, k)
+    assert np.array_equal(Is, I2) and st.shape == (nq,) and np.all(st["total_us"] > 0)
