@@ -7,8 +7,8 @@
 A "step" is ONE search call over one batch of nq synthetic queries (coarse quantize -> inverted-list
 scan -> k-select), k = 10. Workload at every N: BASELINE.json configs[1] ("C2"): IndexIVFFlat
 nlist=4096, METRIC_INNER_PRODUCT, 10M x 128 fp32 (the reference's SyntheticDataset recipe,
-contrib/datasets.py:74-111, L2-normalised), 10k-query batch; nprobe = the smallest power of two in 1..128 whose
-recall@10 against exact brute force is >= 0.95 (the sweep is printed in config.nprobe_sweep).
+contrib/datasets.py:74-111, L2-normalised), 10k-query batch; nprobe = the smallest value of the sweep
+(1, 2, 4, 8, 12, ..., 128: WORKLOADS[...]['nprobes']) whose recall@10 against exact brute force is >= 0.95 (the sweep is printed in config.nprobe_sweep).
 For N > 1 the lists are partitioned by contiguous list range over the ranks (one process per GPU),
 queries are broadcast from rank 0, per-rank top-k tables are all-gathered with NCCL and merged on
 device: total work is fixed, so "scaling": "strong".
