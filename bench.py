@@ -15,9 +15,12 @@ device: total work is fixed, so "scaling": "strong".
 
 Keys of the one JSON line: see the task contract. `value` = device-resident QPS; `e2e` = QPS through
 the C-ABI with HOST (pinned) query / result buffers, copies inside the timed region; `roofline` is
-for the list-scan kernel (ivf_scan_kernel): algorithmic bytes 4*d*ndis (ndis = the reference's
-IndexIVFStats::ndis, faiss/IndexIVF.cpp:624,721) over the kernel's CUDA-event time measured by the
-library on its launch stream; `cpu_baseline` = the UNMODIFIED reference compiled into oracle/_ref
+for the list scan (ivf_scan_tc_kernel / ivf_scan_tcr_kernel / ivf_scan_kernel, whichever the plan
+picks): bytes of the DISTINCT lists the batch probes (the scan is list-major: a list crosses HBM
+once for all its queries) over the scan's CUDA-event time measured by the
+library on its launch stream, with the reference's per-pair figure 4*d*ndis (ndis = the reference's
+IndexIVFStats::ndis, faiss/IndexIVF.cpp:624,721) kept beside it, the ncu DRAM traffic per launch
+(profiles/scan_traffic.json) and the tensor-pipe fraction; `cpu_baseline` = the UNMODIFIED reference compiled into oracle/_ref
 (kind "reference"; the plain-C port if that library is absent) searching a bounded query sample of
 the same index on all host cores.
 
