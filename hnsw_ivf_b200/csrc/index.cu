@@ -91,6 +91,7 @@ struct DeviceGuard {
 constexpr size_t kScanSmemBudget = 200 * 1024;
 // warps the scan should have available: 148 SMs x ~12 resident warps x 2 waves
 constexpr int64_t kTargetScanItems = 148 * 12 * 2;
+constexpr int64_t kTargetScanItemsSimt = 148 * 32 * 4;
 constexpr int kScanRowsPerStep = 4; // RV of the scan kernel
 
 struct ScanCfg {
@@ -201,7 +202,7 @@ struct IndexIVFFlatB200::Impl {
     bool use_graph = true;
     // average queries per probed list at or below which the SIMT warp kernel takes the whole scan
     // (B200IVF_SIMT_MAXQ, A/B runs)
-    double simt_max_avg_q = 1.5;
+    double simt_max_avg_q = 3.0;
     // ... and below which the rows-major tensor-core kernel is preferred to the queries-major one
     double tcr_max_avg_q = kTcrMaxAvgQueries;
     unsigned long long graph_replays = 0;
@@ -494,7 +495,7 @@ void IndexIVFFlatB200::run_coarse_(const float* xd, int64_t n, int kc, int32_t* 
         // worth ~3 tiles) is smallest, instead of a fixed item target (C2: 79 query tiles x 4
         // splits = 316 items = 2.1 waves of 148 ran as 3 waves; x 3 splits = 2 waves, 10 % faster)
         const int64_t T = ceil_div(nblk, rows_step);
-        const int64_t smax = std::max<int64_t>(1, std::min<int64_t>(16, T));
+        const int64_t smax = std::max<int64_t>(1, std::min<int64_t>(64, T));
         int64_t best = 1, best_cost = INT64_MAX;
         for (int64_t c = 1; c <= smax; ++c) {
             const int64_t cost = ceil_div(ngroups * c, 148) * (ceil_div(T, c) + 3);
@@ -620,7 +621,17 @@ static BatchPlan plan_batch(int nf4, int64_t kpart, int64_t nb, int64_t nprobe,
             std::max<int64_t>(1, std::max(ceil_div(pairs, bp.cfg.rq), std::min(pairs, nlists_owned)));
     const int64_t avg_blocks =
             std::max<int64_t>(1, nstored / std::max<int64_t>(1, nlists_owned) / kBlockRows);
+    // When the warp kernel is the whole scan (hardly any list shared between queries) it is a pure
+    // stream and wants many more warps than lists: 4 waves of 32 warps per SM (C2, nprobe 1: 4096
+    // probed lists as 4096 warps ran at 2.8 TB/s, split five ways at 4.4 TB/s). The mixed plans keep
+    // the small target: their row splits multiply the tensor-core items too.
+    static const int64_t simt_target = getenv("B200IVF_SCAN_TARGET") // tuning experiments
+            ? std::max<int64_t>(1, atoll(getenv("B200IVF_SCAN_TARGET")))
+            : kTargetScanItemsSimt;
     int64_t S = ceil_div(kTargetScanItems, items_est);
+    if (simt_only) // ... as long as a warp keeps at least 12 blocks (384 rows) to stream: below
+                   // that the per-warp costs (query staging, final sort) outweigh the extra warps
+        S = std::max(S, std::min(ceil_div(simt_target, items_est), avg_blocks / 12));
     // few pairs (small batches): split down to single blocks so that the whole GPU streams
     if (simt_only && !filtered && bp.cfg.rq == 1 && S > avg_blocks / kScanRowsPerStep) {
         bp.cfg.rv = 1;

@@ -42,6 +42,8 @@ def _pair(d, nb, nlist, metric, seed=1):
     hs = []
     for tc in (True, False):
         g = _handle(d, nlist, metric, tc)
+        if tc:  # these tests are about the tensor-core kernels: keep them on at every shape
+            g.set_option("simt_max_avg_q", 0.5)
         g.set_centroids(cent)
         g.add_core(xb, None, assign)
         hs.append(g)
