@@ -33,7 +33,8 @@ from .binding import (  # noqa: F401
     read_index,
     write_index,
 )
-from .sharded import IndexShardsIVFFlat, list_range_of_rank  # noqa: F401
+from .sharded import (IndexShardsIVFFlat, ShardedSearchModel, list_range_of_rank,  # noqa: F401
+                      nccl_unique_id)
 
 __all__ = [
     "METRIC_INNER_PRODUCT", "METRIC_L2", "B200Error", "IndexIVFFlat", "IndexIVFStats",
@@ -41,5 +42,5 @@ __all__ = [
     "IDSelectorNot", "IDSelectorAnd", "IDSelectorOr", "IDSelectorXOr", "SearchParametersIVF",
     "QueryLatencyStats",
     "IndexShardsIVFFlat", "build_library", "kernel_launches", "tensor_core_launches", "library_path", "load_library", "merge_knn_results", "read_index", "write_index",
-    "list_range_of_rank",
+    "list_range_of_rank", "ShardedSearchModel", "nccl_unique_id",
 ]

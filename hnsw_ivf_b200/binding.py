@@ -118,6 +118,27 @@ SYMBOLS = [
     ("b200_IndexIVFFlat_range_search", C.c_int, [_vp, C.c_int64, _f32p, C.c_float, _vp, _vp]),
     ("b200_IndexIVFFlat_range_search_preassigned", C.c_int,
      [_vp, C.c_int64, _f32p, C.c_float, _i64p, _f32p, _vp, C.c_int, _vp]),
+    ("b200_IndexIVFFlat_reserve_lists", C.c_int, [_vp, _i64p]),
+    ("b200_IndexIVFFlat_get_list_sizes", C.c_int, [_vp, _i64p]),
+    ("b200_IndexIVFFlat_stage_time_sums", C.c_ulonglong, [_vp, C.POINTER(C.c_double)]),
+    ("b200_IndexIVFFlat_synchronize", C.c_int, [_vp]),
+    ("b200_nccl_get_unique_id", C.c_int, [_vp]),
+    ("b200_IndexShardsIVFFlat_new", C.c_int,
+     [C.POINTER(_vp), C.c_size_t, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int, _vp]),
+    ("b200_IndexShardsIVFFlat_free", None, [_vp]),
+    ("b200_IndexShardsIVFFlat_local", _vp, [_vp]),
+    ("b200_IndexShardsIVFFlat_rank", C.c_int, [_vp]),
+    ("b200_IndexShardsIVFFlat_world", C.c_int, [_vp]),
+    ("b200_IndexShardsIVFFlat_ntotal", C.c_int64, [_vp]),
+    ("b200_IndexShardsIVFFlat_set_centroids", C.c_int, [_vp, _f32p, C.c_int]),
+    ("b200_IndexShardsIVFFlat_train", C.c_int, [_vp, C.c_int64, _f32p, C.c_int]),
+    ("b200_IndexShardsIVFFlat_add_with_ids", C.c_int, [_vp, C.c_int64, _f32p, _i64p]),
+    ("b200_IndexShardsIVFFlat_add_core", C.c_int, [_vp, C.c_int64, _f32p, _i64p, _i64p]),
+    ("b200_IndexShardsIVFFlat_search", C.c_int,
+     [_vp, C.c_int64, _f32p, C.c_int64, _f32p, _i64p, C.c_int]),
+    ("b200_IndexShardsIVFFlat_phase_time_sums", C.c_ulonglong, [_vp, C.POINTER(C.c_double)]),
+    ("b200_IndexShardsIVFFlat_reset_phase_times", None, [_vp]),
+    ("b200_IndexShardsIVFFlat_synchronize", C.c_int, [_vp]),
     ("b200_write_index_fname", C.c_int, [_vp, C.c_char_p]),
     ("b200_read_index_fname", C.c_int, [C.c_char_p, C.c_int, C.c_int, C.POINTER(_vp)]),
 ]
@@ -285,7 +306,7 @@ class IndexIVFFlat:
     ``search_stats``. Centroids trained elsewhere can be installed with ``set_centroids``.
     """
 
-    def __init__(self, d, nlist, metric=METRIC_L2, device=0, _handle=None):
+    def __init__(self, d, nlist, metric=METRIC_L2, device=0, _handle=None, _borrowed=False):
         self._lib = load_library()
         h = _vp()
         self._h = None
@@ -295,13 +316,26 @@ class IndexIVFFlat:
             self._check(self._lib.b200_IndexIVFFlat_new_with_metric(C.byref(h), d, nlist, metric,
                                                                     device))
         self._h = h
+        self._borrowed = _borrowed  # a shard of an IndexShardsIVFFlat: freed with its owner
         self.device = device
         self._own_stream = True
 
     def __del__(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and not getattr(self, "_borrowed", False):
             self._lib.b200_IndexIVFFlat_free(self._h)
-            self._h = None
+        self._h = None
+
+    def _settle(self, *arrays):
+        """All-device calls return once their work is enqueued on the handle's stream
+        (b200ivf_c.h, set_stream). While that is the handle's own stream nothing orders torch's
+        next use of the results with it, so wait here; after ``set_stream(torch's stream)`` the
+        call stays asynchronous and stream-ordered."""
+        if self._own_stream and any(a is not None and _is_torch(a) and a.is_cuda for a in arrays):
+            self._check(self._lib.b200_IndexIVFFlat_synchronize(self._h))
+
+    def synchronize(self):
+        """wait for asynchronous calls in flight; raises their deferred failure, if any"""
+        self._check(self._lib.b200_IndexIVFFlat_synchronize(self._h))
 
     def _order_with_torch(self, *arrays):
         """While the handle runs on its own (non-blocking) stream it is not ordered with torch's:
@@ -383,6 +417,17 @@ class IndexIVFFlat:
     def reset(self):
         self._check(self._lib.b200_IndexIVFFlat_reset(self._h))
 
+    def reserve_lists(self, sizes):
+        """room for sizes[l] rows in list l ([nlist] int64) so that later adds append in place"""
+        ks, ps = _ptr(sizes, np.int64, (self.nlist,), "sizes")
+        self._order_with_torch(ks)
+        self._check(self._lib.b200_IndexIVFFlat_reserve_lists(self._h, ps))
+
+    def list_sizes(self):
+        out = np.empty((self.nlist,), np.int64)
+        self._check(self._lib.b200_IndexIVFFlat_get_list_sizes(self._h, out.ctypes.data))
+        return out
+
     def get_list_size(self, l):
         return self._lib.b200_IndexIVFFlat_get_list_size(self._h, l)
 
@@ -414,6 +459,7 @@ class IndexIVFFlat:
         else:
             self._check(self._lib.b200_IndexIVFFlat_search_with_params(self._h, n, px, k,
                                                                        params._h, pd, pi))
+        self._settle(kx, kd, ki)
         return kd, ki
 
     def search_preassigned(self, x, k, assign, centroid_dis=None, D=None, I=None,
@@ -437,6 +483,7 @@ class IndexIVFFlat:
             self._check(self._lib.b200_IndexIVFFlat_search_preassigned_with_params(
                 self._h, n, px, k, pa, pc, pd, pi, int(bool(store_pairs)),
                 params._h if params is not None else None))
+        self._settle(kx, kd, ki)
         return kd, ki
 
     def search_stats(self, x, k, params=None):
@@ -507,11 +554,7 @@ class IndexIVFFlat:
         ki, pi = _ptr(Iq, np.int64, (n, nprobe), "Iq")
         self._order_with_torch(kx, kd, ki)
         self._check(self._lib.b200_IndexIVFFlat_quantize(self._h, n, px, nprobe, pd, pi))
-        if self._own_stream and _is_torch(kx) and kx.is_cuda:
-            # an all-device quantize returns before its kernels finish (b200ivf_c.h, set_stream);
-            # on the handle's own stream nothing orders torch's next read of the result with them
-            import torch
-            torch.cuda.synchronize(self.device)
+        self._settle(kx, kd, ki)
         return kd, ki
 
     # ---- stats / plumbing ----------------------------------------------------------------------
@@ -527,6 +570,12 @@ class IndexIVFFlat:
         ms = (C.c_double * 5)()
         self._lib.b200_IndexIVFFlat_last_timings(self._h, ms)
         return dict(zip(("coarse", "plan", "scan", "select", "total"), list(ms)))
+
+    def stage_time_sums(self):
+        """(calls, {stage: ms summed over the search calls since reset_stats})"""
+        ms = (C.c_double * 5)()
+        calls = self._lib.b200_IndexIVFFlat_stage_time_sums(self._h, ms)
+        return int(calls), dict(zip(("coarse", "plan", "scan", "select", "total"), list(ms)))
 
     def set_option(self, name, value):
         """kernel-selection knobs (see b200ivf_c.h); results do not depend on them"""

@@ -6,6 +6,7 @@
 #include "index.h"
 #include "kernels.h"
 #include "selector.h"
+#include "shards.h"
 
 #include <exception>
 #include <string>
@@ -37,6 +38,12 @@ inline IndexIVFFlatB200* H(B200IndexIVFFlat* p) {
 }
 inline const IndexIVFFlatB200* H(const B200IndexIVFFlat* p) {
     return reinterpret_cast<const IndexIVFFlatB200*>(p);
+}
+inline b200ivf::IndexShardsIVFFlatB200* SH(B200IndexShardsIVFFlat* p) {
+    return reinterpret_cast<b200ivf::IndexShardsIVFFlatB200*>(p);
+}
+inline const b200ivf::IndexShardsIVFFlatB200* SH(const B200IndexShardsIVFFlat* p) {
+    return reinterpret_cast<const b200ivf::IndexShardsIVFFlatB200*>(p);
 }
 inline const b200ivf::IDSelector* S(const B200IDSelector* p) {
     return reinterpret_cast<const b200ivf::IDSelector*>(p);
@@ -126,6 +133,16 @@ int b200_IndexIVFFlat_reset(B200IndexIVFFlat* index) {
     return guarded([&] { H(index)->reset(); });
 }
 
+int b200_IndexIVFFlat_reserve_lists(B200IndexIVFFlat* index, const int64_t* sizes) {
+    return guarded([&] { H(index)->reserve_lists(sizes); });
+}
+int b200_IndexIVFFlat_get_list_sizes(const B200IndexIVFFlat* index, int64_t* sizes_out) {
+    return guarded([&] {
+        if (!sizes_out)
+            throw b200ivf::B200Exception("null output buffer");
+        H(index)->get_list_sizes(sizes_out);
+    });
+}
 size_t b200_IndexIVFFlat_get_list_size(const B200IndexIVFFlat* index, size_t list_no) {
     size_t r = 0;
     guarded([&] { r = H(index)->get_list_size(list_no); });
@@ -161,7 +178,8 @@ int b200_IndexIVFFlat_quantize(const B200IndexIVFFlat* index, b200_idx_t n, cons
 }
 
 void b200_IndexIVFFlat_get_stats(const B200IndexIVFFlat* index, B200IndexIVFStats* stats) {
-    const b200ivf::IndexIVFStatsB200 s = H(index)->get_stats();
+    b200ivf::IndexIVFStatsB200 s;
+    guarded([&] { s = H(index)->get_stats(); }); // (a deferred failure stays in last_error)
     stats->nq = s.nq;
     stats->nlist = s.nlist;
     stats->ndis = s.ndis;
@@ -173,7 +191,19 @@ void b200_IndexIVFFlat_reset_stats(B200IndexIVFFlat* index) {
     guarded([&] { H(index)->reset_stats(); });
 }
 void b200_IndexIVFFlat_last_timings(const B200IndexIVFFlat* index, double* ms5) {
-    H(index)->last_timings(ms5);
+    for (int i = 0; i < 5; ++i)
+        ms5[i] = 0;
+    guarded([&] { H(index)->last_timings(ms5); });
+}
+unsigned long long b200_IndexIVFFlat_stage_time_sums(const B200IndexIVFFlat* index, double* ms5) {
+    unsigned long long r = 0;
+    for (int i = 0; i < 5; ++i)
+        ms5[i] = 0;
+    guarded([&] { r = H(index)->stage_time_sums(ms5); });
+    return r;
+}
+int b200_IndexIVFFlat_synchronize(const B200IndexIVFFlat* index) {
+    return guarded([&] { H(index)->synchronize(); });
 }
 int b200_IndexIVFFlat_set_stream(B200IndexIVFFlat* index, void* cuda_stream) {
     return guarded([&] { H(index)->set_stream((cudaStream_t)cuda_stream); });
@@ -358,6 +388,78 @@ int b200_IndexIVFFlat_range_search_preassigned(const B200IndexIVFFlat* index, b2
         H(index)->range_search_preassigned(n, x, radius, assign, centroid_dis, R(result),
                                            store_pairs != 0, P(params));
     });
+}
+
+int b200_nccl_get_unique_id(void* out128) {
+    return guarded([&] {
+        if (!out128)
+            throw b200ivf::B200Exception("null output buffer");
+        b200ivf::nccl_get_unique_id(out128);
+    });
+}
+int b200_IndexShardsIVFFlat_new(B200IndexShardsIVFFlat** p_index, size_t d, size_t nlist,
+                                B200MetricType metric, int device, int rank, int world,
+                                const void* nccl_unique_id128) {
+    return guarded([&] {
+        if (!p_index)
+            throw b200ivf::B200Exception("null output handle");
+        *p_index = reinterpret_cast<B200IndexShardsIVFFlat*>(new b200ivf::IndexShardsIVFFlatB200(
+                d, nlist, (int)metric, device, rank, world, nccl_unique_id128));
+    });
+}
+void b200_IndexShardsIVFFlat_free(B200IndexShardsIVFFlat* index) {
+    delete SH(index);
+}
+B200IndexIVFFlat* b200_IndexShardsIVFFlat_local(B200IndexShardsIVFFlat* index) {
+    return reinterpret_cast<B200IndexIVFFlat*>(SH(index)->local());
+}
+int b200_IndexShardsIVFFlat_rank(const B200IndexShardsIVFFlat* index) {
+    return SH(index)->rank();
+}
+int b200_IndexShardsIVFFlat_world(const B200IndexShardsIVFFlat* index) {
+    return SH(index)->world();
+}
+b200_idx_t b200_IndexShardsIVFFlat_ntotal(const B200IndexShardsIVFFlat* index) {
+    return SH(index)->ntotal();
+}
+int b200_IndexShardsIVFFlat_set_centroids(B200IndexShardsIVFFlat* index, const float* centroids,
+                                          int root) {
+    return guarded([&] { SH(index)->set_centroids(centroids, root); });
+}
+int b200_IndexShardsIVFFlat_train(B200IndexShardsIVFFlat* index, b200_idx_t n, const float* x,
+                                  int root) {
+    return guarded([&] { SH(index)->train(n, x, root); });
+}
+int b200_IndexShardsIVFFlat_add_with_ids(B200IndexShardsIVFFlat* index, b200_idx_t n,
+                                         const float* x, const b200_idx_t* xids) {
+    return guarded([&] { SH(index)->add_core(n, x, xids, nullptr); });
+}
+int b200_IndexShardsIVFFlat_add_core(B200IndexShardsIVFFlat* index, b200_idx_t n, const float* x,
+                                     const b200_idx_t* xids, const int64_t* precomputed_idx) {
+    return guarded([&] {
+        if (!precomputed_idx && n > 0)
+            throw b200ivf::B200Exception("Error: 'coarse_idx' failed");
+        SH(index)->add_core(n, x, xids, precomputed_idx);
+    });
+}
+int b200_IndexShardsIVFFlat_search(const B200IndexShardsIVFFlat* index, b200_idx_t n,
+                                   const float* x, b200_idx_t k, float* distances,
+                                   b200_idx_t* labels, int root) {
+    return guarded([&] { SH(index)->search(n, x, k, distances, labels, root); });
+}
+unsigned long long b200_IndexShardsIVFFlat_phase_time_sums(const B200IndexShardsIVFFlat* index,
+                                                           double* ms7) {
+    unsigned long long r = 0;
+    for (int i = 0; i < 7; ++i)
+        ms7[i] = 0;
+    guarded([&] { r = SH(index)->phase_time_sums(ms7); });
+    return r;
+}
+void b200_IndexShardsIVFFlat_reset_phase_times(B200IndexShardsIVFFlat* index) {
+    guarded([&] { SH(index)->reset_phase_times(); });
+}
+int b200_IndexShardsIVFFlat_synchronize(const B200IndexShardsIVFFlat* index) {
+    return guarded([&] { SH(index)->synchronize(); });
 }
 
 int b200_write_index_fname(const B200IndexIVFFlat* index, const char* fname) {

@@ -156,8 +156,10 @@ struct IndexIVFFlatB200::Impl {
     // inverted lists
     Buffer slab, ids, list_blk0, list_len, norms;
     std::vector<uint32_t> h_blk0;
+    std::vector<uint32_t> h_cap; // 32-row blocks reserved for each list (>= the blocks in use)
     std::vector<int32_t> h_len;
     size_t slab_blocks = 0;
+    bool norms_dirty = false;    // rows were added since `norms` was computed
     int64_t nstored = 0;
 
     // scratch (grow only)
@@ -183,9 +185,58 @@ struct IndexIVFFlatB200::Impl {
     // scan_tcr.cu below kTcrMaxAvgQueries, queries-major scan_tc.cu above and for the coarse
     // quantizer), 1 / 2 = always queries-major / rows-major (B200IVF_TC_MODE, A/B runs)
     int tc_mode = 0;
-    cudaEvent_t ev[6] = {};
+    // Stage events of the last kEvSets search calls. A call whose buffers are all device pointers
+    // returns as soon as its work is enqueued (include/b200ivf_c.h, set_stream): its event set stays
+    // `pending` and is read out -- into last_ms, the sums and the stats -- when somebody asks
+    // (last_timings, get_stats, ...) or when the ring comes round to it, by which time it is long
+    // complete. Calls that stage host buffers synchronize anyway and read their set at once.
+    static constexpr int kEvSets = 16;
+    struct EvSet {
+        cudaEvent_t ev[6] = {};
+        bool pending = false;
+        bool stages = false; // the per-stage events were recorded (not inside a graph replay)
+    };
+    EvSet evs[kEvSets];
+    int ev_cur = 0;
+    cudaEvent_t* ev = evs[0].ev; // the set of the call in progress / the last call
+    bool async_outstanding = false;
     double last_ms[5] = {0, 0, 0, 0, 0};
+    double sum_ms[5] = {0, 0, 0, 0, 0}; // since reset_stats
+    unsigned long long sum_calls = 0;
     IndexIVFStatsB200 stats;
+
+    // stage times of event set i -> last_ms (when it is the current call's), sums, stats
+    void collect_set(int i, bool to_last) {
+        EvSet& e = evs[i];
+        float ms = 0.f;
+        double v[5] = {0, 0, 0, 0, 0};
+        if (e.stages)
+            for (int s = 0; s < 4; ++s)
+                if (cudaEventElapsedTime(&ms, e.ev[s], e.ev[s + 1]) == cudaSuccess)
+                    v[s] = ms;
+        if (cudaEventElapsedTime(&ms, e.ev[0], e.ev[5]) == cudaSuccess)
+            v[4] = ms;
+        cudaGetLastError();
+        for (int s = 0; s < 5; ++s) {
+            if (to_last)
+                last_ms[s] += v[s];
+            sum_ms[s] += v[s];
+        }
+        stats.quantization_time += v[0];
+        stats.search_time += v[4];
+        e.pending = false;
+    }
+    void begin_call() {
+        ev_cur = (ev_cur + 1) % kEvSets;
+        if (evs[ev_cur].pending) { // 16 calls old: complete long ago
+            cudaEventSynchronize(evs[ev_cur].ev[5]);
+            collect_set(ev_cur, false);
+        }
+        ev = evs[ev_cur].ev;
+        for (double& v : last_ms)
+            v = 0;
+        sum_calls++;
+    }
 
     // small-batch searches are launch-bound (a dozen short kernels): the kernel pipeline of one
     // (batch size, nprobe, k, preassigned?) shape is captured into a CUDA graph the second time the
@@ -206,6 +257,8 @@ struct IndexIVFFlatB200::Impl {
     // ... and below which the rows-major tensor-core kernel is preferred to the queries-major one
     double tcr_max_avg_q = kTcrMaxAvgQueries;
     unsigned long long graph_replays = 0;
+    int coarse_s_override = 0;  // B200IVF_COARSE_S (read once, at construction)
+    bool trace_sync = false;    // B200IVF_TC_TRACE set: no graphs, no asynchronous returns
     void drop_graphs() {
         for (auto& kv : graphs)
             if (kv.second.exec)
@@ -244,6 +297,9 @@ struct IndexIVFFlatB200::Impl {
         use_graph = !(e3 && e3[0] == '1');
         if (const char* e4 = getenv("B200IVF_SIMT_MAXQ"))
             simt_max_avg_q = atof(e4);
+        if (const char* e5 = getenv("B200IVF_COARSE_S")) // tuning experiments
+            coarse_s_override = atoi(e5);
+        trace_sync = getenv("B200IVF_TC_TRACE") != nullptr; // the trace read-out synchronizes
         stage_x.pinned_host = stage_D.pinned_host = stage_I.pinned_host = true;
         stage_assign.pinned_host = host_stats.pinned_host = true;
         host_query_ndis.pinned_host = host_lims.pinned_host = true;
@@ -270,9 +326,11 @@ IndexIVFFlatB200::IndexIVFFlatB200(size_t d_, size_t nlist_, int metric, int dev
     impl_->list_hi = nlist;
     CUDA_CHECK(cudaStreamCreateWithFlags(&impl_->own_stream, cudaStreamNonBlocking));
     impl_->stream = impl_->own_stream;
-    for (auto& ev : impl_->ev)
-        CUDA_CHECK(cudaEventCreate(&ev));
+    for (auto& set : impl_->evs)
+        for (auto& ev : set.ev)
+            CUDA_CHECK(cudaEventCreate(&ev));
     impl_->h_blk0.assign(nlist, 0);
+    impl_->h_cap.assign(nlist, 0);
     impl_->h_len.assign(nlist, 0);
     impl_->list_blk0.reserve(sizeof(uint32_t) * nlist);
     impl_->list_len.reserve(sizeof(int32_t) * nlist);
@@ -303,18 +361,24 @@ IndexIVFFlatB200::~IndexIVFFlatB200() {
     for (Buffer* b : bufs)
         b->release();
     impl_->drop_graphs();
-    for (auto& ev : impl_->ev)
-        if (ev)
-            cudaEventDestroy(ev);
+    for (auto& set : impl_->evs)
+        for (auto& ev : set.ev)
+            if (ev)
+                cudaEventDestroy(ev);
     if (impl_->own_stream)
         cudaStreamDestroy(impl_->own_stream);
     delete impl_;
     cudaSetDevice(prev);
 }
 
+cudaStream_t IndexIVFFlatB200::stream_() const {
+    return impl_->stream;
+}
+
 void IndexIVFFlatB200::set_stream(cudaStream_t s) {
     std::lock_guard<std::mutex> lock(mu_);
     DeviceGuard g(device_);
+    finish_async_();
     CUDA_CHECK(cudaStreamSynchronize(impl_->stream));
     impl_->stream = s ? s : impl_->own_stream;
 }
@@ -330,6 +394,8 @@ void IndexIVFFlatB200::set_centroids(const float* c) {
 void IndexIVFFlatB200::set_centroids_(const float* c) {
     DeviceGuard g(device_);
     Impl& m = *impl_;
+    finish_async_();
+    m.drop_graphs();
     B200_THROW_IF_NOT_MSG(c != nullptr, "null centroids");
     const size_t nfl = nlist * (size_t)d;
     m.h_centroids.resize(nfl);
@@ -395,6 +461,7 @@ void IndexIVFFlatB200::reset() {
 void IndexIVFFlatB200::reset_() {
     DeviceGuard g(device_);
     Impl& m = *impl_;
+    finish_async_();
     CUDA_CHECK(cudaStreamSynchronize(m.stream));
     m.slab.release();
     m.ids.release();
@@ -402,7 +469,10 @@ void IndexIVFFlatB200::reset_() {
     m.slab_blocks = 0;
     m.nstored = 0;
     std::fill(m.h_blk0.begin(), m.h_blk0.end(), 0u);
+    std::fill(m.h_cap.begin(), m.h_cap.end(), 0u);
     std::fill(m.h_len.begin(), m.h_len.end(), 0);
+    m.norms_dirty = false;
+    m.drop_graphs();
     CUDA_CHECK(cudaMemset(m.list_blk0.p, 0, sizeof(uint32_t) * nlist));
     CUDA_CHECK(cudaMemset(m.list_len.p, 0, sizeof(int32_t) * nlist));
     ntotal = 0;
@@ -506,8 +576,9 @@ void IndexIVFFlatB200::run_coarse_(const float* xd, int64_t n, int kc, int32_t* 
         }
         S = best;
     }
-    if (const char* e = getenv("B200IVF_COARSE_S")) // tuning experiments
-        S = std::max<int64_t>(1, std::min<int64_t>(atoi(e), std::max<int64_t>(1, nblk / rows_step)));
+    if (m.coarse_s_override > 0) // tuning experiments
+        S = std::max<int64_t>(1, std::min<int64_t>(m.coarse_s_override,
+                                                   std::max<int64_t>(1, nblk / rows_step)));
     const int pmul = (tc && !tcr) ? 2 : 1;
     m.part.reserve((size_t)n * S * pmul * kp * sizeof(uint64_t));
     m.cplan.reserve(16);
@@ -646,7 +717,7 @@ static BatchPlan plan_batch(int nf4, int64_t kpart, int64_t nb, int64_t nprobe,
 void IndexIVFFlatB200::search(int64_t n, const float* x, int64_t k, float* D, int64_t* I,
                               const SearchParametersIVF* params,
                               QueryLatencyStats* per_query_stats) const {
-    search_impl_(n, x, k, nullptr, D, I, false, params, per_query_stats);
+    search_impl_(n, x, k, nullptr, D, I, false, params, per_query_stats, nullptr);
 }
 
 void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
@@ -655,13 +726,21 @@ void IndexIVFFlatB200::search_preassigned(int64_t n, const float* x, int64_t k,
                                           const SearchParametersIVF* params,
                                           QueryLatencyStats* per_query_stats) const {
     B200_THROW_IF_NOT_MSG(assign != nullptr, "null assign table");
-    search_impl_(n, x, k, assign, D, I, store_pairs, params, per_query_stats);
+    search_impl_(n, x, k, assign, D, I, store_pairs, params, per_query_stats, nullptr);
+}
+
+// search_preassigned with the probe table as the device holds it: [n][nprobe] int32 on the device,
+// -1 = no probe (the table the sharded index all-gathers). Everything must be device memory.
+void IndexIVFFlatB200::search_probed_i32(int64_t n, const float* x, int64_t k,
+                                         const int32_t* probes, float* D, int64_t* I) const {
+    B200_THROW_IF_NOT_MSG(probes != nullptr, "null probe table");
+    search_impl_(n, x, k, nullptr, D, I, false, nullptr, nullptr, probes);
 }
 
 void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const int64_t* assign,
                                     float* D, int64_t* I, bool store_pairs,
                                     const SearchParametersIVF* params,
-                                    QueryLatencyStats* per_query) const {
+                                    QueryLatencyStats* per_query, const int32_t* probes32) const {
     std::lock_guard<std::mutex> lock(mu_);
     DeviceGuard g(device_);
     Impl& m = *impl_;
@@ -676,18 +755,28 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
     B200_THROW_IF_NOT_MSG(!(sel && store_pairs), "selector and store_pairs cannot be combined");
     // selector / max_codes: the exact SIMT scan with a row mask and per-pair row limits
     const bool filtered = sel != nullptr || mc > 0;
-    for (double& v : m.last_ms)
-        v = 0;
+    // an invalid key met by an earlier asynchronous call surfaces here (its counter has landed in
+    // the pinned stats copy by now, or will have by the next call)
+    if (m.async_outstanding && m.host_stats.as<unsigned long long>()[3] != 0)
+        finish_async_();
+    m.begin_call();
     if (per_query) // IndexIVF::search_stats zeroes the table first (faiss/IndexIVF.cpp:737-739)
         std::fill(per_query, per_query + n, QueryLatencyStats());
     if (n == 0)
         return;
     B200_THROW_IF_NOT_MSG(x && D && I, "null buffer");
+    ensure_norms_(m.stream);
 
     const bool x_dev = is_device_pointer(x), D_dev = is_device_pointer(D),
                I_dev = is_device_pointer(I);
     const bool a_dev = assign && is_device_pointer(assign);
+    B200_THROW_IF_NOT_MSG(!probes32 || (x_dev && D_dev && I_dev),
+                          "search_probed_i32 takes device buffers only");
     const int64_t nlists_owned = (int64_t)(m.list_hi - m.list_lo);
+    // every buffer on the device: the call is ordered on the handle's stream and returns once its
+    // work is enqueued (stage times, statistics and the invalid-key check are read out later)
+    const bool async_ok = x_dev && D_dev && I_dev && (!assign || a_dev) && !per_query &&
+            !m.trace_sync;
 
     // tensor-core scan for the lists probed by many queries (d <= 128, moderate k)
     const int kp_q = scan_tc_kpart(m.nf4, (int)std::min<int64_t>(k, 1 << 20));  // d <= 128
@@ -727,13 +816,22 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
     // the kernel pipeline of one batch; every pointer is a device pointer. `timed`: stage events
     // are recorded (not while the pipeline is being captured into a graph)
     auto enqueue = [&](int64_t ni, const float* xd, float* Dd, int64_t* Id, const int64_t* ad,
-                       bool timed) {
+                       bool timed, const int32_t* p32 = nullptr) {
         const int64_t pairs = ni * np;
         bp = plan_batch(m.nf4, kp, ni, np, nlists_owned, m.nstored, simt_only, filtered);
         // stage 1: probe table
         m.coarse_ids.reserve((size_t)pairs * sizeof(int32_t));
         m.coarse_dis.reserve((size_t)pairs * sizeof(float));
-        if (ad) {
+        const int32_t* probe_tab = m.coarse_ids.as<int32_t>();
+        if (p32) {
+            // a device table in the plan's own format: read in place unless the max_codes walk is
+            // going to edit it (keys >= nlist are counted as invalid by the plan)
+            if (mc > 0)
+                CUDA_CHECK(cudaMemcpyAsync(m.coarse_ids.p, p32, (size_t)pairs * sizeof(int32_t),
+                                           cudaMemcpyDeviceToDevice, st));
+            else
+                probe_tab = p32;
+        } else if (ad) {
             CUDA_CHECK(launch_i64_to_i32(ad, m.coarse_ids.as<int32_t>(), pairs, 0, (int32_t)nlist,
                                          dstats + 3, st));
         } else {
@@ -779,7 +877,7 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
                                            (size_t)pairs * bp.S * pmul * kp * sizeof(uint64_t), st));
         }
         PlanArgs pa;
-        pa.coarse_ids = m.coarse_ids.as<int32_t>();
+        pa.coarse_ids = probe_tab;
         pa.n = (int)ni;
         pa.nprobe = (int)np;
         pa.nlists = (int)nlist;
@@ -933,7 +1031,7 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
     // ---- small batches: one CUDA-graph launch per search (see Impl::GraphEntry) ----
     const bool legacy_stream = st == nullptr || st == cudaStreamLegacy || st == cudaStreamPerThread;
     if (m.use_graph && n <= kGraphMaxBatch && !legacy_stream && !filtered && !store_pairs &&
-        !per_query && !getenv("B200IVF_TC_TRACE")) {
+        !per_query && !m.trace_sync && !probes32) {
         const int64_t pairs = n * np;
         m.dev_x.reserve((size_t)n * d * sizeof(float));
         m.dev_D.reserve((size_t)n * k * sizeof(float));
@@ -1020,19 +1118,18 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
         CUDA_CHECK(cudaEventRecord(m.ev[5], st));
         CUDA_CHECK(cudaMemcpyAsync(m.host_stats.p, dstats, 4 * sizeof(unsigned long long),
                                    cudaMemcpyDeviceToHost, st));
+        m.evs[m.ev_cur].stages = !ran;
+        if (async_ok) {
+            m.evs[m.ev_cur].pending = true;
+            m.async_outstanding = true;
+            return;
+        }
         CUDA_CHECK(cudaStreamSynchronize(st));
         if (!D_dev)
             std::memcpy(D, m.stage_D.p, Dbytes);
         if (!I_dev)
             std::memcpy(I, m.stage_I.p, Ibytes);
-        float ms;
-        if (!ran)
-            for (int s = 1; s < 4; ++s) { // stage times exist only for the eager run
-                CUDA_CHECK(cudaEventElapsedTime(&ms, m.ev[s], m.ev[s + 1]));
-                m.last_ms[s] += ms;
-            }
-        CUDA_CHECK(cudaEventElapsedTime(&ms, m.ev[0], m.ev[5]));
-        m.last_ms[4] += ms;
+        m.collect_set(m.ev_cur, true);
     } else
     for (int64_t i0 = 0; i0 < n; i0 += nb) {
         const int64_t ni = std::min(nb, n - i0);
@@ -1065,7 +1162,7 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
         }
         double ms_before[5];
         std::copy(m.last_ms, m.last_ms + 5, ms_before);
-        enqueue(ni, xd, Dd, Id, ad, true);
+        enqueue(ni, xd, Dd, Id, ad, true, probes32 ? probes32 + i0 * np : nullptr);
         CUDA_CHECK(cudaEventRecord(m.ev[4], st));
         if (per_query) {
             m.host_query_ndis.reserve((size_t)ni * sizeof(unsigned long long));
@@ -1082,27 +1179,49 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
         CUDA_CHECK(cudaEventRecord(m.ev[5], st));
         CUDA_CHECK(cudaMemcpyAsync(m.host_stats.p, dstats, 4 * sizeof(unsigned long long),
                                    cudaMemcpyDeviceToHost, st));
-        CUDA_CHECK(cudaStreamSynchronize(st));
-        float ms;
-        for (int s = 0; s < 4; ++s) {
-            CUDA_CHECK(cudaEventElapsedTime(&ms, m.ev[s], m.ev[s + 1]));
-            m.last_ms[s] += ms;
+        m.evs[m.ev_cur].stages = true;
+        if (async_ok && i0 + ni >= n) { // (earlier batches of a long call are read as they go)
+            m.evs[m.ev_cur].pending = true;
+            m.async_outstanding = true;
+            return;
         }
-        CUDA_CHECK(cudaEventElapsedTime(&ms, m.ev[0], m.ev[5]));
-        m.last_ms[4] += ms;
+        CUDA_CHECK(cudaStreamSynchronize(st));
+        m.collect_set(m.ev_cur, true);
         fill_per_query(i0, ni, ms_before);
     }
-    const unsigned long long* hs = m.host_stats.as<unsigned long long>();
+    read_counters_();
+}
+
+// counters of the searches completed so far (the stream must be idle): nq / nlist / ndis, and the
+// reference's "Invalid key" failure (faiss/IndexIVF.cpp:520-524) if a probe table held one
+void IndexIVFFlatB200::read_counters_() const {
+    Impl& m = *impl_;
+    unsigned long long* hs = m.host_stats.as<unsigned long long>();
     m.stats.nq = (size_t)hs[0];
     m.stats.nlist = (size_t)hs[1];
     m.stats.ndis = (size_t)hs[2];
-    m.stats.quantization_time += m.last_ms[0];
-    m.stats.search_time += m.last_ms[4];
     if (hs[3] != 0) {
-        CUDA_CHECK(cudaMemset(dstats + 3, 0, sizeof(unsigned long long)));
-        // faiss/IndexIVF.cpp:520-524
+        hs[3] = 0;
+        CUDA_CHECK(cudaMemset(m.dev_stats.as<unsigned long long>() + 3, 0,
+                              sizeof(unsigned long long)));
         throw B200Exception("Invalid key in search_preassigned (key >= nlist)");
     }
+}
+
+// Bring the handle up to date with the asynchronous calls still in flight: wait for the stream,
+// read their stage events, counters and deferred errors.
+void IndexIVFFlatB200::finish_async_() const {
+    Impl& m = *impl_;
+    if (!m.async_outstanding)
+        return;
+    CUDA_CHECK(cudaStreamSynchronize(m.stream));
+    for (int j = 1; j <= Impl::kEvSets; ++j) { // oldest first, the current call's set last
+        const int i = (m.ev_cur + j) % Impl::kEvSets;
+        if (m.evs[i].pending)
+            m.collect_set(i, i == m.ev_cur);
+    }
+    m.async_outstanding = false;
+    read_counters_();
 }
 
 void IndexIVFFlatB200::quantize(int64_t n, const float* x, int64_t kc, float* Dq,
@@ -1151,6 +1270,23 @@ void IndexIVFFlatB200::quantize(int64_t n, const float* x, int64_t kc, float* Dq
     }
 }
 
+void IndexIVFFlatB200::quantize_i32(int64_t n, const float* x, int64_t kc, int32_t* Iq,
+                                    float* Dq) const {
+    std::lock_guard<std::mutex> lock(mu_);
+    DeviceGuard g(device_);
+    Impl& m = *impl_;
+    B200_THROW_IF_NOT_MSG(is_trained, "index not trained");
+    B200_THROW_IF_NOT_MSG(kc > 0 && kc <= 2048, "nprobe must be in [1, 2048]");
+    if (n == 0)
+        return;
+    B200_THROW_IF_NOT_MSG(is_device_pointer(x) && is_device_pointer(Iq) && is_device_pointer(Dq),
+                          "quantize_i32 takes device buffers only");
+    for (int64_t i0 = 0; i0 < n; i0 += 32768) {
+        const int64_t ni = std::min<int64_t>(32768, n - i0);
+        run_coarse_(x + i0 * d, ni, (int)kc, Iq + i0 * kc, nullptr, Dq + i0 * kc, m.stream);
+    }
+}
+
 void IndexIVFFlatB200::set_option(const char* name, double value) {
     std::lock_guard<std::mutex> lock(mu_);
     DeviceGuard g(device_);
@@ -1175,21 +1311,57 @@ void IndexIVFFlatB200::set_option(const char* name, double value) {
 
 IndexIVFStatsB200 IndexIVFFlatB200::get_stats() const {
     std::lock_guard<std::mutex> lock(mu_);
+    DeviceGuard g(device_);
+    finish_async_();
     return impl_->stats;
 }
 
 void IndexIVFFlatB200::reset_stats() {
     std::lock_guard<std::mutex> lock(mu_);
     DeviceGuard g(device_);
+    try {
+        finish_async_();
+    } catch (const B200Exception&) { // (a deferred invalid-key report: the counters go anyway)
+    }
     CUDA_CHECK(cudaStreamSynchronize(impl_->stream));
     CUDA_CHECK(cudaMemset(impl_->dev_stats.p, 0, 4 * sizeof(unsigned long long)));
+    std::memset(impl_->host_stats.p, 0, 4 * sizeof(unsigned long long));
     impl_->stats = IndexIVFStatsB200();
+    for (double& v : impl_->sum_ms)
+        v = 0;
+    impl_->sum_calls = 0;
 }
 
 void IndexIVFFlatB200::last_timings(double* ms5) const {
     std::lock_guard<std::mutex> lock(mu_);
+    DeviceGuard g(device_);
+    finish_async_();
     for (int i = 0; i < 5; ++i)
         ms5[i] = impl_->last_ms[i];
+}
+
+unsigned long long IndexIVFFlatB200::stage_time_sums(double* ms5) const {
+    std::lock_guard<std::mutex> lock(mu_);
+    DeviceGuard g(device_);
+    finish_async_();
+    for (int i = 0; i < 5; ++i)
+        ms5[i] = impl_->sum_ms[i];
+    return impl_->sum_calls;
+}
+
+void IndexIVFFlatB200::synchronize() const {
+    std::lock_guard<std::mutex> lock(mu_);
+    DeviceGuard g(device_);
+    if (impl_->async_outstanding)
+        finish_async_();
+    else
+        CUDA_CHECK(cudaStreamSynchronize(impl_->stream));
+}
+
+void IndexIVFFlatB200::get_list_sizes(int64_t* out) const {
+    std::lock_guard<std::mutex> lock(mu_);
+    for (size_t l = 0; l < nlist; ++l)
+        out[l] = (int64_t)impl_->h_len[l];
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1214,6 +1386,7 @@ void IndexIVFFlatB200::add_core_(int64_t n, const float* x, const int64_t* xids,
     B200_THROW_IF_NOT_MSG(is_trained, "index not trained"); // IndexIVFFlat.cpp:52
     if (n == 0)
         return;
+    finish_async_();
     B200_THROW_IF_NOT_MSG(x != nullptr, "null vectors");
     cudaStream_t st = m.stream;
     const bool x_dev = is_device_pointer(x);
@@ -1264,39 +1437,31 @@ void IndexIVFFlatB200::add_core_(int64_t n, const float* x, const int64_t* xids,
             dst[(size_t)i] = -1;
             continue;
         }
+        B200_THROW_IF_NOT_MSG(new_len[(size_t)l] < INT32_MAX, "list too long");
         dst[(size_t)i] = new_len[(size_t)l]++; // offset in list for now
         nadd++;
     }
-    std::vector<uint32_t> new_blk0(nlist);
-    size_t blocks = 0;
-    for (size_t l = 0; l < nlist; ++l) {
-        new_blk0[l] = (uint32_t)blocks;
-        blocks += ((size_t)new_len[l] + kBlockRows - 1) / kBlockRows;
+    // Lists that outgrow the blocks reserved for them (reserve_lists; none by default) force a new
+    // slab: every list gets what it needs now, the others keep their reservation. When everything
+    // fits, the rows are appended in place and nothing moves.
+    bool fits = m.slab.p != nullptr || nadd == 0;
+    for (size_t l = 0; l < nlist && fits; ++l)
+        fits = ((size_t)new_len[l] + kBlockRows - 1) / kBlockRows <= (size_t)m.h_cap[l];
+    if (!fits) {
+        std::vector<uint32_t> new_cap(m.h_cap);
+        for (size_t l = 0; l < nlist; ++l)
+            new_cap[l] = std::max<uint32_t>(
+                    new_cap[l], (uint32_t)(((size_t)new_len[l] + kBlockRows - 1) / kBlockRows));
+        relayout_(new_cap);
     }
-    B200_THROW_IF_NOT_MSG(blocks * kBlockRows < ((size_t)1 << 32),
-                          "more than 2^32 rows on one device");
     for (int64_t i = 0; i < n; ++i) {
         const int64_t l = h_assign[(size_t)i];
         if (dst[(size_t)i] >= 0)
-            dst[(size_t)i] += (int64_t)new_blk0[(size_t)l] * kBlockRows;
+            dst[(size_t)i] += (int64_t)m.h_blk0[(size_t)l] * kBlockRows;
     }
 
-    // device: new slab, old blocks moved, new rows scattered
-    Buffer nslab, nids, nblk0;
-    const size_t slab_bytes = blocks * m.nf4 * kBlockRows * sizeof(float4);
-    nslab.reserve(std::max<size_t>(slab_bytes, 16));
-    nids.reserve(std::max<size_t>(blocks * kBlockRows * sizeof(int64_t), 16));
-    nblk0.reserve(nlist * sizeof(uint32_t));
-    CUDA_CHECK(cudaMemsetAsync(nslab.p, 0, slab_bytes, st));
-    CUDA_CHECK(cudaMemsetAsync(nids.p, 0xff, blocks * kBlockRows * sizeof(int64_t), st));
-    CUDA_CHECK(cudaMemcpyAsync(nblk0.p, new_blk0.data(), nlist * sizeof(uint32_t),
-                               cudaMemcpyHostToDevice, st));
-    if (m.nstored > 0)
-        CUDA_CHECK(launch_move_blocks(m.slab.as<float4>(), m.ids.as<int64_t>(),
-                                      m.list_blk0.as<uint32_t>(), m.list_len.as<int32_t>(),
-                                      nblk0.as<uint32_t>(), (int)nlist, m.nf4, nslab.as<float4>(),
-                                      nids.as<int64_t>(), st));
-    for (int64_t i0 = 0; i0 < n; i0 += chunk) {
+    // device: new rows scattered into their lists
+    for (int64_t i0 = 0; i0 < n && nadd > 0; i0 += chunk) {
         const int64_t ni = std::min(chunk, n - i0);
         const float* xd = x + i0 * d;
         if (!x_dev) {
@@ -1319,31 +1484,95 @@ void IndexIVFFlatB200::add_core_(int64_t n, const float* x, const int64_t* xids,
         CUDA_CHECK(cudaMemcpyAsync(m.dev_assign64.p, dst.data() + i0, (size_t)ni * sizeof(int64_t),
                                    cudaMemcpyHostToDevice, st));
         CUDA_CHECK(launch_scatter_rows(xd, idd, m.dev_assign64.as<int64_t>(), ni, d, m.nf4,
-                                       nslab.as<float>(), nids.as<int64_t>(), ntotal + i0, st));
+                                       m.slab.as<float>(), m.ids.as<int64_t>(), ntotal + i0, st));
         CUDA_CHECK(cudaStreamSynchronize(st)); // staging buffers are reused by the next chunk
     }
     CUDA_CHECK(cudaMemcpyAsync(m.list_len.p, new_len.data(), nlist * sizeof(int32_t),
                                cudaMemcpyHostToDevice, st));
+    CUDA_CHECK(cudaStreamSynchronize(st));
+    m.h_len.swap(new_len);
+    m.nstored += nadd;
+    m.norms_dirty = m.norms_dirty || nadd > 0; // |y|^2 of the new rows: before the next search
+    m.drop_graphs();                           // captured launch shapes embody the old lists
+    ntotal += n; // IndexIVFFlat.cpp:90: every input vector counts, skipped or not
+}
+
+// New slab with cap[l] 32-row blocks for list l (>= the blocks the list uses now); the rows already
+// stored move block-wise to their new places.
+void IndexIVFFlatB200::relayout_(const std::vector<uint32_t>& cap) {
+    Impl& m = *impl_;
+    cudaStream_t st = m.stream;
+    std::vector<uint32_t> new_blk0(nlist);
+    size_t blocks = 0;
+    for (size_t l = 0; l < nlist; ++l) {
+        new_blk0[l] = (uint32_t)blocks;
+        blocks += cap[l];
+        B200_THROW_IF_NOT_MSG(blocks * kBlockRows < ((size_t)1 << 32),
+                              "more than 2^32 rows on one device");
+    }
+    Buffer nslab, nids, nblk0, nnorms;
+    const size_t slab_bytes = blocks * m.nf4 * kBlockRows * sizeof(float4);
+    nslab.reserve(std::max<size_t>(slab_bytes, 16));
+    nids.reserve(std::max<size_t>(blocks * kBlockRows * sizeof(int64_t), 16));
+    nblk0.reserve(nlist * sizeof(uint32_t));
+    CUDA_CHECK(cudaMemsetAsync(nslab.p, 0, slab_bytes, st));
+    CUDA_CHECK(cudaMemsetAsync(nids.p, 0xff, blocks * kBlockRows * sizeof(int64_t), st));
+    CUDA_CHECK(cudaMemcpyAsync(nblk0.p, new_blk0.data(), nlist * sizeof(uint32_t),
+                               cudaMemcpyHostToDevice, st));
+    if (m.nstored > 0)
+        CUDA_CHECK(launch_move_blocks(m.slab.as<float4>(), m.ids.as<int64_t>(),
+                                      m.list_blk0.as<uint32_t>(), m.list_len.as<int32_t>(),
+                                      nblk0.as<uint32_t>(), (int)nlist, m.nf4, nslab.as<float4>(),
+                                      nids.as<int64_t>(), st));
     CUDA_CHECK(cudaMemcpyAsync(m.list_blk0.p, new_blk0.data(), nlist * sizeof(uint32_t),
                                cudaMemcpyHostToDevice, st));
     CUDA_CHECK(cudaStreamSynchronize(st));
-    m.slab.release();
-    m.ids.release();
-    m.slab = nslab;
-    m.ids = nids;
+    m.norms.release(); // (before the new one is allocated: they are slab-sized / d)
+    nnorms.reserve(std::max<size_t>(blocks * kBlockRows * sizeof(float), 16));
+    m.slab = std::move(nslab);
+    m.ids = std::move(nids);
+    m.norms = std::move(nnorms);
     CUDA_CHECK(make_slab_tensor_map(m.lists_map, m.slab.p, m.nf4, blocks));
     CUDA_CHECK(make_slab_tensor_map_tc(m.lists_map_tc, m.slab.p, m.nf4, blocks));
-    m.norms.release();
-    m.norms.reserve(std::max<size_t>(blocks * kBlockRows * sizeof(float), 16));
-    CUDA_CHECK(launch_row_norms(m.slab.as<float4>(), (int64_t)(blocks * kBlockRows), m.nf4,
-                                m.norms.as<float>(), st));
-    CUDA_CHECK(cudaStreamSynchronize(st));
-    nblk0.release();
-    m.h_len.swap(new_len);
     m.h_blk0.swap(new_blk0);
+    m.h_cap = cap;
     m.slab_blocks = blocks;
-    m.nstored += nadd;
-    ntotal += n; // IndexIVFFlat.cpp:90: every input vector counts, skipped or not
+    m.norms_dirty = true;
+    m.drop_graphs();
+}
+
+// Room for sizes[l] rows in every list of this handle's range before the vectors arrive (the
+// reference's InvertedLists::resize / GpuIndexIVF::reserveMemory, faiss/gpu/GpuIndexIVF.h:83-86,
+// in list-wise form): later adds that stay within it append in place -- no second slab, no moves.
+void IndexIVFFlatB200::reserve_lists(const int64_t* sizes) {
+    std::lock_guard<std::mutex> lock(mu_);
+    DeviceGuard g(device_);
+    Impl& m = *impl_;
+    B200_THROW_IF_NOT_MSG(sizes != nullptr, "null sizes");
+    std::vector<int64_t> hs(nlist);
+    if (is_device_pointer(sizes))
+        CUDA_CHECK(cudaMemcpy(hs.data(), sizes, nlist * sizeof(int64_t), cudaMemcpyDeviceToHost));
+    else
+        std::memcpy(hs.data(), sizes, nlist * sizeof(int64_t));
+    std::vector<uint32_t> cap(m.h_cap);
+    for (size_t l = m.list_lo; l < m.list_hi; ++l) {
+        B200_THROW_IF_NOT_MSG(hs[l] >= 0 && hs[l] < INT32_MAX, "invalid list size");
+        cap[l] = std::max<uint32_t>(cap[l], (uint32_t)((hs[l] + kBlockRows - 1) / kBlockRows));
+    }
+    finish_async_();
+    CUDA_CHECK(cudaStreamSynchronize(m.stream));
+    relayout_(cap);
+}
+
+// |y|^2 of every slab row (the L2 epilogue of the tensor-core scans) after the lists changed
+void IndexIVFFlatB200::ensure_norms_(cudaStream_t st) const {
+    Impl& m = *impl_;
+    if (!m.norms_dirty)
+        return;
+    if (m.slab_blocks > 0)
+        CUDA_CHECK(launch_row_norms(m.slab.as<float4>(), (int64_t)(m.slab_blocks * kBlockRows),
+                                    m.nf4, m.norms.as<float>(), st));
+    m.norms_dirty = false;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1383,8 +1612,8 @@ void IndexIVFFlatB200::range_impl_(int64_t n, const float* x, float radius, cons
     result->lims.assign((size_t)n + 1, 0);
     result->labels.clear();
     result->distances.clear();
-    for (double& v : m.last_ms)
-        v = 0;
+    finish_async_();
+    m.begin_call();
     if (n == 0)
         return;
     B200_THROW_IF_NOT_MSG(x != nullptr, "null buffer");
@@ -1511,13 +1740,22 @@ void IndexIVFFlatB200::range_impl_(int64_t n, const float* x, float radius, cons
         for (int64_t i = 0; i < ni; ++i)
             result->lims[(size_t)(i0 + i)] = base + (size_t)hl[i];
         base += total;
-        float ms;
-        CUDA_CHECK(cudaEventElapsedTime(&ms, m.ev[0], m.ev[1]));
-        m.last_ms[0] += ms;
-        CUDA_CHECK(cudaEventElapsedTime(&ms, m.ev[1], m.ev[5]));
-        m.last_ms[2] += ms;
-        CUDA_CHECK(cudaEventElapsedTime(&ms, m.ev[0], m.ev[5]));
-        m.last_ms[4] += ms;
+        {
+            float ms;
+            double v[5] = {0, 0, 0, 0, 0};
+            CUDA_CHECK(cudaEventElapsedTime(&ms, m.ev[0], m.ev[1]));
+            v[0] = ms;
+            CUDA_CHECK(cudaEventElapsedTime(&ms, m.ev[1], m.ev[5]));
+            v[2] = ms;
+            CUDA_CHECK(cudaEventElapsedTime(&ms, m.ev[0], m.ev[5]));
+            v[4] = ms;
+            for (int s = 0; s < 5; ++s) {
+                m.last_ms[s] += v[s];
+                m.sum_ms[s] += v[s];
+            }
+            m.stats.quantization_time += v[0];
+            m.stats.search_time += v[4];
+        }
         const unsigned long long* hs = m.host_stats.as<unsigned long long>();
         if (hs[3] != 0) {
             CUDA_CHECK(cudaMemset(dstats + 3, 0, sizeof(unsigned long long)));
@@ -1529,8 +1767,6 @@ void IndexIVFFlatB200::range_impl_(int64_t n, const float* x, float radius, cons
     m.stats.nq = (size_t)hs[0];
     m.stats.nlist = (size_t)hs[1];
     m.stats.ndis = (size_t)hs[2];
-    m.stats.quantization_time += m.last_ms[0];
-    m.stats.search_time += m.last_ms[4];
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1626,6 +1862,15 @@ void IndexIVFFlatB200::train(int64_t n, const float* x) {
     cudaStream_t st = m.stream;
     const size_t k = nlist, dd = (size_t)d;
     const bool x_dev = is_device_pointer(x);
+    finish_async_();
+
+    if ((size_t)n == k) {
+        // "just copy training set to clusters" (faiss/Clustering.cpp:346-368): the training
+        // vectors, in input order, ARE the centroids -- no permutation, no iterations, and no
+        // spherical renormalisation either (the reference returns before post_process_centroids)
+        set_centroids_(x);
+        return;
+    }
 
     // subsample_training_set (faiss/Clustering.cpp:86-133): the first k * max_points_per_centroid
     // entries of a seeded permutation

@@ -44,11 +44,33 @@ struct RangeSearchResult {
     explicit RangeSearchResult(size_t nq_) : nq(nq_), lims(nq_ + 1, 0) {}
 };
 
-// grow-only device / pinned-host buffer
+// grow-only device / pinned-host buffer; owns its allocation (move-only), so a throw between an
+// allocation and its hand-over (an out-of-memory CUDA_CHECK in add_core_, say) frees it
 struct Buffer {
     void* p = nullptr;
     size_t bytes = 0;
     bool pinned_host = false;
+    Buffer() = default;
+    ~Buffer() {
+        release();
+    }
+    Buffer(const Buffer&) = delete;
+    Buffer& operator=(const Buffer&) = delete;
+    Buffer(Buffer&& o) noexcept : p(o.p), bytes(o.bytes), pinned_host(o.pinned_host) {
+        o.p = nullptr;
+        o.bytes = 0;
+    }
+    Buffer& operator=(Buffer&& o) noexcept {
+        if (this != &o) {
+            release();
+            p = o.p;
+            bytes = o.bytes;
+            pinned_host = o.pinned_host;
+            o.p = nullptr;
+            o.bytes = 0;
+        }
+        return *this;
+    }
     void reserve(size_t n);
     void release();
     template <class T>
@@ -83,6 +105,11 @@ class IndexIVFFlatB200 {
     void add_with_ids(int64_t n, const float* x, const int64_t* xids);
     void add_core(int64_t n, const float* x, const int64_t* xids, const int64_t* assign);
     void reset();
+    // room for sizes[l] rows in list l ([nlist] entries, host or device; entries outside this
+    // handle's list range are ignored): adds that stay within it append in place
+    void reserve_lists(const int64_t* sizes);
+    // sizes of all nlist lists at once (0 outside this handle's range), host array
+    void get_list_sizes(int64_t* out) const;
     size_t get_list_size(size_t l) const;
     void get_list_ids(size_t l, int64_t* out) const;
     void get_list_codes(size_t l, float* out) const;
@@ -110,10 +137,19 @@ class IndexIVFFlatB200 {
                                   bool store_pairs = false,
                                   const SearchParametersIVF* params = nullptr) const;
     void quantize(int64_t n, const float* x, int64_t nprobe, float* Dq, int64_t* Iq) const;
+    // search_preassigned with a DEVICE probe table of int32 (-1 = no probe); device buffers only
+    void search_probed_i32(int64_t n, const float* x, int64_t k, const int32_t* probes, float* D,
+                           int64_t* I) const;
+    // quantizer->search into a device int32 table (device buffers only, asynchronous)
+    void quantize_i32(int64_t n, const float* x, int64_t nprobe, int32_t* Iq, float* Dq) const;
 
     IndexIVFStatsB200 get_stats() const;
     void reset_stats();
     void last_timings(double* ms5) const;
+    // the same five stage times summed over the search calls since reset_stats; returns how many
+    unsigned long long stage_time_sums(double* ms5) const;
+    // wait for the asynchronous calls in flight; a deferred failure (invalid key) is thrown here
+    void synchronize() const;
     void set_stream(cudaStream_t s);
     // kernel-selection knobs (the ParameterSpace of this path): "simt_max_avg_q" / "tcr_max_avg_q"
     // (queries per probed list below which the exact warp kernel / the rows-major tensor-core
@@ -126,13 +162,19 @@ class IndexIVFFlatB200 {
     }
 
   private:
+    friend class IndexShardsIVFFlatB200; // shards.cu: shares the handle's stream and scratch
     struct Impl;
     void set_centroids_(const float* c);
     void reset_();
     void add_core_(int64_t n, const float* x, const int64_t* xids, const int64_t* assign);
+    void relayout_(const std::vector<uint32_t>& cap);
+    void ensure_norms_(cudaStream_t st) const;
+    void finish_async_() const;
+    void read_counters_() const;
+    cudaStream_t stream_() const; // the stream every call of this handle is ordered on
     void search_impl_(int64_t n, const float* x, int64_t k, const int64_t* assign, float* D,
                       int64_t* I, bool store_pairs, const SearchParametersIVF* params,
-                      QueryLatencyStats* per_query) const;
+                      QueryLatencyStats* per_query, const int32_t* probes32) const;
     void range_impl_(int64_t n, const float* x, float radius, const int64_t* assign,
                      RangeSearchResult* result, bool store_pairs,
                      const SearchParametersIVF* params) const;

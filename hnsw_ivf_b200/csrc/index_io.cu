@@ -13,6 +13,8 @@
 // add_core with the list numbers given, which keeps the stored order inside every list).
 #include "index.h"
 
+#include <algorithm>
+
 #include <cerrno>
 #include <cstdio>
 #include <cstring>
@@ -163,8 +165,15 @@ IndexIVFFlatB200* read_index(const char* fname, int /*io_flags*/, int device) {
         f.read_vector(arr);
         if (dm_type == 2) { // DirectMap::Hashtable
             const size_t npairs = f.read1<size_t>();
-            std::vector<int64_t> pairs(2 * npairs);
-            f.read(pairs.data(), pairs.size());
+            if (!(npairs < ((uint64_t)1 << 40))) // the bound read_vector puts on every length field
+                throw B200Exception("Error: 'npairs < (uint64_t{1} << 40)' failed");
+            // dropped in bounded pieces: a corrupt count fails in read(), not in an allocation
+            std::vector<int64_t> piece((size_t)1 << 16);
+            for (size_t left = 2 * npairs; left > 0;) {
+                const size_t take = std::min(left, piece.size());
+                f.read(piece.data(), take);
+                left -= take;
+            }
         }
     }
     // inverted lists
@@ -214,6 +223,13 @@ IndexIVFFlatB200* read_index(const char* fname, int /*io_flags*/, int device) {
     // list numbers; the stored order inside a list is kept
     const size_t kGroup = (size_t)1 << 20;
     const size_t d = (size_t)ih.d;
+    {
+        // the sizes are known up front: one slab, filled in place
+        std::vector<int64_t> rs(nlist);
+        for (size_t j = 0; j < nlist; ++j)
+            rs[j] = (int64_t)sizes[j];
+        idx->reserve_lists(rs.data());
+    }
     std::vector<float> codes;
     std::vector<int64_t> ids, assign;
     size_t l = 0;

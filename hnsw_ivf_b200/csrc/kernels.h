@@ -251,6 +251,9 @@ cudaError_t launch_list_means(const float* slab, const uint32_t* list_blk0, cons
 // out[i] = x[idx[i]] for row-major [.][d] tables
 cudaError_t launch_gather_by_index(const float* x, const int64_t* idx, int64_t n, int d, float* out,
                                    cudaStream_t st);
+// out[i] = in[idx[i]], or base + idx[i] when in == nullptr (ids of vectors added without ids)
+cudaError_t launch_gather_i64(const int64_t* in, const int64_t* idx, int64_t n, int64_t base,
+                              int64_t* out, cudaStream_t st);
 cudaError_t launch_i64_to_i32(const int64_t* in, int32_t* out, int64_t n, int32_t lo, int32_t hi,
                               unsigned long long* bad, cudaStream_t st);
 

@@ -214,6 +214,24 @@ cudaError_t launch_list_means(const float* slab, const uint32_t* list_blk0, cons
     return cudaGetLastError();
 }
 
+__global__ void gather_i64_kernel(const int64_t* __restrict__ in, const int64_t* __restrict__ idx,
+                                  int64_t n, int64_t base, int64_t* __restrict__ out) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n;
+         i += (int64_t)gridDim.x * blockDim.x)
+        out[i] = in ? in[idx[i]] : base + idx[i];
+}
+
+cudaError_t launch_gather_i64(const int64_t* in, const int64_t* idx, int64_t n, int64_t base,
+                              int64_t* out, cudaStream_t st) {
+    if (n == 0)
+        return cudaSuccess;
+    const int threads = 256;
+    const int grid = (int)std::min<int64_t>((n + threads - 1) / threads, 148 * 16);
+    gather_i64_kernel<<<grid, threads, 0, st>>>(in, idx, n, base, out);
+    count_launches(1);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_gather_by_index(const float* x, const int64_t* idx, int64_t n, int d, float* out,
                                    cudaStream_t st) {
     if (n == 0)

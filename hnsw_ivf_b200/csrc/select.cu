@@ -38,15 +38,27 @@ __global__ void select_kernel(const SelectArgs a, int M, int prefilter) {
     __shared__ int s_cnt;
     bool fast_done = false;
     if (prefilter) {
+        // Pivot rule (the one select_warp_kernel uses): every partial list is sorted, so at least
+        // r * m keys are <= the r-th smallest of the lists' m-th entries. With m = ceil(kk / L)
+        // and r = ceil(kk / m) that is >= kk keys, whatever kk is against the number of lists
+        // (kk > L happens for k = 100 at nprobe 32/64 with one row split: the heads alone bound
+        // only L keys). No usable pivot (r > L after m was cut to kpart, or fewer than r lists
+        // reach m entries): every real key passes and the chunked sort below takes over if they
+        // do not fit.
         const int L = a.nseg * a.nsplit;
         const int Lp = pow2_ceil(L < 32 ? 32 : L);
+        int m = (kk + L - 1) / L;
+        if (m > a.kpart)
+            m = a.kpart;
+        const int r = (kk + m - 1) / m;
         for (int i = t; i < Lp; i += blockDim.x) {
             uint64_t key = kSentinelKey;
             if (i < L) {
                 const int seg = i / a.nsplit;
                 const int slot = a.slot_of ? a.slot_of[(int64_t)q * a.nseg + seg] : q;
                 if (slot >= 0)
-                    key = a.part[(int64_t)slot * per_seg + (int64_t)(i % a.nsplit) * a.kpart];
+                    key = a.part[(int64_t)slot * per_seg + (int64_t)(i % a.nsplit) * a.kpart +
+                                 (m - 1)];
             }
             keys[i] = key;
         }
@@ -54,14 +66,16 @@ __global__ void select_kernel(const SelectArgs a, int M, int prefilter) {
             s_cnt = 0;
         __syncthreads();
         block_sort_keys(keys, Lp);
-        const uint64_t T = keys[(kk < Lp ? kk : Lp) - 1];
+        uint64_t T = r <= L ? keys[r - 1] : kSentinelKey;
+        if (T == kSentinelKey)
+            T = kSentinelKey - 1; // no bound: all real keys
         __syncthreads();
         for (int64_t c = t; c < total; c += blockDim.x) {
             const int seg = (int)(c / per_seg);
             const int slot = a.slot_of ? a.slot_of[(int64_t)q * a.nseg + seg] : q;
             if (slot >= 0) {
                 const uint64_t key = a.part[(int64_t)slot * per_seg + (c % per_seg)];
-                if (key <= T && key != kSentinelKey) {
+                if (key <= T) {
                     const int pos = atomicAdd(&s_cnt, 1);
                     if (pos < kSelCap)
                         keys[pos] = key;
@@ -70,7 +84,8 @@ __global__ void select_kernel(const SelectArgs a, int M, int prefilter) {
         }
         __syncthreads();
         const int cnt = s_cnt;
-        if (cnt <= kSelCap) {
+        // (cnt < kk under a real bound cannot happen; if it ever did, the full sort is the answer)
+        if (cnt <= kSelCap && (cnt >= kk || T == kSentinelKey - 1)) {
             int P = pow2_ceil(cnt > kk ? cnt : kk);
             if (P < 32)
                 P = 32;
@@ -80,6 +95,7 @@ __global__ void select_kernel(const SelectArgs a, int M, int prefilter) {
             block_sort_keys(keys, P);
             fast_done = true;
         }
+        __syncthreads();
     }
     int kept = 0; // keys[0..kept) hold the running best, sorted
     int64_t done = fast_done ? total : 0;
@@ -450,9 +466,10 @@ __global__ void __launch_bounds__(256, 4) select_warp_kernel(const SelectArgs a)
     }
 }
 
-// One warp per query: merge nshard sorted (n,k) tables. Same output as merge_knn_results
-// (faiss/utils/Heap.cpp:158-232) except that exact ties across shards are ordered by id rather
-// than by shard number.
+// One warp per query: merge nshard sorted (n,k) tables by walking the shard heads. Same output as
+// merge_knn_results (faiss/utils/Heap.cpp:158-232): equal distances come out lower shard first
+// (the reference's heap over the shard heads compares (distance, shard), :186-225), exactly as
+// merge_shards_rank_kernel below orders them.
 __global__ void merge_shards_kernel(int metric, int nshard, int n, int k, const float* all_dis,
                                     const int64_t* all_ids, float* out_dis, int64_t* out_ids) {
     const int q = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -480,10 +497,8 @@ __global__ void merge_shards_kernel(int metric, int nshard, int n, int k, const 
                     bool better;
                     if (best_s < 0)
                         better = true;
-                    else if (dv != best)
+                    else // equal distances: the lower shard (seen first) stays
                         better = l2 ? (dv < best) : (dv > best);
-                    else
-                        better = l2 ? (id < best_id) : (id > best_id);
                     if (better) {
                         best = dv;
                         best_id = id;
@@ -504,8 +519,6 @@ __global__ void merge_shards_kernel(int metric, int nshard, int n, int k, const 
                 take = true;
             else if (od != best)
                 take = l2 ? (od < best) : (od > best);
-            else if (oid != best_id)
-                take = l2 ? (oid < best_id) : (oid > best_id);
             else
                 take = os < best_s;
             if (take) {

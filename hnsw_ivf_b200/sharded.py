@@ -1,21 +1,27 @@
-"""List-sharded IVF-Flat over several B200s, one process per GPU (torch.distributed / NCCL).
+"""List-sharded IVF-Flat over several B200s, one process per GPU.
 
-Behavioural model: IndexShardsIVF::search (faiss/IndexShardsIVF.cpp:158-243) -- a common coarse
-quantizer, one search_preassigned per shard, merge_knn_results -- with the reference's host threads
-and CPU merge replaced by: replicated device quantizer, contiguous list ranges per rank
+``IndexShardsIVFFlat`` binds the C-ABI's ``b200_IndexShardsIVFFlat_*`` (csrc/shards.cu): the C++
+object that owns this rank's shard and its NCCL communicator and runs a sharded search as ONE
+stream of device work -- coarse quantizer split by query, int32 probe-table all-gather, local
+plan + scan + k-select, one grouped all-gather of the per-shard tables, device merge. Behavioural
+model: IndexShardsIVF (faiss/IndexShardsIVF.cpp:102-243) with shards that hold list RANGES
 (shard_type 4 / SUBSET_TYPE_INVLIST: faiss/gpu/GpuCloner.cpp:303-314,
-faiss/invlists/InvertedLists.cpp:168-176), an NCCL all-gather of the per-rank sorted (n,k) tables
-over NVLink, and the device merge kernel (csrc/select.cu). Each (query, probe) pair lands on exactly
-one rank, so total scan bytes do not grow with the number of GPUs.
+faiss/invlists/InvertedLists.cpp:168-176). Each (query, probe) pair lands on exactly one rank, so
+total scan bytes do not grow with the number of GPUs. torch.distributed is used for ONE thing
+here: handing rank 0's NCCL unique id to the other ranks.
 
-Coarse quantization is the common step of IndexShardsIVF::search (faiss/IndexShardsIVF.cpp:175-183:
-ONE quantizer->search, then per-shard search_preassigned). Here every rank holds the full centroid
-table, so the common step is split by QUERY: rank r quantizes queries [r*n/R, (r+1)*n/R), the
-[n][nprobe] probe table is all-gathered (n*nprobe*8 bytes in total) and every rank runs
-search_preassigned on all the queries against its own lists. Collectives per search: that
-all-gather and the (n*k*12 bytes per rank) result all-gather.
+``ShardedSearchModel`` is the same algorithm written over torch.distributed collectives with an
+injectable local index: the host-logic model the CPU test suite runs over gloo with the oracle as
+the local index (tests/test_cabi_host.py). It is not on the product path.
 """
-from .binding import IndexIVFFlat, merge_knn_results
+import ctypes as C
+
+import numpy as np
+
+from .binding import (IndexIVFFlat, _empty_like_input, _is_torch, _ptr, _vp, load_library,
+                      merge_knn_results, B200Error)
+
+PHASES = ("broadcast", "coarse", "probe_gather", "local_search", "result_gather", "merge", "total")
 
 
 def list_range_of_rank(nlist, rank, world):
@@ -23,46 +29,171 @@ def list_range_of_rank(nlist, rank, world):
     return (rank * nlist) // world, ((rank + 1) * nlist) // world
 
 
-def gather_results(D_loc, I_loc, group=None, out=None):
-    """All-gather the per-rank (n,k) tables into [world][n][k] tensors (NCCL on GPU, gloo on CPU).
-    out: optional (all_D, all_I) scratch of shape [world*n][k] to gather into."""
+def nccl_unique_id():
+    """128 bytes of ncclGetUniqueId (b200_nccl_get_unique_id)"""
+    lib = load_library()
+    buf = C.create_string_buffer(128)
+    rc = lib.b200_nccl_get_unique_id(buf)
+    if rc != 0:
+        raise B200Error(rc, lib.b200_get_last_error().decode())
+    return buf.raw
+
+
+class IndexShardsIVFFlat:
+    """This rank's end of a list-sharded IndexIVFFlat (every method is collective: all ranks call
+    it with the same arguments, except where noted).
+
+    ``unique_id``: the 128 NCCL id bytes shared by all ranks; by default rank 0 of the
+    torch.distributed ``group`` makes one and broadcasts it.
+    """
+
+    def __init__(self, d, nlist, metric, device=0, group=None, rank=None, world=None,
+                 unique_id=None):
+        self._lib = load_library()
+        self._h = None
+        if rank is None or world is None:
+            import torch.distributed as dist
+            rank, world = dist.get_rank(group), dist.get_world_size(group)
+        if unique_id is None and world > 1:
+            import torch.distributed as dist
+            box = [nccl_unique_id() if rank == 0 else None]
+            dist.broadcast_object_list(box, src=dist.get_global_rank(group, 0) if group else 0,
+                                       group=group)
+            unique_id = box[0]
+        h = _vp()
+        idbuf = C.create_string_buffer(unique_id, 128) if unique_id is not None else None
+        self._check(self._lib.b200_IndexShardsIVFFlat_new(C.byref(h), d, nlist, metric, device,
+                                                          rank, world, idbuf))
+        self._h = h
+        self.d, self.nlist, self.metric, self.device = d, nlist, metric, device
+        self.rank, self.world = rank, world
+        self.list_lo, self.list_hi = list_range_of_rank(nlist, rank, world)
+        self.local = IndexIVFFlat(d, nlist, metric, device,
+                                  _handle=_vp(self._lib.b200_IndexShardsIVFFlat_local(h)),
+                                  _borrowed=True)
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            self._lib.b200_IndexShardsIVFFlat_free(self._h)
+            self._h = None
+
+    def _check(self, rc):
+        if rc != 0:
+            raise B200Error(rc, self._lib.b200_get_last_error().decode())
+
+    @property
+    def nprobe(self):
+        return self.local.nprobe
+
+    @nprobe.setter
+    def nprobe(self, v):
+        self.local.nprobe = v
+
+    @property
+    def ntotal(self):
+        return self._lib.b200_IndexShardsIVFFlat_ntotal(self._h)
+
+    def set_stream(self, cuda_stream_ptr):
+        self.local.set_stream(cuda_stream_ptr)
+
+    def set_centroids(self, c, root=-1):
+        """root < 0: every rank passes the same table; root >= 0: rank root's is broadcast"""
+        keep, p = _ptr(c, np.float32, (self.nlist, self.d), "centroids")
+        self.local._order_with_torch(keep)
+        self._check(self._lib.b200_IndexShardsIVFFlat_set_centroids(self._h, p, root))
+
+    def train(self, x, root=0):
+        kx, px = _ptr(x, np.float32, None, "x")
+        self.local._order_with_torch(kx)
+        n = kx.shape[0] if kx is not None else 0
+        self._check(self._lib.b200_IndexShardsIVFFlat_train(self._h, n, px, root))
+
+    def add_with_ids(self, x, ids):
+        """NOT replicated: each rank passes ITS OWN vectors (possibly none); the library sends
+        every vector to the rank that owns its list."""
+        self.add_core(x, ids, None)
+
+    def add_core(self, x, ids, assign):
+        kx, px = _ptr(x, np.float32, None, "x")
+        n = kx.shape[0] if kx is not None else 0
+        ki, pi = _ptr(ids, np.int64, (n,), "ids")
+        ka, pa = _ptr(assign, np.int64, (n,), "assign")
+        self.local._order_with_torch(kx, ki, ka)
+        if assign is None:
+            self._check(self._lib.b200_IndexShardsIVFFlat_add_with_ids(self._h, n, px, pi))
+        else:
+            self._check(self._lib.b200_IndexShardsIVFFlat_add_core(self._h, n, px, pi, pa))
+
+    def reserve_lists(self, sizes):
+        self.local.reserve_lists(sizes)
+
+    def search(self, x, k, D=None, I=None, broadcast_from=None):
+        """x: [n][d], the same on every rank -- or, with ``broadcast_from=r``, rank r's queries
+        (the other ranks pass a buffer of the same shape to receive them). Returns the merged
+        (D, I) on every rank, living where x lives."""
+        kx, px = _ptr(x, np.float32, None, "x")
+        n = kx.shape[0]
+        if kx.ndim != 2 or kx.shape[1] != self.d:
+            raise ValueError("x must be [n][%d]" % self.d)
+        if D is None:
+            D = _empty_like_input(kx, (n, k), np.float32)
+        if I is None:
+            I = _empty_like_input(kx, (n, k), np.int64)
+        kd, pd = _ptr(D, np.float32, (n, k), "D")
+        ki, pi = _ptr(I, np.int64, (n, k), "I")
+        self.local._order_with_torch(kx, kd, ki)
+        root = -1 if broadcast_from is None else int(broadcast_from)
+        self._check(self._lib.b200_IndexShardsIVFFlat_search(self._h, n, px, k, pd, pi, root))
+        if self.local._own_stream and _is_torch(kx) and kx.is_cuda:
+            self.synchronize()
+        return kd, ki
+
+    def synchronize(self):
+        self._check(self._lib.b200_IndexShardsIVFFlat_synchronize(self._h))
+
+    def reset_phase_times(self):
+        self._lib.b200_IndexShardsIVFFlat_reset_phase_times(self._h)
+
+    def phase_time_sums(self):
+        """(calls, {phase: device ms summed over the searches since reset_phase_times})"""
+        ms = (C.c_double * 7)()
+        calls = self._lib.b200_IndexShardsIVFFlat_phase_time_sums(self._h, ms)
+        return int(calls), dict(zip(PHASES, list(ms)))
+
+
+# ------------------------------------------------------------------------------------------------
+# host-logic model (CPU tests over gloo; not the product path)
+# ------------------------------------------------------------------------------------------------
+def gather_results(D_loc, I_loc, group=None):
+    """All-gather the per-rank (n,k) tables into [world][n][k] tensors."""
     import torch
     import torch.distributed as dist
     world = dist.get_world_size(group)
     n, k = D_loc.shape
-    # rank r's table lands in rows [r*n, (r+1)*n): the [world][n][k] layout merge_knn_results reads
-    if out is not None:
-        all_D, all_I = out
-    else:
-        all_D = torch.empty((world * n, k), dtype=D_loc.dtype, device=D_loc.device)
-        all_I = torch.empty((world * n, k), dtype=I_loc.dtype, device=I_loc.device)
+    all_D = torch.empty((world * n, k), dtype=D_loc.dtype, device=D_loc.device)
+    all_I = torch.empty((world * n, k), dtype=I_loc.dtype, device=I_loc.device)
     dist.all_gather_into_tensor(all_D, D_loc.contiguous(), group=group)
     dist.all_gather_into_tensor(all_I, I_loc.contiguous(), group=group)
     return all_D.view(world, n, k), all_I.view(world, n, k)
 
 
-class IndexShardsIVFFlat:
-    """One rank's view of a list-sharded IndexIVFFlat.
+class ShardedSearchModel:
+    """The algorithm of csrc/shards.cu over torch.distributed collectives, with the local index
+    and the merge injected (the CPU suite uses the oracle for both, over a 2-process gloo group):
+    same list ranges, same query slices of the common quantizer (padded rows = -1), same probe
+    table on every rank, every pair scanned by the one rank that owns its list, all-gather, merge.
+    Here every rank is SHOWN all the vectors and keeps those of its lists."""
 
-    Every rank calls every method with the same arguments (SPMD). ``local`` may be injected (tests
-    use a CPU stand-in over gloo); by default it is the device index restricted to this rank's
-    list range.
-    """
-
-    def __init__(self, d, nlist, metric, device=0, group=None, local=None, merge=None,
-                 shard_quantizer=True):
+    def __init__(self, d, nlist, metric, local, merge, group=None):
         import torch.distributed as dist
         self.group = group
         self.rank = dist.get_rank(group)
         self.world = dist.get_world_size(group)
-        self.d, self.nlist, self.metric, self.device = d, nlist, metric, device
+        self.d, self.nlist, self.metric = d, nlist, metric
         self.list_lo, self.list_hi = list_range_of_rank(nlist, self.rank, self.world)
-        if local is None:
-            local = IndexIVFFlat(d, nlist, metric, device)
         local.set_list_range(self.list_lo, self.list_hi)
         self.local = local
-        self.shard_quantizer = shard_quantizer
-        self._merge = merge or (lambda m, aD, aI: merge_knn_results(m, aD, aI, device=device))
+        self._merge = merge
 
     @property
     def nprobe(self):
@@ -76,91 +207,33 @@ class IndexShardsIVFFlat:
         self.local.set_centroids(c)
 
     def add_with_ids(self, x, ids):
-        """Every rank is shown the same vectors and keeps those assigned to its lists."""
         self.local.add_with_ids(x, ids)
 
-    def add_core(self, x, ids, assign):
-        self.local.add_core(x, ids, assign)
-
     def search(self, x, k, broadcast_from=None):
-        """x: [n][d] on this rank's device (replicated, or broadcast from rank `broadcast_from`).
-        With ``self.trace = True`` (CUDA only) the device time of each phase of the call is left in
-        ``self.last_phase_ms`` (broadcast, quantize + probe all-gather, local search, result
-        all-gather, merge): one synchronize per call, so not for timed runs."""
-        marks = []
-
-        def mark(name):
-            if getattr(self, "trace", False):
-                import torch
-                e = torch.cuda.Event(enable_timing=True)
-                e.record()
-                marks.append((name, e))
-
-        mark("start")
+        import torch
+        import torch.distributed as dist
         if broadcast_from is not None:
-            import torch.distributed as dist
             dist.broadcast(x, src=broadcast_from, group=self.group)
-        mark("broadcast")
-        if self.world == 1:
-            return self.local.search(x, k)
-        if self.shard_quantizer:
-            Iq = self._quantize_sharded(x)
-            mark("quantize+gather")
-            D_loc, I_loc = self.local.search_preassigned(x, k, Iq)
-        else:
-            D_loc, I_loc = self.local.search(x, k)
-        mark("local search")
-        import torch
-        D_loc, I_loc = torch.as_tensor(D_loc), torch.as_tensor(I_loc)
-        n_, k_ = D_loc.shape
-        out = (self._scratch("all_D", (self.world * n_, k_), D_loc.dtype, D_loc.device),
-               self._scratch("all_I", (self.world * n_, k_), I_loc.dtype, I_loc.device))
-        all_D, all_I = gather_results(D_loc, I_loc, self.group, out=out)
-        mark("result gather")
-        out = self._merge(self.metric, all_D, all_I)
-        mark("merge")
-        if marks:
-            import torch
-            torch.cuda.synchronize()
-            self.last_phase_ms = {marks[i][0]: marks[i - 1][1].elapsed_time(marks[i][1])
-                                  for i in range(1, len(marks))}
-        return out
-
-    def _scratch(self, name, shape, dtype, device):
-        """per-shape scratch tensors kept across calls (no allocator traffic in the search loop)"""
-        import torch
-        cache = self.__dict__.setdefault("_bufs", {})
-        key = (name, tuple(shape), dtype, str(device))
-        t = cache.get(key)
-        if t is None:
-            t = cache[key] = torch.empty(shape, dtype=dtype, device=device)
-        return t
+        Iq = self._quantize_sharded(x)
+        D_loc, I_loc = self.local.search_preassigned(x, k, Iq)
+        all_D, all_I = gather_results(torch.as_tensor(D_loc), torch.as_tensor(I_loc), self.group)
+        return self._merge(self.metric, all_D, all_I)
 
     def _quantize_sharded(self, x):
-        """[n][nprobe] int64 probe table: each rank quantizes its slice of the queries straight
-        into its rows of the gathered table, then one in-place all-gather. Probes of lists this
-        rank does not own are simply skipped by its search_preassigned (the lists are empty there:
-        faiss/IndexIVF.cpp:526-529)."""
         import torch
         import torch.distributed as dist
         n = x.shape[0]
         nprobe = min(self.local.nprobe, self.nlist)
         chunk = (n + self.world - 1) // self.world
         lo, hi = min(self.rank * chunk, n), min((self.rank + 1) * chunk, n)
-        allq = self._scratch("allq", (self.world * chunk, nprobe), torch.int64, x.device)
-        mine = allq[self.rank * chunk:(self.rank + 1) * chunk]
-        if hi - lo < chunk:
-            mine[hi - lo:].fill_(-1)
+        allq = torch.full((self.world * chunk, nprobe), -1, dtype=torch.int64, device=x.device)
         if hi > lo:
-            if _is_device_index(self.local) and x.is_cuda:
-                dq = self._scratch("dq", (hi - lo, nprobe), torch.float32, x.device)
-                self.local.quantize(x[lo:hi], nprobe, Dq=dq, Iq=mine[:hi - lo])
-            else:
-                _, Iq = self.local.quantize(x[lo:hi].contiguous(), nprobe)
-                mine[:hi - lo] = torch.as_tensor(Iq).to(x.device)
+            _, Iq = self.local.quantize(x[lo:hi].contiguous(), nprobe)
+            allq[self.rank * chunk:self.rank * chunk + hi - lo] = torch.as_tensor(Iq).to(x.device)
+        mine = allq[self.rank * chunk:(self.rank + 1) * chunk].clone()
         dist.all_gather_into_tensor(allq, mine, group=self.group)
         return allq[:n]
 
 
-def _is_device_index(ix):
-    return isinstance(ix, IndexIVFFlat)
+__all__ = ["IndexShardsIVFFlat", "ShardedSearchModel", "list_range_of_rank", "nccl_unique_id",
+           "merge_knn_results", "PHASES"]

@@ -37,7 +37,9 @@ typedef struct B200IndexIVFStats {
     size_t nq;
     size_t nlist;
     size_t ndis;
-    size_t nheap_updates; /* not tracked on device: always 0 */
+    size_t nheap_updates; /* always 0: the reference counts replacements of ONE heap fed in probe
+                           * order (faiss/IndexIVFFlat.cpp:163,174-177); a list-major scan has
+                           * no such order, the figure is not reproducible */
     double quantization_time; /* ms, device time of the coarse quantizer */
     double search_time;       /* ms, device time of the whole search */
 } B200IndexIVFStats;
@@ -81,6 +83,16 @@ int b200_IndexIVFFlat_add_core(B200IndexIVFFlat* index, b200_idx_t n, const floa
 /* faiss_Index_reset, c_api/Index_c.h:151 */
 int b200_IndexIVFFlat_reset(B200IndexIVFFlat* index);
 
+/* Room for sizes[l] rows in list l before the vectors arrive (sizes: [nlist] int64, host or
+ * device; entries outside the handle's list range are ignored). Adds that stay within the
+ * reservation append in place: no second slab, nothing moves. The list-wise form of
+ * GpuIndexIVF::reserveMemory (faiss/gpu/GpuIndexIVF.h) / InvertedLists::resize
+ * (faiss/invlists/InvertedLists.h:103). */
+int b200_IndexIVFFlat_reserve_lists(B200IndexIVFFlat* index, const int64_t* sizes);
+/* sizes of all nlist lists at once (InvertedLists::list_size, faiss/invlists/InvertedLists.h:56),
+ * HOST array of nlist entries */
+int b200_IndexIVFFlat_get_list_sizes(const B200IndexIVFFlat* index, int64_t* sizes_out);
+
 /* faiss_IndexIVF_get_list_size, c_api/IndexIVF_c.h:123 */
 size_t b200_IndexIVFFlat_get_list_size(const B200IndexIVFFlat* index, size_t list_no);
 /* faiss_IndexIVF_invlists_get_ids, c_api/IndexIVF_c.h:148-151 (host buffer) */
@@ -111,11 +123,21 @@ void b200_IndexIVFFlat_reset_stats(B200IndexIVFFlat* index);
 /* device time in ms of the stages of the LAST search call: {coarse, plan, scan, select, total} */
 void b200_IndexIVFFlat_last_timings(const B200IndexIVFFlat* index, double* ms5);
 
+/* ... and the same five figures summed over every search call since reset_stats (so a timed loop
+ * need not stop after each call to read them); returns the number of calls */
+unsigned long long b200_IndexIVFFlat_stage_time_sums(const B200IndexIVFFlat* index, double* ms5);
+
 /* Run on a caller-owned CUDA stream (cudaStream_t as void*; NULL = the handle's own stream, a
  * non-blocking one; pass cudaStreamLegacy, (void*)0x1, to be ordered with the legacy default
- * stream). Calls whose buffers are all device pointers may return before the work completes:
- * they are ordered on this stream. */
+ * stream). search / search_preassigned / quantize calls whose buffers are ALL device pointers
+ * return as soon as their work is enqueued on this stream (no host synchronization): results are
+ * ordered with later work on the stream, statistics and stage times are read out when asked for,
+ * and a failure only the device can see -- a key >= nlist in a preassigned table,
+ * faiss/IndexIVF.cpp:520-524 -- is reported by b200_IndexIVFFlat_synchronize or by the next call
+ * on the handle instead of by the call that caused it. */
 int b200_IndexIVFFlat_set_stream(B200IndexIVFFlat* index, void* cuda_stream);
+/* wait for the asynchronous calls in flight; returns their deferred failure, if any */
+int b200_IndexIVFFlat_synchronize(const B200IndexIVFFlat* index);
 
 /* Kernel-selection knobs of the scan (what faiss exposes through ParameterSpace::set_index_parameter,
  * faiss/AutoTune.h:127-170, for its own indexes): "simt_max_avg_q", "tcr_max_avg_q" (queries per
@@ -141,6 +163,63 @@ int b200_debug_trap_info(unsigned long long* out8);
 int b200_merge_knn_results(B200MetricType metric, int nshard, b200_idx_t n, b200_idx_t k,
                            const float* all_distances, const b200_idx_t* all_labels,
                            float* distances, b200_idx_t* labels, int device, void* cuda_stream);
+
+/* ---- list-sharded index over several GPUs ---------------------------------------------------
+ * IndexShardsIVF (faiss/IndexShardsIVF.h:21-44; C API of the family: c_api/IndexShards_c.h) with
+ * shards that hold contiguous list RANGES (shard_type 4 / SUBSET_TYPE_INVLIST,
+ * faiss/gpu/GpuCloner.cpp:303-314): one process per GPU, each creating ITS rank of the index.
+ * The reference fans a search out to its shards with host threads and merges on the CPU
+ * (faiss/IndexShardsIVF.cpp:195-242); here the exchange steps are NCCL all-gathers over NVLink on
+ * the shard's stream and the merge runs on the device. Every call that takes the sharded handle
+ * is COLLECTIVE: all ranks make it, in the same order. */
+typedef struct B200IndexShardsIVFFlat_H B200IndexShardsIVFFlat;
+#define B200_NCCL_UNIQUE_ID_BYTES 128
+/* ncclGetUniqueId: one rank calls it and hands the 128 bytes to the others (MPI, sockets, a
+ * torch.distributed store, ...) */
+int b200_nccl_get_unique_id(void* out128);
+/* rank `rank` of `world`; the rank's shard lives on CUDA device `device` and owns the lists
+ * [rank * nlist / world, (rank + 1) * nlist / world). world == 1 needs no id (may be NULL). */
+int b200_IndexShardsIVFFlat_new(B200IndexShardsIVFFlat** p_index, size_t d, size_t nlist,
+                                B200MetricType metric, int device, int rank, int world,
+                                const void* nccl_unique_id128);
+void b200_IndexShardsIVFFlat_free(B200IndexShardsIVFFlat* index);
+/* faiss_IndexShards_at, c_api/IndexShards_c.h:41: this rank's shard, BORROWED (nprobe, options,
+ * statistics, list access, set_stream go through it) */
+B200IndexIVFFlat* b200_IndexShardsIVFFlat_local(B200IndexShardsIVFFlat* index);
+int b200_IndexShardsIVFFlat_rank(const B200IndexShardsIVFFlat* index);
+int b200_IndexShardsIVFFlat_world(const B200IndexShardsIVFFlat* index);
+b200_idx_t b200_IndexShardsIVFFlat_ntotal(const B200IndexShardsIVFFlat* index);
+/* root >= 0: rank root's table is broadcast (the others may pass NULL); root < 0: every rank
+ * passes the same table */
+int b200_IndexShardsIVFFlat_set_centroids(B200IndexShardsIVFFlat* index, const float* centroids,
+                                          int root);
+/* IndexShardsIVF::train, faiss/IndexShardsIVF.cpp:102-135: the common quantizer is trained once,
+ * on rank root with its n vectors, and shared */
+int b200_IndexShardsIVFFlat_train(B200IndexShardsIVFFlat* index, b200_idx_t n, const float* x,
+                                  int root);
+/* IndexShardsIVF::add_with_ids, faiss/IndexShardsIVF.cpp:137-154, distributed: each rank brings
+ * its OWN n vectors (n may differ per rank and may be 0); they are quantized where they are and
+ * sent to the rank that owns their list (NCCL send/recv). xids NULL: ids continue from ntotal in
+ * rank order. */
+int b200_IndexShardsIVFFlat_add_with_ids(B200IndexShardsIVFFlat* index, b200_idx_t n,
+                                         const float* x, const b200_idx_t* xids);
+/* the same with the list numbers given (faiss_IndexIVFFlat_add_core, c_api/IndexIVFFlat_c.h:60-65) */
+int b200_IndexShardsIVFFlat_add_core(B200IndexShardsIVFFlat* index, b200_idx_t n, const float* x,
+                                     const b200_idx_t* xids, const int64_t* precomputed_idx);
+/* IndexShardsIVF::search, faiss/IndexShardsIVF.cpp:158-243. root < 0: every rank passes the same
+ * n queries; root >= 0: rank root's queries are broadcast (the others pass a device buffer to
+ * receive them, or NULL). Every rank receives the merged tables. All-device calls return once
+ * their work is enqueued on the shard's stream. */
+int b200_IndexShardsIVFFlat_search(const B200IndexShardsIVFFlat* index, b200_idx_t n,
+                                   const float* x, b200_idx_t k, float* distances,
+                                   b200_idx_t* labels, int root);
+/* device ms of the phases of the searches since the last reset, summed: {query broadcast, coarse
+ * quantizer (this rank's query slice), probe-table all-gather, local plan + scan + k-select,
+ * result all-gather, merge, total}; returns the number of search calls */
+unsigned long long b200_IndexShardsIVFFlat_phase_time_sums(const B200IndexShardsIVFFlat* index,
+                                                           double* ms7);
+void b200_IndexShardsIVFFlat_reset_phase_times(B200IndexShardsIVFFlat* index);
+int b200_IndexShardsIVFFlat_synchronize(const B200IndexShardsIVFFlat* index);
 
 /* faiss_write_index_fname / faiss_read_index_fname (c_api/index_io_c.h:31,44) for this index type:
  * the reference's own file format ("IwFl" header, IndexFlat quantizer "IxF2"/"IxFI", "ilar"

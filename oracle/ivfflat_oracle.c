@@ -646,6 +646,12 @@ int orc_index_train(OrcIndex* ix, int64_t n, const float* x, int niter, int seed
     int64_t nx = n;
     float* xt = NULL;
     const float* xs = x;
+    if ((size_t)n == k) { /* "just copy training set to clusters", Clustering.cpp:346-368 */
+        memcpy(ix->centroids, x, sizeof(float) * k * d);
+        if (objective_out)
+            *objective_out = 0;
+        return 0;
+    }
     if ((size_t)n > k * (size_t)max_points_per_centroid) { /* subsample_training_set :86-133 */
         int64_t* perm = (int64_t*)malloc(sizeof(int64_t) * (size_t)n);
         ref_rand_perm(perm, (size_t)n, seed);

@@ -127,7 +127,7 @@ def _rank_main(rank, world, port, q):
             xq = torch.from_numpy(clustered(nq, d, 48, 2))
             merge = lambda m, aD, aI: tuple(map(torch.from_numpy, po.port_merge_knn_results(
                 m, aD.numpy(), aI.numpy())))
-            sh = b2.IndexShardsIVFFlat(d, nlist, metric, local=_CpuLocal(d, nlist, metric),
+            sh = b2.ShardedSearchModel(d, nlist, metric, local=_CpuLocal(d, nlist, metric),
                                        merge=merge)
             sh.set_centroids(cent)
             sh.add_with_ids(xb, None)
