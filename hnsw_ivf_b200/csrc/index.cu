@@ -1305,6 +1305,12 @@ void IndexIVFFlatB200::set_option(const char* name, double value) {
         m.use_tc = value != 0;
     else if (n == "use_graph")
         m.use_graph = value != 0;
+    else if (n == "cp_niter") // ClusteringParameters of the quantizer (faiss/Clustering.h:23-64),
+        cp_niter = std::max(0, (int)value); // index.cp.niter in the reference
+    else if (n == "cp_max_points_per_centroid")
+        cp_max_points_per_centroid = std::max(1, (int)value);
+    else if (n == "cp_seed")
+        cp_seed = (int)value;
     else
         throw B200Exception("unknown option '" + n + "'");
 }

@@ -111,8 +111,8 @@ struct TcScanArgs {
                                 // every score, 2 = no MMAs issued, 4 = split warps do not compute
 };
 constexpr int kTcStages = 9;
-// entries per partial list the tensor-core scan keeps for a request of k (>= k, with a margin
-// when there is room); 0 = not supported (d > 128 or k > 32)
+// entries per partial list the tensor-core scan keeps for a request of k: 16 for k <= 12, 32 for
+// k <= 24 (always a margin over k: the scores are approximate); 0 = not supported (d > 128, k > 24)
 int scan_tc_kpart(int nf4, int k);
 size_t scan_tc_smem_bytes(int nstages);
 cudaError_t make_slab_tensor_map_tc(void* map_out, const void* slab, int nf4, uint64_t nblocks);
@@ -120,8 +120,8 @@ cudaError_t launch_ivf_scan_tc(int metric, uint32_t max_items, const TcScanArgs&
                                cudaStream_t st);
 
 // ---- rows-major tensor-core scan (scan_tcr.cu): same arguments, <= kTcrTQ queries per item, ONE
-// sorted list of kpart keys per (pair, split); nstages is chosen by the launcher --------------------
-constexpr int kTcrTQ = 96;
+// sorted list of kpart keys per (pair, split); nstages is chosen by the launcher. kpart up to 256.
+constexpr int kTcrTQ = 64;
 // d up to 1024; the queries per item shrink with the dimension (the query tile lives in shared
 // memory): scan_tcr_tq(nf4, kpart), 0 = unsupported. scan_tcr_kpart: as scan_tc_kpart.
 int scan_tcr_tq(int nf4, int kp);

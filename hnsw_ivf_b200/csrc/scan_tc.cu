@@ -675,8 +675,8 @@ int scan_tc_kpart(int nf4, int k) {
         return 0;
     if (k + 4 <= 16)
         return 16;
-    if (k <= 32)
-        return 32;
+    if (k + 8 <= 32) // (k = 25..32 would leave the exact re-rank less than 8 spare keys: the
+        return 32;   // rows-major kernel takes those with 64 kept)
     return 0;
 }
 

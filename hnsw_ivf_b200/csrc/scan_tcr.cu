@@ -7,16 +7,23 @@
 // in `part`, sorted. Scores are 3xTF32 products (fp32 accumulate), good to ~1e-6 of |x||y|: enough
 // to SELECT; select.cu re-scores the survivors in plain fp32 before the final ordering.
 //
-// Work item = (list, tile of <= 96 queries probing it, row split); one CTA each.
-//   D[128 rows x N queries] (TMEM, two buffers) += A[128 rows x 8] (TMEM) * B[N queries x 8]^T (smem)
+// Work item = (list, tile of <= 64 queries probing it, row split); one CTA each.
+//   D[128 rows x N] (TMEM, two buffers) += A[128 rows x 8] (TMEM) * B[N x 8]^T (smem)
 // The list rows are the M side of the MMA and the queries the N side, because the time of a
 // tcgen05.mma is max(M,128) * N / 256 cycles: N follows the number of queries that really probe the
-// list (rounded up to 16), M = 128 costs the same whether it is full or not. With few queries per
-// list the kernel is a pure HBM stream; with ~100 it is tensor-pipe bound.
-//  * B: the query tile, scaled by -1 (inner product) or -2 (L2), split into tf32 hi / lo parts,
-//    written once per item into shared memory in the K-major no-swizzle canonical layout
-//    (8 queries x 16 bytes = one core matrix, SBO = 128 B, LBO = 97 * 16 B: odd, so that the
-//    coalesced prologue stores are bank-conflict free).
+// list (rounded up to 16), M = 128 costs the same whether it is full or not -- and an MMA whose A
+// operand sits in tensor memory costs ~60 cycles whatever N is (the 4 KB of A are read at 64 B per
+// cycle), so the number of MMAs per 8 dimensions is what sets the tensor-pipe
+// time of a tile. The 3xTF32 product x.y = xh.yh + xl.yh + xh.yl therefore takes TWO MMAs, not three:
+//  * B: the query tile, scaled by -1 (inner product) or -2 (L2), split into tf32 hi / lo parts and
+//    STACKED along N: rows 0..n16-1 of the operand are x_hi, rows n16..2*n16-1 are x_lo (K-major
+//    no-swizzle canonical layout: 8 rows x 16 bytes = one core matrix, SBO = 128 B, LBO =
+//    (2*n16 + 1) * 16 B: odd, so that the coalesced prologue stores are bank-conflict free).
+//      MMA 1: D[:, 0 : 2*n16] (+)= y_hi * [x_hi | x_lo]^T   (N = 2*n16)
+//      MMA 2: D[:, 0 : n16]    += y_lo * x_hi^T             (N = n16, same buffer, first n16 rows)
+//    and the epilogue adds columns j and n16 + j. (Three separate MMAs were 2.3 k cycles per
+//    128 x 96-dim tile, exactly the time the tile takes to arrive from HBM at 6.5 TB/s -- the kernel
+//    could not be HBM-bound; two are 1.5 k.)
 //  * A: list rows arrive by TMA (box {128 floats, 4 blocks, 8 columns} of the slab = 128 rows x 32
 //    dims per stage). The split warps read a stage once from shared memory (lane = row) and write
 //    BOTH operand parts to tensor memory with tcgen05.st: hi = the raw fp32 bits (the tensor core
@@ -24,11 +31,12 @@
 //    stage is released to the TMA as soon as it is in registers; the MMAs never read row data from
 //    shared memory (per stage: 16 KB TMA write + 16 KB read + 12 * N * 32 B of B reads, against
 //    96 KB for the queries-major form, which was shared-memory-bandwidth bound).
-//  * One elected thread issues the MMAs (3 per 8 dims: lo*hi, hi*lo, hi*hi).
-//  * Epilogue (4 warps, thread = row = TMEM lane): per 16 queries one tcgen05.ld; score (+ |y|^2
+//  * One elected thread issues the MMAs (2 per 8 dims, see above).
+//  * Epilogue (8 warps, thread = row = TMEM lane): per 16 queries two tcgen05.ld (the two column
+//    groups) and 16 adds; score (+ |y|^2
 //    for L2) is compared with the query's pruning bound held in shared memory; a warp ballot skips
 //    the column when no row passes (the steady state). Passing (score, row) keys are appended to
-//    the query's candidate buffer (64 entries: KP kept + free ones) with a shared-memory atomic; at the
+//    the query's candidate buffer (C = max(64, 2 KP) entries: KP kept + free ones) with a shared-memory atomic; at the
 //    end of a tile the warps compact the buffers that filled up (warp bitonic sort, keep KP,
 //    tighten the bound, publish it in qthr for the other CTAs working on the same query). A tile
 //    that overflows a buffer is re-examined for the dropped rows after the compaction (at most 8
@@ -62,15 +70,21 @@ constexpr uint32_t kRColsD = 0;   // two accumulator buffers of 128 columns
 constexpr uint32_t kRColsA = 256; // kRAStages x (32 hi + 32 lo) columns
 constexpr int kRMaxChunks = 256;  // float4 columns of a query (d <= 1024)
 constexpr uint32_t kRBSBO = 128;
-// Candidate buffer of a query: kRCand entries = the KP kept + free ones. A buffer is compacted
-// (sorted, cut to KP, bound tightened) once it holds kRCompactAt entries, which leaves kRCand -
-// kRCompactAt slots for the rest of the tile before rows start to be dropped and re-examined.
+// Candidate buffer of a query: C entries = the KP kept + free ones. A buffer is compacted
+// (sorted, cut to KP, bound tightened) once it holds CompactAt entries, which leaves C -
+// CompactAt slots for the rest of the tile before rows start to be dropped and re-examined.
 // A compaction stops the whole epilogue at two block barriers, and the epilogue is the stage that
 // paces the kernel when few queries meet in a list: with 16 free slots and a compaction every 8
 // new candidates there was about one per tile (10 queries x ~1 candidate per tile each); 64 entries
 // compacted at 48 make it one tile in four.
-constexpr int kRCand = 64;
-constexpr int kRCompactAt = 48;
+// KP up to 256 (the reference's reservoir range, faiss/impl/ResultHandler.h:369-477: k >= 100):
+// C = 2 KP entries, compacted when three quarters full.
+__host__ __device__ constexpr int tcr_cand(int kp) {
+    return kp <= 32 ? 64 : 2 * kp;
+}
+__host__ __device__ constexpr int tcr_compact_at(int kp) {
+    return tcr_cand(kp) - tcr_cand(kp) / 4;
+}
 
 __device__ __forceinline__ float tf32_trunc(float x) {
     return __uint_as_float(__float_as_uint(x) & 0xffffe000u);
@@ -84,8 +98,9 @@ __device__ __forceinline__ float tf32_lo(float y) {
 
 template <int KP>
 struct RCfg {
-    static constexpr int C = kRCand;                // candidate entries per query
-    static_assert(KP + 16 <= kRCompactAt, "compaction must leave room above the kept entries");
+    static constexpr int C = tcr_cand(KP);          // candidate entries per query
+    static constexpr int CompactAt = tcr_compact_at(KP);
+    static_assert(KP + 16 <= CompactAt, "compaction must leave room above the kept entries");
 };
 
 // ascending bitonic sort of one key per lane
@@ -147,8 +162,7 @@ __device__ __forceinline__ float loosen(float x) {
 
 struct RSmem {
     float4* raw;        // [nst][kRStageF4]
-    unsigned char* bhi; // query tile, hi part
-    unsigned char* blo; // query tile, lo part
+    unsigned char* b;   // query tile: per 16-byte K chunk, n16 rows of x_hi then n16 rows of x_lo
     uint64_t* cand;     // [kTcrTQ][C]
     uint32_t* thr;      // [kTcrTQ] ordered bits of the pruning bound (full score)
     float* thrp;        // [kTcrTQ] bound minus |x|^2: what the raw accumulator is compared with
@@ -169,13 +183,13 @@ struct RSmem {
 // Shared memory is carved per ITEM: the B operand and the candidate buffers are sized by the item's
 // query count (n16) and dimension (nch chunks), and the raw ring gets every 16 KB stage that is
 // left -- with few queries the kernel is an HBM stream and lives on bytes in flight.
-//   B part: nch chunks x LBO bytes, LBO = (n16 + 1) * 16 (odd multiple of 16: the coalesced
+//   B: nch chunks x LBO bytes, LBO = (2 * n16 + 1) * 16 (odd multiple of 16: the coalesced
 //   prologue stores of one query row hit 8 different 16-byte bank groups)
 __host__ __device__ inline uint32_t tcr_lbo(int n16) {
-    return (uint32_t)(n16 + 1) * 16u;
+    return (uint32_t)(2 * n16 + 1) * 16u;
 }
 __host__ __device__ inline size_t tcr_rest_bytes(int kp, int n16, int nch) {
-    return 2 * (size_t)nch * tcr_lbo(n16) + (size_t)n16 * kRCand * 8 +
+    return (size_t)nch * tcr_lbo(n16) + (size_t)n16 * tcr_cand(kp) * 8 +
             (size_t)kTcrTQ * 6 * 4 + 4 * 4 + (2 * kRMaxStages + 2 * kRAStages + 4) * 8 + 16;
 }
 __host__ __device__ inline int tcr_stages(size_t smem_total, int kp, int n16, int nch) {
@@ -197,9 +211,8 @@ __device__ __forceinline__ RSmem carve_r(unsigned char* raw, int nst, int n16, i
     RSmem s;
     const size_t bbytes = (size_t)nch * tcr_lbo(n16);
     s.raw = reinterpret_cast<float4*>(raw);
-    s.bhi = raw + (size_t)nst * kRStageF4 * sizeof(float4);
-    s.blo = s.bhi + bbytes;
-    s.cand = reinterpret_cast<uint64_t*>(s.blo + bbytes);
+    s.b = raw + (size_t)nst * kRStageF4 * sizeof(float4);
+    s.cand = reinterpret_cast<uint64_t*>(s.b + bbytes);
     s.thr = reinterpret_cast<uint32_t*>(s.cand + (size_t)n16 * RCfg<KP>::C);
     s.thrp = reinterpret_cast<float*>(s.thr + kTcrTQ);
     s.thrf = s.thrp + kTcrTQ;
@@ -224,23 +237,18 @@ __device__ __noinline__ void tcr_compact(uint64_t* cand, int* cnt, uint32_t* thr
                                          float* thrf, const float* xn, const int* qid,
                                          uint32_t* qthr, int nqw, int warp, int lane,
                                          bool final_pass) {
-    constexpr int C = kRCand;
+    constexpr int C = RCfg<KP>::C;
     const int qmine = lane * kREpiWarps + warp;
-    const bool need = qmine < nqw && (final_pass || cnt[qmine] >= kRCompactAt);
+    const bool need = qmine < nqw && (final_pass || cnt[qmine] >= RCfg<KP>::CompactAt);
     unsigned todo = __ballot_sync(0xffffffffu, need);
     while (todo != 0u) {
         const int qi = (__ffs(todo) - 1) * kREpiWarps + warp;
         todo &= todo - 1u;
         const int n = min(cnt[qi], C);
         uint64_t* buf = cand + (size_t)qi * C;
-        uint64_t k0 = lane < n ? buf[lane] : kSentinelKey;
         uint64_t kth;
-        if (C <= 32) {
-            k0 = warp_sort32(k0, lane);
-            if (lane < KP)
-                buf[lane] = k0;
-            kth = __shfl_sync(0xffffffffu, k0, KP - 1);
-        } else {
+        if (C == 64) {
+            uint64_t k0 = lane < n ? buf[lane] : kSentinelKey;
             uint64_t k1 = lane + 32 < n ? buf[lane + 32] : kSentinelKey;
             warp_sort64(k0, k1, lane);
             if (lane < KP)
@@ -249,6 +257,14 @@ __device__ __noinline__ void tcr_compact(uint64_t* cand, int* cnt, uint32_t* thr
                 buf[lane + 32] = k1;
             kth = KP <= 32 ? __shfl_sync(0xffffffffu, k0, (KP - 1) & 31)
                            : __shfl_sync(0xffffffffu, k1, (KP - 1) & 31);
+        } else {
+            // larger buffers: bitonic network in shared memory (rare: one compaction per
+            // C / 4 accepted candidates of a query)
+            for (int i = n + lane; i < C; i += 32)
+                buf[i] = kSentinelKey;
+            __syncwarp();
+            warp_sort_keys(buf, C, lane);
+            kth = buf[KP - 1];
         }
         if (lane == 0) {
             cnt[qi] = min(n, KP);
@@ -460,8 +476,8 @@ __global__ void __launch_bounds__(kRThreads, 1)
                     lo.z = tf32_lo(h.z);
                     lo.w = tf32_lo(h.w);
                     const size_t off = (size_t)c * lbo + (size_t)n * 16;
-                    *reinterpret_cast<float4*>(s.bhi + off) = h;
-                    *reinterpret_cast<float4*>(s.blo + off) = lo;
+                    *reinterpret_cast<float4*>(s.b + off) = h;                     // row n
+                    *reinterpret_cast<float4*>(s.b + off + (size_t)n16 * 16) = lo; // row n16 + n
                 }
             }
         }
@@ -499,9 +515,12 @@ __global__ void __launch_bounds__(kRThreads, 1)
     if (warp == kRMmaWarp) {
         // ======================= MMA issuer =====================================================
         // The whole warp runs the loop (converged control flow); one elected lane issues.
-        const uint32_t idesc = make_idesc_tf32(kRTileBlocks * kBlockRows, n16);
+        // MMA 1: N = 2 * n16 (x_hi | x_lo stacked), MMA 2: N = n16 (x_hi: the first n16 rows of the
+        // same chunks)
+        const uint32_t idesc2 = make_idesc_tf32(kRTileBlocks * kBlockRows, 2 * n16);
+        const uint32_t idesc1 = make_idesc_tf32(kRTileBlocks * kBlockRows, n16);
         const uint64_t desc0 = make_smem_desc_kmajor_noswz(0, lbo, kRBSBO);
-        const uint32_t bhi0 = smem_u32(s.bhi), blo0 = smem_u32(s.blo);
+        const uint32_t b0a = smem_u32(s.b);
         tc_fence_after_sync();
         int as = 0;
         uint32_t aph = 0;
@@ -523,21 +542,18 @@ __global__ void __launch_bounds__(kRThreads, 1)
                 const int ksn = (a.dbg & 8) ? 0 : nks - ks0; // >= 1
                 const uint32_t ahi = tmem + kRColsA + (uint32_t)as * 64u;
                 const uint32_t alo = ahi + 32u;
-                // B descriptors advance by 2 chunks (2 * LBO bytes, in 16-byte units) per k-step
-                const uint64_t dhi = desc0 + (uint64_t)((bhi0 + (uint32_t)(ks0 * 2) * lbo) >> 4);
-                const uint64_t dlo = desc0 + (uint64_t)((blo0 + (uint32_t)(ks0 * 2) * lbo) >> 4);
+                // the B descriptor advances by 2 chunks (2 * LBO bytes, in 16-byte units) per k-step
+                const uint64_t db = desc0 + (uint64_t)((b0a + (uint32_t)(ks0 * 2) * lbo) >> 4);
                 const int nas = as + 1 == kRAStages ? 0 : as + 1;
                 const uint32_t naph = as + 1 == kRAStages ? aph ^ 1u : aph;
                 if (elect_one_sync()) {
 #pragma unroll
                     for (int ks = 0; ks < kRKC / 2 - 1; ++ks) {
                         if (ks < ksn) {
-                            const uint64_t kh = dhi + (uint64_t)((uint32_t)ks * ((2u * lbo) >> 4));
-                            const uint64_t kl = dlo + (uint64_t)((uint32_t)ks * ((2u * lbo) >> 4));
-                            // small terms first, the big product last
-                            mma_tf32_ts(tD, alo + ks * 8, kh, idesc, (sg | ks) != 0 ? 1u : 0u);
-                            mma_tf32_ts(tD, ahi + ks * 8, kl, idesc, 1u);
-                            mma_tf32_ts(tD, ahi + ks * 8, kh, idesc, 1u);
+                            const uint64_t kb = db + (uint64_t)((uint32_t)ks * ((2u * lbo) >> 4));
+                            // the first MMA of a tile overwrites all 2 * n16 columns
+                            mma_tf32_ts(tD, ahi + ks * 8, kb, idesc2, (sg | ks) != 0 ? 1u : 0u);
+                            mma_tf32_ts(tD, alo + ks * 8, kb, idesc1, 1u);
                         }
                     }
                 }
@@ -546,11 +562,9 @@ __global__ void __launch_bounds__(kRThreads, 1)
                 if (elect_one_sync()) {
                     constexpr int ks = kRKC / 2 - 1;
                     if (ks < ksn) {
-                        const uint64_t kh = dhi + (uint64_t)((uint32_t)ks * ((2u * lbo) >> 4));
-                        const uint64_t kl = dlo + (uint64_t)((uint32_t)ks * ((2u * lbo) >> 4));
-                        mma_tf32_ts(tD, alo + ks * 8, kh, idesc, 1u);
-                        mma_tf32_ts(tD, ahi + ks * 8, kl, idesc, 1u);
-                        mma_tf32_ts(tD, ahi + ks * 8, kh, idesc, 1u);
+                        const uint64_t kb = db + (uint64_t)((uint32_t)ks * ((2u * lbo) >> 4));
+                        mma_tf32_ts(tD, ahi + ks * 8, kb, idesc2, 1u);
+                        mma_tf32_ts(tD, alo + ks * 8, kb, idesc1, 1u);
                     }
                     if (a.dbg & 128) {
                         mbar_arrive(&s.a_empty[as]);
@@ -654,7 +668,7 @@ __global__ void __launch_bounds__(kRThreads, 1)
                                      : (METRIC == kMetricL2 ? __ldg(a.norms + rowid) : 0.f);
             const float nrmf = nrm * (1.f - 4.76837158e-7f); // the filter errs on the accept side
             const uint32_t gthr = (myq >= 0 && a.qthr) ? __ldcg(a.qthr + myq) : 0xffffffffu;
-            uint32_t drop[kTcrTQ / 32] = {0u, 0u, 0u};
+            uint32_t drop[3] = {0u, 0u, 0u}; // (16 queries per half word; 4 chunks at most)
             TCR_WAIT(&s.d_full[b], (uint32_t)((t >> 1) & 1), w_dfull, 6, t);
             tc_fence_after_sync();
             const uint32_t tD = tmem + lane_addr + kRColsD + (uint32_t)b * 128u;
@@ -669,8 +683,16 @@ __global__ void __launch_bounds__(kRThreads, 1)
                     uint32_t v[16];
                     if (a.dbg & 64)
                         continue;
-                    tmem_ld_32x32b_x16(tD + (uint32_t)ch * 16u, v);
-                    tmem_ld_wait();
+                    {
+                        // y_hi.x_hi + y_lo.x_hi sits in column j, y_hi.x_lo in column n16 + j
+                        uint32_t w[16];
+                        tmem_ld_32x32b_x16(tD + (uint32_t)ch * 16u, v);
+                        tmem_ld_32x32b_x16(tD + (uint32_t)(n16 + ch * 16), w);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int j = 0; j < 16; ++j)
+                            v[j] = __float_as_uint(__uint_as_float(v[j]) + __uint_as_float(w[j]));
+                    }
                     if (a.dbg & 1)
                         continue;
                     const uint32_t dword = ch < 2 ? drop[0] : (ch < 4 ? drop[1] : drop[2]);
@@ -717,7 +739,7 @@ __global__ void __launch_bounds__(kRThreads, 1)
                                 ndrop |= 1u << j;
                                 fl |= 2;
                             }
-                            if (slot + 1 >= kRCompactAt)
+                            if (slot + 1 >= RCfg<KP>::CompactAt)
                                 fl |= 1;
                         }
                     }
@@ -889,7 +911,8 @@ static cudaError_t launch_tcr_one(uint32_t max_items, const TcScanArgs& a_in, cu
 // queries per item for dimension nf4*4 and kp kept keys: the largest multiple of 16 (<= kTcrTQ) that
 // leaves the raw ring at least 4 stages; 0 = the kernel cannot take this shape
 int scan_tcr_tq(int nf4, int kp) {
-    if (nf4 < 1 || nf4 > kRMaxChunks || (kp != 16 && kp != 32))
+    if (nf4 < 1 || nf4 > kRMaxChunks ||
+        (kp != 16 && kp != 32 && kp != 64 && kp != 128 && kp != 256))
         return 0;
     const int nch = 2 * ((nf4 + 1) >> 1);
     for (int tq = kTcrTQ; tq >= 16; tq -= 16)
@@ -897,8 +920,16 @@ int scan_tcr_tq(int nf4, int kp) {
             return tq;
     return 0;
 }
+// keys kept per partial list for a request of k: always a few more than k, because the scores
+// that select them are 3xTF32 ones and the exact fp32 re-rank (select.cu) can only re-order what
+// was kept: margin >= 4 for k <= 12, >= 8 above
 int scan_tcr_kpart(int nf4, int k) {
-    const int kp = k + 4 <= 16 ? 16 : (k <= 32 ? 32 : 0);
+    const int kp = k + 4 <= 16 ? 16
+            : k + 8 <= 32      ? 32
+            : k + 8 <= 64      ? 64
+            : k + 8 <= 128     ? 128
+            : k + 8 <= 256     ? 256
+                               : 0;
     return kp && scan_tcr_tq(nf4, kp) ? kp : 0;
 }
 
@@ -912,6 +943,15 @@ cudaError_t launch_ivf_scan_tcr(int metric, uint32_t max_items, const TcScanArgs
     if (a.kpart == 32)
         return metric == kMetricL2 ? launch_tcr_one<kMetricL2, 32>(max_items, a, st)
                                    : launch_tcr_one<kMetricInnerProduct, 32>(max_items, a, st);
+    if (a.kpart == 64)
+        return metric == kMetricL2 ? launch_tcr_one<kMetricL2, 64>(max_items, a, st)
+                                   : launch_tcr_one<kMetricInnerProduct, 64>(max_items, a, st);
+    if (a.kpart == 128)
+        return metric == kMetricL2 ? launch_tcr_one<kMetricL2, 128>(max_items, a, st)
+                                   : launch_tcr_one<kMetricInnerProduct, 128>(max_items, a, st);
+    if (a.kpart == 256)
+        return metric == kMetricL2 ? launch_tcr_one<kMetricL2, 256>(max_items, a, st)
+                                   : launch_tcr_one<kMetricInnerProduct, 256>(max_items, a, st);
     return cudaErrorInvalidValue;
 }
 

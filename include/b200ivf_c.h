@@ -143,7 +143,10 @@ int b200_IndexIVFFlat_synchronize(const B200IndexIVFFlat* index);
  * faiss/AutoTune.h:127-170, for its own indexes): "simt_max_avg_q", "tcr_max_avg_q" (queries per
  * probed list below which the exact warp kernel / the rows-major tensor-core kernel takes the
  * scan), "tc_mode" (0 auto, 1 queries-major, 2 rows-major), "use_tc", "use_graph". They change
- * which kernels run, never the results. Unknown names fail with -2. */
+ * which kernels run, never the results. Also here, for want of a struct accessor in a C API: the
+ * quantizer's ClusteringParameters as IndexIVF exposes them (index.cp, faiss/IndexIVF.h:39-41,
+ * faiss/Clustering.h:23-64): "cp_niter", "cp_max_points_per_centroid", "cp_seed" -- read by train.
+ * Unknown names fail with -2. */
 int b200_IndexIVFFlat_set_option(B200IndexIVFFlat* index, const char* name, double value);
 
 /* Number of CUDA kernels this library has launched in this process (all handles). */
