@@ -575,6 +575,8 @@ cudaError_t launch_select(const SelectArgs& a, cudaStream_t st) {
     if (prefilter)
         threads = few_wide ? (int)std::min<int64_t>(1024, pow2_ceil((int)std::min<int64_t>(total / 4, 1024)))
                            : 128;
+    if (a.slab) // the exact re-rank gives one thread to each of the kk survivors
+        threads = std::max(threads, (kk + 31) / 32 * 32);
     if (smem > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(select_kernel,
                                              cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
