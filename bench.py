@@ -60,6 +60,11 @@ WORKLOADS = {
     "C3": dict(desc="IVFFlat nlist=1024 L2, synthetic GIST-shape 1Mx960 fp32, 10k queries", d=960,
                nb=1_000_000, nlist=1024, metric=METRIC_L2, nq=10_000, k=10, normalize=False,
                nprobes=[1, 2, 4, 8, 16, 32, 64]),
+    # BASELINE.json configs[3], weak-scaling form: per-GPU figures, multiplied by the world size
+    "C4": dict(desc="IVFFlat L2, synthetic Deep1B-shape x96 fp32, 125M vectors + 32768 lists per "
+                    "GPU (8 GPUs: 1B, nlist 262144), list-sharded, 10k-query batch", d=96,
+               nb=125_000_000, nlist=32768, metric=METRIC_L2, nq=10_000, k=10, normalize=False,
+               nprobes=[1, 2, 4, 8, 16, 24, 32, 48, 64, 96, 128]),
     # development size
     "tiny": dict(desc="dev: IVFFlat nlist=256 IP 200kx128", d=128, nb=200_000, nlist=256,
                  metric=METRIC_IP, nq=2000, k=10, normalize=True, nprobes=[1, 2, 4, 8, 16]),
@@ -243,6 +248,65 @@ def scan_traffic_bytes(workload, nprobe):
         return None
 
 
+def measure_tf32_peak(torch, dev, n=8192, reps=8):
+    """Dense TF32 GEMM rate of this box (cuBLAS, allow_tf32: a library GEMM used as a yardstick
+    only): the ONE tensor-pipe denominator of the line (roofline.tensor, roofline.coarse)."""
+    old = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = True
+    try:
+        a = torch.randn((n, n), device=dev, dtype=torch.float32)
+        b = torch.randn((n, n), device=dev, dtype=torch.float32)
+        for _ in range(2):
+            a @ b
+        best = 1e30
+        for _ in range(reps):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            a @ b
+            e1.record()
+            e1.synchronize()
+            best = min(best, e0.elapsed_time(e1))
+        del a, b
+        return 2.0 * n ** 3 / (best * 1e-3) / 1e12
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = old
+        torch.cuda.empty_cache()
+
+
+def parity_detail(D_ref, I_ref, D_new, I_new):
+    """Reference vs this library on the same queries: position-wise id agreement, and every
+    differing slot classified -- `exact_ties`: the two distances at that rank are the same fp32
+    number (the reference's own tie order decides); `near_ties`: they differ, by at most
+    max_rel_gap relative (two summation orders of the same row sets, faiss compiles its distance
+    loops with reassociation); `unexplained`: anything the tie-aware rule of tests/helpers.py
+    (contrib/evaluation.py:243-262) does not cover; `bad_dist`: distances off by > 1e-4 relative."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from helpers import compare_knn
+    D_ref, I_ref, D_new, I_new = map(np.asarray, (D_ref, I_ref, D_new, I_new))
+    r = compare_knn(D_ref, I_ref, D_new, I_new)
+    neq = I_ref != I_new
+    dr, dn = D_ref[neq].astype(np.float64), D_new[neq].astype(np.float64)
+    exact = int((dr == dn).sum())
+    gap = np.abs(dr - dn) / np.maximum(np.maximum(np.abs(dr), np.abs(dn)), 1e-30)
+    ok = I_ref >= 0
+    rel_all = np.abs(D_ref[ok].astype(np.float64) - D_new[ok]) / np.maximum(np.abs(D_ref[ok]), 1e-30)
+    return {"queries": int(I_ref.shape[0]), "k": int(I_ref.shape[1]),
+            "exact_id_rate": r["exact_id_rate"], "differing_slots": int(neq.sum()),
+            "exact_ties": exact, "near_ties": int(neq.sum()) - exact - r["unexplained"],
+            "max_rel_gap_at_differing_slots": float(gap.max()) if gap.size else 0.0,
+            "max_rel_distance_error": float(rel_all.max()) if rel_all.size else 0.0,
+            "unexplained": r["unexplained"], "bad_dist": r["bad_dist"]}
+
+
+def scan_kernel_name(avg_q, d, k, simt_max=3.0, tcr_max=48.0):
+    """the list-scan kernel the library's plan picks (csrc/index.cu search_impl_) for this shape"""
+    if avg_q <= simt_max:
+        return "ivf_scan_kernel (exact fp32 warp kernel)"
+    if d > 128 or k > 24 or avg_q < tcr_max:
+        return "ivf_scan_tcr_kernel (rows-major tcgen05 3xTF32, 2 MMAs per k-step)"
+    return "ivf_scan_tc_kernel (queries-major tcgen05 3xTF32, 3 MMAs per k-step)"
+
+
 # ------------------------------------------------------------------------------------------------
 # CPU baseline (the reference compiled into oracle/_ref, or the C port)
 # ------------------------------------------------------------------------------------------------
@@ -296,6 +360,13 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--gt-queries", type=int, default=1000)
+    ap.add_argument("--no-c4", action="store_true", help="leave the c4 object out of the line")
+    ap.add_argument("--c4-rows-per-gpu", type=int, default=0,
+                    help="C4: vectors per GPU (default 125M; lists scale with it)")
+    ap.add_argument("--c4-steps", type=int, default=10)
+    ap.add_argument("--c4-nprobe", type=int, default=0)
+    ap.add_argument("--c4-slice", type=int, default=10_000_000,
+                    help="vectors of the C4 slice searched by the reference too (0 = skip)")
     return ap.parse_args()
 
 
