@@ -391,6 +391,17 @@ def pick_nprobe(sweep, want):
     return sweep[-1][0]
 
 
+def unique_probed_rows(torch, g, xq, nprobe, lo_l, hi_l):
+    """rows of the distinct lists of [lo_l, hi_l) the batch probes: what a list-major scan must
+    stream from HBM once per step (the physical lower bound the roofline is taken against)"""
+    _, Iq_all = g.quantize(xq, nprobe)
+    torch.cuda.synchronize()
+    uniq = torch.unique(Iq_all.reshape(-1))
+    uniq = uniq[(uniq >= lo_l) & (uniq < hi_l)].cpu().numpy()
+    sizes = g.list_sizes()
+    return int(sizes[uniq].sum())
+
+
 # ------------------------------------------------------------------------------------------------
 def run_b200(args):
     import torch
@@ -408,8 +419,29 @@ def run_b200(args):
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=dev)
+    ctx = dict(torch=torch, b2=b2, dist=dist, rank=rank, world=world, local=local, dev=dev)
+    tf32_peak = measure_tf32_peak(torch, dev)
+    if args.workload == "C4":
+        out = bench_c4(args, ctx, tf32_peak, headline=True)
+    else:
+        out = bench_flat(args, ctx, tf32_peak)
+        if not args.no_c4 and args.workload == "C2":
+            c4 = bench_c4(args, ctx, tf32_peak, headline=False)
+            if rank == 0:
+                out["c4"] = c4
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank == 0:
+        print(json.dumps(out), flush=True)
+
+
+def bench_flat(args, ctx, tf32_peak):
+    """C1 / C2 / C3 / tiny: one index of fixed size, list-sharded over the ranks (strong scaling)"""
+    torch, b2, dist = ctx["torch"], ctx["b2"], ctx["dist"]
+    rank, world, local, dev = ctx["rank"], ctx["world"], ctx["local"], ctx["dev"]
     w = WORKLOADS[args.workload]
-    d, nlist, metric, nq, k = w["d"], w["nlist"], w["metric"], w["nq"], w["k"]
+    d, nlist, metric, nq, k, nb = w["d"], w["nlist"], w["metric"], w["nq"], w["k"], w["nb"]
     t_setup = time.perf_counter()
     xb, xq, cent = setup_data(torch, w, dev)
     if world > 1:
@@ -417,18 +449,20 @@ def run_b200(args):
         # run differs in the last bits, which would make list ownership inconsistent across shards)
         dist.broadcast(cent, src=0)
 
-    # ---- index: this rank's list range ----------------------------------------------------------
-    if world > 1:
-        index = b2.IndexShardsIVFFlat(d, nlist, metric, device=local)
-        g = index.local
-    else:
-        index = g = b2.IndexIVFFlat(d, nlist, metric, device=local)
+    # ---- index: rank r of the list-sharded index (world 1: the plain index behind it) ------------
+    index = b2.IndexShardsIVFFlat(d, nlist, metric, device=local, rank=rank, world=world)
+    g = index.local
+    index.set_stream(torch.cuda.current_stream().cuda_stream)
     index.set_centroids(cent)
-    g.set_stream(torch.cuda.current_stream().cuda_stream)
     t0 = time.perf_counter()
-    index.add_with_ids(xb, None)
+    # every rank brings ITS slice of the base; the library quantizes it there and sends each
+    # vector to the rank that owns its list (ids = positions in the whole base)
+    lo_v, hi_v = rank * nb // world, (rank + 1) * nb // world
+    ids = torch.arange(lo_v, hi_v, device=dev, dtype=torch.int64)
+    index.add_with_ids(xb[lo_v:hi_v], ids)
     torch.cuda.synchronize()
     t_add = time.perf_counter() - t0
+    del ids
 
     # ---- recall sweep on a query subset (untimed) -----------------------------------------------
     ngt = min(args.gt_queries, nq)
@@ -437,6 +471,7 @@ def run_b200(args):
     for p in w["nprobes"]:
         index.nprobe = p
         _, I = index.search(xq[:ngt].contiguous(), k)
+        torch.cuda.synchronize()
         sweep.append((p, recall_at_k(I.cpu().numpy(), gt)))
         if sweep[-1][1] >= 0.999 and not args.nprobe:
             break
@@ -445,27 +480,31 @@ def run_b200(args):
     recall = dict(sweep).get(nprobe)
     if recall is None:
         _, I = index.search(xq[:ngt].contiguous(), k)
+        torch.cuda.synchronize()
         recall = recall_at_k(I.cpu().numpy(), gt)
-    if world == 1:
-        del xb  # the index holds the vectors; keep HBM for scratch
-    # distinct inverted lists the batch probes on THIS rank, in rows: what a list-major scan must
-    # stream from HBM once per step (the physical lower bound the roofline is taken against)
-    _, Iq_all = g.quantize(xq, nprobe)
-    uniq = torch.unique(Iq_all.reshape(-1))
-    uniq = uniq[uniq >= 0].cpu().numpy()
-    lo_l, hi_l = (index.list_lo, index.list_hi) if world > 1 else (0, nlist)
-    unique_rows = int(sum(g.get_list_size(int(l)) for l in uniq if lo_l <= l < hi_l))
-    del Iq_all
+    unique_rows = unique_probed_rows(torch, g, xq, nprobe, index.list_lo, index.list_hi)
+    # N > 1: the table one GPU returns for the same index, kept for parity_vs_single (C2 fits)
+    single_ref = None
+    if world > 1 and rank == 0:
+        sg = b2.IndexIVFFlat(d, nlist, metric, device=local)
+        sg.set_centroids(cent)
+        sg.add_with_ids(xb, torch.arange(nb, device=dev, dtype=torch.int64))
+        sg.nprobe = nprobe
+        Ds, Is = sg.search(xq, k)
+        torch.cuda.synchronize()
+        single_ref = (Ds.cpu().numpy(), Is.cpu().numpy())
+        del sg, Ds, Is
+    del xb
+    torch.cuda.empty_cache()
     t_setup = time.perf_counter() - t_setup
 
     # ---- timed region 1: device-resident ---------------------------------------------------------
     Dd = torch.empty((nq, k), dtype=torch.float32, device=dev)
     Id = torch.empty((nq, k), dtype=torch.int64, device=dev)
+    root = 0 if world > 1 else None
 
     def step_device():
-        if world > 1:
-            return index.search(xq, k, broadcast_from=0)
-        return index.search(xq, k, D=Dd, I=Id)
+        index.search(xq, k, D=Dd, I=Id, broadcast_from=root)
 
     def barrier():
         if world > 1:
@@ -474,8 +513,9 @@ def run_b200(args):
 
     for _ in range(max(args.warmup, 3)):
         step_device()
+    barrier()
     g.reset_stats()
-    scan_ms, coarse_ms, total_ms, sel_ms, plan_ms = [], [], [], [], []
+    index.reset_phase_times()
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
@@ -485,18 +525,17 @@ def run_b200(args):
     torch.cuda.profiler.start()  # ncu --profile-from-start off sees only the timed steps
     e0.record()
     for _ in range(args.steps):
-        step_device()
-        t = g.last_timings()
-        scan_ms.append(t["scan"])
-        coarse_ms.append(t["coarse"])
-        sel_ms.append(t["select"])
-        plan_ms.append(t["plan"])
-        total_ms.append(t["total"])
+        step_device()  # all-device call: enqueued, no host synchronization between steps
     e1.record()
     barrier()
     torch.cuda.profiler.stop()
     launches = b2.kernel_launches() - launches0
     ms = e0.elapsed_time(e1)
+    # stage events were recorded by the library on its launch stream inside the timed region
+    ncalls, sums = g.stage_time_sums()
+    stage = {s: sums[s] / max(ncalls, 1) for s in sums}
+    _, phases = index.phase_time_sums()
+    phase = {s: phases[s] / float(args.steps) for s in phases} if world > 1 else None
     st = g.get_stats()
     ndis_per_step = st.ndis / float(args.steps)
 
@@ -506,20 +545,11 @@ def run_b200(args):
     D_h = torch.empty((nq, k), dtype=torch.float32, pin_memory=True)
     I_h = torch.empty((nq, k), dtype=torch.int64, pin_memory=True)
     xq_np, D_np, I_np = xq_h.numpy(), D_h.numpy(), I_h.numpy()
-    xq_stage = torch.empty_like(xq)
 
     def step_host():
-        if world > 1:
-            # rank 0 owns the host queries: H2D there, broadcast over NVLink, D2H of the merged table
-            if rank == 0:
-                xq_stage.copy_(xq_h, non_blocking=True)
-            Dm, Im = index.search(xq_stage, k, broadcast_from=0)
-            if rank == 0:
-                D_h.copy_(Dm, non_blocking=True)
-                I_h.copy_(Im, non_blocking=True)
-                torch.cuda.current_stream().synchronize()
-        else:
-            g.search(xq_np, k, D=D_np, I=I_np)
+        # rank 0 owns the host queries: the call copies them to its device, broadcasts them over
+        # NVLink, and every rank's call ends with the merged table in ITS host buffers
+        index.search(xq_np, k, D=D_np, I=I_np, broadcast_from=root)
 
     for _ in range(max(args.warmup, 3)):
         step_host()
@@ -535,18 +565,31 @@ def run_b200(args):
     ms_e2e = max(h0.elapsed_time(h1), 0.0)
     clocks = sampler.stop() if rank == 0 else None
 
+    # per-rank figures to rank 0
+    mine = {"scan_ms": stage["scan"], "unique_rows": unique_rows, "ndis": ndis_per_step,
+            "launches": float(launches), "stage": stage}
     if world > 1:
         tt = torch.tensor([ms, ms_e2e], dtype=torch.float64, device=dev)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         ms, ms_e2e = tt.tolist()
-        nd = torch.tensor([ndis_per_step, float(launches)], dtype=torch.float64, device=dev)
-        dist.all_reduce(nd, op=dist.ReduceOp.SUM)
-        ndis_total, launches_total = nd.tolist()
+        per_rank = [None] * world
+        dist.all_gather_object(per_rank, mine)
     else:
-        ndis_total, launches_total = ndis_per_step, float(launches)
+        per_rank = [mine]
 
-    # ---- CPU baseline on rank 0 at N = 1 ----------------------------------------------------------
-    cpu = None
+    # ---- N > 1: the reference's own multi-GPU assertion (faiss/gpu/test/test_multi_gpu.py:88-95)
+    parity_vs_single = None
+    if single_ref is not None:
+        Ds, Is = single_ref
+        Dm, Im = Dd.cpu().numpy(), Id.cpu().numpy()
+        neq = Is != Im
+        parity_vs_single = {"queries": int(nq), "ids_equal": bool(not neq.any()),
+                            "distances_bit_equal": bool(np.array_equal(Ds, Dm)),
+                            "differing_slots": int(neq.sum()),
+                            "differing_slots_at_exact_ties": int((Ds[neq] == Dm[neq]).sum())}
+
+    # ---- CPU reference on rank 0: baseline timing (N = 1) and parity of the timed configuration
+    cpu, parity = None, None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cent_np = cent.cpu().numpy()
         lists = ((l,) + tuple(reversed(g.get_list(l))) for l in range(nlist))
@@ -556,27 +599,31 @@ def run_b200(args):
             po.ref_set_threads(threads)
         qps_cpu, ns, dt, (Dc, Ic) = time_cpu_sample(idx, kind, po, xq_np, k, nprobe, threads,
                                                     args.cpu_seconds)
-        # parity of the timed configuration against the checker, on the sample
-        sys.path.insert(0, os.path.join(ROOT, "tests"))
-        from helpers import compare_knn
-        r = compare_knn(Dc, Ic, D_np[:ns], I_np[:ns])
         cpu = {"value": qps_cpu, "unit": "queries/s", "cores": threads, "kind": kind,
-               "sample": "%d of the %d queries, same index and nprobe, %.1f s" % (ns, nq, dt),
-               "parity_vs_gpu": {"exact_id_rate": r["exact_id_rate"],
-                                 "unexplained": r["unexplained"], "bad_dist": r["bad_dist"]}}
+               "sample": "%d of the %d queries, same index and nprobe, %.1f s" % (ns, nq, dt)}
+        parity = parity_detail(Dc, Ic, D_np[:ns], I_np[:ns])
+        parity["against"] = "oracle/_ref (the unmodified reference)" if kind == "reference" \
+            else "oracle port"
+        del idx
 
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
+        return None
     peak, peak_src = measured_hbm_peak()
-    scan_s = statistics.mean(scan_ms) / 1e3
-    ref_bytes = 4.0 * d * ndis_per_step  # what the reference streams: every pair its whole list
-    alg_bytes = 4.0 * d * unique_rows    # what a list-major scan must stream: every list once
+    # the scan roofline is per GPU: the slowest rank's launch over the bytes that rank must stream
+    slow = max(per_rank, key=lambda r: r["scan_ms"])
+    scan_s = slow["scan_ms"] / 1e3
+    ndis_all = sum(r["ndis"] for r in per_rank)
+    rows_all = sum(r["unique_rows"] for r in per_rank)
+    ref_bytes = 4.0 * d * ndis_all             # what the reference streams: every pair its list
+    alg_bytes = 4.0 * d * slow["unique_rows"]  # what a list-major scan must stream: a list once
     achieved = alg_bytes / scan_s / 1e9 if scan_s > 0 else 0.0
     traffic = scan_traffic_bytes(args.workload, nprobe) if world == 1 else None
-    tensor_peak = measured_tensor_peak()
-    useful_tflops = 2.0 * d * ndis_per_step / scan_s / 1e12 if scan_s > 0 else 0.0
+    useful_tflops = 2.0 * d * slow["ndis"] / scan_s / 1e12 if scan_s > 0 else 0.0
+    avg_q = ndis_all / max(rows_all, 1)
+    kname = scan_kernel_name(avg_q, d, k)
+    coarse_s = (phase["coarse"] if phase else stage["coarse"]) / 1e3
+    coarse_flops = 2.0 * (nq / float(world)) * nlist * d  # this rank's query slice
+    coarse_tf = coarse_flops / coarse_s / 1e12 if coarse_s > 0 else 0.0
     out = {
         "metric": "QPS @ recall@10>=0.95, IVFFlat",
         "value": nq * args.steps / (ms / 1e3),
@@ -592,34 +639,47 @@ def run_b200(args):
                    "nq_per_step": nq, "recall_at_10": recall,
                    "nprobe_sweep": [[p, round(r, 4)] for p, r in sweep],
                    "recall_queries": ngt,
-                   "parallelism": "list-range shards x%d" % world,
+                   "parallelism": "list-range shards x%d (C++ IndexShardsIVFFlat, NCCL)" % world,
                    "l2_policy": "no flush: every step streams the %.2f GB list slab (>> 126 MB L2)"
-                                % (w["nb"] * d * 4 / 1e9),
-                   "centroids": "k-means niter=10 on 256*nlist points (torch, setup)",
+                                % (nb * d * 4 / 1e9),
+                   "data_generator": "reference SyntheticDataset recipe (contrib/datasets.py:74-111:"
+                                     " 10-d latent -> projection -> sin), torch generators; not the "
+                                     "Gaussian mixture of BASELINE.md section 3",
+                   "centroids": "torch k-means niter=10 on 256*nlist points (setup, both arms)",
                    "setup_s": round(t_setup, 1), "add_s": round(t_add, 2)},
         "e2e": {"value": nq * args.steps / (ms_e2e / 1e3), "unit": "queries/s",
-                "h2d_bytes_per_step": nq * d * 4, "d2h_bytes_per_step": nq * k * 12,
+                "h2d_bytes_per_step": nq * d * 4, "d2h_bytes_per_step": nq * k * 12 * world,
                 "wall_ms_per_step": t_wall * 1e3 / args.steps},
-        "gpu_launches": int(launches_total),
-        "stage_ms": {"coarse": statistics.mean(coarse_ms), "plan": statistics.mean(plan_ms),
-                     "scan": statistics.mean(scan_ms), "select": statistics.mean(sel_ms),
-                     "total": statistics.mean(total_ms)},
-        "roofline": {"kernel": "ivf_scan_tc_kernel (+ ivf_scan_kernel for lists probed by <= 8 "
-                               "queries), one launch each per step",
+        "gpu_launches": int(sum(r["launches"] for r in per_rank)),
+        "stage_ms": stage,
+        "roofline": {"kernel": kname + ", one launch per step",
                      "bound": "hbm", "achieved": achieved,
                      "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                     "traffic_source": ("profiles/scan_traffic.json: ncu --set full capture of the "
+                                        "scan at this workload and nprobe (dram bytes read + "
+                                        "written per launch), not measured in this run")
+                     if traffic is not None else None,
                      "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": alg_bytes,
-                     "unique_rows_per_launch": unique_rows,
-                     "ndis_per_launch": ndis_per_step,
+                     "unique_rows_per_launch": slow["unique_rows"],
+                     "ndis_per_launch": slow["ndis"],
+                     "queries_per_probed_row": avg_q,
+                     "scan_ms": slow["scan_ms"],
                      "reference_streamed_bytes_per_launch": ref_bytes,
                      "reference_streamed_equiv_gbs": ref_bytes / scan_s / 1e9 if scan_s > 0 else 0.0,
                      "tensor": {"useful_tflops": useful_tflops,
-                                "issued_tf32_tflops": 3.0 * useful_tflops,
-                                "tf32_peak_tflops_est": tensor_peak / 2.0,
-                                "frac_issued": 3.0 * useful_tflops / (tensor_peak / 2.0),
-                                "note": "3xTF32: 3 MMAs per useful product; TF32 peak taken as "
-                                        "half the measured dense bf16 peak"},
+                                "mmas_per_useful_product": 3 if "queries-major" in kname else 2,
+                                "tf32_peak_tflops": tf32_peak,
+                                "frac_useful": useful_tflops / tf32_peak,
+                                "note": "3xTF32 split; the peak is a dense cuBLAS TF32 GEMM "
+                                        "(8192^3) timed in this run"},
+                     "coarse": {"kernel": "ivf_scan_tc_kernel over the centroid table (nprobe <= 24)"
+                                          " / ivf_scan_tcr_kernel (above)",
+                                "flops": coarse_flops, "ms": coarse_s * 1e3,
+                                "useful_tflops": coarse_tf, "tf32_peak_tflops": tf32_peak,
+                                "frac_useful": coarse_tf / tf32_peak,
+                                "note": "2*n*nlist*d over the quantizer's event time (queries per "
+                                        "rank = n / world); 3 MMAs issued per useful product"},
                      "note": "algorithmic bytes = 4*d*(rows of the distinct lists the batch probes):"
                              " the scan is list-major, a list is streamed once for ALL the queries "
                              "that probe it (on tensor cores), so this is what must cross HBM; "
@@ -627,11 +687,16 @@ def run_b200(args):
                              "is reference_streamed_bytes_per_launch -- see DESIGN.md section 3"},
         "clocks": clocks,
         "cpu_baseline": cpu,
+        "parity": parity,
     }
     if world > 1:
-        out["config"]["ndis_all_ranks"] = ndis_total
-        dist.destroy_process_group()
-    print(json.dumps(out), flush=True)
+        out["phase_ms"] = phase
+        out["parity_vs_single"] = parity_vs_single
+        out["per_rank"] = [{"scan_ms": r["scan_ms"], "unique_rows": r["unique_rows"],
+                            "scan_gbs": 4.0 * d * r["unique_rows"] / (r["scan_ms"] / 1e3) / 1e9
+                            if r["scan_ms"] > 0 else 0.0} for r in per_rank]
+        out["config"]["ndis_all_ranks"] = ndis_all
+    return out
 
 
 # ------------------------------------------------------------------------------------------------
