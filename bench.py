@@ -700,6 +700,91 @@ def bench_flat(args, ctx, tf32_peak):
 
 
 # ------------------------------------------------------------------------------------------------
+# C4: the 1B-shape config, built in place and list-sharded (weak scaling: fixed work per GPU)
+# ------------------------------------------------------------------------------------------------
+C4_CHUNK = 1 << 22  # vectors per generated chunk (chunk c holds ids [c * C4_CHUNK, ...))
+
+
+def c4_proj(torch, d, dev):
+    g = torch.Generator(device=dev)
+    g.manual_seed(SEED_PROJ)
+    a = torch.rand((D_LATENT, d), generator=g, device=dev, dtype=torch.float32)
+    scale = torch.rand((d,), generator=g, device=dev, dtype=torch.float32) * 4 + 0.1
+    return a * scale[None, :]
+
+
+def c4_chunk(torch, c, n, proj, dev, seed=SEED_BASE):
+    """chunk c of the base set: the same bits on whichever rank generates it"""
+    g = torch.Generator(device=dev)
+    g.manual_seed(seed * 1000003 + c)
+    z = torch.randn((n, D_LATENT), generator=g, device=dev, dtype=torch.float32)
+    return torch.sin(z @ proj)
+
+
+def c4_topk_update(torch, best, xq, x, id0, k):
+    """running exact top-k (L2) of the ground-truth queries against one more chunk"""
+    s = (x * x).sum(1)[None, :] - 2.0 * (xq @ x.T)
+    dd, ii = torch.topk(s, k, dim=1, largest=False)
+    ii = ii + id0
+    if best is None:
+        return dd, ii
+    cd, ci = torch.cat([best[0], dd], 1), torch.cat([best[1], ii], 1)
+    dd, sel = torch.topk(cd, k, dim=1, largest=False)
+    return dd, torch.gather(ci, 1, sel)
+
+
+def c4_build(ctx, d, nlist, nb, proj, xq_gt, k, niter=2, pts_per_centroid=40):
+    """sharded index over nb vectors: train on rank 0, every rank generates, quantizes and ships
+    its chunks; returns (index, exact ground truth of xq_gt, timings)"""
+    torch, b2, dist = ctx["torch"], ctx["b2"], ctx["dist"]
+    rank, world, local, dev = ctx["rank"], ctx["world"], ctx["local"], ctx["dev"]
+    t0 = time.perf_counter()
+    sh = b2.IndexShardsIVFFlat(d, nlist, METRIC_L2, device=local, rank=rank, world=world)
+    sh.set_stream(torch.cuda.current_stream().cuda_stream)
+    sh.local.set_option("cp_niter", niter)
+    sh.local.set_option("cp_max_points_per_centroid", pts_per_centroid)
+    xt = None
+    if rank == 0:
+        nt = min(nb, pts_per_centroid * nlist)
+        xt = torch.cat([c4_chunk(torch, c, min(C4_CHUNK, nt - c * C4_CHUNK), proj, dev, SEED_TRAIN)
+                        for c in range((nt + C4_CHUNK - 1) // C4_CHUNK)])
+    sh.train(xt, root=0)
+    del xt
+    torch.cuda.empty_cache()
+    t1 = time.perf_counter()
+    nchunks = (nb + C4_CHUNK - 1) // C4_CHUNK
+    rounds = (nchunks + world - 1) // world
+    best = None
+    for r in range(rounds):
+        c = r * world + rank
+        ni = max(0, min(C4_CHUNK, nb - c * C4_CHUNK)) if c < nchunks else 0
+        if ni > 0:
+            x = c4_chunk(torch, c, ni, proj, dev)
+            ids = torch.arange(c * C4_CHUNK, c * C4_CHUNK + ni, device=dev, dtype=torch.int64)
+            best = c4_topk_update(torch, best, xq_gt, x, c * C4_CHUNK, k)
+        else:
+            x = torch.empty((0, d), device=dev, dtype=torch.float32)
+            ids = torch.empty((0,), device=dev, dtype=torch.int64)
+        sh.add_with_ids(x, ids)
+        del x, ids
+    torch.cuda.synchronize()
+    torch.cuda.empty_cache()
+    t2 = time.perf_counter()
+    if best is None:
+        best = (torch.full((xq_gt.shape[0], k), float("inf"), device=dev),
+                torch.full((xq_gt.shape[0], k), -1, device=dev, dtype=torch.int64))
+    if world > 1:
+        gd = [torch.empty_like(best[0]) for _ in range(world)]
+        gi = [torch.empty_like(best[1]) for _ in range(world)]
+        dist.all_gather(gd, best[0].contiguous())
+        dist.all_gather(gi, best[1].contiguous())
+        cd, ci = torch.cat(gd, 1), torch.cat(gi, 1)
+        dd, sel = torch.topk(cd, k, dim=1, largest=False)
+        best = (dd, torch.gather(ci, 1, sel))
+    return sh, best[1].cpu().numpy(), {"train_s": round(t1 - t0, 1), "add_s": round(t2 - t1, 1)}
+
+
+# ------------------------------------------------------------------------------------------------
 def run_reference(args):
     """The reference's own CPU IndexIVFFlat::search (oracle/_ref when present) on the host cores."""
     rank, world, local = dist_env()
