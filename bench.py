@@ -784,6 +784,77 @@ def c4_build(ctx, d, nlist, nb, proj, xq_gt, k, niter=2, pts_per_centroid=40):
     return sh, best[1].cpu().numpy(), {"train_s": round(t1 - t0, 1), "add_s": round(t2 - t1, 1)}
 
 
+def c4_slice_parity(args, ctx, proj, xq, k):
+    """A slice of the same data (first `--c4-slice` vectors, nlist = slice / 3815) searched three
+    ways: by the list-sharded index over all the ranks, by one GPU, and by the compiled reference on
+    the host cores -- the reference's multi-GPU assertion (faiss/gpu/test/test_multi_gpu.py:88-95)
+    plus CPU parity and the CPU baseline of BASELINE.md section 4 for C4."""
+    torch, b2, dist = ctx["torch"], ctx["b2"], ctx["dist"]
+    rank, world, local, dev = ctx["rank"], ctx["world"], ctx["local"], ctx["dev"]
+    d, nb = 96, int(args.c4_slice)
+    nlist = max(64, int(round(nb / 3815.0)))
+    ngt = min(500, xq.shape[0])
+    sh, gt, tb = c4_build(ctx, d, nlist, nb, proj, xq[:ngt].contiguous(), k)
+    sweep, nprobe = [], None
+    for p in [1, 2, 4, 8, 16, 24, 32, 48, 64, 96, 128]:
+        sh.nprobe = p
+        _, I = sh.search(xq[:ngt].contiguous(), k)
+        torch.cuda.synchronize()
+        sweep.append((p, recall_at_k(I.cpu().numpy(), gt)))
+        if sweep[-1][1] >= 0.95:
+            nprobe = p
+            break
+    nprobe = nprobe or sweep[-1][0]
+    sh.nprobe = nprobe
+    Dm, Im = sh.search(xq, k, broadcast_from=0 if world > 1 else None)
+    torch.cuda.synchronize()
+    out = None
+    if rank == 0:
+        Dm, Im = Dm.cpu().numpy(), Im.cpu().numpy()
+        cent = sh.local.get_centroids()
+        single = b2.IndexIVFFlat(d, nlist, METRIC_L2, device=local)
+        single.set_centroids(cent)
+        for c in range((nb + C4_CHUNK - 1) // C4_CHUNK):
+            ni = min(C4_CHUNK, nb - c * C4_CHUNK)
+            single.add_with_ids(c4_chunk(torch, c, ni, proj, dev),
+                                torch.arange(c * C4_CHUNK, c * C4_CHUNK + ni, device=dev,
+                                             dtype=torch.int64))
+        single.nprobe = nprobe
+        Ds, Is = single.search(xq, k)
+        torch.cuda.synchronize()
+        Ds, Is = Ds.cpu().numpy(), Is.cpu().numpy()
+        neq = Is != Im
+        out = {"workload": "C4 slice: %d x 96 L2, nlist %d, %d queries" % (nb, nlist, xq.shape[0]),
+               "nprobe": nprobe, "recall_at_10": dict(sweep)[nprobe],
+               "nprobe_sweep": [[p, round(r, 4)] for p, r in sweep], "build": tb,
+               "sharded_vs_single": {"ids_equal": bool(not neq.any()),
+                                     "distances_bit_equal": bool(np.array_equal(Ds, Dm)),
+                                     "differing_slots": int(neq.sum()),
+                                     "differing_slots_at_exact_ties":
+                                         int((Ds[neq] == Dm[neq]).sum())}}
+        if not args.no_cpu_baseline:
+            w = dict(d=d, nlist=nlist, metric=METRIC_L2)
+            lists = ((l,) + tuple(reversed(single.get_list(l))) for l in range(nlist))
+            threads = os.cpu_count() or 1
+            idx, kind, po = make_cpu_index(w, cent, lists)
+            if kind == "reference":
+                po.ref_set_threads(threads)
+            xq_np = xq.cpu().numpy()
+            qps_cpu, ns, dt, (Dc, Ic) = time_cpu_sample(idx, kind, po, xq_np, k, nprobe, threads,
+                                                        args.cpu_seconds)
+            out["cpu_baseline"] = {"value": qps_cpu, "unit": "queries/s", "cores": threads,
+                                   "kind": kind, "sample": "%d of the %d queries, %.1f s"
+                                                           % (ns, xq_np.shape[0], dt)}
+            out["sharded_vs_reference"] = parity_detail(Dc, Ic, Dm[:ns], Im[:ns])
+            del idx
+        del single
+    del sh
+    torch.cuda.empty_cache()
+    if world > 1:
+        dist.barrier()
+    return out
+
+
 # ------------------------------------------------------------------------------------------------
 def run_reference(args):
     """The reference's own CPU IndexIVFFlat::search (oracle/_ref when present) on the host cores."""
