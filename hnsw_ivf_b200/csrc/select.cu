@@ -467,9 +467,9 @@ __global__ void __launch_bounds__(256, 4) select_warp_kernel(const SelectArgs a)
 }
 
 // One warp per query: merge nshard sorted (n,k) tables by walking the shard heads. Same output as
-// merge_knn_results (faiss/utils/Heap.cpp:158-232): equal distances come out lower shard first
-// (the reference's heap over the shard heads compares (distance, shard), :186-225), exactly as
-// merge_shards_rank_kernel below orders them.
+// merge_knn_results (faiss/utils/Heap.cpp:158-232): equal distances come out in shard order (the
+// reference's heap over the shard heads compares (distance, shard), :186-225: lower shard first
+// for L2, higher first for inner product), exactly as merge_shards_rank_kernel below orders them.
 __global__ void merge_shards_kernel(int metric, int nshard, int n, int k, const float* all_dis,
                                     const int64_t* all_ids, float* out_dis, int64_t* out_ids) {
     const int q = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -497,8 +497,9 @@ __global__ void merge_shards_kernel(int metric, int nshard, int n, int k, const 
                     bool better;
                     if (best_s < 0)
                         better = true;
-                    else // equal distances: the lower shard (seen first) stays
-                        better = l2 ? (dv < best) : (dv > best);
+                    else // equal distances: L2 keeps the lower shard (seen first), inner
+                         // product takes the higher one (CMax::cmp2)
+                        better = l2 ? (dv < best) : (dv >= best);
                     if (better) {
                         best = dv;
                         best_id = id;
@@ -520,7 +521,7 @@ __global__ void merge_shards_kernel(int metric, int nshard, int n, int k, const 
             else if (od != best)
                 take = l2 ? (od < best) : (od > best);
             else
-                take = os < best_s;
+                take = l2 ? os < best_s : os > best_s;
             if (take) {
                 best = od;
                 best_id = oid;
@@ -596,13 +597,16 @@ cudaError_t launch_select(const SelectArgs& a, cudaStream_t st) {
 constexpr int kMergeRankMax = 512;
 constexpr int kMergeRankWarps = 4;
 
-// equal distances: the lower shard number first, as the reference's heap over the shard heads
-// orders them (cmp2 on (distance, shard), faiss/utils/Heap.cpp:186-225); ids take no part, so the
-// order inside a shard's own run of equal distances is whatever the shard delivered
+// equal distances: ordered by shard number as the reference's heap over the shard heads orders
+// them (cmp2 on (distance, shard), faiss/utils/Heap.cpp:186-225): lower shard first for L2, higher
+// shard first for inner product; ids take no part, so the order inside a shard's own run of equal
+// distances is whatever the shard delivered
 __device__ __forceinline__ bool merge_before(bool l2, float da, int sa, float db, int sb) {
     if (da != db)
         return l2 ? (da < db) : (da > db);
-    return sa < sb;
+    // CMin::cmp2 (L2) pops the LOWER shard first, CMax::cmp2 (inner product) the HIGHER one
+    // (faiss/utils/ordered_key_value.h:51-53,74-76 applied to (distance, shard))
+    return l2 ? sa < sb : sa > sb;
 }
 
 __global__ void __launch_bounds__(kMergeRankWarps * 32)
