@@ -855,6 +855,113 @@ def c4_slice_parity(args, ctx, proj, xq, k):
     return out
 
 
+def bench_c4(args, ctx, tf32_peak, headline):
+    """BASELINE.json configs[3], weak-scaling form. Returns the c4 object (rank 0; None elsewhere),
+    or the whole JSON line when it is the headline."""
+    torch, b2, dist = ctx["torch"], ctx["b2"], ctx["dist"]
+    rank, world, local, dev = ctx["rank"], ctx["world"], ctx["local"], ctx["dev"]
+    w = WORKLOADS["C4"]
+    d, k, nq = w["d"], w["k"], w["nq"]
+    rows = int(args.c4_rows_per_gpu or w["nb"])
+    nb = rows * world
+    nlist = max(64, int(round(w["nlist"] * (rows / float(w["nb"]))))) * world
+    steps = args.steps if headline else args.c4_steps
+    t_all = time.perf_counter()
+    proj = c4_proj(torch, d, dev)
+    gq = torch.Generator(device=dev)
+    gq.manual_seed(SEED_QUERY)
+    xq = torch.sin(torch.randn((nq, D_LATENT), generator=gq, device=dev, dtype=torch.float32) @ proj)
+    ngt = min(500, nq)
+    sh, gt, tb = c4_build(ctx, d, nlist, nb, proj, xq[:ngt].contiguous(), k)
+    g = sh.local
+    sweep, nprobe = [], (args.c4_nprobe or (args.nprobe if headline else 0))
+    if not nprobe:
+        for p in w["nprobes"]:
+            sh.nprobe = p
+            _, I = sh.search(xq[:ngt].contiguous(), k)
+            torch.cuda.synchronize()
+            sweep.append((p, recall_at_k(I.cpu().numpy(), gt)))
+            if sweep[-1][1] >= 0.95:
+                break
+        nprobe = pick_nprobe(sweep, 0.95)
+    sh.nprobe = nprobe
+    _, I = sh.search(xq[:ngt].contiguous(), k)
+    torch.cuda.synchronize()
+    recall = recall_at_k(I.cpu().numpy(), gt)
+    unique_rows = unique_probed_rows(torch, g, xq, nprobe, sh.list_lo, sh.list_hi)
+
+    Dd = torch.empty((nq, k), dtype=torch.float32, device=dev)
+    Id = torch.empty((nq, k), dtype=torch.int64, device=dev)
+    root = 0 if world > 1 else None
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(3):
+        sh.search(xq, k, D=Dd, I=Id, broadcast_from=root)
+    barrier()
+    g.reset_stats()
+    sh.reset_phase_times()
+    sampler = ClockSampler(local)
+    if rank == 0 and headline:
+        sampler.start()
+    launches0 = b2.kernel_launches()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for _ in range(steps):
+        sh.search(xq, k, D=Dd, I=Id, broadcast_from=root)
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = b2.kernel_launches() - launches0
+    ncalls, sums = g.stage_time_sums()
+    stage = {s: sums[s] / max(ncalls, 1) for s in sums}
+    _, phases = sh.phase_time_sums()
+    phase = {s: phases[s] / float(steps) for s in phases} if world > 1 else None
+    ndis = g.get_stats().ndis / float(steps)
+
+    # end to end with host buffers (rank 0's queries; every rank's call returns the merged table)
+    ms_e2e, t_wall = 0.0, 0.0
+    if headline:
+        xq_h = torch.empty((nq, d), dtype=torch.float32, pin_memory=True)
+        xq_h.copy_(xq)
+        D_h = torch.empty((nq, k), dtype=torch.float32, pin_memory=True)
+        I_h = torch.empty((nq, k), dtype=torch.int64, pin_memory=True)
+        for _ in range(3):
+            sh.search(xq_h.numpy(), k, D=D_h.numpy(), I=I_h.numpy(), broadcast_from=root)
+        barrier()
+        h0, h1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t_wall = time.perf_counter()
+        h0.record()
+        for _ in range(steps):
+            sh.search(xq_h.numpy(), k, D=D_h.numpy(), I=I_h.numpy(), broadcast_from=root)
+        h1.record()
+        barrier()
+        t_wall = time.perf_counter() - t_wall
+        ms_e2e = h0.elapsed_time(h1)
+    clocks = sampler.stop() if (rank == 0 and headline) else None
+
+    mine = {"scan_ms": stage["scan"], "unique_rows": unique_rows, "ndis": ndis,
+            "launches": float(launches), "stage": stage, "rows": int(g.list_sizes().sum())}
+    if world > 1:
+        tt = torch.tensor([ms, ms_e2e], dtype=torch.float64, device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms, ms_e2e = tt.tolist()
+        per_rank = [None] * world
+        dist.all_gather_object(per_rank, mine)
+    else:
+        per_rank = [mine]
+    del sh, g, Dd, Id
+    torch.cuda.empty_cache()
+    sl = c4_slice_parity(args, ctx, proj, xq, k) if args.c4_slice > 0 else None
+    if rank != 0:
+        return None
+    return None  # (part 2 follows)
+
+
 # ------------------------------------------------------------------------------------------------
 def run_reference(args):
     """The reference's own CPU IndexIVFFlat::search (oracle/_ref when present) on the host cores."""
