@@ -959,7 +959,60 @@ def bench_c4(args, ctx, tf32_peak, headline):
     sl = c4_slice_parity(args, ctx, proj, xq, k) if args.c4_slice > 0 else None
     if rank != 0:
         return None
-    return None  # (part 2 follows)
+    peak, peak_src = measured_hbm_peak()
+    ranks = []
+    for r in per_rank:
+        gbs = 4.0 * d * r["unique_rows"] / (r["scan_ms"] / 1e3) / 1e9 if r["scan_ms"] > 0 else 0.0
+        ranks.append({"rows_stored": r["rows"], "scan_ms": r["scan_ms"],
+                      "unique_rows_per_launch": r["unique_rows"], "scan_gbs": gbs,
+                      "frac": gbs / peak, "ndis_per_launch": r["ndis"],
+                      "queries_per_probed_row": r["ndis"] / max(r["unique_rows"], 1)})
+    slow = max(ranks, key=lambda r: r["scan_ms"])
+    avg_q = slow["queries_per_probed_row"]
+    coarse_ms = phase["coarse"] if phase else stage["coarse"]
+    coarse_flops = 2.0 * (nq / float(world)) * nlist * d
+    c4 = {"workload": "C4 (weak scaling): %d x 96 fp32 L2, nlist %d, %d vectors and %d lists per "
+                      "GPU over %d GPU(s), 10k-query batch" % (nb, nlist, rows, nlist // world,
+                                                               world),
+          "scaling": "weak", "n_gpus": world, "nb": nb, "nlist": nlist, "nprobe": nprobe,
+          "recall_at_10": recall, "recall_queries": ngt,
+          "recall_ground_truth": "exact brute force over all %d vectors (torch fp32, per chunk)" % nb,
+          "nprobe_sweep": [[p, round(r, 4)] for p, r in sweep],
+          "qps": nq * steps / (ms / 1e3), "ms_per_step": ms / steps, "steps": steps,
+          "stage_ms_rank0": stage, "phase_ms_rank0": phase, "build": tb,
+          "scan": {"kernel": scan_kernel_name(avg_q, d, k), "per_rank": ranks,
+                   "min_frac_of_hbm_peak": min(r["frac"] for r in ranks),
+                   "peak_gbs": peak, "peak_source": peak_src},
+          "coarse": {"flops_per_rank": coarse_flops, "ms": coarse_ms,
+                     "useful_tflops": coarse_flops / (coarse_ms / 1e3) / 1e12 if coarse_ms > 0 else 0,
+                     "tf32_peak_tflops": tf32_peak},
+          "gpu_launches": int(sum(r["launches"] for r in per_rank)),
+          "slice": sl, "total_s": round(time.perf_counter() - t_all, 1)}
+    if not headline:
+        return c4
+    out = {"metric": "QPS @ recall@10>=0.95, IVFFlat", "value": c4["qps"], "unit": "queries/s",
+           "n_gpus": world, "steps": steps, "warmup": 3, "ms_per_step": c4["ms_per_step"],
+           "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+           "data": "synthetic",
+           "config": {"workload": c4["workload"], "nprobe": nprobe, "k": k, "nq_per_step": nq,
+                      "recall_at_10": recall, "nprobe_sweep": c4["nprobe_sweep"],
+                      "parallelism": "list-range shards x%d (C++ IndexShardsIVFFlat, NCCL)" % world,
+                      "l2_policy": "no flush: every step streams %.1f GB of lists per GPU"
+                                   % (slow["unique_rows_per_launch"] * d * 4 / 1e9)},
+           "e2e": {"value": nq * steps / (ms_e2e / 1e3), "unit": "queries/s",
+                   "h2d_bytes_per_step": nq * d * 4, "d2h_bytes_per_step": nq * k * 12 * world,
+                   "wall_ms_per_step": t_wall * 1e3 / steps},
+           "gpu_launches": c4["gpu_launches"], "stage_ms": stage, "phase_ms": phase,
+           "roofline": {"kernel": c4["scan"]["kernel"] + ", one launch per step per GPU",
+                        "bound": "hbm", "achieved": slow["scan_gbs"], "peak": peak, "unit": "GB/s",
+                        "frac": slow["frac"], "traffic": None, "peak_source": peak_src,
+                        "algorithmic_bytes_per_launch": 4.0 * d * slow["unique_rows_per_launch"],
+                        "scan_ms": slow["scan_ms"], "per_rank": ranks, "coarse": c4["coarse"]},
+           "clocks": clocks,
+           "cpu_baseline": (sl or {}).get("cpu_baseline"),
+           "parity": (sl or {}).get("sharded_vs_reference"),
+           "c4": c4}
+    return out
 
 
 # ------------------------------------------------------------------------------------------------
