@@ -401,7 +401,10 @@ void IndexIVFFlatB200::set_centroids_(const float* c) {
     m.h_centroids.resize(nfl);
     const float* cd = c;
     if (is_device_pointer(c)) {
-        CUDA_CHECK(cudaMemcpy(m.h_centroids.data(), c, nfl * sizeof(float), cudaMemcpyDeviceToHost));
+        // (on the handle's stream: device inputs are ordered with it, not with the legacy stream)
+        CUDA_CHECK(cudaMemcpyAsync(m.h_centroids.data(), c, nfl * sizeof(float),
+                                   cudaMemcpyDeviceToHost, m.stream));
+        CUDA_CHECK(cudaStreamSynchronize(m.stream));
     } else {
         std::memcpy(m.h_centroids.data(), c, nfl * sizeof(float));
         m.dev_x.reserve(nfl * sizeof(float));
@@ -1403,10 +1406,11 @@ void IndexIVFFlatB200::add_core_(int64_t n, const float* x, const int64_t* xids,
     // pass 1: list number of every vector, on the host
     std::vector<int64_t> h_assign((size_t)n);
     if (assign) {
-        if (a_dev)
-            CUDA_CHECK(cudaMemcpy(h_assign.data(), assign, (size_t)n * sizeof(int64_t),
-                                  cudaMemcpyDeviceToHost));
-        else
+        if (a_dev) {
+            CUDA_CHECK(cudaMemcpyAsync(h_assign.data(), assign, (size_t)n * sizeof(int64_t),
+                                       cudaMemcpyDeviceToHost, st));
+            CUDA_CHECK(cudaStreamSynchronize(st));
+        } else
             std::memcpy(h_assign.data(), assign, (size_t)n * sizeof(int64_t));
     } else {
         for (int64_t i0 = 0; i0 < n; i0 += chunk) {
@@ -1557,7 +1561,11 @@ void IndexIVFFlatB200::reserve_lists(const int64_t* sizes) {
     B200_THROW_IF_NOT_MSG(sizes != nullptr, "null sizes");
     std::vector<int64_t> hs(nlist);
     if (is_device_pointer(sizes))
-        CUDA_CHECK(cudaMemcpy(hs.data(), sizes, nlist * sizeof(int64_t), cudaMemcpyDeviceToHost));
+    {
+        CUDA_CHECK(cudaMemcpyAsync(hs.data(), sizes, nlist * sizeof(int64_t),
+                                   cudaMemcpyDeviceToHost, m.stream));
+        CUDA_CHECK(cudaStreamSynchronize(m.stream));
+    }
     else
         std::memcpy(hs.data(), sizes, nlist * sizeof(int64_t));
     std::vector<uint32_t> cap(m.h_cap);
@@ -1904,15 +1912,17 @@ void IndexIVFFlatB200::train(int64_t n, const float* x) {
                 CUDA_CHECK(launch_gather_by_index(x, didx.as<int64_t>(), nx, d, xt.as<float>(), st));
                 CUDA_CHECK(cudaStreamSynchronize(st));
             } else if (pick.empty()) {
-                CUDA_CHECK(cudaMemcpy(xt.p, x, (size_t)nx * dd * sizeof(float),
-                                      cudaMemcpyHostToDevice));
+                CUDA_CHECK(cudaMemcpyAsync(xt.p, x, (size_t)nx * dd * sizeof(float),
+                                           cudaMemcpyHostToDevice, st));
+                CUDA_CHECK(cudaStreamSynchronize(st));
             } else {
                 std::vector<float> hx((size_t)nx * dd);
                 for (int64_t i = 0; i < nx; ++i)
                     std::memcpy(hx.data() + (size_t)i * dd, x + (size_t)pick[(size_t)i] * dd,
                                 dd * sizeof(float));
-                CUDA_CHECK(cudaMemcpy(xt.p, hx.data(), hx.size() * sizeof(float),
-                                      cudaMemcpyHostToDevice));
+                CUDA_CHECK(cudaMemcpyAsync(xt.p, hx.data(), hx.size() * sizeof(float),
+                                           cudaMemcpyHostToDevice, st));
+                CUDA_CHECK(cudaStreamSynchronize(st));
             }
             xt_dev = xt.as<float>();
         }
