@@ -73,6 +73,8 @@ SYMBOLS = [
     ("b200_IndexIVFFlat_search_preassigned", C.c_int,
      [_vp, C.c_int64, _f32p, C.c_int64, _i64p, _f32p, _f32p, _i64p, C.c_int]),
     ("b200_IndexIVFFlat_quantize", C.c_int, [_vp, C.c_int64, _f32p, C.c_int64, _f32p, _i64p]),
+    ("b200_IndexIVFFlat_quantize_noalloc", C.c_int,
+     [_vp, C.c_int64, _f32p, C.c_int64, _f32p, _i64p]),
     ("b200_IndexIVFFlat_get_stats", None, [_vp, C.POINTER(IndexIVFStats)]),
     ("b200_IndexIVFFlat_reset_stats", None, [_vp]),
     ("b200_IndexIVFFlat_last_timings", None, [_vp, C.POINTER(C.c_double)]),
@@ -554,6 +556,18 @@ class IndexIVFFlat:
         ki, pi = _ptr(Iq, np.int64, (n, nprobe), "Iq")
         self._order_with_torch(kx, kd, ki)
         self._check(self._lib.b200_IndexIVFFlat_quantize(self._h, n, px, nprobe, pd, pi))
+        self._settle(kx, kd, ki)
+        return kd, ki
+
+    def quantize_noalloc(self, x, nprobe, Dq, Iq):
+        """quantize() without any device allocation (b200ivf_c.h): CUDA tensors only, the caller
+        supplies the outputs; n <= 4096, nprobe <= 64. Enqueued on the handle's stream."""
+        kx, px = _ptr(x, np.float32, None, "x")
+        n = kx.shape[0]
+        kd, pd = _ptr(Dq, np.float32, (n, nprobe), "Dq")
+        ki, pi = _ptr(Iq, np.int64, (n, nprobe), "Iq")
+        self._order_with_torch(kx, kd, ki)
+        self._check(self._lib.b200_IndexIVFFlat_quantize_noalloc(self._h, n, px, nprobe, pd, pi))
         self._settle(kx, kd, ki)
         return kd, ki
 

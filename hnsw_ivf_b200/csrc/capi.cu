@@ -177,6 +177,11 @@ int b200_IndexIVFFlat_quantize(const B200IndexIVFFlat* index, b200_idx_t n, cons
     return guarded([&] { H(index)->quantize(n, x, nprobe, centroid_dis, assign); });
 }
 
+int b200_IndexIVFFlat_quantize_noalloc(const B200IndexIVFFlat* index, b200_idx_t n, const float* x,
+                                       b200_idx_t nprobe, float* centroid_dis, b200_idx_t* assign) {
+    return guarded([&] { H(index)->quantize_noalloc(n, x, nprobe, centroid_dis, assign); });
+}
+
 void b200_IndexIVFFlat_get_stats(const B200IndexIVFFlat* index, B200IndexIVFStats* stats) {
     b200ivf::IndexIVFStatsB200 s;
     guarded([&] { s = H(index)->get_stats(); }); // (a deferred failure stays in last_error)

@@ -375,6 +375,11 @@ cudaStream_t IndexIVFFlatB200::stream_() const {
     return impl_->stream;
 }
 
+IndexIVFFlatB200::CoarseView IndexIVFFlatB200::coarse_view_() const {
+    const Impl& m = *impl_;
+    return {m.cent_slab.p, m.cent_meta.as<uint32_t>(), m.cent_meta.as<int32_t>() + 1, m.nf4};
+}
+
 void IndexIVFFlatB200::set_stream(cudaStream_t s) {
     std::lock_guard<std::mutex> lock(mu_);
     DeviceGuard g(device_);

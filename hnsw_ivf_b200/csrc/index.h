@@ -79,6 +79,10 @@ struct Buffer {
     }
 };
 
+constexpr int64_t kNoAllocMaxQueries = 4096;
+constexpr int64_t kNoAllocMaxProbe = 64;
+constexpr size_t kNoAllocScratchBytes = (size_t)8 << 20; // per GPU that loads the library
+
 class IndexIVFFlatB200 {
   public:
     IndexIVFFlatB200(size_t d, size_t nlist, int metric, int device);
@@ -140,6 +144,11 @@ class IndexIVFFlatB200 {
     // search_preassigned with a DEVICE probe table of int32 (-1 = no probe); device buffers only
     void search_probed_i32(int64_t n, const float* x, int64_t k, const int32_t* probes, float* D,
                            int64_t* I) const;
+    // quantize() for callers that may not allocate (noalloc.cu): device buffers only, scratch in a
+    // fixed file-scope __device__ array shared by every call; n <= kNoAllocMaxQueries,
+    // nprobe <= kNoAllocMaxProbe. No cudaMalloc / cudaFree on this path. Asynchronous on the
+    // handle's stream.
+    void quantize_noalloc(int64_t n, const float* x, int64_t nprobe, float* Dq, int64_t* Iq) const;
     // quantizer->search into a device int32 table (device buffers only, asynchronous)
     void quantize_i32(int64_t n, const float* x, int64_t nprobe, int32_t* Iq, float* Dq) const;
 
@@ -172,6 +181,14 @@ class IndexIVFFlatB200 {
     void finish_async_() const;
     void read_counters_() const;
     cudaStream_t stream_() const; // the stream every call of this handle is ordered on
+    // the centroid table as the scan kernels read it (one-list slab + its blk0 / len words)
+    struct CoarseView {
+        const void* slab;
+        const uint32_t* blk0;
+        const int32_t* len;
+        int nf4;
+    };
+    CoarseView coarse_view_() const;
     void search_impl_(int64_t n, const float* x, int64_t k, const int64_t* assign, float* D,
                       int64_t* I, bool store_pairs, const SearchParametersIVF* params,
                       QueryLatencyStats* per_query, const int32_t* probes32) const;

@@ -117,6 +117,17 @@ int b200_IndexIVFFlat_search_preassigned(const B200IndexIVFFlat* index, b200_idx
 int b200_IndexIVFFlat_quantize(const B200IndexIVFFlat* index, b200_idx_t n, const float* x,
                                b200_idx_t nprobe, float* centroid_dis, b200_idx_t* assign);
 
+/* b200_IndexIVFFlat_quantize for callers that cannot allocate device memory (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc). It has NO counterpart in the
+ * reference. x, centroid_dis, assign must be
+ * DEVICE pointers; n <= 4096 and nprobe <= min(nlist, 64), anything larger fails with -2 and a
+ * message naming the limit. The call makes no cudaMalloc / cudaFree: its scratch (launch plan and
+ * partial candidate lists) is a fixed 8 MiB file-scope __device__ array that every GPU which loads
+ * the library holds until exit. ALL calls on a device share that array: calls that overlap on the
+ * GPU race on it -- serialise them. Work is enqueued on the handle's stream (set_stream). */
+int b200_IndexIVFFlat_quantize_noalloc(const B200IndexIVFFlat* index, b200_idx_t n, const float* x,
+                                       b200_idx_t nprobe, float* centroid_dis, b200_idx_t* assign);
+
 /* indexIVF_stats (faiss/IndexIVF.cpp:1764) is per handle here */
 void b200_IndexIVFFlat_get_stats(const B200IndexIVFFlat* index, B200IndexIVFStats* stats);
 void b200_IndexIVFFlat_reset_stats(B200IndexIVFFlat* index);
