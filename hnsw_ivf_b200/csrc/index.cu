@@ -686,9 +686,10 @@ struct BatchPlan {
 
 static BatchPlan plan_batch(int nf4, int64_t kpart, int64_t nb, int64_t nprobe,
                             int64_t nlists_owned, int64_t nstored, bool simt_only = false,
-                            bool filtered = false) {
+                            bool filtered = false, double own_frac = 1.0) {
     BatchPlan bp;
-    const int64_t pairs = nb * nprobe;
+    // the (query, probe) pairs expected to fall into this handle's list range
+    const int64_t pairs = std::max<int64_t>(1, (int64_t)((double)(nb * nprobe) * own_frac));
     // queries that meet in a probed list, on average (uniform-probe estimate)
     const double avg_q =
             (double)pairs / (double)std::max<int64_t>(1, std::min<int64_t>(nlists_owned, pairs));
@@ -793,8 +794,10 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
     int64_t nb = std::min<int64_t>(n, 32768);
     // queries per probed list, on average: few -> rows-major kernel (its MMA time follows the
     // query count and it streams a list at any count), many -> queries-major (128-query tiles)
-    const double avg_q = (double)std::min<int64_t>(n, 32768) * np /
-            (double)std::max<int64_t>(1, std::min<int64_t>(nlists_owned, std::min<int64_t>(n, 32768) * np));
+    // (a list-range shard sees only its share of the probes: pairs * owned / nlist)
+    const double own_frac = (double)nlists_owned / (double)nlist;
+    const double pairs_own = std::max(1.0, (double)std::min<int64_t>(n, 32768) * np * own_frac);
+    const double avg_q = pairs_own / std::max(1.0, std::min((double)nlists_owned, pairs_own));
     // hardly any list shared between queries (small batches, huge nlist): nothing to multiply, the
     // scan is a pure stream -> the SIMT warp kernel alone (exact fp32, no re-rank needed)
     const bool simt_only =
@@ -804,13 +807,13 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
                                                                           avg_q < m.tcr_max_avg_q))));
     const int64_t kp = tc ? (tcr ? kp_r : kp_q) : k; // entries per partial list
     const int tcr_tq = tcr ? scan_tcr_tq(m.nf4, (int)kp) : 0;
-    BatchPlan bp = plan_batch(m.nf4, kp, nb, np, nlists_owned, m.nstored, simt_only, filtered);
+    BatchPlan bp = plan_batch(m.nf4, kp, nb, np, nlists_owned, m.nstored, simt_only, filtered, own_frac);
     const int pmul = (tc && !tcr) ? 2 : 1; // partial lists per (pair, split)
     const int tc_tq = tcr ? tcr_tq : kTcTQ;
     const int tc_min = tcr ? 0 : kTileMinQueries; // lists with more queries than this: tensor cores
     while (nb > 1 && (size_t)nb * np * bp.S * pmul * kp * sizeof(uint64_t) > ((size_t)2 << 30)) {
         nb = (nb + 1) / 2;
-        bp = plan_batch(m.nf4, kp, nb, np, nlists_owned, m.nstored, simt_only, filtered);
+        bp = plan_batch(m.nf4, kp, nb, np, nlists_owned, m.nstored, simt_only, filtered, own_frac);
     }
     cudaStream_t st = m.stream;
     unsigned long long* dstats = m.dev_stats.as<unsigned long long>();
@@ -826,7 +829,7 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
     auto enqueue = [&](int64_t ni, const float* xd, float* Dd, int64_t* Id, const int64_t* ad,
                        bool timed, const int32_t* p32 = nullptr) {
         const int64_t pairs = ni * np;
-        bp = plan_batch(m.nf4, kp, ni, np, nlists_owned, m.nstored, simt_only, filtered);
+        bp = plan_batch(m.nf4, kp, ni, np, nlists_owned, m.nstored, simt_only, filtered, own_frac);
         // stage 1: probe table
         m.coarse_ids.reserve((size_t)pairs * sizeof(int32_t));
         m.coarse_dis.reserve((size_t)pairs * sizeof(float));
@@ -888,8 +891,12 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
         pa.coarse_ids = probe_tab;
         pa.n = (int)ni;
         pa.nprobe = (int)np;
-        pa.nlists = (int)nlist;
-        pa.list_len = m.list_len.as<int32_t>();
+        // the plan and the scans cover this handle's list range only (per-list arrays in local
+        // numbering): a shard of a 262144-list index does not walk the other shards' lists
+        pa.nlists = (int)nlists_owned;
+        pa.list_lo = (int)m.list_lo;
+        pa.nlist_total = (int)nlist;
+        pa.list_len = m.list_len.as<int32_t>() + m.list_lo;
         pa.count = m.count.as<int32_t>();
         pa.fill = m.fill.as<int32_t>();
         pa.grp_start = m.grp_start.as<int32_t>();
@@ -902,7 +909,7 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
         pa.tile_min = tc ? tc_min : kTileMinQueries;
         pa.item_off_tile = m.item_off_tile.as<uint32_t>();
         const int64_t max_tc_items =
-                (pairs / tc_tq + std::min<int64_t>(pairs / (tc_min + 1), (int64_t)nlist)) * bp.S;
+                (pairs / tc_tq + std::min<int64_t>(pairs / (tc_min + 1), nlists_owned)) * bp.S;
         if (tc) {
             m.item_list.reserve((size_t)(max_tc_items + 1) * sizeof(int32_t));
             pa.item_list_tile = m.item_list.as<int32_t>();
@@ -917,12 +924,12 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
             CUDA_CHECK(cudaEventRecord(m.ev[2], st));
         ScanArgs sa;
         sa.slab = m.slab.as<float4>();
-        sa.list_blk0 = m.list_blk0.as<uint32_t>();
-        sa.list_len = m.list_len.as<int32_t>();
+        sa.list_blk0 = m.list_blk0.as<uint32_t>() + m.list_lo;
+        sa.list_len = m.list_len.as<int32_t>() + m.list_lo;
         sa.grp_start = pa.grp_start;
         sa.pair_query = pa.pair_query;
         sa.item_off = pa.item_off;
-        sa.nlists = (int)nlist;
+        sa.nlists = (int)nlists_owned;
         sa.nsplit = (int)bp.S;
         sa.k = (int)kp;
         sa.cap = bp.cfg.cap;
@@ -934,7 +941,7 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
         sa.row_mask = row_mask;
         sa.pair_limit = mc > 0 ? m.limit_slot.as<int32_t>() : nullptr;
         const int64_t max_items =
-                (ceil_div(pairs, bp.cfg.rq) + std::min<int64_t>(pairs, (int64_t)nlist)) * bp.S;
+                (ceil_div(pairs, bp.cfg.rq) + std::min<int64_t>(pairs, nlists_owned)) * bp.S;
         if (!tcr) // (every probed list goes to the rows-major tensor-core kernel otherwise)
             CUDA_CHECK(launch_ivf_scan(metric_type, bp.cfg.rq, bp.cfg.wpc, (uint32_t)max_items, sa,
                                        st, bp.cfg.rv));
@@ -948,7 +955,7 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
             ta.pair_query = pa.pair_query;
             ta.item_off = pa.item_off_tile;
             ta.norms = m.norms.as<float>();
-            ta.nlists = (int)nlist;
+            ta.nlists = (int)nlists_owned;
             ta.nsplit = (int)bp.S;
             ta.kpart = (int)kp;
             ta.d = d;
@@ -974,7 +981,7 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
             ta.grp_start = pa.grp_start;
             ta.pair_query = pa.pair_query;
             ta.item_off = pa.item_off_tile;
-            ta.nlists = (int)nlist;
+            ta.nlists = (int)nlists_owned;
             ta.nsplit = (int)bp.S;
             ta.k = (int)kp;
             ta.cap = tcfg.cap;
@@ -984,7 +991,7 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
             ta.queries = xd;
             ta.part = sa.part;
             const int64_t max_tiles =
-                    (pairs / tcfg.tq + std::min<int64_t>(pairs / (kTileMinQueries + 1), (int64_t)nlist)) *
+                    (pairs / tcfg.tq + std::min<int64_t>(pairs / (kTileMinQueries + 1), nlists_owned)) *
                     bp.S;
             CUDA_CHECK(launch_ivf_scan_tile(metric_type, (uint32_t)max_tiles, ta, st));
         }

@@ -136,9 +136,13 @@ const unsigned long long* tc_trap_info_host();
 
 // ---- planning: invert the probe table into per-list query groups -------------------------------
 struct PlanArgs {
-    const int32_t* coarse_ids;  // [n][nprobe], -1 = no probe
-    int n, nprobe, nlists;
-    const int32_t* list_len;    // [nlists]
+    const int32_t* coarse_ids;  // [n][nprobe], -1 = no probe (GLOBAL list numbers)
+    int n, nprobe, nlists;      // nlists: lists this plan covers = [list_lo, list_lo + nlists)
+    int list_lo = 0;            // first list of the handle's range (a list-range shard plans only
+                                // over its own lists: probes of other lists are simply not its)
+    int nlist_total = 0;        // lists of the whole index: keys >= this are invalid (0: = nlists)
+    const int32_t* list_len;    // [nlists], LOCAL numbering (list list_lo + i at i), as every
+                                // per-list array below
     int32_t* count;             // [nlists] scratch (zeroed by launch_plan)
     int32_t* fill;              // [nlists] scratch (zeroed by launch_plan)
     int32_t* grp_start;         // [nlists+1] out

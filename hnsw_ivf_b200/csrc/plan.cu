@@ -21,13 +21,16 @@ __global__ void plan_count_kernel(const PlanArgs a) {
     unsigned long long ndis = 0, nvis = 0, bad = 0;
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
          i += (int64_t)gridDim.x * blockDim.x) {
-        const int l = a.coarse_ids[i];
+        int l = a.coarse_ids[i];
         if (l < 0)
             continue;
-        if (l >= a.nlists) {
+        if (l >= (a.nlist_total ? a.nlist_total : a.nlists)) {
             bad++;
             continue;
         }
+        l -= a.list_lo;
+        if (l < 0 || l >= a.nlists) // another shard's list
+            continue;
         const int len = a.list_len[l];
         if (len == 0)
             continue;
@@ -166,7 +169,7 @@ __global__ void plan_scatter_kernel(const PlanArgs a) {
     const int64_t total = (int64_t)a.n * a.nprobe;
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total;
          i += (int64_t)gridDim.x * blockDim.x) {
-        const int l = a.coarse_ids[i];
+        const int l = a.coarse_ids[i] < 0 ? -1 : a.coarse_ids[i] - a.list_lo;
         int slot = -1;
         if (l >= 0 && l < a.nlists && a.list_len[l] > 0) {
             slot = a.grp_start[l] + atomicAdd(&a.fill[l], 1);

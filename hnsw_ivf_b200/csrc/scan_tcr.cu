@@ -25,12 +25,16 @@
 //    128 x 96-dim tile, exactly the time the tile takes to arrive from HBM at 6.5 TB/s -- the kernel
 //    could not be HBM-bound; two are 1.5 k.)
 //  * A: list rows arrive by TMA (box {128 floats, 4 blocks, 8 columns} of the slab = 128 rows x 32
-//    dims per stage). The split warps read a stage once from shared memory (lane = row) and write
-//    BOTH operand parts to tensor memory with tcgen05.st: hi = the raw fp32 bits (the tensor core
-//    ignores the low 13 mantissa bits, tools/tc_probe.cu), lo = tf32(y - trunc_tf32(y)). The raw
-//    stage is released to the TMA as soon as it is in registers; the MMAs never read row data from
-//    shared memory (per stage: 16 KB TMA write + 16 KB read + 12 * N * 32 B of B reads, against
-//    96 KB for the queries-major form, which was shared-memory-bandwidth bound).
+//    dims per stage). The hi part needs no work at all: the raw fp32 stage in shared memory IS a
+//    K-major no-swizzle tf32 operand (the slab's block layout is the canonical one, and the tensor
+//    core ignores the low 13 mantissa bits, tools/tc_probe.cu), so MMA 1 reads A straight from the
+//    TMA stage through a shared-memory descriptor. Only lo = y - trunc_tf32(y) is computed: the
+//    split warps read a stage once (lane = row) and write lo to tensor memory with tcgen05.st (the
+//    tensor core truncates it to tf32 itself: 2^-20 |y|, the size of the dropped lo*lo term). A raw
+//    stage goes back to the TMA when both its readers are done: the split warps have it in
+//    registers and the MMAs that read it have completed (tcgen05.commit). Half the tcgen05.st
+//    traffic and half the conversion work of writing both parts -- the split warps' stage latency
+//    was what paced the kernel at ~60 % of the HBM rate.
 //  * One elected thread issues the MMAs (2 per 8 dims, see above).
 //  * Epilogue (8 warps, thread = row = TMEM lane): per 16 queries two tcgen05.ld (the two column
 //    groups) and 16 adds; score (+ |y|^2
@@ -65,9 +69,10 @@ constexpr int kRKC = 8;           // float4 columns per stage (4 MMA k-steps)
 constexpr int kRTileBlocks = 4;   // 32-row blocks per tile (M = 128)
 constexpr int kRStageF4 = kRKC * kRTileBlocks * kBlockRows; // 1024 float4 = 16 KB
 constexpr int kRMaxStages = 12;   // raw ring (as deep as the item's query tile leaves room for)
-constexpr int kRAStages = 4;      // operand ring in tensor memory
+constexpr int kRAStages = 8;      // operand (lo) ring in tensor memory
 constexpr uint32_t kRColsD = 0;   // two accumulator buffers of 128 columns
-constexpr uint32_t kRColsA = 256; // kRAStages x (32 hi + 32 lo) columns
+constexpr uint32_t kRColsA = 256; // kRAStages x 32 columns (lo part of a stage)
+constexpr uint32_t kRALBO = kRTileBlocks * 512, kRASBO = 128; // A (hi) straight from a raw stage
 constexpr int kRMaxChunks = 256;  // float4 columns of a query (d <= 1024)
 constexpr uint32_t kRBSBO = 128;
 // Candidate buffer of a query: C entries = the KP kept + free ones. A buffer is compacted
@@ -94,6 +99,10 @@ __device__ __forceinline__ float tf32_rn(float x) {
 }
 __device__ __forceinline__ float tf32_lo(float y) {
     return tf32_rn(y - tf32_trunc(y));
+}
+// ... for the list rows: exact residual, truncated to tf32 by the tensor core itself
+__device__ __forceinline__ float tf32_lo_raw(float y) {
+    return y - tf32_trunc(y);
 }
 
 template <int KP>
@@ -172,7 +181,8 @@ struct RSmem {
     int* qid;           // [kTcrTQ] query number
     int* flag;          // [4] by barrier epoch: 1 = some buffer wants compaction, 2 = overflowed
     uint64_t* full;     // [kRMaxStages] TMA landed
-    uint64_t* empty;    // [kRMaxStages] the split warps have the stage in registers
+    uint64_t* empty;    // [kRMaxStages] the split warps have the stage in registers AND the MMAs
+                        //               that read it are done
     uint64_t* a_rdy;    // [kRAStages] operand stage written to tensor memory
     uint64_t* a_empty;  // [kRAStages] MMAs that read the operand stage are done
     uint64_t* d_full;   // [2] accumulator buffer complete
@@ -368,7 +378,7 @@ __global__ void __launch_bounds__(kRThreads, 1)
     if (tid == 0) {
         for (int i = 0; i < kRMaxStages; ++i) {
             mbar_init(&s.full[i], 1);
-            mbar_init(&s.empty[i], kRSplitWarps / 2);
+            mbar_init(&s.empty[i], kRSplitWarps / 2 + 1);
         }
         for (int i = 0; i < kRAStages; ++i) {
             mbar_init(&s.a_rdy[i], kRSplitWarps / 2);
@@ -520,9 +530,10 @@ __global__ void __launch_bounds__(kRThreads, 1)
         const uint32_t idesc2 = make_idesc_tf32(kRTileBlocks * kBlockRows, 2 * n16);
         const uint32_t idesc1 = make_idesc_tf32(kRTileBlocks * kBlockRows, n16);
         const uint64_t desc0 = make_smem_desc_kmajor_noswz(0, lbo, kRBSBO);
-        const uint32_t b0a = smem_u32(s.b);
+        const uint64_t adesc0 = make_smem_desc_kmajor_noswz(0, kRALBO, kRASBO);
+        const uint32_t b0a = smem_u32(s.b), raw0 = smem_u32(s.raw);
         tc_fence_after_sync();
-        int as = 0;
+        int as = 0, rst = 0;
         uint32_t aph = 0;
         bool ready = false;
         long long w_ardy = 0, w_dempty = 0, w_issue = 0;
@@ -540,8 +551,10 @@ __global__ void __launch_bounds__(kRThreads, 1)
                 const long long i0_ = tracing ? clock64() : 0;
                 const int ks0 = sg * (kRKC / 2);
                 const int ksn = (a.dbg & 8) ? 0 : nks - ks0; // >= 1
-                const uint32_t ahi = tmem + kRColsA + (uint32_t)as * 64u;
-                const uint32_t alo = ahi + 32u;
+                const uint32_t alo = tmem + kRColsA + (uint32_t)as * 32u;
+                // hi: the raw stage itself (2 chunks = 2 * kRALBO bytes per k-step)
+                const uint64_t dah =
+                        adesc0 + (uint64_t)((raw0 + (uint32_t)rst * kRStageF4 * 16u) >> 4);
                 // the B descriptor advances by 2 chunks (2 * LBO bytes, in 16-byte units) per k-step
                 const uint64_t db = desc0 + (uint64_t)((b0a + (uint32_t)(ks0 * 2) * lbo) >> 4);
                 const int nas = as + 1 == kRAStages ? 0 : as + 1;
@@ -552,7 +565,8 @@ __global__ void __launch_bounds__(kRThreads, 1)
                         if (ks < ksn) {
                             const uint64_t kb = db + (uint64_t)((uint32_t)ks * ((2u * lbo) >> 4));
                             // the first MMA of a tile overwrites all 2 * n16 columns
-                            mma_tf32_ts(tD, ahi + ks * 8, kb, idesc2, (sg | ks) != 0 ? 1u : 0u);
+                            const uint64_t ka = dah + (uint64_t)(ks * ((2 * kRALBO) >> 4));
+                            mma_tf32_ss(tD, ka, kb, idesc2, (sg | ks) != 0 ? 1u : 0u);
                             mma_tf32_ts(tD, alo + ks * 8, kb, idesc1, 1u);
                         }
                     }
@@ -563,20 +577,25 @@ __global__ void __launch_bounds__(kRThreads, 1)
                     constexpr int ks = kRKC / 2 - 1;
                     if (ks < ksn) {
                         const uint64_t kb = db + (uint64_t)((uint32_t)ks * ((2u * lbo) >> 4));
-                        mma_tf32_ts(tD, ahi + ks * 8, kb, idesc2, 1u);
+                        const uint64_t ka = dah + (uint64_t)(ks * ((2 * kRALBO) >> 4));
+                        mma_tf32_ss(tD, ka, kb, idesc2, 1u);
                         mma_tf32_ts(tD, alo + ks * 8, kb, idesc1, 1u);
                     }
                     if (a.dbg & 128) {
+                        mbar_arrive(&s.empty[rst]);
                         mbar_arrive(&s.a_empty[as]);
                         if (sg == nsg - 1)
                             mbar_arrive(&s.d_full[b]);
                     } else {
+                        mma_commit(&s.empty[rst]); // the raw stage may be refilled
                         mma_commit(&s.a_empty[as]);
                         if (sg == nsg - 1)
                             mma_commit(&s.d_full[b]);
                     }
                 }
                 __syncwarp();
+                if (++rst == nst)
+                    rst = 0;
                 if (tracing)
                     w_issue += clock64() - i0_;
                 as = nas;
@@ -611,24 +630,19 @@ __global__ void __launch_bounds__(kRThreads, 1)
                 TCR_WAIT(&s.a_empty[as], aph ^ 1u, w_aempty, 5, it);
                 tc_fence_after_sync();
             }
-            const uint32_t ta = tmem + lane_addr + kRColsA + (uint32_t)as * 64u;
+            const uint32_t ta = tmem + lane_addr + kRColsA + (uint32_t)as * 32u;
 #pragma unroll
             for (int h = 0; h < 2 && !(a.dbg & 4); ++h) {
-                uint32_t hi[16], lo[16];
+                uint32_t lo[16];
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
                     const float4 y = src[(h * 4 + u) * 128];
-                    hi[4 * u + 0] = __float_as_uint(y.x);
-                    hi[4 * u + 1] = __float_as_uint(y.y);
-                    hi[4 * u + 2] = __float_as_uint(y.z);
-                    hi[4 * u + 3] = __float_as_uint(y.w);
-                    lo[4 * u + 0] = __float_as_uint(tf32_lo(y.x));
-                    lo[4 * u + 1] = __float_as_uint(tf32_lo(y.y));
-                    lo[4 * u + 2] = __float_as_uint(tf32_lo(y.z));
-                    lo[4 * u + 3] = __float_as_uint(tf32_lo(y.w));
+                    lo[4 * u + 0] = __float_as_uint(tf32_lo_raw(y.x));
+                    lo[4 * u + 1] = __float_as_uint(tf32_lo_raw(y.y));
+                    lo[4 * u + 2] = __float_as_uint(tf32_lo_raw(y.z));
+                    lo[4 * u + 3] = __float_as_uint(tf32_lo_raw(y.w));
                 }
-                tmem_st_32x32b_x16(ta + (uint32_t)h * 16u, hi);
-                tmem_st_32x32b_x16(ta + 32u + (uint32_t)h * 16u, lo);
+                tmem_st_32x32b_x16(ta + (uint32_t)h * 16u, lo);
             }
             __syncwarp();
             if (lane == 0)
