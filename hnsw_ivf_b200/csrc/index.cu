@@ -21,6 +21,8 @@ namespace b200ivf {
 
 std::atomic<unsigned long long> g_kernel_launches{0};
 std::atomic<unsigned long long> g_tc_launches{0};
+static std::atomic<int> g_force_nsplit{0}; // set_option("scan_nsplit"): row splits per list, 0 = auto
+std::atomic<int> g_tc_dbg{getenv("B200IVF_TC_DBG") ? atoi(getenv("B200IVF_TC_DBG")) : 0};
 
 #define CUDA_CHECK(expr)                                                                     \
     do {                                                                                     \
@@ -720,6 +722,8 @@ static BatchPlan plan_batch(int nf4, int64_t kpart, int64_t nb, int64_t nprobe,
         S = std::max<int64_t>(1, std::min(S, std::max<int64_t>(1, avg_blocks / kScanRowsPerStep)));
     }
     bp.S = std::min<int64_t>(S, 32);
+    if (const int f = g_force_nsplit.load(std::memory_order_relaxed)) // tuning experiments
+        bp.S = std::max<int64_t>(1, std::min<int64_t>(f, std::max<int64_t>(1, avg_blocks / 4)));
     return bp;
 }
 
@@ -1320,6 +1324,10 @@ void IndexIVFFlatB200::set_option(const char* name, double value) {
         m.use_tc = value != 0;
     else if (n == "use_graph")
         m.use_graph = value != 0;
+    else if (n == "scan_nsplit") // timing experiments; process-wide
+        g_force_nsplit.store((int)value);
+    else if (n == "tc_dbg") // timing experiments (kernels.h); process-wide
+        g_tc_dbg.store((int)value);
     else if (n == "cp_niter") // ClusteringParameters of the quantizer (faiss/Clustering.h:23-64),
         cp_niter = std::max(0, (int)value); // index.cp.niter in the reference
     else if (n == "cp_max_points_per_centroid")

@@ -12,6 +12,9 @@ namespace b200ivf {
 extern std::atomic<unsigned long long> g_kernel_launches;
 // ... and how many of them were tensor-core (tcgen05) scans
 extern std::atomic<unsigned long long> g_tc_launches;
+// timing experiments only: bits that switch stages of the tensor-core scans off (scan_tcr.cu);
+// from B200IVF_TC_DBG at load, or set_option("tc_dbg"). Results are WRONG while it is non-zero.
+extern std::atomic<int> g_tc_dbg;
 inline void count_launches(int n) {
     g_kernel_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed);
 }

@@ -656,10 +656,16 @@ cudaError_t make_slab_tensor_map_tc(void* map_out, const void* slab, int nf4, ui
     const cuuint64_t gstride[2] = {(cuuint64_t)nf4 * 512, 512};
     const cuuint32_t box[3] = {128, (cuuint32_t)kTcTileBlocks, (cuuint32_t)kTcKC};
     const cuuint32_t estr[3] = {1, 1, 1};
+    // (tuning experiments: B200IVF_TMA_PROMO = 0 none, 1 64 B, 2 128 B, 3 256 B)
+    static const int promo_i = getenv("B200IVF_TMA_PROMO") ? atoi(getenv("B200IVF_TMA_PROMO")) : 3;
+    const CUtensorMapL2promotion promo = promo_i == 0 ? CU_TENSOR_MAP_L2_PROMOTION_NONE
+            : promo_i == 1                            ? CU_TENSOR_MAP_L2_PROMOTION_L2_64B
+            : promo_i == 2                            ? CU_TENSOR_MAP_L2_PROMOTION_L2_128B
+                                                      : CU_TENSOR_MAP_L2_PROMOTION_L2_256B;
     const CUresult r = encode(reinterpret_cast<CUtensorMap*>(map_out),
                               CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<void*>(slab), gdim,
                               gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                              CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                              CU_TENSOR_MAP_SWIZZLE_NONE, promo,
                               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     return r == CUDA_SUCCESS ? cudaSuccess : cudaErrorInvalidValue;
 }
@@ -683,7 +689,7 @@ int scan_tc_kpart(int nf4, int k) {
 template <int METRIC, int KP>
 static cudaError_t launch_tc_one(uint32_t max_items, const TcScanArgs& a_in, cudaStream_t st) {
     TcScanArgs a = a_in;
-    static const int dbg = getenv("B200IVF_TC_DBG") ? atoi(getenv("B200IVF_TC_DBG")) : 0;
+    const int dbg = g_tc_dbg.load(std::memory_order_relaxed); // B200IVF_TC_DBG / "tc_dbg"
     a.dbg = a.nlists > 1 ? dbg : 0; // never for the coarse quantizer: the probes must stay real
     const size_t smem = scan_tc_smem_bytes(a.nstages);
     auto kern = ivf_scan_tc_kernel<METRIC, KP>;

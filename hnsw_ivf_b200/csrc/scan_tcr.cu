@@ -566,8 +566,10 @@ __global__ void __launch_bounds__(kRThreads, 1)
                             const uint64_t kb = db + (uint64_t)((uint32_t)ks * ((2u * lbo) >> 4));
                             // the first MMA of a tile overwrites all 2 * n16 columns
                             const uint64_t ka = dah + (uint64_t)(ks * ((2 * kRALBO) >> 4));
-                            mma_tf32_ss(tD, ka, kb, idesc2, (sg | ks) != 0 ? 1u : 0u);
-                            mma_tf32_ts(tD, alo + ks * 8, kb, idesc1, 1u);
+                            if (!(a.dbg & 512))
+                                mma_tf32_ss(tD, ka, kb, idesc2, (sg | ks) != 0 ? 1u : 0u);
+                            if (!(a.dbg & 256))
+                                mma_tf32_ts(tD, alo + ks * 8, kb, idesc1, 1u);
                         }
                     }
                 }
@@ -578,8 +580,10 @@ __global__ void __launch_bounds__(kRThreads, 1)
                     if (ks < ksn) {
                         const uint64_t kb = db + (uint64_t)((uint32_t)ks * ((2u * lbo) >> 4));
                         const uint64_t ka = dah + (uint64_t)(ks * ((2 * kRALBO) >> 4));
-                        mma_tf32_ss(tD, ka, kb, idesc2, 1u);
-                        mma_tf32_ts(tD, alo + ks * 8, kb, idesc1, 1u);
+                        if (!(a.dbg & 512))
+                            mma_tf32_ss(tD, ka, kb, idesc2, 1u);
+                        if (!(a.dbg & 256))
+                            mma_tf32_ts(tD, alo + ks * 8, kb, idesc1, 1u);
                     }
                     if (a.dbg & 128) {
                         mbar_arrive(&s.empty[rst]);
@@ -869,7 +873,7 @@ static cudaError_t launch_tcr_one(uint32_t max_items, const TcScanArgs& a_in, cu
     if (a.tq < 16 || a.tq > kTcrTQ || (a.tq & 15) ||
         tcr_stages(smem, KP, a.tq, 2 * ((a.nf4 + 1) >> 1)) < 3)
         return cudaErrorInvalidValue;
-    static const int dbg = getenv("B200IVF_TC_DBG") ? atoi(getenv("B200IVF_TC_DBG")) : 0;
+    const int dbg = g_tc_dbg.load(std::memory_order_relaxed); // B200IVF_TC_DBG / "tc_dbg"
     a.dbg = a.nlists > 1 ? dbg : 0; // timing experiments; never for the coarse quantizer
     auto kern = ivf_scan_tcr_kernel<METRIC, KP>;
     cudaError_t e =
