@@ -298,12 +298,13 @@ def parity_detail(D_ref, I_ref, D_new, I_new):
             "unexplained": r["unexplained"], "bad_dist": r["bad_dist"]}
 
 
-def scan_kernel_name(avg_q, d, k, simt_max=3.0, tcr_max=48.0):
+def scan_kernel_name(avg_q, d, k, simt_max=2.0, tcr_max=48.0):
     """the list-scan kernel the library's plan picks (csrc/index.cu search_impl_) for this shape"""
     if avg_q <= simt_max:
         return "ivf_scan_kernel (exact fp32 warp kernel)"
     if d > 128 or k > 24 or avg_q < tcr_max:
-        return "ivf_scan_tcr_kernel (rows-major tcgen05 3xTF32, 2 MMAs per k-step)"
+        shape = "two CTAs per SM" if (avg_q <= 32 and d <= 128) else "one CTA per SM"
+        return "ivf_scan_tcr_kernel (rows-major tcgen05 3xTF32, 2 MMAs per k-step, %s)" % shape
     return "ivf_scan_tc_kernel (queries-major tcgen05 3xTF32, 3 MMAs per k-step)"
 
 

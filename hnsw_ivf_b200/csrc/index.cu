@@ -255,9 +255,12 @@ struct IndexIVFFlatB200::Impl {
     bool use_graph = true;
     // average queries per probed list at or below which the SIMT warp kernel takes the whole scan
     // (B200IVF_SIMT_MAXQ, A/B runs)
-    double simt_max_avg_q = 3.0;
+    double simt_max_avg_q = 2.0;
     // ... and below which the rows-major tensor-core kernel is preferred to the queries-major one
     double tcr_max_avg_q = kTcrMaxAvgQueries;
+    // ... and below which that kernel runs in its two-CTAs-per-SM shape
+    double tcr_small_factor = 1.0;
+    double tcr_small_max_avg_q = 1e9; // (cap for A/B runs; the rule is 3/4 of the small item size)
     unsigned long long graph_replays = 0;
     int coarse_s_override = 0;  // B200IVF_COARSE_S (read once, at construction)
     bool trace_sync = false;    // B200IVF_TC_TRACE set: no graphs, no asynchronous returns
@@ -810,7 +813,14 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
     const bool tcr = tc && (kp_q == 0 || (kp_r > 0 && (m.tc_mode == 2 || (m.tc_mode == 0 &&
                                                                           avg_q < m.tcr_max_avg_q))));
     const int64_t kp = tc ? (tcr ? kp_r : kp_q) : k; // entries per partial list
-    const int tcr_tq = tcr ? scan_tcr_tq(m.nf4, (int)kp) : 0;
+    // few queries per list: the two-CTAs-per-SM shape of the rows-major kernel (<= 32 queries per
+    // item; a list probed by more is cut into several items)
+    // (worth it while most lists fit one or two items: up to that shape's item size on average;
+    // measured on C2: 30 queries per list 1.49 ms against 1.66, 41 per list 1.85 against 1.78)
+    int tq_small = tcr ? scan_tcr_tq_small(m.nf4, (int)kp) : 0;
+    if (avg_q > std::min(m.tcr_small_max_avg_q, m.tcr_small_factor * tq_small))
+        tq_small = 0;
+    const int tcr_tq = tcr ? (tq_small ? tq_small : scan_tcr_tq(m.nf4, (int)kp)) : 0;
     BatchPlan bp = plan_batch(m.nf4, kp, nb, np, nlists_owned, m.nstored, simt_only, filtered, own_frac);
     const int pmul = (tc && !tcr) ? 2 : 1; // partial lists per (pair, split)
     const int tc_tq = tcr ? tcr_tq : kTcTQ;
@@ -1318,6 +1328,10 @@ void IndexIVFFlatB200::set_option(const char* name, double value) {
         m.simt_max_avg_q = value;
     else if (n == "tcr_max_avg_q")
         m.tcr_max_avg_q = value;
+    else if (n == "tcr_small_factor")
+        m.tcr_small_factor = value;
+    else if (n == "tcr_small_max_avg_q")
+        m.tcr_small_max_avg_q = value;
     else if (n == "tc_mode")
         m.tc_mode = (int)value;
     else if (n == "use_tc")

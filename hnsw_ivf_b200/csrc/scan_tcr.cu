@@ -58,20 +58,36 @@ namespace {
 
 using namespace ptx;
 
-constexpr int kREpiWarps = 8;     // warps 0-7
-constexpr int kRTmaWarp = 8;
-constexpr int kRMmaWarp = 9;
-constexpr int kRSplitWarp0 = 10;  // warps 10-17
-constexpr int kRSplitWarps = 8;
-constexpr int kRThreads = (kRSplitWarp0 + kRSplitWarps) * 32; // 576
-constexpr int kRLoaderWarps = 17; // every warp but the TMA producer fills B in the prologue
+// Two CTA shapes. BIG: 8 epilogue + 8 split warps, all of an SM's shared and tensor memory, one
+// CTA per SM (many queries per item: the epilogue and the B operand need the room). SMALL: 4 + 4
+// warps, half the shared memory, 256 TMEM columns, <= 32 queries per item -- TWO CTAs per SM, so
+// that one CTA's per-item costs (launch, query-tile prologue, pipeline fill and drain: ~7 us per
+// item, measured by forcing row splits; 2 ms of a 12 ms scan on the C4 shard) are covered by the
+// other CTA's streaming.
+template <bool SMALL>
+struct RShape {
+    static constexpr int EpiWarps = SMALL ? 4 : 8;      // warps 0 .. EpiWarps-1
+    static constexpr int TmaWarp = EpiWarps;
+    static constexpr int MmaWarp = EpiWarps + 1;
+    static constexpr int SplitWarp0 = EpiWarps + 2;
+    static constexpr int SplitWarps = SMALL ? 4 : 8;    // groups of 4 (one warp per TMEM quarter)
+    static constexpr int SplitGroups = SplitWarps / 4;
+    static constexpr int Threads = (SplitWarp0 + SplitWarps) * 32; // 320 / 576
+    static constexpr int LoaderWarps = EpiWarps + 1 + SplitWarps;  // all but the TMA producer
+    static constexpr int CtasPerSM = SMALL ? 2 : 1;
+    static constexpr int AStages = SMALL ? 4 : 8;       // lo ring in tensor memory
+    static constexpr uint32_t TmemCols = SMALL ? 256 : 512;
+    static constexpr uint32_t DStride = SMALL ? 64 : 128; // columns per accumulator buffer
+    static constexpr uint32_t ColsA = SMALL ? 128 : 256;  // first column of the lo ring
+    static constexpr int MaxTQ = SMALL ? 32 : 64;
+};
+constexpr size_t kRSmemBig = 227 * 1024, kRSmemSmall = 113 * 1024;
 constexpr int kRKC = 8;           // float4 columns per stage (4 MMA k-steps)
 constexpr int kRTileBlocks = 4;   // 32-row blocks per tile (M = 128)
 constexpr int kRStageF4 = kRKC * kRTileBlocks * kBlockRows; // 1024 float4 = 16 KB
 constexpr int kRMaxStages = 12;   // raw ring (as deep as the item's query tile leaves room for)
-constexpr int kRAStages = 8;      // operand (lo) ring in tensor memory
-constexpr uint32_t kRColsD = 0;   // two accumulator buffers of 128 columns
-constexpr uint32_t kRColsA = 256; // kRAStages x 32 columns (lo part of a stage)
+constexpr int kRAStages = 8;      // barrier slots of the lo ring (RShape::AStages of them in use)
+constexpr uint32_t kRColsD = 0;   // two accumulator buffers, RShape::DStride columns apart
 constexpr uint32_t kRALBO = kRTileBlocks * 512, kRASBO = 128; // A (hi) straight from a raw stage
 constexpr int kRMaxChunks = 256;  // float4 columns of a query (d <= 1024)
 constexpr uint32_t kRBSBO = 128;
@@ -202,7 +218,8 @@ __host__ __device__ inline size_t tcr_rest_bytes(int kp, int n16, int nch) {
     return (size_t)nch * tcr_lbo(n16) + (size_t)n16 * tcr_cand(kp) * 8 +
             (size_t)kTcrTQ * 6 * 4 + 4 * 4 + (2 * kRMaxStages + 2 * kRAStages + 4) * 8 + 16;
 }
-__host__ __device__ inline int tcr_stages(size_t smem_total, int kp, int n16, int nch) {
+__host__ __device__ inline int tcr_stages(size_t smem_total, int kp, int n16, int nch,
+                                          bool even = true) {
     const size_t rest = tcr_rest_bytes(kp, n16, nch);
     const int n = smem_total > rest ? (int)((smem_total - rest) / (kRStageF4 * sizeof(float4))) : 0;
     // EVEN, always: the two split-warp groups take alternate iterations, so with an even ring a
@@ -213,7 +230,9 @@ __host__ __device__ inline int tcr_stages(size_t smem_total, int kp, int n16, in
     // phase preceding the current one), and the ring protocol falls apart: stale stages, a second
     // expect_tx on a barrier whose load is still in flight, loads landing after the CTA has gone
     // (seen as rare launch failures on cold first searches at d = 960, where the ring had 5 stages).
-    return (n > kRMaxStages ? kRMaxStages : n) & ~1;
+    // (one split group -- the two-CTAs-per-SM shape -- has no such constraint: even = false)
+    const int c = n > kRMaxStages ? kRMaxStages : n;
+    return even ? (c & ~1) : c;
 }
 
 template <int KP>
@@ -242,7 +261,7 @@ __device__ __forceinline__ RSmem carve_r(unsigned char* raw, int nst, int n16, i
 
 // Compaction of the candidate buffers a warp owns (queries = warp mod 8), out of line: sort, keep
 // the best KP, tighten the query's bound and publish it for the other CTAs.
-template <int KP>
+template <int KP, int kREpiWarps>
 __device__ __noinline__ void tcr_compact(uint64_t* cand, int* cnt, uint32_t* thr, float* thrp,
                                          float* thrf, const float* xn, const int* qid,
                                          uint32_t* qthr, int nqw, int warp, int lane,
@@ -313,10 +332,16 @@ __device__ __noinline__ void tcr_compact(uint64_t* cand, int* cnt, uint32_t* thr
             a.trace[(role) * 64 + (idx)] = clock64();                    \
     } while (0)
 
-template <int METRIC, int KP>
-__global__ void __launch_bounds__(kRThreads, 1)
+template <int METRIC, int KP, bool SMALL>
+__global__ void __launch_bounds__(RShape<SMALL>::Threads, RShape<SMALL>::CtasPerSM)
         ivf_scan_tcr_kernel(const TcScanArgs a, const __grid_constant__ CUtensorMap tmap) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
+    using SH = RShape<SMALL>;
+    constexpr int kREpiWarps = SH::EpiWarps, kRTmaWarp = SH::TmaWarp, kRMmaWarp = SH::MmaWarp;
+    constexpr int kRSplitWarp0 = SH::SplitWarp0;
+    constexpr int kRLoaderWarps = SH::LoaderWarps, kRSplitGroups = SH::SplitGroups;
+    constexpr int kAStages = SH::AStages;
+    constexpr uint32_t kRColsA = SH::ColsA, kDStride = SH::DStride;
     constexpr int C = RCfg<KP>::C;
     const int tid = threadIdx.x;
     const int lane = tid & 31;
@@ -362,7 +387,7 @@ __global__ void __launch_bounds__(kRThreads, 1)
     const int nsg = (nf4 + kRKC - 1) / kRKC;  // stages per tile
     const int nks = (nf4 + 1) >> 1;           // MMA k-steps (8 dims each) per tile
     const int niter = ntiles * nsg;
-    const int nst = tcr_stages((size_t)a.nstages * 1024, KP, n16, 2 * nks);
+    const int nst = tcr_stages((size_t)a.nstages * 1024, KP, n16, 2 * nks, !SMALL);
     const uint32_t lbo = tcr_lbo(n16);
 
     const RSmem s = carve_r<KP>(smem_raw, nst, n16, 2 * nks);
@@ -378,10 +403,10 @@ __global__ void __launch_bounds__(kRThreads, 1)
     if (tid == 0) {
         for (int i = 0; i < kRMaxStages; ++i) {
             mbar_init(&s.full[i], 1);
-            mbar_init(&s.empty[i], kRSplitWarps / 2 + 1);
+            mbar_init(&s.empty[i], 4 + 1); // one split group (4 warps) + the MMA commit
         }
         for (int i = 0; i < kRAStages; ++i) {
-            mbar_init(&s.a_rdy[i], kRSplitWarps / 2);
+            mbar_init(&s.a_rdy[i], 4);
             mbar_init(&s.a_empty[i], 1);
         }
         for (int i = 0; i < 2; ++i) {
@@ -393,7 +418,7 @@ __global__ void __launch_bounds__(kRThreads, 1)
         fence_barrier_init();
     }
     if (warp == kRMmaWarp) {
-        tmem_alloc(s.tmem, 512);
+        tmem_alloc(s.tmem, SH::TmemCols);
         tmem_relinquish();
     }
     tc_fence_before_sync();
@@ -441,7 +466,7 @@ __global__ void __launch_bounds__(kRThreads, 1)
         const float scale = METRIC == kMetricL2 ? -2.f : -1.f;
         const bool vec = (a.d & 3) == 0 && (reinterpret_cast<uintptr_t>(a.queries) & 15) == 0;
         const int nch = 2 * nks; // chunks the MMAs read (the last one may be padding)
-        constexpr int kPer = (kTcrTQ + kRLoaderWarps - 1) / kRLoaderWarps; // 6
+        constexpr int kPer = (SH::MaxTQ + kRLoaderWarps - 1) / kRLoaderWarps;
         int qn[kPer];
         float nn[kPer];
 #pragma unroll
@@ -543,7 +568,7 @@ __global__ void __launch_bounds__(kRThreads, 1)
                 TCR_WAIT(&s.d_empty[b], (uint32_t)(((t >> 1) & 1) ^ 1), w_dempty, 2, t);
                 tc_fence_after_sync();
             }
-            const uint32_t tD = tmem + kRColsD + (uint32_t)b * 128u;
+            const uint32_t tD = tmem + kRColsD + (uint32_t)b * kDStride;
             for (int sg = 0; sg < nsg; ++sg) {
                 if (!ready)
                     TCR_WAIT(&s.a_rdy[as], aph, w_ardy, 3, t * nsg + sg);
@@ -557,8 +582,8 @@ __global__ void __launch_bounds__(kRThreads, 1)
                         adesc0 + (uint64_t)((raw0 + (uint32_t)rst * kRStageF4 * 16u) >> 4);
                 // the B descriptor advances by 2 chunks (2 * LBO bytes, in 16-byte units) per k-step
                 const uint64_t db = desc0 + (uint64_t)((b0a + (uint32_t)(ks0 * 2) * lbo) >> 4);
-                const int nas = as + 1 == kRAStages ? 0 : as + 1;
-                const uint32_t naph = as + 1 == kRAStages ? aph ^ 1u : aph;
+                const int nas = as + 1 == kAStages ? 0 : as + 1;
+                const uint32_t naph = as + 1 == kAStages ? aph ^ 1u : aph;
                 if (elect_one_sync()) {
 #pragma unroll
                     for (int ks = 0; ks < kRKC / 2 - 1; ++ks) {
@@ -591,8 +616,15 @@ __global__ void __launch_bounds__(kRThreads, 1)
                         if (sg == nsg - 1)
                             mbar_arrive(&s.d_full[b]);
                     } else {
-                        mma_commit(&s.empty[rst]); // the raw stage may be refilled
-                        mma_commit(&s.a_empty[as]);
+                        // (bits 1024 / 2048: plain arrives instead, to time what a commit costs)
+                        if (a.dbg & 1024)
+                            mbar_arrive(&s.empty[rst]);
+                        else
+                            mma_commit(&s.empty[rst]); // the raw stage may be refilled
+                        if (a.dbg & 2048)
+                            mbar_arrive(&s.a_empty[as]);
+                        else
+                            mma_commit(&s.a_empty[as]);
                         if (sg == nsg - 1)
                             mma_commit(&s.d_full[b]);
                     }
@@ -623,14 +655,14 @@ __global__ void __launch_bounds__(kRThreads, 1)
         const int row = quarter * 32 + lane;
         const uint32_t lane_addr = (uint32_t)(quarter * 32) << 16;
         long long w_full = 0, w_aempty = 0;
-        for (int it = grp; it < niter; it += 2) {
+        for (int it = grp; it < niter; it += kRSplitGroups) {
             const int st = it % nst;
             const uint32_t ph = (uint32_t)((it / nst) & 1);
-            const int as = it % kRAStages;
-            const uint32_t aph = (uint32_t)((it / kRAStages) & 1);
+            const int as = it % kAStages;
+            const uint32_t aph = (uint32_t)((it / kAStages) & 1);
             TCR_WAIT(&s.full[st], ph, w_full, 4, it);
             const float4* src = s.raw + (size_t)st * kRStageF4 + row;
-            if (it >= kRAStages) {
+            if (it >= kAStages) {
                 TCR_WAIT(&s.a_empty[as], aph ^ 1u, w_aempty, 5, it);
                 tc_fence_after_sync();
             }
@@ -689,7 +721,7 @@ __global__ void __launch_bounds__(kRThreads, 1)
             uint32_t drop[3] = {0u, 0u, 0u}; // (16 queries per half word; 4 chunks at most)
             TCR_WAIT(&s.d_full[b], (uint32_t)((t >> 1) & 1), w_dfull, 6, t);
             tc_fence_after_sync();
-            const uint32_t tD = tmem + lane_addr + kRColsD + (uint32_t)b * 128u;
+            const uint32_t tD = tmem + lane_addr + kRColsD + (uint32_t)b * kDStride;
             int n_events = 0, n_rounds = 0;
             long long c_scan = 0, c_comp = 0;
             for (int round = 0;; ++round) {
@@ -697,7 +729,7 @@ __global__ void __launch_bounds__(kRThreads, 1)
                 ++n_rounds;
                 int fl = 0;
 #pragma unroll 1
-                for (int ch = half; ch < nch16; ch += 2) {
+                for (int ch = half; ch < nch16; ch += kREpiWarps / 4) {
                     uint32_t v[16];
                     if (a.dbg & 64)
                         continue;
@@ -787,7 +819,7 @@ __global__ void __launch_bounds__(kRThreads, 1)
                     c_comp += (tracing ? clock64() : 0) - tt1;
                     break; // the common case: one barrier per tile
                 }
-                tcr_compact<KP>(s.cand, s.cnt, s.thr, s.thrp, s.thrf, s.xn, s.qid, a.qthr, nqw, warp, lane,
+                tcr_compact<KP, kREpiWarps>(s.cand, s.cnt, s.thr, s.thrp, s.thrf, s.xn, s.qid, a.qthr, nqw, warp, lane,
                                 false);
                 named_bar_sync(2, kREpiWarps * 32);
                 c_comp += (tracing ? clock64() : 0) - tt1;
@@ -813,7 +845,7 @@ __global__ void __launch_bounds__(kRThreads, 1)
             a.trace[9 * 64 + 5] = w_dfull;
         // ---- item done: best KP of every query, sorted, to `part` --------------------------------
         named_bar_sync(2, kREpiWarps * 32);
-        tcr_compact<KP>(s.cand, s.cnt, s.thr, s.thrp, s.thrf, s.xn, s.qid, a.qthr, nqw, warp, lane, true);
+        tcr_compact<KP, kREpiWarps>(s.cand, s.cnt, s.thr, s.thrp, s.thrf, s.xn, s.qid, a.qthr, nqw, warp, lane, true);
         __syncwarp();
         for (int qi = warp; qi < nqw; qi += kREpiWarps) {
             const int n = s.cnt[qi];
@@ -829,7 +861,7 @@ __global__ void __launch_bounds__(kRThreads, 1)
     named_bar_sync(1, kRLoaderWarps * 32);
     if (warp == kRMmaWarp) {
         tc_fence_after_sync();
-        tmem_dealloc(tmem, 512);
+        tmem_dealloc(tmem, SH::TmemCols);
     }
     if (tid == 0)
         TCR_TRACE(0, 5);
@@ -865,17 +897,17 @@ const unsigned long long* tc_trap_info_host() {
     return g_trap_host;
 }
 
-template <int METRIC, int KP>
-static cudaError_t launch_tcr_one(uint32_t max_items, const TcScanArgs& a_in, cudaStream_t st) {
+template <int METRIC, int KP, bool SMALL>
+static cudaError_t launch_tcr_shape(uint32_t max_items, const TcScanArgs& a_in, cudaStream_t st) {
     TcScanArgs a = a_in;
-    const size_t smem = 227 * 1024;
+    const size_t smem = SMALL ? kRSmemSmall : kRSmemBig;
     a.nstages = (int)(smem / 1024); // the kernel carves per item (tcr_stages)
-    if (a.tq < 16 || a.tq > kTcrTQ || (a.tq & 15) ||
-        tcr_stages(smem, KP, a.tq, 2 * ((a.nf4 + 1) >> 1)) < 3)
+    if (a.tq < 16 || a.tq > RShape<SMALL>::MaxTQ || (a.tq & 15) ||
+        tcr_stages(smem, KP, a.tq, 2 * ((a.nf4 + 1) >> 1), !SMALL) < 3)
         return cudaErrorInvalidValue;
     const int dbg = g_tc_dbg.load(std::memory_order_relaxed); // B200IVF_TC_DBG / "tc_dbg"
     a.dbg = a.nlists > 1 ? dbg : 0; // timing experiments; never for the coarse quantizer
-    auto kern = ivf_scan_tcr_kernel<METRIC, KP>;
+    auto kern = ivf_scan_tcr_kernel<METRIC, KP, SMALL>;
     cudaError_t e =
             cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess)
@@ -893,7 +925,8 @@ static cudaError_t launch_tcr_one(uint32_t max_items, const TcScanArgs& a_in, cu
         a.trace = buf;
         a.trace_item = (uint32_t)atoi(tr);
     }
-    kern<<<max_items, kRThreads, smem, st>>>(a, *reinterpret_cast<const CUtensorMap*>(a.tmap));
+    kern<<<max_items, RShape<SMALL>::Threads, smem, st>>>(
+            a, *reinterpret_cast<const CUtensorMap*>(a.tmap));
     count_launches(1);
     g_tc_launches.fetch_add(1, std::memory_order_relaxed);
     if (a.trace) {
@@ -926,6 +959,15 @@ static cudaError_t launch_tcr_one(uint32_t max_items, const TcScanArgs& a_in, cu
     return cudaGetLastError();
 }
 
+// tq <= 32: the two-CTAs-per-SM shape, else the whole-SM one
+template <int METRIC, int KP>
+static cudaError_t launch_tcr_one(uint32_t max_items, const TcScanArgs& a, cudaStream_t st) {
+    if (a.tq <= RShape<true>::MaxTQ &&
+        tcr_stages(kRSmemSmall, KP, a.tq, 2 * ((a.nf4 + 1) >> 1), false) >= 3)
+        return launch_tcr_shape<METRIC, KP, true>(max_items, a, st);
+    return launch_tcr_shape<METRIC, KP, false>(max_items, a, st);
+}
+
 // queries per item for dimension nf4*4 and kp kept keys: the largest multiple of 16 (<= kTcrTQ) that
 // leaves the raw ring at least 4 stages; 0 = the kernel cannot take this shape
 int scan_tcr_tq(int nf4, int kp) {
@@ -941,6 +983,16 @@ int scan_tcr_tq(int nf4, int kp) {
 // keys kept per partial list for a request of k: always a few more than k, because the scores
 // that select them are 3xTF32 ones and the exact fp32 re-rank (select.cu) can only re-order what
 // was kept: margin >= 4 for k <= 12, >= 8 above
+// queries per item of the two-CTAs-per-SM shape (<= 32), 0 = that shape cannot take (nf4, kp)
+int scan_tcr_tq_small(int nf4, int kp) {
+    if (!scan_tcr_tq(nf4, kp))
+        return 0;
+    const int nch = 2 * ((nf4 + 1) >> 1);
+    for (int tq = RShape<true>::MaxTQ; tq >= 16; tq -= 16)
+        if (tcr_stages(kRSmemSmall, kp, tq, nch, false) >= 3)
+            return tq;
+    return 0;
+}
 int scan_tcr_kpart(int nf4, int k) {
     const int kp = k + 4 <= 16 ? 16
             : k + 8 <= 32      ? 32
