@@ -262,7 +262,8 @@ struct IndexIVFFlatB200::Impl {
     double tcr_small_factor = 1.0;
     double tcr_small_max_avg_q = 1e9; // (cap for A/B runs; the rule is 3/4 of the small item size)
     unsigned long long graph_replays = 0;
-    int coarse_s_override = 0;  // B200IVF_COARSE_S (read once, at construction)
+    int coarse_s_override = 0;  // B200IVF_COARSE_S (read once, at construction) / "coarse_s"
+    int coarse_tq = 0;          // "coarse_tq": queries per item of the rows-major coarse scan
     bool trace_sync = false;    // B200IVF_TC_TRACE set: no graphs, no asynchronous returns
     void drop_graphs() {
         for (auto& kv : graphs)
@@ -557,7 +558,12 @@ void IndexIVFFlatB200::run_coarse_(const float* xd, int64_t n, int kc, int32_t* 
     // full 128-query tiles: the queries-major kernel where it exists
     const bool tcr = tc && (kp_q == 0 || (m.tc_mode == 2 && kp_r > 0));
     const int kp = tc ? (tcr ? kp_r : kp_q) : kc;
-    const int tcr_tq = tcr ? scan_tcr_tq(nf4, kp) : 0;
+    int tcr_tq = tcr ? scan_tcr_tq(nf4, kp) : 0;
+    if (tcr && m.coarse_tq > 0) { // tuning experiments
+        const int small = scan_tcr_tq_small(nf4, kp);
+        tcr_tq = m.coarse_tq <= small ? std::min(m.coarse_tq, small) : std::min(m.coarse_tq, tcr_tq);
+        tcr_tq = std::max(16, tcr_tq & ~15);
+    }
     const TileCfg tcfg = choose_tile_cfg(nf4, kp);
     // few queries: a warp carries no more query accumulators than there are queries
     const ScanCfg cfg = choose_scan_cfg(nf4, kp, n <= 1 ? 1 : (n <= 4 ? 4 : 8));
@@ -769,7 +775,7 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
     const IDSelector* sel = params ? params->sel : nullptr;
     const size_t mc = params ? params->max_codes : max_codes;
     B200_THROW_IF_NOT_MSG(!(sel && store_pairs), "selector and store_pairs cannot be combined");
-    // selector / max_codes: the exact SIMT scan with a row mask and per-pair row limits
+    // selector / max_codes: a row mask and per-pair row limits in the scan
     const bool filtered = sel != nullptr || mc > 0;
     // an invalid key met by an earlier asynchronous call surfaces here (its counter has landed in
     // the pinned stats copy by now, or will have by the next call)
@@ -807,11 +813,14 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
     const double avg_q = pairs_own / std::max(1.0, std::min((double)nlists_owned, pairs_own));
     // hardly any list shared between queries (small batches, huge nlist): nothing to multiply, the
     // scan is a pure stream -> the SIMT warp kernel alone (exact fp32, no re-rank needed)
-    const bool simt_only =
-            filtered || !m.use_tc || avg_q <= m.simt_max_avg_q || (kp_q == 0 && kp_r == 0);
+    // A filtered search (selector / max_codes) keeps the list-major reuse: the rows-major
+    // tensor-core kernel has the mask and row-limit arms (the queries-major one does not).
+    const bool simt_only = (filtered && kp_r == 0) || !m.use_tc || avg_q <= m.simt_max_avg_q ||
+            (kp_q == 0 && kp_r == 0);
     const bool tc = !simt_only;
-    const bool tcr = tc && (kp_q == 0 || (kp_r > 0 && (m.tc_mode == 2 || (m.tc_mode == 0 &&
-                                                                          avg_q < m.tcr_max_avg_q))));
+    const bool tcr = tc && (filtered || kp_q == 0 ||
+                            (kp_r > 0 && (m.tc_mode == 2 ||
+                                          (m.tc_mode == 0 && avg_q < m.tcr_max_avg_q))));
     const int64_t kp = tc ? (tcr ? kp_r : kp_q) : k; // entries per partial list
     // few queries per list: the two-CTAs-per-SM shape of the rows-major kernel (<= 32 queries per
     // item; a list probed by more is cut into several items)
@@ -982,6 +991,10 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
             ta.qthr = m.qthr.as<uint32_t>();
             ta.item_list = m.item_list.as<int32_t>();
             ta.tq = tcr_tq;
+            if (tcr) {
+                ta.row_mask = row_mask;
+                ta.pair_limit = mc > 0 ? m.limit_slot.as<int32_t>() : nullptr;
+            }
             if (tcr)
                 CUDA_CHECK(launch_ivf_scan_tcr(metric_type, (uint32_t)max_tc_items, ta, st));
             else
@@ -1328,6 +1341,10 @@ void IndexIVFFlatB200::set_option(const char* name, double value) {
         m.simt_max_avg_q = value;
     else if (n == "tcr_max_avg_q")
         m.tcr_max_avg_q = value;
+    else if (n == "coarse_tq")
+        m.coarse_tq = (int)value;
+    else if (n == "coarse_s")
+        m.coarse_s_override = (int)value;
     else if (n == "tcr_small_factor")
         m.tcr_small_factor = value;
     else if (n == "tcr_small_max_avg_q")

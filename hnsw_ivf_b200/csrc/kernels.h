@@ -107,6 +107,10 @@ struct TcScanArgs {
     // query across its probes, faiss/IndexIVF.cpp:597-631; this is that heap's top). Filled with
     // ordered_bits(FLT_MAX) before the launch (launch_fill_u32). nullptr: off.
     uint32_t* qthr = nullptr;
+    // SearchParametersIVF (rows-major kernel only): selector row mask ([slab blocks], bit = row in
+    // block) and max_codes row limits per pair slot; nullptr = unfiltered
+    const uint32_t* row_mask = nullptr;
+    const int32_t* pair_limit = nullptr;
     unsigned long long* trap = nullptr; // host-mapped note of a wait that gave up (tc_trap_info_*)
     long long* trace = nullptr; // timing experiments only (B200IVF_TC_TRACE=<item>): clock64
     uint32_t trace_item = 0;    // stamps of one CTA, [role][tile]

@@ -195,6 +195,7 @@ struct RSmem {
     float* xn;          // [kTcrTQ] |x|^2 (L2) or 0
     int* cnt;           // [kTcrTQ] entries in the candidate buffer (may run past C: overflow)
     int* qid;           // [kTcrTQ] query number
+    int* lim;           // [kTcrTQ] rows of the list that count for the query (max_codes)
     int* flag;          // [4] by barrier epoch: 1 = some buffer wants compaction, 2 = overflowed
     uint64_t* full;     // [kRMaxStages] TMA landed
     uint64_t* empty;    // [kRMaxStages] the split warps have the stage in registers AND the MMAs
@@ -216,7 +217,7 @@ __host__ __device__ inline uint32_t tcr_lbo(int n16) {
 }
 __host__ __device__ inline size_t tcr_rest_bytes(int kp, int n16, int nch) {
     return (size_t)nch * tcr_lbo(n16) + (size_t)n16 * tcr_cand(kp) * 8 +
-            (size_t)kTcrTQ * 6 * 4 + 4 * 4 + (2 * kRMaxStages + 2 * kRAStages + 4) * 8 + 16;
+            (size_t)kTcrTQ * 7 * 4 + 4 * 4 + (2 * kRMaxStages + 2 * kRAStages + 4) * 8 + 16;
 }
 __host__ __device__ inline int tcr_stages(size_t smem_total, int kp, int n16, int nch,
                                           bool even = true) {
@@ -248,7 +249,8 @@ __device__ __forceinline__ RSmem carve_r(unsigned char* raw, int nst, int n16, i
     s.xn = s.thrf + kTcrTQ;
     s.cnt = reinterpret_cast<int*>(s.xn + kTcrTQ);
     s.qid = s.cnt + kTcrTQ;
-    s.flag = s.qid + kTcrTQ;
+    s.lim = s.qid + kTcrTQ;
+    s.flag = s.lim + kTcrTQ;
     s.full = reinterpret_cast<uint64_t*>(s.flag + 4);
     s.empty = s.full + kRMaxStages;
     s.a_rdy = s.empty + kRMaxStages;
@@ -531,6 +533,8 @@ __global__ void __launch_bounds__(RShape<SMALL>::Threads, RShape<SMALL>::CtasPer
                     if (q >= 0 && a.qthr)
                         tb = min(tb, a.qthr[q]);
                     s.qid[n] = q;
+                    s.lim[n] = (a.pair_limit != nullptr && q >= 0) ? a.pair_limit[q0 + n]
+                                                                    : 0x7fffffff;
                     s.xn[n] = xnq;
                     s.cnt[n] = 0;
                     s.thr[n] = tb;
@@ -711,8 +715,15 @@ __global__ void __launch_bounds__(RShape<SMALL>::Threads, RShape<SMALL>::CtasPer
         for (int t = 0; t < ntiles; ++t) {
             const int b = t & 1;
             const int r_in_split = t * (kRTileBlocks * kBlockRows) + quarter * 32 + lane;
-            const bool valid = r_in_split < row_lim;
+            bool valid = r_in_split < row_lim;
             const uint32_t rowid = (blk0 + (uint32_t)b0) * kBlockRows + (uint32_t)r_in_split;
+            // SearchParametersIVF::sel (IVFFlatScanner's use_sel arm, faiss/IndexIVFFlat.cpp:166):
+            // the selector was evaluated into one mask word per 32-row block, bit = lane
+            if (a.row_mask != nullptr && valid)
+                valid = (__ldg(a.row_mask + (rowid >> 5)) >> lane) & 1u;
+            // max_codes: only the first pair_limit[pair] rows of the list count for a query
+            // (scan_one_list's list_size_max, faiss/IndexIVF.cpp:545-548)
+            const int row_in_list = b0 * kBlockRows + r_in_split;
             // a row that does not exist scores +inf
             const float nrm = !valid ? __int_as_float(0x7f800000)
                                      : (METRIC == kMetricL2 ? __ldg(a.norms + rowid) : 0.f);
@@ -781,7 +792,8 @@ __global__ void __launch_bounds__(RShape<SMALL>::Threads, RShape<SMALL>::CtasPer
                         ++n_events;
                         const int qi = ch * 16 + j;
                         const float sc = __uint_as_float(sel16(v, j)) + nrm;
-                        if (sc <= s.thrp[qi]) {
+                        if (sc <= s.thrp[qi] &&
+                            (a.pair_limit == nullptr || row_in_list < s.lim[qi])) {
                             const int slot = atomicAdd(&s.cnt[qi], 1);
                             if (slot < C) {
                                 s.cand[(size_t)qi * C + slot] = make_key(sc + s.xn[qi], rowid);
