@@ -174,6 +174,18 @@ CLOCK_FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.a
                 "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
 
+def clock_soak(step, barrier, ms_per_step, covered_ms, want_ms=500.0):
+    """Untimed repeats of the timed step so that nvidia-smi sees >= want_ms of the same load. The
+    count is computed from rank-reduced times, so every rank makes the same number of (collective)
+    calls."""
+    n = int(max(0.0, want_ms - covered_ms) / max(ms_per_step, 1e-3))
+    n = min(n, 5000)
+    for _ in range(n):
+        step()
+    barrier()
+    return n
+
+
 class ClockSampler:
     def __init__(self, gpu_index):
         self.gpu, self.p, self.path = gpu_index, None, "/tmp/b200ivf_clocks_%d.csv" % os.getpid()
@@ -183,7 +195,7 @@ class ClockSampler:
             self.f = open(self.path, "w")
             self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu),
                                        "--query-gpu=" + CLOCK_FIELDS, "--format=csv,noheader,nounits",
-                                       "-lms", "100"], stdout=self.f, stderr=subprocess.DEVNULL)
+                                       "-lms", "20"], stdout=self.f, stderr=subprocess.DEVNULL)
         except OSError:
             self.p = None
 
@@ -512,14 +524,17 @@ def bench_flat(args, ctx, tf32_peak):
             dist.barrier()
         torch.cuda.synchronize()
 
+    # the sampler runs from the warm-up to the end of the second timed region (a 20-step timed
+    # region is ~20-40 ms: nvidia-smi needs longer than that just to attach), and through a short
+    # untimed soak of the same step after it when the whole window was under half a second
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
     for _ in range(max(args.warmup, 3)):
         step_device()
     barrier()
     g.reset_stats()
     index.reset_phase_times()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
     launches0 = b2.kernel_launches()
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -564,7 +579,6 @@ def bench_flat(args, ctx, tf32_peak):
     barrier()
     t_wall = time.perf_counter() - t_wall
     ms_e2e = max(h0.elapsed_time(h1), 0.0)
-    clocks = sampler.stop() if rank == 0 else None
 
     # per-rank figures to rank 0
     mine = {"scan_ms": stage["scan"], "unique_rows": unique_rows, "ndis": ndis_per_step,
@@ -577,6 +591,10 @@ def bench_flat(args, ctx, tf32_peak):
         dist.all_gather_object(per_rank, mine)
     else:
         per_rank = [mine]
+    soak = clock_soak(step_device, barrier, ms / args.steps, (ms + ms_e2e) * 2.0)
+    clocks = sampler.stop() if rank == 0 else None
+    if clocks is not None:
+        clocks["window"] = "warm-up + both timed regions + %d untimed steps of the same call" % soak
 
     # ---- N > 1: the reference's own multi-GPU assertion (faiss/gpu/test/test_multi_gpu.py:88-95)
     parity_vs_single = None
@@ -900,14 +918,14 @@ def bench_c4(args, ctx, tf32_peak, headline):
             dist.barrier()
         torch.cuda.synchronize()
 
+    sampler = ClockSampler(local)
+    if rank == 0 and headline:
+        sampler.start()
     for _ in range(3):
         sh.search(xq, k, D=Dd, I=Id, broadcast_from=root)
     barrier()
     g.reset_stats()
     sh.reset_phase_times()
-    sampler = ClockSampler(local)
-    if rank == 0 and headline:
-        sampler.start()
     launches0 = b2.kernel_launches()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
@@ -943,7 +961,6 @@ def bench_c4(args, ctx, tf32_peak, headline):
         barrier()
         t_wall = time.perf_counter() - t_wall
         ms_e2e = h0.elapsed_time(h1)
-    clocks = sampler.stop() if (rank == 0 and headline) else None
 
     mine = {"scan_ms": stage["scan"], "unique_rows": unique_rows, "ndis": ndis,
             "launches": float(launches), "stage": stage, "rows": int(g.list_sizes().sum())}
@@ -955,6 +972,14 @@ def bench_c4(args, ctx, tf32_peak, headline):
         dist.all_gather_object(per_rank, mine)
     else:
         per_rank = [mine]
+    clocks = None
+    if headline:
+        soak = clock_soak(lambda: sh.search(xq, k, D=Dd, I=Id, broadcast_from=root), barrier,
+                          ms / steps, (ms + ms_e2e) * 2.0)
+        clocks = sampler.stop() if rank == 0 else None
+        if clocks is not None:
+            clocks["window"] = ("warm-up + both timed regions + %d untimed steps of the same call"
+                                % soak)
     del sh, g, Dd, Id
     torch.cuda.empty_cache()
     sl = c4_slice_parity(args, ctx, proj, xq, k) if args.c4_slice > 0 else None
