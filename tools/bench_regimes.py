@@ -225,10 +225,12 @@ def regime_sweep(args, torch, b2, dev):
         k = w["k"]
         Dd = torch.empty((w["nq"], k), dtype=torch.float32, device=dev)
         Id = torch.empty((w["nq"], k), dtype=torch.int64, device=dev)
-        for p, opts in [(p, o) for p in w["nprobes"] for o in option_grid(args.options)]:
+        nprobes = ([int(t) for t in args.sweep_nprobes.split(",")] if args.sweep_nprobes
+                   else w["nprobes"])
+        for p, opts in [(p, o) for p in nprobes for o in option_grid(args.options)]:
             g.nprobe = p
-            for name, v in opts.items():
-                g.set_option(name, v)
+            for oname, v in opts.items():
+                g.set_option(oname, v)
             ur = unique_rows(torch, g, xq, p, w["nlist"])
             for _ in range(3):
                 g.search(xq, k, D=Dd, I=Id)
@@ -269,6 +271,7 @@ def main():
                     help="C5: only run three searches of this batch size between cudaProfilerStart/Stop")
     ap.add_argument("--nprobes", default="1,2,4,8,16,32,64")
     ap.add_argument("--workloads", default="C1,C2,C3")
+    ap.add_argument("--sweep-nprobes", default="", help="sweep: these instead of the workload's list")
     ap.add_argument("--options", default="",
                     help="A/B runs: name=v1:v2:...,name2=... every combination of set_option values "
                          "is measured at every nprobe (e.g. simt_max_avg_q=1.5:4:8)")
