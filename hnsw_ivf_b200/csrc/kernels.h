@@ -111,6 +111,11 @@ struct TcScanArgs {
     // block) and max_codes row limits per pair slot; nullptr = unfiltered
     const uint32_t* row_mask = nullptr;
     const int32_t* pair_limit = nullptr;
+    // 1 = ONE tcgen05.mma per 8 dimensions (tf32(x) . trunc_tf32(y)) instead of the 3xTF32 split:
+    // scores are then good to |x||y| (2^-10 + 2^-11 + slack) only, and the k-select must be told
+    // (SelectArgs::err_coef) so that it re-scores everything inside that window and checks that
+    // nothing outside it could matter
+    int one_mma = 0;
     unsigned long long* trap = nullptr; // host-mapped note of a wait that gave up (tc_trap_info_*)
     long long* trace = nullptr; // timing experiments only (B200IVF_TC_TRACE=<item>): clock64
     uint32_t trace_item = 0;    // stamps of one CTA, [role][tile]

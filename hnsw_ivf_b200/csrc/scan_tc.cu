@@ -370,9 +370,13 @@ __global__ void __launch_bounds__(kTcThreads, 1)
                                 const uint64_t kh = dhi + (uint64_t)(ks * ((2 * kTcLBO) >> 4));
                                 const uint64_t kl = dlo + (uint64_t)(ks * ((2 * kTcLBO) >> 4));
                                 // small terms first, the big product last
-                                mma_tf32_ts(tD, alo + ks * 8, kh, idesc, (sg | ks) != 0 ? 1u : 0u);
-                                mma_tf32_ts(tD, ahi + ks * 8, kl, idesc, 1u);
-                                mma_tf32_ts(tD, ahi + ks * 8, kh, idesc, 1u);
+                                if (a.dbg & 16) { // timing experiment: the hi x hi product alone
+                                    mma_tf32_ts(tD, ahi + ks * 8, kh, idesc, (sg | ks) != 0 ? 1u : 0u);
+                                } else {
+                                    mma_tf32_ts(tD, alo + ks * 8, kh, idesc, (sg | ks) != 0 ? 1u : 0u);
+                                    mma_tf32_ts(tD, ahi + ks * 8, kl, idesc, 1u);
+                                    mma_tf32_ts(tD, ahi + ks * 8, kh, idesc, 1u);
+                                }
                             }
                         }
                     }
@@ -383,9 +387,13 @@ __global__ void __launch_bounds__(kTcThreads, 1)
                         if (ks < ksn) {
                             const uint64_t kh = dhi + (uint64_t)(ks * ((2 * kTcLBO) >> 4));
                             const uint64_t kl = dlo + (uint64_t)(ks * ((2 * kTcLBO) >> 4));
-                            mma_tf32_ts(tD, alo + ks * 8, kh, idesc, 1u);
-                            mma_tf32_ts(tD, ahi + ks * 8, kl, idesc, 1u);
-                            mma_tf32_ts(tD, ahi + ks * 8, kh, idesc, 1u);
+                            if (a.dbg & 16) {
+                                mma_tf32_ts(tD, ahi + ks * 8, kh, idesc, 1u);
+                            } else {
+                                mma_tf32_ts(tD, alo + ks * 8, kh, idesc, 1u);
+                                mma_tf32_ts(tD, ahi + ks * 8, kl, idesc, 1u);
+                                mma_tf32_ts(tD, ahi + ks * 8, kh, idesc, 1u);
+                            }
                         }
                         mma_commit(&s.empty[st]);
                         mma_commit(&s.lo_empty[ls]);

@@ -394,6 +394,9 @@ __global__ void __launch_bounds__(RShape<SMALL>::Threads, RShape<SMALL>::CtasPer
 
     const RSmem s = carve_r<KP>(smem_raw, nst, n16, 2 * nks);
     const bool tracing = a.trace != nullptr && item == a.trace_item;
+    // one MMA per k-step (y_hi . x_hi only): the tensor core is a FILTER with a known error bound,
+    // see TcScanArgs::one_mma
+    const bool one = a.one_mma != 0;
     if (tid == 0) {
         TCR_TRACE(0, 0);
         if (tracing) {
@@ -405,7 +408,7 @@ __global__ void __launch_bounds__(RShape<SMALL>::Threads, RShape<SMALL>::CtasPer
     if (tid == 0) {
         for (int i = 0; i < kRMaxStages; ++i) {
             mbar_init(&s.full[i], 1);
-            mbar_init(&s.empty[i], 4 + 1); // one split group (4 warps) + the MMA commit
+            mbar_init(&s.empty[i], one ? 1 : 4 + 1); // one split group (4 warps) + the MMA commit
         }
         for (int i = 0; i < kRAStages; ++i) {
             mbar_init(&s.a_rdy[i], 4);
@@ -508,6 +511,12 @@ __global__ void __launch_bounds__(RShape<SMALL>::Threads, RShape<SMALL>::CtasPer
                     h.y = x.y * scale;
                     h.z = x.z * scale;
                     h.w = x.w * scale;
+                    if (one) { // no lo part follows: round to nearest instead of the MMA's truncation
+                        h.x = tf32_rn(h.x);
+                        h.y = tf32_rn(h.y);
+                        h.z = tf32_rn(h.z);
+                        h.w = tf32_rn(h.w);
+                    }
                     lo.x = tf32_lo(h.x);
                     lo.y = tf32_lo(h.y);
                     lo.z = tf32_lo(h.z);
@@ -553,18 +562,22 @@ __global__ void __launch_bounds__(RShape<SMALL>::Threads, RShape<SMALL>::CtasPer
 
     if (warp == kRMmaWarp) {
         // ======================= MMA issuer =====================================================
-        // The whole warp runs the loop (converged control flow); one elected lane issues.
+        // The whole warp runs the loop (converged control flow); one elected lane issues. What the
+        // issuing lane executes between two tcgen05.mma is what paces this role (an MMA with N <= 64
+        // is 16-32 cycles of tensor pipe, tools/tc_probe.cu): the block under the elect is straight
+        // line, with every operand prepared before it and nothing to decide inside.
         // MMA 1: N = 2 * n16 (x_hi | x_lo stacked), MMA 2: N = n16 (x_hi: the first n16 rows of the
-        // same chunks)
+        // same chunks); one_mma: MMA 1 alone with N = n16
         const uint32_t idesc2 = make_idesc_tf32(kRTileBlocks * kBlockRows, 2 * n16);
         const uint32_t idesc1 = make_idesc_tf32(kRTileBlocks * kBlockRows, n16);
         const uint64_t desc0 = make_smem_desc_kmajor_noswz(0, lbo, kRBSBO);
         const uint64_t adesc0 = make_smem_desc_kmajor_noswz(0, kRALBO, kRASBO);
         const uint32_t b0a = smem_u32(s.b), raw0 = smem_u32(s.raw);
+        const uint64_t kb_step = (uint64_t)((2u * lbo) >> 4);  // 2 chunks of B per k-step
+        constexpr uint64_t ka_step = (2 * kRALBO) >> 4;        // 2 chunks of the raw stage
         tc_fence_after_sync();
         int as = 0, rst = 0;
-        uint32_t aph = 0;
-        bool ready = false;
+        uint32_t aph = 0, rph = 0;
         long long w_ardy = 0, w_dempty = 0, w_issue = 0;
         for (int t = 0; t < ntiles; ++t) {
             const int b = t & 1;
@@ -574,72 +587,67 @@ __global__ void __launch_bounds__(RShape<SMALL>::Threads, RShape<SMALL>::CtasPer
             }
             const uint32_t tD = tmem + kRColsD + (uint32_t)b * kDStride;
             for (int sg = 0; sg < nsg; ++sg) {
-                if (!ready)
+                if (one)
+                    TCR_WAIT(&s.full[rst], rph, w_ardy, 3, t * nsg + sg);
+                else
                     TCR_WAIT(&s.a_rdy[as], aph, w_ardy, 3, t * nsg + sg);
                 tc_fence_after_sync();
                 const long long i0_ = tracing ? clock64() : 0;
                 const int ks0 = sg * (kRKC / 2);
-                const int ksn = (a.dbg & 8) ? 0 : nks - ks0; // >= 1
+                const int ksn = nks - ks0; // >= 1 k-steps of this stage
                 const uint32_t alo = tmem + kRColsA + (uint32_t)as * 32u;
                 // hi: the raw stage itself (2 chunks = 2 * kRALBO bytes per k-step)
                 const uint64_t dah =
                         adesc0 + (uint64_t)((raw0 + (uint32_t)rst * kRStageF4 * 16u) >> 4);
                 // the B descriptor advances by 2 chunks (2 * LBO bytes, in 16-byte units) per k-step
                 const uint64_t db = desc0 + (uint64_t)((b0a + (uint32_t)(ks0 * 2) * lbo) >> 4);
-                const int nas = as + 1 == kAStages ? 0 : as + 1;
-                const uint32_t naph = as + 1 == kAStages ? aph ^ 1u : aph;
+                const uint32_t acc0 = sg != 0 ? 1u : 0u; // the first MMA of a tile overwrites
+                const bool last = sg == nsg - 1;
                 if (elect_one_sync()) {
+                    if (one) {
+                        if (ksn >= kRKC / 2) {
 #pragma unroll
-                    for (int ks = 0; ks < kRKC / 2 - 1; ++ks) {
-                        if (ks < ksn) {
-                            const uint64_t kb = db + (uint64_t)((uint32_t)ks * ((2u * lbo) >> 4));
-                            // the first MMA of a tile overwrites all 2 * n16 columns
-                            const uint64_t ka = dah + (uint64_t)(ks * ((2 * kRALBO) >> 4));
-                            if (!(a.dbg & 512))
-                                mma_tf32_ss(tD, ka, kb, idesc2, (sg | ks) != 0 ? 1u : 0u);
-                            if (!(a.dbg & 256))
-                                mma_tf32_ts(tD, alo + ks * 8, kb, idesc1, 1u);
+                            for (int ks = 0; ks < kRKC / 2; ++ks)
+                                mma_tf32_ss(tD, dah + ks * ka_step, db + ks * kb_step, idesc1,
+                                            ks ? 1u : acc0);
+                        } else {
+                            for (int ks = 0; ks < ksn; ++ks)
+                                mma_tf32_ss(tD, dah + ks * ka_step, db + ks * kb_step, idesc1,
+                                            ks ? 1u : acc0);
                         }
-                    }
-                }
-                __syncwarp();
-                ready = mbar_test_wait(&s.a_rdy[nas], naph); // next stage, MMAs still queued
-                if (elect_one_sync()) {
-                    constexpr int ks = kRKC / 2 - 1;
-                    if (ks < ksn) {
-                        const uint64_t kb = db + (uint64_t)((uint32_t)ks * ((2u * lbo) >> 4));
-                        const uint64_t ka = dah + (uint64_t)(ks * ((2 * kRALBO) >> 4));
-                        if (!(a.dbg & 512))
-                            mma_tf32_ss(tD, ka, kb, idesc2, 1u);
-                        if (!(a.dbg & 256))
-                            mma_tf32_ts(tD, alo + ks * 8, kb, idesc1, 1u);
-                    }
-                    if (a.dbg & 128) {
-                        mbar_arrive(&s.empty[rst]);
-                        mbar_arrive(&s.a_empty[as]);
-                        if (sg == nsg - 1)
-                            mbar_arrive(&s.d_full[b]);
+                        mma_commit(&s.empty[rst]); // the raw stage may be refilled
                     } else {
-                        // (bits 1024 / 2048: plain arrives instead, to time what a commit costs)
-                        if (a.dbg & 1024)
-                            mbar_arrive(&s.empty[rst]);
-                        else
-                            mma_commit(&s.empty[rst]); // the raw stage may be refilled
-                        if (a.dbg & 2048)
-                            mbar_arrive(&s.a_empty[as]);
-                        else
-                            mma_commit(&s.a_empty[as]);
-                        if (sg == nsg - 1)
-                            mma_commit(&s.d_full[b]);
+                        if (ksn >= kRKC / 2) {
+#pragma unroll
+                            for (int ks = 0; ks < kRKC / 2; ++ks) {
+                                mma_tf32_ss(tD, dah + ks * ka_step, db + ks * kb_step, idesc2,
+                                            ks ? 1u : acc0);
+                                mma_tf32_ts(tD, alo + ks * 8, db + ks * kb_step, idesc1, 1u);
+                            }
+                        } else {
+                            for (int ks = 0; ks < ksn; ++ks) {
+                                mma_tf32_ss(tD, dah + ks * ka_step, db + ks * kb_step, idesc2,
+                                            ks ? 1u : acc0);
+                                mma_tf32_ts(tD, alo + ks * 8, db + ks * kb_step, idesc1, 1u);
+                            }
+                        }
+                        mma_commit(&s.empty[rst]);
+                        mma_commit(&s.a_empty[as]);
                     }
+                    if (last)
+                        mma_commit(&s.d_full[b]);
                 }
                 __syncwarp();
-                if (++rst == nst)
+                if (++rst == nst) {
                     rst = 0;
+                    rph ^= 1u;
+                }
+                if (++as == kAStages) {
+                    as = 0;
+                    aph ^= 1u;
+                }
                 if (tracing)
                     w_issue += clock64() - i0_;
-                as = nas;
-                aph = naph;
             }
             if (lane == 0)
                 TCR_TRACE(2, t);
@@ -659,7 +667,7 @@ __global__ void __launch_bounds__(RShape<SMALL>::Threads, RShape<SMALL>::CtasPer
         const int row = quarter * 32 + lane;
         const uint32_t lane_addr = (uint32_t)(quarter * 32) << 16;
         long long w_full = 0, w_aempty = 0;
-        for (int it = grp; it < niter; it += kRSplitGroups) {
+        for (int it = grp; it < niter && !one; it += kRSplitGroups) {
             const int st = it % nst;
             const uint32_t ph = (uint32_t)((it / nst) & 1);
             const int as = it % kAStages;
@@ -746,13 +754,19 @@ __global__ void __launch_bounds__(RShape<SMALL>::Threads, RShape<SMALL>::CtasPer
                         continue;
                     {
                         // y_hi.x_hi + y_lo.x_hi sits in column j, y_hi.x_lo in column n16 + j
-                        uint32_t w[16];
-                        tmem_ld_32x32b_x16(tD + (uint32_t)ch * 16u, v);
-                        tmem_ld_32x32b_x16(tD + (uint32_t)(n16 + ch * 16), w);
-                        tmem_ld_wait();
+                        if (one) {
+                            tmem_ld_32x32b_x16(tD + (uint32_t)ch * 16u, v);
+                            tmem_ld_wait();
+                        } else {
+                            uint32_t w[16];
+                            tmem_ld_32x32b_x16(tD + (uint32_t)ch * 16u, v);
+                            tmem_ld_32x32b_x16(tD + (uint32_t)(n16 + ch * 16), w);
+                            tmem_ld_wait();
 #pragma unroll
-                        for (int j = 0; j < 16; ++j)
-                            v[j] = __float_as_uint(__uint_as_float(v[j]) + __uint_as_float(w[j]));
+                            for (int j = 0; j < 16; ++j)
+                                v[j] = __float_as_uint(__uint_as_float(v[j]) +
+                                                       __uint_as_float(w[j]));
+                        }
                     }
                     if (a.dbg & 1)
                         continue;
@@ -919,6 +933,8 @@ static cudaError_t launch_tcr_shape(uint32_t max_items, const TcScanArgs& a_in, 
         return cudaErrorInvalidValue;
     const int dbg = g_tc_dbg.load(std::memory_order_relaxed); // B200IVF_TC_DBG / "tc_dbg"
     a.dbg = a.nlists > 1 ? dbg : 0; // timing experiments; never for the coarse quantizer
+    if (a.dbg & 4096)
+        a.one_mma = 1;
     auto kern = ivf_scan_tcr_kernel<METRIC, KP, SMALL>;
     cudaError_t e =
             cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

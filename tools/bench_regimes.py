@@ -99,6 +99,16 @@ def regime_c5(args, torch, b2, dev):
             g.search(xq_np[r * bs:(r + 1) * bs], w["k"])
         torch.cuda.cudart().cudaProfilerStop()
         return
+    # the reference on this box's host cores, same index, same batches (BASELINE.md section 4;
+    # timing model: tutorial/cpp/benchmark-ivf/benchmark_ivf.cpp:309, one search call per batch)
+    cpu = None
+    if not args.no_cpu:
+        lists = ((l,) + tuple(reversed(g.get_list(l))) for l in range(w["nlist"]))
+        idx, kind, po = B.make_cpu_index(w, cent.cpu().numpy(), lists)
+        threads = os.cpu_count() or 1
+        if kind == "reference":
+            po.ref_set_threads(threads)
+        cpu = (idx, kind, po, threads)
     for bs in (1, 2, 4, 8, 16, 32, 64):
         D = np.empty((bs, w["k"]), np.float32)
         I = np.empty((bs, w["k"]), np.int64)
@@ -142,6 +152,28 @@ def regime_c5(args, torch, b2, dev):
             q0 = (r * bs) % (w["nq"] - bs + 1)
             rows.append(unique_rows(torch, g, xq[q0:q0 + bs].contiguous(), 32, w["nlist"]))
         ub = statistics.mean(rows) * w["d"] * 4
+        cpu_out = None
+        if cpu is not None:
+            idx, kind, po, threads = cpu
+            cw, same, slots = [], 0, 0
+            creps = max(20, min(reps, 200))
+            for r in range(creps + 5):
+                q0 = (r * bs) % (w["nq"] - bs + 1)
+                xs = np.ascontiguousarray(xq_np[q0:q0 + bs])
+                t0 = time.perf_counter()
+                Dc, Ic = B.cpu_search(idx, kind, po, xs, w["k"], 32, threads)
+                t1 = time.perf_counter()
+                if r >= 5:
+                    cw.append((t1 - t0) * 1e6)
+                if r < 8:
+                    g.search(xs, w["k"], D=D, I=I)
+                    same += int((np.asarray(Ic) == I).sum())
+                    slots += I.size
+            cpu_out = {"kind": kind, "cores": threads, "reps": creps,
+                       "call_us": {"p50": pct(cw, 50), "p99": pct(cw, 99),
+                                   "mean": statistics.mean(cw)},
+                       "qps": bs / (statistics.mean(cw) * 1e-6),
+                       "id_slots_equal_to_gpu": [same, slots]}
         out = {"regime": "C5", "workload": w["desc"], "nb": w["nb"], "batch": bs, "reps": reps,
                "host_call_us": {"p50": pct(wall, 50), "p99": pct(wall, 99), "mean": statistics.mean(wall)},
                "device_resident_call_us": {"p50": pct(dwall, 50), "p99": pct(dwall, 99)},
@@ -152,6 +184,7 @@ def regime_c5(args, torch, b2, dev):
                "scan_gbs": ub / (pct(scan, 50) * 1e-6) / 1e9,
                "scan_frac_of_hbm_peak": ub / (pct(scan, 50) * 1e-6) / 1e9 / peak,
                "centroid_table_bytes": w["nlist"] * w["d"] * 4,
+               "cpu_baseline": cpu_out,
                "build": tb}
         print(json.dumps(out), flush=True)
 
@@ -267,6 +300,7 @@ def main():
     ap.add_argument("--reps", type=int, default=300)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--niter", type=int, default=10)
+    ap.add_argument("--no-cpu", action="store_true", help="C5: skip the reference's latency")
     ap.add_argument("--profile-batch", type=int, default=0,
                     help="C5: only run three searches of this batch size between cudaProfilerStart/Stop")
     ap.add_argument("--nprobes", default="1,2,4,8,16,32,64")

@@ -37,6 +37,57 @@ __device__ __forceinline__ float tf32_rn(float x) { // round to nearest (ties aw
     return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xffffe000u);
 }
 
+
+// rows-major issue forms, BLK k-steps per elect block (bits 20..: see main): per 1 SS alone,
+// 2 SS + TS, 3 SS(2N) + TS, 4 TS alone
+template <int BLK>
+__device__ __forceinline__ void issue_rows_major(int reps, int per, int nn, uint32_t tD, uint32_t tAlo,
+                                                 uint32_t bhi, uint32_t blo, uint64_t* bars,
+                                                 bool commits, bool lane0_loop) {
+    const uint32_t idesc = make_idesc_tf32(M, nn);
+    const uint32_t id2 = make_idesc_tf32(M, 2 * nn > 256 ? 256 : 2 * nn);
+    const uint64_t d0 = make_smem_desc_kmajor_noswz(0, LBO, SBO);
+    const bool me = lane0_loop ? (threadIdx.x & 31) == 0 : true;
+    if (!me)
+        return;
+    for (int r = 0; r < reps; ++r)
+        for (int g = 0; g < (K / 8) / BLK; ++g) {
+            const uint32_t tDb = tD + ((r & 1) ? 128u : 0u);
+            const uint64_t dhi = d0 + (uint64_t)((bhi + g * BLK * 2 * LBO) >> 4);
+            const uint64_t dlo = d0 + (uint64_t)((blo + g * BLK * 2 * LBO) >> 4);
+            if (lane0_loop || elect_one_sync()) {
+#pragma unroll
+                for (int ks = 0; ks < BLK; ++ks) {
+                    const uint64_t kh = dhi + (uint64_t)(ks * ((2 * LBO) >> 4));
+                    const uint64_t kl = dlo + (uint64_t)(ks * ((2 * LBO) >> 4));
+                    if (per == 5) { // the queries-major triple: operands shared between neighbours
+                        mma_tf32_ts(tDb, tAlo + (g * BLK + ks) * 8, kh, idesc, 1);
+                        mma_tf32_ts(tDb, tAlo + 128 + (g * BLK + ks) * 8, kl, idesc, 1);
+                        mma_tf32_ts(tDb, tAlo + 128 + (g * BLK + ks) * 8, kh, idesc, 1);
+                        continue;
+                    }
+                    if (per == 6) { // three TS MMAs, all operands fresh
+                        mma_tf32_ts(tDb, tAlo + (g * BLK + ks) * 8, kh, idesc, 1);
+                        mma_tf32_ts(tDb, tAlo + 128 + (g * BLK + ks) * 8, kl, idesc, 1);
+                        mma_tf32_ts(tDb, tAlo + ((g * BLK + ks + 1) & 15) * 8, kh + 256, idesc, 1);
+                        continue;
+                    }
+                    if (per != 4)
+                        mma_tf32_ss(tDb, kh, kl, per == 3 ? id2 : idesc, 1);
+                    if (per != 1)
+                        mma_tf32_ts(tDb, tAlo + (g * BLK + ks) * 8, kl, idesc, 1);
+                }
+                if (commits) {
+                    mma_commit(&bars[2]);
+                    if (!(per & 0x40))
+                        mma_commit(&bars[3]);
+                }
+            }
+            if (!lane0_loop)
+                __syncwarp();
+        }
+}
+
 // mode 1: D = A*B^T with raw fp32 bits (one MMA per k-step); mode 3: 3xTF32
 __global__ void __launch_bounds__(256, 1)
         probe_kernel(const float* __restrict__ A, const __grid_constant__ CUtensorMap tmap,
@@ -113,12 +164,24 @@ __global__ void __launch_bounds__(256, 1)
         // the whole warp runs the loop, one elected lane issues (see scan_tcr.cu)
         // timing: `reps` passes over the K loop, nmma MMAs (N = nmma_n) per k-step, one commit
         // bit 8 of nmma: N = 256 (reads past Bhi into Blo); bits 16+: N given explicitly
-        const int nn = (nmma >> 16) ? (nmma >> 16) : ((nmma & 0x100) ? 256 : 128);
+        const int nn = ((nmma >> 16) & 0xff) ? ((nmma >> 16) & 0xff) : ((nmma & 0x100) ? 256 : 128);
         const int per = nmma & 0xff;
         const uint32_t idesc = make_idesc_tf32(M, nn);
         const uint32_t bhi = smem_u32(Bhi), blo = smem_u32(Blo);
         const long long t0 = clock64();
-        if (nmma & 0x4000) {
+        if (nmma & 0x8000) {
+            const int blk = (nmma >> 24) & 0xff ? (nmma >> 24) & 0xff : 4;
+            const int n2 = (nmma >> 16) & 0xff;
+            const bool l0 = (nmma & 0x1000) != 0, cm = (nmma & 0x200) != 0;
+            if (blk == 2)
+                issue_rows_major<2>(reps, per, n2, tD, tAlo, bhi, blo, bars, cm, l0);
+            else if (blk == 4)
+                issue_rows_major<4>(reps, per, n2, tD, tAlo, bhi, blo, bars, cm, l0);
+            else if (blk == 8)
+                issue_rows_major<8>(reps, per, n2, tD, tAlo, bhi, blo, bars, cm, l0);
+            else
+                issue_rows_major<16>(reps, per, n2, tD, tAlo, bhi, blo, bars, cm, l0);
+        } else if (nmma & 0x4000) {
             // the kernels' issue shape: 12 MMAs of a stage (4 k-steps) straight-line under one elect
             const uint64_t d0 = make_smem_desc_kmajor_noswz(0, LBO, SBO);
             for (int r = 0; r < reps; ++r)
@@ -126,7 +189,24 @@ __global__ void __launch_bounds__(256, 1)
                     const uint32_t tDb = tD + ((r & 1) ? 128u : 0u);
                     const uint64_t dhi = d0 + (uint64_t)((bhi + sg * 8 * LBO) >> 4);
                     const uint64_t dlo = d0 + (uint64_t)((blo + sg * 8 * LBO) >> 4);
-                    if (elect_one_sync()) {
+                    if ((nmma & 0x8000) && elect_one_sync()) {
+                        // rows-major forms, straight-line: per 1 SS alone, 2 SS + TS, 3 SS(2N) + TS,
+                        // 4 TS alone
+                        const uint32_t id2 = make_idesc_tf32(M, 2 * nn > 256 ? 256 : 2 * nn);
+#pragma unroll
+                        for (int ks = 0; ks < 4; ++ks) {
+                            const uint64_t kh = dhi + (uint64_t)(ks * ((2 * LBO) >> 4));
+                            const uint64_t kl = dlo + (uint64_t)(ks * ((2 * LBO) >> 4));
+                            if (per != 4)
+                                mma_tf32_ss(tDb, kh, kl, per == 3 ? id2 : idesc, 1);
+                            if (per != 1)
+                                mma_tf32_ts(tDb, tAlo + (sg * 4 + ks) * 8, kl, idesc, 1);
+                        }
+                        if (nmma & 0x200) {
+                            mma_commit(&bars[2]);
+                            mma_commit(&bars[3]);
+                        }
+                    } else if (!(nmma & 0x8000) && elect_one_sync()) {
 #pragma unroll
                         for (int ks = 0; ks < 4; ++ks) {
                             const uint64_t kh = dhi + (uint64_t)(ks * ((2 * LBO) >> 4));
@@ -149,7 +229,22 @@ __global__ void __launch_bounds__(256, 1)
                 const uint64_t dlo = make_smem_desc_kmajor_noswz(blo + ks * 2 * LBO, LBO, SBO);
                 if (!elect_one_sync())
                     continue;
-                if (nmma & 0x400) { // the real kernel's operand order, alternating D buffers
+                if (nmma & 0x8000) {
+                    // rows-major forms (scan_tcr.cu): A = the raw stage through a shared-memory
+                    // descriptor (M = 128 rows), B = nn "queries" from the other region.
+                    //   per 1: SS alone; per 2: SS (N = nn) + TS (A lo from tensor memory, N = nn);
+                    //   per 3: SS with N = 2 nn (stacked) + TS N = nn
+                    const uint32_t idn = make_idesc_tf32(M, nn);
+                    const uint32_t id2 = make_idesc_tf32(M, 2 * nn > 256 ? 256 : 2 * nn);
+                    const uint32_t tDb = tD + ((r & 1) ? 128u : 0u);
+                    if (per == 4) { // TS alone
+                        mma_tf32_ts(tDb, tAlo + ks * 8, dlo, idn, 1);
+                    } else {
+                        mma_tf32_ss(tDb, dhi, dlo, per == 3 ? id2 : idn, 1);
+                        if (per > 1)
+                            mma_tf32_ts(tDb, tAlo + ks * 8, dlo, idn, 1);
+                    }
+                } else if (nmma & 0x400) { // the real kernel's operand order, alternating D buffers
                     // 0x2000: alternate the accumulator every k-step (two dependency chains)
                     const uint32_t tDb =
                             tD + ((((nmma & 0x2000) ? ks : r) & 1) ? 128u : 0u);
@@ -313,7 +408,8 @@ int main() {
     long long* dC;
     CK(cudaMalloc(&dC, 16 * 148));
     for (int grid : {1, 148})
-        for (int nm : {3, 0x403, 0x603, (128 << 16) | 0x403, (96 << 16) | 0x403, (48 << 16) | 0x403,
+        for (int nm : {(4 << 24) | (16 << 16) | 0x8001, (4 << 24) | (64 << 16) | 0x8001, (4 << 24) | (128 << 16) | 0x8001, (4 << 24) | (16 << 16) | 0x8004, (4 << 24) | (64 << 16) | 0x8004, (4 << 24) | (128 << 16) | 0x8004, (4 << 24) | (16 << 16) | 0x8005, (4 << 24) | (64 << 16) | 0x8005, (4 << 24) | (128 << 16) | 0x8005, (4 << 24) | (16 << 16) | 0x8006, (4 << 24) | (64 << 16) | 0x8006, (4 << 24) | (128 << 16) | 0x8006, (4 << 24) | (16 << 16) | 0x8201, (4 << 24) | (64 << 16) | 0x8201, (4 << 24) | (128 << 16) | 0x8201, (4 << 24) | (16 << 16) | 0x8204, (4 << 24) | (64 << 16) | 0x8204, (4 << 24) | (128 << 16) | 0x8204, (4 << 24) | (16 << 16) | 0x8205, (4 << 24) | (64 << 16) | 0x8205, (4 << 24) | (128 << 16) | 0x8205, (4 << 24) | (16 << 16) | 0x8206, (4 << 24) | (64 << 16) | 0x8206, (4 << 24) | (128 << 16) | 0x8206, (16 << 24) | (16 << 16) | 0x8001, (16 << 24) | (64 << 16) | 0x8001, (16 << 24) | (128 << 16) | 0x8001, (16 << 24) | (16 << 16) | 0x8004, (16 << 24) | (64 << 16) | 0x8004, (16 << 24) | (128 << 16) | 0x8004, (16 << 24) | (16 << 16) | 0x8005, (16 << 24) | (64 << 16) | 0x8005, (16 << 24) | (128 << 16) | 0x8005, (16 << 24) | (16 << 16) | 0x8006, (16 << 24) | (64 << 16) | 0x8006, (16 << 24) | (128 << 16) | 0x8006, (16 << 24) | (16 << 16) | 0x8201, (16 << 24) | (64 << 16) | 0x8201, (16 << 24) | (128 << 16) | 0x8201, (16 << 24) | (16 << 16) | 0x8204, (16 << 24) | (64 << 16) | 0x8204, (16 << 24) | (128 << 16) | 0x8204, (16 << 24) | (16 << 16) | 0x8205, (16 << 24) | (64 << 16) | 0x8205, (16 << 24) | (128 << 16) | 0x8205, (16 << 24) | (16 << 16) | 0x8206, (16 << 24) | (64 << 16) | 0x8206, (16 << 24) | (128 << 16) | 0x8206,
+                       3, 0x403, 0x603, (128 << 16) | 0x403, (96 << 16) | 0x403, (48 << 16) | 0x403,
                        (16 << 16) | 0x403, (96 << 16) | 0x2403, (48 << 16) | 0x2403,
                        (16 << 16) | 0x2403, (128 << 16) | 0x4603, (96 << 16) | 0x4603, (64 << 16) | 0x4603, (48 << 16) | 0x4603,
                        (32 << 16) | 0x4603, (16 << 16) | 0x4603}) {
@@ -323,7 +419,11 @@ int main() {
             CK(cudaDeviceSynchronize());
             std::vector<long long> hc(2 * grid);
             CK(cudaMemcpy(hc.data(), dC, 16 * grid, cudaMemcpyDeviceToHost));
-            const int nmma = reps * (K / 8) * (nm & 0xff);
+            const int pp = nm & 0xff;
+            const int per_k = (nm & 0x8000) ? (pp == 1 || pp == 4 ? 1 : (pp >= 5 ? 3 : 2)) : pp;
+            if (grid == 148)
+                continue;
+            const int nmma = reps * (K / 8) * per_k;
             long long mn = hc[1], mx = hc[1];
             for (int b = 0; b < grid; ++b) {
                 mn = std::min(mn, hc[2 * b + 1]);
@@ -331,7 +431,7 @@ int main() {
             }
             printf("timing grid %d, flags 0x%x (N %d), %d MMA/k-step%s: %d MMAs, issue %lld cyc, complete min %lld max %lld "
                    "-> %.1f .. %.1f cyc/MMA\n",
-                   grid, nm & 0xffff, (nm >> 16) ? (nm >> 16) : 128, nm & 0xff, (nm & 0x200) ? " + 2 commits per 12" : "", nmma, hc[0], mn, mx,
+                   grid, nm & 0xff00ffff, ((nm >> 16) & 0xff) ? ((nm >> 16) & 0xff) : 128, nm & 0xff, (nm & 0x200) ? " + 2 commits per 12" : "", nmma, hc[0], mn, mx,
                    (double)mn / nmma, (double)mx / nmma);
         }
     return 0;
