@@ -123,6 +123,7 @@ SYMBOLS = [
     ("b200_IndexIVFFlat_reserve_lists", C.c_int, [_vp, _i64p]),
     ("b200_IndexIVFFlat_get_list_sizes", C.c_int, [_vp, _i64p]),
     ("b200_IndexIVFFlat_stage_time_sums", C.c_ulonglong, [_vp, C.POINTER(C.c_double)]),
+    ("b200_IndexIVFFlat_exact_redo_count", C.c_ulonglong, [_vp]),
     ("b200_IndexIVFFlat_synchronize", C.c_int, [_vp]),
     ("b200_nccl_get_unique_id", C.c_int, [_vp]),
     ("b200_IndexShardsIVFFlat_new", C.c_int,
@@ -590,6 +591,10 @@ class IndexIVFFlat:
         ms = (C.c_double * 5)()
         calls = self._lib.b200_IndexIVFFlat_stage_time_sums(self._h, ms)
         return int(calls), dict(zip(("coarse", "plan", "scan", "select", "total"), list(ms)))
+
+    def exact_redo_count(self):
+        """queries redone on the exact kernel so far (tc_split = 1, see b200ivf_c.h)"""
+        return int(self._lib.b200_IndexIVFFlat_exact_redo_count(self._h))
 
     def set_option(self, name, value):
         """kernel-selection knobs (see b200ivf_c.h); results do not depend on them"""

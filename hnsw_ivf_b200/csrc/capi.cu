@@ -207,6 +207,11 @@ unsigned long long b200_IndexIVFFlat_stage_time_sums(const B200IndexIVFFlat* ind
     guarded([&] { r = H(index)->stage_time_sums(ms5); });
     return r;
 }
+unsigned long long b200_IndexIVFFlat_exact_redo_count(const B200IndexIVFFlat* index) {
+    unsigned long long r = 0;
+    guarded([&] { r = H(index)->exact_redo_count(); });
+    return r;
+}
 int b200_IndexIVFFlat_synchronize(const B200IndexIVFFlat* index) {
     return guarded([&] { H(index)->synchronize(); });
 }

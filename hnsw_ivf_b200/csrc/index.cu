@@ -167,6 +167,12 @@ struct IndexIVFFlatB200::Impl {
     // scratch (grow only)
     Buffer item_list; // list number of every tensor-core work item (written by the plan)
     Buffer qthr; // per-query pruning bound shared by the tensor-core work items of one search
+    // ONE-MMA filter mode of the rows-major scan (TcScanArgs::one_mma, SelectArgs::err_coef):
+    // max |y|^2 over the slab, the queries whose result the checked re-rank could not prove, and
+    // the scratch of their second, exact pass
+    Buffer ymax2, flag_list, flag_count, host_flag, fb_x, fb_D, fb_I, fb_assign, fb_p32;
+    int tc_split = 3;                   // "tc_split": 3 = 3xTF32 (default), 1 = one MMA + checked re-rank
+    unsigned long long fallback_queries = 0; // queries redone on the exact path so far
     Buffer coarse_ids, coarse_dis, part, count, fill, grp_start, item_off, item_off_tile,
             pair_query, slot_of,
             cplan, stage_x, stage_D, stage_I, stage_assign, dev_x, dev_D, dev_I, dev_assign64,
@@ -307,7 +313,7 @@ struct IndexIVFFlatB200::Impl {
             coarse_s_override = atoi(e5);
         trace_sync = getenv("B200IVF_TC_TRACE") != nullptr; // the trace read-out synchronizes
         stage_x.pinned_host = stage_D.pinned_host = stage_I.pinned_host = true;
-        stage_assign.pinned_host = host_stats.pinned_host = true;
+        stage_assign.pinned_host = host_stats.pinned_host = host_flag.pinned_host = true;
         host_query_ndis.pinned_host = host_lims.pinned_host = true;
     }
 };
@@ -541,6 +547,12 @@ inline int64_t ceil_div(int64_t a, int64_t b) {
 // partial lists keep a few more than k entries (scan_tc_kpart), and the k-select re-scores
 // k + kRerankExtra survivors exactly, whenever the tensor-core scan (approximate scores) takes part
 constexpr int kRerankExtra = 8;
+// ONE-MMA filter: |tf32(x) . trunc_tf32(y) - x . y| <= (2^-11 + 2^-10 + 2^-21) |x||y| from the two
+// operand roundings (round-to-nearest for the query, the tensor core's truncation for the rows),
+// plus 2^-13 |x||y| for everything else (fp32 accumulation inside the tensor core and in the exact
+// chain, the norms of the L2 epilogue): E = kOneMmaErrCoef * |x||y| for the inner product and
+// kOneMmaErrCoef * (|x|^2 + |y|^2) >= 2 kOneMmaErrCoef |x||y| for L2 (score = |y|^2 - 2 x.y + |x|^2)
+constexpr float kOneMmaErrCoef = 0.00048828125f + 0.0009765625f + 0.0001220703125f + 4.8e-7f;
 // searches of at most this many queries go through a captured CUDA graph
 constexpr int64_t kGraphMaxBatch = 256;
 
@@ -815,13 +827,21 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
     // scan is a pure stream -> the SIMT warp kernel alone (exact fp32, no re-rank needed)
     // A filtered search (selector / max_codes) keeps the list-major reuse: the rows-major
     // tensor-core kernel has the mask and row-limit arms (the queries-major one does not).
-    const bool simt_only = (filtered && kp_r == 0) || !m.use_tc || avg_q <= m.simt_max_avg_q ||
+    // (not const: the exact second pass of the one-MMA mode switches them, see below)
+    bool simt_only = (filtered && kp_r == 0) || !m.use_tc || avg_q <= m.simt_max_avg_q ||
             (kp_q == 0 && kp_r == 0);
-    const bool tc = !simt_only;
-    const bool tcr = tc && (filtered || kp_q == 0 ||
-                            (kp_r > 0 && (m.tc_mode == 2 ||
-                                          (m.tc_mode == 0 && avg_q < m.tcr_max_avg_q))));
-    const int64_t kp = tc ? (tcr ? kp_r : kp_q) : k; // entries per partial list
+    bool tc = !simt_only;
+    bool tcr = tc && (filtered || kp_q == 0 ||
+                      (kp_r > 0 && (m.tc_mode == 2 ||
+                                    (m.tc_mode == 0 && avg_q < m.tcr_max_avg_q))));
+    // ONE-MMA filter mode (rows-major kernel only): the tensor core computes tf32(x) . tf32(y)
+    // alone -- a third of the MMAs, no operand split -- and the k-select proves, query by query,
+    // that nothing outside the exactly re-scored set could have reached the top k
+    // (SelectArgs::err_coef); the few queries it cannot prove are searched again on the exact
+    // warp kernel before the call returns
+    const int kp_one = scan_tcr_kpart_one(m.nf4, (int)std::min<int64_t>(k, 1 << 20));
+    bool one = tc && tcr && m.tc_split == 1 && kp_one > 0;
+    int64_t kp = tc ? (tcr ? (one ? kp_one : kp_r) : kp_q) : k; // entries per partial list
     // few queries per list: the two-CTAs-per-SM shape of the rows-major kernel (<= 32 queries per
     // item; a list probed by more is cut into several items)
     // (worth it while most lists fit one or two items: up to that shape's item size on average;
@@ -831,7 +851,7 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
         tq_small = 0;
     const int tcr_tq = tcr ? (tq_small ? tq_small : scan_tcr_tq(m.nf4, (int)kp)) : 0;
     BatchPlan bp = plan_batch(m.nf4, kp, nb, np, nlists_owned, m.nstored, simt_only, filtered, own_frac);
-    const int pmul = (tc && !tcr) ? 2 : 1; // partial lists per (pair, split)
+    int pmul = (tc && !tcr) ? 2 : 1; // partial lists per (pair, split)
     const int tc_tq = tcr ? tcr_tq : kTcTQ;
     const int tc_min = tcr ? 0 : kTileMinQueries; // lists with more queries than this: tensor cores
     while (nb > 1 && (size_t)nb * np * bp.S * pmul * kp * sizeof(uint64_t) > ((size_t)2 << 30)) {
@@ -849,6 +869,9 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
 
     // the kernel pipeline of one batch; every pointer is a device pointer. `timed`: stage events
     // are recorded (not while the pipeline is being captured into a graph)
+    bool count_stats = true; // (off for the second pass: its queries were counted by the first)
+    bool want_pq = per_query != nullptr; // per-query nscan (search_stats): first pass only
+    const int32_t* last_probe_tab = nullptr; // the probe table the last enqueue() searched
     auto enqueue = [&](int64_t ni, const float* xd, float* Dd, int64_t* Id, const int64_t* ad,
                        bool timed, const int32_t* p32 = nullptr) {
         const int64_t pairs = ni * np;
@@ -857,6 +880,7 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
         m.coarse_ids.reserve((size_t)pairs * sizeof(int32_t));
         m.coarse_dis.reserve((size_t)pairs * sizeof(float));
         const int32_t* probe_tab = m.coarse_ids.as<int32_t>();
+        last_probe_tab = probe_tab;
         if (p32) {
             // a device table in the plan's own format: read in place unless the max_codes walk is
             // going to edit it (keys >= nlist are counted as invalid by the plan)
@@ -864,7 +888,7 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
                 CUDA_CHECK(cudaMemcpyAsync(m.coarse_ids.p, p32, (size_t)pairs * sizeof(int32_t),
                                            cudaMemcpyDeviceToDevice, st));
             else
-                probe_tab = p32;
+                probe_tab = last_probe_tab = p32;
         } else if (ad) {
             CUDA_CHECK(launch_i64_to_i32(ad, m.coarse_ids.as<int32_t>(), pairs, 0, (int32_t)nlist,
                                          dstats + 3, st));
@@ -874,19 +898,19 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
         }
         if (timed)
             CUDA_CHECK(cudaEventRecord(m.ev[1], st));
-        if (mc > 0 || per_query) {
+        if (mc > 0 || want_pq) {
             if (mc > 0) {
                 m.limit_qp.reserve((size_t)pairs * sizeof(int32_t));
                 m.limit_slot.reserve((size_t)pairs * sizeof(int32_t));
             }
-            if (per_query)
+            if (want_pq)
                 m.query_ndis.reserve((size_t)ni * sizeof(unsigned long long));
             CUDA_CHECK(launch_probe_limits(
                     m.coarse_ids.as<int32_t>(), (int)ni, (int)np, (int)nlist,
                     m.list_len.as<int32_t>(),
                     mc > 0 ? (long long)std::min<size_t>(mc, (size_t)LLONG_MAX) : LLONG_MAX,
                     mc > 0 ? m.limit_qp.as<int32_t>() : nullptr,
-                    per_query ? m.query_ndis.as<unsigned long long>() : nullptr, st));
+                    want_pq ? m.query_ndis.as<unsigned long long>() : nullptr, st));
         }
         // stage 2: invert the probe table, scan the lists
         m.count.reserve(nlist * sizeof(int32_t));
@@ -937,7 +961,7 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
             m.item_list.reserve((size_t)(max_tc_items + 1) * sizeof(int32_t));
             pa.item_list_tile = m.item_list.as<int32_t>();
         }
-        pa.stats = dstats;
+        pa.stats = count_stats ? dstats : nullptr;
         if (mc > 0) {
             pa.limit_qp = m.limit_qp.as<int32_t>();
             pa.limit_slot = m.limit_slot.as<int32_t>();
@@ -994,6 +1018,7 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
             if (tcr) {
                 ta.row_mask = row_mask;
                 ta.pair_limit = mc > 0 ? m.limit_slot.as<int32_t>() : nullptr;
+                ta.one_mma = one ? 1 : 0;
             }
             if (tcr)
                 CUDA_CHECK(launch_ivf_scan_tcr(metric_type, (uint32_t)max_tc_items, ta, st));
@@ -1041,6 +1066,16 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
             se.d = d;
             se.nf4 = m.nf4;
             se.rerank_extra = (int)std::min<int64_t>(kRerankExtra, kp - k);
+            if (one) {
+                // checked re-rank: everything inside the error window of the k-th score is
+                // re-scored (the window holds a handful of rows: a margin of max(16, k / 4))
+                se.rerank_extra = (int)std::min<int64_t>(std::max<int64_t>(16, k / 4), kp - k);
+                se.err_coef = kOneMmaErrCoef;
+                se.ymax2 = m.ymax2.as<float>();
+                se.qthr = m.qthr.as<uint32_t>();
+                se.flag_list = m.flag_list.as<int32_t>();
+                se.flag_count = m.flag_count.as<int32_t>();
+            }
         }
         se.out_dis = Dd;
         se.out_ids64 = Id;
@@ -1073,7 +1108,7 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
     // ---- small batches: one CUDA-graph launch per search (see Impl::GraphEntry) ----
     const bool legacy_stream = st == nullptr || st == cudaStreamLegacy || st == cudaStreamPerThread;
     if (m.use_graph && n <= kGraphMaxBatch && !legacy_stream && !filtered && !store_pairs &&
-        !per_query && !m.trace_sync && !probes32) {
+        !per_query && !m.trace_sync && !probes32 && !one) {
         const int64_t pairs = n * np;
         m.dev_x.reserve((size_t)n * d * sizeof(float));
         m.dev_D.reserve((size_t)n * k * sizeof(float));
@@ -1204,7 +1239,54 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
         }
         double ms_before[5];
         std::copy(m.last_ms, m.last_ms + 5, ms_before);
+        if (one) {
+            m.flag_list.reserve((size_t)ni * sizeof(int32_t));
+            m.flag_count.reserve(sizeof(int32_t));
+            m.host_flag.reserve(sizeof(int32_t));
+            CUDA_CHECK(cudaMemsetAsync(m.flag_count.p, 0, sizeof(int32_t), st));
+        }
         enqueue(ni, xd, Dd, Id, ad, true, probes32 ? probes32 + i0 * np : nullptr);
+        if (one) {
+            // the queries the checked re-rank could not prove: search them again, exactly (same
+            // probe table, the SIMT warp kernel, no statistics: they were counted already)
+            CUDA_CHECK(cudaMemcpyAsync(m.host_flag.p, m.flag_count.p, sizeof(int32_t),
+                                       cudaMemcpyDeviceToHost, st));
+            CUDA_CHECK(cudaStreamSynchronize(st));
+            const int64_t nf = *m.host_flag.as<int32_t>();
+            if (nf > 0) {
+                m.fallback_queries += (unsigned long long)nf;
+                m.fb_x.reserve((size_t)nf * d * sizeof(float));
+                m.fb_D.reserve((size_t)nf * k * sizeof(float));
+                m.fb_I.reserve((size_t)nf * k * sizeof(int64_t));
+                m.fb_p32.reserve((size_t)nf * np * sizeof(int32_t));
+                const int32_t* fl = m.flag_list.as<int32_t>();
+                CUDA_CHECK(launch_gather_rows_w(xd, fl, nf, d, m.fb_x.p, st));
+                CUDA_CHECK(launch_gather_rows_w(last_probe_tab, fl, nf, (int)np, m.fb_p32.p, st));
+                const bool s_simt = simt_only, s_tc = tc, s_tcr = tcr;
+                const int64_t s_kp = kp;
+                const int s_pmul = pmul;
+                simt_only = true;
+                tc = tcr = one = false;
+                kp = k;
+                pmul = 1;
+                count_stats = false;
+                want_pq = false;
+                try {
+                    enqueue(nf, m.fb_x.as<float>(), m.fb_D.as<float>(), m.fb_I.as<int64_t>(),
+                            nullptr, false, m.fb_p32.as<int32_t>());
+                } catch (...) {
+                    simt_only = s_simt, tc = s_tc, tcr = s_tcr, one = true, kp = s_kp, pmul = s_pmul;
+                    count_stats = true;
+                    want_pq = per_query != nullptr;
+                    throw;
+                }
+                simt_only = s_simt, tc = s_tc, tcr = s_tcr, one = true, kp = s_kp, pmul = s_pmul;
+                count_stats = true;
+                want_pq = per_query != nullptr;
+                CUDA_CHECK(launch_scatter_results(m.fb_D.as<float>(), m.fb_I.as<int64_t>(), fl, nf,
+                                                  (int)k, Dd, Id, st));
+            }
+        }
         CUDA_CHECK(cudaEventRecord(m.ev[4], st));
         if (per_query) {
             m.host_query_ndis.reserve((size_t)ni * sizeof(unsigned long long));
@@ -1345,6 +1427,8 @@ void IndexIVFFlatB200::set_option(const char* name, double value) {
         m.coarse_tq = (int)value;
     else if (n == "coarse_s")
         m.coarse_s_override = (int)value;
+    else if (n == "tc_split") // 1 = one MMA + checked re-rank (rows-major kernel), 3 = 3xTF32
+        m.tc_split = value == 1 ? 1 : 3;
     else if (n == "tcr_small_factor")
         m.tcr_small_factor = value;
     else if (n == "tcr_small_max_avg_q")
@@ -1398,6 +1482,11 @@ void IndexIVFFlatB200::last_timings(double* ms5) const {
     finish_async_();
     for (int i = 0; i < 5; ++i)
         ms5[i] = impl_->last_ms[i];
+}
+
+unsigned long long IndexIVFFlatB200::exact_redo_count() const {
+    std::lock_guard<std::mutex> lock(mu_);
+    return impl_->fallback_queries;
 }
 
 unsigned long long IndexIVFFlatB200::stage_time_sums(double* ms5) const {
@@ -1634,9 +1723,11 @@ void IndexIVFFlatB200::ensure_norms_(cudaStream_t st) const {
     Impl& m = *impl_;
     if (!m.norms_dirty)
         return;
+    m.ymax2.reserve(sizeof(float));
+    CUDA_CHECK(cudaMemsetAsync(m.ymax2.p, 0, sizeof(float), st));
     if (m.slab_blocks > 0)
         CUDA_CHECK(launch_row_norms(m.slab.as<float4>(), (int64_t)(m.slab_blocks * kBlockRows),
-                                    m.nf4, m.norms.as<float>(), st));
+                                    m.nf4, m.norms.as<float>(), st, m.ymax2.as<float>()));
     m.norms_dirty = false;
 }
 

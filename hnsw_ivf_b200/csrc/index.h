@@ -157,6 +157,9 @@ class IndexIVFFlatB200 {
     void last_timings(double* ms5) const;
     // the same five stage times summed over the search calls since reset_stats; returns how many
     unsigned long long stage_time_sums(double* ms5) const;
+    // queries searched a second time on the exact kernel because the checked re-rank of the
+    // one-MMA filter mode ("tc_split" = 1) could not prove their result, since construction
+    unsigned long long exact_redo_count() const;
     // wait for the asynchronous calls in flight; a deferred failure (invalid key) is thrown here
     void synchronize() const;
     void set_stream(cudaStream_t s);

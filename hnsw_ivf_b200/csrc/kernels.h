@@ -137,6 +137,9 @@ constexpr int kTcrTQ = 64;
 // d up to 1024; the queries per item shrink with the dimension (the query tile lives in shared
 // memory): scan_tcr_tq(nf4, kpart), 0 = unsupported. scan_tcr_kpart: as scan_tc_kpart.
 int scan_tcr_tq(int nf4, int kp);
+// entries per partial list under the ONE-MMA filter (TcScanArgs::one_mma): the kept set must hold
+// everything inside the error window of the k-th score, so the margin is max(16, k / 4); 0 = none
+int scan_tcr_kpart_one(int nf4, int k);
 // ... and of the two-CTAs-per-SM shape (<= 32 queries per item, half the shared memory): chosen by
 // the launcher whenever TcScanArgs::tq is at most this. 0 = not available for (nf4, kp).
 int scan_tcr_tq_small(int nf4, int kp);
@@ -238,6 +241,20 @@ struct SelectArgs {
     const float* queries = nullptr;
     int d = 0, nf4 = 0;
     int rerank_extra = 0;
+    // Scores that came from the ONE-MMA tensor-core filter (TcScanArgs::one_mma) are only good to
+    //   E(q) = err_coef * (|x_q|^2 + max|y|^2)   (L2)     err_coef * |x_q| * max|y|   (inner product)
+    // of the exact ones. err_coef > 0 turns the re-rank into a CHECKED one: after the k + rerank_extra
+    // best approximate keys have been re-scored exactly, the smallest approximate score B that was
+    // NOT re-scored (the next merged key, the gather bound, or the scan's own pruning bound
+    // qthr[q]: whatever the scan dropped scored at least that) must satisfy B - E > exact k-th
+    // score. Then nothing outside the re-scored set can reach the exact top k (not even as a tie)
+    // and the result is the exact one; otherwise the query number is appended to flag_list for
+    // the caller to redo on the exact path.
+    float err_coef = 0.f;
+    const float* ymax2 = nullptr;      // device scalar: max over the slab rows of |y|^2
+    const uint32_t* qthr = nullptr;    // [n] ordered bits of the scan's final pruning bound
+    int32_t* flag_list = nullptr;      // [n]
+    int32_t* flag_count = nullptr;     // device counter (zeroed by the caller)
 };
 cudaError_t launch_select(const SelectArgs& a, cudaStream_t st);
 
@@ -260,8 +277,14 @@ cudaError_t launch_move_blocks(const float4* old_slab, const int64_t* old_ids,
 cudaError_t launch_gather_rows(const float* slab, int64_t row0, int64_t nrows, int d, int nf4,
                                float* out, cudaStream_t st);
 // |row|^2 of every slab row (the L2 epilogue of the tensor-core scan): rows [0, nrows)
+// max_out (optional, zeroed by the caller): max |row|^2
 cudaError_t launch_row_norms(const float4* slab, int64_t nrows, int nf4, float* norms,
-                             cudaStream_t st);
+                             cudaStream_t st, float* max_out = nullptr);
+// flagged queries of a checked re-rank: rows idx[0..cnt) of a table of `words` 4-byte words per row
+cudaError_t launch_gather_rows_w(const void* in, const int32_t* idx, int64_t cnt, int words,
+                                 void* out, cudaStream_t st);
+cudaError_t launch_scatter_results(const float* Df, const int64_t* If, const int32_t* idx,
+                                   int64_t cnt, int k, float* D, int64_t* I, cudaStream_t st);
 cudaError_t launch_fill_u32(uint32_t* p, int64_t n, uint32_t v, cudaStream_t st);
 // k-means update (Clustering.cpp:150-221 compute_centroids): centroid l = sum of the rows of list l
 // in list order (= input order, the reference's summation order) times 1/len; empty lists give 0

@@ -115,7 +115,8 @@ cudaError_t launch_move_blocks(const float4* old_slab, const int64_t* old_ids,
 
 // one thread per row: lane = row within its 32-row block, so each column read is coalesced
 __global__ void row_norms_kernel(const float4* __restrict__ slab, int64_t nrows, int nf4,
-                                 float* __restrict__ norms) {
+                                 float* __restrict__ norms, float* __restrict__ max_out) {
+    float mx = 0.f;
     for (int64_t row = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; row < nrows;
          row += (int64_t)gridDim.x * blockDim.x) {
         const float4* p =
@@ -129,14 +130,21 @@ __global__ void row_norms_kernel(const float4* __restrict__ slab, int64_t nrows,
             acc = fmaf(v.w, v.w, acc);
         }
         norms[row] = acc;
+        mx = fmaxf(mx, acc);
+    }
+    if (max_out) { // (non-negative floats order like their bit patterns)
+        for (int o = 16; o > 0; o >>= 1)
+            mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        if ((threadIdx.x & 31) == 0 && mx > 0.f)
+            atomicMax(reinterpret_cast<unsigned*>(max_out), __float_as_uint(mx));
     }
 }
 
 cudaError_t launch_row_norms(const float4* slab, int64_t nrows, int nf4, float* norms,
-                             cudaStream_t st) {
+                             cudaStream_t st, float* max_out) {
     if (nrows == 0)
         return cudaSuccess;
-    row_norms_kernel<<<grid_for(nrows, 256), 256, 0, st>>>(slab, nrows, nf4, norms);
+    row_norms_kernel<<<grid_for(nrows, 256), 256, 0, st>>>(slab, nrows, nf4, norms, max_out);
     count_launches(1);
     return cudaGetLastError();
 }
@@ -240,6 +248,47 @@ cudaError_t launch_gather_by_index(const float* x, const int64_t* idx, int64_t n
     const int64_t total = n * d;
     const int grid = (int)std::min<int64_t>((total + threads - 1) / threads, 148 * 16);
     gather_by_index_kernel<<<grid, threads, 0, st>>>(x, idx, n, d, out);
+    count_launches(1);
+    return cudaGetLastError();
+}
+
+// ---- the flagged queries of a checked re-rank (SelectArgs::flag_list) ---------------------------
+// rows idx[0..cnt) of a row-major table to a dense one (cnt is a host value: the caller has read
+// the flag counter); W 4-byte words per row
+__global__ void gather_rows_w_kernel(const uint32_t* __restrict__ in, const int32_t* __restrict__ idx,
+                                     int64_t cnt, int W, uint32_t* __restrict__ out) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < cnt * W;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / W;
+        out[i] = in[(int64_t)idx[r] * W + (i - r * W)];
+    }
+}
+cudaError_t launch_gather_rows_w(const void* in, const int32_t* idx, int64_t cnt, int words,
+                                 void* out, cudaStream_t st) {
+    if (cnt == 0)
+        return cudaSuccess;
+    gather_rows_w_kernel<<<grid_for(cnt * words, 256), 256, 0, st>>>(
+            static_cast<const uint32_t*>(in), idx, cnt, words, static_cast<uint32_t*>(out));
+    count_launches(1);
+    return cudaGetLastError();
+}
+// ... and the result rows of the redone queries back to their places
+__global__ void scatter_results_kernel(const float* __restrict__ Df, const int64_t* __restrict__ If,
+                                       const int32_t* __restrict__ idx, int64_t cnt, int k,
+                                       float* __restrict__ D, int64_t* __restrict__ I) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < cnt * k;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / k;
+        const int64_t o = (int64_t)idx[r] * k + (i - r * k);
+        D[o] = Df[i];
+        I[o] = If[i];
+    }
+}
+cudaError_t launch_scatter_results(const float* Df, const int64_t* If, const int32_t* idx,
+                                   int64_t cnt, int k, float* D, int64_t* I, cudaStream_t st) {
+    if (cnt == 0)
+        return cudaSuccess;
+    scatter_results_kernel<<<grid_for(cnt * k, 256), 256, 0, st>>>(Df, If, idx, cnt, k, D, I);
     count_launches(1);
     return cudaGetLastError();
 }

@@ -337,7 +337,7 @@ __global__ void __launch_bounds__(kTcThreads, 1)
             const uint32_t hi0 = smem_u32(s.hi), lo0 = smem_u32(s.lo);
             int st = 0, ls = 0;
             uint32_t lph = 0;
-            bool ready = false;
+            constexpr uint64_t kstep = (2 * kTcLBO) >> 4; // 2 float4 columns per k-step
             for (int t = 0; t < ntiles; ++t) {
                 const int b = t & 1;
                 if (t >= 2) {
@@ -346,11 +346,8 @@ __global__ void __launch_bounds__(kTcThreads, 1)
                 }
                 const uint32_t tD = tmem + kTcColsD + (uint32_t)b * 128u;
                 for (int sg = 0; sg < nsg; ++sg) {
-                    // lo_rdy implies full: the split warps waited for the TMA before they wrote lo.
-                    // The barrier was usually polled already, between the MMAs of the stage before
-                    // (the tensor pipe's queue is short: it drains during a try_wait).
-                    if (!ready)
-                        mbar_wait(&s.lo_rdy[ls], lph);
+                    // lo_rdy implies full: the split warps waited for the TMA before they wrote lo
+                    mbar_wait(&s.lo_rdy[ls], lph);
                     tc_fence_after_sync();
                     // descriptors advance by 2 columns (2 * LBO bytes, in 16-byte units) per k-step
                     const uint64_t dhi =
@@ -358,53 +355,43 @@ __global__ void __launch_bounds__(kTcThreads, 1)
                     const uint64_t dlo =
                             desc0 + (uint64_t)((lo0 + (uint32_t)ls * kTcStageF4 * 16u) >> 4);
                     const int ks0 = sg * (kTcKC / 2);
-                    const int ksn = (a.dbg & 2) ? 0 : nks - ks0; // >= 1
+                    const int ksn = nks - ks0; // >= 1
                     const uint32_t ahi = tmem + kTcColsAhi + (uint32_t)ks0 * 8u;
                     const uint32_t alo = tmem + kTcColsAlo + (uint32_t)ks0 * 8u;
-                    const int nls = ls + 1 == kTcLoStages ? 0 : ls + 1;
-                    const uint32_t nlph = ls + 1 == kTcLoStages ? lph ^ 1u : lph;
+                    const uint32_t acc0 = sg != 0 ? 1u : 0u;
+                    const bool last = sg == nsg - 1;
+                    // straight line under the elect, every operand prepared before it: what the
+                    // issuing lane executes between two tcgen05.mma paces this role
                     if (elect_one_sync()) {
+                        if (ksn >= kTcKC / 2) {
 #pragma unroll
-                        for (int ks = 0; ks < kTcKC / 2 - 1; ++ks) {
-                            if (ks < ksn) {
-                                const uint64_t kh = dhi + (uint64_t)(ks * ((2 * kTcLBO) >> 4));
-                                const uint64_t kl = dlo + (uint64_t)(ks * ((2 * kTcLBO) >> 4));
+                            for (int ks = 0; ks < kTcKC / 2; ++ks) {
                                 // small terms first, the big product last
-                                if (a.dbg & 16) { // timing experiment: the hi x hi product alone
-                                    mma_tf32_ts(tD, ahi + ks * 8, kh, idesc, (sg | ks) != 0 ? 1u : 0u);
-                                } else {
-                                    mma_tf32_ts(tD, alo + ks * 8, kh, idesc, (sg | ks) != 0 ? 1u : 0u);
-                                    mma_tf32_ts(tD, ahi + ks * 8, kl, idesc, 1u);
-                                    mma_tf32_ts(tD, ahi + ks * 8, kh, idesc, 1u);
-                                }
+                                mma_tf32_ts(tD, alo + ks * 8, dhi + ks * kstep, idesc,
+                                            ks ? 1u : acc0);
+                                mma_tf32_ts(tD, ahi + ks * 8, dlo + ks * kstep, idesc, 1u);
+                                mma_tf32_ts(tD, ahi + ks * 8, dhi + ks * kstep, idesc, 1u);
                             }
-                        }
-                    }
-                    __syncwarp();
-                    ready = mbar_test_wait(&s.lo_rdy[nls], nlph); // next stage, MMAs still queued
-                    if (elect_one_sync()) {
-                        constexpr int ks = kTcKC / 2 - 1;
-                        if (ks < ksn) {
-                            const uint64_t kh = dhi + (uint64_t)(ks * ((2 * kTcLBO) >> 4));
-                            const uint64_t kl = dlo + (uint64_t)(ks * ((2 * kTcLBO) >> 4));
-                            if (a.dbg & 16) {
-                                mma_tf32_ts(tD, ahi + ks * 8, kh, idesc, 1u);
-                            } else {
-                                mma_tf32_ts(tD, alo + ks * 8, kh, idesc, 1u);
-                                mma_tf32_ts(tD, ahi + ks * 8, kl, idesc, 1u);
-                                mma_tf32_ts(tD, ahi + ks * 8, kh, idesc, 1u);
+                        } else {
+                            for (int ks = 0; ks < ksn; ++ks) {
+                                mma_tf32_ts(tD, alo + ks * 8, dhi + ks * kstep, idesc,
+                                            ks ? 1u : acc0);
+                                mma_tf32_ts(tD, ahi + ks * 8, dlo + ks * kstep, idesc, 1u);
+                                mma_tf32_ts(tD, ahi + ks * 8, dhi + ks * kstep, idesc, 1u);
                             }
                         }
                         mma_commit(&s.empty[st]);
                         mma_commit(&s.lo_empty[ls]);
-                        if (sg == nsg - 1)
+                        if (last)
                             mma_commit(&s.d_full[b]);
                     }
                     __syncwarp();
                     if (++st == nst)
                         st = 0;
-                    ls = nls;
-                    lph = nlph;
+                    if (++ls == kTcLoStages) {
+                        ls = 0;
+                        lph ^= 1u;
+                    }
                 }
                 if (lane == 0)
                     TC_TRACE(2, t);

@@ -933,8 +933,6 @@ static cudaError_t launch_tcr_shape(uint32_t max_items, const TcScanArgs& a_in, 
         return cudaErrorInvalidValue;
     const int dbg = g_tc_dbg.load(std::memory_order_relaxed); // B200IVF_TC_DBG / "tc_dbg"
     a.dbg = a.nlists > 1 ? dbg : 0; // timing experiments; never for the coarse quantizer
-    if (a.dbg & 4096)
-        a.one_mma = 1;
     auto kern = ivf_scan_tcr_kernel<METRIC, KP, SMALL>;
     cudaError_t e =
             cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -1028,6 +1026,12 @@ int scan_tcr_kpart(int nf4, int k) {
             : k + 8 <= 128     ? 128
             : k + 8 <= 256     ? 256
                                : 0;
+    return kp && scan_tcr_tq(nf4, kp) ? kp : 0;
+}
+
+int scan_tcr_kpart_one(int nf4, int k) {
+    const int need = k + (k / 4 > 16 ? k / 4 : 16);
+    const int kp = need <= 32 ? 32 : need <= 64 ? 64 : need <= 128 ? 128 : need <= 256 ? 256 : 0;
     return kp && scan_tcr_tq(nf4, kp) ? kp : 0;
 }
 

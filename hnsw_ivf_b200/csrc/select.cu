@@ -17,6 +17,30 @@ namespace b200ivf {
 
 namespace {
 
+
+// the checked re-rank's verdict (SelectArgs::err_coef): true = the exact top k is proven
+__device__ __forceinline__ bool rerank_proven(const SelectArgs& a, int q, float xn2, float bound,
+                                              uint64_t kth_key) {
+    if (kth_key == kSentinelKey)
+        bound = fminf(bound, kNeutralScore); // fewer than k results: nothing may remain anywhere
+    float b = bound;
+    if (a.qthr)
+        b = fminf(b, from_ordered_bits(a.qthr[q]));
+    if (b >= kNeutralScore)
+        return true; // nothing was left out
+    if (kth_key == kSentinelKey)
+        return false;
+    const float ym2 = a.ymax2 ? *a.ymax2 : 0.f;
+    const float e = a.metric == kMetricL2 ? a.err_coef * (xn2 + ym2)
+                                          : a.err_coef * sqrtf(xn2 * ym2);
+    // (rounded against the claim: the subtraction may only make the test harder to pass)
+    return __fsub_rd(b, e) > key_score(kth_key);
+}
+__device__ __forceinline__ void flag_query(const SelectArgs& a, int q) {
+    if (a.flag_list && a.flag_count)
+        a.flag_list[atomicAdd(a.flag_count, 1)] = q;
+}
+
 // One CTA per query. Shared memory: keys[M] then dis[k] then ids[k].
 // Fast path (prefilter != 0): every partial list is sorted, so the kk-th smallest of the list HEADS
 // is an upper bound T of the kk-th smallest key overall; only the keys <= T (a few dozen) are
@@ -37,6 +61,7 @@ __global__ void select_kernel(const SelectArgs a, int M, int prefilter) {
     const int kk = a.slab ? a.k + a.rerank_extra : a.k;
     __shared__ int s_cnt;
     bool fast_done = false;
+    uint64_t cut_key = kSentinelKey; // checked re-rank: every key left out so far was >= this
     if (prefilter) {
         // Pivot rule (the one select_warp_kernel uses): every partial list is sorted, so at least
         // r * m keys are <= the r-th smallest of the lists' m-th entries. With m = ceil(kk / L)
@@ -86,7 +111,7 @@ __global__ void select_kernel(const SelectArgs a, int M, int prefilter) {
         const int cnt = s_cnt;
         // (cnt < kk under a real bound cannot happen; if it ever did, the full sort is the answer)
         if (cnt <= kSelCap && (cnt >= kk || T == kSentinelKey - 1)) {
-            int P = pow2_ceil(cnt > kk ? cnt : kk);
+            int P = pow2_ceil(cnt > kk ? cnt : kk + 1);
             if (P < 32)
                 P = 32;
             for (int i = cnt + t; i < P; i += blockDim.x)
@@ -94,6 +119,8 @@ __global__ void select_kernel(const SelectArgs a, int M, int prefilter) {
             __syncthreads();
             block_sort_keys(keys, P);
             fast_done = true;
+            if (T != kSentinelKey - 1)
+                cut_key = T; // keys > T were not gathered
         }
         __syncthreads();
     }
@@ -117,10 +144,24 @@ __global__ void select_kernel(const SelectArgs a, int M, int prefilter) {
         }
         __syncthreads();
         block_sort_keys(keys, M);
+        if (keys[kk] < cut_key)
+            cut_key = keys[kk]; // what this round cuts off is >= its first cut key
+        __syncthreads();        // (slot kk is overwritten by the next round's load)
         kept = kk;
         done += take;
     }
 
+    // checked re-rank: the smallest approximate score among the keys that will NOT be re-scored
+    float nb_bound = kNeutralScore;
+    if (a.slab && a.err_coef > 0.f) {
+        // (every path above leaves keys[0..] sorted with at least kk + 1 valid slots: the next key,
+        // a sentinel if there is none; keys cut by the gather bound or by a chunked round were
+        // all >= a key that is still in the array or >= the bound T)
+        const uint64_t nk = keys[kk] < cut_key ? keys[kk] : cut_key;
+        if (nk != kSentinelKey)
+            nb_bound = key_score(nk);
+        __syncthreads();
+    }
     if (a.slab) {
         // exact re-rank of the survivors: plain fp32, dimension order 0..d-1 in one accumulator,
         // the arithmetic of scan.cu / scan_tile.cu (fvec_L2sqr / fvec_inner_product,
@@ -190,6 +231,15 @@ __global__ void select_kernel(const SelectArgs a, int M, int prefilter) {
             keys[i] = kSentinelKey;
         __syncthreads();
         block_sort_keys(keys, P);
+        if (a.err_coef > 0.f && t == 0) {
+            float xn2 = 0.f;
+            for (int j = 0; j < a.d; ++j) {
+                const float xv = __ldg(xp + j);
+                xn2 = fmaf(xv, xv, xn2);
+            }
+            if (!rerank_proven(a, q, xn2, nb_bound, keys[a.k - 1]))
+                flag_query(a, q);
+        }
     }
 
     // decode the k best, map rows to user ids
@@ -395,7 +445,7 @@ __global__ void __launch_bounds__(256, 4) select_warp_kernel(const SelectArgs a)
     // 3. sort what was kept
     {
         const int tot = kept + cnt;
-        int P = pow2_ceil(tot > kk ? tot : kk);
+        int P = pow2_ceil(tot > kk ? tot : kk + 1); // (slot kk is read by the checked re-rank)
         if (P < 32)
             P = 32;
         for (int i = tot + lane; i < P; i += 32)
@@ -404,6 +454,15 @@ __global__ void __launch_bounds__(256, 4) select_warp_kernel(const SelectArgs a)
         warp_sort_keys(keys, P, lane);
     }
     // 4. exact re-rank of the kk survivors (lane = candidate), see select_kernel
+    float nb_bound = kNeutralScore; // checked re-rank: best approximate score left out
+    if (a.slab && a.err_coef > 0.f) {
+        const uint64_t nk = keys[kk]; // (P >= kk + 1 slots are valid: sentinel if none)
+        if (nk != kSentinelKey)
+            nb_bound = key_score(nk);
+        if (T != kSentinelKey - 1)
+            nb_bound = fminf(nb_bound, key_score(T)); // keys > T were never gathered
+        __syncwarp();
+    }
     if (a.slab) {
         for (int i = lane; i < kk; i += 32) {
             const uint64_t key = keys[i];
@@ -421,6 +480,19 @@ __global__ void __launch_bounds__(256, 4) select_warp_kernel(const SelectArgs a)
             keys[i] = kSentinelKey;
         __syncwarp();
         warp_sort_keys(keys, P, lane);
+        if (a.err_coef > 0.f) {
+            const float* xp = a.queries + (size_t)q * a.d;
+            float xn2 = 0.f;
+            for (int j = lane; j < a.d; j += 32) {
+                const float xv = __ldg(xp + j);
+                xn2 = fmaf(xv, xv, xn2);
+            }
+            for (int o = 16; o > 0; o >>= 1)
+                xn2 += __shfl_xor_sync(0xffffffffu, xn2, o);
+            xn2 *= 1.0000005f; // (summation order differs from the scan's: err on the safe side)
+            if (lane == 0 && !rerank_proven(a, q, xn2, nb_bound, keys[a.k - 1]))
+                flag_query(a, q);
+        }
     }
     // 5. decode, order exact ties by id as cmp2 does, write
     const bool l2 = a.metric == kMetricL2;

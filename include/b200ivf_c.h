@@ -137,6 +137,13 @@ void b200_IndexIVFFlat_last_timings(const B200IndexIVFFlat* index, double* ms5);
 /* ... and the same five figures summed over every search call since reset_stats (so a timed loop
  * need not stop after each call to read them); returns the number of calls */
 unsigned long long b200_IndexIVFFlat_stage_time_sums(const B200IndexIVFFlat* index, double* ms5);
+/* Queries that were searched a second time on the exact kernel, since the handle was created. With
+ * set_option("tc_split", 1) the list scan uses the tensor cores as a FILTER (one tf32 product, known
+ * error bound) and the k-select proves per query that the exactly re-scored candidates contain the
+ * exact top k; a query it cannot prove (many rows within the bound of the k-th distance) is redone
+ * exactly before the call returns. Results never depend on the option; this counter says how
+ * often the second pass ran. No counterpart in the reference. */
+unsigned long long b200_IndexIVFFlat_exact_redo_count(const B200IndexIVFFlat* index);
 
 /* Run on a caller-owned CUDA stream (cudaStream_t as void*; NULL = the handle's own stream, a
  * non-blocking one; pass cudaStreamLegacy, (void*)0x1, to be ordered with the legacy default
