@@ -172,6 +172,7 @@ struct IndexIVFFlatB200::Impl {
     // the scratch of their second, exact pass
     Buffer ymax2, flag_list, flag_count, host_flag, fb_x, fb_D, fb_I, fb_assign, fb_p32;
     int tc_split = 3;                   // "tc_split": 3 = 3xTF32 (default), 1 = one MMA + checked re-rank
+    int one_margin = 16;                // "one_margin": keys kept beyond k in that mode (at least)
     unsigned long long fallback_queries = 0; // queries redone on the exact path so far
     Buffer coarse_ids, coarse_dis, part, count, fill, grp_start, item_off, item_off_tile,
             pair_query, slot_of,
@@ -839,7 +840,8 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
     // that nothing outside the exactly re-scored set could have reached the top k
     // (SelectArgs::err_coef); the few queries it cannot prove are searched again on the exact
     // warp kernel before the call returns
-    const int kp_one = scan_tcr_kpart_one(m.nf4, (int)std::min<int64_t>(k, 1 << 20));
+    const int kp_one =
+            scan_tcr_kpart_one(m.nf4, (int)std::min<int64_t>(k, 1 << 20), m.one_margin);
     bool one = tc && tcr && m.tc_split == 1 && kp_one > 0;
     int64_t kp = tc ? (tcr ? (one ? kp_one : kp_r) : kp_q) : k; // entries per partial list
     // few queries per list: the two-CTAs-per-SM shape of the rows-major kernel (<= 32 queries per
@@ -1069,7 +1071,8 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
             if (one) {
                 // checked re-rank: everything inside the error window of the k-th score is
                 // re-scored (the window holds a handful of rows: a margin of max(16, k / 4))
-                se.rerank_extra = (int)std::min<int64_t>(std::max<int64_t>(16, k / 4), kp - k);
+                se.rerank_extra =
+                        (int)std::min<int64_t>(std::max<int64_t>(m.one_margin, k / 4), kp - k);
                 se.err_coef = kOneMmaErrCoef;
                 se.ymax2 = m.ymax2.as<float>();
                 se.qthr = m.qthr.as<uint32_t>();
@@ -1429,6 +1432,8 @@ void IndexIVFFlatB200::set_option(const char* name, double value) {
         m.coarse_s_override = (int)value;
     else if (n == "tc_split") // 1 = one MMA + checked re-rank (rows-major kernel), 3 = 3xTF32
         m.tc_split = value == 1 ? 1 : 3;
+    else if (n == "one_margin")
+        m.one_margin = std::max(1, (int)value);
     else if (n == "tcr_small_factor")
         m.tcr_small_factor = value;
     else if (n == "tcr_small_max_avg_q")

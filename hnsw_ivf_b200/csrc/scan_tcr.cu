@@ -64,20 +64,21 @@ using namespace ptx;
 // that one CTA's per-item costs (launch, query-tile prologue, pipeline fill and drain: ~7 us per
 // item, measured by forcing row splits; 2 ms of a 12 ms scan on the C4 shard) are covered by the
 // other CTA's streaming.
-template <bool SMALL>
+template <bool SMALL, bool ONE = false>
 struct RShape {
     static constexpr int EpiWarps = SMALL ? 4 : 8;      // warps 0 .. EpiWarps-1
     static constexpr int TmaWarp = EpiWarps;
     static constexpr int MmaWarp = EpiWarps + 1;
     static constexpr int SplitWarp0 = EpiWarps + 2;
-    static constexpr int SplitWarps = SMALL ? 4 : 8;    // groups of 4 (one warp per TMEM quarter)
+    // groups of 4 (one warp per TMEM quarter); none under the one-MMA filter (no lo operand)
+    static constexpr int SplitWarps = ONE ? 0 : (SMALL ? 4 : 8);
     static constexpr int SplitGroups = SplitWarps / 4;
-    static constexpr int Threads = (SplitWarp0 + SplitWarps) * 32; // 320 / 576
+    static constexpr int Threads = (SplitWarp0 + SplitWarps) * 32; // 320 / 576; ONE: 192 / 320
     static constexpr int LoaderWarps = EpiWarps + 1 + SplitWarps;  // all but the TMA producer
     static constexpr int CtasPerSM = SMALL ? 2 : 1;
     static constexpr int AStages = SMALL ? 4 : 8;       // lo ring in tensor memory
-    static constexpr uint32_t TmemCols = SMALL ? 256 : 512;
-    static constexpr uint32_t DStride = SMALL ? 64 : 128; // columns per accumulator buffer
+    static constexpr uint32_t TmemCols = ONE ? 128 : (SMALL ? 256 : 512);
+    static constexpr uint32_t DStride = ONE ? 64 : (SMALL ? 64 : 128); // columns per accumulator
     static constexpr uint32_t ColsA = SMALL ? 128 : 256;  // first column of the lo ring
     static constexpr int MaxTQ = SMALL ? 32 : 64;
 };
@@ -316,6 +317,65 @@ __device__ __noinline__ void tcr_compact(uint64_t* cand, int* cnt, uint32_t* thr
 }
 
 
+
+// One chunk of 16 queries of the epilogue (thread = row): filter the 16 accumulators against the
+// queries' loosened bounds (one vote per chunk: in the steady state no row passes and the warp
+// moves on), then the lanes that hold candidates walk their own columns, test them exactly and
+// append them to the queries' buffers. Returns the columns this lane pushed past a full buffer
+// (re-examined after the compaction); fl collects what the block must do after the tile
+// (1 = compact, 2 = a buffer overflowed).
+template <int KP>
+__device__ __forceinline__ uint32_t tcr_filter_chunk(const uint32_t (&v)[16], int ch, bool first,
+                                                     uint32_t dbits, float nrm, float nrmf,
+                                                     uint32_t rowid, int row_in_list, bool limited,
+                                                     const RSmem& s, int& fl, int& n_events) {
+    constexpr int C = RCfg<KP>::C;
+    float dd[16];
+#pragma unroll
+    for (int j4 = 0; j4 < 4; ++j4) {
+        const float4 th = *reinterpret_cast<const float4*>(s.thrf + ch * 16 + j4 * 4);
+        dd[4 * j4 + 0] = __uint_as_float(v[4 * j4 + 0]) - th.x;
+        dd[4 * j4 + 1] = __uint_as_float(v[4 * j4 + 1]) - th.y;
+        dd[4 * j4 + 2] = __uint_as_float(v[4 * j4 + 2]) - th.z;
+        dd[4 * j4 + 3] = __uint_as_float(v[4 * j4 + 3]) - th.w;
+    }
+    float mn = dd[0];
+#pragma unroll
+    for (int j = 1; j < 16; ++j)
+        mn = fminf(mn, dd[j]);
+    const bool hit = first ? (mn + nrmf <= 0.f) : dbits != 0u;
+    if (!__any_sync(0xffffffffu, hit))
+        return first ? 0u : dbits;
+    uint32_t pm = 0u;
+    if (first) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j)
+            pm |= (dd[j] + nrmf <= 0.f) ? (1u << j) : 0u;
+    } else {
+        pm = dbits;
+    }
+    uint32_t ndrop = 0u;
+    while (pm != 0u) {
+        const int j = __ffs(pm) - 1;
+        pm &= pm - 1u;
+        ++n_events;
+        const int qi = ch * 16 + j;
+        const float sc = __uint_as_float(sel16(v, j)) + nrm;
+        if (sc <= s.thrp[qi] && (!limited || row_in_list < s.lim[qi])) {
+            const int slot = atomicAdd(&s.cnt[qi], 1);
+            if (slot < C) {
+                s.cand[(size_t)qi * C + slot] = make_key(sc + s.xn[qi], rowid);
+            } else {
+                ndrop |= 1u << j;
+                fl |= 2;
+            }
+            if (slot + 1 >= RCfg<KP>::CompactAt)
+                fl |= 1;
+        }
+    }
+    return ndrop;
+}
+
 // wait with the waiting time added to a trace counter (timing experiments only)
 #define TCR_WAIT(bar, par, acc, code, aux)                               \
     do {                                                                 \
@@ -334,11 +394,11 @@ __device__ __noinline__ void tcr_compact(uint64_t* cand, int* cnt, uint32_t* thr
             a.trace[(role) * 64 + (idx)] = clock64();                    \
     } while (0)
 
-template <int METRIC, int KP, bool SMALL>
-__global__ void __launch_bounds__(RShape<SMALL>::Threads, RShape<SMALL>::CtasPerSM)
+template <int METRIC, int KP, bool SMALL, bool ONE>
+__global__ void __launch_bounds__(RShape<SMALL, ONE>::Threads, RShape<SMALL, ONE>::CtasPerSM)
         ivf_scan_tcr_kernel(const TcScanArgs a, const __grid_constant__ CUtensorMap tmap) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
-    using SH = RShape<SMALL>;
+    using SH = RShape<SMALL, ONE>;
     constexpr int kREpiWarps = SH::EpiWarps, kRTmaWarp = SH::TmaWarp, kRMmaWarp = SH::MmaWarp;
     constexpr int kRSplitWarp0 = SH::SplitWarp0;
     constexpr int kRLoaderWarps = SH::LoaderWarps, kRSplitGroups = SH::SplitGroups;
@@ -389,14 +449,14 @@ __global__ void __launch_bounds__(RShape<SMALL>::Threads, RShape<SMALL>::CtasPer
     const int nsg = (nf4 + kRKC - 1) / kRKC;  // stages per tile
     const int nks = (nf4 + 1) >> 1;           // MMA k-steps (8 dims each) per tile
     const int niter = ntiles * nsg;
-    const int nst = tcr_stages((size_t)a.nstages * 1024, KP, n16, 2 * nks, !SMALL);
+    const int nst = tcr_stages((size_t)a.nstages * 1024, KP, n16, 2 * nks, !SMALL && !ONE);
     const uint32_t lbo = tcr_lbo(n16);
 
     const RSmem s = carve_r<KP>(smem_raw, nst, n16, 2 * nks);
     const bool tracing = a.trace != nullptr && item == a.trace_item;
     // one MMA per k-step (y_hi . x_hi only): the tensor core is a FILTER with a known error bound,
     // see TcScanArgs::one_mma
-    const bool one = a.one_mma != 0;
+    constexpr bool one = ONE;
     if (tid == 0) {
         TCR_TRACE(0, 0);
         if (tracing) {
@@ -657,7 +717,7 @@ __global__ void __launch_bounds__(RShape<SMALL>::Threads, RShape<SMALL>::CtasPer
             a.trace[9 * 64 + 3] = w_dempty;
             a.trace[9 * 64 + 6] = w_issue;
         }
-    } else if (warp >= kRSplitWarp0) {
+    } else if (!ONE && warp >= kRSplitWarp0) {
         // ======================= split warps: raw stage -> (hi, lo) in tensor memory ============
         // Two groups of 4 warps (one per TMEM lane quarter) take alternate stages, so that the
         // load -> convert -> tcgen05.st -> wait chain of one stage overlaps the next stage's.
@@ -667,7 +727,7 @@ __global__ void __launch_bounds__(RShape<SMALL>::Threads, RShape<SMALL>::CtasPer
         const int row = quarter * 32 + lane;
         const uint32_t lane_addr = (uint32_t)(quarter * 32) << 16;
         long long w_full = 0, w_aempty = 0;
-        for (int it = grp; it < niter && !one; it += kRSplitGroups) {
+        for (int it = grp; it < niter; it += (kRSplitGroups > 0 ? kRSplitGroups : 1)) {
             const int st = it % nst;
             const uint32_t ph = (uint32_t)((it / nst) & 1);
             const int as = it % kAStages;
@@ -737,93 +797,73 @@ __global__ void __launch_bounds__(RShape<SMALL>::Threads, RShape<SMALL>::CtasPer
                                      : (METRIC == kMetricL2 ? __ldg(a.norms + rowid) : 0.f);
             const float nrmf = nrm * (1.f - 4.76837158e-7f); // the filter errs on the accept side
             const uint32_t gthr = (myq >= 0 && a.qthr) ? __ldcg(a.qthr + myq) : 0xffffffffu;
-            uint32_t drop[3] = {0u, 0u, 0u}; // (16 queries per half word; 4 chunks at most)
+            // The warp's chunks of 16 queries: ch = half + u * (epilogue warps per quarter), u < 2
+            constexpr int kChStride = kREpiWarps / 4;
+            constexpr int kChPerWarp = (SH::MaxTQ / 16 + kChStride - 1) / kChStride;
+            static_assert(kChPerWarp == 2, "two chunks per epilogue warp");
+            uint32_t dropw = 0u; // 16 bits per chunk: columns pushed past a full buffer
+            const bool limited = a.pair_limit != nullptr;
             TCR_WAIT(&s.d_full[b], (uint32_t)((t >> 1) & 1), w_dfull, 6, t);
             tc_fence_after_sync();
             const uint32_t tD = tmem + lane_addr + kRColsD + (uint32_t)b * kDStride;
+            // one-MMA filter: ALL of the tile's accumulator columns this warp owns are fetched at
+            // once (one tcgen05.ld round trip per tile, not one per chunk: that round trip is
+            // what an epilogue warp spends its time on) and the buffer goes back to the MMA warp
+            // before anything is filtered. (The 3xTF32 form has twice the columns to fetch and
+            // eight more warps to share the register file with: it goes chunk by chunk.)
+            uint32_t vv[ONE ? kChPerWarp : 1][16];
+            if (ONE) {
+#pragma unroll
+                for (int u = 0; u < kChPerWarp; ++u) {
+                    const int ch = half + u * kChStride;
+                    if (ch < nch16)
+                        tmem_ld_32x32b_x16(tD + (uint32_t)ch * 16u, vv[ONE ? u : 0]);
+                }
+                tmem_ld_wait();
+                tc_fence_before_sync();
+                __syncwarp();
+                if (lane == 0)
+                    mbar_arrive(&s.d_empty[b]); // accumulator buffer drained
+            }
             int n_events = 0, n_rounds = 0;
             long long c_scan = 0, c_comp = 0;
             for (int round = 0;; ++round) {
                 long long tt0 = tracing ? clock64() : 0;
                 ++n_rounds;
                 int fl = 0;
+                if (ONE) {
+#pragma unroll
+                    for (int u = 0; u < kChPerWarp; ++u) {
+                        const int ch = half + u * kChStride;
+                        if (ch >= nch16 || (a.dbg & 1))
+                            continue;
+                        const uint32_t nd = tcr_filter_chunk<KP>(
+                                vv[ONE ? u : 0], ch, round == 0, (dropw >> (u * 16)) & 0xffffu, nrm,
+                                nrmf, rowid, row_in_list, limited, s, fl, n_events);
+                        dropw = (dropw & ~(0xffffu << (u * 16))) | (nd << (u * 16));
+                    }
+                } else {
 #pragma unroll 1
-                for (int ch = half; ch < nch16; ch += kREpiWarps / 4) {
-                    uint32_t v[16];
-                    if (a.dbg & 64)
-                        continue;
-                    {
+                    for (int u = 0; u < kChPerWarp; ++u) {
+                        const int ch = half + u * kChStride;
+                        if (ch >= nch16)
+                            break;
                         // y_hi.x_hi + y_lo.x_hi sits in column j, y_hi.x_lo in column n16 + j
-                        if (one) {
-                            tmem_ld_32x32b_x16(tD + (uint32_t)ch * 16u, v);
-                            tmem_ld_wait();
-                        } else {
-                            uint32_t w[16];
-                            tmem_ld_32x32b_x16(tD + (uint32_t)ch * 16u, v);
-                            tmem_ld_32x32b_x16(tD + (uint32_t)(n16 + ch * 16), w);
-                            tmem_ld_wait();
-#pragma unroll
-                            for (int j = 0; j < 16; ++j)
-                                v[j] = __float_as_uint(__uint_as_float(v[j]) +
-                                                       __uint_as_float(w[j]));
-                        }
-                    }
-                    if (a.dbg & 1)
-                        continue;
-                    const uint32_t dword = ch < 2 ? drop[0] : (ch < 4 ? drop[1] : drop[2]);
-                    const uint32_t dbits = (dword >> ((ch & 1) * 16)) & 0xffffu;
-                    // filter: min over the 16 queries of (accumulator - loosened bound), one
-                    // FADD and half an FMNMX3 per element, one vote per chunk
-                    float dd[16];
-#pragma unroll
-                    for (int j4 = 0; j4 < 4; ++j4) {
-                        const float4 th = *reinterpret_cast<const float4*>(s.thrf + ch * 16 + j4 * 4);
-                        dd[4 * j4 + 0] = __uint_as_float(v[4 * j4 + 0]) - th.x;
-                        dd[4 * j4 + 1] = __uint_as_float(v[4 * j4 + 1]) - th.y;
-                        dd[4 * j4 + 2] = __uint_as_float(v[4 * j4 + 2]) - th.z;
-                        dd[4 * j4 + 3] = __uint_as_float(v[4 * j4 + 3]) - th.w;
-                    }
-                    float mn = dd[0];
-#pragma unroll
-                    for (int j = 1; j < 16; ++j)
-                        mn = fminf(mn, dd[j]);
-                    const bool hit = round == 0 ? (mn + nrmf <= 0.f) : dbits != 0u;
-                    if (!__any_sync(0xffffffffu, hit))
-                        continue;
-                    // the lanes that hold a candidate walk their own columns (divergent)
-                    uint32_t pm = 0u;
-                    if (round == 0) {
+                        uint32_t w[16];
+                        tmem_ld_32x32b_x16(tD + (uint32_t)ch * 16u, vv[0]);
+                        tmem_ld_32x32b_x16(tD + (uint32_t)(n16 + ch * 16), w);
+                        tmem_ld_wait();
 #pragma unroll
                         for (int j = 0; j < 16; ++j)
-                            pm |= (dd[j] + nrmf <= 0.f) ? (1u << j) : 0u;
-                    } else {
-                        pm = dbits;
+                            vv[0][j] = __float_as_uint(__uint_as_float(vv[0][j]) +
+                                                       __uint_as_float(w[j]));
+                        if (a.dbg & 1)
+                            continue;
+                        const uint32_t nd = tcr_filter_chunk<KP>(
+                                vv[0], ch, round == 0, (dropw >> (u * 16)) & 0xffffu, nrm, nrmf,
+                                rowid, row_in_list, limited, s, fl, n_events);
+                        dropw = (dropw & ~(0xffffu << (u * 16))) | (nd << (u * 16));
                     }
-                    uint32_t ndrop = 0u;
-                    while (pm != 0u) {
-                        const int j = __ffs(pm) - 1;
-                        pm &= pm - 1u;
-                        ++n_events;
-                        const int qi = ch * 16 + j;
-                        const float sc = __uint_as_float(sel16(v, j)) + nrm;
-                        if (sc <= s.thrp[qi] &&
-                            (a.pair_limit == nullptr || row_in_list < s.lim[qi])) {
-                            const int slot = atomicAdd(&s.cnt[qi], 1);
-                            if (slot < C) {
-                                s.cand[(size_t)qi * C + slot] = make_key(sc + s.xn[qi], rowid);
-                            } else {
-                                ndrop |= 1u << j;
-                                fl |= 2;
-                            }
-                            if (slot + 1 >= RCfg<KP>::CompactAt)
-                                fl |= 1;
-                        }
-                    }
-                    const uint32_t nword =
-                            (dword & ~(0xffffu << ((ch & 1) * 16))) | (ndrop << ((ch & 1) * 16));
-                    drop[0] = ch < 2 ? nword : drop[0];
-                    drop[1] = (ch >= 2 && ch < 4) ? nword : drop[1];
-                    drop[2] = ch >= 4 ? nword : drop[2];
                 }
                 if (fl)
                     atomicOr(&s.flag[ep & 3], fl);
@@ -852,11 +892,12 @@ __global__ void __launch_bounds__(RShape<SMALL>::Threads, RShape<SMALL>::CtasPer
                 if (!(f & 2) || round >= 16) // (8 rounds drain any tile; the cap is a safety net)
                     break;
             }
-            // accumulator buffer drained
-            tc_fence_before_sync();
-            __syncwarp();
-            if (lane == 0)
-                mbar_arrive(&s.d_empty[b]);
+            if (!ONE) { // accumulator buffer drained (re-examination rounds read it again)
+                tc_fence_before_sync();
+                __syncwarp();
+                if (lane == 0)
+                    mbar_arrive(&s.d_empty[b]);
+            }
             if (tid == 0) {
                 TCR_TRACE(4, t);
                 if (tracing && t < 64) {
@@ -923,17 +964,17 @@ const unsigned long long* tc_trap_info_host() {
     return g_trap_host;
 }
 
-template <int METRIC, int KP, bool SMALL>
+template <int METRIC, int KP, bool SMALL, bool ONE>
 static cudaError_t launch_tcr_shape(uint32_t max_items, const TcScanArgs& a_in, cudaStream_t st) {
     TcScanArgs a = a_in;
     const size_t smem = SMALL ? kRSmemSmall : kRSmemBig;
     a.nstages = (int)(smem / 1024); // the kernel carves per item (tcr_stages)
-    if (a.tq < 16 || a.tq > RShape<SMALL>::MaxTQ || (a.tq & 15) ||
-        tcr_stages(smem, KP, a.tq, 2 * ((a.nf4 + 1) >> 1), !SMALL) < 3)
+    if (a.tq < 16 || a.tq > RShape<SMALL, ONE>::MaxTQ || (a.tq & 15) ||
+        tcr_stages(smem, KP, a.tq, 2 * ((a.nf4 + 1) >> 1), !SMALL && !ONE) < 3)
         return cudaErrorInvalidValue;
     const int dbg = g_tc_dbg.load(std::memory_order_relaxed); // B200IVF_TC_DBG / "tc_dbg"
     a.dbg = a.nlists > 1 ? dbg : 0; // timing experiments; never for the coarse quantizer
-    auto kern = ivf_scan_tcr_kernel<METRIC, KP, SMALL>;
+    auto kern = ivf_scan_tcr_kernel<METRIC, KP, SMALL, ONE>;
     cudaError_t e =
             cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess)
@@ -951,7 +992,7 @@ static cudaError_t launch_tcr_shape(uint32_t max_items, const TcScanArgs& a_in, 
         a.trace = buf;
         a.trace_item = (uint32_t)atoi(tr);
     }
-    kern<<<max_items, RShape<SMALL>::Threads, smem, st>>>(
+    kern<<<max_items, RShape<SMALL, ONE>::Threads, smem, st>>>(
             a, *reinterpret_cast<const CUtensorMap*>(a.tmap));
     count_launches(1);
     g_tc_launches.fetch_add(1, std::memory_order_relaxed);
@@ -988,10 +1029,13 @@ static cudaError_t launch_tcr_shape(uint32_t max_items, const TcScanArgs& a_in, 
 // tq <= 32: the two-CTAs-per-SM shape, else the whole-SM one
 template <int METRIC, int KP>
 static cudaError_t launch_tcr_one(uint32_t max_items, const TcScanArgs& a, cudaStream_t st) {
-    if (a.tq <= RShape<true>::MaxTQ &&
-        tcr_stages(kRSmemSmall, KP, a.tq, 2 * ((a.nf4 + 1) >> 1), false) >= 3)
-        return launch_tcr_shape<METRIC, KP, true>(max_items, a, st);
-    return launch_tcr_shape<METRIC, KP, false>(max_items, a, st);
+    const bool small = a.tq <= RShape<true>::MaxTQ &&
+            tcr_stages(kRSmemSmall, KP, a.tq, 2 * ((a.nf4 + 1) >> 1), false) >= 3;
+    if (a.one_mma)
+        return small ? launch_tcr_shape<METRIC, KP, true, true>(max_items, a, st)
+                     : launch_tcr_shape<METRIC, KP, false, true>(max_items, a, st);
+    return small ? launch_tcr_shape<METRIC, KP, true, false>(max_items, a, st)
+                 : launch_tcr_shape<METRIC, KP, false, false>(max_items, a, st);
 }
 
 // queries per item for dimension nf4*4 and kp kept keys: the largest multiple of 16 (<= kTcrTQ) that
@@ -1029,9 +1073,14 @@ int scan_tcr_kpart(int nf4, int k) {
     return kp && scan_tcr_tq(nf4, kp) ? kp : 0;
 }
 
-int scan_tcr_kpart_one(int nf4, int k) {
-    const int need = k + (k / 4 > 16 ? k / 4 : 16);
-    const int kp = need <= 32 ? 32 : need <= 64 ? 64 : need <= 128 ? 128 : need <= 256 ? 256 : 0;
+int scan_tcr_kpart_one(int nf4, int k, int margin_min) {
+    const int need = k + (k / 4 > margin_min ? k / 4 : margin_min);
+    const int kp = need <= 16  ? 16
+            : need <= 32       ? 32
+            : need <= 64       ? 64
+            : need <= 128      ? 128
+            : need <= 256      ? 256
+                               : 0;
     return kp && scan_tcr_tq(nf4, kp) ? kp : 0;
 }
 

@@ -18,6 +18,13 @@ namespace b200ivf {
 namespace {
 
 
+// E(q) of SelectArgs::err_coef, rounded up
+__device__ __forceinline__ float rerank_err(const SelectArgs& a, float xn2) {
+    const float ym2 = a.ymax2 ? *a.ymax2 : 0.f;
+    const float e = a.metric == kMetricL2 ? a.err_coef * (xn2 + ym2)
+                                          : a.err_coef * sqrtf(xn2 * ym2);
+    return e * 1.000001f;
+}
 // the checked re-rank's verdict (SelectArgs::err_coef): true = the exact top k is proven
 __device__ __forceinline__ bool rerank_proven(const SelectArgs& a, int q, float xn2, float bound,
                                               uint64_t kth_key) {
@@ -30,11 +37,8 @@ __device__ __forceinline__ bool rerank_proven(const SelectArgs& a, int q, float 
         return true; // nothing was left out
     if (kth_key == kSentinelKey)
         return false;
-    const float ym2 = a.ymax2 ? *a.ymax2 : 0.f;
-    const float e = a.metric == kMetricL2 ? a.err_coef * (xn2 + ym2)
-                                          : a.err_coef * sqrtf(xn2 * ym2);
     // (rounded against the claim: the subtraction may only make the test harder to pass)
-    return __fsub_rd(b, e) > key_score(kth_key);
+    return __fsub_rd(b, rerank_err(a, xn2)) > key_score(kth_key);
 }
 __device__ __forceinline__ void flag_query(const SelectArgs& a, int q) {
     if (a.flag_list && a.flag_count)
@@ -153,13 +157,37 @@ __global__ void select_kernel(const SelectArgs a, int M, int prefilter) {
 
     // checked re-rank: the smallest approximate score among the keys that will NOT be re-scored
     float nb_bound = kNeutralScore;
+    float xn2 = 0.f;
+    int nre = kk; // keys to re-score (see select_warp_kernel)
     if (a.slab && a.err_coef > 0.f) {
         // (every path above leaves keys[0..] sorted with at least kk + 1 valid slots: the next key,
         // a sentinel if there is none; keys cut by the gather bound or by a chunked round were
         // all >= a key that is still in the array or >= the bound T)
-        const uint64_t nk = keys[kk] < cut_key ? keys[kk] : cut_key;
+        const float* xq = a.queries + (size_t)q * a.d;
+        for (int j = 0; j < a.d; ++j) { // (every thread: the same value without a reduction)
+            const float xv = __ldg(xq + j);
+            xn2 = fmaf(xv, xv, xn2);
+        }
+        xn2 *= 1.0000005f;
+        const uint64_t ak = keys[a.k - 1];
+        if (ak != kSentinelKey) {
+            const float lim = key_score(ak) + 2.f * rerank_err(a, xn2);
+            int lo = a.k, hi = kk; // first index in [k, kk] whose key is outside the window
+            while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                if (keys[mid] != kSentinelKey && key_score(keys[mid]) <= lim)
+                    lo = mid + 1;
+                else
+                    hi = mid;
+            }
+            nre = lo;
+        }
+        const uint64_t nk = keys[nre] < cut_key ? keys[nre] : cut_key;
         if (nk != kSentinelKey)
             nb_bound = key_score(nk);
+        __syncthreads();
+        for (int i = nre + t; i < kk; i += blockDim.x)
+            keys[i] = kSentinelKey;
         __syncthreads();
     }
     if (a.slab) {
@@ -232,11 +260,6 @@ __global__ void select_kernel(const SelectArgs a, int M, int prefilter) {
         __syncthreads();
         block_sort_keys(keys, P);
         if (a.err_coef > 0.f && t == 0) {
-            float xn2 = 0.f;
-            for (int j = 0; j < a.d; ++j) {
-                const float xv = __ldg(xp + j);
-                xn2 = fmaf(xv, xv, xn2);
-            }
             if (!rerank_proven(a, q, xn2, nb_bound, keys[a.k - 1]))
                 flag_query(a, q);
         }
@@ -455,16 +478,43 @@ __global__ void __launch_bounds__(256, 4) select_warp_kernel(const SelectArgs a)
     }
     // 4. exact re-rank of the kk survivors (lane = candidate), see select_kernel
     float nb_bound = kNeutralScore; // checked re-rank: best approximate score left out
+    float xn2 = 0.f;
+    int nre = kk; // keys to re-score
     if (a.slab && a.err_coef > 0.f) {
-        const uint64_t nk = keys[kk]; // (P >= kk + 1 slots are valid: sentinel if none)
+        const float* xp = a.queries + (size_t)q * a.d;
+        for (int j = lane; j < a.d; j += 32) {
+            const float xv = __ldg(xp + j);
+            xn2 = fmaf(xv, xv, xn2);
+        }
+        for (int o = 16; o > 0; o >>= 1)
+            xn2 += __shfl_xor_sync(0xffffffffu, xn2, o);
+        xn2 *= 1.0000005f; // (summation order differs from the scan's: err on the safe side)
+        // Only the keys inside the error window of the k-th approximate score A can reach the
+        // exact top k: k rows score <= A, so the exact k-th score is <= A + E, and a row with an
+        // approximate score > A + 2 E scores > A + E exactly. Usually that is k keys and one or two
+        // more; the cut is then proven by construction.
+        const uint64_t ak = keys[a.k - 1];
+        if (ak != kSentinelKey) {
+            const float lim = key_score(ak) + 2.f * rerank_err(a, xn2);
+            int c = 0;
+            for (int i = lane; i < kk; i += 32)
+                c += (keys[i] != kSentinelKey && key_score(keys[i]) <= lim) ? 1 : 0;
+            for (int o = 16; o > 0; o >>= 1)
+                c += __shfl_xor_sync(0xffffffffu, c, o);
+            nre = c < a.k ? a.k : c;
+        }
+        const uint64_t nk = keys[nre]; // (P >= kk + 1 slots are valid: sentinel if none)
         if (nk != kSentinelKey)
             nb_bound = key_score(nk);
         if (T != kSentinelKey - 1)
             nb_bound = fminf(nb_bound, key_score(T)); // keys > T were never gathered
         __syncwarp();
+        for (int i = nre + lane; i < kk; i += 32)
+            keys[i] = kSentinelKey; // approximate scores must not meet exact ones
+        __syncwarp();
     }
     if (a.slab) {
-        for (int i = lane; i < kk; i += 32) {
+        for (int i = lane; i < nre; i += 32) {
             const uint64_t key = keys[i];
             if (key != kSentinelKey) {
                 const uint32_t row = key_row(key);
@@ -481,15 +531,6 @@ __global__ void __launch_bounds__(256, 4) select_warp_kernel(const SelectArgs a)
         __syncwarp();
         warp_sort_keys(keys, P, lane);
         if (a.err_coef > 0.f) {
-            const float* xp = a.queries + (size_t)q * a.d;
-            float xn2 = 0.f;
-            for (int j = lane; j < a.d; j += 32) {
-                const float xv = __ldg(xp + j);
-                xn2 = fmaf(xv, xv, xn2);
-            }
-            for (int o = 16; o > 0; o >>= 1)
-                xn2 += __shfl_xor_sync(0xffffffffu, xn2, o);
-            xn2 *= 1.0000005f; // (summation order differs from the scan's: err on the safe side)
             if (lane == 0 && !rerank_proven(a, q, xn2, nb_bound, keys[a.k - 1]))
                 flag_query(a, q);
         }

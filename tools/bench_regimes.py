@@ -281,6 +281,7 @@ def regime_sweep(args, torch, b2, dev):
             scan = statistics.mean(t["scan"] for t in st)
             ndis = g.get_stats().ndis / args.steps
             out = {"regime": "sweep", "workload": name, "nprobe": p, "options": opts,
+                   "exact_redo_total": g.exact_redo_count(),
                    "ms_per_step": ms,
                    "qps": w["nq"] / (ms * 1e-3),
                    "stage_ms": {s: round(statistics.mean(t[s] for t in st), 4) for s in st[0]},
