@@ -848,10 +848,10 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
     // item; a list probed by more is cut into several items)
     // (worth it while most lists fit one or two items: up to that shape's item size on average;
     // measured on C2: 30 queries per list 1.49 ms against 1.66, 41 per list 1.85 against 1.78)
-    int tq_small = tcr ? scan_tcr_tq_small(m.nf4, (int)kp) : 0;
+    int tq_small = tcr ? scan_tcr_tq_small(m.nf4, (int)kp, one) : 0;
     if (avg_q > std::min(m.tcr_small_max_avg_q, m.tcr_small_factor * tq_small))
         tq_small = 0;
-    const int tcr_tq = tcr ? (tq_small ? tq_small : scan_tcr_tq(m.nf4, (int)kp)) : 0;
+    const int tcr_tq = tcr ? (tq_small ? tq_small : scan_tcr_tq(m.nf4, (int)kp, one)) : 0;
     BatchPlan bp = plan_batch(m.nf4, kp, nb, np, nlists_owned, m.nstored, simt_only, filtered, own_frac);
     int pmul = (tc && !tcr) ? 2 : 1; // partial lists per (pair, split)
     const int tc_tq = tcr ? tcr_tq : kTcTQ;

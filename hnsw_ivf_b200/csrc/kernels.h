@@ -136,13 +136,13 @@ cudaError_t launch_ivf_scan_tc(int metric, uint32_t max_items, const TcScanArgs&
 constexpr int kTcrTQ = 64;
 // d up to 1024; the queries per item shrink with the dimension (the query tile lives in shared
 // memory): scan_tcr_tq(nf4, kpart), 0 = unsupported. scan_tcr_kpart: as scan_tc_kpart.
-int scan_tcr_tq(int nf4, int kp);
+int scan_tcr_tq(int nf4, int kp, bool one = false);
 // entries per partial list under the ONE-MMA filter (TcScanArgs::one_mma): the kept set must hold
 // everything inside the error window of the k-th score: margin max(margin_min, k / 4); 0 = none
 int scan_tcr_kpart_one(int nf4, int k, int margin_min);
 // ... and of the two-CTAs-per-SM shape (<= 32 queries per item, half the shared memory): chosen by
 // the launcher whenever TcScanArgs::tq is at most this. 0 = not available for (nf4, kp).
-int scan_tcr_tq_small(int nf4, int kp);
+int scan_tcr_tq_small(int nf4, int kp, bool one = false);
 int scan_tcr_kpart(int nf4, int k);
 cudaError_t launch_ivf_scan_tcr(int metric, uint32_t max_items, const TcScanArgs& a,
                                 cudaStream_t st);

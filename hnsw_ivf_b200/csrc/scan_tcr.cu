@@ -80,7 +80,7 @@ struct RShape {
     static constexpr uint32_t TmemCols = ONE ? 128 : (SMALL ? 256 : 512);
     static constexpr uint32_t DStride = ONE ? 64 : (SMALL ? 64 : 128); // columns per accumulator
     static constexpr uint32_t ColsA = SMALL ? 128 : 256;  // first column of the lo ring
-    static constexpr int MaxTQ = SMALL ? 32 : 64;
+    static constexpr int MaxTQ = (SMALL && !ONE) ? 32 : 64;
 };
 constexpr size_t kRSmemBig = 227 * 1024, kRSmemSmall = 113 * 1024;
 constexpr int kRKC = 8;           // float4 columns per stage (4 MMA k-steps)
@@ -101,11 +101,13 @@ constexpr uint32_t kRBSBO = 128;
 // compacted at 48 make it one tile in four.
 // KP up to 256 (the reference's reservoir range, faiss/impl/ResultHandler.h:369-477: k >= 100):
 // C = 2 KP entries, compacted when three quarters full.
-__host__ __device__ constexpr int tcr_cand(int kp) {
-    return kp <= 32 ? 64 : 2 * kp;
+__host__ __device__ constexpr int tcr_cand(int kp, bool one = false) {
+    // (one-MMA kernels, KP = 16: 32 entries, so that 64 queries' buffers fit beside the ring in
+    // the half of an SM's shared memory a two-CTAs-per-SM item has)
+    return (one && kp == 16) ? 32 : (kp <= 32 ? 64 : 2 * kp);
 }
-__host__ __device__ constexpr int tcr_compact_at(int kp) {
-    return tcr_cand(kp) - tcr_cand(kp) / 4;
+__host__ __device__ constexpr int tcr_compact_at(int kp, bool one = false) {
+    return tcr_cand(kp, one) - tcr_cand(kp, one) / 4;
 }
 
 __device__ __forceinline__ float tf32_trunc(float x) {
@@ -122,11 +124,11 @@ __device__ __forceinline__ float tf32_lo_raw(float y) {
     return y - tf32_trunc(y);
 }
 
-template <int KP>
+template <int KP, bool ONE = false>
 struct RCfg {
-    static constexpr int C = tcr_cand(KP);          // candidate entries per query
-    static constexpr int CompactAt = tcr_compact_at(KP);
-    static_assert(KP + 16 <= CompactAt, "compaction must leave room above the kept entries");
+    static constexpr int C = tcr_cand(KP, ONE);     // candidate entries per query
+    static constexpr int CompactAt = tcr_compact_at(KP, ONE);
+    static_assert(KP + 8 <= CompactAt, "compaction must leave room above the kept entries");
 };
 
 // ascending bitonic sort of one key per lane
@@ -213,38 +215,38 @@ struct RSmem {
 // left -- with few queries the kernel is an HBM stream and lives on bytes in flight.
 //   B: nch chunks x LBO bytes, LBO = (2 * n16 + 1) * 16 (odd multiple of 16: the coalesced
 //   prologue stores of one query row hit 8 different 16-byte bank groups)
-__host__ __device__ inline uint32_t tcr_lbo(int n16) {
-    return (uint32_t)(2 * n16 + 1) * 16u;
+__host__ __device__ inline uint32_t tcr_lbo(int n16, bool one = false) {
+    // (one-MMA kernels keep x_hi alone: n16 rows per chunk)
+    return (uint32_t)((one ? n16 : 2 * n16) + 1) * 16u;
 }
-__host__ __device__ inline size_t tcr_rest_bytes(int kp, int n16, int nch) {
-    return (size_t)nch * tcr_lbo(n16) + (size_t)n16 * tcr_cand(kp) * 8 +
+__host__ __device__ inline size_t tcr_rest_bytes(int kp, int n16, int nch, bool one = false) {
+    return (size_t)nch * tcr_lbo(n16, one) + (size_t)n16 * tcr_cand(kp, one) * 8 +
             (size_t)kTcrTQ * 7 * 4 + 4 * 4 + (2 * kRMaxStages + 2 * kRAStages + 4) * 8 + 16;
 }
 __host__ __device__ inline int tcr_stages(size_t smem_total, int kp, int n16, int nch,
-                                          bool even = true) {
-    const size_t rest = tcr_rest_bytes(kp, n16, nch);
+                                          bool even = true, bool one = false) {
+    const size_t rest = tcr_rest_bytes(kp, n16, nch, one);
     const int n = smem_total > rest ? (int)((smem_total - rest) / (kRStageF4 * sizeof(float4))) : 0;
-    // EVEN, always: the two split-warp groups take alternate iterations, so with an even ring a
-    // stage is always consumed by the same group, which therefore saw the stage's previous phase
-    // complete before it waits for the next one. With an odd ring the groups swap stages every
-    // lap; a group that runs ahead then waits on parity p of a barrier still in the phase BEFORE
-    // the one it thinks it follows, the wait passes at once (try_wait.parity is true for the
-    // phase preceding the current one), and the ring protocol falls apart: stale stages, a second
-    // expect_tx on a barrier whose load is still in flight, loads landing after the CTA has gone
-    // (seen as rare launch failures on cold first searches at d = 960, where the ring had 5 stages).
-    // (one split group -- the two-CTAs-per-SM shape -- has no such constraint: even = false)
+    // EVEN, always (3xTF32 kernels with two split-warp groups): the groups take alternate
+    // iterations, so with an even ring a stage is always consumed by the same group, which
+    // therefore saw the stage's previous phase complete before it waits for the next one. With an
+    // odd ring the groups swap stages every lap; a group that runs ahead then waits on parity p of
+    // a barrier still in the phase BEFORE the one it thinks it follows, the wait passes at once
+    // (try_wait.parity is true for the phase preceding the current one), and the ring protocol
+    // falls apart (seen as rare launch failures on cold first searches at d = 960, where the ring
+    // had 5 stages). One split group, or none, has no such constraint: even = false.
     const int c = n > kRMaxStages ? kRMaxStages : n;
     return even ? (c & ~1) : c;
 }
 
-template <int KP>
+template <int KP, bool ONE>
 __device__ __forceinline__ RSmem carve_r(unsigned char* raw, int nst, int n16, int nch) {
     RSmem s;
-    const size_t bbytes = (size_t)nch * tcr_lbo(n16);
+    const size_t bbytes = (size_t)nch * tcr_lbo(n16, ONE);
     s.raw = reinterpret_cast<float4*>(raw);
     s.b = raw + (size_t)nst * kRStageF4 * sizeof(float4);
     s.cand = reinterpret_cast<uint64_t*>(s.b + bbytes);
-    s.thr = reinterpret_cast<uint32_t*>(s.cand + (size_t)n16 * RCfg<KP>::C);
+    s.thr = reinterpret_cast<uint32_t*>(s.cand + (size_t)n16 * RCfg<KP, ONE>::C);
     s.thrp = reinterpret_cast<float*>(s.thr + kTcrTQ);
     s.thrf = s.thrp + kTcrTQ;
     s.xn = s.thrf + kTcrTQ;
@@ -264,14 +266,14 @@ __device__ __forceinline__ RSmem carve_r(unsigned char* raw, int nst, int n16, i
 
 // Compaction of the candidate buffers a warp owns (queries = warp mod 8), out of line: sort, keep
 // the best KP, tighten the query's bound and publish it for the other CTAs.
-template <int KP, int kREpiWarps>
+template <int KP, int kREpiWarps, bool ONE>
 __device__ __noinline__ void tcr_compact(uint64_t* cand, int* cnt, uint32_t* thr, float* thrp,
                                          float* thrf, const float* xn, const int* qid,
                                          uint32_t* qthr, int nqw, int warp, int lane,
                                          bool final_pass) {
-    constexpr int C = RCfg<KP>::C;
+    constexpr int C = RCfg<KP, ONE>::C;
     const int qmine = lane * kREpiWarps + warp;
-    const bool need = qmine < nqw && (final_pass || cnt[qmine] >= RCfg<KP>::CompactAt);
+    const bool need = qmine < nqw && (final_pass || cnt[qmine] >= RCfg<KP, ONE>::CompactAt);
     unsigned todo = __ballot_sync(0xffffffffu, need);
     while (todo != 0u) {
         const int qi = (__ffs(todo) - 1) * kREpiWarps + warp;
@@ -279,7 +281,13 @@ __device__ __noinline__ void tcr_compact(uint64_t* cand, int* cnt, uint32_t* thr
         const int n = min(cnt[qi], C);
         uint64_t* buf = cand + (size_t)qi * C;
         uint64_t kth;
-        if (C == 64) {
+        if (C == 32) {
+            uint64_t k0 = lane < n ? buf[lane] : kSentinelKey;
+            k0 = warp_sort32(k0, lane);
+            if (lane < KP)
+                buf[lane] = k0;
+            kth = __shfl_sync(0xffffffffu, k0, (KP - 1) & 31);
+        } else if (C == 64) {
             uint64_t k0 = lane < n ? buf[lane] : kSentinelKey;
             uint64_t k1 = lane + 32 < n ? buf[lane + 32] : kSentinelKey;
             warp_sort64(k0, k1, lane);
@@ -324,12 +332,12 @@ __device__ __noinline__ void tcr_compact(uint64_t* cand, int* cnt, uint32_t* thr
 // append them to the queries' buffers. Returns the columns this lane pushed past a full buffer
 // (re-examined after the compaction); fl collects what the block must do after the tile
 // (1 = compact, 2 = a buffer overflowed).
-template <int KP>
+template <int KP, bool ONE>
 __device__ __forceinline__ uint32_t tcr_filter_chunk(const uint32_t (&v)[16], int ch, bool first,
                                                      uint32_t dbits, float nrm, float nrmf,
                                                      uint32_t rowid, int row_in_list, bool limited,
                                                      const RSmem& s, int& fl, int& n_events) {
-    constexpr int C = RCfg<KP>::C;
+    constexpr int C = RCfg<KP, ONE>::C;
     float dd[16];
 #pragma unroll
     for (int j4 = 0; j4 < 4; ++j4) {
@@ -369,7 +377,7 @@ __device__ __forceinline__ uint32_t tcr_filter_chunk(const uint32_t (&v)[16], in
                 ndrop |= 1u << j;
                 fl |= 2;
             }
-            if (slot + 1 >= RCfg<KP>::CompactAt)
+            if (slot + 1 >= RCfg<KP, ONE>::CompactAt)
                 fl |= 1;
         }
     }
@@ -404,7 +412,7 @@ __global__ void __launch_bounds__(RShape<SMALL, ONE>::Threads, RShape<SMALL, ONE
     constexpr int kRLoaderWarps = SH::LoaderWarps, kRSplitGroups = SH::SplitGroups;
     constexpr int kAStages = SH::AStages;
     constexpr uint32_t kRColsA = SH::ColsA, kDStride = SH::DStride;
-    constexpr int C = RCfg<KP>::C;
+    constexpr int C = RCfg<KP, ONE>::C;
     const int tid = threadIdx.x;
     const int lane = tid & 31;
     const int warp = tid >> 5;
@@ -449,10 +457,10 @@ __global__ void __launch_bounds__(RShape<SMALL, ONE>::Threads, RShape<SMALL, ONE
     const int nsg = (nf4 + kRKC - 1) / kRKC;  // stages per tile
     const int nks = (nf4 + 1) >> 1;           // MMA k-steps (8 dims each) per tile
     const int niter = ntiles * nsg;
-    const int nst = tcr_stages((size_t)a.nstages * 1024, KP, n16, 2 * nks, !SMALL && !ONE);
-    const uint32_t lbo = tcr_lbo(n16);
+    const int nst = tcr_stages((size_t)a.nstages * 1024, KP, n16, 2 * nks, !SMALL && !ONE, ONE);
+    const uint32_t lbo = tcr_lbo(n16, ONE);
 
-    const RSmem s = carve_r<KP>(smem_raw, nst, n16, 2 * nks);
+    const RSmem s = carve_r<KP, ONE>(smem_raw, nst, n16, 2 * nks);
     const bool tracing = a.trace != nullptr && item == a.trace_item;
     // one MMA per k-step (y_hi . x_hi only): the tensor core is a FILTER with a known error bound,
     // see TcScanArgs::one_mma
@@ -583,7 +591,8 @@ __global__ void __launch_bounds__(RShape<SMALL, ONE>::Threads, RShape<SMALL, ONE
                     lo.w = tf32_lo(h.w);
                     const size_t off = (size_t)c * lbo + (size_t)n * 16;
                     *reinterpret_cast<float4*>(s.b + off) = h;                     // row n
-                    *reinterpret_cast<float4*>(s.b + off + (size_t)n16 * 16) = lo; // row n16 + n
+                    if (!ONE)
+                        *reinterpret_cast<float4*>(s.b + off + (size_t)n16 * 16) = lo; // row n16 + n
                 }
             }
         }
@@ -800,8 +809,8 @@ __global__ void __launch_bounds__(RShape<SMALL, ONE>::Threads, RShape<SMALL, ONE
             // The warp's chunks of 16 queries: ch = half + u * (epilogue warps per quarter), u < 2
             constexpr int kChStride = kREpiWarps / 4;
             constexpr int kChPerWarp = (SH::MaxTQ / 16 + kChStride - 1) / kChStride;
-            static_assert(kChPerWarp == 2, "two chunks per epilogue warp");
-            uint32_t dropw = 0u; // 16 bits per chunk: columns pushed past a full buffer
+            static_assert(ONE || kChPerWarp == 2, "two chunks per epilogue warp (16 drop bits each)");
+            uint64_t dropw = 0u; // 16 bits per chunk: columns pushed past a full buffer
             const bool limited = a.pair_limit != nullptr;
             TCR_WAIT(&s.d_full[b], (uint32_t)((t >> 1) & 1), w_dfull, 6, t);
             tc_fence_after_sync();
@@ -837,10 +846,11 @@ __global__ void __launch_bounds__(RShape<SMALL, ONE>::Threads, RShape<SMALL, ONE
                         const int ch = half + u * kChStride;
                         if (ch >= nch16 || (a.dbg & 1))
                             continue;
-                        const uint32_t nd = tcr_filter_chunk<KP>(
-                                vv[ONE ? u : 0], ch, round == 0, (dropw >> (u * 16)) & 0xffffu, nrm,
-                                nrmf, rowid, row_in_list, limited, s, fl, n_events);
-                        dropw = (dropw & ~(0xffffu << (u * 16))) | (nd << (u * 16));
+                        const uint32_t nd = tcr_filter_chunk<KP, ONE>(
+                                vv[ONE ? u : 0], ch, round == 0,
+                                (uint32_t)(dropw >> (u * 16)) & 0xffffu, nrm, nrmf, rowid,
+                                row_in_list, limited, s, fl, n_events);
+                        dropw = (dropw & ~(0xffffull << (u * 16))) | ((uint64_t)nd << (u * 16));
                     }
                 } else {
 #pragma unroll 1
@@ -859,10 +869,10 @@ __global__ void __launch_bounds__(RShape<SMALL, ONE>::Threads, RShape<SMALL, ONE
                                                        __uint_as_float(w[j]));
                         if (a.dbg & 1)
                             continue;
-                        const uint32_t nd = tcr_filter_chunk<KP>(
-                                vv[0], ch, round == 0, (dropw >> (u * 16)) & 0xffffu, nrm, nrmf,
-                                rowid, row_in_list, limited, s, fl, n_events);
-                        dropw = (dropw & ~(0xffffu << (u * 16))) | (nd << (u * 16));
+                        const uint32_t nd = tcr_filter_chunk<KP, ONE>(
+                                vv[0], ch, round == 0, (uint32_t)(dropw >> (u * 16)) & 0xffffu, nrm,
+                                nrmf, rowid, row_in_list, limited, s, fl, n_events);
+                        dropw = (dropw & ~(0xffffull << (u * 16))) | ((uint64_t)nd << (u * 16));
                     }
                 }
                 if (fl)
@@ -885,7 +895,7 @@ __global__ void __launch_bounds__(RShape<SMALL, ONE>::Threads, RShape<SMALL, ONE
                     c_comp += (tracing ? clock64() : 0) - tt1;
                     break; // the common case: one barrier per tile
                 }
-                tcr_compact<KP, kREpiWarps>(s.cand, s.cnt, s.thr, s.thrp, s.thrf, s.xn, s.qid, a.qthr, nqw, warp, lane,
+                tcr_compact<KP, kREpiWarps, ONE>(s.cand, s.cnt, s.thr, s.thrp, s.thrf, s.xn, s.qid, a.qthr, nqw, warp, lane,
                                 false);
                 named_bar_sync(2, kREpiWarps * 32);
                 c_comp += (tracing ? clock64() : 0) - tt1;
@@ -912,7 +922,7 @@ __global__ void __launch_bounds__(RShape<SMALL, ONE>::Threads, RShape<SMALL, ONE
             a.trace[9 * 64 + 5] = w_dfull;
         // ---- item done: best KP of every query, sorted, to `part` --------------------------------
         named_bar_sync(2, kREpiWarps * 32);
-        tcr_compact<KP, kREpiWarps>(s.cand, s.cnt, s.thr, s.thrp, s.thrf, s.xn, s.qid, a.qthr, nqw, warp, lane, true);
+        tcr_compact<KP, kREpiWarps, ONE>(s.cand, s.cnt, s.thr, s.thrp, s.thrf, s.xn, s.qid, a.qthr, nqw, warp, lane, true);
         __syncwarp();
         for (int qi = warp; qi < nqw; qi += kREpiWarps) {
             const int n = s.cnt[qi];
@@ -970,7 +980,7 @@ static cudaError_t launch_tcr_shape(uint32_t max_items, const TcScanArgs& a_in, 
     const size_t smem = SMALL ? kRSmemSmall : kRSmemBig;
     a.nstages = (int)(smem / 1024); // the kernel carves per item (tcr_stages)
     if (a.tq < 16 || a.tq > RShape<SMALL, ONE>::MaxTQ || (a.tq & 15) ||
-        tcr_stages(smem, KP, a.tq, 2 * ((a.nf4 + 1) >> 1), !SMALL && !ONE) < 3)
+        tcr_stages(smem, KP, a.tq, 2 * ((a.nf4 + 1) >> 1), !SMALL && !ONE, ONE) < 3)
         return cudaErrorInvalidValue;
     const int dbg = g_tc_dbg.load(std::memory_order_relaxed); // B200IVF_TC_DBG / "tc_dbg"
     a.dbg = a.nlists > 1 ? dbg : 0; // timing experiments; never for the coarse quantizer
@@ -1029,40 +1039,45 @@ static cudaError_t launch_tcr_shape(uint32_t max_items, const TcScanArgs& a_in, 
 // tq <= 32: the two-CTAs-per-SM shape, else the whole-SM one
 template <int METRIC, int KP>
 static cudaError_t launch_tcr_one(uint32_t max_items, const TcScanArgs& a, cudaStream_t st) {
-    const bool small = a.tq <= RShape<true>::MaxTQ &&
-            tcr_stages(kRSmemSmall, KP, a.tq, 2 * ((a.nf4 + 1) >> 1), false) >= 3;
-    if (a.one_mma)
+    const int nch = 2 * ((a.nf4 + 1) >> 1);
+    if (a.one_mma) {
+        const bool small = a.tq <= RShape<true, true>::MaxTQ &&
+                tcr_stages(kRSmemSmall, KP, a.tq, nch, false, true) >= 3;
         return small ? launch_tcr_shape<METRIC, KP, true, true>(max_items, a, st)
                      : launch_tcr_shape<METRIC, KP, false, true>(max_items, a, st);
+    }
+    const bool small = a.tq <= RShape<true, false>::MaxTQ &&
+            tcr_stages(kRSmemSmall, KP, a.tq, nch, false) >= 3;
     return small ? launch_tcr_shape<METRIC, KP, true, false>(max_items, a, st)
                  : launch_tcr_shape<METRIC, KP, false, false>(max_items, a, st);
 }
 
 // queries per item for dimension nf4*4 and kp kept keys: the largest multiple of 16 (<= kTcrTQ) that
 // leaves the raw ring at least 4 stages; 0 = the kernel cannot take this shape
-int scan_tcr_tq(int nf4, int kp) {
+int scan_tcr_tq(int nf4, int kp, bool one) {
     if (nf4 < 1 || nf4 > kRMaxChunks ||
         (kp != 16 && kp != 32 && kp != 64 && kp != 128 && kp != 256))
         return 0;
     const int nch = 2 * ((nf4 + 1) >> 1);
     for (int tq = kTcrTQ; tq >= 16; tq -= 16)
-        if (tcr_stages(227 * 1024, kp, tq, nch) >= 4)
+        if (tcr_stages(227 * 1024, kp, tq, nch, !one, one) >= 4)
+            return tq;
+    return 0;
+}
+// queries per item of the two-CTAs-per-SM shape (<= 32; <= 64 for the one-MMA kernels, whose
+// accumulators are half as wide), 0 = that shape cannot take (nf4, kp)
+int scan_tcr_tq_small(int nf4, int kp, bool one) {
+    if (!scan_tcr_tq(nf4, kp, one))
+        return 0;
+    const int nch = 2 * ((nf4 + 1) >> 1);
+    for (int tq = one ? RShape<true, true>::MaxTQ : RShape<true, false>::MaxTQ; tq >= 16; tq -= 16)
+        if (tcr_stages(kRSmemSmall, kp, tq, nch, false, one) >= 3)
             return tq;
     return 0;
 }
 // keys kept per partial list for a request of k: always a few more than k, because the scores
 // that select them are 3xTF32 ones and the exact fp32 re-rank (select.cu) can only re-order what
 // was kept: margin >= 4 for k <= 12, >= 8 above
-// queries per item of the two-CTAs-per-SM shape (<= 32), 0 = that shape cannot take (nf4, kp)
-int scan_tcr_tq_small(int nf4, int kp) {
-    if (!scan_tcr_tq(nf4, kp))
-        return 0;
-    const int nch = 2 * ((nf4 + 1) >> 1);
-    for (int tq = RShape<true>::MaxTQ; tq >= 16; tq -= 16)
-        if (tcr_stages(kRSmemSmall, kp, tq, nch, false) >= 3)
-            return tq;
-    return 0;
-}
 int scan_tcr_kpart(int nf4, int k) {
     const int kp = k + 4 <= 16 ? 16
             : k + 8 <= 32      ? 32
@@ -1070,7 +1085,7 @@ int scan_tcr_kpart(int nf4, int k) {
             : k + 8 <= 128     ? 128
             : k + 8 <= 256     ? 256
                                : 0;
-    return kp && scan_tcr_tq(nf4, kp) ? kp : 0;
+    return kp && scan_tcr_tq(nf4, kp, false) ? kp : 0;
 }
 
 int scan_tcr_kpart_one(int nf4, int k, int margin_min) {
@@ -1081,7 +1096,7 @@ int scan_tcr_kpart_one(int nf4, int k, int margin_min) {
             : need <= 128      ? 128
             : need <= 256      ? 256
                                : 0;
-    return kp && scan_tcr_tq(nf4, kp) ? kp : 0;
+    return kp && scan_tcr_tq(nf4, kp, true) ? kp : 0;
 }
 
 cudaError_t launch_ivf_scan_tcr(int metric, uint32_t max_items, const TcScanArgs& a,
