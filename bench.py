@@ -310,10 +310,16 @@ def parity_detail(D_ref, I_ref, D_new, I_new):
             "unexplained": r["unexplained"], "bad_dist": r["bad_dist"]}
 
 
-def scan_kernel_name(avg_q, d, k, simt_max=2.0, tcr_max=48.0):
-    """the list-scan kernel the library's plan picks (csrc/index.cu search_impl_) for this shape"""
+def scan_kernel_name(avg_q, d, k, simt_max=2.0, tcr_max=48.0, one_max=72.0, level=0):
+    """the list-scan kernel the library's plan picks (csrc/index.cu search_impl_) for this shape;
+    level: the handle's one-MMA level (0 / 1: one MMA + checked re-rank, 2: 3xTF32)"""
     if avg_q <= simt_max:
         return "ivf_scan_kernel (exact fp32 warp kernel)"
+    margin = max(6 if level == 0 else 16, k // 4)
+    one = level < 2 and k + margin <= 256
+    if one and (d > 128 or k > 24 or avg_q < max(tcr_max, one_max)):
+        return ("ivf_scan_tcr_kernel<ONE> (rows-major tcgen05, ONE tf32 MMA per k-step as a filter with "
+                "a proven error bound + checked exact re-rank, <= 64 queries per item)")
     if d > 128 or k > 24 or avg_q < tcr_max:
         shape = "two CTAs per SM" if (avg_q <= 32 and d <= 128) else "one CTA per SM"
         return "ivf_scan_tcr_kernel (rows-major tcgen05 3xTF32, 2 MMAs per k-step, %s)" % shape
@@ -687,11 +693,12 @@ def bench_flat(args, ctx, tf32_peak):
                      "reference_streamed_bytes_per_launch": ref_bytes,
                      "reference_streamed_equiv_gbs": ref_bytes / scan_s / 1e9 if scan_s > 0 else 0.0,
                      "tensor": {"useful_tflops": useful_tflops,
-                                "mmas_per_useful_product": 3 if "queries-major" in kname else 2,
+                                "mmas_per_useful_product": (1 if "<ONE>" in kname else
+                                                            3 if "queries-major" in kname else 2),
                                 "tf32_peak_tflops": tf32_peak,
                                 "frac_useful": useful_tflops / tf32_peak,
-                                "note": "3xTF32 split; the peak is a dense cuBLAS TF32 GEMM "
-                                        "(8192^3) timed in this run"},
+                                "note": "the peak is a dense cuBLAS TF32 GEMM (8192^3) timed in "
+                                        "this run"},
                      "coarse": {"kernel": "ivf_scan_tc_kernel over the centroid table (nprobe <= 24)"
                                           " / ivf_scan_tcr_kernel (above)",
                                 "flops": coarse_flops, "ms": coarse_s * 1e3,
@@ -707,6 +714,9 @@ def bench_flat(args, ctx, tf32_peak):
         "clocks": clocks,
         "cpu_baseline": cpu,
         "parity": parity,
+        # queries the checked re-rank could not prove and the library searched again on the exact
+        # kernel, over every search of this handle (sweeps, warm-up, timed)
+        "exact_redo_queries": int(g.exact_redo_count()),
     }
     if world > 1:
         out["phase_ms"] = phase

@@ -171,8 +171,19 @@ struct IndexIVFFlatB200::Impl {
     // max |y|^2 over the slab, the queries whose result the checked re-rank could not prove, and
     // the scratch of their second, exact pass
     Buffer ymax2, flag_list, flag_count, host_flag, fb_x, fb_D, fb_I, fb_assign, fb_p32;
-    int tc_split = 3;                   // "tc_split": 3 = 3xTF32 (default), 1 = one MMA + checked re-rank
-    int one_margin = 16;                // "one_margin": keys kept beyond k in that mode (at least)
+    // "tc_split" / B200IVF_TC_SPLIT: 1 = one MMA per k-step + checked re-rank (default),
+    // 3 = the 3xTF32 split with a fixed re-rank margin (A/B runs)
+    int tc_split = 1;
+    // "one_margin": keys kept beyond k in that mode, at least (the error window of the k-th score
+    // holds one or two rows beyond k on real data; what does not fit is redone exactly)
+    int one_margin = 6;
+    // queries per probed list below which the one-MMA rows-major kernel is preferred to the
+    // queries-major 3xTF32 one (an item takes 64 queries: up to about one item per list)
+    double one_max_avg_q = 72.0;
+    // How well the error window fits the data is a property of the data (tight clusters far from
+    // the origin crowd it): a handle whose second pass took more than 1/64 of a batch moves up a
+    // level and stays there -- 0: one_margin, 1: a margin of 16 at least, 2: the 3xTF32 split
+    int one_level = 0;
     unsigned long long fallback_queries = 0; // queries redone on the exact path so far
     Buffer coarse_ids, coarse_dis, part, count, fill, grp_start, item_off, item_off_tile,
             pair_query, slot_of,
@@ -304,6 +315,8 @@ struct IndexIVFFlatB200::Impl {
     Impl() {
         const char* e = getenv("B200IVF_NO_TC");
         use_tc = !(e && e[0] == '1');
+        if (const char* sp = getenv("B200IVF_TC_SPLIT"))
+            tc_split = atoi(sp) == 3 ? 3 : 1;
         const char* e2 = getenv("B200IVF_TC_MODE");
         tc_mode = e2 ? atoi(e2) : 0;
         const char* e3 = getenv("B200IVF_NO_GRAPH");
@@ -832,17 +845,23 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
     bool simt_only = (filtered && kp_r == 0) || !m.use_tc || avg_q <= m.simt_max_avg_q ||
             (kp_q == 0 && kp_r == 0);
     bool tc = !simt_only;
+    const int one_margin = m.one_level == 0 ? m.one_margin : std::max(m.one_margin, 16);
+    const int kp_one = scan_tcr_kpart_one(m.nf4, (int)std::min<int64_t>(k, 1 << 20), one_margin);
+    const bool one_ok = m.tc_split == 1 && m.one_level < 2 && kp_one > 0;
     bool tcr = tc && (filtered || kp_q == 0 ||
-                      (kp_r > 0 && (m.tc_mode == 2 ||
-                                    (m.tc_mode == 0 && avg_q < m.tcr_max_avg_q))));
+                      ((kp_r > 0 || one_ok) &&
+                       (m.tc_mode == 2 ||
+                        (m.tc_mode == 0 &&
+                         avg_q < (one_ok ? std::max(m.one_max_avg_q, m.tcr_max_avg_q)
+                                         : m.tcr_max_avg_q)))));
+    if (tcr && kp_r == 0 && !one_ok) // (filtered, k beyond what the rows-major kernel keeps)
+        tcr = false, tc = false, simt_only = true;
     // ONE-MMA filter mode (rows-major kernel only): the tensor core computes tf32(x) . tf32(y)
     // alone -- a third of the MMAs, no operand split -- and the k-select proves, query by query,
     // that nothing outside the exactly re-scored set could have reached the top k
     // (SelectArgs::err_coef); the few queries it cannot prove are searched again on the exact
     // warp kernel before the call returns
-    const int kp_one =
-            scan_tcr_kpart_one(m.nf4, (int)std::min<int64_t>(k, 1 << 20), m.one_margin);
-    bool one = tc && tcr && m.tc_split == 1 && kp_one > 0;
+    bool one = tc && tcr && one_ok;
     int64_t kp = tc ? (tcr ? (one ? kp_one : kp_r) : kp_q) : k; // entries per partial list
     // few queries per list: the two-CTAs-per-SM shape of the rows-major kernel (<= 32 queries per
     // item; a list probed by more is cut into several items)
@@ -1072,7 +1091,7 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
                 // checked re-rank: everything inside the error window of the k-th score is
                 // re-scored (the window holds a handful of rows: a margin of max(16, k / 4))
                 se.rerank_extra =
-                        (int)std::min<int64_t>(std::max<int64_t>(m.one_margin, k / 4), kp - k);
+                        (int)std::min<int64_t>(std::max<int64_t>(one_margin, k / 4), kp - k);
                 se.err_coef = kOneMmaErrCoef;
                 se.ymax2 = m.ymax2.as<float>();
                 se.qthr = m.qthr.as<uint32_t>();
@@ -1256,6 +1275,8 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
                                        cudaMemcpyDeviceToHost, st));
             CUDA_CHECK(cudaStreamSynchronize(st));
             const int64_t nf = *m.host_flag.as<int32_t>();
+            if (nf * 64 > ni && ni >= 256 && m.one_level < 2)
+                m.one_level++; // (takes effect with the next call)
             if (nf > 0) {
                 m.fallback_queries += (unsigned long long)nf;
                 m.fb_x.reserve((size_t)nf * d * sizeof(float));
@@ -1430,10 +1451,16 @@ void IndexIVFFlatB200::set_option(const char* name, double value) {
         m.coarse_tq = (int)value;
     else if (n == "coarse_s")
         m.coarse_s_override = (int)value;
-    else if (n == "tc_split") // 1 = one MMA + checked re-rank (rows-major kernel), 3 = 3xTF32
+    else if (n == "tc_split") { // 1 = one MMA + checked re-rank (rows-major kernel), 3 = 3xTF32
         m.tc_split = value == 1 ? 1 : 3;
-    else if (n == "one_margin")
+        m.one_level = 0;
+    }
+    else if (n == "one_max_avg_q")
+        m.one_max_avg_q = value;
+    else if (n == "one_margin") {
         m.one_margin = std::max(1, (int)value);
+        m.one_level = 0;
+    }
     else if (n == "tcr_small_factor")
         m.tcr_small_factor = value;
     else if (n == "tcr_small_max_avg_q")

@@ -674,7 +674,8 @@ __global__ void __launch_bounds__(RShape<SMALL, ONE>::Threads, RShape<SMALL, ONE
                 const bool last = sg == nsg - 1;
                 if (elect_one_sync()) {
                     if (one) {
-                        if (ksn >= kRKC / 2) {
+                        if (a.dbg & 8) { // timing experiment: no MMAs
+                        } else if (ksn >= kRKC / 2) {
 #pragma unroll
                             for (int ks = 0; ks < kRKC / 2; ++ks)
                                 mma_tf32_ss(tD, dah + ks * ka_step, db + ks * kb_step, idesc1,
@@ -822,11 +823,26 @@ __global__ void __launch_bounds__(RShape<SMALL, ONE>::Threads, RShape<SMALL, ONE
             // eight more warps to share the register file with: it goes chunk by chunk.)
             uint32_t vv[ONE ? kChPerWarp : 1][16];
             if (ONE) {
+                if (kChStride == 1) {
+                    // (columns 0 .. n16-1 are this warp's: ONE load instruction for all of them)
+                    constexpr int u1 = ONE && kChPerWarp > 1 ? 1 : 0, u2 = ONE && kChPerWarp > 2 ? 2 : 0,
+                                  u3 = ONE && kChPerWarp > 3 ? 3 : 0;
+                    if (nch16 == 4)
+                        tmem_ld_32x32b_x64_split(tD, vv[0], vv[u1], vv[u2], vv[u3]);
+                    else if (nch16 == 3) {
+                        tmem_ld_32x32b_x32_split(tD, vv[0], vv[u1]);
+                        tmem_ld_32x32b_x16(tD + 32u, vv[u2]);
+                    } else if (nch16 == 2)
+                        tmem_ld_32x32b_x32_split(tD, vv[0], vv[u1]);
+                    else
+                        tmem_ld_32x32b_x16(tD, vv[0]);
+                } else {
 #pragma unroll
-                for (int u = 0; u < kChPerWarp; ++u) {
-                    const int ch = half + u * kChStride;
-                    if (ch < nch16)
-                        tmem_ld_32x32b_x16(tD + (uint32_t)ch * 16u, vv[ONE ? u : 0]);
+                    for (int u = 0; u < kChPerWarp; ++u) {
+                        const int ch = half + u * kChStride;
+                        if (ch < nch16)
+                            tmem_ld_32x32b_x16(tD + (uint32_t)ch * 16u, vv[ONE ? u : 0]);
+                    }
                 }
                 tmem_ld_wait();
                 tc_fence_before_sync();
