@@ -137,12 +137,15 @@ void b200_IndexIVFFlat_last_timings(const B200IndexIVFFlat* index, double* ms5);
 /* ... and the same five figures summed over every search call since reset_stats (so a timed loop
  * need not stop after each call to read them); returns the number of calls */
 unsigned long long b200_IndexIVFFlat_stage_time_sums(const B200IndexIVFFlat* index, double* ms5);
-/* Queries that were searched a second time on the exact kernel, since the handle was created. With
- * set_option("tc_split", 1) the list scan uses the tensor cores as a FILTER (one tf32 product, known
+/* Queries that were searched a second time on the exact kernel, since the handle was created. By
+ * default ("tc_split" = 1) the list scan uses the tensor cores as a FILTER (one tf32 product, known
  * error bound) and the k-select proves per query that the exactly re-scored candidates contain the
  * exact top k; a query it cannot prove (many rows within the bound of the k-th distance) is redone
  * exactly before the call returns. Results never depend on the option; this counter says how
- * often the second pass ran. No counterpart in the reference. */
+ * often the second pass ran. A handle whose second pass takes more than 1/64 of a batch keeps more
+ * spare candidates from then on, and falls back to the 3xTF32 split if that is not enough.
+ * (Searches in this mode read one 4-byte counter back before they return, so they complete
+ * synchronously even with device buffers.) No counterpart in the reference. */
 unsigned long long b200_IndexIVFFlat_exact_redo_count(const B200IndexIVFFlat* index);
 
 /* Run on a caller-owned CUDA stream (cudaStream_t as void*; NULL = the handle's own stream, a
@@ -160,7 +163,10 @@ int b200_IndexIVFFlat_synchronize(const B200IndexIVFFlat* index);
 /* Kernel-selection knobs of the scan (what faiss exposes through ParameterSpace::set_index_parameter,
  * faiss/AutoTune.h:127-170, for its own indexes): "simt_max_avg_q", "tcr_max_avg_q" (queries per
  * probed list below which the exact warp kernel / the rows-major tensor-core kernel takes the
- * scan), "tc_mode" (0 auto, 1 queries-major, 2 rows-major), "use_tc", "use_graph". They change
+ * scan), "tc_mode" (0 auto, 1 queries-major, 2 rows-major), "use_tc", "use_graph", "tc_split" (1 =
+ * one tf32 product per 8 dimensions + checked re-rank, the default; 3 = 3xTF32 with a fixed re-rank
+ * margin), "one_margin" (spare candidates kept per partial list in that mode, default 6),
+ * "one_max_avg_q" (queries per probed list up to which that kernel is preferred). They change
  * which kernels run, never the results. Also here, for want of a struct accessor in a C API: the
  * quantizer's ClusteringParameters as IndexIVF exposes them (index.cp, faiss/IndexIVF.h:39-41,
  * faiss/Clustering.h:23-64): "cp_niter", "cp_max_points_per_centroid", "cp_seed" -- read by train.
