@@ -219,6 +219,7 @@ def regime_c4s(args, torch, b2, dev):
         st, tot = [], []
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         torch.cuda.synchronize()
+        torch.cuda.profiler.start()  # ncu --profile-from-start off sees only the timed steps
         e0.record()
         for _ in range(args.steps):
             g.search(xq, k, D=Dd, I=Id)
@@ -226,6 +227,7 @@ def regime_c4s(args, torch, b2, dev):
             st.append(t)
         e1.record()
         torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
         ms = e0.elapsed_time(e1) / args.steps
         scan = statistics.mean(t["scan"] for t in st)
         ndis = g.get_stats().ndis / args.steps
