@@ -479,9 +479,7 @@ __global__ void __launch_bounds__(RShape<SMALL, ONE>::Threads, RShape<SMALL, ONE
             mbar_init(&s.empty[i], one ? 1 : 4 + 1); // one split group (4 warps) + the MMA commit
         }
         for (int i = 0; i < kRAStages; ++i) {
-            // (one-MMA kernels have no lo ring: slots 0 / 1 say "the epilogue has ISSUED its
-            // loads of accumulator buffer 0 / 1")
-            mbar_init(&s.a_rdy[i], ONE ? kREpiWarps : 4);
+            mbar_init(&s.a_rdy[i], 4);
             mbar_init(&s.a_empty[i], 1);
         }
         for (int i = 0; i < 2; ++i) {
@@ -657,12 +655,6 @@ __global__ void __launch_bounds__(RShape<SMALL, ONE>::Threads, RShape<SMALL, ONE
                 tc_fence_after_sync();
             }
             const uint32_t tD = tmem + kRColsD + (uint32_t)b * kDStride;
-            if (ONE && t >= 1 && (a.dbg & 16)) {
-                // experiment: the tensor pipe takes its work in order, so the epilogue's
-                // tcgen05.ld of tile t - 1 should enter it BEFORE the MMAs of tile t
-                TCR_WAIT(&s.a_rdy[(t - 1) & 1], (uint32_t)(((t - 1) >> 1) & 1), w_dempty, 7, t);
-                tc_fence_after_sync();
-            }
             for (int sg = 0; sg < nsg; ++sg) {
                 if (one)
                     TCR_WAIT(&s.full[rst], rph, w_ardy, 3, t * nsg + sg);
@@ -851,11 +843,6 @@ __global__ void __launch_bounds__(RShape<SMALL, ONE>::Threads, RShape<SMALL, ONE
                         if (ch < nch16)
                             tmem_ld_32x32b_x16(tD + (uint32_t)ch * 16u, vv[ONE ? u : 0]);
                     }
-                }
-                if (a.dbg & 16) {
-                    __syncwarp();
-                    if (lane == 0)
-                        mbar_arrive(&s.a_rdy[b]); // loads issued
                 }
                 tmem_ld_wait();
                 tc_fence_before_sync();
