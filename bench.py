@@ -310,13 +310,16 @@ def parity_detail(D_ref, I_ref, D_new, I_new):
             "unexplained": r["unexplained"], "bad_dist": r["bad_dist"]}
 
 
-def scan_kernel_name(avg_q, d, k, simt_max=2.0, tcr_max=48.0, one_max=72.0, level=0):
+def scan_kernel_name(avg_q, d, k, simt_max=2.0, tcr_max=48.0, one_max=72.0, level=0,
+                     lists_probed=1e9, one_min_items=1184.0):
     """the list-scan kernel the library's plan picks (csrc/index.cu search_impl_) for this shape;
     level: the handle's one-MMA level (0 / 1: one MMA + checked re-rank, 2: 3xTF32)"""
     if avg_q <= simt_max:
         return "ivf_scan_kernel (exact fp32 warp kernel)"
     margin = max(6 if level == 0 else 16, k // 4)
-    one = level < 2 and k + margin <= 256
+    import math
+    one = (level < 2 and k + margin <= 256 and
+           (lists_probed * math.ceil(avg_q / 64.0) >= one_min_items or d > 128 or k > 24))
     if one and (d > 128 or k > 24 or avg_q < max(tcr_max, one_max)):
         return ("ivf_scan_tcr_kernel<ONE> (rows-major tcgen05, ONE tf32 MMA per k-step as a filter with "
                 "a proven error bound + checked exact re-rank, <= 64 queries per item)")
@@ -645,7 +648,8 @@ def bench_flat(args, ctx, tf32_peak):
     traffic = scan_traffic_bytes(args.workload, nprobe) if world == 1 else None
     useful_tflops = 2.0 * d * slow["ndis"] / scan_s / 1e12 if scan_s > 0 else 0.0
     avg_q = ndis_all / max(rows_all, 1)
-    kname = scan_kernel_name(avg_q, d, k)
+    kname = scan_kernel_name(avg_q, d, k,
+                             lists_probed=min(nlist / float(world), nq * nprobe / float(world)))
     coarse_s = (phase["coarse"] if phase else stage["coarse"]) / 1e3
     coarse_flops = 2.0 * (nq / float(world)) * nlist * d  # this rank's query slice
     coarse_tf = coarse_flops / coarse_s / 1e12 if coarse_s > 0 else 0.0
@@ -1018,7 +1022,10 @@ def bench_c4(args, ctx, tf32_peak, headline):
           "nprobe_sweep": [[p, round(r, 4)] for p, r in sweep],
           "qps": nq * steps / (ms / 1e3), "ms_per_step": ms / steps, "steps": steps,
           "stage_ms_rank0": stage, "phase_ms_rank0": phase, "build": tb,
-          "scan": {"kernel": scan_kernel_name(avg_q, d, k), "per_rank": ranks,
+          "scan": {"kernel": scan_kernel_name(avg_q, d, k,
+                                              lists_probed=min(nlist / float(world),
+                                                               nq * nprobe / float(world))),
+                   "per_rank": ranks,
                    "min_frac_of_hbm_peak": min(r["frac"] for r in ranks),
                    "peak_gbs": peak, "peak_source": peak_src,
                    "peak_note": ("the measured peak is a COPY (bytes read + written); the scan only reads, and a read-only stream can pass it -- the HGX B200 figure is 7700 GB/s (B200_PROFILING.md)"),

@@ -180,6 +180,7 @@ struct IndexIVFFlatB200::Impl {
     // queries per probed list below which the one-MMA rows-major kernel is preferred to the
     // queries-major 3xTF32 one (an item takes 64 queries: up to about one item per list)
     double one_max_avg_q = 72.0;
+    double one_min_items = 1184.0; // "one_min_items": 4 waves of 2 x 148 CTAs
     // How well the error window fits the data is a property of the data (tight clusters far from
     // the origin crowd it): a handle whose second pass took more than 1/64 of a batch moves up a
     // level and stays there -- 0: one_margin, 1: a margin of 16 at least, 2: the 3xTF32 split
@@ -847,7 +848,13 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
     bool tc = !simt_only;
     const int one_margin = m.one_level == 0 ? m.one_margin : std::max(m.one_margin, 16);
     const int kp_one = scan_tcr_kpart_one(m.nf4, (int)std::min<int64_t>(k, 1 << 20), one_margin);
-    const bool one_ok = m.tc_split == 1 && m.one_level < 2 && kp_one > 0;
+    // ... and it needs enough work items to keep two CTAs per SM busy for several waves: the first
+    // wave runs with cold pruning bounds and with every prologue at once, the last one half empty
+    // (C2 over 8 GPUs: 512 lists per rank = 3.3 waves took 0.43 ms against 0.33 ms for the
+    // queries-major kernel, and the counter read-back delayed the result gather by 0.08 ms)
+    const double est_items = std::min((double)nlists_owned, pairs_own) * std::ceil(avg_q / 64.0);
+    const bool one_ok = m.tc_split == 1 && m.one_level < 2 && kp_one > 0 &&
+            (est_items >= m.one_min_items || filtered || kp_q == 0);
     bool tcr = tc && (filtered || kp_q == 0 ||
                       ((kp_r > 0 || one_ok) &&
                        (m.tc_mode == 2 ||
@@ -1455,6 +1462,8 @@ void IndexIVFFlatB200::set_option(const char* name, double value) {
         m.tc_split = value == 1 ? 1 : 3;
         m.one_level = 0;
     }
+    else if (n == "one_min_items")
+        m.one_min_items = value;
     else if (n == "one_max_avg_q")
         m.one_max_avg_q = value;
     else if (n == "one_margin") {

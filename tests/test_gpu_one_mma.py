@@ -41,6 +41,7 @@ def _pair(xb, cent, metric, assign=None, margin=6):
             g.set_option("tc_mode", 2)           # rows-major kernel
             g.set_option("tc_split", 1)          # one MMA + checked re-rank
             g.set_option("one_margin", margin)
+            g.set_option("one_min_items", 0)     # (small test shapes: few work items)
         g.set_centroids(cent)
         if assign is None:
             g.add_with_ids(xb, np.arange(xb.shape[0], dtype=np.int64))

@@ -2,7 +2,6 @@
 """tools/shard_phases.py -- per-phase device time of the list-sharded search (torchrun, N ranks):
 C2-shaped index (2M x 128 IP, nlist 4096, nprobe 24, 10k queries) split over the ranks."""
 import os
-import statistics
 import sys
 
 import torch
@@ -24,29 +23,27 @@ xq = torch.randn((nq, d), generator=g, device=dev)
 xq /= xq.norm(dim=1, keepdim=True)
 cent = xb[:nlist].contiguous()
 ix = b2.IndexShardsIVFFlat(d, nlist, 0, device=local)
-ix.local.set_stream(torch.cuda.current_stream().cuda_stream)
+ix.set_stream(torch.cuda.current_stream().cuda_stream)
 ix.set_centroids(cent)
-ix.add_with_ids(xb, None)
+lo, hi = rank * nb // world, (rank + 1) * nb // world
+ix.add_with_ids(xb[lo:hi].contiguous(), torch.arange(lo, hi, device=dev, dtype=torch.int64))
 ix.nprobe = nprobe
 for _ in range(5):
     ix.search(xq, k, broadcast_from=0)
-ix.trace = True
-acc = {}
-for _ in range(20):
-    ix.search(xq, k, broadcast_from=0)
-    for name, v in ix.last_phase_ms.items():
-        acc.setdefault(name, []).append(v)
-ix.trace = False
+# every rank brings 1/world of the vectors (distributed add); phase times come from the C++
+# object's CUDA events (b200_IndexShardsIVFFlat_phase_time_sums)
 torch.cuda.synchronize()
 dist.barrier()
+ix.reset_phase_times()
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 e0.record()
 for _ in range(20):
     ix.search(xq, k, broadcast_from=0)
 e1.record()
 torch.cuda.synchronize()
+calls, acc = ix.phase_time_sums()
 if rank == 0:
     print("world", world, "ms per step", round(e0.elapsed_time(e1) / 20, 3),
-          {n: round(statistics.median(v), 3) for n, v in acc.items()},
+          {n: round(v / max(calls, 1), 3) for n, v in acc.items()},
           "lib", {n: round(v, 3) for n, v in ix.local.last_timings().items()})
 dist.destroy_process_group()
