@@ -311,15 +311,14 @@ def parity_detail(D_ref, I_ref, D_new, I_new):
 
 
 def scan_kernel_name(avg_q, d, k, simt_max=2.0, tcr_max=48.0, one_max=72.0, level=0,
-                     lists_probed=1e9, one_min_items=1184.0):
+                     lists_probed=1e9, one_min_items=2368.0):
     """the list-scan kernel the library's plan picks (csrc/index.cu search_impl_) for this shape;
     level: the handle's one-MMA level (0 / 1: one MMA + checked re-rank, 2: 3xTF32)"""
     if avg_q <= simt_max:
         return "ivf_scan_kernel (exact fp32 warp kernel)"
     margin = max(6 if level == 0 else 16, k // 4)
-    import math
     one = (level < 2 and k + margin <= 256 and
-           (lists_probed * math.ceil(avg_q / 64.0) >= one_min_items or d > 128 or k > 24))
+           (lists_probed * max(1.0, avg_q / 64.0 + 0.5) >= one_min_items or d > 128 or k > 24))
     if one and (d > 128 or k > 24 or avg_q < max(tcr_max, one_max)):
         return ("ivf_scan_tcr_kernel<ONE> (rows-major tcgen05, ONE tf32 MMA per k-step as a filter with "
                 "a proven error bound + checked exact re-rank, <= 64 queries per item)")

@@ -171,6 +171,9 @@ struct IndexIVFFlatB200::Impl {
     // max |y|^2 over the slab, the queries whose result the checked re-rank could not prove, and
     // the scratch of their second, exact pass
     Buffer ymax2, flag_list, flag_count, host_flag, fb_x, fb_D, fb_I, fb_assign, fb_p32;
+    Buffer cent_ymax2;                  // max |c|^2 over the centroid table (one-MMA coarse scan)
+    int coarse_level = 0;               // as one_level, for the coarse quantizer
+    bool coarse_exact = false;          // the second, exact pass of a checked coarse scan is running
     // "tc_split" / B200IVF_TC_SPLIT: 1 = one MMA per k-step + checked re-rank (default),
     // 3 = the 3xTF32 split with a fixed re-rank margin (A/B runs)
     int tc_split = 1;
@@ -180,7 +183,7 @@ struct IndexIVFFlatB200::Impl {
     // queries per probed list below which the one-MMA rows-major kernel is preferred to the
     // queries-major 3xTF32 one (an item takes 64 queries: up to about one item per list)
     double one_max_avg_q = 72.0;
-    double one_min_items = 1184.0; // "one_min_items": 4 waves of 2 x 148 CTAs
+    double one_min_items = 2368.0; // "one_min_items": 8 waves of 2 x 148 CTAs
     // How well the error window fits the data is a property of the data (tight clusters far from
     // the origin crowd it): a handle whose second pass took more than 1/64 of a batch moves up a
     // level and stays there -- 0: one_margin, 1: a margin of 16 at least, 2: the 3xTF32 split
@@ -461,9 +464,11 @@ void IndexIVFFlatB200::set_centroids_(const float* c) {
                                    m.nf4, m.cent_slab.as<float>(), m.dev_I.as<int64_t>(), 0,
                                    m.stream));
     CUDA_CHECK(make_slab_tensor_map_tc(m.cent_map_tc, m.cent_slab.p, m.nf4, nblk));
+    m.cent_ymax2.reserve(sizeof(float));
+    CUDA_CHECK(cudaMemsetAsync(m.cent_ymax2.p, 0, sizeof(float), m.stream));
     m.cent_norms.reserve(nblk * kBlockRows * sizeof(float));
     CUDA_CHECK(launch_row_norms(m.cent_slab.as<float4>(), (int64_t)(nblk * kBlockRows), m.nf4,
-                                m.cent_norms.as<float>(), m.stream));
+                                m.cent_norms.as<float>(), m.stream, m.cent_ymax2.as<float>()));
     m.cent_meta.reserve(16);
     const uint32_t blk0 = 0;
     const int32_t len = (int32_t)nlist;
@@ -581,12 +586,30 @@ void IndexIVFFlatB200::run_coarse_(const float* xd, int64_t n, int kc, int32_t* 
     const int nf4 = m.nf4;
     const int kp_q = scan_tc_kpart(nf4, kc);   // queries-major kernel: d <= 128
     const int kp_r = scan_tcr_kpart(nf4, kc);  // rows-major kernel: d <= 1024
-    const bool tc = m.use_tc && n > 32 && (kp_q > 0 || kp_r > 0);
+    const bool tc = m.use_tc && n > 32 && (kp_q > 0 || kp_r > 0) && !m.coarse_exact;
     // full 128-query tiles: the queries-major kernel where it exists
     const bool tcr = tc && (kp_q == 0 || (m.tc_mode == 2 && kp_r > 0));
-    const int kp = tc ? (tcr ? kp_r : kp_q) : kc;
-    int tcr_tq = tcr ? scan_tcr_tq(nf4, kp) : 0;
-    if (tcr && m.coarse_tq > 0) { // tuning experiments
+    // Where the rows-major kernel takes the table (nprobe > 24, d > 128): its one-MMA filter form
+    // with the checked re-rank (see search_impl_); queries it cannot prove are quantized again on
+    // the exact SIMT kernels. Not while a CUDA graph is being captured (the check reads a counter
+    // back).
+    const int c_margin = m.coarse_level == 0 ? m.one_margin : std::max(m.one_margin, 16);
+    const int kp_one = scan_tcr_kpart_one(nf4, kc, c_margin);
+    bool one = tcr && m.tc_split == 1 && m.coarse_level < 2 && kp_one > 0 && n >= 256;
+    if (one) {
+        cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+        if (cudaStreamIsCapturing(st, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone)
+            one = false;
+        cudaGetLastError();
+    }
+    const int kp = tc ? (tcr ? (one ? kp_one : kp_r) : kp_q) : kc;
+    int tcr_tq = tcr ? scan_tcr_tq(nf4, kp, one) : 0;
+    if (one) { // two CTAs per SM where the shape exists
+        const int small = scan_tcr_tq_small(nf4, kp, true);
+        if (small > 0)
+            tcr_tq = small;
+    }
+    if (tcr && !one && m.coarse_tq > 0) { // tuning experiments
         const int small = scan_tcr_tq_small(nf4, kp);
         tcr_tq = m.coarse_tq <= small ? std::min(m.coarse_tq, small) : std::min(m.coarse_tq, tcr_tq);
         tcr_tq = std::max(16, tcr_tq & ~15);
@@ -652,6 +675,7 @@ void IndexIVFFlatB200::run_coarse_(const float* xd, int64_t n, int kc, int32_t* 
         CUDA_CHECK(launch_fill_u32(m.qthr.as<uint32_t>(), n, ordered_bits(kNeutralScore), st));
         a.qthr = m.qthr.as<uint32_t>();
         a.tq = tcr_tq;
+        a.one_mma = one ? 1 : 0;
         if (tcr)
             CUDA_CHECK(launch_ivf_scan_tcr(metric_type, (uint32_t)(ngroups * S), a, st));
         else
@@ -712,8 +736,53 @@ void IndexIVFFlatB200::run_coarse_(const float* xd, int64_t n, int kc, int32_t* 
         s.d = d;
         s.nf4 = nf4;
         s.rerank_extra = std::min(kRerankExtra, kp - kc);
+        if (one) {
+            s.rerank_extra = std::min(std::max(c_margin, kc / 4), kp - kc);
+            s.err_coef = kOneMmaErrCoef;
+            s.ymax2 = m.cent_ymax2.as<float>();
+            s.qthr = m.qthr.as<uint32_t>();
+            m.flag_list.reserve((size_t)n * sizeof(int32_t));
+            m.flag_count.reserve(sizeof(int32_t));
+            m.host_flag.reserve(sizeof(int32_t));
+            CUDA_CHECK(cudaMemsetAsync(m.flag_count.p, 0, sizeof(int32_t), st));
+            s.flag_list = m.flag_list.as<int32_t>();
+            s.flag_count = m.flag_count.as<int32_t>();
+        }
     }
     CUDA_CHECK(launch_select(s, st));
+    if (one) {
+        CUDA_CHECK(cudaMemcpyAsync(m.host_flag.p, m.flag_count.p, sizeof(int32_t),
+                                   cudaMemcpyDeviceToHost, st));
+        CUDA_CHECK(cudaStreamSynchronize(st));
+        const int64_t nf = *m.host_flag.as<int32_t>();
+        if (nf * 64 > n && m.coarse_level < 2)
+            m.coarse_level++;
+        if (nf > 0) {
+            // the flagged queries again, exactly, and their rows back into the tables
+            m.fallback_queries += (unsigned long long)nf;
+            m.fb_x.reserve((size_t)nf * d * sizeof(float));
+            m.fb_D.reserve((size_t)nf * kc * sizeof(float));
+            m.fb_I.reserve((size_t)nf * kc * sizeof(int64_t));
+            m.fb_p32.reserve((size_t)nf * kc * sizeof(int32_t));
+            const int32_t* fl = m.flag_list.as<int32_t>();
+            CUDA_CHECK(launch_gather_rows_w(xd, fl, nf, d, m.fb_x.p, st));
+            m.coarse_exact = true;
+            try {
+                run_coarse_(m.fb_x.as<float>(), nf, kc, out_ids32 ? m.fb_p32.as<int32_t>() : nullptr,
+                            out_ids64 ? m.fb_I.as<int64_t>() : nullptr, m.fb_D.as<float>(), st);
+            } catch (...) {
+                m.coarse_exact = false;
+                throw;
+            }
+            m.coarse_exact = false;
+            if (out_ids32)
+                CUDA_CHECK(launch_scatter_rows_w(m.fb_p32.p, fl, nf, kc, out_ids32, st));
+            if (out_ids64)
+                CUDA_CHECK(launch_scatter_rows_w(m.fb_I.p, fl, nf, 2 * kc, out_ids64, st));
+            if (out_dis)
+                CUDA_CHECK(launch_scatter_rows_w(m.fb_D.p, fl, nf, kc, out_dis, st));
+        }
+    }
 }
 
 // device-side search of one batch: coarse ids given -> results written to device D/I
@@ -850,9 +919,12 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
     const int kp_one = scan_tcr_kpart_one(m.nf4, (int)std::min<int64_t>(k, 1 << 20), one_margin);
     // ... and it needs enough work items to keep two CTAs per SM busy for several waves: the first
     // wave runs with cold pruning bounds and with every prologue at once, the last one half empty
-    // (C2 over 8 GPUs: 512 lists per rank = 3.3 waves took 0.43 ms against 0.33 ms for the
-    // queries-major kernel, and the counter read-back delayed the result gather by 0.08 ms)
-    const double est_items = std::min((double)nlists_owned, pairs_own) * std::ceil(avg_q / 64.0);
+    // (C2 over 8 / 4 GPUs: 512 / 1024 lists per rank = 3.3 / 6.6 waves took 0.43 / 0.59 ms against
+    // 0.33 / 0.57 ms for the queries-major kernel, and the counter read-back delayed the result
+    // gather by 0.08 ms; over 2 GPUs the one-MMA kernel wins, 0.875 ms)
+    // (a list probed by q queries makes ceil(q / 64) items: about q / 64 + 1/2 on average)
+    const double est_items =
+            std::min((double)nlists_owned, pairs_own) * std::max(1.0, avg_q / 64.0 + 0.5);
     const bool one_ok = m.tc_split == 1 && m.one_level < 2 && kp_one > 0 &&
             (est_items >= m.one_min_items || filtered || kp_q == 0);
     bool tcr = tc && (filtered || kp_q == 0 ||

@@ -283,6 +283,8 @@ cudaError_t launch_row_norms(const float4* slab, int64_t nrows, int nf4, float* 
 // flagged queries of a checked re-rank: rows idx[0..cnt) of a table of `words` 4-byte words per row
 cudaError_t launch_gather_rows_w(const void* in, const int32_t* idx, int64_t cnt, int words,
                                  void* out, cudaStream_t st);
+cudaError_t launch_scatter_rows_w(const void* in, const int32_t* idx, int64_t cnt, int words,
+                                  void* out, cudaStream_t st);
 cudaError_t launch_scatter_results(const float* Df, const int64_t* If, const int32_t* idx,
                                    int64_t cnt, int k, float* D, int64_t* I, cudaStream_t st);
 cudaError_t launch_fill_u32(uint32_t* p, int64_t n, uint32_t v, cudaStream_t st);

@@ -293,4 +293,23 @@ cudaError_t launch_scatter_results(const float* Df, const int64_t* If, const int
     return cudaGetLastError();
 }
 
+// rows of a dense table back to rows idx[0..cnt) of a larger one (`words` 4-byte words per row)
+__global__ void scatter_rows_w_kernel(const uint32_t* __restrict__ in, const int32_t* __restrict__ idx,
+                                      int64_t cnt, int W, uint32_t* __restrict__ out) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < cnt * W;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / W;
+        out[(int64_t)idx[r] * W + (i - r * W)] = in[i];
+    }
+}
+cudaError_t launch_scatter_rows_w(const void* in, const int32_t* idx, int64_t cnt, int words,
+                                  void* out, cudaStream_t st) {
+    if (cnt == 0)
+        return cudaSuccess;
+    scatter_rows_w_kernel<<<grid_for(cnt * words, 256), 256, 0, st>>>(
+            static_cast<const uint32_t*>(in), idx, cnt, words, static_cast<uint32_t*>(out));
+    count_launches(1);
+    return cudaGetLastError();
+}
+
 } // namespace b200ivf

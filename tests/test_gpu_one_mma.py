@@ -166,3 +166,31 @@ def test_one_mma_handle_adapts_to_crowded_data(cuda_device):
     first, later = redo[0], redo[2] - redo[1]
     assert first > nq // 64, redo          # the first batch paid for the narrow margin
     assert later <= first // 3, redo       # the handle widened it
+
+
+@pytest.mark.parametrize("metric", [L2, IP])
+@pytest.mark.parametrize("d,nlist,nprobe,nq", [
+    (128, 4096, 32, 3000),    # the rows-major kernel takes the centroid table above nprobe 24
+    (96, 8192, 64, 2000),
+    (64, 2048, 128, 1000),
+    (256, 1024, 8, 1500),     # d > 128: rows-major at any nprobe
+])
+def test_one_mma_coarse_quantizer_equals_simt(cuda_device, metric, d, nlist, nprobe, nq):
+    """K1 in the checked one-MMA form: probe ids and centroid distances identical to the SIMT
+    quantizer's (the flagged queries, if any, are quantized again exactly)."""
+    import hnsw_ivf_b200 as b2
+    rng = np.random.default_rng(21)
+    cent = rng.standard_normal((nlist, d)).astype(np.float32)
+    if metric == IP:
+        cent /= np.linalg.norm(cent, axis=1, keepdims=True)
+    xq = (cent[rng.integers(0, nlist, nq)] + 0.3 * rng.standard_normal((nq, d))).astype(np.float32)
+    g1 = _handle(d, nlist, metric, True)
+    gs = _handle(d, nlist, metric, False)
+    for g in (g1, gs):
+        g.set_centroids(cent)
+    n0 = b2.tensor_core_launches()
+    D1, I1 = g1.quantize(xq, nprobe)
+    assert b2.tensor_core_launches() > n0
+    Ds, Is = gs.quantize(xq, nprobe)
+    assert np.array_equal(I1, Is)
+    assert np.array_equal(D1, Ds)
