@@ -173,6 +173,7 @@ struct IndexIVFFlatB200::Impl {
     Buffer ymax2, flag_list, flag_count, host_flag, fb_x, fb_D, fb_I, fb_assign, fb_p32;
     Buffer cent_ymax2;                  // max |c|^2 over the centroid table (one-MMA coarse scan)
     int coarse_level = 0;               // as one_level, for the coarse quantizer
+    int64_t coarse_one_min_nlist = 16384; // "coarse_one_min_nlist"
     bool coarse_exact = false;          // the second, exact pass of a checked coarse scan is running
     // "tc_split" / B200IVF_TC_SPLIT: 1 = one MMA per k-step + checked re-rank (default),
     // 3 = the 3xTF32 split with a fixed re-rank margin (A/B runs)
@@ -595,7 +596,11 @@ void IndexIVFFlatB200::run_coarse_(const float* xd, int64_t n, int kc, int32_t* 
     // back).
     const int c_margin = m.coarse_level == 0 ? m.one_margin : std::max(m.one_margin, 16);
     const int kp_one = scan_tcr_kpart_one(nf4, kc, c_margin);
-    bool one = tcr && m.tc_split == 1 && m.coarse_level < 2 && kp_one > 0 && n >= 256;
+    // (long tables only: over the 32768 centroids of a C4 shard it takes the nprobe 64 scan from 4.3
+    // to 3.2 ms; over C2's 4096 an item is a handful of tiles and the smaller query tiles of the
+    // two-CTA shape cost more than the MMAs they save, 0.9 against 0.72 ms at nprobe 32)
+    bool one = tcr && m.tc_split == 1 && m.coarse_level < 2 && kp_one > 0 && n >= 256 &&
+            (int64_t)nlist >= m.coarse_one_min_nlist;
     if (one) {
         cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
         if (cudaStreamIsCapturing(st, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone)
@@ -1534,6 +1539,8 @@ void IndexIVFFlatB200::set_option(const char* name, double value) {
         m.tc_split = value == 1 ? 1 : 3;
         m.one_level = 0;
     }
+    else if (n == "coarse_one_min_nlist")
+        m.coarse_one_min_nlist = (int64_t)value;
     else if (n == "one_min_items")
         m.one_min_items = value;
     else if (n == "one_max_avg_q")
