@@ -172,6 +172,7 @@ struct IndexIVFFlatB200::Impl {
     // the scratch of their second, exact pass
     Buffer ymax2, flag_list, flag_count, host_flag, fb_x, fb_D, fb_I, fb_assign, fb_p32;
     Buffer cent_ymax2;                  // max |c|^2 over the centroid table (one-MMA coarse scan)
+    Buffer pair_len, pair_blk0;         // pair-major plan (small batches): the "list" tables
     int coarse_level = 0;               // as one_level, for the coarse quantizer
     int64_t coarse_one_min_nlist = 16384; // "coarse_one_min_nlist"
     bool coarse_exact = false;          // the second, exact pass of a checked coarse scan is running
@@ -276,6 +277,7 @@ struct IndexIVFFlatB200::Impl {
     };
     std::map<std::array<int64_t, 4>, GraphEntry> graphs;
     bool use_graph = true;
+    bool use_pair_plan = true; // "use_pair_plan": pair-major plan for small batches (A/B runs)
     // average queries per probed list at or below which the SIMT warp kernel takes the whole scan
     // (B200IVF_SIMT_MAXQ, A/B runs)
     double simt_max_avg_q = 2.0;
@@ -1018,13 +1020,23 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
                     want_pq ? m.query_ndis.as<unsigned long long>() : nullptr, st));
         }
         // stage 2: invert the probe table, scan the lists
+        // small batches: pair-major plan (every pair its own work-item group: nothing to share
+        // between a handful of queries, and no pass over the nlist per-list counters)
+        const bool pair_major = simt_only && !filtered && bp.cfg.rq == 1 && pairs <= 4096 &&
+                m.use_pair_plan;
+        const size_t nl_plan = pair_major ? (size_t)pairs : nlist;
         m.count.reserve(nlist * sizeof(int32_t));
         m.fill.reserve(nlist * sizeof(int32_t));
-        m.grp_start.reserve((nlist + 1) * sizeof(int32_t));
-        m.item_off.reserve((nlist + 1) * sizeof(uint32_t));
+        m.grp_start.reserve((std::max<size_t>(nlist, 4096) + 1) * sizeof(int32_t));
+        m.item_off.reserve((std::max<size_t>(nlist, 4096) + 1) * sizeof(uint32_t));
         m.item_off_tile.reserve((nlist + 1) * sizeof(uint32_t));
+        if (pair_major) {
+            m.pair_len.reserve(4096 * sizeof(int32_t));
+            m.pair_blk0.reserve(4096 * sizeof(uint32_t));
+        }
+        (void)nl_plan;
         TileCfg tcfg = choose_tile_cfg(m.nf4, (int)kp);
-        if (tc || filtered)
+        if (tc || filtered || pair_major)
             tcfg.ok = false; // the tensor-core kernel takes the many-query lists instead (and a
                              // filtered search stays in the warp kernel, which knows the mask)
         m.pair_query.reserve((size_t)pairs * sizeof(int32_t));
@@ -1067,6 +1079,11 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
             pa.item_list_tile = m.item_list.as<int32_t>();
         }
         pa.stats = count_stats ? dstats : nullptr;
+        if (pair_major) {
+            pa.vlen = m.pair_len.as<int32_t>();
+            pa.vblk0 = m.pair_blk0.as<uint32_t>();
+            pa.list_blk0 = m.list_blk0.as<uint32_t>() + m.list_lo;
+        }
         if (mc > 0) {
             pa.limit_qp = m.limit_qp.as<int32_t>();
             pa.limit_slot = m.limit_slot.as<int32_t>();
@@ -1082,6 +1099,11 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
         sa.pair_query = pa.pair_query;
         sa.item_off = pa.item_off;
         sa.nlists = (int)nlists_owned;
+        if (pair_major) { // the pairs are the lists
+            sa.list_blk0 = m.pair_blk0.as<uint32_t>();
+            sa.list_len = m.pair_len.as<int32_t>();
+            sa.nlists = (int)pairs;
+        }
         sa.nsplit = (int)bp.S;
         sa.k = (int)kp;
         sa.cap = bp.cfg.cap;
@@ -1092,8 +1114,9 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
         sa.part_mul = pmul;
         sa.row_mask = row_mask;
         sa.pair_limit = mc > 0 ? m.limit_slot.as<int32_t>() : nullptr;
-        const int64_t max_items =
-                (ceil_div(pairs, bp.cfg.rq) + std::min<int64_t>(pairs, nlists_owned)) * bp.S;
+        const int64_t max_items = pair_major
+                ? pairs * bp.S
+                : (ceil_div(pairs, bp.cfg.rq) + std::min<int64_t>(pairs, nlists_owned)) * bp.S;
         if (!tcr) // (every probed list goes to the rows-major tensor-core kernel otherwise)
             CUDA_CHECK(launch_ivf_scan(metric_type, bp.cfg.rq, bp.cfg.wpc, (uint32_t)max_items, sa,
                                        st, bp.cfg.rv));
@@ -1557,6 +1580,8 @@ void IndexIVFFlatB200::set_option(const char* name, double value) {
         m.tc_mode = (int)value;
     else if (n == "use_tc")
         m.use_tc = value != 0;
+    else if (n == "use_pair_plan")
+        m.use_pair_plan = value != 0;
     else if (n == "use_graph")
         m.use_graph = value != 0;
     else if (n == "scan_nsplit") // timing experiments; process-wide

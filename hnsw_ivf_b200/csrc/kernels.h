@@ -178,6 +178,15 @@ struct PlanArgs {
     // re-ordered by pair slot for the scan (both nullptr: every probed list counts whole)
     const int32_t* limit_qp = nullptr; // [n][nprobe]
     int32_t* limit_slot = nullptr;     // [n*nprobe] out
+    // Pair-major plan (small batches): every (query, probe) pair becomes a "list" of its own -- pair
+    // i at index i, one query each, nsplit items -- described by vlen / vblk0 (length and first
+    // block of the probed list, 0 rows for a skipped probe). One launch, no per-list counters, no
+    // prefix scan over nlist entries (38 us of a 120 us batch-1 search at nlist = 16384); the scan
+    // is then given nlists = n * nprobe and these two arrays as its list tables. grp_start and
+    // item_off must hold n * nprobe + 1 entries. Needs rq == 1, no tiling, no limits.
+    int32_t* vlen = nullptr;           // [n*nprobe] out; non-null selects this plan
+    uint32_t* vblk0 = nullptr;         // [n*nprobe] out
+    const uint32_t* list_blk0 = nullptr; // [nlists] (pair-major plan only)
 };
 // max_codes walk of IndexIVF::search_preassigned (faiss/IndexIVF.cpp:597-631): writes the rows
 // that count per (query, probe) (limit_qp, may be nullptr), turns the probes after the stop into

@@ -211,6 +211,55 @@ __global__ void probe_limits_kernel(int32_t* coarse_ids, int n, int nprobe, int 
     }
 }
 
+// pair-major plan: see PlanArgs::vlen
+__global__ void plan_pairs_kernel(const PlanArgs a) {
+    const int total = a.n * a.nprobe;
+    unsigned long long ndis = 0, nvis = 0, bad = 0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        int l = a.coarse_ids[i];
+        int len = 0;
+        uint32_t blk0 = 0;
+        if (l >= (a.nlist_total ? a.nlist_total : a.nlists)) {
+            bad++;
+        } else if (l >= 0) {
+            l -= a.list_lo;
+            if (l >= 0 && l < a.nlists) { // (else: another shard's list)
+                len = a.list_len[l];
+                blk0 = a.list_blk0[l];
+            }
+        }
+        a.vlen[i] = len;
+        a.vblk0[i] = blk0;
+        a.grp_start[i] = i;
+        a.item_off[i] = (uint32_t)i * (uint32_t)a.nsplit;
+        a.pair_query[i] = i / a.nprobe;
+        a.slot_of[i] = len > 0 ? i : -1;
+        if (len > 0) {
+            ndis += (unsigned long long)len;
+            nvis++;
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        ndis += __shfl_down_sync(0xffffffffu, ndis, o);
+        nvis += __shfl_down_sync(0xffffffffu, nvis, o);
+        bad += __shfl_down_sync(0xffffffffu, bad, o);
+    }
+    if ((threadIdx.x & 31) == 0 && a.stats) {
+        if (nvis)
+            atomicAdd(&a.stats[1], nvis);
+        if (ndis)
+            atomicAdd(&a.stats[2], ndis);
+        if (bad)
+            atomicAdd(&a.stats[3], bad);
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        a.grp_start[total] = total;
+        a.item_off[total] = (uint32_t)total * (uint32_t)a.nsplit;
+        if (a.stats)
+            atomicAdd(&a.stats[0], (unsigned long long)a.n);
+    }
+}
+
 __global__ void plan_single_kernel(int32_t* grp_start, uint32_t* item_off, int n, uint32_t items) {
     grp_start[0] = 0;
     grp_start[1] = n;
@@ -241,6 +290,14 @@ cudaError_t launch_probe_limits(int32_t* coarse_ids, int n, int nprobe, int nlis
 
 cudaError_t launch_plan(const PlanArgs& a, cudaStream_t st) {
     cudaError_t e;
+    if (a.vlen) { // pair-major: one launch
+        const int total = a.n * a.nprobe;
+        if (total == 0 || a.rq != 1 || a.tile_tq != 0 || a.limit_qp || !a.vblk0 || !a.list_blk0)
+            return total == 0 ? cudaSuccess : cudaErrorInvalidValue;
+        plan_pairs_kernel<<<(total + 255) / 256, 256, 0, st>>>(a);
+        count_launches(1);
+        return cudaGetLastError();
+    }
     if ((e = cudaMemsetAsync(a.count, 0, sizeof(int32_t) * a.nlists, st)) != cudaSuccess)
         return e;
     if ((e = cudaMemsetAsync(a.fill, 0, sizeof(int32_t) * a.nlists, st)) != cudaSuccess)
