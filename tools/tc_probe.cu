@@ -60,18 +60,6 @@ __device__ __forceinline__ void issue_rows_major(int reps, int per, int nn, uint
                 for (int ks = 0; ks < BLK; ++ks) {
                     const uint64_t kh = dhi + (uint64_t)(ks * ((2 * LBO) >> 4));
                     const uint64_t kl = dlo + (uint64_t)(ks * ((2 * LBO) >> 4));
-                    if (per == 5) { // the queries-major triple: operands shared between neighbours
-                        mma_tf32_ts(tDb, tAlo + (g * BLK + ks) * 8, kh, idesc, 1);
-                        mma_tf32_ts(tDb, tAlo + 128 + (g * BLK + ks) * 8, kl, idesc, 1);
-                        mma_tf32_ts(tDb, tAlo + 128 + (g * BLK + ks) * 8, kh, idesc, 1);
-                        continue;
-                    }
-                    if (per == 6) { // three TS MMAs, all operands fresh
-                        mma_tf32_ts(tDb, tAlo + (g * BLK + ks) * 8, kh, idesc, 1);
-                        mma_tf32_ts(tDb, tAlo + 128 + (g * BLK + ks) * 8, kl, idesc, 1);
-                        mma_tf32_ts(tDb, tAlo + ((g * BLK + ks + 1) & 15) * 8, kh + 256, idesc, 1);
-                        continue;
-                    }
                     if (per != 4)
                         mma_tf32_ss(tDb, kh, kl, per == 3 ? id2 : idesc, 1);
                     if (per != 1)
@@ -79,8 +67,7 @@ __device__ __forceinline__ void issue_rows_major(int reps, int per, int nn, uint
                 }
                 if (commits) {
                     mma_commit(&bars[2]);
-                    if (!(per & 0x40))
-                        mma_commit(&bars[3]);
+                    mma_commit(&bars[3]);
                 }
             }
             if (!lane0_loop)
@@ -408,7 +395,7 @@ int main() {
     long long* dC;
     CK(cudaMalloc(&dC, 16 * 148));
     for (int grid : {1, 148})
-        for (int nm : {(4 << 24) | (16 << 16) | 0x8001, (4 << 24) | (64 << 16) | 0x8001, (4 << 24) | (128 << 16) | 0x8001, (4 << 24) | (16 << 16) | 0x8004, (4 << 24) | (64 << 16) | 0x8004, (4 << 24) | (128 << 16) | 0x8004, (4 << 24) | (16 << 16) | 0x8005, (4 << 24) | (64 << 16) | 0x8005, (4 << 24) | (128 << 16) | 0x8005, (4 << 24) | (16 << 16) | 0x8006, (4 << 24) | (64 << 16) | 0x8006, (4 << 24) | (128 << 16) | 0x8006, (4 << 24) | (16 << 16) | 0x8201, (4 << 24) | (64 << 16) | 0x8201, (4 << 24) | (128 << 16) | 0x8201, (4 << 24) | (16 << 16) | 0x8204, (4 << 24) | (64 << 16) | 0x8204, (4 << 24) | (128 << 16) | 0x8204, (4 << 24) | (16 << 16) | 0x8205, (4 << 24) | (64 << 16) | 0x8205, (4 << 24) | (128 << 16) | 0x8205, (4 << 24) | (16 << 16) | 0x8206, (4 << 24) | (64 << 16) | 0x8206, (4 << 24) | (128 << 16) | 0x8206, (16 << 24) | (16 << 16) | 0x8001, (16 << 24) | (64 << 16) | 0x8001, (16 << 24) | (128 << 16) | 0x8001, (16 << 24) | (16 << 16) | 0x8004, (16 << 24) | (64 << 16) | 0x8004, (16 << 24) | (128 << 16) | 0x8004, (16 << 24) | (16 << 16) | 0x8005, (16 << 24) | (64 << 16) | 0x8005, (16 << 24) | (128 << 16) | 0x8005, (16 << 24) | (16 << 16) | 0x8006, (16 << 24) | (64 << 16) | 0x8006, (16 << 24) | (128 << 16) | 0x8006, (16 << 24) | (16 << 16) | 0x8201, (16 << 24) | (64 << 16) | 0x8201, (16 << 24) | (128 << 16) | 0x8201, (16 << 24) | (16 << 16) | 0x8204, (16 << 24) | (64 << 16) | 0x8204, (16 << 24) | (128 << 16) | 0x8204, (16 << 24) | (16 << 16) | 0x8205, (16 << 24) | (64 << 16) | 0x8205, (16 << 24) | (128 << 16) | 0x8205, (16 << 24) | (16 << 16) | 0x8206, (16 << 24) | (64 << 16) | 0x8206, (16 << 24) | (128 << 16) | 0x8206,
+        for (int nm : {(4 << 24) | (16 << 16) | 0x8201, (4 << 24) | (64 << 16) | 0x8201, (4 << 24) | (128 << 16) | 0x8201, (4 << 24) | (16 << 16) | 0x8204, (4 << 24) | (64 << 16) | 0x8204, (4 << 24) | (128 << 16) | 0x8204, (4 << 24) | (16 << 16) | 0x8202, (4 << 24) | (64 << 16) | 0x8202, (4 << 24) | (128 << 16) | 0x8202, (4 << 24) | (16 << 16) | 0x8203, (4 << 24) | (64 << 16) | 0x8203, (4 << 24) | (128 << 16) | 0x8203, (16 << 24) | (16 << 16) | 0x8201, (16 << 24) | (64 << 16) | 0x8201, (16 << 24) | (128 << 16) | 0x8201, (16 << 24) | (16 << 16) | 0x8204, (16 << 24) | (64 << 16) | 0x8204, (16 << 24) | (128 << 16) | 0x8204, (16 << 24) | (16 << 16) | 0x8202, (16 << 24) | (64 << 16) | 0x8202, (16 << 24) | (128 << 16) | 0x8202, (16 << 24) | (16 << 16) | 0x8203, (16 << 24) | (64 << 16) | 0x8203, (16 << 24) | (128 << 16) | 0x8203,
                        3, 0x403, 0x603, (128 << 16) | 0x403, (96 << 16) | 0x403, (48 << 16) | 0x403,
                        (16 << 16) | 0x403, (96 << 16) | 0x2403, (48 << 16) | 0x2403,
                        (16 << 16) | 0x2403, (128 << 16) | 0x4603, (96 << 16) | 0x4603, (64 << 16) | 0x4603, (48 << 16) | 0x4603,
@@ -420,7 +407,7 @@ int main() {
             std::vector<long long> hc(2 * grid);
             CK(cudaMemcpy(hc.data(), dC, 16 * grid, cudaMemcpyDeviceToHost));
             const int pp = nm & 0xff;
-            const int per_k = (nm & 0x8000) ? (pp == 1 || pp == 4 ? 1 : (pp >= 5 ? 3 : 2)) : pp;
+            const int per_k = (nm & 0x8000) ? (pp == 1 || pp == 4 ? 1 : 2) : pp;
             if (grid == 148)
                 continue;
             const int nmma = reps * (K / 8) * per_k;
