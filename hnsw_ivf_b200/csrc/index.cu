@@ -600,9 +600,11 @@ void IndexIVFFlatB200::run_coarse_(const float* xd, int64_t n, int kc, int32_t* 
     const int kp_one = scan_tcr_kpart_one(nf4, kc, c_margin);
     // (long tables only: over the 32768 centroids of a C4 shard it takes the nprobe 64 scan from 4.3
     // to 3.2 ms; over C2's 4096 an item is a handful of tiles and the smaller query tiles of the
-    // two-CTA shape cost more than the MMAs they save, 0.9 against 0.72 ms at nprobe 32)
+    // two-CTA shape cost more than the MMAs they save, 0.9 against 0.72 ms at nprobe 32). Above
+    // d = 128 always: there the query operand is what limits the queries per item, and x_hi alone
+    // is half of it (C3, d = 960, nprobe 16: 0.87 -> 0.54 ms)
     bool one = tcr && m.tc_split == 1 && m.coarse_level < 2 && kp_one > 0 && n >= 256 &&
-            (int64_t)nlist >= m.coarse_one_min_nlist;
+            ((int64_t)nlist >= m.coarse_one_min_nlist || nf4 > 32);
     if (one) {
         cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
         if (cudaStreamIsCapturing(st, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone)
