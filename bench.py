@@ -978,7 +978,8 @@ def bench_c4(args, ctx, tf32_peak, headline):
         ms_e2e = h0.elapsed_time(h1)
 
     mine = {"scan_ms": stage["scan"], "unique_rows": unique_rows, "ndis": ndis,
-            "launches": float(launches), "stage": stage, "rows": int(g.list_sizes().sum())}
+            "launches": float(launches), "stage": stage, "rows": int(g.list_sizes().sum()),
+            "redo": int(g.exact_redo_count())}
     if world > 1:
         tt = torch.tensor([ms, ms_e2e], dtype=torch.float64, device=dev)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
@@ -1033,6 +1034,9 @@ def bench_c4(args, ctx, tf32_peak, headline):
                      "useful_tflops": coarse_flops / (coarse_ms / 1e3) / 1e12 if coarse_ms > 0 else 0,
                      "tf32_peak_tflops": tf32_peak},
           "gpu_launches": int(sum(r["launches"] for r in per_rank)),
+          # queries searched a second time on the exact kernel (unproven by the checked re-rank),
+          # all ranks, over every search of the C4 index (sweep, warm-up, timed steps)
+          "exact_redo_queries": int(sum(r["redo"] for r in per_rank)),
           "slice": sl, "total_s": round(time.perf_counter() - t_all, 1)}
     if not headline:
         return c4

@@ -239,6 +239,7 @@ def regime_c4s(args, torch, b2, dev):
                "queries_per_probed_list": ndis / max(ur, 1),
                "scan_gbs": ur * w["d"] * 4.0 / (scan * 1e-3) / 1e9,
                "scan_frac_of_hbm_peak": ur * w["d"] * 4.0 / (scan * 1e-3) / 1e9 / peak,
+               "exact_redo_total": g.exact_redo_count(),
                "build": tb}
         print(json.dumps(out), flush=True)
 
