@@ -220,4 +220,60 @@ struct IndexIVFFlat {
     };
 };
 
+// ---- one rank of the list-sharded index: faiss::IndexShardsIVF (faiss/IndexShardsIVF.h:21-44) with
+// one process per GPU instead of one thread per shard. Every method is collective over the ranks
+// that share `nccl_unique_id` (rank 0 makes it with nccl_unique_id() and hands the 128 bytes to the
+// others by whatever channel the application has).
+inline void nccl_unique_id(unsigned char (&out)[B200_NCCL_UNIQUE_ID_BYTES]) {
+    check(b200_nccl_get_unique_id(out));
+}
+
+struct IndexShardsIVFFlat {
+    B200IndexShardsIVFFlat* h = nullptr;
+    size_t nprobe = 1;
+
+    IndexShardsIVFFlat(size_t d, size_t nlist, MetricType metric, int device, int rank, int world,
+                       const void* nccl_unique_id128) {
+        check(b200_IndexShardsIVFFlat_new(&h, d, nlist, (B200MetricType)metric, device, rank, world,
+                                          nccl_unique_id128));
+    }
+    IndexShardsIVFFlat(const IndexShardsIVFFlat&) = delete;
+    IndexShardsIVFFlat& operator=(const IndexShardsIVFFlat&) = delete;
+    ~IndexShardsIVFFlat() {
+        b200_IndexShardsIVFFlat_free(h);
+    }
+    int rank() const {
+        return b200_IndexShardsIVFFlat_rank(h);
+    }
+    int world() const {
+        return b200_IndexShardsIVFFlat_world(h);
+    }
+    idx_t ntotal() const {
+        return b200_IndexShardsIVFFlat_ntotal(h);
+    }
+    // IndexShards::at (faiss/IndexShards.h): this rank's shard, borrowed (options, stats, lists)
+    B200IndexIVFFlat* local() const {
+        return b200_IndexShardsIVFFlat_local(h);
+    }
+    void train(idx_t n, const float* x, int root = 0) {
+        check(b200_IndexShardsIVFFlat_train(h, n, x, root));
+    }
+    void set_centroids(const float* centroids, int root = -1) {
+        check(b200_IndexShardsIVFFlat_set_centroids(h, centroids, root));
+    }
+    // each rank brings ITS OWN vectors; they travel to the rank that owns their list
+    void add_with_ids(idx_t n, const float* x, const idx_t* xids) {
+        check(b200_IndexShardsIVFFlat_add_with_ids(h, n, x, xids));
+    }
+    // root < 0: every rank passes the same queries; root >= 0: rank root's are broadcast
+    void search(idx_t n, const float* x, idx_t k, float* distances, idx_t* labels,
+                int root = -1) const {
+        b200_IndexIVFFlat_set_nprobe(b200_IndexShardsIVFFlat_local(h), nprobe);
+        check(b200_IndexShardsIVFFlat_search(h, n, x, k, distances, labels, root));
+    }
+    void synchronize() const {
+        check(b200_IndexShardsIVFFlat_synchronize(h));
+    }
+};
+
 } // namespace b200

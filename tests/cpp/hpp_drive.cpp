@@ -51,6 +51,25 @@ int main(int argc, char** argv) {
         fclose(o);
         printf("OK ntotal=%lld trained=%d results=%zu\n", (long long)index.ntotal(),
                (int)index.is_trained(), res.labels.size());
+        // the sharded face with a world of one rank (no NCCL needed): same vectors, same result
+        {
+            b200::IndexShardsIVFFlat sh(d, nlist, (b200::MetricType)hd[6], 0, 0, 1, nullptr);
+            sh.set_centroids(cent.data());
+            std::vector<b200::idx_t> ids(nb);
+            for (int64_t i = 0; i < nb; ++i)
+                ids[i] = i;
+            sh.add_with_ids(nb, xb.data(), ids.data());
+            sh.nprobe = nprobe;
+            std::vector<float> D2(nq * k);
+            std::vector<b200::idx_t> I2(nq * k);
+            sh.search(nq, xq.data(), k, D2.data(), I2.data());
+            sh.synchronize();
+            if (I2 != I || D2 != D || sh.ntotal() != nb || sh.world() != 1) {
+                printf("SHARDED_MISMATCH\n");
+                return 1;
+            }
+            printf("SHARDED_OK\n");
+        }
         // error path: k = 0 must throw with the reference's message shape (faiss/IndexIVF.cpp:310)
         try {
             index.search(nq, xq.data(), 0, D.data(), I.data());
