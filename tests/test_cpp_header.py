@@ -69,6 +69,7 @@ def test_header_results_equal_ctypes(cuda_device, tmp_path, metric):
                        capture_output=True, text=True)
     assert r.returncode == 0 and "OK ntotal=%d trained=1" % nb in r.stdout, r.stdout + r.stderr
     assert "THROWS code=-2" in r.stdout and "k > 0" in r.stdout
+    assert "SHARDED_OK" in r.stdout, r.stdout  # b200::IndexShardsIVFFlat, world of one rank
     buf = open(tmp_path / "out.bin", "rb").read()
     off = 0
 
