@@ -617,6 +617,8 @@ void IndexIVFFlatB200::run_coarse_(const float* xd, int64_t n, int kc, int32_t* 
         const int small = scan_tcr_tq_small(nf4, kp, true);
         if (small > 0)
             tcr_tq = small;
+        if (m.coarse_tq > 0) // tuning experiments
+            tcr_tq = std::max(16, std::min(m.coarse_tq, scan_tcr_tq(nf4, kp, true)) & ~15);
     }
     if (tcr && !one && m.coarse_tq > 0) { // tuning experiments
         const int small = scan_tcr_tq_small(nf4, kp);
