@@ -311,7 +311,7 @@ def parity_detail(D_ref, I_ref, D_new, I_new):
 
 
 def scan_kernel_name(avg_q, d, k, simt_max=2.0, tcr_max=48.0, one_max=72.0, level=0,
-                     lists_probed=1e9, one_min_items=2368.0):
+                     lists_probed=1e9, one_min_items=2368.0, rows_per_list=1024.0):
     """the list-scan kernel the library's plan picks (csrc/index.cu search_impl_) for this shape;
     level: the handle's one-MMA level (0 / 1: one MMA + checked re-rank, 2: 3xTF32)"""
     if avg_q <= simt_max:
@@ -319,6 +319,7 @@ def scan_kernel_name(avg_q, d, k, simt_max=2.0, tcr_max=48.0, one_max=72.0, leve
     margin = max(6 if level == 0 else 16, k // 4)
     one = (level < 2 and k + margin <= 256 and
            (lists_probed * max(1.0, avg_q / 64.0 + 0.5) >= one_min_items or d > 128 or k > 24))
+    one_max = one_max * max(1.0, rows_per_list / 1024.0) ** 3
     if one and (d > 128 or k > 24 or avg_q < max(tcr_max, one_max)):
         return ("ivf_scan_tcr_kernel<ONE> (rows-major tcgen05, ONE tf32 MMA per k-step as a filter with "
                 "a proven error bound + checked exact re-rank, <= 64 queries per item)")
@@ -647,7 +648,7 @@ def bench_flat(args, ctx, tf32_peak):
     traffic = scan_traffic_bytes(args.workload, nprobe) if world == 1 else None
     useful_tflops = 2.0 * d * slow["ndis"] / scan_s / 1e12 if scan_s > 0 else 0.0
     avg_q = ndis_all / max(rows_all, 1)
-    kname = scan_kernel_name(avg_q, d, k,
+    kname = scan_kernel_name(avg_q, d, k, rows_per_list=w["nb"] / float(nlist),
                              lists_probed=min(nlist / float(world), nq * nprobe / float(world)))
     coarse_s = (phase["coarse"] if phase else stage["coarse"]) / 1e3
     coarse_flops = 2.0 * (nq / float(world)) * nlist * d  # this rank's query slice

@@ -938,11 +938,19 @@ void IndexIVFFlatB200::search_impl_(int64_t n, const float* x, int64_t k, const 
             std::min((double)nlists_owned, pairs_own) * std::max(1.0, avg_q / 64.0 + 0.5);
     const bool one_ok = m.tc_split == 1 && m.one_level < 2 && kp_one > 0 &&
             (est_items >= m.one_min_items || filtered || kp_q == 0);
+    // Against the queries-major 3xTF32 kernel the one-MMA kernel wins by more the longer the
+    // lists are (its per-item costs amortise over more tiles): C1, 977 rows per list, loses above
+    // ~72 queries per list (0.46 against 0.35 ms at 80); C2, 2441 rows per list, wins at every
+    // count measured (82 / 123 / 163 / 244 per list: 1.67 / 2.15 / 2.62 / 3.53 ms against 1.99 /
+    // 2.36 / 2.96 / 3.99)
+    const double rows_per_list = (double)m.nstored / (double)std::max<int64_t>(1, nlists_owned);
+    const double rl = std::max(1.0, rows_per_list / 1024.0);
+    const double one_cap = m.one_max_avg_q * rl * rl * rl;
     bool tcr = tc && (filtered || kp_q == 0 ||
                       ((kp_r > 0 || one_ok) &&
                        (m.tc_mode == 2 ||
                         (m.tc_mode == 0 &&
-                         avg_q < (one_ok ? std::max(m.one_max_avg_q, m.tcr_max_avg_q)
+                         avg_q < (one_ok ? std::max(one_cap, m.tcr_max_avg_q)
                                          : m.tcr_max_avg_q)))));
     if (tcr && kp_r == 0 && !one_ok) // (filtered, k beyond what the rows-major kernel keeps)
         tcr = false, tc = false, simt_only = true;
