@@ -166,7 +166,11 @@ int b200_IndexIVFFlat_synchronize(const B200IndexIVFFlat* index);
  * scan), "tc_mode" (0 auto, 1 queries-major, 2 rows-major), "use_tc", "use_graph", "tc_split" (1 =
  * one tf32 product per 8 dimensions + checked re-rank, the default; 3 = 3xTF32 with a fixed re-rank
  * margin), "one_margin" (spare candidates kept per partial list in that mode, default 6),
- * "one_max_avg_q" (queries per probed list up to which that kernel is preferred). They change
+ * "one_max_avg_q" (queries per probed list up to which that kernel is preferred, for 1024-row
+ * lists; the cap grows with the cube of the list length), "one_min_items" (work items a search must
+ * have for that kernel: 8 waves of CTAs by default), "coarse_one_min_nlist" (centroid tables at
+ * least this long are scanned in the same checked form above nprobe 24), "use_pair_plan" (small
+ * batches: one plan launch per search instead of three). They change
  * which kernels run, never the results. Also here, for want of a struct accessor in a C API: the
  * quantizer's ClusteringParameters as IndexIVF exposes them (index.cp, faiss/IndexIVF.h:39-41,
  * faiss/Clustering.h:23-64): "cp_niter", "cp_max_points_per_centroid", "cp_seed" -- read by train.
