@@ -119,8 +119,11 @@ struct TcScanArgs {
     unsigned long long* trap = nullptr; // host-mapped note of a wait that gave up (tc_trap_info_*)
     long long* trace = nullptr; // timing experiments only (B200IVF_TC_TRACE=<item>): clock64
     uint32_t trace_item = 0;    // stamps of one CTA, [role][tile]
-    int dbg = 0;                // timing experiments only (B200IVF_TC_DBG): 1 = epilogue drops
-                                // every score, 2 = no MMAs issued, 4 = split warps do not compute
+    int dbg = 0;                // timing experiments only (B200IVF_TC_DBG / "tc_dbg"; results are
+                                // wrong while a bit is set): 1 = the epilogue drops every score,
+                                // 4 = split warps do not convert, 8 = no MMAs (rows-major one-MMA
+                                // form) / stages recycled without loads (queries-major), 16 = no
+                                // TMA loads (rows-major), 32 = no query-tile prologue loads
 };
 constexpr int kTcStages = 9;
 // entries per partial list the tensor-core scan keeps for a request of k: 16 for k <= 12, 32 for
