@@ -11,10 +11,18 @@
 //   D[128 rows x N] (TMEM, two buffers) += A[128 rows x 8] (TMEM) * B[N x 8]^T (smem)
 // The list rows are the M side of the MMA and the queries the N side, because the time of a
 // tcgen05.mma is max(M,128) * N / 256 cycles: N follows the number of queries that really probe the
-// list (rounded up to 16), M = 128 costs the same whether it is full or not -- and an MMA whose A
-// operand sits in tensor memory costs ~60 cycles whatever N is (the 4 KB of A are read at 64 B per
-// cycle), so the number of MMAs per 8 dimensions is what sets the tensor-pipe
-// time of a tile. The 3xTF32 product x.y = xh.yh + xl.yh + xh.yl therefore takes TWO MMAs, not three:
+// list (rounded up to 16), M = 128 costs the same whether it is full or not. What the issuing lane
+// executes per MMA matters as much as the pipe time at these small N (round 1
+// mistook an issue-bound loop for "an A-in-TMEM MMA costs ~60 cycles whatever N is"), so the MMA
+// role issues straight-line blocks and the number of MMAs per 8 dimensions is kept down.
+//
+// TWO forms, chosen at compile time (template parameter ONE):
+//  ONE (the default list scan): a single MMA per 8 dimensions, tf32_rn(x) . trunc_tf32(y) -- A
+//  straight from the TMA stage, B = x_hi alone, no split warps, no lo ring. The scores are then a
+//  FILTER with a known error bound; select.cu re-scores what could matter exactly and proves the
+//  rest away (kernels.h, SelectArgs::err_coef). 4 epilogue warps + TMA + MMA warp, <= 64 queries
+//  per item, two CTAs per SM.
+//  3xTF32 (coarse quantizer; handles that fell back): x.y = xh.yh + xl.yh + xh.yl in TWO MMAs:
 //  * B: the query tile, scaled by -1 (inner product) or -2 (L2), split into tf32 hi / lo parts and
 //    STACKED along N: rows 0..n16-1 of the operand are x_hi, rows n16..2*n16-1 are x_lo (K-major
 //    no-swizzle canonical layout: 8 rows x 16 bytes = one core matrix, SBO = 128 B, LBO =
